@@ -1,0 +1,206 @@
+/*
+ * nsof.h -- C ABI of libnsof: the B200 (sm_100a) implementation of the ROI-gated Farneback
+ * hot path of RTCartist/Neuromorphic-Spatiotemporal-Optical-Flow.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns an int status
+ * (0 = ok, negative = error, text via nsof_last_error()) and never throws.  Citations
+ * (file:line) are relative to the reference repository and name the interface each entry point
+ * replaces.  There is no CPU fallback: without a CUDA device nsof_create() fails.
+ *
+ * Threading: one handle per (GPU, stream).  Calls on one handle are serialised by the caller.
+ * "_host" entry points take host pointers, copy in/out and synchronise; the others take device
+ * pointers, enqueue on `cuda_stream` (a cudaStream_t passed as void*) and return.
+ */
+#ifndef NSOF_H
+#define NSOF_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define NSOF_API __declspec(dllexport)
+#else
+#define NSOF_API __attribute__((visibility("default")))
+#endif
+
+#define NSOF_OK 0
+#define NSOF_ERR_BAD_ARG (-1)     /* what cv2 reports as cv2.error -215 (empty input, size mismatch, pyr_scale >= 1) */
+#define NSOF_ERR_UNSUPPORTED (-2) /* legal for OpenCV but outside this library (flags != 0, poly_n > 31, ...) */
+#define NSOF_ERR_CUDA (-3)
+#define NSOF_ERR_NOMEM (-4)
+
+typedef struct nsof_handle nsof_handle;
+
+/* The kwargs of `farneback_params` (optical_flow_seg.py:73-81), same names and meaning as
+ * cv2.calcOpticalFlowFarneback(prev, next, flow, pyr_scale, levels, winsize, iterations, poly_n,
+ * poly_sigma, flags).  poly_n is the radius of the (2*poly_n+1)^2 fit window, as in OpenCV. */
+typedef struct nsof_fb_params {
+    double pyr_scale;
+    int levels;
+    int winsize;
+    int iterations;
+    int poly_n;
+    double poly_sigma;
+    int flags; /* only 0 is implemented; the reference never passes anything else */
+} nsof_fb_params;
+
+/* One crop pair = one independent Farneback problem (the `prev_region` / `next_region` views of
+ * optical_flow_seg.py:186-187).  Pointers address the first pixel of the crop inside its frame;
+ * pitches are the frame's row strides in bytes, so a crop is described without copying.
+ * flow: (dx, dy) float32 interleaved, the layout cv2 returns; flow_pitch in bytes (multiple of 8). */
+typedef struct nsof_crop_desc {
+    const uint8_t *prev;
+    const uint8_t *next;
+    int h, w;
+    ptrdiff_t prev_pitch, next_pitch;
+    float *flow;
+    ptrdiff_t flow_pitch;
+} nsof_crop_desc;
+
+NSOF_API const char *nsof_last_error(void);
+NSOF_API int nsof_version(void);
+
+/* Creates the per-(GPU, stream) context that owns the workspace (I, R0, R1, M ping-pong, coarse
+ * flow, job tables).  Fails with NSOF_ERR_CUDA when `device` is not a usable CUDA device. */
+NSOF_API int nsof_create(int device, nsof_handle **out);
+NSOF_API int nsof_destroy(nsof_handle *h);
+/* Optional: size the workspace once for batches of up to `max_items` crops totalling
+ * `total_crop_pixels` pixels (otherwise it grows on demand, which synchronises the device). */
+NSOF_API int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_items);
+/* Bytes of device workspace currently held. */
+NSOF_API size_t nsof_workspace_bytes(const nsof_handle *h);
+
+/* ---- stage 2: dense Farneback ----------------------------------------------------------- */
+/* Replaces cv2.calcOpticalFlowFarneback(prev_region, next_region, None, **farneback_params)
+ * (optical_flow_seg.py:158, 203, 494; optical_flow_ob.py:225, 270, 616;
+ *  optical_flow_prediction.py:161, 206, 570; optical_flow_yolo.py:199, 244, 898)
+ * for `n` crop pairs at once; device pointers; asynchronous on `cuda_stream`. */
+NSOF_API int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items, int n,
+                                  const nsof_fb_params *params, void *cuda_stream);
+/* Single pair, device pointers. */
+NSOF_API int nsof_farneback_u8(nsof_handle *h, const uint8_t *prev, const uint8_t *next, int height, int width,
+                               ptrdiff_t prev_pitch, ptrdiff_t next_pitch, const nsof_fb_params *params,
+                               float *flow, ptrdiff_t flow_pitch, void *cuda_stream);
+/* Same with HOST pointers: H2D of the crops, kernels, D2H of the flow, synchronous -- the call
+ * the Python `calcOpticalFlowFarneback` drop-in makes for numpy arrays. */
+NSOF_API int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *items, int n,
+                                       const nsof_fb_params *params);
+NSOF_API int nsof_farneback_u8_host(nsof_handle *h, const uint8_t *prev, const uint8_t *next, int height,
+                                    int width, ptrdiff_t prev_pitch, ptrdiff_t next_pitch,
+                                    const nsof_fb_params *params, float *flow, ptrdiff_t flow_pitch);
+
+/* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
+ * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
+NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,
+                                    int *ksize, double *sigma);
+/* Algorithmic HBM bytes of one crop pair under the per-level fusion this library implements
+ * (DESIGN.md "byte model"); used by bench.py for the roofline. */
+NSOF_API double nsof_fb_algorithmic_bytes(int height, int width, const nsof_fb_params *params);
+
+/* Test hooks (used by tests/ only): truncate the pyramid after `stop_level` with `stop_iters`
+ * UpdateFlow iterations on that level (-1, -1 = off), then read back a stage of item `item`:
+ * what = 0 I(prev) 1 I(next) 2 R0 3 R1 4 M (current) 5 flow of that level.  `out` is a HOST
+ * buffer of ch*h*w floats, planar [ch][h][w] (flow: interleaved [h][w][2]). */
+NSOF_API int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iters);
+NSOF_API int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w);
+
+/* ---- stage 1: synaptic temporal memory -> ROI ------------------------------------------- */
+/* Rectangle in frame pixels, half-open: rows [y0, y1), cols [x0, x1)  (regions_info tuples of
+ * optical_flow_seg.py:138, 180-183 are (x_start, y_start, x_end, y_end)). */
+typedef struct nsof_rect {
+    int x0, y0, x1, y1;
+} nsof_rect;
+
+typedef struct nsof_roi_params {
+    int cells_h, cells_w;  /* Hc x Wc: shape of one slice of constructed3DMatrix */
+    int frame_h, frame_w;  /* H x W of the grey frames */
+    int pixel_h, pixel_w;  /* MEMSIZE (optical_flow_seg.py:455-458 passes it twice) */
+    int ext_left, ext_right, ext_upper, ext_lower; /* EXTEND_* (optical_flow_seg.py:38-41) */
+    int flag;              /* FLAG: 1 separate regions, 2 merged region (optical_flow_seg.py:31) */
+    int thres;             /* THRES on the uint8 map (optical_flow_seg.py:36) */
+    double map_a, map_b;   /* u8 = uint8(clip(map_a / log10(I) + map_b, 0, 255)); reference: -3366, -306 */
+} nsof_roi_params;
+
+#define NSOF_MAX_RECTS 256
+
+/* Replaces, for `n` independent array states at once, the stage-1 tail of the reference:
+ * current -> uint8 map (optical_flow_seg.py:426-435), update_transition_pic (:115-121),
+ * cv2.connectedComponentsWithStats(connectivity=4) (:223-224) and the bbox arithmetic of
+ * process_merged_region / process_separate_regions (:129-138, :174-183).
+ * currents: n slices of cells_h x cells_w doubles (device).  thr_table: 256 doubles (device),
+ * thr_table[v] = smallest current whose uint8 map value is >= v, found by the host wrapper by
+ * bisection with numpy's own log10 so that the device comparison is bit-exact by construction
+ * (thr_table[0] unused).  Outputs (device): memimg n*Hc*Wc uint8 map; labels n*Hc*Wc int32 (cv2
+ * numbering: raster order of each component's first cell, 0 = background); n_components[n]
+ * (= cv2's num_labels - 1); n_rects[n] (flag 2: 0 or 1; flag 1: n_components, of which at most
+ * NSOF_MAX_RECTS are stored); rects[n][NSOF_MAX_RECTS]; stats[n][NSOF_MAX_RECTS][5] = cv2
+ * CC_STAT_(LEFT,TOP,WIDTH,HEIGHT,AREA) of components 1.. (row 0 = component 1).
+ * Any output pointer may be NULL. */
+NSOF_API int nsof_roi_from_state_f64(nsof_handle *h, const double *currents, int n, const nsof_roi_params *p,
+                                     const double *thr_table, uint8_t *memimg, int32_t *labels,
+                                     int32_t *n_components, int32_t *n_rects, nsof_rect *rects, int32_t *stats,
+                                     void *cuda_stream);
+/* HOST-pointer variant (copies in/out, synchronous). */
+NSOF_API int nsof_roi_from_state_f64_host(nsof_handle *h, const double *currents, int n,
+                                          const nsof_roi_params *p, const double *thr_table, uint8_t *memimg,
+                                          int32_t *labels, int32_t *n_components, int32_t *n_rects,
+                                          nsof_rect *rects, int32_t *stats);
+
+/* Memristor model constants: PARAMS of eventsim/event_mem_sim.py:20-27 == simulation/
+ * simulationcode_v4_transistor_vehicle.m:26-33. */
+typedef struct nsof_synapse_params {
+    double alphaoff, alphaon, voff, von, koff, kon, son, soff, bon, boff, Ron, Roff, won, woff, wini;
+} nsof_synapse_params;
+
+/* bincount_2d (eventsim/event_mem_sim.py:100-104): per-slice event histogram, int32, bit-exact.
+ * x, y: device int16 arrays of n_events; counts: device int32 H*W, overwritten. */
+NSOF_API int nsof_event_hist(nsof_handle *h, const int16_t *x, const int16_t *y, size_t n_events, int H, int W,
+                             int32_t *counts, void *cuda_stream);
+/* update_state (eventsim/event_mem_sim.py:40-57), float32 arrays of n elements, in place on w:
+ * w <- clip(w + dwdt(w, V) * dt, 0, 1) with the float32-demoted constants numpy uses. */
+NSOF_API int nsof_synapse_step_f32(nsof_handle *h, float *w, const float *V, size_t n,
+                                   const nsof_synapse_params *p, double dt, void *cuda_stream);
+/* Scheme 1 of simulate() (eventsim/event_mem_sim.py:204-228) for a run of `n_slices` consecutive
+ * time windows, fused: events are time-sorted, slice s owns events [slice_begin[s], slice_begin[s+1]).
+ * For each slice: counts = bincount_2d; V = silent_v, V[counts >= theta] = active_v; w = update_state(w, V).
+ * w stays in registers across the slices of a chunk; only the final state is written.
+ * slice_begin: device int64[n_slices + 1]. */
+NSOF_API int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const int16_t *y,
+                                    const int64_t *slice_begin, int n_slices, int H, int W, int theta,
+                                    float active_v, float silent_v, const nsof_synapse_params *p, double dt,
+                                    float *w, void *cuda_stream);
+/* resistance_exp (eventsim/event_mem_sim.py:60-63): R = Ron / exp(-ln(Roff/Ron) * (1 - w)) for float32 w.
+ * The result is float64, as in numpy (np.log returns a float64 scalar, which promotes the array). */
+NSOF_API int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n, const nsof_synapse_params *p,
+                                     double *R, void *cuda_stream);
+
+/* Frame-mode simulator (simulation/simulationcode_v4_transistor_vehicle.m:111-121, 146-236, 306-321):
+ * one step of simulate_memristor_array for `n` clips at once.
+ *   cells_prev/cells_next: device double [n][Hc][Wc], the Lanczos-3 compressed frames in [0,1]
+ *   w: device double [n][Hc][Wc] state, updated in place with nsubsteps Euler sub-steps of dt/nsubsteps
+ *   current_out (may be NULL): device double [n][Hc][Wc] = vds / R(w)   (fixture-compatible current)
+ */
+typedef struct nsof_frame_sim_params {
+    double th1, th2; /* vehicle.m:40-41 */
+    double dt;       /* vehicle.m:55 */
+    int nsubsteps;   /* vehicle.m:56-59 */
+    double vds;      /* vehicle.m:36 */
+} nsof_frame_sim_params;
+NSOF_API int nsof_frame_sim_step_f64(nsof_handle *h, const double *cells_prev, const double *cells_next,
+                                     double *w, double *current_out, int n, int Hc, int Wc,
+                                     const nsof_synapse_params *p, const nsof_frame_sim_params *fp,
+                                     void *cuda_stream);
+/* compress_image (vehicle.m:111-121): im2double + imresize(., [floor(H/n), floor(W/m)], 'lanczos3')
+ * with MATLAB's antialiasing, for `n` uint8 frames (device) of H x W with row pitch `pitch` bytes and
+ * frame stride `frame_stride` bytes -> device double [n][Hc][Wc]. */
+NSOF_API int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, int n, int H, int W,
+                                       ptrdiff_t pitch, ptrdiff_t frame_stride, int Hc, int Wc, double *cells,
+                                       void *cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NSOF_H */

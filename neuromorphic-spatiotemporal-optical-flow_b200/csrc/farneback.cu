@@ -1,0 +1,638 @@
+// farneback.cu -- host driver + C ABI of stage 2 (dense Farneback), see include/nsof.h.
+//
+// Follows the level loop of OpenCV's FarnebackOpticalFlowImpl::calc, restated for
+// a batch of independent crop pairs: every kernel launch covers one stage of one pyramid level of
+// ALL crops of the batch (grid = max tiles x items), so small ROI crops still fill 148 SMs.
+#include "nsof_handle.h"
+#include "farneback_kernels.cuh"
+#include <float.h>
+#include <algorithm>
+
+// ------------------------------------------------------------------------------ error + handle
+static thread_local char g_err[512] = "";
+void nsof_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char *nsof_last_error(void) { return g_err; }
+extern "C" int nsof_version(void) { return 100; }
+
+int NsofDevBuf::ensure(size_t need)
+{
+    if (need <= bytes) return NSOF_OK;
+    if (p) {
+        NSOF_CUDA_TRY(cudaDeviceSynchronize());
+        NSOF_CUDA_TRY(cudaFree(p));
+        p = nullptr;
+        bytes = 0;
+    }
+    size_t want = need + need / 8;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+        p = nullptr;
+        (void)cudaGetLastError();
+        NSOF_FAIL(NSOF_ERR_NOMEM, "cudaMalloc of %zu bytes failed: %s", want, cudaGetErrorString(e));
+    }
+    bytes = want;
+    return NSOF_OK;
+}
+void NsofDevBuf::release()
+{
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+}
+
+int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **out)
+{
+    NsofStageSlot &s = h->stage[h->stage_next];
+    h->stage_next = (h->stage_next + 1) % 4;
+    if (s.pending) {
+        NSOF_CUDA_TRY(cudaEventSynchronize(s.done));
+        s.pending = false;
+    }
+    if (!s.done) NSOF_CUDA_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    if (s.bytes < bytes) {
+        if (s.host) NSOF_CUDA_TRY(cudaFreeHost(s.host));
+        s.host = nullptr;
+        s.bytes = 0;
+        NSOF_CUDA_TRY(cudaMallocHost(&s.host, bytes + bytes / 4 + 4096));
+        s.bytes = bytes + bytes / 4 + 4096;
+    }
+    *out = &s;
+    return NSOF_OK;
+}
+
+struct FbItemPlan {
+    int scales;
+    int hk[64], wk[64], pitch[64];
+    size_t off_I, off_R, off_Ma, off_Mb, off_fA, off_fB;  // floats from arena base
+    nsof_crop_desc d;
+};
+
+extern "C" int nsof_create(int device, nsof_handle **out)
+{
+    if (!out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {
+        (void)cudaGetLastError();
+        NSOF_FAIL(NSOF_ERR_CUDA, "nsof_create: no CUDA device (%s); libnsof has no CPU fallback",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (device < 0 || device >= count) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_create: device %d of %d", device, count);
+    NSOF_CUDA_TRY(cudaSetDevice(device));
+    nsof_handle *h = new nsof_handle();
+    h->device = device;
+    h->last_plan = new std::vector<FbItemPlan>();
+    *out = h;
+    return NSOF_OK;
+}
+
+extern "C" int nsof_destroy(nsof_handle *h)
+{
+    if (!h) return NSOF_OK;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    h->arena.release();
+    h->tables.release();
+    h->io.release();
+    h->s1.release();
+    h->lz.release();
+    for (auto &s : h->stage) {
+        if (s.host) cudaFreeHost(s.host);
+        if (s.done) cudaEventDestroy(s.done);
+    }
+    delete h->last_plan;
+    delete h;
+    return NSOF_OK;
+}
+
+extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
+{
+    return h ? h->arena.bytes + h->tables.bytes + h->io.bytes + h->s1.bytes : 0;
+}
+
+// ------------------------------------------------------------------------------ geometry (A.1)
+static int cv_round(double v) { return (int)nearbyint(v); }  // round-half-even like cvRound
+
+extern "C" int nsof_fb_level_geometry(int h, int w, double pyr_scale, int levels, int *hk, int *wk, int *ksize,
+                                      double *sigma)
+{
+    if (levels > 62) levels = 62;
+    double scale = 1;
+    int cropped = 0;
+    for (; cropped < levels; cropped++) {
+        scale *= pyr_scale;
+        if (w * scale < 32 || h * scale < 32) break;
+    }
+    for (int k = 0; k <= cropped; k++) {
+        scale = 1;
+        for (int i = 0; i < k; i++) scale *= pyr_scale;
+        double sg = (1. / scale - 1) * 0.5;
+        int ks = cv_round(sg * 5) | 1;
+        ks = std::max(ks, 3);
+        if (hk) hk[k] = cv_round(h * scale);
+        if (wk) wk[k] = cv_round(w * scale);
+        if (ksize) ksize[k] = ks;
+        if (sigma) sigma[k] = sg;
+    }
+    return cropped + 1;
+}
+
+// cv::getGaussianKernel(ksize, sigma, CV_32F) -> half kernel: gk[0] centre, gk[i] distance i (A.2)
+static void gaussian_half_kernel(int ksize, double sigma, float *gk)
+{
+    const int r = ksize / 2;
+    if (sigma <= 0 && ksize <= 7) {
+        static const float t1[] = {1.f};
+        static const float t3[] = {0.5f, 0.25f};
+        static const float t5[] = {0.375f, 0.25f, 0.0625f};
+        static const float t7[] = {0.28125f, 0.21875f, 0.109375f, 0.03125f};
+        const float *t = ksize == 1 ? t1 : ksize == 3 ? t3 : ksize == 5 ? t5 : t7;
+        for (int i = 0; i <= r; i++) gk[i] = t[i];
+        return;
+    }
+    const double sx = sigma > 0 ? sigma : ((ksize - 1) * 0.5 - 1) * 0.3 + 0.8;
+    const double scale2 = -0.5 / (sx * sx);
+    std::vector<double> tmp(ksize);
+    double sum = 0;
+    for (int i = 0; i < ksize; i++) {
+        double x = i - (ksize - 1) * 0.5;
+        tmp[i] = exp(scale2 * x * x);
+        sum += tmp[i];
+    }
+    sum = 1. / sum;
+    for (int i = 0; i <= r; i++) gk[i] = (float)(tmp[r + i] * sum);
+}
+
+// 6x6 inverse by Gauss-Jordan with partial pivoting (double)
+static void invert6(double a[6][6], double inv[6][6])
+{
+    double m[6][12];
+    for (int i = 0; i < 6; i++)
+        for (int j = 0; j < 6; j++) {
+            m[i][j] = a[i][j];
+            m[i][j + 6] = (i == j);
+        }
+    for (int c = 0; c < 6; c++) {
+        int p = c;
+        for (int i = c + 1; i < 6; i++)
+            if (fabs(m[i][c]) > fabs(m[p][c])) p = i;
+        if (p != c)
+            for (int j = 0; j < 12; j++) std::swap(m[c][j], m[p][j]);
+        const double d = 1.0 / m[c][c];
+        for (int j = 0; j < 12; j++) m[c][j] *= d;
+        for (int i = 0; i < 6; i++)
+            if (i != c) {
+                const double f = m[i][c];
+                if (f != 0)
+                    for (int j = 0; j < 12; j++) m[i][j] -= f * m[c][j];
+            }
+    }
+    for (int i = 0; i < 6; i++)
+        for (int j = 0; j < 6; j++) inv[i][j] = m[i][j + 6];
+}
+
+// FarnebackPrepareGaussian (A.4)
+static void prepare_poly(int n, double sigma, PolyConst *pc)
+{
+    if (sigma < FLT_EPSILON) sigma = n * 0.3;
+    std::vector<float> g(2 * n + 1), xg(2 * n + 1), xxg(2 * n + 1);
+    double s = 0.;
+    for (int x = -n; x <= n; x++) {
+        g[x + n] = (float)exp(-x * x / (2 * sigma * sigma));
+        s += g[x + n];
+    }
+    s = 1. / s;
+    for (int x = -n; x <= n; x++) {
+        g[x + n] = (float)(g[x + n] * s);
+        xg[x + n] = (float)(x * g[x + n]);
+        xxg[x + n] = (float)(x * x * g[x + n]);
+    }
+    double G[6][6] = {}, inv[6][6];
+    for (int y = -n; y <= n; y++)
+        for (int x = -n; x <= n; x++) {
+            const float gg = g[y + n] * g[x + n];
+            G[0][0] += gg;
+            G[1][1] += gg * x * x;
+            G[3][3] += gg * x * x * x * x;
+            G[5][5] += gg * x * x * y * y;
+        }
+    G[2][2] = G[0][3] = G[0][4] = G[3][0] = G[4][0] = G[1][1];
+    G[4][4] = G[3][3];
+    G[3][4] = G[4][3] = G[5][5];
+    invert6(G, inv);
+    memset(pc, 0, sizeof(*pc));
+    pc->n = n;
+    for (int k = 0; k <= n; k++) {
+        pc->g[k] = g[n + k];
+        pc->xg[k] = xg[n + k];
+        pc->xxg[k] = xxg[n + k];
+    }
+    pc->ig11 = (float)inv[1][1];
+    pc->ig03 = (float)inv[0][3];
+    pc->ig33 = (float)inv[3][3];
+    pc->ig55 = (float)inv[5][5];
+}
+
+static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int validate_params(const nsof_fb_params *p)
+{
+    if (!p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: params is NULL");
+    if (!(p->pyr_scale < 1.) || !(p->pyr_scale > 0.))
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: pyr_scale must be in (0, 1) (cv2: assertion pyrScale_ < 1)");
+    if (p->levels < 0 || p->winsize < 1 || p->iterations < 0)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: levels >= 0, winsize >= 1, iterations >= 0 required");
+    if (p->winsize < 2)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED,
+                  "farneback: winsize 1 is not implemented (OpenCV's running-sum initialisation adds row 0 / "
+                  "column 0 to every 1x1 window there; see oracle/farneback_oracle.c A.7)");
+    if (p->poly_n < 1 || p->poly_n > NSOF_MAX_POLY_N)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: poly_n must be in 1..%d", NSOF_MAX_POLY_N);
+    if (p->flags != 0)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED,
+                  "farneback: flags=%d; only 0 is implemented (OPTFLOW_USE_INITIAL_FLOW / "
+                  "OPTFLOW_FARNEBACK_GAUSSIAN are never selected by the reference)", p->flags);
+    return NSOF_OK;
+}
+
+// Tile of k_fb_blur_solve for a window radius m: largest candidate that keeps >= 3 CTAs per SM,
+// else anything that fits the 227 KB opt-in limit.
+static bool pick_blur_tile(int m, int *TW, int *TH, size_t *smem)
+{
+    static const int cand[][2] = {{64, 32}, {64, 16}, {32, 32}, {32, 16}, {16, 16}, {16, 8}, {8, 8}, {4, 4}};
+    for (int pass = 0; pass < 2; pass++) {
+        const size_t limit = pass == 0 ? 75 * 1024 : 227 * 1024;
+        for (auto &c : cand) {
+            const size_t pw = round_up(c[0] + 2 * m, 4);
+            const size_t b = 5 * (size_t)(c[1] + 2 * m) * pw * sizeof(float);
+            if (b <= limit) {
+                *TW = c[0];
+                *TH = c[1];
+                *smem = b;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
+extern "C" double nsof_fb_algorithmic_bytes(int h, int w, const nsof_fb_params *p)
+{
+    // DESIGN.md byte model: per level k (N_k pixels, N_0 source pixels, T iterations):
+    //   pyramid   : read 2*N_0 (uint8 x2)        write 8*N_k  (I0, I1)
+    //   polyexp   : read 8*N_k                    write 40*N_k (R0, R1)
+    //   um_first  : read 40*N_k + 8*N_{k+1}       write 20*N_k (M)
+    //   iteration : read 20 (M) + 40 (R0,R1)      write 20*N_k (M')   x (T-1)
+    //   last      : read 20*N_k                   write 8*N_k  (flow)
+    if (!p || h < 1 || w < 1) return 0.;
+    int hk[64], wk[64];
+    const int S = nsof_fb_level_geometry(h, w, p->pyr_scale, p->levels, hk, wk, nullptr, nullptr);
+    const double N0 = (double)h * w;
+    double bytes = 0;
+    for (int k = 0; k < S; k++) {
+        const double Nk = (double)hk[k] * wk[k];
+        const double Nc = k + 1 < S ? (double)hk[k + 1] * wk[k + 1] : 0.;
+        bytes += 2 * N0 + 8 * Nk + 8 * Nk + 40 * Nk;
+        if (p->iterations > 0) {
+            bytes += 40 * Nk + 8 * Nc + 20 * Nk;
+            bytes += 80 * Nk * (p->iterations - 1);
+            bytes += 28 * Nk;
+        } else {
+            bytes += 8 * Nc + 8 * Nk;
+        }
+    }
+    return bytes;
+}
+
+// ------------------------------------------------------------------------------ batch driver
+static int configure_smem(nsof_handle *h)
+{
+    if (h->smem_configured) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    h->smem_configured = true;
+    return NSOF_OK;
+}
+
+static int plan_item(const nsof_crop_desc &d, const nsof_fb_params *p, FbItemPlan *pl, int index)
+{
+    if (!d.prev || !d.next || !d.flow) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a NULL pointer", index);
+    if (d.h < 1 || d.w < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d is empty (%dx%d) (cv2: assertion !_src.empty())", index, d.h, d.w);
+    if (d.prev_pitch < d.w || d.next_pitch < d.w || d.flow_pitch < (ptrdiff_t)d.w * 8 || d.flow_pitch % 8)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a bad pitch", index);
+    if ((uintptr_t)d.flow % 8) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d flow pointer is not 8-byte aligned", index);
+    pl->d = d;
+    pl->scales = nsof_fb_level_geometry(d.h, d.w, p->pyr_scale, p->levels, pl->hk, pl->wk, nullptr, nullptr);
+    for (int k = 0; k < pl->scales; k++) {
+        if (pl->hk[k] < 1 || pl->wk[k] < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d level %d is empty", index, k);
+        pl->pitch[k] = (int)round_up(pl->wk[k], 32);
+    }
+    return NSOF_OK;
+}
+
+extern "C" int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_items)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_reserve: NULL handle");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    // 26 floats per padded level-0 pixel (I 2, R 10, Ma 5, Mb 5, coarse flow 2x2); padding <= 31 px per row
+    const size_t floats = (total_crop_pixels + (size_t)max_items * 32 * 8192) * 26;
+    int rc = h->arena.ensure(floats * sizeof(float));
+    if (rc) return rc;
+    return h->tables.ensure((size_t)max_items * 8 * sizeof(FbJob) + 65536);
+}
+
+extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params,
+                                    void *cuda_stream)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: NULL handle");
+    if (n < 0 || (n > 0 && !items)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: bad item list");
+    int rc = validate_params(params);
+    if (rc) return rc;
+    if (n == 0) return NSOF_OK;
+    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: at most 65535 items per batch");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    rc = configure_smem(h);
+    if (rc) return rc;
+
+    // ---- plan: geometry + arena offsets
+    std::vector<FbItemPlan> &plan = *h->last_plan;
+    plan.resize(n);
+    size_t arena_floats = 0;
+    int max_scales = 0;
+    for (int i = 0; i < n; i++) {
+        rc = plan_item(items[i], params, &plan[i], i);
+        if (rc) return rc;
+        FbItemPlan &pl = plan[i];
+        const size_t n0 = (size_t)pl.pitch[0] * pl.hk[0];
+        const size_t n1 = pl.scales > 1 ? (size_t)pl.pitch[1] * pl.hk[1] : 0;
+        pl.off_I = arena_floats;  arena_floats += 2 * n0;
+        pl.off_R = arena_floats;  arena_floats += 10 * n0;
+        pl.off_Ma = arena_floats; arena_floats += 5 * n0;
+        pl.off_Mb = arena_floats; arena_floats += 5 * n0;
+        pl.off_fA = arena_floats; arena_floats += 2 * n1;
+        pl.off_fB = arena_floats; arena_floats += 2 * n1;
+        arena_floats = round_up(arena_floats, 64);
+        max_scales = std::max(max_scales, pl.scales);
+    }
+    rc = h->arena.ensure(arena_floats * sizeof(float));
+    if (rc) return rc;
+    float *base = (float *)h->arena.p;
+
+    int ksize[64];
+    double sigma[64];
+    {
+        // ksize/sigma depend on the level index only; take them from a geometry with all levels present
+        double scale = 1;
+        for (int k = 0; k < max_scales; k++) {
+            sigma[k] = (1. / scale - 1) * 0.5;
+            ksize[k] = std::max(cv_round(sigma[k] * 5) | 1, 3);
+            scale *= params->pyr_scale;
+        }
+    }
+    const int stop_level = (h->dbg_level >= 0 && h->dbg_level < max_scales) ? h->dbg_level : 0;
+    h->last_stop_level = stop_level;
+    h->last_params = *params;
+
+    // ---- job tables for every level + Gaussian taps, one upload
+    size_t gk_floats = 0;
+    std::vector<size_t> gk_off(max_scales), job_off(max_scales);
+    std::vector<int> n_active(max_scales, 0);
+    for (int k = 0; k < max_scales; k++) {
+        if (ksize[k] / 2 > 4096) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: pyramid blur ksize %d too large", ksize[k]);
+        gk_off[k] = gk_floats;
+        gk_floats += round_up(ksize[k] / 2 + 1, 4);
+        for (int i = 0; i < n; i++) n_active[k] += plan[i].scales > k;
+    }
+    size_t table_bytes = round_up(gk_floats * sizeof(float), 16);
+    for (int k = 0; k < max_scales; k++) {
+        job_off[k] = table_bytes;
+        table_bytes += round_up((size_t)n_active[k] * sizeof(FbJob), 16);
+    }
+    NsofStageSlot *slot;
+    rc = nsof_stage_acquire(h, table_bytes, &slot);
+    if (rc) return rc;
+    rc = h->tables.ensure(table_bytes);
+    if (rc) return rc;
+    unsigned char *hs = (unsigned char *)slot->host;
+    unsigned char *ds = (unsigned char *)h->tables.p;
+    std::vector<int> max_tiles_pyr(max_scales, 0), max_tiles_pe(max_scales, 0), max_tiles_um(max_scales, 0),
+        max_tiles_bs(max_scales, 0);
+    const int m = params->winsize / 2;
+    int BTW = 0, BTH = 0;
+    size_t bs_smem = 0;
+    if (params->iterations > 0 && !pick_blur_tile(m, &BTW, &BTH, &bs_smem))
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
+    for (int k = 0; k < max_scales; k++) {
+        gaussian_half_kernel(ksize[k], sigma[k], (float *)hs + gk_off[k]);
+        FbJob *jobs = (FbJob *)(hs + job_off[k]);
+        int a = 0;
+        for (int i = 0; i < n; i++) {
+            const FbItemPlan &pl = plan[i];
+            if (pl.scales <= k) continue;
+            FbJob J;
+            memset(&J, 0, sizeof(J));
+            J.h = pl.hk[k]; J.w = pl.wk[k]; J.pitch = pl.pitch[k];
+            const bool coarsest = (k == pl.scales - 1);
+            if (!coarsest) {
+                J.ch = pl.hk[k + 1]; J.cw = pl.wk[k + 1]; J.cpitch = pl.pitch[k + 1];
+                J.fsx = (double)J.cw / J.w; J.fsy = (double)J.ch / J.h;
+            }
+            J.sh = pl.d.h; J.sw = pl.d.w;
+            J.spitch0 = (int)pl.d.prev_pitch; J.spitch1 = (int)pl.d.next_pitch;
+            J.src0 = pl.d.prev; J.src1 = pl.d.next;
+            if (J.h == J.sh && J.w == J.sw) J.resize_mode = 0;
+            else if (J.sh == 2 * J.h && J.sw == 2 * J.w) J.resize_mode = 1;  // cv::resize takes INTER_AREA at exact 2x
+            else J.resize_mode = 2;
+            J.sx = (double)J.sw / J.w; J.sy = (double)J.sh / J.h;
+            J.I = base + pl.off_I; J.R = base + pl.off_R; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
+            // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
+            float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
+            float *fl_coarse = (k & 1) ? base + pl.off_fB : base + pl.off_fA;
+            if (k == 0) { J.flow = (float2 *)pl.d.flow; J.fpitch = (int)(pl.d.flow_pitch / 8); }
+            else { J.flow = (float2 *)fl_this; J.fpitch = J.pitch; }
+            J.cflow = (const float2 *)fl_coarse;
+            jobs[a++] = J;
+            auto tiles = [&](int tw, int th) { return ((J.w + tw - 1) / tw) * ((J.h + th - 1) / th); };
+            max_tiles_pyr[k] = std::max(max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH));
+            max_tiles_pe[k] = std::max(max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH));
+            max_tiles_um[k] = std::max(max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH));
+            if (BTW) max_tiles_bs[k] = std::max(max_tiles_bs[k], tiles(BTW, BTH));
+        }
+    }
+    NSOF_CUDA_TRY(cudaMemcpyAsync(ds, hs, table_bytes, cudaMemcpyHostToDevice, stream));
+    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
+    slot->pending = true;
+
+    PolyConst pc;
+    prepare_poly(params->poly_n, params->poly_sigma, &pc);
+    const int pn = params->poly_n;
+    const size_t pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
+    const float flow_mul = (float)(1. / params->pyr_scale);
+    const float bscale = (float)(1. / ((double)params->winsize * params->winsize));
+
+    // ---- level loop, coarse to fine (A.1)
+    for (int k = max_scales - 1; k >= stop_level; k--) {
+        const FbJob *jobs = (const FbJob *)(ds + job_off[k]);
+        const float *gk = (const float *)ds + gk_off[k];
+        const int na = n_active[k];
+        int iters = params->iterations;
+        if (k == stop_level && h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
+        NSOF_LAUNCH(k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, ksize[k] / 2);
+        NSOF_LAUNCH(k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream, jobs, pc);
+        if (params->iterations == 0) {
+            NSOF_LAUNCH(k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs, flow_mul);
+        } else {
+            NSOF_LAUNCH(k_fb_um_first, max_tiles_um[k], na, 1, 256, 0, stream, jobs, flow_mul);
+            for (int it = 0; it < iters; it++)
+                NSOF_LAUNCH(k_fb_blur_solve, max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale,
+                            (it & 1) == 0, it == iters - 1);
+        }
+        NSOF_CUDA_TRY(cudaGetLastError());
+    }
+    return NSOF_OK;
+}
+
+extern "C" int nsof_farneback_u8(nsof_handle *h, const uint8_t *prev, const uint8_t *next, int height, int width,
+                                 ptrdiff_t prev_pitch, ptrdiff_t next_pitch, const nsof_fb_params *params, float *flow,
+                                 ptrdiff_t flow_pitch, void *cuda_stream)
+{
+    nsof_crop_desc d = {prev, next, height, width, prev_pitch, next_pitch, flow, flow_pitch};
+    return nsof_farneback_batch(h, &d, 1, params, cuda_stream);
+}
+
+// HOST-pointer entry: stage crops into h->io, run, copy flow back, synchronise.
+extern "C" int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: NULL handle");
+    if (n < 0 || (n > 0 && !items)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: bad item list");
+    int rc = validate_params(params);
+    if (rc) return rc;
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    std::vector<nsof_crop_desc> dev(n);
+    size_t bytes = 0;
+    std::vector<size_t> off_img(n), off_flow(n), ipitch(n);
+    for (int i = 0; i < n; i++) {
+        const nsof_crop_desc &d = items[i];
+        if (!d.prev || !d.next || !d.flow) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a NULL pointer", i);
+        if (d.h < 1 || d.w < 1)
+            NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d is empty (%dx%d) (cv2: assertion !_src.empty())", i, d.h, d.w);
+        if (d.prev_pitch < d.w || d.next_pitch < d.w || d.flow_pitch < (ptrdiff_t)d.w * 8)
+            NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a bad pitch", i);
+        ipitch[i] = round_up(d.w, 128);
+        off_img[i] = bytes;
+        bytes += 2 * ipitch[i] * d.h;
+        bytes = round_up(bytes, 256);
+        off_flow[i] = bytes;
+        bytes += (size_t)d.w * d.h * 8;
+        bytes = round_up(bytes, 256);
+    }
+    rc = h->io.ensure(bytes);
+    if (rc) return rc;
+    unsigned char *io = (unsigned char *)h->io.p;
+    cudaStream_t stream = nullptr;
+    for (int i = 0; i < n; i++) {
+        const nsof_crop_desc &d = items[i];
+        uint8_t *p0 = io + off_img[i], *p1 = p0 + ipitch[i] * d.h;
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p0, ipitch[i], d.prev, d.prev_pitch, d.w, d.h, cudaMemcpyHostToDevice, stream));
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p1, ipitch[i], d.next, d.next_pitch, d.w, d.h, cudaMemcpyHostToDevice, stream));
+        dev[i].prev = p0; dev[i].next = p1; dev[i].h = d.h; dev[i].w = d.w;
+        dev[i].prev_pitch = dev[i].next_pitch = (ptrdiff_t)ipitch[i];
+        dev[i].flow = (float *)(io + off_flow[i]);
+        dev[i].flow_pitch = (ptrdiff_t)d.w * 8;
+    }
+    rc = nsof_farneback_batch(h, dev.data(), n, params, stream);
+    if (rc) return rc;
+    for (int i = 0; i < n; i++) {
+        const nsof_crop_desc &d = items[i];
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(d.flow, d.flow_pitch, dev[i].flow, dev[i].flow_pitch, (size_t)d.w * 8, d.h,
+                                        cudaMemcpyDeviceToHost, stream));
+    }
+    NSOF_CUDA_TRY(cudaStreamSynchronize(stream));
+    return NSOF_OK;
+}
+
+extern "C" int nsof_farneback_u8_host(nsof_handle *h, const uint8_t *prev, const uint8_t *next, int height, int width,
+                                      ptrdiff_t prev_pitch, ptrdiff_t next_pitch, const nsof_fb_params *params,
+                                      float *flow, ptrdiff_t flow_pitch)
+{
+    nsof_crop_desc d = {prev, next, height, width, prev_pitch, next_pitch, flow, flow_pitch};
+    return nsof_farneback_batch_host(h, &d, 1, params);
+}
+
+// ------------------------------------------------------------------------------ test hooks
+extern "C" int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iters)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_level = stop_level;
+    h->dbg_iters = stop_iters;
+    return NSOF_OK;
+}
+
+extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w)
+{
+    if (!h || !out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: NULL argument");
+    std::vector<FbItemPlan> &plan = *h->last_plan;
+    if (item < 0 || item >= (int)plan.size()) NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: no item %d in the last batch", item);
+    const FbItemPlan &pl = plan[item];
+    const int k = h->last_stop_level;
+    if (k >= pl.scales) NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: item %d has no level %d", item, k);
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    NSOF_CUDA_TRY(cudaDeviceSynchronize());
+    const int hh = pl.hk[k], ww = pl.wk[k], pitch = pl.pitch[k];
+    const size_t plane = (size_t)pitch * hh;
+    float *base = (float *)h->arena.p;
+    if (out_h) *out_h = hh;
+    if (out_w) *out_w = ww;
+    const float *src;
+    int ch;
+    switch (what) {
+    case 0: src = base + pl.off_I; ch = 1; break;
+    case 1: src = base + pl.off_I + plane; ch = 1; break;
+    case 2: src = base + pl.off_R; ch = 5; break;
+    case 3: src = base + pl.off_R + 5 * plane; ch = 5; break;
+    case 4: {
+        // M currently valid: Ma after um_first, then the iterations alternate a->b->a ...
+        int iters = h->last_params.iterations;
+        if (h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
+        const int writes = iters > 0 ? iters - 1 : 0;  // the last iteration writes flow, not M
+        src = base + ((writes & 1) ? pl.off_Mb : pl.off_Ma);
+        ch = 5;
+        break;
+    }
+    case 5: {
+        if (k == 0) {
+            NSOF_CUDA_TRY(cudaMemcpy2DAsync(out, (size_t)ww * 8, pl.d.flow, pl.d.flow_pitch, (size_t)ww * 8, hh,
+                                            cudaMemcpyDeviceToHost, nullptr));
+        } else {
+            const float *f = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
+            NSOF_CUDA_TRY(cudaMemcpy2DAsync(out, (size_t)ww * 8, f, (size_t)pitch * 8, (size_t)ww * 8, hh,
+                                            cudaMemcpyDeviceToHost, nullptr));
+        }
+        NSOF_CUDA_TRY(cudaDeviceSynchronize());
+        return NSOF_OK;
+    }
+    default: NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: what=%d", what);
+    }
+    for (int c = 0; c < ch; c++)
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(out + (size_t)c * hh * ww, (size_t)ww * 4, src + c * plane, (size_t)pitch * 4,
+                                        (size_t)ww * 4, hh, cudaMemcpyDeviceToHost, nullptr));
+    NSOF_CUDA_TRY(cudaDeviceSynchronize());
+    return NSOF_OK;
+}
+
+#ifdef NSOF_EMU
+namespace nsof_emu {
+thread_local int bx, by, bz;
+thread_local unsigned char *smem;
+}
+#endif

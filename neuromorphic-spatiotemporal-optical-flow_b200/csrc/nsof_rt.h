@@ -1,0 +1,84 @@
+// nsof_rt.h -- kernel/launch vocabulary shared by every .cu file of libnsof.
+//
+// The product build (nvcc, sm_100a) maps these macros 1:1 onto CUDA.  A second,
+// TEST-ONLY build (g++ -DNSOF_EMU, see tests/emu/) maps them onto a sequential
+// "one logical thread per block" executor so that the *same kernel source* can be
+// checked for indexing / border / tiling logic against the oracle on a box with
+// no GPU.  That build is never loaded by the package; it exists for
+// `pytest -m "not gpu"` only.  To make it possible, kernels are written in the
+// block-stride style:
+//     for (int i = NSOF_TID; i < n_work_items; i += NSOF_NT) { ... }
+//     NSOF_SYNC();
+// and never assume a particular thread count for correctness.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+#include <math.h>
+
+#ifdef NSOF_EMU
+// ------------------------------------------------------------------ emulator
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+struct float2 { float x, y; };
+struct float4 { float x, y, z, w; };
+static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r; }
+static inline float4 make_float4(float x, float y, float z, float w) { float4 r = {x, y, z, w}; return r; }
+namespace nsof_emu {
+extern thread_local int bx, by, bz;
+extern thread_local unsigned char *smem;
+template <class F> static inline void launch(int gx, int gy, int gz, size_t smem_bytes, F f)
+{
+    std::vector<unsigned char> buf(smem_bytes + 64);
+    smem = buf.data();
+    for (bz = 0; bz < gz; bz++)
+        for (by = 0; by < gy; by++)
+            for (bx = 0; bx < gx; bx++) f();
+    smem = nullptr;
+}
+}  // namespace nsof_emu
+#define NSOF_GLOBAL static void
+#define NSOF_DEV static inline
+#define NSOF_HD static inline
+#define NSOF_RESTRICT
+#define NSOF_BX (nsof_emu::bx)
+#define NSOF_BY (nsof_emu::by)
+#define NSOF_BZ (nsof_emu::bz)
+#define NSOF_TID 0
+#define NSOF_NT 1
+#define NSOF_SYNC() ((void)0)
+#define NSOF_DYN_SMEM(name) unsigned char *name = nsof_emu::smem
+#define NSOF_LDG(p) (*(p))
+#define NSOF_LAUNCH(kern, gx, gy, gz, nt, smem_bytes, stream, ...) \
+    nsof_emu::launch((gx), (gy), (gz), (smem_bytes), [&] { kern(__VA_ARGS__); })
+#define NSOF_LAUNCH_BOUNDS(nt, minb)
+#else
+// ---------------------------------------------------------------- CUDA build
+#include <cuda_runtime.h>
+#define NSOF_GLOBAL __global__ void
+#define NSOF_DEV __device__ __forceinline__
+#define NSOF_HD __host__ __device__ __forceinline__
+#define NSOF_RESTRICT __restrict__
+#define NSOF_BX ((int)blockIdx.x)
+#define NSOF_BY ((int)blockIdx.y)
+#define NSOF_BZ ((int)blockIdx.z)
+#define NSOF_TID ((int)threadIdx.x)
+#define NSOF_NT ((int)blockDim.x)
+#define NSOF_SYNC() __syncthreads()
+#define NSOF_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#define NSOF_LDG(p) __ldg(p)
+#define NSOF_LAUNCH(kern, gx, gy, gz, nt, smem_bytes, stream, ...) \
+    kern<<<dim3((gx), (gy), (gz)), dim3(nt), (smem_bytes), (stream)>>>(__VA_ARGS__)
+#define NSOF_LAUNCH_BOUNDS(nt, minb) __launch_bounds__(nt, minb)
+#endif
+
+NSOF_HD int nsof_imin(int a, int b) { return a < b ? a : b; }
+NSOF_HD int nsof_imax(int a, int b) { return a > b ? a : b; }
+NSOF_HD int nsof_clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+// cv::BORDER_REFLECT_101 (gfedcb|abcdefgh|gfedcba)
+NSOF_HD int nsof_reflect101(int p, int len)
+{
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}

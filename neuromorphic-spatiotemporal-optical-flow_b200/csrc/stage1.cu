@@ -1,0 +1,284 @@
+// stage1.cu -- host driver + C ABI of stage 1 (synaptic temporal memory -> ROI), see include/nsof.h.
+#include "nsof_handle.h"
+#include "stage1_kernels.cuh"
+#include <algorithm>
+#include <cmath>
+
+static const int S1_NT = 256;
+static const int S1_PER_BLOCK = 1024;
+
+static SynF32 syn_f32(const nsof_synapse_params *p, double dt)
+{
+    SynF32 s;
+    s.voff = (float)p->voff; s.von = (float)p->von; s.koff = (float)p->koff; s.kon = (float)p->kon;
+    s.son = (float)p->son; s.soff = (float)p->soff; s.bon = (float)p->bon; s.boff = (float)p->boff;
+    s.alphaoff = (float)p->alphaoff; s.alphaon = (float)p->alphaon; s.dt = (float)dt;
+    return s;
+}
+
+static inline int blocks_for(size_t n, int per_block) { return (int)((n + per_block - 1) / per_block); }
+
+extern "C" int nsof_event_hist(nsof_handle *h, const int16_t *x, const int16_t *y, size_t n_events, int H, int W,
+                               int32_t *counts, void *cuda_stream)
+{
+    if (!h || !counts || H < 1 || W < 1 || (n_events && (!x || !y))) NSOF_FAIL(NSOF_ERR_BAD_ARG, "event_hist: bad argument");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    NSOF_CUDA_TRY(cudaMemsetAsync(counts, 0, (size_t)H * W * sizeof(int32_t), st));
+    if (n_events) {
+        NSOF_LAUNCH(k_s1_event_hist, blocks_for(n_events, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, n_events, H, W, counts,
+                    S1_PER_BLOCK);
+        NSOF_CUDA_TRY(cudaGetLastError());
+    }
+    return NSOF_OK;
+}
+
+extern "C" int nsof_synapse_step_f32(nsof_handle *h, float *w, const float *V, size_t n, const nsof_synapse_params *p,
+                                     double dt, void *cuda_stream)
+{
+    if (!h || !w || !V || !p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "synapse_step: bad argument");
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    NSOF_LAUNCH(k_s1_synapse_step, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, V, n,
+                syn_f32(p, dt), S1_PER_BLOCK);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+extern "C" int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const int16_t *y, const int64_t *slice_begin,
+                                      int n_slices, int H, int W, int theta, float active_v, float silent_v,
+                                      const nsof_synapse_params *p, double dt, float *w, void *cuda_stream)
+{
+    if (!h || !x || !y || !slice_begin || !p || !w || n_slices < 0 || H < 1 || W < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "event_scheme1: bad argument");
+    if (n_slices == 0) return NSOF_OK;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t npx = (size_t)H * W;
+    const bool first_use = h->s1.bytes < npx * 4;
+    int rc = h->s1.ensure(npx * 4);
+    if (rc) return rc;
+    const SynF32 sp = syn_f32(p, dt);
+    // slice_begin lives on the device; the host needs the event counts per chunk to size grids.
+    std::vector<int64_t> sb(n_slices + 1);
+    NSOF_CUDA_TRY(cudaMemcpyAsync(sb.data(), slice_begin, sizeof(int64_t) * (n_slices + 1), cudaMemcpyDeviceToHost, st));
+    NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+    if (theta <= 1) {
+        uint32_t *bits = (uint32_t *)h->s1.p;
+        if (first_use || true) NSOF_CUDA_TRY(cudaMemsetAsync(bits, 0, npx * 4, st));
+        for (int s0 = 0; s0 < n_slices; s0 += 32) {
+            const int ns = std::min(32, n_slices - s0);
+            const int64_t ne = sb[s0 + ns] - sb[s0];
+            if (ne > 0) {
+                NSOF_LAUNCH(k_s1_slice_bits, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, slice_begin + s0,
+                            ns, H, W, bits, S1_PER_BLOCK);
+            }
+            const bool silent_is_idle = !(silent_v < sp.voff) && !(silent_v > sp.von);
+            if (ne > 0 || !silent_is_idle) {
+                NSOF_LAUNCH(k_s1_replay_bits, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, bits, npx, ns, active_v,
+                            silent_v, sp, S1_PER_BLOCK);
+            }
+        }
+    } else {
+        int32_t *counts = (int32_t *)h->s1.p;
+        for (int s = 0; s < n_slices; s++) {
+            const int64_t ne = sb[s + 1] - sb[s];
+            NSOF_CUDA_TRY(cudaMemsetAsync(counts, 0, npx * 4, st));
+            if (ne > 0)
+                NSOF_LAUNCH(k_s1_event_hist, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x + sb[s], y + sb[s],
+                            (size_t)ne, H, W, counts, S1_PER_BLOCK);
+            NSOF_LAUNCH(k_s1_step_from_counts, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, counts, npx, theta,
+                        active_v, silent_v, sp, S1_PER_BLOCK);
+        }
+    }
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+extern "C" int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n, const nsof_synapse_params *p, double *R,
+                                       void *cuda_stream)
+{
+    if (!h || !w || !R || !p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "resistance_exp: bad argument");
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const double lam = log(p->Roff / p->Ron);
+    NSOF_LAUNCH(k_s1_resistance_exp, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, n, p->Ron,
+                lam, R, S1_PER_BLOCK);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+// ------------------------------------------------------------------------------ frame mode
+// MATLAB imresize 'lanczos3' contributions for one dimension (antialiased when shrinking):
+//   scale = out/in; kernel width 6 (/scale when scale < 1); u = x/scale + 0.5*(1 - 1/scale), x = 1..out;
+//   left = floor(u - kw/2); P = ceil(kw) + 2 taps; weights h(u - idx) normalised to sum 1;
+//   indices mirrored at the borders (aux = [1:in, in:-1:1]).
+static double lanczos3(double x)
+{
+    const double pi = 3.14159265358979323846;
+    const double eps = 2.220446049250313e-16;
+    double f = (sin(pi * x) * sin(pi * x / 3.) + eps) / ((pi * pi * x * x / 3.) + eps);
+    return fabs(x) < 3. ? f : 0.;
+}
+static int lanczos_contrib(int in, int out, std::vector<double> &wgt, std::vector<int> &idx)
+{
+    const double scale = (double)out / in;
+    double kw = 6.;
+    const bool aa = scale < 1.;
+    if (aa) kw = kw / scale;
+    const int P = (int)ceil(kw) + 2;
+    wgt.assign((size_t)out * P, 0.);
+    idx.assign((size_t)out * P, 0);
+    for (int o = 0; o < out; o++) {
+        const double x = o + 1;
+        const double u = x / scale + 0.5 * (1. - 1. / scale);
+        const double left = floor(u - kw / 2.);
+        double sum = 0.;
+        for (int k = 0; k < P; k++) {
+            const double ind = left + k;
+            const double v = aa ? scale * lanczos3(scale * (u - ind)) : lanczos3(u - ind);
+            wgt[(size_t)o * P + k] = v;
+            sum += v;
+            // mirror: aux = [1:in, in:-1:1]; aux(mod(ind-1, 2*in) + 1)
+            long long m = ((long long)ind - 1) % (2LL * in);
+            if (m < 0) m += 2LL * in;
+            const int one_based = m < in ? (int)m + 1 : (int)(2LL * in - m);
+            idx[(size_t)o * P + k] = one_based - 1;
+        }
+        for (int k = 0; k < P; k++) wgt[(size_t)o * P + k] /= sum;
+    }
+    return P;
+}
+
+extern "C" int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, int n, int H, int W, ptrdiff_t pitch,
+                                         ptrdiff_t frame_stride, int Hc, int Wc, double *cells, void *cuda_stream)
+{
+    if (!h || !frames || !cells || n < 0 || H < 1 || W < 1 || Hc < 1 || Wc < 1 || pitch < W)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "lanczos3_compress: bad argument");
+    if (n == 0) return NSOF_OK;
+    if (n > 65535 || Hc > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "lanczos3_compress: too many frames/cells per call");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    int rc;
+    if (h->lz_key[0] != H || h->lz_key[1] != W || h->lz_key[2] != Hc || h->lz_key[3] != Wc) {
+        std::vector<double> wy, wx;
+        std::vector<int> iy, ix;
+        const int Py = lanczos_contrib(H, Hc, wy, iy), Px = lanczos_contrib(W, Wc, wx, ix);
+        const size_t bytes = (wy.size() + wx.size()) * sizeof(double) + (iy.size() + ix.size()) * sizeof(int) + 64;
+        rc = h->lz.ensure(bytes);
+        if (rc) return rc;
+        // tables are tiny and change only with the geometry: plain synchronous upload
+        char *d = (char *)h->lz.p;
+        NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, wy.data(), wy.size() * 8, cudaMemcpyHostToDevice, st)); d += wy.size() * 8;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, wx.data(), wx.size() * 8, cudaMemcpyHostToDevice, st)); d += wx.size() * 8;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, iy.data(), iy.size() * 4, cudaMemcpyHostToDevice, st)); d += iy.size() * 4;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, ix.data(), ix.size() * 4, cudaMemcpyHostToDevice, st));
+        NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+        h->lz_key[0] = H; h->lz_key[1] = W; h->lz_key[2] = Hc; h->lz_key[3] = Wc;
+        h->lz_P[0] = Py; h->lz_P[1] = Px;
+    }
+    const int Py = h->lz_P[0], Px = h->lz_P[1];
+    const double *d_wy = (const double *)h->lz.p;
+    const double *d_wx = d_wy + (size_t)Hc * Py;
+    const int *d_iy = (const int *)(d_wx + (size_t)Wc * Px);
+    const int *d_ix = d_iy + (size_t)Hc * Py;
+    rc = h->s1.ensure((size_t)n * Hc * W * sizeof(double));
+    if (rc) return rc;
+    double *tmp = (double *)h->s1.p;
+    const int cols = 256;
+    NSOF_LAUNCH(k_s1_lanczos_rows, (W + cols - 1) / cols, Hc, n, S1_NT, 0, st, frames, pitch, frame_stride, W, Hc, d_wy, d_iy,
+                Py, tmp, cols);
+    NSOF_LAUNCH(k_s1_lanczos_cols, n, 1, 1, S1_NT, 0, st, tmp, W, Hc, Wc, d_wx, d_ix, Px, cells);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+extern "C" int nsof_frame_sim_step_f64(nsof_handle *h, const double *cells_prev, const double *cells_next, double *w,
+                                       double *current_out, int n, int Hc, int Wc, const nsof_synapse_params *p,
+                                       const nsof_frame_sim_params *fp, void *cuda_stream)
+{
+    if (!h || !cells_prev || !cells_next || !w || !p || !fp || n < 0 || Hc < 1 || Wc < 1 || fp->nsubsteps < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "frame_sim_step: bad argument");
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    FrameSimConst c;
+    c.th1 = fp->th1; c.th2 = fp->th2; c.dt_sub = fp->dt / fp->nsubsteps; c.vds = fp->vds; c.nsub = fp->nsubsteps;
+    c.alphaoff = p->alphaoff; c.alphaon = p->alphaon; c.voff = p->voff; c.von = p->von; c.koff = p->koff; c.kon = p->kon;
+    c.son = p->son; c.soff = p->soff; c.bon = p->bon; c.boff = p->boff; c.Ron = p->Ron; c.lam = log(p->Roff / p->Ron);
+    const size_t total = (size_t)n * Hc * Wc;
+    // few cells, long dependent chains: small blocks so the cells spread over many SMs
+    const int per_block = 32;
+    NSOF_LAUNCH(k_s1_frame_step, blocks_for(total, per_block), 1, 1, 32, 0, (cudaStream_t)cuda_stream, cells_prev, cells_next,
+                w, current_out, total, c, per_block);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+// ------------------------------------------------------------------------------ ROI tail
+static int validate_roi(const nsof_roi_params *p)
+{
+    if (!p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "roi: params is NULL");
+    if (p->cells_h < 1 || p->cells_w < 1 || p->frame_h < 1 || p->frame_w < 1 || p->pixel_h < 1 || p->pixel_w < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "roi: bad geometry");
+    if ((size_t)p->cells_h * p->cells_w > 40000) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "roi: more than 40000 cells per state");
+    if (p->flag != 1 && p->flag != 2) NSOF_FAIL(NSOF_ERR_BAD_ARG, "roi: flag must be 1 (separate) or 2 (merged)");
+    return NSOF_OK;
+}
+
+static bool g_roi_smem_set = false;
+
+extern "C" int nsof_roi_from_state_f64(nsof_handle *h, const double *currents, int n, const nsof_roi_params *p,
+                                       const double *thr_table, uint8_t *memimg, int32_t *labels, int32_t *n_components,
+                                       int32_t *n_rects, nsof_rect *rects, int32_t *stats, void *cuda_stream)
+{
+    if (!h || !currents || !thr_table || n < 0) NSOF_FAIL(NSOF_ERR_BAD_ARG, "roi: bad argument");
+    int rc = validate_roi(p);
+    if (rc) return rc;
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t smem = ((size_t)p->cells_h * p->cells_w + 1 + 5 * NSOF_MAX_RECTS) * sizeof(int);
+    if (!g_roi_smem_set) {
+        NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_roi, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        g_roi_smem_set = true;
+    }
+    NSOF_LAUNCH(k_s1_roi, n, 1, 1, 128, smem, (cudaStream_t)cuda_stream, currents, *p, thr_table, memimg, labels,
+                n_components, n_rects, rects, stats);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+extern "C" int nsof_roi_from_state_f64_host(nsof_handle *h, const double *currents, int n, const nsof_roi_params *p,
+                                            const double *thr_table, uint8_t *memimg, int32_t *labels,
+                                            int32_t *n_components, int32_t *n_rects, nsof_rect *rects, int32_t *stats)
+{
+    if (!h || !currents || !thr_table || n < 0) NSOF_FAIL(NSOF_ERR_BAD_ARG, "roi: bad argument");
+    int rc = validate_roi(p);
+    if (rc) return rc;
+    if (n == 0) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t N = (size_t)p->cells_h * p->cells_w;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_cur = 0, o_thr = o_cur + up(n * N * 8), o_mem = o_thr + up(256 * 8), o_lab = o_mem + up(n * N),
+                 o_nc = o_lab + up(n * N * 4), o_nr = o_nc + up((size_t)n * 4), o_rc = o_nr + up((size_t)n * 4),
+                 o_st = o_rc + up((size_t)n * NSOF_MAX_RECTS * sizeof(nsof_rect)),
+                 total = o_st + up((size_t)n * NSOF_MAX_RECTS * 5 * 4);
+    rc = h->io.ensure(total);
+    if (rc) return rc;
+    char *d = (char *)h->io.p;
+    cudaStream_t st = nullptr;
+    NSOF_CUDA_TRY(cudaMemcpyAsync(d + o_cur, currents, n * N * 8, cudaMemcpyHostToDevice, st));
+    NSOF_CUDA_TRY(cudaMemcpyAsync(d + o_thr, thr_table, 256 * 8, cudaMemcpyHostToDevice, st));
+    rc = nsof_roi_from_state_f64(h, (const double *)(d + o_cur), n, p, (const double *)(d + o_thr), (uint8_t *)(d + o_mem),
+                                 (int32_t *)(d + o_lab), (int32_t *)(d + o_nc), (int32_t *)(d + o_nr), (nsof_rect *)(d + o_rc),
+                                 (int32_t *)(d + o_st), st);
+    if (rc) return rc;
+    if (memimg) NSOF_CUDA_TRY(cudaMemcpyAsync(memimg, d + o_mem, n * N, cudaMemcpyDeviceToHost, st));
+    if (labels) NSOF_CUDA_TRY(cudaMemcpyAsync(labels, d + o_lab, n * N * 4, cudaMemcpyDeviceToHost, st));
+    if (n_components) NSOF_CUDA_TRY(cudaMemcpyAsync(n_components, d + o_nc, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    if (n_rects) NSOF_CUDA_TRY(cudaMemcpyAsync(n_rects, d + o_nr, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    if (rects) NSOF_CUDA_TRY(cudaMemcpyAsync(rects, d + o_rc, (size_t)n * NSOF_MAX_RECTS * sizeof(nsof_rect), cudaMemcpyDeviceToHost, st));
+    if (stats) NSOF_CUDA_TRY(cudaMemcpyAsync(stats, d + o_st, (size_t)n * NSOF_MAX_RECTS * 5 * 4, cudaMemcpyDeviceToHost, st));
+    NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+    return NSOF_OK;
+}

@@ -1,0 +1,43 @@
+// emu_cuda.h -- TEST INFRASTRUCTURE ONLY.
+// Host stand-ins for the handful of CUDA runtime calls libnsof's driver code makes, so that the
+// unmodified kernel + driver sources compile with g++ -DNSOF_EMU into tests/emu/_build/libnsof_emu.so
+// (see nsof_rt.h).  "Device" memory is host memory and streams are synchronous.  The package never
+// loads this library; `pytest -m "not gpu"` uses it to check kernel indexing logic against the oracle.
+#pragma once
+#include <stdlib.h>
+#include <string.h>
+typedef int cudaError_t;
+enum { cudaSuccess = 0, cudaErrorMemoryAllocation = 2 };
+typedef void *cudaStream_t;
+typedef void *cudaEvent_t;
+enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
+static inline const char *cudaGetErrorString(cudaError_t e) { return e ? "emulated failure" : "ok"; }
+static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+static inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
+static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return cudaSuccess; }
+static inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
+static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+static inline cudaError_t cudaMalloc(void **p, size_t n) { *p = malloc(n ? n : 1); return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
+static inline cudaError_t cudaFree(void *p) { free(p); return cudaSuccess; }
+static inline cudaError_t cudaMallocHost(void **p, size_t n) { return cudaMalloc(p, n); }
+static inline cudaError_t cudaFreeHost(void *p) { free(p); return cudaSuccess; }
+static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind, cudaStream_t) { memcpy(d, s, n); return cudaSuccess; }
+static inline cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size_t wbytes, size_t rows, cudaMemcpyKind, cudaStream_t)
+{
+    for (size_t r = 0; r < rows; r++) memcpy((char *)d + r * dp, (const char *)s + r * sp, wbytes);
+    return cudaSuccess;
+}
+static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t) { memset(d, v, n); return cudaSuccess; }
+static inline cudaError_t cudaMemset2DAsync(void *d, size_t dp, int v, size_t wbytes, size_t rows, cudaStream_t)
+{
+    for (size_t r = 0; r < rows; r++) memset((char *)d + r * dp, v, wbytes);
+    return cudaSuccess;
+}
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned) { *e = (void *)1; return cudaSuccess; }
+static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }
+static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
+#define cudaEventDisableTiming 2
+#define cudaFuncSetAttribute(f, a, v) (cudaSuccess)
+#define cudaFuncAttributeMaxDynamicSharedMemorySize 8

@@ -1,0 +1,211 @@
+#!/usr/bin/env python3
+"""Generates the golden fixtures under tests/golden/ by running the REFERENCE's own code in the
+build container:
+
+* stage 2: `cv2.calcOpticalFlowFarneback` (cv2 4.13.0 here; the reference pins opencv-python 4.9.0) on
+  small synthetic pairs and on real data/grasp + data/autodriving crops, for the three parameter sets
+  the reference ships (optical_flow_seg.py:61-112, data/*/Parameters.txt).
+* stage-1 tail: the reference's functions `update_transition_pic`, `process_merged_region`,
+  `process_separate_regions`, `opticalFlow3D` loaded by SOURCE SLICING from
+  /root/reference/optical_flow_seg.py (the script runs its experiment at import time), driven with the
+  shipped `constructed_3D_matrix.mat` of data/grasp and data/autodriving.
+* event mode: `generate_synthetic_events`, `bincount_2d`, `update_state`, `resistance_exp`,
+  `slice_indices` imported from /root/reference/eventsim/event_mem_sim.py with a stub `h5py`.
+
+Run from the repo root:  python tests/golden/make_golden.py
+/root/reference is only needed here; tests read the committed .npz files.
+"""
+import ast
+import os
+import sys
+import types
+
+import cv2
+import numpy as np
+import scipy.io
+
+REF = "/root/reference"
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+PARAM_SETS = {
+    "grasp": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0),
+    "autodriving_txt": dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3, poly_n=10, poly_sigma=1.05, flags=0),
+    "tabletennis": dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2, poly_n=1, poly_sigma=1.05, flags=0),
+}
+
+
+def load_reference_functions(script, consts):
+    """exec only the named top-level functions of a reference script, with the script's constants."""
+    src = open(os.path.join(REF, script), encoding="utf-8").read()
+    tree = ast.parse(src)
+    want = {"update_transition_pic", "process_separate_regions", "process_merged_region", "opticalFlow3D"}
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in want]
+    mod = ast.Module(body=body, type_ignores=[])
+    import time
+    from numba import njit
+    ns = dict(cv2=cv2, np=np, time=time, njit=njit, print=lambda *a, **k: None, mem_cal_times=[], mem_velocity_times=[],
+              mem_opticalflow_times=[])
+    ns.update(consts)
+    exec(compile(mod, script, "exec"), ns)
+    return ns
+
+
+def synth_pair(rng, h, w, dx=3.0, dy=-1.5):
+    base = rng.integers(0, 256, (h + 40, w + 40)).astype(np.float32)
+    base = cv2.GaussianBlur(base, (0, 0), 3)
+    base = (base - base.min()) / (base.max() - base.min()) * 255
+    a = base[20:20 + h, 20:20 + w]
+    M = np.float32([[1, 0, dx], [0, 1, dy]])
+    b = cv2.warpAffine(base, M, (w + 40, h + 40), flags=cv2.INTER_LINEAR)[20:20 + h, 20:20 + w]
+    return np.ascontiguousarray(a.astype(np.uint8)), np.ascontiguousarray(b.astype(np.uint8))
+
+
+def grey(path):
+    return cv2.cvtColor(cv2.imread(path), cv2.COLOR_RGB2GRAY)  # BGR read as RGB, as optical_flow_seg.py:439-443
+
+
+def make_farneback():
+    rng = np.random.default_rng(20260411)
+    out = {}
+    cases = []
+    for (h, w) in [(96, 128), (75, 101), (40, 33), (17, 260)]:
+        cases.append((f"synth_{h}x{w}",) + synth_pair(rng, h, w))
+    g40, g41 = grey(f"{REF}/data/grasp/RGB/41.jpg"), grey(f"{REF}/data/grasp/RGB/42.jpg")
+    cases.append(("grasp_crop", np.ascontiguousarray(g40[700:860, 400:590]), np.ascontiguousarray(g41[700:860, 400:590])))
+    a0, a1 = grey(f"{REF}/data/autodriving/RGB/20.jpg"), grey(f"{REF}/data/autodriving/RGB/21.jpg")
+    cases.append(("autodriving_crop", np.ascontiguousarray(a0[300:431, 250:420]), np.ascontiguousarray(a1[300:431, 250:420])))
+    names = []
+    for name, a, b in cases:
+        names.append(name)
+        out[f"{name}__prev"] = a
+        out[f"{name}__next"] = b
+        for pname, p in PARAM_SETS.items():
+            out[f"{name}__{pname}"] = cv2.calcOpticalFlowFarneback(a, b, None, **p)
+    out["cases"] = np.array(names)
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(OUT, "farneback_cv2.npz"), **out)
+    print("farneback_cv2.npz", len(names), "cases")
+
+
+def make_roi():
+    out = {}
+    for ds, script, consts, frame_hw in [
+        ("grasp", "optical_flow_seg.py",
+         dict(MEMSIZE=80, OFFSET=0, EXTEND_HEIGHT_UPPER=20, EXTEND_HEIGHT_LOWER=20, EXTEND_WIDTH_LEFT=20,
+              EXTEND_WIDTH_RIGHT=20, THRES=250, CONNECT=4), (1920, 1080)),
+        ("autodriving", "optical_flow_yolo.py",
+         dict(MEMSIZE=200, OFFSET=15, EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, EXTEND_WIDTH_LEFT=60,
+              EXTEND_WIDTH_RIGHT=60, THRES=114, CONNECT=4), (801, 801)),
+    ]:
+        mat = scipy.io.loadmat(f"{REF}/data/{ds}/constructed_3D_matrix.mat")["constructed3DMatrix"]
+        out[f"{ds}__currents"] = np.ascontiguousarray(np.moveaxis(mat, 2, 0)).astype(np.float64)  # (T, Hc, Wc)
+        T = mat.shape[2]
+        H, W = frame_hw
+        blank = np.zeros((H, W), np.uint8)
+        # memimg as the script computes it (optical_flow_seg.py:426-435)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            u8 = np.clip(-3366 / np.log10(np.moveaxis(mat, 2, 0).astype(np.double)) - 306, 0, 255).astype(np.uint8)
+        out[f"{ds}__memimg"] = u8
+        for flag in (1, 2):
+            # farneback on blank frames is irrelevant here: stub cv2.calcOpticalFlowFarneback out of the namespace
+            ns = load_reference_functions(script, dict(consts, FLAG=flag, farneback_params={}))
+            fake_cv2 = types.SimpleNamespace(**{k: getattr(cv2, k) for k in dir(cv2) if k.startswith("CC_STAT") or k == "connectedComponentsWithStats"})
+            fake_cv2.calcOpticalFlowFarneback = lambda a, b, f, **kw: np.zeros(a.shape + (2,), np.float32)
+            ns["cv2"] = fake_cv2
+            rects = np.zeros((T, 64, 4), np.int32)
+            nrect = np.zeros(T, np.int32)
+            nlab = np.zeros(T, np.int32)
+            for t in range(T):
+                res = ns["opticalFlow3D"](u8[t], u8[t], blank, blank, consts["MEMSIZE"], consts["MEMSIZE"])
+                if flag == 1:
+                    nlab[t] = res[4]
+                    info = res[5]
+                    nrect[t] = len(info)
+                    for j, r in enumerate(info):
+                        rects[t, j] = r
+                else:
+                    r = res[4]
+                    if r != (0, 0, 0, 0):
+                        nrect[t] = 1
+                        rects[t, 0] = r
+            out[f"{ds}__flag{flag}__rects"] = rects
+            out[f"{ds}__flag{flag}__nrect"] = nrect
+            if flag == 1:
+                out[f"{ds}__num_labels"] = nlab
+        # cv2 CC labels + stats on the transition picture
+        labels = np.zeros(u8.shape, np.int32)
+        stats = np.zeros((T, 64, 5), np.int32)
+        for t in range(T):
+            tp = np.where(u8[t] >= consts["THRES"], 255, 0).astype(np.uint8)
+            n, lab, st, _ = cv2.connectedComponentsWithStats(tp, connectivity=4)
+            labels[t] = lab
+            stats[t, :n - 1] = st[1:]
+        out[f"{ds}__labels"] = labels
+        out[f"{ds}__stats"] = stats
+    # random masks: CC numbering/stats pin against cv2 on denser patterns than the datasets offer
+    rng = np.random.default_rng(7)
+    masks = (rng.random((40, 24, 13)) < rng.uniform(0.1, 0.7, (40, 1, 1))).astype(np.uint8) * 255
+    lab = np.zeros(masks.shape, np.int32)
+    st = np.zeros((40, 200, 5), np.int32)
+    nl = np.zeros(40, np.int32)
+    for i in range(40):
+        n, l, s, _ = cv2.connectedComponentsWithStats(masks[i], connectivity=4)
+        lab[i] = l
+        st[i, :n - 1] = s[1:]
+        nl[i] = n
+    out["random__masks"], out["random__labels"], out["random__stats"], out["random__num_labels"] = masks, lab, st, nl
+    np.savez_compressed(os.path.join(OUT, "roi_reference.npz"), **out)
+    print("roi_reference.npz")
+
+
+def make_events():
+    sys.modules.setdefault("h5py", types.ModuleType("h5py"))
+    sys.path.insert(0, f"{REF}/eventsim")
+    import event_mem_sim as ems
+    x, y, p, t = ems.generate_synthetic_events()
+    H, W = 240, 320
+    out = dict(x=x.astype(np.int16), y=y.astype(np.int16), p=p.astype(np.int8), t=t.astype(np.int64), H=H, W=W)
+    slices = list(ems.slice_indices(t, 1000))
+    out["slice_bounds"] = np.array([s.start for s in slices] + [slices[-1].stop], np.int64)
+    # bincount of a few slices
+    pick = [0, 1, 100, 500, len(slices) - 1]
+    out["hist_slices"] = np.array(pick)
+    out["hist"] = np.stack([ems.bincount_2d(x[slices[i]], y[slices[i]], H, W) for i in pick])
+    # scheme 1 exactly as simulate() runs it (event_mem_sim.py:204-228), CLI defaults active_v=-6, silent_v=0
+    w = ems.PARAMS["wini"] * np.ones((H, W), dtype=np.float32)
+    snaps = {}
+    for i, sl in enumerate(slices):
+        V = np.full((H, W), 0.0, dtype=np.float32)
+        if sl.stop > sl.start:
+            ec = ems.bincount_2d(x[sl], y[sl], H, W)
+            m = ec >= ems.THETA_EVENTS
+            if m.any():
+                V[m] = -6.0
+        w = ems.update_state(w, V)
+        if i in (0, 31, 32, 200, len(slices) - 1):
+            snaps[i] = w.copy()
+    out["w_snap_idx"] = np.array(sorted(snaps))
+    out["w_snaps"] = np.stack([snaps[i] for i in sorted(snaps)])
+    out["R_final"] = ems.resistance_exp(w)
+    # a decaying variant: silent_v = 0.5 (> von) so every pixel updates every slice; first 64 slices
+    w2 = ems.PARAMS["wini"] * np.ones((H, W), dtype=np.float32)
+    for i, sl in enumerate(slices[:64]):
+        V = np.full((H, W), 0.5, dtype=np.float32)
+        if sl.stop > sl.start:
+            ec = ems.bincount_2d(x[sl], y[sl], H, W)
+            V[ec >= 1] = -6.0
+        w2 = ems.update_state(w2, V)
+    out["w_decay64"] = w2
+    # single update_state call on a random state/voltage field
+    rng = np.random.default_rng(3)
+    w0 = rng.random((64, 96), dtype=np.float32)
+    V0 = rng.uniform(-8, 2, (64, 96)).astype(np.float32)
+    out["us_w0"], out["us_V0"], out["us_w1"] = w0, V0, ems.update_state(w0, V0)
+    np.savez_compressed(os.path.join(OUT, "events_reference.npz"), **out)
+    print("events_reference.npz", len(x), "events", len(slices), "slices")
+
+
+if __name__ == "__main__":
+    make_farneback()
+    make_roi()
+    make_events()

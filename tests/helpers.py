@@ -1,0 +1,128 @@
+"""Shared test plumbing: oracle loader (ctypes over oracle/_build/libnsof_oracle.so), emulator build,
+golden fixtures, synthetic inputs, comparison metrics."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+PARAM_SETS = {
+    "grasp": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0),
+    "autodriving_txt": dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3, poly_n=10, poly_sigma=1.05, flags=0),
+    "tabletennis": dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2, poly_n=1, poly_sigma=1.05, flags=0),
+}
+# Flow tolerances vs OpenCV's float Farneback (BASELINE.json bar: EPE <= 0.01 px).  Pixels whose 2x2 system is
+# near-singular (aperture problem inside a tiny window: winsize 3/4) amplify 1-ulp differences of ANY
+# implementation -- the C oracle itself differs from cv2 by up to 0.6 px on 0.003 % of such pixels of a 1080p
+# frame, and by 5e-3 px at the 99.9th percentile of the autodriving crop -- so for those parameter sets the
+# bound is taken at the 99th percentile; the mean EPE is always checked.
+TOL = {
+    "grasp": dict(epe_mean=1e-4, q=1.0, qmax=1e-3),
+    "autodriving_txt": dict(epe_mean=1e-3, q=0.99, qmax=1e-2),
+    "tabletennis": dict(epe_mean=1e-3, q=0.99, qmax=1e-2),
+}
+
+
+def build_oracle():
+    path = os.path.join(ROOT, "oracle", "_build", "libnsof_oracle.so")
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
+    return path
+
+
+def build_emu():
+    path = os.path.join(ROOT, "tests", "emu", "_build", "libnsof_emu.so")
+    csrc = os.path.join(ROOT, "neuromorphic-spatiotemporal-optical-flow_b200", "csrc")
+    subprocess.run(["make", "-s", "-C", csrc, "emu"], check=True)
+    return path
+
+
+DUMP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_int)
+
+
+class Oracle:
+    def __init__(self, path):
+        self.lib = C.CDLL(path)
+        self.lib.nsof_oracle_farneback_dump.argtypes = [
+            C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_ssize_t, C.c_double, C.c_int, C.c_int, C.c_int,
+            C.c_int, C.c_double, C.c_int, C.c_void_p, DUMP_FN, C.c_void_p]
+        self.lib.nsof_oracle_level_geometry.argtypes = [C.c_int, C.c_int, C.c_double, C.c_int] + [C.c_void_p] * 4
+
+    def farneback(self, prev, nxt, pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags=0, dump=False):
+        prev = np.ascontiguousarray(prev)
+        nxt = np.ascontiguousarray(nxt)
+        h, w = prev.shape
+        out = np.zeros((h, w, 2), np.float32)
+        stages = {}
+
+        def cb(user, tag, k, it, data, hh, ww, ch):
+            arr = np.ctypeslib.as_array(data, shape=(hh, ww, ch)).copy()
+            stages[(tag, k, it)] = arr
+
+        fn = DUMP_FN(cb) if dump else C.cast(None, DUMP_FN)
+        rc = self.lib.nsof_oracle_farneback_dump(prev.ctypes.data, nxt.ctypes.data, h, w, w, w, pyr_scale, levels,
+                                                 winsize, iterations, poly_n, poly_sigma, flags, out.ctypes.data, fn,
+                                                 None)
+        assert rc == 0, rc
+        return (out, stages) if dump else out
+
+    def level_geometry(self, h, w, pyr_scale, levels):
+        hk = (C.c_int * 64)()
+        wk = (C.c_int * 64)()
+        ks = (C.c_int * 64)()
+        sg = (C.c_double * 64)()
+        n = self.lib.nsof_oracle_level_geometry(h, w, pyr_scale, levels, hk, wk, ks, sg)
+        return [(hk[i], wk[i], ks[i], sg[i]) for i in range(n)]
+
+
+def load_oracle():
+    return Oracle(build_oracle())
+
+
+class Golden:
+    def __init__(self):
+        self.fb = np.load(os.path.join(GOLDEN, "farneback_cv2.npz"))
+        self.roi = np.load(os.path.join(GOLDEN, "roi_reference.npz"))
+        self.ev = np.load(os.path.join(GOLDEN, "events_reference.npz"))
+
+
+def textured_pair(seed, h, w, dx=3.0, dy=-1.5):
+    """Smooth random texture and its sub-pixel translation (numpy only: must run on the GPU box)."""
+    rng = np.random.default_rng(seed)
+    H, W = h + 32, w + 32
+    base = rng.random((H, W)).astype(np.float64)
+    k = np.exp(-0.5 * (np.arange(-9, 10) / 3.0) ** 2)
+    k /= k.sum()
+    base = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 1, base)
+    base = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 0, base)
+    base = (base - base.min()) / (base.max() - base.min()) * 255.0
+    ys, xs = np.mgrid[0:h, 0:w].astype(np.float64)
+    a = base[16:16 + h, 16:16 + w]
+    sy, sx = ys + 16 - dy, xs + 16 - dx  # b(y, x) = a(y - dy, x - dx): content moves by (+dx, +dy)
+    y0, x0 = np.floor(sy).astype(int), np.floor(sx).astype(int)
+    fy, fx = sy - y0, sx - x0
+    b = (base[y0, x0] * (1 - fx) * (1 - fy) + base[y0, x0 + 1] * fx * (1 - fy)
+         + base[y0 + 1, x0] * (1 - fx) * fy + base[y0 + 1, x0 + 1] * fx * fy)
+    return np.ascontiguousarray(a.astype(np.uint8)), np.ascontiguousarray(b.astype(np.uint8))
+
+
+def flow_err(a, b):
+    d = np.sqrt(((a.astype(np.float64) - b.astype(np.float64)) ** 2).sum(-1))
+    return d
+
+
+def assert_flow_close(got, want, pname, what=""):
+    tol = TOL[pname]
+    d = flow_err(got, want)
+    epe = d.mean()
+    qv = np.quantile(d, tol["q"]) if tol["q"] < 1.0 else d.max()
+    assert epe <= tol["epe_mean"], f"{what} {pname}: mean EPE {epe:.3e} > {tol['epe_mean']}"
+    assert qv <= tol["qmax"], f"{what} {pname}: q{tol['q']} EPE {qv:.3e} > {tol['qmax']}"
+    assert epe <= 0.01  # BASELINE.json bar
+    return epe, qv
+
+
+def planar_to_aos(p):
+    return np.ascontiguousarray(np.moveaxis(p, 0, -1))

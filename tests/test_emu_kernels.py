@@ -1,0 +1,160 @@
+"""Kernel-logic checks WITHOUT a GPU: the same .cu sources compiled by g++ -DNSOF_EMU into a sequential
+block emulator (tests/emu, nsof_rt.h) are driven through the same C ABI and compared with the oracle and the
+golden vectors.  This exercises tiling, halos, borders, batching and the host driver; it says nothing about
+races or performance -- the `-m gpu` tests are the parity tests proper."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle import stage1_oracle as s1
+
+
+@pytest.mark.parametrize("pname", list(helpers.PARAM_SETS))
+def test_emu_farneback_vs_golden(emu_engine, golden, pname):
+    p = helpers.PARAM_SETS[pname]
+    for case in golden.fb["cases"]:
+        prev, nxt = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"]
+        got = emu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
+        helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"emu vs cv2 {case}")
+
+
+def test_emu_stage_dumps_vs_oracle(emu_engine, oracle):
+    """Every intermediate (I, R0, R1, M, per-iteration flow) of every level against the oracle's dump."""
+    prev, nxt = helpers.textured_pair(5, 150, 203)
+    p = helpers.PARAM_SETS["grasp"]
+    _, st = oracle.farneback(prev, nxt, **p, dump=True)
+    geo = oracle.level_geometry(150, 203, p["pyr_scale"], p["levels"])
+    assert len(geo) == 3
+    try:
+        for k, (hk, wk, _, _) in enumerate(geo):
+            for it in (0, 1, p["iterations"]):
+                emu_engine.debug_truncate(k, it)
+                emu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
+                if it == 0:
+                    for what, tag in ((0, 0), (1, 1), (2, 2), (3, 3), (4, 4)):
+                        got = helpers.planar_to_aos(emu_engine.debug_fetch(0, what, hk, wk))
+                        want = st[(tag, k, 0)]
+                        scale = max(1.0, float(np.abs(want).max()))
+                        assert np.abs(got - want).max() <= 2e-5 * scale, (k, what)
+                else:
+                    got = emu_engine.debug_fetch(0, 5, hk, wk)
+                    want = st[(5, k, it - 1)]
+                    assert np.abs(got - want).max() <= 1e-4, (k, it)
+    finally:
+        emu_engine.debug_truncate(-1, -1)
+
+
+def test_emu_batch_ragged_and_strided(emu_engine, oracle):
+    p = helpers.PARAM_SETS["grasp"]
+    big_a, big_b = helpers.textured_pair(11, 240, 320)
+    views = [(slice(0, 240), slice(0, 320)), (slice(13, 140), slice(7, 96)), (slice(100, 133), slice(20, 300)),
+             (slice(200, 208), slice(300, 308))]
+    pairs = [(big_a[v], big_b[v]) for v in views]  # non-contiguous views, like the reference's crops
+    flows = emu_engine.farneback_batch(pairs, **p)
+    for (a, b), f in zip(pairs, flows):
+        want = oracle.farneback(np.ascontiguousarray(a), np.ascontiguousarray(b), **p)
+        helpers.assert_flow_close(f, want, "grasp", "emu batch")
+        single = emu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+        assert np.array_equal(single, f)  # batching never changes a crop's result
+
+
+def test_emu_errors_mirror_cv2(emu_engine, nsof):
+    a = np.zeros((40, 40), np.uint8)
+    p = dict(helpers.PARAM_SETS["grasp"])
+    with pytest.raises(nsof.error):
+        emu_engine.calcOpticalFlowFarneback(a[:0], a[:0], None, **p)
+    with pytest.raises(nsof.error):
+        emu_engine.calcOpticalFlowFarneback(a, a[:, :20], None, **p)
+    with pytest.raises(nsof.error):
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
+    with pytest.raises(NotImplementedError):
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=256))
+    with pytest.raises(NotImplementedError):
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, winsize=1))
+    z = emu_engine.calcOpticalFlowFarneback(a, a, None, **p)
+    assert z.shape == (40, 40, 2) and z.dtype == np.float32 and not z.any()
+
+
+@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801))])
+def test_emu_roi_bit_exact_vs_reference(emu_engine, nsof, golden, ds, cfgname, hw):
+    cfg = getattr(nsof.RoiConfig, cfgname)()
+    cur = golden.roi[f"{ds}__currents"]
+    for flag in (1, 2):
+        cfg.FLAG = flag
+        r = emu_engine.roi_from_currents(cur, hw, cfg=cfg)
+        assert np.array_equal(r["memimg"], golden.roi[f"{ds}__memimg"])
+        assert np.array_equal(r["labels"], golden.roi[f"{ds}__labels"])
+        for t in range(cur.shape[0]):
+            n = int(golden.roi[f"{ds}__flag{flag}__nrect"][t])
+            assert r["rects"][t] == [tuple(v) for v in golden.roi[f"{ds}__flag{flag}__rects"][t, :n]]
+            assert np.array_equal(r["stats"][t], golden.roi[f"{ds}__stats"][t, :len(r["stats"][t])])
+        if flag == 1:
+            assert np.array_equal(r["num_labels"], golden.roi[f"{ds}__num_labels"])
+
+
+def test_emu_cc_random_masks_vs_cv2(emu_engine, nsof, golden):
+    masks = golden.roi["random__masks"]
+    cfg = nsof.RoiConfig(THRES=255, MEMSIZE=1, EXTEND_WIDTH_LEFT=0, EXTEND_WIDTH_RIGHT=0, EXTEND_HEIGHT_UPPER=0,
+                         EXTEND_HEIGHT_LOWER=0, FLAG=1)
+    r = emu_engine.roi_from_memimg(masks, masks.shape[1:], 1, 1, cfg)
+    assert np.array_equal(r["labels"], golden.roi["random__labels"])
+    assert np.array_equal(r["num_labels"], golden.roi["random__num_labels"])
+    for i in range(len(masks)):
+        n = int(golden.roi["random__num_labels"][i]) - 1
+        assert np.array_equal(r["stats"][i], golden.roi["random__stats"][i, :n])
+        # FLAG 1 rectangles with MEMSIZE 1 and no extension are the stats boxes
+        assert r["rects"][i] == [(int(s[0]), int(s[1]), int(s[0] + s[2]), int(s[1] + s[3])) for s in r["stats"][i]]
+
+
+def test_emu_opticalflow3d_matches_reference_structure(emu_engine, nsof, golden, oracle):
+    cfg = nsof.RoiConfig.autodriving()
+    emu_engine.config = cfg
+    memimg = golden.roi["autodriving__memimg"]
+    t = int(np.argmax(golden.roi["autodriving__flag2__nrect"]))  # a slice with a non-empty ROI
+    a, b = helpers.textured_pair(3, 801, 801)
+    flow, cal, vel, region_list, info = emu_engine.opticalFlow3D(memimg[t], memimg[t], a, b, cfg.MEMSIZE, cfg.MEMSIZE)
+    x0, y0, x1, y1 = info
+    assert info == tuple(golden.roi["autodriving__flag2__rects"][t, 0])
+    assert flow.dtype == np.float64 and flow.shape == (801, 801, 2)
+    want = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(b[y0:y1, x0:x1]), **cfg.farneback_params)
+    helpers.assert_flow_close(flow[y0:y1, x0:x1].astype(np.float32), want, "grasp", "opticalFlow3D crop")
+    outside = np.ones((801, 801), bool)
+    outside[y0:y1, x0:x1] = False
+    assert not flow[outside].any()
+    # empty ROI -> zeros and (0,0,0,0), optical_flow_seg.py:227-234
+    t0 = int(np.argmin(golden.roi["autodriving__flag2__nrect"]))
+    res = emu_engine.opticalFlow3D(memimg[t0], memimg[t0], a, b, cfg.MEMSIZE, cfg.MEMSIZE)
+    assert not res[0].any() and res[4] == (0, 0, 0, 0)
+    emu_engine.config = nsof.RoiConfig()
+
+
+def test_emu_events_vs_reference(emu_engine, golden):
+    ev = golden.ev
+    x, y, t = ev["x"], ev["y"], ev["t"]
+    H, W = int(ev["H"]), int(ev["W"])
+    b = ev["slice_bounds"]
+    for k, i in enumerate(ev["hist_slices"]):
+        sl = slice(b[i], b[i + 1])
+        assert np.array_equal(emu_engine.bincount_2d(x[sl], y[sl], H, W), ev["hist"][k])  # integer: bit-exact
+    got = emu_engine.update_state(ev["us_w0"], ev["us_V0"])
+    assert np.abs(got - ev["us_w1"]).max() <= 4 * np.finfo(np.float32).eps
+    w = emu_engine.simulate_scheme1(x, y, t, H, W, 1000)
+    assert np.abs(w - ev["w_snaps"][-1]).max() <= 2e-6
+    assert np.array_equal(w != np.float32(0.5), ev["w_snaps"][-1] != np.float32(0.5))  # same set of touched pixels
+    w64 = emu_engine.simulate_scheme1(x[:b[64]], y[:b[64]], t[:b[64]], H, W, 1000, silent_v=0.5)
+    # t[:b[64]] ends inside slice 63, so the stream has 64 windows
+    assert np.abs(w64 - ev["w_decay64"]).max() <= 2e-5
+    R = emu_engine.resistance_exp(ev["w_snaps"][-1])
+    assert R.dtype == np.float64 and np.allclose(R, ev["R_final"], rtol=1e-12)
+
+
+def test_emu_frame_mode_vs_oracle(emu_engine):
+    rng = np.random.default_rng(0)
+    frames = rng.integers(0, 256, (3, 161, 203), dtype=np.uint8)
+    cells = emu_engine.compress_images(frames, 40, 40)
+    for i in range(3):
+        assert np.allclose(cells[i], s1.compress_image(frames[i], 40, 40), rtol=0, atol=1e-13)
+    seq = np.clip(0.5 + 0.02 * rng.standard_normal((4, 3, 5)), 0, 1)
+    w, cur = emu_engine.simulate_memristor_array(seq, nSubSteps=20)
+    w_o, cur_o = s1.simulate_memristor_array(seq, nSubSteps=20)
+    assert np.allclose(w, w_o, rtol=0, atol=1e-12) and np.allclose(cur, cur_o, rtol=1e-11)

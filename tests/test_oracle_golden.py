@@ -1,0 +1,79 @@
+"""Pins the oracle (oracle/farneback_oracle.c, oracle/stage1_oracle.py) against the golden vectors the
+reference's own code produced (tests/golden/make_golden.py).  CPU only."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle import stage1_oracle as s1
+
+
+@pytest.mark.parametrize("pname", list(helpers.PARAM_SETS))
+def test_farneback_oracle_matches_cv2_golden(oracle, golden, pname):
+    p = helpers.PARAM_SETS[pname]
+    for case in golden.fb["cases"]:
+        prev, nxt = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"]
+        want = golden.fb[f"{case}__{pname}"]
+        got = oracle.farneback(prev, nxt, **p)
+        helpers.assert_flow_close(got, want, pname, f"oracle vs cv2 {case}")
+
+
+def test_level_geometry_matches_spec(oracle):
+    # 1080x1920 at (0.5, 3) -> 4 scales, ksize 3,3,9,19
+    g = oracle.level_geometry(1080, 1920, 0.5, 3)
+    assert [(a, b, c) for a, b, c, _ in g] == [(1080, 1920, 3), (540, 960, 3), (270, 480, 9), (135, 240, 19)]
+    # truncation while min(h, w) * scale < 32
+    assert len(oracle.level_geometry(40, 500, 0.5, 3)) == 1
+    assert len(oracle.level_geometry(64, 64, 0.5, 3)) == 2
+
+
+@pytest.mark.parametrize("ds,cfg", [("grasp", dict(MEMSIZE=80, THRES=250, ext=(20, 20, 20, 20), hw=(1920, 1080))),
+                                    ("autodriving", dict(MEMSIZE=200, THRES=114, ext=(60, 60, 60, 60), hw=(801, 801)))])
+def test_roi_oracle_matches_reference(golden, ds, cfg):
+    cur = golden.roi[f"{ds}__currents"]
+    memimg = s1.current_to_u8(cur)
+    assert np.array_equal(memimg, golden.roi[f"{ds}__memimg"])
+    for t in range(cur.shape[0]):
+        for flag in (1, 2):
+            n, labels, stats, rects = s1.roi_from_memimg(memimg[t], cfg["hw"], cfg["MEMSIZE"], cfg["MEMSIZE"], cfg["THRES"],
+                                                         cfg["ext"], flag)
+            want_n = int(golden.roi[f"{ds}__flag{flag}__nrect"][t])
+            assert len(rects) == want_n
+            assert [tuple(r) for r in golden.roi[f"{ds}__flag{flag}__rects"][t, :want_n]] == rects
+        assert np.array_equal(labels, golden.roi[f"{ds}__labels"][t])
+        assert np.array_equal(stats[1:], golden.roi[f"{ds}__stats"][t, :n - 1])
+        assert n == golden.roi[f"{ds}__num_labels"][t] or n == 1
+
+
+def test_cc_oracle_matches_cv2_on_random_masks(golden):
+    for i, m in enumerate(golden.roi["random__masks"]):
+        n, labels, stats = s1.connected_components_4(m)
+        assert n == golden.roi["random__num_labels"][i]
+        assert np.array_equal(labels, golden.roi["random__labels"][i])
+        assert np.array_equal(stats[1:], golden.roi["random__stats"][i, :n - 1])
+
+
+def test_event_oracle_matches_reference(golden):
+    ev = golden.ev
+    x, y, t = ev["x"], ev["y"], ev["t"]
+    H, W = int(ev["H"]), int(ev["W"])
+    b = s1.slice_bounds(t, 1000)
+    assert np.array_equal(b, ev["slice_bounds"])
+    for k, i in enumerate(ev["hist_slices"]):
+        sl = slice(b[i], b[i + 1])
+        assert np.array_equal(s1.bincount_2d(x[sl], y[sl], H, W), ev["hist"][k])
+    assert np.array_equal(s1.update_state(ev["us_w0"], ev["us_V0"]), ev["us_w1"])
+    for k, i in enumerate(ev["w_snap_idx"][:3]):
+        assert np.array_equal(s1.scheme1(x, y, t, H, W, 1000, n_slices=int(i) + 1), ev["w_snaps"][k])
+    assert np.array_equal(s1.scheme1(x, y, t, H, W, 1000, silent_v=0.5, n_slices=64), ev["w_decay64"])
+
+
+def test_frame_mode_oracle_sanity():
+    """Frame mode is parity-unpinned (no MATLAB here): check the properties the .m text implies."""
+    wts, idx = s1.lanczos3_contributions(800, 4)
+    assert np.allclose(wts.sum(1), 1.0) and idx.min() >= 0 and idx.max() < 800
+    flat = np.full((160, 160), 77, np.uint8)
+    assert np.allclose(s1.compress_image(flat, 40, 40), 77 / 255.0, atol=1e-12)  # weights sum to 1
+    # a static scene decays towards w = 0 (d = 0 <= th1 -> func1 < 0 -> v_mod > von -> kon < 0)
+    cells = np.full((3, 2, 2), 0.5)
+    w, cur = s1.simulate_memristor_array(cells, nSubSteps=50)
+    assert (w < 0.5).all() and np.allclose(cur[0], 1 / (163305 / np.exp(-np.log(2104377 / 163305) * 0.5)))
