@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py -- ROI-gated Farneback frame-pairs/s at 1080p (BASELINE.json metric), one process per GPU.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path on the host cores
+
+Workload (config.workload): BASELINE.json configs[3] -- synthetic 1920x1080 clips, sequence-parallel, no
+collective.  Every rank holds `--clips` clips of `--frames` frames resident in HBM (weak scaling: 8 clips per GPU
+-> 64 clips at 8 GPUs).  One step = one pass of the hot path over all the rank's clips: stage 1 (compress_image ->
+synapse array update -> ROI rectangles) and stage 2 (Farneback on every ROI crop, pasted into zeroed flow frames).
+`value` = pairs of all ranks / max-over-ranks device time.  See DESIGN.md "Measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "roi_gated_farneback_frame_pairs_per_sec_1080p"
+UNIT = "frame-pairs/s"
+H, W = 1080, 1920
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="nsof", choices=["nsof", "reference"])
+    ap.add_argument("--clips", type=int, default=8, help="clips per GPU")
+    ap.add_argument("--frames", type=int, default=16, help="frames per clip")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the full-frame and per-kernel legs")
+    return ap.parse_args()
+
+
+def workload_config(args, n_gpus):
+    return {"workload": "configs[3]: synthetic 1920x1080 clips, sequence-parallel (no collective)",
+            "frame": [H, W], "clips_per_gpu": args.clips, "frames_per_clip": args.frames,
+            "pairs_per_step_per_gpu": args.clips * (args.frames - 1), "clips_total": args.clips * n_gpus,
+            "roi": "synapse-array gate (MEMSIZE 80, THRES 250, EXT 20, FLAG 2)",
+            "farneback": [0.5, 3, 15, 3, 5, 1.2, 0], "stage1": "frame mode, nSubSteps 1000",
+            "l2": "inputs exceed L2 (frames + flow frames per step >> 126 MB)"}
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------- CPU legs
+def host_clips(n_clips, frames, seed0=1234):
+    import importlib
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    return [syn.make_clip(seed0 + c, H, W, frames, "cpu").numpy() for c in range(n_clips)]
+
+
+def cpu_baseline_leg(clip_np):
+    """Bounded sample on rank 0: the reference CPU path over ONE clip in ONE process (cv2's default threads)."""
+    from oracle import cpu_reference as ref
+    ref.process_clip(clip_np[:3])  # warm-up (page-in, cv2 thread pool)
+    n, dt, rects, _ = ref.process_clip(clip_np)
+    nf, dtf, _, _ = ref.process_clip(clip_np[:3], full_frame=True)
+    cores = ref.cv2.getNumThreads() if ref.cv2 is not None else 1
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": ref.KIND,
+            "sample": f"1 clip x {clip_np.shape[0]} frames ({n} pairs) of the same synthetic workload, one process, "
+                      f"numpy stage 1 + {'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback "
+                      f"on the ROI crop; host has {os.cpu_count()} cores",
+            "full_frame_value": nf / dtf}
+
+
+def reference_arm(args):
+    """--impl reference: the reference CPU path on all host cores (one process per core, one clip per task)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import cpu_reference as ref
+    cores = os.cpu_count() or 1
+    workers = max(1, cores)
+    ref_frames = 5  # 4 pairs per clip and task: bounded sample
+    clips = host_clips(min(workers, 16), ref_frames)
+    clips = [clips[i % len(clips)] for i in range(workers)]
+    for _ in range(max(1, min(args.warmup, 1))):
+        ref.process_clips_parallel(clips, workers)
+    t0 = time.perf_counter()
+    pairs = 0
+    for _ in range(args.steps):
+        n, _ = ref.process_clips_parallel(clips, workers)
+        pairs += n
+    dt = time.perf_counter() - t0
+    val = pairs / dt
+    sample = (f"each step = {workers} clips x {ref_frames} frames ({workers * (ref_frames - 1)} pairs) of the same "
+              f"synthetic 1080p workload, one process per host core, numpy stage 1 + "
+              f"{'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback on the ROI crop")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, args.gpus),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": workers, "kind": ref.KIND, "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+def gpu_arm(args):
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libnsof has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    nsof = importlib.import_module("nsof_b200")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    eng = nsof.Engine(local)
+    Cn, F = args.clips, args.frames
+    pipe = pipe_mod.SequencePipeline(eng, Cn, F, H, W)
+
+    # synthetic clips, generated on the device, layout [F][C][H][W]
+    frames = torch.empty((F, Cn, H, W), dtype=torch.uint8, device=dev)
+    for c in range(Cn):
+        frames[:, c] = syn.make_clip(1234 + rank * Cn + c, H, W, F, dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = eng.launch_count()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), eng.launch_count() - l0
+
+    pairs_step = pipe.n_pairs
+    # ---- value: device-resident step, clocks sampled during the timed region
+    clk = ClockSampler(local)
+    if rank == 0:
+        clk.start()
+    ms, launches = timed(lambda: pipe.step(frames), args.steps, args.warmup)
+    clocks = clk.stop() if rank == 0 else None
+    value = pairs_step * world * args.steps / (ms * 1e-3)
+    roi_frac = pipe.last_crop_pixels / (pairs_step * H * W)
+    crop_px_step = pipe.last_crop_pixels
+
+    # ---- e2e: pinned host frames in, rectangles + ROI flow crops out, copies inside the timed region
+    pipe.alloc_host()
+    frames_host = torch.empty((F, Cn, H, W), dtype=torch.uint8).pin_memory()
+    frames_host.copy_(frames)
+    ms_e2e, _ = timed(lambda: pipe.step_host(frames_host), args.steps, 1)
+    e2e = {"value": pairs_step * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": int(pipe.last_h2d_bytes), "d2h_bytes_per_step": int(pipe.last_d2h_bytes),
+           "api": "SequencePipeline.step_host (pinned uint8 frames -> rectangles + packed float32 ROI flow)"}
+    return finish(args, locals())
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """Per-launch DRAM traffic of `kernel` from the committed ncu --set full summary, if one exists."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
+def finish(args, L):
+    import importlib
+
+    import torch
+    eng, pipe, frames, rank, world, dev = L["eng"], L["pipe"], L["frames"], L["rank"], L["world"], L["dev"]
+    timed, Cn, F = L["timed"], L["Cn"], L["F"]
+    peak, peak_src = measured_peak()
+    extras = {}
+    # ---- per-kernel leg: CUDA event pair around every launch of a few extra steps (not part of `value`)
+    eng.profile(True)
+    for _ in range(2):
+        pipe.step(frames)
+    eng.profile(False)
+    stats = eng.profile_read()
+    tot_ms = sum(s["ms"] for s in stats.values()) or 1.0
+    kernels = {k: {"launches": s["launches"] // 2, "ms_per_step": s["ms"] / 2, "share": s["ms"] / tot_ms,
+                   "algorithmic_GB_per_step": s["algorithmic_bytes"] / 2 / 1e9,
+                   "achieved_GBps": (s["algorithmic_bytes"] / (s["ms"] * 1e-3) / 1e9) if s["ms"] > 0 else None}
+               for k, s in stats.items()}
+    dom = max(stats, key=lambda k: stats[k]["ms"])
+    ach = stats[dom]["algorithmic_bytes"] / (stats[dom]["ms"] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": ncu_traffic(dom), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": stats[dom]["algorithmic_bytes"] / stats[dom]["launches"],
+                "avg_launch_ms": stats[dom]["ms"] / stats[dom]["launches"]}
+    fb_bytes = sum(s["algorithmic_bytes"] for k, s in stats.items() if k.startswith("fb_")) / 2
+    fb_ms = sum(s["ms"] for k, s in stats.items() if k.startswith("fb_")) / 2
+    extras["stage2_all_kernels"] = {"algorithmic_GB_per_step": fb_bytes / 1e9, "ms_per_step": fb_ms,
+                                    "achieved_GBps": fb_bytes / (fb_ms * 1e-3) / 1e9 if fb_ms else None,
+                                    "frac_of_peak": fb_bytes / (fb_ms * 1e-3) / 1e9 / peak if fb_ms else None}
+    # ---- ROI = 100 % leg (full-frame Farneback, the configuration the >= 50 % roofline target is stated on)
+    if not args.no_extras:
+        pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+        del pipe.flow
+        torch.cuda.empty_cache()
+        ff_clips = min(Cn, 4)
+        pf = pipe_mod.SequencePipeline(eng, ff_clips, F, H, W, full_frame=True)
+        ff_frames = frames[:, :ff_clips].contiguous()
+        ms_ff, _ = timed(lambda: pf.step(ff_frames), max(2, args.steps // 2), 2)
+        n_ff = max(2, args.steps // 2) * pf.n_pairs
+        bytes_pair = eng.algorithmic_bytes(H, W)
+        extras["full_frame"] = {"value": n_ff * world / (ms_ff * 1e-3), "unit": UNIT,
+                                "algorithmic_MB_per_pair": bytes_pair / 1e6,
+                                "achieved_GBps_per_gpu": n_ff * bytes_pair / (ms_ff * 1e-3) / 1e9,
+                                "frac_of_peak": n_ff * bytes_pair / (ms_ff * 1e-3) / 1e9 / peak,
+                                "pairs_per_step_per_gpu": pf.n_pairs}
+    if rank != 0:
+        return 0
+    line = {"metric": METRIC, "value": L["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": L["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+            "clocks": L["clocks"], "e2e": L["e2e"], "gpu_launches": int(L["launches"]), "roofline": roofline,
+            "roi_fraction_of_frame": L["roi_frac"], "kernels": kernels, **extras}
+    line["config"]["parallelism"] = f"sequence-parallel x{world}"
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_leg(frames[:, 0].cpu().numpy())
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    rc = gpu_arm(args)
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+    return rc
+
+
+if __name__ == "__main__":
+    sys.exit(main())

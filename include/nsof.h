@@ -73,6 +73,22 @@ NSOF_API int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_item
 /* Bytes of device workspace currently held. */
 NSOF_API size_t nsof_workspace_bytes(const nsof_handle *h);
 
+/* ---- launch accounting ------------------------------------------------------------------- */
+/* Kernels launched on this handle since nsof_create (bench.py's gpu_launches). */
+NSOF_API unsigned long long nsof_launch_count(const nsof_handle *h);
+/* Optional per-launch timing: nsof_profile(h, 1) synchronises, clears the records and brackets every
+ * following kernel launch with a CUDA event pair on its stream; nsof_profile(h, 0) stops;
+ * nsof_profile_read() synchronises and returns one row per kernel class that ran: launches, summed
+ * device time, summed algorithmic bytes (the DESIGN.md byte model).  Used by bench.py's roofline leg. */
+typedef struct nsof_kernel_stat {
+    char name[32];
+    int launches;
+    double ms;
+    double algorithmic_bytes;
+} nsof_kernel_stat;
+NSOF_API int nsof_profile(nsof_handle *h, int enable);
+NSOF_API int nsof_profile_read(nsof_handle *h, nsof_kernel_stat *out, int max_out, int *n_out);
+
 /* ---- stage 2: dense Farneback ----------------------------------------------------------- */
 /* Replaces cv2.calcOpticalFlowFarneback(prev_region, next_region, None, **farneback_params)
  * (optical_flow_seg.py:158, 203, 494; optical_flow_ob.py:225, 270, 616;

@@ -56,6 +56,10 @@ class FrameSimParams(C.Structure):
                 ("vds", C.c_double)]
 
 
+class KernelStat(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("launches", C.c_int), ("ms", C.c_double), ("algorithmic_bytes", C.c_double)]
+
+
 _P = C.POINTER
 _SIGNATURES = {
     # name: (restype, argtypes)
@@ -65,6 +69,9 @@ _SIGNATURES = {
     "nsof_destroy": (C.c_int, [C.c_void_p]),
     "nsof_reserve": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int]),
     "nsof_workspace_bytes": (C.c_size_t, [C.c_void_p]),
+    "nsof_launch_count": (C.c_ulonglong, [C.c_void_p]),
+    "nsof_profile": (C.c_int, [C.c_void_p, C.c_int]),
+    "nsof_profile_read": (C.c_int, [C.c_void_p, _P(KernelStat), C.c_int, _P(C.c_int)]),
     "nsof_farneback_batch": (C.c_int, [C.c_void_p, _P(CropDesc), C.c_int, _P(FbParams), C.c_void_p]),
     "nsof_farneback_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_ssize_t,
                                     _P(FbParams), C.c_void_p, C.c_ssize_t, C.c_void_p]),

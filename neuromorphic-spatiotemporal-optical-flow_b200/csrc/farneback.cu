@@ -107,6 +107,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
         if (s.host) cudaFreeHost(s.host);
         if (s.done) cudaEventDestroy(s.done);
     }
+    for (auto e : h->prof_pool) cudaEventDestroy(e);
     delete h->last_plan;
     delete h;
     return NSOF_OK;
@@ -115,6 +116,50 @@ extern "C" int nsof_destroy(nsof_handle *h)
 extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 {
     return h ? h->arena.bytes + h->tables.bytes + h->io.bytes + h->s1.bytes : 0;
+}
+
+// ------------------------------------------------------------------------------ launch accounting
+const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
+    "fb_pyr", "fb_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
+    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance"};
+
+extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
+
+extern "C" int nsof_profile(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_profile: NULL handle");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    NSOF_CUDA_TRY(cudaDeviceSynchronize());
+    h->prof_on = enable != 0;
+    if (enable) {
+        h->prof_used = 0;
+        h->prof_recs.clear();
+    }
+    return NSOF_OK;
+}
+
+extern "C" int nsof_profile_read(nsof_handle *h, nsof_kernel_stat *out, int max_out, int *n_out)
+{
+    if (!h || !out || !n_out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_profile_read: NULL argument");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    NSOF_CUDA_TRY(cudaDeviceSynchronize());
+    nsof_kernel_stat acc[NSOF_K_CLASSES];
+    memset(acc, 0, sizeof(acc));
+    for (const NsofProfRec &r : h->prof_recs) {
+        float ms = 0.f;
+        NSOF_CUDA_TRY(cudaEventElapsedTime(&ms, h->prof_pool[r.ev], h->prof_pool[r.ev + 1]));
+        acc[r.cls].launches += 1;
+        acc[r.cls].ms += ms;
+        acc[r.cls].algorithmic_bytes += r.bytes;
+    }
+    int n = 0;
+    for (int c = 0; c < NSOF_K_CLASSES && n < max_out; c++) {
+        if (!acc[c].launches) continue;
+        snprintf(acc[c].name, sizeof(acc[c].name), "%s", nsof_kernel_class_names[c]);
+        out[n++] = acc[c];
+    }
+    *n_out = n;
+    return NSOF_OK;
 }
 
 // ------------------------------------------------------------------------------ geometry (A.1)
@@ -285,12 +330,9 @@ static bool pick_blur_tile(int m, int *TW, int *TH, size_t *smem)
 
 extern "C" double nsof_fb_algorithmic_bytes(int h, int w, const nsof_fb_params *p)
 {
-    // DESIGN.md byte model: per level k (N_k pixels, N_0 source pixels, T iterations):
-    //   pyramid   : read 2*N_0 (uint8 x2)        write 8*N_k  (I0, I1)
-    //   polyexp   : read 8*N_k                    write 40*N_k (R0, R1)
-    //   um_first  : read 40*N_k + 8*N_{k+1}       write 20*N_k (M)
-    //   iteration : read 20 (M) + 40 (R0,R1)      write 20*N_k (M')   x (T-1)
-    //   last      : read 20*N_k                   write 8*N_k  (flow)
+    // DESIGN.md byte model == SURVEY.md 8(d): per level k (N_k pixels, N_0 source pixels, T iterations), with I
+    // never in HBM:   2*N_0 (uint8 sources) + 40*N_k (write R0,R1) + 60*N_k + 8*N_{k+1} (first UpdateMatrices)
+    //                 + 80*N_k*(T-1) (read M,R0,R1; write M) + 28*N_k (read M, write flow)
     if (!p || h < 1 || w < 1) return 0.;
     int hk[64], wk[64];
     const int S = nsof_fb_level_geometry(h, w, p->pyr_scale, p->levels, hk, wk, nullptr, nullptr);
@@ -299,14 +341,9 @@ extern "C" double nsof_fb_algorithmic_bytes(int h, int w, const nsof_fb_params *
     for (int k = 0; k < S; k++) {
         const double Nk = (double)hk[k] * wk[k];
         const double Nc = k + 1 < S ? (double)hk[k + 1] * wk[k + 1] : 0.;
-        bytes += 2 * N0 + 8 * Nk + 8 * Nk + 40 * Nk;
-        if (p->iterations > 0) {
-            bytes += 40 * Nk + 8 * Nc + 20 * Nk;
-            bytes += 80 * Nk * (p->iterations - 1);
-            bytes += 28 * Nk;
-        } else {
-            bytes += 8 * Nc + 8 * Nk;
-        }
+        bytes += 2 * N0 + 40 * Nk;
+        if (p->iterations > 0) bytes += 60 * Nk + 8 * Nc + 80 * Nk * (p->iterations - 1) + 28 * Nk;
+        else bytes += 8 * Nc + 8 * Nk;
     }
     return bytes;
 }
@@ -424,6 +461,7 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     if (rc) return rc;
     unsigned char *hs = (unsigned char *)slot->host;
     unsigned char *ds = (unsigned char *)h->tables.p;
+    std::vector<double> sumN(max_scales + 1, 0.), sumN0(max_scales, 0.);
     std::vector<int> max_tiles_pyr(max_scales, 0), max_tiles_pe(max_scales, 0), max_tiles_um(max_scales, 0),
         max_tiles_bs(max_scales, 0);
     const int m = params->winsize / 2;
@@ -461,6 +499,8 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             else { J.flow = (float2 *)fl_this; J.fpitch = J.pitch; }
             J.cflow = (const float2 *)fl_coarse;
             jobs[a++] = J;
+            sumN[k] += (double)J.h * J.w;
+            sumN0[k] += (double)J.sh * J.sw;
             auto tiles = [&](int tw, int th) { return ((J.w + tw - 1) / tw) * ((J.h + th - 1) / th); };
             max_tiles_pyr[k] = std::max(max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH));
             max_tiles_pe[k] = std::max(max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH));
@@ -486,15 +526,25 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
         const int na = n_active[k];
         int iters = params->iterations;
         if (k == stop_level && h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
-        NSOF_LAUNCH(k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, ksize[k] / 2);
-        NSOF_LAUNCH(k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream, jobs, pc);
+        // algorithmic bytes per launch: the per-level terms of nsof_fb_algorithmic_bytes, summed over the batch;
+        // items that have no level k keep the coarse-flow term at zero via sumN of the items that do
+        double Nc = 0.;
+        for (int i = 0; i < n; i++)
+            if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
+        const double Nk = sumN[k];
+        NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * sumN0[k], k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, ksize[k] / 2);
+        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * Nk, k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream, jobs, pc);
         if (params->iterations == 0) {
-            NSOF_LAUNCH(k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs, flow_mul);
+            NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * Nc + 8 * Nk, k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
+                         flow_mul);
         } else {
-            NSOF_LAUNCH(k_fb_um_first, max_tiles_um[k], na, 1, 256, 0, stream, jobs, flow_mul);
-            for (int it = 0; it < iters; it++)
-                NSOF_LAUNCH(k_fb_blur_solve, max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale,
-                            (it & 1) == 0, it == iters - 1);
+            NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * Nk + 8 * Nc, k_fb_um_first, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
+                         flow_mul);
+            for (int it = 0; it < iters; it++) {
+                const bool last = it == iters - 1;
+                NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve,
+                             max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale, (it & 1) == 0, last);
+            }
         }
         NSOF_CUDA_TRY(cudaGetLastError());
     }

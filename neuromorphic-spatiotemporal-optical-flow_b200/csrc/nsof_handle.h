@@ -46,6 +46,20 @@ struct NsofStageSlot {
 
 struct FbItemPlan;  // farneback.cu
 
+// Kernel classes for the launch counter and the optional per-launch event timing (nsof_profile*).
+enum NsofKernelClass {
+    NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
+    NSOF_K_LANCZOS, NSOF_K_FRAME_SIM, NSOF_K_ROI, NSOF_K_EVENT_HIST, NSOF_K_EVENT_REPLAY, NSOF_K_SYNAPSE_STEP,
+    NSOF_K_RESISTANCE, NSOF_K_CLASSES
+};
+extern const char *const nsof_kernel_class_names[NSOF_K_CLASSES];
+
+struct NsofProfRec {
+    int cls;
+    size_t ev;  // index of the start event in the pool; stop event is ev + 1
+    double bytes;
+};
+
 struct nsof_handle {
     int device = 0;
     NsofDevBuf arena;      // I, R, M, coarse flow of every item of the current batch
@@ -64,6 +78,39 @@ struct nsof_handle {
     int last_stop_level = 0;
     nsof_fb_params last_params = {};
     bool smem_configured = false;
+    // launch accounting
+    unsigned long long launches = 0;
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_pool;
+    size_t prof_used = 0;
+    std::vector<NsofProfRec> prof_recs;
 };
+
+// Bracket one kernel launch: counts it, and when profiling is on records a CUDA event pair on `st`.
+static inline void nsof_prof_pre(nsof_handle *h, int cls, double bytes, cudaStream_t st)
+{
+    h->launches++;
+    if (!h->prof_on) return;
+    while (h->prof_pool.size() < h->prof_used + 2) {
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        h->prof_pool.push_back(e);
+    }
+    NsofProfRec r = {cls, h->prof_used, bytes};
+    h->prof_recs.push_back(r);
+    cudaEventRecord(h->prof_pool[h->prof_used], st);
+}
+static inline void nsof_prof_post(nsof_handle *h, cudaStream_t st)
+{
+    if (!h->prof_on) return;
+    cudaEventRecord(h->prof_pool[h->prof_used + 1], st);
+    h->prof_used += 2;
+}
+#define NSOF_KLAUNCH(h, cls, bytes, kern, gx, gy, gz, nt, smem_bytes, stream, ...)  \
+    do {                                                                            \
+        nsof_prof_pre((h), (cls), (bytes), (stream));                               \
+        NSOF_LAUNCH(kern, gx, gy, gz, nt, smem_bytes, stream, __VA_ARGS__);         \
+        nsof_prof_post((h), (stream));                                              \
+    } while (0)
 
 int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **slot);

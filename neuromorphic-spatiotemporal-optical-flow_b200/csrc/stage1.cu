@@ -26,7 +26,7 @@ extern "C" int nsof_event_hist(nsof_handle *h, const int16_t *x, const int16_t *
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     NSOF_CUDA_TRY(cudaMemsetAsync(counts, 0, (size_t)H * W * sizeof(int32_t), st));
     if (n_events) {
-        NSOF_LAUNCH(k_s1_event_hist, blocks_for(n_events, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, n_events, H, W, counts,
+        NSOF_KLAUNCH(h, NSOF_K_EVENT_HIST, 4. * n_events + 4. * H * W, k_s1_event_hist, blocks_for(n_events, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, n_events, H, W, counts,
                     S1_PER_BLOCK);
         NSOF_CUDA_TRY(cudaGetLastError());
     }
@@ -39,7 +39,7 @@ extern "C" int nsof_synapse_step_f32(nsof_handle *h, float *w, const float *V, s
     if (!h || !w || !V || !p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "synapse_step: bad argument");
     if (n == 0) return NSOF_OK;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    NSOF_LAUNCH(k_s1_synapse_step, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, V, n,
+    NSOF_KLAUNCH(h, NSOF_K_SYNAPSE_STEP, 12. * n, k_s1_synapse_step, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, V, n,
                 syn_f32(p, dt), S1_PER_BLOCK);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
@@ -70,12 +70,12 @@ extern "C" int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const in
             const int ns = std::min(32, n_slices - s0);
             const int64_t ne = sb[s0 + ns] - sb[s0];
             if (ne > 0) {
-                NSOF_LAUNCH(k_s1_slice_bits, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, slice_begin + s0,
+                NSOF_KLAUNCH(h, NSOF_K_EVENT_HIST, 4. * ne, k_s1_slice_bits, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, slice_begin + s0,
                             ns, H, W, bits, S1_PER_BLOCK);
             }
             const bool silent_is_idle = !(silent_v < sp.voff) && !(silent_v > sp.von);
             if (ne > 0 || !silent_is_idle) {
-                NSOF_LAUNCH(k_s1_replay_bits, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, bits, npx, ns, active_v,
+                NSOF_KLAUNCH(h, NSOF_K_EVENT_REPLAY, 8. * npx, k_s1_replay_bits, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, bits, npx, ns, active_v,
                             silent_v, sp, S1_PER_BLOCK);
             }
         }
@@ -85,9 +85,9 @@ extern "C" int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const in
             const int64_t ne = sb[s + 1] - sb[s];
             NSOF_CUDA_TRY(cudaMemsetAsync(counts, 0, npx * 4, st));
             if (ne > 0)
-                NSOF_LAUNCH(k_s1_event_hist, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x + sb[s], y + sb[s],
+                NSOF_KLAUNCH(h, NSOF_K_EVENT_HIST, 4. * ne, k_s1_event_hist, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x + sb[s], y + sb[s],
                             (size_t)ne, H, W, counts, S1_PER_BLOCK);
-            NSOF_LAUNCH(k_s1_step_from_counts, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, counts, npx, theta,
+            NSOF_KLAUNCH(h, NSOF_K_EVENT_REPLAY, 12. * npx, k_s1_step_from_counts, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w, counts, npx, theta,
                         active_v, silent_v, sp, S1_PER_BLOCK);
         }
     }
@@ -102,7 +102,7 @@ extern "C" int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n,
     if (n == 0) return NSOF_OK;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     const double lam = log(p->Roff / p->Ron);
-    NSOF_LAUNCH(k_s1_resistance_exp, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, n, p->Ron,
+    NSOF_KLAUNCH(h, NSOF_K_RESISTANCE, 12. * n, k_s1_resistance_exp, blocks_for(n, S1_PER_BLOCK), 1, 1, S1_NT, 0, (cudaStream_t)cuda_stream, w, n, p->Ron,
                 lam, R, S1_PER_BLOCK);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
@@ -187,9 +187,9 @@ extern "C" int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, 
     if (rc) return rc;
     double *tmp = (double *)h->s1.p;
     const int cols = 256;
-    NSOF_LAUNCH(k_s1_lanczos_rows, (W + cols - 1) / cols, Hc, n, S1_NT, 0, st, frames, pitch, frame_stride, W, Hc, d_wy, d_iy,
+    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, (double)n * H * W, k_s1_lanczos_rows, (W + cols - 1) / cols, Hc, n, S1_NT, 0, st, frames, pitch, frame_stride, W, Hc, d_wy, d_iy,
                 Py, tmp, cols);
-    NSOF_LAUNCH(k_s1_lanczos_cols, n, 1, 1, S1_NT, 0, st, tmp, W, Hc, Wc, d_wx, d_ix, Px, cells);
+    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, 0., k_s1_lanczos_cols, n, 1, 1, S1_NT, 0, st, tmp, W, Hc, Wc, d_wx, d_ix, Px, cells);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
 }
@@ -209,7 +209,7 @@ extern "C" int nsof_frame_sim_step_f64(nsof_handle *h, const double *cells_prev,
     const size_t total = (size_t)n * Hc * Wc;
     // few cells, long dependent chains: small blocks so the cells spread over many SMs
     const int per_block = 32;
-    NSOF_LAUNCH(k_s1_frame_step, blocks_for(total, per_block), 1, 1, 32, 0, (cudaStream_t)cuda_stream, cells_prev, cells_next,
+    NSOF_KLAUNCH(h, NSOF_K_FRAME_SIM, 40. * total, k_s1_frame_step, blocks_for(total, per_block), 1, 1, 32, 0, (cudaStream_t)cuda_stream, cells_prev, cells_next,
                 w, current_out, total, c, per_block);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
@@ -242,7 +242,7 @@ extern "C" int nsof_roi_from_state_f64(nsof_handle *h, const double *currents, i
         NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_roi, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         g_roi_smem_set = true;
     }
-    NSOF_LAUNCH(k_s1_roi, n, 1, 1, 128, smem, (cudaStream_t)cuda_stream, currents, *p, thr_table, memimg, labels,
+    NSOF_KLAUNCH(h, NSOF_K_ROI, (double)n * p->cells_h * p->cells_w * 13., k_s1_roi, n, 1, 1, 128, smem, (cudaStream_t)cuda_stream, currents, *p, thr_table, memimg, labels,
                 n_components, n_rects, rects, stats);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;

@@ -238,6 +238,21 @@ class Engine:
         p = _fb_params(**kw)
         return float(self.lib.nsof_fb_algorithmic_bytes(int(h), int(w), C.byref(p)))
 
+    # launch accounting (bench.py)
+    def launch_count(self) -> int:
+        return int(self.lib.nsof_launch_count(self.handle))
+
+    def profile(self, enable: bool):
+        self.lib.check(self.lib.nsof_profile(self.handle, 1 if enable else 0), "nsof_profile")
+
+    def profile_read(self):
+        """-> {kernel class: dict(launches, ms, algorithmic_bytes)} for the launches since profile(True)."""
+        rows = (_lib.KernelStat * 32)()
+        n = C.c_int()
+        self.lib.check(self.lib.nsof_profile_read(self.handle, rows, 32, C.byref(n)), "nsof_profile_read")
+        return {rows[i].name.decode(): dict(launches=rows[i].launches, ms=rows[i].ms,
+                                            algorithmic_bytes=rows[i].algorithmic_bytes) for i in range(n.value)}
+
     # test hooks
     def debug_truncate(self, stop_level=-1, stop_iters=-1):
         self.lib.check(self.lib.nsof_debug_truncate(self.handle, stop_level, stop_iters))

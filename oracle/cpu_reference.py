@@ -1,0 +1,101 @@
+"""cpu_reference.py -- TEST / BASELINE INFRASTRUCTURE ONLY: the reference's CPU path for one clip, timed by
+bench.py's `cpu_baseline` leg and `--impl reference` arm and used by tests as the end-to-end checker.
+
+Path per frame pair, as the reference runs it on the host (optical_flow_seg.py:413-461):
+  stage 1  frame-mode synapse simulator (simulation/simulationcode_v4_transistor_vehicle.m, numpy restatement in
+           stage1_oracle.py -- there is no MATLAB on these boxes) -> current -> uint8 map -> transition_pic ->
+           4-connected components -> merged rectangle (FLAG 2)
+  stage 2  cv2.calcOpticalFlowFarneback on the crop (the reference's own call; `kind` = "reference"); when cv2
+           cannot be imported, the C restatement oracle/farneback_oracle.c (`kind` = "port").
+The product path never imports this module.
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(_HERE))
+from oracle import stage1_oracle as s1  # noqa: E402
+
+FARNEBACK_PARAMS = dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0)
+GRASP = dict(MEMSIZE=80, THRES=250, ext=(20, 20, 20, 20))
+
+try:
+    import cv2
+    KIND = "reference"
+except Exception:  # pragma: no cover
+    cv2 = None
+    KIND = "port"
+
+_oracle = None
+
+
+def farneback(prev, nxt, **p):
+    global _oracle
+    if cv2 is not None:
+        return cv2.calcOpticalFlowFarneback(prev, nxt, None, **p)
+    if _oracle is None:
+        sys.path.insert(0, os.path.join(os.path.dirname(_HERE), "tests"))
+        import helpers
+        _oracle = helpers.load_oracle()
+    return _oracle.farneback(np.ascontiguousarray(prev), np.ascontiguousarray(nxt), **p)
+
+
+def clip_rects(frames, cfg=GRASP, sim=None):
+    """Stage 1 for one clip (F, H, W) uint8 -> (memimg (F-1, Hc, Wc), rects list of (x0,y0,x1,y1) or None)."""
+    sim = sim or {}
+    M = cfg["MEMSIZE"]
+    H, W = frames.shape[1:]
+    cells = np.stack([s1.compress_image(f, M, M) for f in frames])
+    _, cur = s1.simulate_memristor_array_vec(cells, **sim)
+    memimg = s1.current_to_u8(cur[1:])  # slice t = state after pair (t, t+1)
+    rects = []
+    for t in range(len(frames) - 1):
+        n, _, _, r = s1.roi_from_memimg(memimg[t], (H, W), M, M, cfg["THRES"], cfg["ext"], 2)
+        rects.append(r[0] if r else None)
+    return memimg, rects
+
+
+def process_clip(frames, cfg=GRASP, params=FARNEBACK_PARAMS, full_frame=False, keep_flow=False, sim=None):
+    """The reference path over one clip.  Returns (pairs, seconds, rects, flows or None)."""
+    t0 = time.perf_counter()
+    F, H, W = frames.shape
+    flows = []
+    if full_frame:
+        rects = [(0, 0, W, H)] * (F - 1)
+    else:
+        _, rects = clip_rects(frames, cfg, sim)
+    for t in range(F - 1):
+        flow = np.zeros((H, W, 2))  # optical_flow_seg.py:215
+        r = rects[t]
+        if r is not None:
+            x0, y0, x1, y1 = r
+            a, b = frames[t, y0:y1, x0:x1], frames[t + 1, y0:y1, x0:x1]
+            if a.size > 0:
+                flow[y0:y1, x0:x1] = farneback(a, b, **params)
+        if keep_flow:
+            flows.append(flow)
+    return F - 1, time.perf_counter() - t0, rects, (flows if keep_flow else None)
+
+
+def _worker(args):
+    frames, full_frame = args
+    if cv2 is not None:
+        cv2.setNumThreads(1)
+    n, dt, _, _ = process_clip(frames, full_frame=full_frame)
+    return n
+
+
+def process_clips_parallel(clips, workers, full_frame=False):
+    """clips: list of (F, H, W) arrays, one task each, over a fork pool of `workers` processes.
+    Returns (pairs, wall seconds)."""
+    import multiprocessing as mp
+    t0 = time.perf_counter()
+    if workers <= 1:
+        n = sum(_worker((c, full_frame)) for c in clips)
+    else:
+        with mp.get_context("fork").Pool(workers) as pool:
+            n = sum(pool.map(_worker, [(c, full_frame) for c in clips]))
+    return n, time.perf_counter() - t0

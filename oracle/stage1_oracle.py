@@ -248,3 +248,29 @@ def simulate_memristor_array(compressed, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1
                 w[y, x] = wv
         cur.append(vds / R(w))
     return w, np.stack(cur)
+
+
+def simulate_memristor_array_vec(compressed, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS, vds=1.0):
+    """Same recurrence as simulate_memristor_array, vectorised over the cells (the sub-step loop stays
+    sequential).  Used as the timed CPU baseline of stage 1; tests check it equals the scalar version."""
+    compressed = np.asarray(compressed, np.float64)
+    T = compressed.shape[0]
+    dt_sub = dt / nSubSteps
+    w = p["wini"] * np.ones(compressed.shape[1:])
+    lam = np.log(p["Roff"] / p["Ron"])
+    R = lambda w_: p["Ron"] / np.exp(-lam * (1 - w_))
+    cur = [vds / R(w)]
+    for i in range(T - 1):
+        diff = calculate_difference_matrix(compressed[i] * 256, compressed[i + 1] * 256, th1, th2)
+        vm = -np.where(diff > 0, 0.3 * diff + 0, np.where(diff < 0, 3 * diff + -3, 0.0))
+        off, on = vm < p["voff"], vm > p["von"]
+        g_off = p["koff"] * (vm[off] / p["voff"] - 1) ** p["alphaoff"]
+        g_on = p["kon"] * (vm[on] / p["von"] - 1) ** p["alphaon"]
+        w_off, w_on = w[off], w[on]
+        for _ in range(nSubSteps):
+            w_off = np.clip(w_off + g_off * (1 - w_off * p["soff"]) ** p["boff"] * dt_sub, 0.0, 1.0)
+            w_on = np.clip(w_on + g_on * (1 - w_on * p["son"]) ** p["bon"] * dt_sub, 0.0, 1.0)
+        w = w.copy()
+        w[off], w[on] = w_off, w_on
+        cur.append(vds / R(w))
+    return w, np.stack(cur)

@@ -1,0 +1,263 @@
+"""Parity tests proper: libnsof (sm_100a CUDA) through its C ABI against the oracle and the golden vectors
+produced by the reference's own code (cv2 4.13 Farneback, the scripts' ROI functions, eventsim).  Run on the
+B200 box with `pytest -m gpu`.  Nothing here reads /root/reference."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle import stage1_oracle as s1
+
+pytestmark = pytest.mark.gpu
+
+
+def test_gpu_library_is_the_cuda_build(gpu_engine, nsof):
+    assert gpu_engine.lib.path.endswith("csrc/libnsof.so")
+    assert not gpu_engine._emulated
+
+
+# ------------------------------------------------------------------------------------------- stage 2
+@pytest.mark.parametrize("pname", list(helpers.PARAM_SETS))
+def test_farneback_vs_cv2_golden(gpu_engine, golden, pname):
+    p = helpers.PARAM_SETS[pname]
+    for case in golden.fb["cases"]:
+        prev, nxt = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"]
+        got = gpu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
+        helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"gpu vs cv2 {case}")
+
+
+def test_stage_dumps_vs_oracle(gpu_engine, oracle):
+    """Every intermediate (I, R0, R1, M, per-iteration flow) of every level against the oracle's dump."""
+    prev, nxt = helpers.textured_pair(5, 150, 203)
+    p = helpers.PARAM_SETS["grasp"]
+    _, st = oracle.farneback(prev, nxt, **p, dump=True)
+    geo = oracle.level_geometry(150, 203, p["pyr_scale"], p["levels"])
+    try:
+        for k, (hk, wk, _, _) in enumerate(geo):
+            for it in (0, 1, p["iterations"]):
+                gpu_engine.debug_truncate(k, it)
+                gpu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
+                if it == 0:
+                    for what, tag in ((2, 2), (3, 3), (4, 4)):
+                        got = helpers.planar_to_aos(gpu_engine.debug_fetch(0, what, hk, wk))
+                        want = st[(tag, k, 0)]
+                        scale = max(1.0, float(np.abs(want).max()))
+                        assert np.abs(got - want).max() <= 5e-5 * scale, (k, what)
+                else:
+                    got = gpu_engine.debug_fetch(0, 5, hk, wk)
+                    want = st[(5, k, it - 1)]
+                    assert np.abs(got - want).max() <= 2e-4, (k, it)
+    finally:
+        gpu_engine.debug_truncate(-1, -1)
+
+
+def test_batch_ragged_and_strided(gpu_engine, oracle):
+    p = helpers.PARAM_SETS["grasp"]
+    big_a, big_b = helpers.textured_pair(11, 240, 320)
+    views = [(slice(0, 240), slice(0, 320)), (slice(13, 140), slice(7, 96)), (slice(100, 133), slice(20, 300)),
+             (slice(200, 208), slice(300, 308)), (slice(5, 6), slice(0, 320)), (slice(0, 240), slice(9, 10))]
+    pairs = [(big_a[v], big_b[v]) for v in views]  # non-contiguous views, like the reference's crops
+    flows = gpu_engine.farneback_batch(pairs, **p)
+    for (a, b), f in zip(pairs, flows):
+        want = oracle.farneback(np.ascontiguousarray(a), np.ascontiguousarray(b), **p)
+        helpers.assert_flow_close(f, want, "grasp", "gpu batch")
+        single = gpu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+        assert np.array_equal(single, f)  # batching never changes a crop's result
+
+
+@pytest.mark.parametrize("hw", [(1080, 1920), (1920, 1080), (801, 801)])
+def test_full_frame_vs_oracle(gpu_engine, oracle, hw):
+    """BASELINE.json sizes: 1080p (both orientations: grasp frames are 1920 rows x 1080 cols) and autodriving."""
+    p = helpers.PARAM_SETS["grasp"]
+    a, b = helpers.textured_pair(21, *hw)
+    got = gpu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+    want = oracle.farneback(a, b, **p)
+    epe, mx = helpers.assert_flow_close(got, want, "grasp", f"gpu {hw}")
+    # known answer: content moves by (+3, -1.5); the interior of the field recovers it
+    med = np.median(got[200:-200, 200:-200].reshape(-1, 2), axis=0)
+    assert abs(med[0] - 3.0) < 0.15 and abs(med[1] + 1.5) < 0.15, med
+
+
+def test_full_size_properties(gpu_engine):
+    """Size-independent properties at 1080p: identical frames -> exactly zero flow; determinism; a crop computed
+    inside a batch equals the same crop computed alone, bit for bit."""
+    p = helpers.PARAM_SETS["grasp"]
+    a, b = helpers.textured_pair(22, 1080, 1920)
+    z = gpu_engine.calcOpticalFlowFarneback(a, a, None, **p)
+    assert not z.any()
+    f1 = gpu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+    f2 = gpu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+    assert np.array_equal(f1, f2)
+    crops = [(a[100:700, 300:1500], b[100:700, 300:1500]), (a, b), (a[500:560, 40:1900], b[500:560, 40:1900])]
+    flows = gpu_engine.farneback_batch(crops, **p)
+    assert np.array_equal(flows[1], f1)
+    assert np.array_equal(flows[0], gpu_engine.calcOpticalFlowFarneback(*crops[0], None, **p))
+    # swapping the frames flips the sign of a pure translation (interior, first order)
+    g = gpu_engine.calcOpticalFlowFarneback(b, a, None, **p)
+    inner = (slice(300, -300), slice(300, -300))
+    assert np.abs(np.median((f1[inner] + g[inner]).reshape(-1, 2), axis=0)).max() < 0.1
+
+
+def test_device_pointer_entry_and_pitched_output(gpu_engine, oracle):
+    """nsof_farneback_batch on device pointers (torch tensors as plain memory), flow written into a pitched frame."""
+    import torch
+    p = helpers.PARAM_SETS["grasp"]
+    a, b = helpers.textured_pair(23, 300, 400)
+    da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.zeros((300, 400, 2), dtype=torch.float32, device="cuda")
+    y0, y1, x0, x1 = 40, 260, 64, 360
+    crop = (da.data_ptr() + y0 * 400 + x0, db.data_ptr() + y0 * 400 + x0, y1 - y0, x1 - x0, 400, 400,
+            out.data_ptr() + (y0 * 400 + x0) * 8, 400 * 8)
+    gpu_engine.farneback_batch_device([crop], torch.cuda.current_stream().cuda_stream, **p)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    want = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(b[y0:y1, x0:x1]), **p)
+    helpers.assert_flow_close(got[y0:y1, x0:x1], want, "grasp", "device crop")
+    outside = np.ones((300, 400), bool)
+    outside[y0:y1, x0:x1] = False
+    assert not got[outside].any()
+
+
+def test_errors_mirror_cv2(gpu_engine, nsof):
+    a = np.zeros((40, 40), np.uint8)
+    p = dict(helpers.PARAM_SETS["grasp"])
+    with pytest.raises(nsof.error):
+        gpu_engine.calcOpticalFlowFarneback(a[:0], a[:0], None, **p)
+    with pytest.raises(nsof.error):
+        gpu_engine.calcOpticalFlowFarneback(a, a[:, :20], None, **p)
+    with pytest.raises(nsof.error):
+        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
+    with pytest.raises(NotImplementedError):
+        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=256))
+    z = gpu_engine.calcOpticalFlowFarneback(a, a, None, **p)
+    assert z.shape == (40, 40, 2) and z.dtype == np.float32 and not z.any()
+
+
+# ------------------------------------------------------------------------------------------- stage 1
+@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801))])
+def test_roi_bit_exact_vs_reference(gpu_engine, nsof, golden, ds, cfgname, hw):
+    cfg = getattr(nsof.RoiConfig, cfgname)()
+    cur = golden.roi[f"{ds}__currents"]
+    for flag in (1, 2):
+        cfg.FLAG = flag
+        r = gpu_engine.roi_from_currents(cur, hw, cfg=cfg)
+        assert np.array_equal(r["memimg"], golden.roi[f"{ds}__memimg"])
+        assert np.array_equal(r["labels"], golden.roi[f"{ds}__labels"])
+        for t in range(cur.shape[0]):
+            n = int(golden.roi[f"{ds}__flag{flag}__nrect"][t])
+            assert r["rects"][t] == [tuple(v) for v in golden.roi[f"{ds}__flag{flag}__rects"][t, :n]]
+            assert np.array_equal(r["stats"][t], golden.roi[f"{ds}__stats"][t, :len(r["stats"][t])])
+        if flag == 1:
+            assert np.array_equal(r["num_labels"], golden.roi[f"{ds}__num_labels"])
+
+
+def test_cc_random_masks_vs_cv2(gpu_engine, nsof, golden):
+    masks = golden.roi["random__masks"]
+    cfg = nsof.RoiConfig(THRES=255, MEMSIZE=1, EXTEND_WIDTH_LEFT=0, EXTEND_WIDTH_RIGHT=0, EXTEND_HEIGHT_UPPER=0,
+                         EXTEND_HEIGHT_LOWER=0, FLAG=1)
+    r = gpu_engine.roi_from_memimg(masks, masks.shape[1:], 1, 1, cfg)
+    assert np.array_equal(r["labels"], golden.roi["random__labels"])
+    assert np.array_equal(r["num_labels"], golden.roi["random__num_labels"])
+    for i in range(len(masks)):
+        n = int(golden.roi["random__num_labels"][i]) - 1
+        assert np.array_equal(r["stats"][i], golden.roi["random__stats"][i, :n])
+
+
+def test_cc_large_grid_vs_oracle(gpu_engine, nsof):
+    """Maximum cell grids (8K frame at MEMSIZE 80 -> 54 x 96) with snake-shaped components (worst case for
+    label propagation)."""
+    rng = np.random.default_rng(5)
+    masks = (rng.random((6, 54, 96)) < 0.55).astype(np.uint8) * 255
+    snake = np.zeros((54, 96), np.uint8)
+    snake[::2] = 255
+    snake[1::4, -1] = 255
+    snake[3::4, 0] = 255
+    masks[0] = snake
+    cfg = nsof.RoiConfig(THRES=255, MEMSIZE=1, EXTEND_WIDTH_LEFT=0, EXTEND_WIDTH_RIGHT=0, EXTEND_HEIGHT_UPPER=0,
+                         EXTEND_HEIGHT_LOWER=0, FLAG=2)
+    r = gpu_engine.roi_from_memimg(masks, masks.shape[1:], 1, 1, cfg)
+    for i in range(len(masks)):
+        n, labels, stats = s1.connected_components_4(masks[i])
+        assert r["num_labels"][i] == n and np.array_equal(r["labels"][i], labels)
+
+
+def test_opticalflow3d_matches_reference_structure(gpu_engine, nsof, golden, oracle):
+    cfg = nsof.RoiConfig.autodriving()
+    memimg = golden.roi["autodriving__memimg"]
+    t = int(np.argmax(golden.roi["autodriving__flag2__nrect"]))
+    a, b = helpers.textured_pair(3, 801, 801)
+    flow, cal, vel, region_list, info = gpu_engine.opticalFlow3D(memimg[t], memimg[t], a, b, cfg.MEMSIZE, cfg.MEMSIZE, cfg)
+    x0, y0, x1, y1 = info
+    assert info == tuple(golden.roi["autodriving__flag2__rects"][t, 0])
+    assert flow.dtype == np.float64 and flow.shape == (801, 801, 2)
+    want = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(b[y0:y1, x0:x1]), **cfg.farneback_params)
+    helpers.assert_flow_close(flow[y0:y1, x0:x1].astype(np.float32), want, "grasp", "opticalFlow3D crop")
+    outside = np.ones((801, 801), bool)
+    outside[y0:y1, x0:x1] = False
+    assert not flow[outside].any()
+    t0 = int(np.argmin(golden.roi["autodriving__flag2__nrect"]))
+    res = gpu_engine.opticalFlow3D(memimg[t0], memimg[t0], a, b, cfg.MEMSIZE, cfg.MEMSIZE, cfg)
+    assert not res[0].any() and res[4] == (0, 0, 0, 0)
+
+
+def test_events_vs_reference(gpu_engine, golden):
+    ev = golden.ev
+    x, y, t = ev["x"], ev["y"], ev["t"]
+    H, W = int(ev["H"]), int(ev["W"])
+    b = ev["slice_bounds"]
+    for k, i in enumerate(ev["hist_slices"]):
+        sl = slice(b[i], b[i + 1])
+        assert np.array_equal(gpu_engine.bincount_2d(x[sl], y[sl], H, W), ev["hist"][k])  # integer: bit-exact
+    # duplicates: every event on one pixel
+    assert gpu_engine.bincount_2d(np.full(5000, 7), np.full(5000, 3), H, W)[3, 7] == 5000
+    assert not gpu_engine.bincount_2d(np.zeros(0, np.int16), np.zeros(0, np.int16), H, W).any()
+    got = gpu_engine.update_state(ev["us_w0"], ev["us_V0"])
+    # float32 powf: CUDA's is not bit-identical to numpy's (neither is correctly rounded); tolerance 4 ulp of 1.0
+    assert np.abs(got - ev["us_w1"]).max() <= 4 * np.finfo(np.float32).eps
+    w = gpu_engine.simulate_scheme1(x, y, t, H, W, 1000)
+    assert np.abs(w - ev["w_snaps"][-1]).max() <= 2e-6
+    assert np.array_equal(w != np.float32(0.5), ev["w_snaps"][-1] != np.float32(0.5))  # same set of touched pixels
+    w64 = gpu_engine.simulate_scheme1(x[:b[64]], y[:b[64]], t[:b[64]], H, W, 1000, silent_v=0.5)
+    assert np.abs(w64 - ev["w_decay64"]).max() <= 2e-5
+    R = gpu_engine.resistance_exp(ev["w_snaps"][-1])
+    assert R.dtype == np.float64 and np.allclose(R, ev["R_final"], rtol=1e-12)
+
+
+def test_event_state_to_mask_has_no_flip(gpu_engine, nsof, golden):
+    """The float32 state differs from numpy's by ulps; the thresholded ROI mask must not."""
+    ev = golden.ev
+    H, W = int(ev["H"]), int(ev["W"])
+    w = gpu_engine.simulate_scheme1(ev["x"], ev["y"], ev["t"], H, W, 1000)
+    cur_gpu = 1.0 / gpu_engine.resistance_exp(w)
+    cur_ref = 1.0 / ev["R_final"]
+    for thres in (200, 226, 230, 250):
+        assert np.array_equal(s1.current_to_u8(cur_gpu) >= thres, s1.current_to_u8(cur_ref) >= thres)
+
+
+def test_frame_mode_vs_oracle(gpu_engine):
+    rng = np.random.default_rng(0)
+    frames = rng.integers(0, 256, (3, 161, 203), dtype=np.uint8)
+    cells = gpu_engine.compress_images(frames, 40, 40)
+    for i in range(3):
+        assert np.allclose(cells[i], s1.compress_image(frames[i], 40, 40), rtol=0, atol=1e-13)
+    seq = np.clip(0.5 + 0.02 * rng.standard_normal((4, 3, 5)), 0, 1)
+    w, cur = gpu_engine.simulate_memristor_array(seq, nSubSteps=1000)
+    w_o, cur_o = s1.simulate_memristor_array(seq, nSubSteps=1000)
+    assert np.allclose(w, w_o, rtol=0, atol=1e-10) and np.allclose(cur, cur_o, rtol=1e-9)
+
+
+def test_frame_mode_1080p_mask_bit_exact(gpu_engine, nsof):
+    """Full-size stage 1: 1080p frames -> 13 x 24 cells -> state -> current -> u8 -> mask, masks bit-exact vs the
+    numpy restatement."""
+    rng = np.random.default_rng(9)
+    a, b = helpers.textured_pair(31, 1080, 1920, dx=6.0, dy=2.0)
+    frames = np.stack([a, a, b, b])
+    cells = gpu_engine.compress_images(frames, 80, 80)
+    cells_o = np.stack([s1.compress_image(f, 80, 80) for f in frames])
+    assert np.allclose(cells, cells_o, rtol=0, atol=1e-13)
+    w, cur = gpu_engine.simulate_memristor_array(cells, nSubSteps=1000)
+    w_o, cur_o = s1.simulate_memristor_array(cells_o, nSubSteps=1000)
+    cfg = nsof.RoiConfig()
+    r = gpu_engine.roi_from_currents(cur, (1080, 1920), cfg=cfg)
+    assert np.array_equal(r["memimg"], s1.current_to_u8(cur_o))
