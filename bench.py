@@ -258,16 +258,25 @@ def finish(args, L):
     peak, peak_src = measured_peak()
     extras = {}
     # ---- per-kernel leg: CUDA event pair around every launch of a few extra steps (not part of `value`)
-    eng.profile(True)
-    for _ in range(2):
-        pipe.step(frames)
-    eng.profile(False)
-    stats = eng.profile_read()
-    tot_ms = sum(s["ms"] for s in stats.values()) or 1.0
-    kernels = {k: {"launches": s["launches"] // 2, "ms_per_step": s["ms"] / 2, "share": s["ms"] / tot_ms,
-                   "algorithmic_GB_per_step": s["algorithmic_bytes"] / 2 / 1e9,
-                   "achieved_GBps": (s["algorithmic_bytes"] / (s["ms"] * 1e-3) / 1e9) if s["ms"] > 0 else None}
-               for k, s in stats.items()}
+    def kernel_tables(step_fn, nsteps=2):
+        eng.profile(True)
+        for _ in range(nsteps):
+            step_fn()
+        eng.profile(False)
+        st = eng.profile_read()
+        tot = sum(s["ms"] for s in st.values()) or 1.0
+        rows = {k: {"launches": s["launches"] // nsteps, "ms_per_step": round(s["ms"] / nsteps, 4),
+                    "share": round(s["ms"] / tot, 4), "algorithmic_MB_per_step": round(s["algorithmic_bytes"] / nsteps / 1e6, 3),
+                    "achieved_GBps": round(s["algorithmic_bytes"] / (s["ms"] * 1e-3) / 1e9, 1) if s["ms"] > 0 else None}
+                for k, s in st.items()}
+        cls = {}
+        for k, s in st.items():
+            c = cls.setdefault(k.split(".")[0], dict(launches=0, ms=0.0, algorithmic_bytes=0.0))
+            for f in c:
+                c[f] += s[f]
+        return rows, cls
+
+    kernels, stats = kernel_tables(lambda: pipe.step(frames))
     dom = max(stats, key=lambda k: stats[k]["ms"])
     ach = stats[dom]["algorithmic_bytes"] / (stats[dom]["ms"] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -295,6 +304,7 @@ def finish(args, L):
                                 "achieved_GBps_per_gpu": n_ff * bytes_pair / (ms_ff * 1e-3) / 1e9,
                                 "frac_of_peak": n_ff * bytes_pair / (ms_ff * 1e-3) / 1e9 / peak,
                                 "pairs_per_step_per_gpu": pf.n_pairs}
+        extras["full_frame"]["kernels"] = kernel_tables(lambda: pf.step(ff_frames))[0]
     if rank != 0:
         return 0
     line = {"metric": METRIC, "value": L["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -78,7 +78,8 @@ NSOF_API size_t nsof_workspace_bytes(const nsof_handle *h);
 NSOF_API unsigned long long nsof_launch_count(const nsof_handle *h);
 /* Optional per-launch timing: nsof_profile(h, 1) synchronises, clears the records and brackets every
  * following kernel launch with a CUDA event pair on its stream; nsof_profile(h, 0) stops;
- * nsof_profile_read() synchronises and returns one row per kernel class that ran: launches, summed
+ * nsof_profile_read() synchronises and returns one row per (kernel class, pyramid level) that ran
+ * (name "fb_blur_um.L0", ...): launches, summed
  * device time, summed algorithmic bytes (the DESIGN.md byte model).  Used by bench.py's roofline leg. */
 typedef struct nsof_kernel_stat {
     char name[32];
@@ -209,6 +210,13 @@ NSOF_API int nsof_frame_sim_step_f64(nsof_handle *h, const double *cells_prev, c
                                      double *w, double *current_out, int n, int Hc, int Wc,
                                      const nsof_synapse_params *p, const nsof_frame_sim_params *fp,
                                      void *cuda_stream);
+/* simulate_memristor_array (vehicle.m:187-227) over a whole clip in ONE launch: cells is device double
+ * [n_frames][n][Hc][Wc] (time-major, so that time slice t of all n clips is contiguous); w [n][Hc][Wc] is
+ * the state, updated in place through all n_frames - 1 pairs; current_out (may be NULL) is
+ * [n_frames - 1][n][Hc][Wc], slice t = vds / R(w) after the pair (t, t + 1). */
+NSOF_API int nsof_frame_sim_run_f64(nsof_handle *h, const double *cells, int n_frames, int n, int Hc, int Wc,
+                                    double *w, double *current_out, const nsof_synapse_params *p,
+                                    const nsof_frame_sim_params *fp, void *cuda_stream);
 /* compress_image (vehicle.m:111-121): im2double + imresize(., [floor(H/n), floor(W/m)], 'lanczos3')
  * with MATLAB's antialiasing, for `n` uint8 frames (device) of H x W with row pitch `pitch` bytes and
  * frame stride `frame_stride` bytes -> device double [n][Hc][Wc]. */

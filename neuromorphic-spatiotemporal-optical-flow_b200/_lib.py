@@ -99,6 +99,8 @@ _SIGNATURES = {
                                           C.c_void_p]),
     "nsof_frame_sim_step_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                           C.c_int, C.c_int, _P(SynapseParams), _P(FrameSimParams), C.c_void_p]),
+    "nsof_frame_sim_run_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, _P(SynapseParams), _P(FrameSimParams), C.c_void_p]),
     "nsof_lanczos3_compress_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_ssize_t,
                                             C.c_ssize_t, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
 }

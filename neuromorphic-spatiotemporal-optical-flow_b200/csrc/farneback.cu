@@ -143,21 +143,27 @@ extern "C" int nsof_profile_read(nsof_handle *h, nsof_kernel_stat *out, int max_
     if (!h || !out || !n_out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_profile_read: NULL argument");
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     NSOF_CUDA_TRY(cudaDeviceSynchronize());
-    nsof_kernel_stat acc[NSOF_K_CLASSES];
-    memset(acc, 0, sizeof(acc));
+    const int LV = 9;  // levels 0..7 and "no level"
+    std::vector<nsof_kernel_stat> acc((size_t)NSOF_K_CLASSES * LV);
+    memset(acc.data(), 0, acc.size() * sizeof(nsof_kernel_stat));
     for (const NsofProfRec &r : h->prof_recs) {
         float ms = 0.f;
         NSOF_CUDA_TRY(cudaEventElapsedTime(&ms, h->prof_pool[r.ev], h->prof_pool[r.ev + 1]));
-        acc[r.cls].launches += 1;
-        acc[r.cls].ms += ms;
-        acc[r.cls].algorithmic_bytes += r.bytes;
+        const int lv = (r.level >= 0 && r.level < LV - 1) ? r.level : LV - 1;
+        nsof_kernel_stat &a = acc[(size_t)r.cls * LV + lv];
+        a.launches += 1;
+        a.ms += ms;
+        a.algorithmic_bytes += r.bytes;
     }
     int n = 0;
-    for (int c = 0; c < NSOF_K_CLASSES && n < max_out; c++) {
-        if (!acc[c].launches) continue;
-        snprintf(acc[c].name, sizeof(acc[c].name), "%s", nsof_kernel_class_names[c]);
-        out[n++] = acc[c];
-    }
+    for (int c = 0; c < NSOF_K_CLASSES; c++)
+        for (int lv = 0; lv < LV && n < max_out; lv++) {
+            nsof_kernel_stat &a = acc[(size_t)c * LV + lv];
+            if (!a.launches) continue;
+            if (lv == LV - 1) snprintf(a.name, sizeof(a.name), "%s", nsof_kernel_class_names[c]);
+            else snprintf(a.name, sizeof(a.name), "%s.L%d", nsof_kernel_class_names[c], lv);
+            out[n++] = a;
+        }
     *n_out = n;
     return NSOF_OK;
 }
@@ -532,6 +538,7 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
         for (int i = 0; i < n; i++)
             if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
         const double Nk = sumN[k];
+        h->prof_level = k;
         NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * sumN0[k], k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, ksize[k] / 2);
         NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * Nk, k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream, jobs, pc);
         if (params->iterations == 0) {
@@ -548,6 +555,7 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
         }
         NSOF_CUDA_TRY(cudaGetLastError());
     }
+    h->prof_level = -1;
     return NSOF_OK;
 }
 
@@ -682,7 +690,7 @@ extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, 
 
 #ifdef NSOF_EMU
 namespace nsof_emu {
-thread_local int bx, by, bz;
+thread_local int bx, by, bz, gdx;
 thread_local unsigned char *smem;
 }
 #endif

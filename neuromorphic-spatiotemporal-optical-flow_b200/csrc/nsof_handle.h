@@ -55,7 +55,7 @@ enum NsofKernelClass {
 extern const char *const nsof_kernel_class_names[NSOF_K_CLASSES];
 
 struct NsofProfRec {
-    int cls;
+    int cls, level;  // pyramid level of a stage-2 launch, -1 otherwise
     size_t ev;  // index of the start event in the pool; stop event is ev + 1
     double bytes;
 };
@@ -68,7 +68,8 @@ struct nsof_handle {
     NsofDevBuf s1;         // stage-1 scratch
     NsofDevBuf lz;         // Lanczos-3 weight/index tables (device), cached for lz_key
     int lz_key[4] = {0, 0, 0, 0};
-    int lz_P[2] = {0, 0};
+    int lz_P[2] = {0, 0};  // seg_rows, n_seg of the cached Lanczos geometry
+    bool lz_smem_set = false;
     NsofStageSlot stage[4];
     int stage_next = 0;
     // debug truncation (tests only)
@@ -81,6 +82,7 @@ struct nsof_handle {
     // launch accounting
     unsigned long long launches = 0;
     bool prof_on = false;
+    int prof_level = -1;
     std::vector<cudaEvent_t> prof_pool;
     size_t prof_used = 0;
     std::vector<NsofProfRec> prof_recs;
@@ -96,7 +98,7 @@ static inline void nsof_prof_pre(nsof_handle *h, int cls, double bytes, cudaStre
         cudaEventCreate(&e);
         h->prof_pool.push_back(e);
     }
-    NsofProfRec r = {cls, h->prof_used, bytes};
+    NsofProfRec r = {cls, h->prof_level, h->prof_used, bytes};
     h->prof_recs.push_back(r);
     cudaEventRecord(h->prof_pool[h->prof_used], st);
 }

@@ -25,12 +25,13 @@ struct float4 { float x, y, z, w; };
 static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r; }
 static inline float4 make_float4(float x, float y, float z, float w) { float4 r = {x, y, z, w}; return r; }
 namespace nsof_emu {
-extern thread_local int bx, by, bz;
+extern thread_local int bx, by, bz, gdx;
 extern thread_local unsigned char *smem;
 template <class F> static inline void launch(int gx, int gy, int gz, size_t smem_bytes, F f)
 {
     std::vector<unsigned char> buf(smem_bytes + 64);
     smem = buf.data();
+    gdx = gx;
     for (bz = 0; bz < gz; bz++)
         for (by = 0; by < gy; by++)
             for (bx = 0; bx < gx; bx++) f();
@@ -46,6 +47,9 @@ template <class F> static inline void launch(int gx, int gy, int gz, size_t smem
 #define NSOF_BZ (nsof_emu::bz)
 #define NSOF_TID 0
 #define NSOF_NT 1
+#define NSOF_WARP 1
+static inline int nsof_grid_x() { return nsof_emu::gdx; }
+static inline double nsof_warp_sum_f64(double v) { return v; }
 #define NSOF_SYNC() ((void)0)
 #define NSOF_DYN_SMEM(name) unsigned char *name = nsof_emu::smem
 #define NSOF_LDG(p) (*(p))
@@ -64,6 +68,14 @@ template <class F> static inline void launch(int gx, int gy, int gz, size_t smem
 #define NSOF_BZ ((int)blockIdx.z)
 #define NSOF_TID ((int)threadIdx.x)
 #define NSOF_NT ((int)blockDim.x)
+#define NSOF_WARP 32
+__device__ __forceinline__ int nsof_grid_x() { return (int)gridDim.x; }
+// fixed-order butterfly: deterministic for a given lane assignment
+__device__ __forceinline__ double nsof_warp_sum_f64(double v)
+{
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
 #define NSOF_SYNC() __syncthreads()
 #define NSOF_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
 #define NSOF_LDG(p) __ldg(p)

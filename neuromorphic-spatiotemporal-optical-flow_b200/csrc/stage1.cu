@@ -150,6 +150,30 @@ static int lanczos_contrib(int in, int out, std::vector<double> &wgt, std::vecto
     return P;
 }
 
+// Dense per-axis matrix D[out][in] of the resize (mirrored taps merged) and, per output, its non-zero band.
+static void lanczos_dense(int in, int out, std::vector<double> &D, std::vector<int> &band)
+{
+    std::vector<double> wgt;
+    std::vector<int> idx;
+    const int P = lanczos_contrib(in, out, wgt, idx);
+    D.assign((size_t)out * in, 0.);
+    band.assign((size_t)out * 2, 0);
+    for (int o = 0; o < out; o++) {
+        int lo = in, hi = 0;
+        for (int k = 0; k < P; k++) {
+            const double v = wgt[(size_t)o * P + k];
+            if (v == 0.) continue;
+            const int i = idx[(size_t)o * P + k];
+            D[(size_t)o * in + i] += v;
+            lo = std::min(lo, i);
+            hi = std::max(hi, i + 1);
+        }
+        if (lo >= hi) { lo = 0; hi = 0; }
+        band[2 * o] = lo;
+        band[2 * o + 1] = hi;
+    }
+}
+
 extern "C" int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, int n, int H, int W, ptrdiff_t pitch,
                                          ptrdiff_t frame_stride, int Hc, int Wc, double *cells, void *cuda_stream)
 {
@@ -157,39 +181,92 @@ extern "C" int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, 
         NSOF_FAIL(NSOF_ERR_BAD_ARG, "lanczos3_compress: bad argument");
     if (n == 0) return NSOF_OK;
     if (n > 65535 || Hc > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "lanczos3_compress: too many frames/cells per call");
+    if ((size_t)W * sizeof(double) > 200 * 1024) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "lanczos3_compress: frame wider than 25600 px");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     int rc;
     if (h->lz_key[0] != H || h->lz_key[1] != W || h->lz_key[2] != Hc || h->lz_key[3] != Wc) {
-        std::vector<double> wy, wx;
-        std::vector<int> iy, ix;
-        const int Py = lanczos_contrib(H, Hc, wy, iy), Px = lanczos_contrib(W, Wc, wx, ix);
-        const size_t bytes = (wy.size() + wx.size()) * sizeof(double) + (iy.size() + ix.size()) * sizeof(int) + 64;
+        std::vector<double> Dy, Dx;
+        std::vector<int> yband, xband;
+        lanczos_dense(H, Hc, Dy, yband);
+        lanczos_dense(W, Wc, Dx, xband);
+        // row segments: the largest seg_rows (<= 96) whose segments all touch at most LZ_MAXC consecutive cell rows
+        int seg_rows = std::min(96, H), n_seg = 0;
+        std::vector<int> cbase;
+        for (;; seg_rows = std::max(1, seg_rows / 2)) {
+            n_seg = (H + seg_rows - 1) / seg_rows;
+            cbase.assign(n_seg, 0);
+            bool ok = true;
+            for (int sgm = 0; sgm < n_seg && ok; sgm++) {
+                const int y0 = sgm * seg_rows, y1 = std::min(H, y0 + seg_rows);
+                int lo = Hc, hi = -1;
+                for (int cy = 0; cy < Hc; cy++)
+                    if (yband[2 * cy] < y1 && yband[2 * cy + 1] > y0) { lo = std::min(lo, cy); hi = std::max(hi, cy); }
+                if (hi < lo) { lo = 0; hi = 0; }
+                cbase[sgm] = lo;
+                if (hi - lo + 1 > LZ_MAXC) ok = false;
+            }
+            if (ok) break;
+            if (seg_rows == 1) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "lanczos3_compress: a source row feeds more than %d cell rows", LZ_MAXC);
+        }
+        const size_t bytes = (Dy.size() + Dx.size()) * sizeof(double) + (xband.size() + cbase.size()) * sizeof(int) + 64;
         rc = h->lz.ensure(bytes);
         if (rc) return rc;
-        // tables are tiny and change only with the geometry: plain synchronous upload
+        // tables are small and change only with the geometry: plain synchronous upload
         char *d = (char *)h->lz.p;
         NSOF_CUDA_TRY(cudaStreamSynchronize(st));
-        NSOF_CUDA_TRY(cudaMemcpyAsync(d, wy.data(), wy.size() * 8, cudaMemcpyHostToDevice, st)); d += wy.size() * 8;
-        NSOF_CUDA_TRY(cudaMemcpyAsync(d, wx.data(), wx.size() * 8, cudaMemcpyHostToDevice, st)); d += wx.size() * 8;
-        NSOF_CUDA_TRY(cudaMemcpyAsync(d, iy.data(), iy.size() * 4, cudaMemcpyHostToDevice, st)); d += iy.size() * 4;
-        NSOF_CUDA_TRY(cudaMemcpyAsync(d, ix.data(), ix.size() * 4, cudaMemcpyHostToDevice, st));
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, Dy.data(), Dy.size() * 8, cudaMemcpyHostToDevice, st)); d += Dy.size() * 8;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, Dx.data(), Dx.size() * 8, cudaMemcpyHostToDevice, st)); d += Dx.size() * 8;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, xband.data(), xband.size() * 4, cudaMemcpyHostToDevice, st)); d += xband.size() * 4;
+        NSOF_CUDA_TRY(cudaMemcpyAsync(d, cbase.data(), cbase.size() * 4, cudaMemcpyHostToDevice, st));
         NSOF_CUDA_TRY(cudaStreamSynchronize(st));
         h->lz_key[0] = H; h->lz_key[1] = W; h->lz_key[2] = Hc; h->lz_key[3] = Wc;
-        h->lz_P[0] = Py; h->lz_P[1] = Px;
+        h->lz_P[0] = seg_rows; h->lz_P[1] = n_seg;
     }
-    const int Py = h->lz_P[0], Px = h->lz_P[1];
-    const double *d_wy = (const double *)h->lz.p;
-    const double *d_wx = d_wy + (size_t)Hc * Py;
-    const int *d_iy = (const int *)(d_wx + (size_t)Wc * Px);
-    const int *d_ix = d_iy + (size_t)Hc * Py;
-    rc = h->s1.ensure((size_t)n * Hc * W * sizeof(double));
+    const int seg_rows = h->lz_P[0], n_seg = h->lz_P[1];
+    const double *d_Dy = (const double *)h->lz.p;
+    const double *d_Dx = d_Dy + (size_t)Hc * H;
+    const int *d_xband = (const int *)(d_Dx + (size_t)Wc * W);
+    const int *d_cbase = d_xband + 2 * (size_t)Wc;
+    rc = h->s1.ensure((size_t)n * n_seg * LZ_MAXC * W * sizeof(double));
     if (rc) return rc;
-    double *tmp = (double *)h->s1.p;
-    const int cols = 256;
-    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, (double)n * H * W, k_s1_lanczos_rows, (W + cols - 1) / cols, Hc, n, S1_NT, 0, st, frames, pitch, frame_stride, W, Hc, d_wy, d_iy,
-                Py, tmp, cols);
-    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, 0., k_s1_lanczos_cols, n, 1, 1, S1_NT, 0, st, tmp, W, Hc, Wc, d_wx, d_ix, Px, cells);
+    double *part = (double *)h->s1.p;
+    if (!h->lz_smem_set) {
+        NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_lanczos_cols, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        h->lz_smem_set = true;
+    }
+    const int nt = 128, ngroups = (W + 3) / 4;
+    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, (double)n * H * W, k_s1_lanczos_rows, (ngroups + nt - 1) / nt, n_seg, n, nt,
+                 (size_t)LZ_MAXC * seg_rows * sizeof(double), st, frames, pitch, frame_stride, H, W, Hc, d_Dy, d_cbase,
+                 seg_rows, n_seg, part);
+    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, 0., k_s1_lanczos_cols, Hc, n, 1, S1_NT, (size_t)W * sizeof(double), st, part, W, Hc, Wc,
+                 d_Dx, d_xband, d_cbase, n_seg, cells);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+static FrameSimConst frame_sim_const(const nsof_synapse_params *p, const nsof_frame_sim_params *fp)
+{
+    FrameSimConst c;
+    c.th1 = fp->th1; c.th2 = fp->th2; c.dt_sub = fp->dt / fp->nsubsteps; c.vds = fp->vds; c.nsub = fp->nsubsteps;
+    c.alphaoff = p->alphaoff; c.alphaon = p->alphaon; c.voff = p->voff; c.von = p->von; c.koff = p->koff; c.kon = p->kon;
+    c.son = p->son; c.soff = p->soff; c.bon = p->bon; c.boff = p->boff; c.Ron = p->Ron; c.lam = log(p->Roff / p->Ron);
+    return c;
+}
+
+extern "C" int nsof_frame_sim_run_f64(nsof_handle *h, const double *cells, int n_frames, int n, int Hc, int Wc, double *w,
+                                      double *current_out, const nsof_synapse_params *p, const nsof_frame_sim_params *fp,
+                                      void *cuda_stream)
+{
+    if (!h || !cells || !w || !p || !fp || n < 0 || n_frames < 1 || Hc < 1 || Wc < 1 || fp->nsubsteps < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "frame_sim_run: bad argument");
+    if (n == 0 || n_frames < 2) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const FrameSimConst c = frame_sim_const(p, fp);
+    const size_t total = (size_t)n * Hc * Wc;
+    const int per_block = 32;  // few cells, long dependent chains: one warp per block spreads the cells over the SMs
+    NSOF_KLAUNCH(h, NSOF_K_FRAME_SIM, 8. * total * (2. * n_frames - 1), k_s1_frame_run, blocks_for(total, per_block), 1, 1, 32,
+                 0, (cudaStream_t)cuda_stream, cells, total, n_frames, w, current_out, total, c, per_block);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
 }
@@ -202,10 +279,7 @@ extern "C" int nsof_frame_sim_step_f64(nsof_handle *h, const double *cells_prev,
         NSOF_FAIL(NSOF_ERR_BAD_ARG, "frame_sim_step: bad argument");
     if (n == 0) return NSOF_OK;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    FrameSimConst c;
-    c.th1 = fp->th1; c.th2 = fp->th2; c.dt_sub = fp->dt / fp->nsubsteps; c.vds = fp->vds; c.nsub = fp->nsubsteps;
-    c.alphaoff = p->alphaoff; c.alphaon = p->alphaon; c.voff = p->voff; c.von = p->von; c.koff = p->koff; c.kon = p->kon;
-    c.son = p->son; c.soff = p->soff; c.bon = p->bon; c.boff = p->boff; c.Ron = p->Ron; c.lam = log(p->Roff / p->Ron);
+    const FrameSimConst c = frame_sim_const(p, fp);
     const size_t total = (size_t)n * Hc * Wc;
     // few cells, long dependent chains: small blocks so the cells spread over many SMs
     const int per_block = 32;

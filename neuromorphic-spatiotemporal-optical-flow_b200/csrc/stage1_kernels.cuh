@@ -138,43 +138,93 @@ NSOF_GLOBAL k_s1_resistance_exp(const float *NSOF_RESTRICT w, size_t n, double R
 }
 
 // ---------------------------------------------------------------------------------------------
-// Frame mode.  Lanczos-3 antialiased imresize, dimension 1 (rows) first as MATLAB does for equal
-// scales.  Weight/index tables come from the host (double); P taps per output.
-// pass 1: tmp[n][Hc][W] = sum_k wy[cy][k] * (src[iy[cy][k]][x] / 255)
+// Frame mode.  compress_image = im2double + imresize(.,'lanczos3') with antialiasing is a separable
+// linear map: cells = Wy * (img / 255) * Wx^T with DENSE per-axis matrices Wy [Hc][H], Wx [Wc][W]
+// built on the host in double from MATLAB's contribution tables (mirrored taps that land on the same
+// source index are merged).  Only a band of each row of Wy / Wx is non-zero (about 6/scale taps).
+//
+// pass 1 (k_s1_lanczos_rows): every source byte is read ONCE (uchar4 per thread, 128 B per warp).
+//   grid (ceil(W/4/NT), S row segments, n frames).  A segment of seg_rows source rows touches at most
+//   LZ_MAXC consecutive cell rows starting at cbase[seg]; the thread keeps LZ_MAXC x 4 double
+//   accumulators of sum_y Wy * u8 in registers and writes them to part[f][seg][j][x] (im2double's 1/255 is
+//   applied in pass 2).  Weights of the segment are staged
+//   in shared memory: sw[j][r] = Wy[cbase + j][y0 + r].   dynamic smem: LZ_MAXC * seg_rows doubles.
+// pass 2 (k_s1_lanczos_cols): block per (cell row, frame): tmp[x] = sum over segments in fixed order
+//   (deterministic), then one warp per cell column reduces its tap band with a fixed-order shuffle tree.
 // ---------------------------------------------------------------------------------------------
-NSOF_GLOBAL k_s1_lanczos_rows(const uint8_t *NSOF_RESTRICT frames, ptrdiff_t pitch, ptrdiff_t frame_stride, int W,
-                              int Hc, const double *NSOF_RESTRICT wy, const int *NSOF_RESTRICT iy, int P,
-                              double *NSOF_RESTRICT tmp, int cols_per_block)
+#define LZ_MAXC 8
+
+NSOF_GLOBAL k_s1_lanczos_rows(const uint8_t *NSOF_RESTRICT frames, ptrdiff_t pitch, ptrdiff_t frame_stride, int H, int W,
+                              int Hc, const double *NSOF_RESTRICT Wy, const int *NSOF_RESTRICT cbase, int seg_rows,
+                              int n_seg, double *NSOF_RESTRICT part)
 {
-    const int cy = NSOF_BY, f = NSOF_BZ;
+    const int seg = NSOF_BY, f = NSOF_BZ;
+    const int y0 = seg * seg_rows, y1 = nsof_imin(y0 + seg_rows, H);
+    const int cb = cbase[seg];
+    NSOF_DYN_SMEM(smem_raw);
+    double *sw = (double *)smem_raw;
+    for (int i = NSOF_TID; i < LZ_MAXC * seg_rows; i += NSOF_NT) {
+        const int j = i / seg_rows, r = i % seg_rows;
+        const int cy = cb + j, y = y0 + r;
+        sw[i] = (cy < Hc && y < y1) ? Wy[(size_t)cy * H + y] : 0.;
+    }
+    NSOF_SYNC();
     const uint8_t *src = frames + (size_t)f * frame_stride;
-    const int x0 = NSOF_BX * cols_per_block;
-    for (int i = NSOF_TID; i < cols_per_block; i += NSOF_NT) {
-        const int x = x0 + i;
-        if (x >= W) continue;
-        double acc = 0.;
-        for (int k = 0; k < P; k++) {
-            const double wgt = wy[cy * P + k];
-            if (wgt != 0.) acc += wgt * ((double)NSOF_LDG(src + (size_t)iy[cy * P + k] * pitch + x) / 255.0);
+    const int ngroups = (W + 3) / 4;
+    for (int g = NSOF_BX * NSOF_NT + NSOF_TID; g < ngroups; g += NSOF_NT * nsof_grid_x()) {
+        const int x = g * 4;
+        double acc[LZ_MAXC][4];
+        for (int j = 0; j < LZ_MAXC; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.;
+        const bool vec = (x + 3 < W) && ((((uintptr_t)src + x) & 3) == 0) && ((pitch & 3) == 0);
+        for (int y = y0; y < y1; y++) {
+            const uint8_t *row = src + (size_t)y * pitch + x;
+            double v[4];
+            if (vec) {
+                const uint32_t u = NSOF_LDG((const uint32_t *)row);
+                v[0] = (double)(u & 255u); v[1] = (double)((u >> 8) & 255u);
+                v[2] = (double)((u >> 16) & 255u); v[3] = (double)(u >> 24);
+            } else {
+                for (int q = 0; q < 4; q++) v[q] = x + q < W ? (double)NSOF_LDG(row + q) : 0.;
+            }
+            const double *wr = sw + (y - y0);
+#pragma unroll
+            for (int j = 0; j < LZ_MAXC; j++) {
+                const double wj = wr[j * seg_rows];
+                acc[j][0] += wj * v[0]; acc[j][1] += wj * v[1]; acc[j][2] += wj * v[2]; acc[j][3] += wj * v[3];
+            }
         }
-        tmp[((size_t)f * Hc + cy) * W + x] = acc;
+        for (int j = 0; j < LZ_MAXC; j++) {
+            double *o = part + (((size_t)f * n_seg + seg) * LZ_MAXC + j) * W + x;
+            for (int q = 0; q < 4; q++)
+                if (x + q < W) o[q] = acc[j][q];
+        }
     }
 }
 
-// pass 2: cells[n][Hc][Wc] = sum_k wx[cx][k] * tmp[cy][ix[cx][k]]
-NSOF_GLOBAL k_s1_lanczos_cols(const double *NSOF_RESTRICT tmp, int W, int Hc, int Wc, const double *NSOF_RESTRICT wx,
-                              const int *NSOF_RESTRICT ix, int P, double *NSOF_RESTRICT cells)
+// dynamic smem: W doubles
+NSOF_GLOBAL k_s1_lanczos_cols(const double *NSOF_RESTRICT part, int W, int Hc, int Wc, const double *NSOF_RESTRICT Wx,
+                              const int *NSOF_RESTRICT xband, const int *NSOF_RESTRICT cbase, int n_seg,
+                              double *NSOF_RESTRICT cells)
 {
-    const int f = NSOF_BX;
-    for (int i = NSOF_TID; i < Hc * Wc; i += NSOF_NT) {
-        const int cx = i % Wc, cy = i / Wc;
-        const double *row = tmp + ((size_t)f * Hc + cy) * W;
-        double acc = 0.;
-        for (int k = 0; k < P; k++) {
-            const double wgt = wx[cx * P + k];
-            if (wgt != 0.) acc += wgt * row[ix[cx * P + k]];
+    const int cy = NSOF_BX, f = NSOF_BY;
+    NSOF_DYN_SMEM(smem_raw);
+    double *tmp = (double *)smem_raw;
+    for (int x = NSOF_TID; x < W; x += NSOF_NT) {
+        double s = 0.;
+        for (int seg = 0; seg < n_seg; seg++) {
+            const int j = cy - cbase[seg];
+            if (j >= 0 && j < LZ_MAXC) s += part[(((size_t)f * n_seg + seg) * LZ_MAXC + j) * W + x];
         }
-        cells[(size_t)f * Hc * Wc + i] = acc;
+        tmp[x] = s / 255.0;  // im2double, applied once to the row-pass sum (linear map)
+    }
+    NSOF_SYNC();
+    const int lane = NSOF_TID & 31, warp = NSOF_TID >> 5, nwarps = NSOF_NT >> 5;
+    for (int cx = warp; cx < Wc; cx += (nwarps > 0 ? nwarps : 1)) {
+        const int xa = xband[2 * cx], xb = xband[2 * cx + 1];
+        double s = 0.;
+        for (int x = xa + lane; x < xb; x += NSOF_WARP) s += Wx[(size_t)cx * W + x] * tmp[x];
+        s = nsof_warp_sum_f64(s);
+        if (lane == 0) cells[((size_t)f * Hc + cy) * Wc + cx] = s;
     }
 }
 
@@ -221,6 +271,52 @@ NSOF_GLOBAL k_s1_frame_step(const double *NSOF_RESTRICT a, const double *NSOF_RE
         }
         w[e] = wv;
         if (current) current[e] = c.vds / (c.Ron / exp(-c.lam * (1. - wv)));
+    }
+}
+
+// simulate_memristor_array over a whole clip in one launch: thread = (clip, cell), loop over the frames
+// inside; cells[t] is [n_cells] at stride `stride_t` doubles; current_out[t] = state after the pair (t, t+1).
+// x^b is evaluated as exp(b * log(x)) -- the chain of nsub dependent sub-steps per frame is pure latency, and
+// CUDA's double pow() is ~3x deeper than exp+log; the difference is ~1e-16 relative per sub-step.
+NSOF_DEV double s1_pow_pos(double x, double b) { return x > 0. ? exp(b * log(x)) : pow(x, b); }
+
+NSOF_GLOBAL k_s1_frame_run(const double *NSOF_RESTRICT cells, size_t stride_t, int n_frames, double *NSOF_RESTRICT w,
+                           double *NSOF_RESTRICT current, size_t n, FrameSimConst c, int per_block)
+{
+    const size_t base = (size_t)NSOF_BX * per_block;
+    for (int i = NSOF_TID; i < per_block; i += NSOF_NT) {
+        const size_t e = base + i;
+        if (e >= n) continue;
+        double wv = w[e];
+        double a = cells[e];
+        for (int t = 0; t + 1 < n_frames; t++) {
+            const double b = cells[(size_t)(t + 1) * stride_t + e];
+            const double d = fabs(a * 256. - b * 256.);
+            double V = 0.;
+            if (d > c.th2) V = (d + 4.) * 0.75;
+            if (d > c.th1 && d <= c.th2) V = (d + 4.) * 0.75;
+            if (d <= c.th1) V = (d - 5.5) * 0.6;
+            double vm = 0.;
+            if (V > 0.) vm = 0.3 * V + 0.;
+            else if (V < 0.) vm = 3. * V + -3.;
+            vm = -vm;
+            if (vm < c.voff) {
+                const double g = c.koff * pow(vm / c.voff - 1., c.alphaoff) * c.dt_sub;
+                for (int s = 0; s < c.nsub; s++) {
+                    wv = wv + g * s1_pow_pos(1. - wv * c.soff, c.boff);
+                    wv = fmax(0., fmin(wv, 1.));
+                }
+            } else if (vm > c.von) {
+                const double g = c.kon * pow(vm / c.von - 1., c.alphaon) * c.dt_sub;
+                for (int s = 0; s < c.nsub; s++) {
+                    wv = wv + g * s1_pow_pos(1. - wv * c.son, c.bon);
+                    wv = fmax(0., fmin(wv, 1.));
+                }
+            }
+            if (current) current[(size_t)t * stride_t + e] = c.vds / (c.Ron / exp(-c.lam * (1. - wv)));
+            a = b;
+        }
+        w[e] = wv;
     }
 }
 

@@ -247,9 +247,9 @@ class Engine:
 
     def profile_read(self):
         """-> {kernel class: dict(launches, ms, algorithmic_bytes)} for the launches since profile(True)."""
-        rows = (_lib.KernelStat * 32)()
+        rows = (_lib.KernelStat * 128)()
         n = C.c_int()
-        self.lib.check(self.lib.nsof_profile_read(self.handle, rows, 32, C.byref(n)), "nsof_profile_read")
+        self.lib.check(self.lib.nsof_profile_read(self.handle, rows, 128, C.byref(n)), "nsof_profile_read")
         return {rows[i].name.decode(): dict(launches=rows[i].launches, ms=rows[i].ms,
                                             algorithmic_bytes=rows[i].algorithmic_bytes) for i in range(n.value)}
 
@@ -491,9 +491,10 @@ class Engine:
         self.lib.check(rc, "lanczos3_compress")
         return out.cpu().numpy()
 
-    def simulate_memristor_array(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS, vds=1.0):
-        """simulate_memristor_array (vehicle.m:187-227): returns (w_array, currents (T, Hc, Wc) with slice 0 the
-        initial state -- the layout of constructed3DMatrix = vds / resistances_over_time)."""
+    def simulate_memristor_array_stepwise(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS,
+                                          vds=1.0):
+        """Same as simulate_memristor_array through the per-pair entry point nsof_frame_sim_step_f64 (streaming use:
+        one call per arriving frame)."""
         import torch
         cells = np.ascontiguousarray(compressed_images, dtype=np.float64)
         T, Hc, Wc = cells.shape
@@ -509,6 +510,24 @@ class Engine:
             rc = self.lib.nsof_frame_sim_step_f64(self.handle, d[i].data_ptr(), d[i + 1].data_ptr(), w.data_ptr(),
                                                   cur[i + 1].data_ptr(), 1, Hc, Wc, C.byref(sp), C.byref(fp), st)
             self.lib.check(rc, "frame_sim_step")
+        return w.cpu().numpy(), cur.cpu().numpy()
+
+    def simulate_memristor_array(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS, vds=1.0):
+        """simulate_memristor_array (vehicle.m:187-227): returns (w_array, currents (T, Hc, Wc) with slice 0 the
+        initial state -- the layout of constructed3DMatrix = vds / resistances_over_time)."""
+        import torch
+        cells = np.ascontiguousarray(compressed_images, dtype=np.float64)
+        T, Hc, Wc = cells.shape
+        (d,) = self._dev_roundtrip([cells])
+        w = torch.full((Hc, Wc), float(p["wini"]), dtype=torch.float64, device=d.device)
+        cur = torch.empty((T, Hc, Wc), dtype=torch.float64, device=d.device)
+        sp = _synapse_params(p)
+        lam = np.log(p["Roff"] / p["Ron"])
+        cur[0] = vds / (p["Ron"] / torch.exp(-lam * (1.0 - w)))
+        fp = FrameSimParams(float(th1), float(th2), float(dt), int(nSubSteps), float(vds))
+        rc = self.lib.nsof_frame_sim_run_f64(self.handle, d.data_ptr(), T, 1, Hc, Wc, w.data_ptr(), cur[1:].data_ptr(),
+                                             C.byref(sp), C.byref(fp), self._stream())
+        self.lib.check(rc, "frame_sim_run")
         return w.cpu().numpy(), cur.cpu().numpy()
 
 

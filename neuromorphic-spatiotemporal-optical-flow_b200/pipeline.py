@@ -6,7 +6,7 @@ For a rank's `C` clips of `F` grey frames (layout [F][C][H][W] uint8, so that ti
 contiguous block) one `step` is:
 
   1. compress_image for all F*C frames                       nsof_lanczos3_compress_u8   (1 B / source pixel)
-  2. simulate_memristor_array, F-1 sequential array updates  nsof_frame_sim_step_f64     (cells only)
+  2. simulate_memristor_array, all F-1 pairs in one launch   nsof_frame_sim_run_f64      (cells only)
   3. current -> u8 -> transition_pic -> CC -> rectangles     nsof_roi_from_state_f64     (cells only)
   4. rectangles D2H (the one host sync of the step), crop descriptors
   5. zero the flow frames, ROI-gated Farneback on every crop nsof_farneback_batch        (DESIGN.md byte model)
@@ -73,10 +73,9 @@ class SequencePipeline:
         lib.check(lib.nsof_lanczos3_compress_u8(h, frames.data_ptr(), F * Cn, H, W, W, H * W, self.Hc, self.Wc,
                                                 self.cells.data_ptr(), st), "lanczos3_compress")
         self.w.fill_(float(PARAMS["wini"]))
-        for t in range(F - 1):
-            lib.check(lib.nsof_frame_sim_step_f64(h, self.cells[t].data_ptr(), self.cells[t + 1].data_ptr(),
-                                                  self.w.data_ptr(), self.currents[t].data_ptr(), Cn, self.Hc, self.Wc,
-                                                  C.byref(self.sp), C.byref(self.fsp), st), "frame_sim_step")
+        lib.check(lib.nsof_frame_sim_run_f64(h, self.cells.data_ptr(), F, Cn, self.Hc, self.Wc, self.w.data_ptr(),
+                                             self.currents.data_ptr(), C.byref(self.sp), C.byref(self.fsp), st),
+                  "frame_sim_run")
         lib.check(lib.nsof_roi_from_state_f64(h, self.currents.data_ptr(), self.n_pairs, C.byref(self.rp),
                                               self.thr.data_ptr(), self.memimg.data_ptr(), None, None,
                                               self.n_rects.data_ptr(), self.rects.data_ptr(), None, st), "roi")

@@ -158,3 +158,5 @@ def test_emu_frame_mode_vs_oracle(emu_engine):
     w, cur = emu_engine.simulate_memristor_array(seq, nSubSteps=20)
     w_o, cur_o = s1.simulate_memristor_array(seq, nSubSteps=20)
     assert np.allclose(w, w_o, rtol=0, atol=1e-12) and np.allclose(cur, cur_o, rtol=1e-11)
+    w2, cur2 = emu_engine.simulate_memristor_array_stepwise(seq, nSubSteps=20)
+    assert np.allclose(w2, w_o, rtol=0, atol=1e-12) and np.allclose(cur2, cur_o, rtol=1e-11)
