@@ -359,6 +359,7 @@ static int configure_smem(nsof_handle *h)
 {
     if (h->smem_configured) return NSOF_OK;
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     h->smem_configured = true;
     return NSOF_OK;
@@ -473,7 +474,9 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     const int m = params->winsize / 2;
     int BTW = 0, BTH = 0;
     size_t bs_smem = 0;
-    if (params->iterations > 0 && !pick_blur_tile(m, &BTW, &BTH, &bs_smem))
+    const bool bs_m7 = (m == 7);  // winsize 14/15: the tuned kernel (every BASELINE.json config)
+    if (bs_m7) { BTW = FB_BS7_TW; BTH = FB_BS7_TH; bs_smem = FB_BS7_SMEM; }
+    else if (params->iterations > 0 && !pick_blur_tile(m, &BTW, &BTH, &bs_smem))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
     for (int k = 0; k < max_scales; k++) {
         gaussian_half_kernel(ksize[k], sigma[k], (float *)hs + gk_off[k]);
@@ -549,8 +552,12 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
                          flow_mul);
             for (int it = 0; it < iters; it++) {
                 const bool last = it == iters - 1;
-                NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve,
-                             max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale, (it & 1) == 0, last);
+                if (bs_m7)
+                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7,
+                                 max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, bscale, (it & 1) == 0, last);
+                else
+                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve,
+                                 max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale, (it & 1) == 0, last);
             }
         }
         NSOF_CUDA_TRY(cudaGetLastError());

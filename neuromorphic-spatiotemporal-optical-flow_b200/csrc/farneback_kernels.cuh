@@ -409,3 +409,158 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
         }
     }
 }
+
+// ---------------------------------------------------------------------------------------------
+// S2-e (+ S2-d fused), tuned variant for a compile-time window radius M and tile TW x TH.
+// Same arithmetic, same order of operations per pixel as k_fb_blur_solve (results are bit-identical);
+// what changes is how the work is laid out:
+//   phase 1  the M tile + halo (5 planes x (TH+2M) rows) arrives by bulk asynchronous row copies
+//            (cp.async.bulk global->shared on an mbarrier, SASS UBLKCP): no per-element index arithmetic,
+//            no register staging, every row in flight at once.  Rows are 16-byte aligned runs starting at
+//            tx0 - ML (ML = M rounded up to 4); replicate borders are patched in shared memory afterwards
+//            (border tiles only).
+//   phase 2  vertical running sums in double, one thread per (plane, column)
+//   phase 3  4 pixels per thread: aligned float4 shared-memory reads of the 2M+4 window columns,
+//            float4 loads of R0, float4 stores of M'
+// dynamic smem: 16 B (mbarrier) + 5 * (TH+2M) * (TW+2ML) floats.
+// ---------------------------------------------------------------------------------------------
+template <int M, int TW, int TH>
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
+{
+    constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, LW = TW + 2 * M, SP = LH * PW;
+    constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
+    const FbJob J = jobs[NSOF_BY];
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const size_t plane = (size_t)J.pitch * J.h;
+    const float *Min = src_is_a ? J.Ma : J.Mb;
+    float *Mout = src_is_a ? J.Mb : J.Ma;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    NSOF_DYN_SMEM(smem_raw);
+    nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
+    float *sM = (float *)(smem_raw + 16);
+
+    // ---- phase 1
+    const int gx0 = tx0 - ML;                                         // global x of shared column 0
+    const int cx0 = nsof_imax(gx0, 0), cx1 = nsof_imin(tx0 + TW + ML, J.pitch);  // copied run, multiples of 4
+    const unsigned row_bytes = (unsigned)(cx1 - cx0) * 4u;
+    if (NSOF_TID == 0) nsof_mbar_init(bar, 1);
+    NSOF_SYNC();
+    if (NSOF_TID < NSOF_WARP) {
+        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(5 * LH));
+        NSOF_SYNCWARP();
+        for (int r = NSOF_TID; r < 5 * LH; r += NSOF_WARP) {
+            const int c = r / LH, ly = r - c * LH;
+            const int gy = nsof_clampi(ty0 - M + ly, 0, J.h - 1);
+            nsof_bulk_g2s(sM + c * SP + ly * PW + (cx0 - gx0), Min + c * plane + (size_t)gy * J.pitch + cx0, row_bytes, bar);
+        }
+    }
+    nsof_mbar_wait(bar, 0);
+    if (tx0 - M < 0 || tx0 + TW + M > J.w) {  // replicate the first / last image column into the halo
+        const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
+        const int s_first = -gx0, s_last = J.w - 1 - gx0;  // shared columns of image x = 0 and x = w - 1
+        for (int r = warp; r < 5 * LH; r += nw) {
+            float *row = sM + (r / LH) * SP + (r % LH) * PW;
+            if (tx0 - M < 0) {
+                const float v = row[s_first];
+                for (int sx = ML - M + lane; sx < s_first; sx += NSOF_WARP) row[sx] = v;
+            }
+            if (tx0 + TW + M > J.w) {
+                const float v = row[s_last];
+                NSOF_SYNCWARP();
+                for (int sx = s_last + 1 + lane; sx < ML + TW + M; sx += NSOF_WARP) row[sx] = v;
+            }
+        }
+    }
+    NSOF_SYNC();
+    // ---- phase 2
+    for (int col = NSOF_TID; col < 5 * LW; col += NSOF_NT) {
+        const int c = col / LW;
+        float *p = sM + c * SP + (ML - M) + (col - c * LW);
+        double s = 0.;
+#pragma unroll
+        for (int j = 0; j <= 2 * M; j++) s += (double)p[j * PW];
+#pragma unroll 4
+        for (int y = 0; y < TH; y++) {
+            const float old = p[y * PW];
+            p[y * PW] = (float)s;
+            if (y + 1 < TH) s += (double)p[(y + 2 * M + 1) * PW] - (double)old;
+        }
+    }
+    NSOF_SYNC();
+    // ---- phase 3
+    constexpr int GW = TW / 4;
+    for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
+        const int lx = (i % GW) * 4, ly = i / GW;
+        const int x = tx0 + lx, y = ty0 + ly;
+        if (x >= J.w || y >= J.h) continue;
+        float s[5][4];
+#pragma unroll
+        for (int c = 0; c < 5; c++) {
+            float v[NV * 4];
+            const float4 *q = (const float4 *)(sM + c * SP + ly * PW + lx);
+#pragma unroll
+            for (int k = 0; k < NV; k++) {
+                const float4 t = q[k];
+                v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
+            }
+            constexpr int B = ML - M;  // window of output 0 starts at v[B]
+            float common = 0.f;
+#pragma unroll
+            for (int j = 3; j <= 2 * M; j++) common += v[B + j];
+            const float v0 = v[B], v1 = v[B + 1], v2 = v[B + 2];
+            const float w1 = v[B + 2 * M + 1], w2 = v[B + 2 * M + 2], w3 = v[B + 2 * M + 3];
+            s[c][0] = common + ((v0 + v1) + v2);
+            s[c][1] = common + ((v1 + v2) + w1);
+            s[c][2] = common + ((v2 + w1) + w2);
+            s[c][3] = common + ((w1 + w2) + w3);
+        }
+        float fxv[4], fyv[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float g11 = s[0][q] * scale, g12 = s[1][q] * scale, g22 = s[2][q] * scale;
+            const float h1 = s[3][q] * scale, h2 = s[4][q] * scale;
+            const float idet = 1.f / (g11 * g22 - g12 * g12 + 1e-3f);
+            fxv[q] = (g11 * h2 - g12 * h1) * idet;
+            fyv[q] = (g22 * h1 - g12 * h2) * idet;
+        }
+        if (last) {
+            float2 *fo = J.flow + (size_t)y * J.fpitch + x;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (x + q < J.w) fo[q] = make_float2(fxv[q], fyv[q]);
+        } else {
+            const size_t o = (size_t)y * J.pitch + x;
+            float r0[5][4];
+#pragma unroll
+            for (int c = 0; c < 5; c++) {
+                const float4 t = NSOF_LDG((const float4 *)(J.R + c * plane + o));
+                r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
+            }
+            float mo[5][4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                float r0v[5], mm[5];
+                if (x + q < J.w) {
+#pragma unroll
+                    for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
+                    fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, fxv[q], fyv[q], r0v, mm);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 5; c++) mm[c] = 0.f;
+                }
+#pragma unroll
+                for (int c = 0; c < 5; c++) mo[c][q] = mm[c];
+            }
+#pragma unroll
+            for (int c = 0; c < 5; c++)
+                *(float4 *)(Mout + c * plane + o) = make_float4(mo[c][0], mo[c][1], mo[c][2], mo[c][3]);
+        }
+    }
+}
+
+#define FB_BS7_TW 64
+#define FB_BS7_TH 32
+// a plain function-pointer name: template commas do not survive nested launch macros
+static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH>;
+#define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))

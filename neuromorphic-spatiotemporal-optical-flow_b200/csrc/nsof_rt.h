@@ -94,3 +94,54 @@ NSOF_HD int nsof_reflect101(int p, int len)
     while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
     return p;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Bulk asynchronous row copies global -> shared (cp.async.bulk, the non-tensor TMA path: SASS UBLKCP)
+// completing on an mbarrier.  Rows of a halo tile are contiguous runs of 16-byte multiples, so no
+// tensor map is needed; border replication is fixed up in shared memory afterwards.
+// The emulator build copies synchronously.
+// ---------------------------------------------------------------------------------------------
+#ifdef NSOF_EMU
+typedef unsigned long long nsof_mbar_t;
+static inline void nsof_mbar_init(nsof_mbar_t *, int) {}
+static inline void nsof_mbar_expect_tx(nsof_mbar_t *, unsigned) {}
+static inline void nsof_bulk_g2s(void *dst, const void *src, unsigned bytes, nsof_mbar_t *) { memcpy(dst, src, bytes); }
+static inline void nsof_mbar_wait(nsof_mbar_t *, unsigned) {}
+#define NSOF_LANE 0
+#define NSOF_SYNCWARP() ((void)0)
+#else
+typedef unsigned long long nsof_mbar_t;
+__device__ __forceinline__ unsigned nsof_smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void nsof_mbar_init(nsof_mbar_t *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(nsof_smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void nsof_mbar_expect_tx(nsof_mbar_t *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(nsof_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void nsof_bulk_g2s(void *dst, const void *src, unsigned bytes, nsof_mbar_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     nsof_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(nsof_smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void nsof_mbar_wait(nsof_mbar_t *bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "NSOF_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra NSOF_MBAR_DONE;\n"
+        "bra NSOF_MBAR_WAIT;\n"
+        "NSOF_MBAR_DONE:\n"
+        "}\n" ::"r"(nsof_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+#define NSOF_LANE ((int)(threadIdx.x & 31))
+#define NSOF_SYNCWARP() __syncwarp()
+#endif
