@@ -122,6 +122,8 @@ NSOF_API double nsof_fb_algorithmic_bytes(int height, int width, const nsof_fb_p
  * what = 0 I(prev) 1 I(next) 2 R0 3 R1 4 M (current) 5 flow of that level.  `out` is a HOST
  * buffer of ch*h*w floats, planar [ch][h][w] (flow: interleaved [h][w][2]). */
 NSOF_API int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iters);
+/* enable = 0 forces the unfused pyramid + PolyExp kernels, which write I to the workspace (what = 0, 1). */
+NSOF_API int nsof_debug_fuse(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w);
 
 /* ---- stage 1: synaptic temporal memory -> ROI ------------------------------------------- */

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-DEFAULT_LIB_PATH = os.path.join(_HERE, "csrc", "libnsof.so")
+# NSOF_LIB_PATH: kernel-tuning experiments load an alternative build of the same sources
+DEFAULT_LIB_PATH = os.environ.get("NSOF_LIB_PATH") or os.path.join(_HERE, "csrc", "libnsof.so")
 
 NSOF_OK = 0
 NSOF_ERR_BAD_ARG = -1
@@ -82,6 +83,7 @@ _SIGNATURES = {
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),
     "nsof_debug_truncate": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "nsof_debug_fuse": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, _P(C.c_int), _P(C.c_int)]),
     "nsof_roi_from_state_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _P(RoiParams), C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

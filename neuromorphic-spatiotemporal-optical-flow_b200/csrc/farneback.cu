@@ -120,7 +120,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 
 // ------------------------------------------------------------------------------ launch accounting
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
-    "fb_pyr", "fb_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
+    "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
     "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
@@ -360,6 +360,9 @@ static int configure_smem(nsof_handle *h)
     if (h->smem_configured) return NSOF_OK;
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(1)));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     h->smem_configured = true;
     return NSOF_OK;
@@ -469,6 +472,11 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     unsigned char *hs = (unsigned char *)slot->host;
     unsigned char *ds = (unsigned char *)h->tables.p;
     std::vector<double> sumN(max_scales + 1, 0.), sumN0(max_scales, 0.);
+    // per level and pyramid path (0 generic, 1 fused level-0 shape, 2 fused exact-2x shape): items, pixels, source pixels
+    std::vector<int> path_n(3 * max_scales, 0), max_tiles_pp(max_scales, 0), max_tiles_ps(max_scales, 0);
+    std::vector<int> ps_sw(max_scales, 0), ps_sh(max_scales, 0);  // largest source window of a k_fb_pyr_sep tile
+    std::vector<double> path_N(3 * max_scales, 0.), path_N0(3 * max_scales, 0.);
+    const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
     std::vector<int> max_tiles_pyr(max_scales, 0), max_tiles_pe(max_scales, 0), max_tiles_um(max_scales, 0),
         max_tiles_bs(max_scales, 0);
     const int m = params->winsize / 2;
@@ -500,6 +508,10 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             else if (J.sh == 2 * J.h && J.sw == 2 * J.w) J.resize_mode = 1;  // cv::resize takes INTER_AREA at exact 2x
             else J.resize_mode = 2;
             J.sx = (double)J.sw / J.w; J.sy = (double)J.sh / J.h;
+            J.fast = (may_fuse && ksize[k] == 3 && J.resize_mode < 2) ? J.resize_mode + 1 : 0;
+            path_n[3 * k + J.fast] += 1;
+            path_N[3 * k + J.fast] += (double)J.h * J.w;
+            path_N0[3 * k + J.fast] += (double)J.sh * J.sw;
             J.I = base + pl.off_I; J.R = base + pl.off_R; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
             // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
             float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
@@ -513,6 +525,12 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             auto tiles = [&](int tw, int th) { return ((J.w + tw - 1) / tw) * ((J.h + th - 1) / th); };
             max_tiles_pyr[k] = std::max(max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH));
             max_tiles_pe[k] = std::max(max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH));
+            max_tiles_pp[k] = std::max(max_tiles_pp[k], tiles(FB_PP_TW, FB_PP_TH));
+            if (!J.fast) {
+                max_tiles_ps[k] = std::max(max_tiles_ps[k], tiles(FB_PS_TW, FB_PS_TH));
+                ps_sw[k] = std::max(ps_sw[k], (int)ceil(FB_PS_TW * J.sx) + 2 * (ksize[k] / 2) + 4);
+                ps_sh[k] = std::max(ps_sh[k], (int)ceil(FB_PS_TH * J.sy) + 2 * (ksize[k] / 2) + 4);
+            }
             max_tiles_um[k] = std::max(max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH));
             if (BTW) max_tiles_bs[k] = std::max(max_tiles_bs[k], tiles(BTW, BTH));
         }
@@ -542,8 +560,23 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
         const double Nk = sumN[k];
         h->prof_level = k;
-        NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * sumN0[k], k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, ksize[k] / 2);
-        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * Nk, k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream, jobs, pc);
+        if (path_n[3 * k + 1])
+            NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * path_N0[3 * k + 1] + 40 * path_N[3 * k + 1], FB_PYR_POLYEXP_M0,
+                         max_tiles_pp[k], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
+        if (path_n[3 * k + 2])
+            NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * path_N0[3 * k + 2] + 40 * path_N[3 * k + 2], FB_PYR_POLYEXP_M1,
+                         max_tiles_pp[k], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
+        if (path_n[3 * k]) {
+            const size_t ps_smem = fb_ps_smem(ksize[k] / 2, ps_sw[k], ps_sh[k]);
+            if (ps_smem <= 100 * 1024)  // two CTAs per SM; larger windows (extreme ratios) take the direct kernel
+                NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * path_N0[3 * k], k_fb_pyr_sep, max_tiles_ps[k], na, 2, 256, ps_smem, stream, jobs,
+                             gk, ksize[k] / 2, ps_sw[k], ps_sh[k]);
+            else
+                NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * path_N0[3 * k], k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk,
+                             ksize[k] / 2);
+            NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * path_N[3 * k], k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream,
+                         jobs, pc);
+        }
         if (params->iterations == 0) {
             NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * Nc + 8 * Nk, k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
                          flow_mul);
@@ -554,7 +587,7 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
                 const bool last = it == iters - 1;
                 if (bs_m7)
                     NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7,
-                                 max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, bscale, (it & 1) == 0, last);
+                                 max_tiles_bs[k], na, 1, FB_BS7_NT, bs_smem, stream, jobs, bscale, (it & 1) == 0, last);
                 else
                     NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve,
                                  max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale, (it & 1) == 0, last);
@@ -643,6 +676,13 @@ extern "C" int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iter
     return NSOF_OK;
 }
 
+extern "C" int nsof_debug_fuse(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_no_fuse = !enable;
+    return NSOF_OK;
+}
+
 extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w)
 {
     if (!h || !out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: NULL argument");
@@ -660,6 +700,8 @@ extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, 
     if (out_w) *out_w = ww;
     const float *src;
     int ch;
+    if (what <= 1 && !h->dbg_no_fuse)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: I is not materialised by the fused pyramid kernels; call nsof_debug_fuse(h, 0) first");
     switch (what) {
     case 0: src = base + pl.off_I; ch = 1; break;
     case 1: src = base + pl.off_I + plane; ch = 1; break;

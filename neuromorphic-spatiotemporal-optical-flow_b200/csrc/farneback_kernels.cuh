@@ -19,8 +19,20 @@
 // blocks past an item's tile count exit at once, which is how ragged ROI crops batch.
 #pragma once
 #include "nsof_rt.h"
+#include <algorithm>
 
 #define NSOF_MAX_POLY_N 31
+#define FB_BS7_TW 64
+#ifndef FB_BS7_TH
+#define FB_BS7_TH 32
+#endif
+#ifndef FB_BS7_NT
+#define FB_BS7_NT 256
+#endif
+#ifndef FB_BS7_MINB
+#define FB_BS7_MINB 3
+#endif
+
 
 struct FbJob {
     int h, w, pitch;       // this level
@@ -29,6 +41,7 @@ struct FbJob {
     int spitch0, spitch1;  // source row pitches, bytes
     int fpitch;            // pitch of `flow`, float2 units
     int resize_mode;       // 0 identity, 1 exact 2x (2x2 mean), 2 bilinear
+    int fast;              // 0: generic k_fb_pyr + k_fb_polyexp; 1 / 2: fused k_fb_pyr_polyexp_t<MODE 0 / 1>
     double sx, sy;         // src/dst ratio of the pyramid resize
     double fsx, fsy;       // coarse/this ratio of the flow upsample
     const uint8_t *src0, *src1;
@@ -95,6 +108,7 @@ NSOF_DEV void fb_lin_coord(int d, double ratio, int len, int *i0, int *i1, float
 NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk, int r)
 {
     const FbJob J = jobs[NSOF_BY];
+    if (J.fast) return;
     const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW, tiles_y = (J.h + FB_PYR_TH - 1) / FB_PYR_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
@@ -142,6 +156,7 @@ NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT
 NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, PolyConst pc)
 {
     const FbJob J = jobs[NSOF_BY];
+    if (J.fast) return;
     const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW, tiles_y = (J.h + FB_PE_TH - 1) / FB_PE_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
@@ -425,7 +440,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
 // dynamic smem: 16 B (mbarrier) + 5 * (TH+2M) * (TW+2ML) floats.
 // ---------------------------------------------------------------------------------------------
 template <int M, int TW, int TH>
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
 {
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, LW = TW + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
@@ -444,16 +459,16 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTR
     const int gx0 = tx0 - ML;                                         // global x of shared column 0
     const int cx0 = nsof_imax(gx0, 0), cx1 = nsof_imin(tx0 + TW + ML, J.pitch);  // copied run, multiples of 4
     const unsigned row_bytes = (unsigned)(cx1 - cx0) * 4u;
-    if (NSOF_TID == 0) nsof_mbar_init(bar, 1);
+    if (NSOF_TID == 0) {
+        nsof_mbar_init(bar, 1);
+        nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(5 * LH));
+    }
     NSOF_SYNC();
-    if (NSOF_TID < NSOF_WARP) {
-        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(5 * LH));
-        NSOF_SYNCWARP();
-        for (int r = NSOF_TID; r < 5 * LH; r += NSOF_WARP) {
-            const int c = r / LH, ly = r - c * LH;
-            const int gy = nsof_clampi(ty0 - M + ly, 0, J.h - 1);
-            nsof_bulk_g2s(sM + c * SP + ly * PW + (cx0 - gx0), Min + c * plane + (size_t)gy * J.pitch + cx0, row_bytes, bar);
-        }
+    // every thread issues at most a few row copies: the issue cost is spread over all warps
+    for (int r = NSOF_TID; r < 5 * LH; r += NSOF_NT) {
+        const int c = r / LH, ly = r - c * LH;
+        const int gy = nsof_clampi(ty0 - M + ly, 0, J.h - 1);
+        nsof_bulk_g2s(sM + c * SP + ly * PW + (cx0 - gx0), Min + c * plane + (size_t)gy * J.pitch + cx0, row_bytes, bar);
     }
     nsof_mbar_wait(bar, 0);
     if (tx0 - M < 0 || tx0 + TW + M > J.w) {  // replicate the first / last image column into the halo
@@ -477,6 +492,17 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTR
     for (int col = NSOF_TID; col < 5 * LW; col += NSOF_NT) {
         const int c = col / LW;
         float *p = sM + c * SP + (ML - M) + (col - c * LW);
+#ifdef FB_BS_FLOAT_V
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j <= 2 * M; j++) s += p[j * PW];
+#pragma unroll 4
+        for (int y = 0; y < TH; y++) {
+            const float old = p[y * PW];
+            p[y * PW] = s;
+            if (y + 1 < TH) s += p[(y + 2 * M + 1) * PW] - old;
+        }
+#else
         double s = 0.;
 #pragma unroll
         for (int j = 0; j <= 2 * M; j++) s += (double)p[j * PW];
@@ -486,6 +512,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTR
             p[y * PW] = (float)s;
             if (y + 1 < TH) s += (double)p[(y + 2 * M + 1) * PW] - (double)old;
         }
+#endif
     }
     NSOF_SYNC();
     // ---- phase 3
@@ -559,8 +586,347 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_blur_solve_t(const FbJob *NSOF_RESTR
     }
 }
 
-#define FB_BS7_TW 64
-#define FB_BS7_TH 32
 // a plain function-pointer name: template commas do not survive nested launch macros
 static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH>;
 #define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
+
+// ---------------------------------------------------------------------------------------------
+// S2-b + S2-c fused for the two pyramid shapes every BASELINE.json config spends its time in:
+//   MODE 0  level 0        : I = GaussianBlur3x3(src)                       (no resize)
+//   MODE 1  exact 2x level : I = 2x2 mean of GaussianBlur3x3(src)           (cv::resize at exactly 1/2)
+// followed by FarnebackPolyExp with compile-time radius N.  The blurred image I never exists in HBM: the
+// uint8 source window of the tile (+ N halo, + blur taps) is staged in shared memory, I is built there,
+// the vertical moment pass writes three planes to shared memory and the horizontal pass writes R with
+// float4 stores.  Per-pixel arithmetic (order of operations) is that of k_fb_pyr + k_fb_polyexp.
+// grid (tiles, items, 2 images); items whose FbJob.fast != MODE + 1 exit (they take the generic kernels).
+// static smem: max(3*TH*IP*4, SH*SW) + IH*IP*4 bytes  (IP = roundup4(TW+2N)).
+// ---------------------------------------------------------------------------------------------
+template <int MODE, int N, int TW, int TH>
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk,
+                                                         PolyConst pc)
+{
+    constexpr int IW = TW + 2 * N, IH = TH + 2 * N, IP = (IW + 3) & ~3;
+    constexpr int SWN = (MODE ? 2 * IW : IW) + 2, SHN = (MODE ? 2 * IH : IH) + 2;  // source window actually needed
+    constexpr int SW = (SWN + 3) & ~3;                                              // pitch of the float window
+    constexpr int RP = (SWN + 32 + 15) & ~15;                                       // pitch of the raw uint8 window
+    constexpr int A_BYTES = (3 * TH * IP * 4 > SHN * SW * 4 ? 3 * TH * IP * 4 : SHN * SW * 4);  // S (float) | sr
+    constexpr int B_BYTES = (IH * IP * 4 > SHN * RP ? IH * IP * 4 : SHN * RP);                  // raw u8 | sI
+    constexpr int BSTRIP = 14, BNS = (IH + BSTRIP - 1) / BSTRIP;
+    static_assert(A_BYTES % 16 == 0 && B_BYTES % 16 == 0, "shared regions must stay 16-byte aligned");
+    const FbJob J = jobs[NSOF_BY];
+    if (J.fast != MODE + 1) return;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const int img = NSOF_BZ;
+    const uint8_t *src = img ? J.src1 : J.src0;
+    const int sp = img ? J.spitch1 : J.spitch0;
+    const size_t plane = (size_t)J.pitch * J.h;
+    float *R = J.R + (size_t)img * 5 * plane;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    NSOF_DYN_SMEM(smem_raw);
+    nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
+    float *sS = (float *)(smem_raw + 16);                 // phases A2/B
+    float *sr = (float *)(smem_raw + 16);                 // phases C/D (aliases sS)
+    uint8_t *sraw = smem_raw + 16 + A_BYTES;              // phase A
+    float *sI = (float *)(smem_raw + 16 + A_BYTES);       // phases B/C (aliases sraw)
+    const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
+
+    // I positions of the tile + halo that lie inside the level image: lx in [lx_lo, lx_hi), ly in [ly_lo, ly_hi).
+    // Positions outside are PolyExp's replicate border and are filled from these after phase B.
+    const int lx_lo = nsof_imax(0, N - tx0), lx_hi = nsof_imin(IW, J.w - (tx0 - N));
+    const int ly_lo = nsof_imax(0, N - ty0), ly_hi = nsof_imin(IH, J.h - (ty0 - N));
+    const int cx_lo = tx0 - N + lx_lo, cy_lo = ty0 - N + ly_lo;
+    // source window: shared (sy, sx) <-> source (Ylo + sy, Xlo + sx), BORDER_REFLECT_101 outside the source
+    const int Xlo = (MODE ? 2 * cx_lo : cx_lo) - 1, Ylo = (MODE ? 2 * cy_lo : cy_lo) - 1;
+
+    // ---- A: stage the window.  Interior tiles: one bulk asynchronous copy per row (16-byte aligned superset of
+    // the row), then uint8 -> float once per source pixel.  Border tiles: per-pixel loads with reflection.
+    const bool bulk = Xlo >= 16 && Xlo + SWN + 16 <= J.sw && Ylo >= 0 && Ylo + SHN <= J.sh && (sp & 15) == 0;
+    if (bulk) {
+        const uint8_t *a0 = src + (size_t)Ylo * sp + Xlo;
+        const int shift = (int)((uintptr_t)a0 & 15);
+        const unsigned row_bytes = (unsigned)((shift + SWN + 15) & ~15);
+        if (NSOF_TID == 0) {
+            nsof_mbar_init(bar, 1);
+            nsof_mbar_expect_tx(bar, row_bytes * (unsigned)SHN);
+        }
+        NSOF_SYNC();
+        for (int r = NSOF_TID; r < SHN; r += NSOF_NT) nsof_bulk_g2s(sraw + r * RP, a0 - shift + (size_t)r * sp, row_bytes, bar);
+        nsof_mbar_wait(bar, 0);
+        // A2: 4 source pixels per thread: two aligned words, funnel shift by the misalignment, 4 conversions
+        constexpr int G = SW / 4;
+        for (int i = NSOF_TID; i < SHN * G; i += NSOF_NT) {
+            const int sy = i / G, g = i - sy * G;
+            const uint32_t *wp = (const uint32_t *)(sraw + sy * RP) + g + (shift >> 2);
+            const uint32_t w0 = wp[0], w1 = wp[1];
+            const int sh8 = (shift & 3) * 8;
+            const uint32_t u = sh8 ? ((w0 >> sh8) | (w1 << (32 - sh8))) : w0;
+            *(float4 *)(sS + sy * SW + 4 * g) =
+                make_float4((float)(u & 255u), (float)((u >> 8) & 255u), (float)((u >> 16) & 255u), (float)(u >> 24));
+        }
+    } else {
+        for (int sy = warp; sy < SHN; sy += nw) {
+            const uint8_t *row = src + (size_t)nsof_reflect101(Ylo + sy, J.sh) * sp;
+            for (int sx = lane; sx < SWN; sx += NSOF_WARP) sS[sy * SW + sx] = (float)NSOF_LDG(row + nsof_reflect101(Xlo + sx, J.sw));
+        }
+    }
+    NSOF_SYNC();
+    // ---- B: I tile with halo; one thread per (column, strip of BSTRIP rows), row-blurred samples slide down
+    {
+        const float g0 = gk[0], g1 = gk[1];
+        for (int i = NSOF_TID; i < IW * BNS; i += NSOF_NT) {
+            const int st = i / IW, lx = i - st * IW;
+            if (lx < lx_lo || lx >= lx_hi) continue;
+            const int y_a = nsof_imax(st * BSTRIP, ly_lo), y_b = nsof_imin(nsof_imin((st + 1) * BSTRIP, IH), ly_hi);
+            if (y_a >= y_b) continue;
+            if (MODE == 0) {
+                const float *c = sS + (y_a - ly_lo) * SW + (lx - lx_lo) + 1;  // row above the first centre row
+                float rbm, rb0;
+                { float acc = g0 * c[0]; acc = acc + g1 * (c[-1] + c[1]); rbm = acc; }
+                c += SW;
+                { float acc = g0 * c[0]; acc = acc + g1 * (c[-1] + c[1]); rb0 = acc; }
+                for (int ly = y_a; ly < y_b; ly++) {
+                    c += SW;
+                    float rbp = g0 * c[0];
+                    rbp = rbp + g1 * (c[-1] + c[1]);
+                    float acc = g0 * rb0;
+                    acc = acc + g1 * (rbm + rbp);
+                    sI[ly * IP + lx] = acc;
+                    rbm = rb0;
+                    rb0 = rbp;
+                }
+            } else {
+                // I(ly) needs source rows 2(ly-ly_lo) .. +3 and columns 2(lx-lx_lo) .. +3 of the window
+                const float *c = sS + 2 * (y_a - ly_lo) * SW + 2 * (lx - lx_lo);
+                float h0[2], h1[2], h2[2], h3[2];
+#define FB_HB(dst, row)                                                                  \
+    {                                                                                    \
+        const float2 pa = *(const float2 *)(row), pb = *(const float2 *)((row) + 2);     \
+        float a0 = g0 * pa.y; a0 = a0 + g1 * (pa.x + pb.x);                              \
+        float a1 = g0 * pb.x; a1 = a1 + g1 * (pa.y + pb.y);                              \
+        dst[0] = a0; dst[1] = a1;                                                        \
+    }
+                FB_HB(h0, c);
+                FB_HB(h1, c + SW);
+                for (int ly = y_a; ly < y_b; ly++) {
+                    FB_HB(h2, c + 2 * SW);
+                    FB_HB(h3, c + 3 * SW);
+                    float s00 = g0 * h1[0]; s00 = s00 + g1 * (h0[0] + h2[0]);
+                    float s01 = g0 * h1[1]; s01 = s01 + g1 * (h0[1] + h2[1]);
+                    float s10 = g0 * h2[0]; s10 = s10 + g1 * (h1[0] + h3[0]);
+                    float s11 = g0 * h2[1]; s11 = s11 + g1 * (h1[1] + h3[1]);
+                    sI[ly * IP + lx] = (s00 + s01 + s10 + s11) * 0.25f;
+                    h0[0] = h2[0]; h0[1] = h2[1]; h1[0] = h3[0]; h1[1] = h3[1];
+                    c += 2 * SW;
+                }
+#undef FB_HB
+            }
+        }
+    }
+    NSOF_SYNC();
+    if (lx_lo > 0 || lx_hi < IW || ly_lo > 0 || ly_hi < IH) {  // replicate border of the level image
+        for (int ly = warp; ly < IH; ly += nw) {
+            const int sy = nsof_clampi(ly, ly_lo, ly_hi - 1);
+            for (int lx = lane; lx < IW; lx += NSOF_WARP) {
+                const int sx = nsof_clampi(lx, lx_lo, lx_hi - 1);
+                if (sx != lx || sy != ly) sI[ly * IP + lx] = sI[sy * IP + sx];
+            }
+        }
+        NSOF_SYNC();
+    }
+    // ---- C: vertical moments, one thread per (column, strip of 8 rows), the column window kept in registers
+    {
+        constexpr int STRIP = 8, NS = TH / STRIP;
+        for (int i = NSOF_TID; i < IW * NS; i += NSOF_NT) {
+            const int lx = i % IW, st = i / IW;
+            float col[STRIP + 2 * N];
+#pragma unroll
+            for (int j = 0; j < STRIP + 2 * N; j++) col[j] = sI[(st * STRIP + j) * IP + lx];
+#pragma unroll
+            for (int y = 0; y < STRIP; y++) {
+                float r0 = col[y + N] * pc.g[0], r1 = 0.f, r2 = 0.f;
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float a = col[y + N - k], b = col[y + N + k];
+                    const float p = a + b;
+                    r0 = r0 + pc.g[k] * p;
+                    r1 = r1 + pc.xg[k] * (b - a);
+                    r2 = r2 + pc.xxg[k] * p;
+                }
+                const int o = (st * STRIP + y) * IP + lx;
+                sr[o] = r0;
+                sr[TH * IP + o] = r1;
+                sr[2 * TH * IP + o] = r2;
+            }
+        }
+    }
+    NSOF_SYNC();
+    // ---- D: horizontal pass, 4 outputs per thread
+    {
+        constexpr int GW = TW / 4, NV = (4 + 2 * N + 3) / 4;
+        for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
+            const int lx = (i % GW) * 4, ly = i / GW;
+            const int x = tx0 + lx, y = ty0 + ly;
+            if (x >= J.w || y >= J.h) continue;
+            float q[3][NV * 4];
+#pragma unroll
+            for (int p = 0; p < 3; p++) {
+                const float4 *s4 = (const float4 *)(sr + p * TH * IP + ly * IP + lx);
+#pragma unroll
+                for (int k = 0; k < NV; k++) {
+                    const float4 t = s4[k];
+                    q[p][4 * k] = t.x; q[p][4 * k + 1] = t.y; q[p][4 * k + 2] = t.z; q[p][4 * k + 3] = t.w;
+                }
+            }
+            float o0[4], o1[4], o2[4], o3[4], o4[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int ctr = e + N;
+                const float g0 = pc.g[0];
+                float b1 = q[0][ctr] * g0, b2 = 0.f, b3 = q[1][ctr] * g0, b4 = 0.f, b5 = q[2][ctr] * g0, b6 = 0.f;
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float gkk = pc.g[k], xgk = pc.xg[k], xxgk = pc.xxg[k];
+                    const float p0 = q[0][ctr + k], m0 = q[0][ctr - k], p1 = q[1][ctr + k], m1 = q[1][ctr - k];
+                    const float p2 = q[2][ctr + k], m2 = q[2][ctr - k];
+                    const float tg = p0 + m0;
+                    b1 += tg * gkk;
+                    b4 += tg * xxgk;
+                    b2 += (p0 - m0) * xgk;
+                    b3 += (p1 + m1) * gkk;
+                    b6 += (p1 - m1) * xgk;
+                    b5 += (p2 + m2) * gkk;
+                }
+                o0[e] = b3 * pc.ig11;
+                o1[e] = b2 * pc.ig11;
+                o2[e] = b1 * pc.ig03 + b5 * pc.ig33;
+                o3[e] = b1 * pc.ig03 + b4 * pc.ig33;
+                o4[e] = b6 * pc.ig55;
+            }
+            const size_t o = (size_t)y * J.pitch + x;
+            *(float4 *)(R + o) = make_float4(o0[0], o0[1], o0[2], o0[3]);
+            *(float4 *)(R + plane + o) = make_float4(o1[0], o1[1], o1[2], o1[3]);
+            *(float4 *)(R + 2 * plane + o) = make_float4(o2[0], o2[1], o2[2], o2[3]);
+            *(float4 *)(R + 3 * plane + o) = make_float4(o3[0], o3[1], o3[2], o3[3]);
+            *(float4 *)(R + 4 * plane + o) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+        }
+    }
+}
+
+#define FB_PP_TW 64
+#define FB_PP_TH 32
+#define FB_PP_N 5
+static void (*const FB_PYR_POLYEXP_M0)(const FbJob *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, FB_PP_N, FB_PP_TW, FB_PP_TH>;
+static void (*const FB_PYR_POLYEXP_M1)(const FbJob *, const float *, PolyConst) = k_fb_pyr_polyexp_t<1, FB_PP_N, FB_PP_TW, FB_PP_TH>;
+static inline size_t fb_pp_smem(int mode)
+{
+    const int IW = FB_PP_TW + 2 * FB_PP_N, IH = FB_PP_TH + 2 * FB_PP_N, IP = (IW + 3) & ~3;
+    const int SWN = (mode ? 2 * IW : IW) + 2, SHN = (mode ? 2 * IH : IH) + 2, SW = (SWN + 3) & ~3, RP = (SWN + 32 + 15) & ~15;
+    const int a = std::max(3 * FB_PP_TH * IP * 4, SHN * SW * 4), b = std::max(IH * IP * 4, SHN * RP);
+    return 16 + (size_t)a + (size_t)b;
+}
+
+// ---------------------------------------------------------------------------------------------
+// S2-b generic (any ksize, any resize ratio), separable through shared memory.  Same per-sample arithmetic as
+// k_fb_pyr (horizontal taps first, then the vertical combination, then the resize formula) but each blurred
+// sample the resize touches is computed once per tile instead of once per output pixel:
+//   1  resize source coordinates of the tile's columns / rows                  -> cols[2*TW], rows[2*TH]
+//   2  uint8 source window (reflect-101 applied while loading)                 -> sS
+//   3  horizontal blur at the needed columns for every window row              -> sHb
+//   4  vertical blur at the needed rows                                        -> sB  (2TH x 2TW)
+//   5  resize combine, write I
+// dynamic smem (host-sized from the largest ratio of the batch): see fb_ps_smem().
+// ---------------------------------------------------------------------------------------------
+#define FB_PS_TW 32
+#define FB_PS_TH 16
+
+NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk, int r, int SWmax, int SHmax)
+{
+    constexpr int TW = FB_PS_TW, TH = FB_PS_TH;
+    const FbJob J = jobs[NSOF_BY];
+    if (J.fast) return;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const int img = NSOF_BZ;
+    const uint8_t *src = img ? J.src1 : J.src0;
+    const int sp = img ? J.spitch1 : J.spitch0;
+    float *dst = J.I + (size_t)img * J.pitch * J.h;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    const int twn = nsof_imin(TW, J.w - tx0), thn = nsof_imin(TH, J.h - ty0);
+    const int SWp = (SWmax + 3) & ~3;
+    NSOF_DYN_SMEM(smem_raw);
+    int *cols = (int *)smem_raw, *rows = cols + 2 * TW;
+    float *ax = (float *)(rows + 2 * TH), *ay = ax + TW, *sg = ay + TH;  // sg: r + 1 taps
+    float *sB = sg + ((r + 1 + 3) & ~3);
+    float *sHb = sB + 2 * TH * 2 * TW;
+    uint8_t *sS = (uint8_t *)(sHb + (size_t)SHmax * 2 * TW);
+    const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
+
+    for (int i = NSOF_TID; i < TW + TH + r + 1; i += NSOF_NT) {
+        if (i < TW + TH) {
+            const bool isx = i < TW;
+            const int d = isx ? nsof_imin(tx0 + i, J.w - 1) : nsof_imin(ty0 + (i - TW), J.h - 1);
+            int i0, i1;
+            float a;
+            if (J.resize_mode == 0) { i0 = i1 = d; a = 0.f; }
+            else if (J.resize_mode == 1) { i0 = 2 * d; i1 = 2 * d + 1; a = 0.5f; }
+            else fb_lin_coord(d, isx ? J.sx : J.sy, isx ? J.sw : J.sh, &i0, &i1, &a);
+            if (isx) { cols[2 * i] = i0; cols[2 * i + 1] = i1; ax[i] = a; }
+            else { rows[2 * (i - TW)] = i0; rows[2 * (i - TW) + 1] = i1; ay[i - TW] = a; }
+        } else {
+            sg[i - TW - TH] = gk[i - TW - TH];
+        }
+    }
+    NSOF_SYNC();
+    const int Xmin = cols[0] - r, Ymin = rows[0] - r;
+    const int swn = nsof_imin(cols[2 * twn - 1] + r - Xmin + 1, SWmax), shn = nsof_imin(rows[2 * thn - 1] + r - Ymin + 1, SHmax);
+    for (int sy = warp; sy < shn; sy += nw) {
+        const uint8_t *row = src + (size_t)nsof_reflect101(Ymin + sy, J.sh) * sp;
+        for (int sx = lane; sx < swn; sx += NSOF_WARP) sS[sy * SWp + sx] = NSOF_LDG(row + nsof_reflect101(Xmin + sx, J.sw));
+    }
+    NSOF_SYNC();
+    const float g0 = sg[0];
+    for (int sy = warp; sy < shn; sy += nw) {
+        const uint8_t *row = sS + sy * SWp;
+        for (int ci = lane; ci < 2 * twn; ci += NSOF_WARP) {
+            const uint8_t *c = row + (cols[ci] - Xmin);
+            float acc = g0 * (float)c[0];
+            for (int i = 1; i <= r; i++) acc = acc + sg[i] * ((float)c[-i] + (float)c[i]);
+            sHb[sy * 2 * TW + ci] = acc;
+        }
+    }
+    NSOF_SYNC();
+    for (int ri = warp; ri < 2 * thn; ri += nw) {
+        const float *rowc = sHb + (rows[ri] - Ymin) * 2 * TW;
+        for (int ci = lane; ci < 2 * twn; ci += NSOF_WARP) {
+            const float *c = rowc + ci;
+            float acc = g0 * c[0];
+            for (int i = 1; i <= r; i++) acc = acc + sg[i] * (c[-i * 2 * TW] + c[i * 2 * TW]);
+            sB[ri * 2 * TW + ci] = acc;
+        }
+    }
+    NSOF_SYNC();
+    for (int ly = warp; ly < thn; ly += nw) {
+        for (int lx = lane; lx < twn; lx += NSOF_WARP) {
+            const float s00 = sB[(2 * ly) * 2 * TW + 2 * lx], s01 = sB[(2 * ly) * 2 * TW + 2 * lx + 1];
+            const float s10 = sB[(2 * ly + 1) * 2 * TW + 2 * lx], s11 = sB[(2 * ly + 1) * 2 * TW + 2 * lx + 1];
+            float v;
+            if (J.resize_mode == 0) v = s00;
+            else if (J.resize_mode == 1) v = (s00 + s01 + s10 + s11) * 0.25f;
+            else {
+                const float a = ax[lx], b = ay[ly];
+                const float top = s00 * (1.f - a) + s01 * a;
+                const float bot = s10 * (1.f - a) + s11 * a;
+                v = top * (1.f - b) + bot * b;
+            }
+            dst[(size_t)(ty0 + ly) * J.pitch + tx0 + lx] = v;
+        }
+    }
+}
+
+static inline size_t fb_ps_smem(int r, int SWmax, int SHmax)
+{
+    const size_t SWp = (SWmax + 3) & ~3;
+    return (2 * FB_PS_TW + 2 * FB_PS_TH) * sizeof(int) + (FB_PS_TW + FB_PS_TH + ((r + 1 + 3) & ~3)) * sizeof(float) +
+           (size_t)2 * FB_PS_TH * 2 * FB_PS_TW * sizeof(float) + (size_t)SHmax * 2 * FB_PS_TW * sizeof(float) + SWp * SHmax;
+}

@@ -48,7 +48,7 @@ struct FbItemPlan;  // farneback.cu
 
 // Kernel classes for the launch counter and the optional per-launch event timing (nsof_profile*).
 enum NsofKernelClass {
-    NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
+    NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_PYR_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
     NSOF_K_LANCZOS, NSOF_K_FRAME_SIM, NSOF_K_ROI, NSOF_K_EVENT_HIST, NSOF_K_EVENT_REPLAY, NSOF_K_SYNAPSE_STEP,
     NSOF_K_RESISTANCE, NSOF_K_CLASSES
 };
@@ -74,6 +74,7 @@ struct nsof_handle {
     int stage_next = 0;
     // debug truncation (tests only)
     int dbg_level = -1, dbg_iters = -1;
+    bool dbg_no_fuse = false;  // force the generic pyramid + PolyExp kernels (so that I exists and can be fetched)
     // geometry of the last batch, kept for nsof_debug_fetch
     std::vector<FbItemPlan> *last_plan = nullptr;
     int last_stop_level = 0;

@@ -257,6 +257,9 @@ class Engine:
     def debug_truncate(self, stop_level=-1, stop_iters=-1):
         self.lib.check(self.lib.nsof_debug_truncate(self.handle, stop_level, stop_iters))
 
+    def debug_fuse(self, enable: bool):
+        self.lib.check(self.lib.nsof_debug_fuse(self.handle, 1 if enable else 0))
+
     def debug_fetch(self, item, what, h, w):
         ch = {0: 1, 1: 1, 2: 5, 3: 5, 4: 5, 5: 2}[what]
         out = np.empty((ch, h, w) if what != 5 else (h, w, 2), dtype=np.float32)

@@ -27,19 +27,26 @@ def test_farneback_vs_cv2_golden(gpu_engine, golden, pname):
         helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"gpu vs cv2 {case}")
 
 
-def test_stage_dumps_vs_oracle(gpu_engine, oracle):
-    """Every intermediate (I, R0, R1, M, per-iteration flow) of every level against the oracle's dump."""
-    prev, nxt = helpers.textured_pair(5, 150, 203)
+@pytest.mark.parametrize("hw,fuse", [((150, 203), False), ((152, 204), True), ((150, 203), True)])
+def test_stage_dumps_vs_oracle(gpu_engine, oracle, hw, fuse):
+    """Every intermediate (I, R0, R1, M, per-iteration flow) of every level against the oracle's dump, through the
+    generic pyramid + PolyExp kernels (fuse off: I is materialised) and through the fused ones (152 x 204 has an
+    exact-2x level 1)."""
+    prev, nxt = helpers.textured_pair(5, *hw)
     p = helpers.PARAM_SETS["grasp"]
     _, st = oracle.farneback(prev, nxt, **p, dump=True)
-    geo = oracle.level_geometry(150, 203, p["pyr_scale"], p["levels"])
+    geo = oracle.level_geometry(hw[0], hw[1], p["pyr_scale"], p["levels"])
+    assert len(geo) == 3
     try:
+        gpu_engine.debug_fuse(fuse)
         for k, (hk, wk, _, _) in enumerate(geo):
             for it in (0, 1, p["iterations"]):
                 gpu_engine.debug_truncate(k, it)
                 gpu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
                 if it == 0:
-                    for what, tag in ((2, 2), (3, 3), (4, 4)):
+                    for what, tag in ((0, 0), (1, 1), (2, 2), (3, 3), (4, 4)):
+                        if what <= 1 and fuse:
+                            continue
                         got = helpers.planar_to_aos(gpu_engine.debug_fetch(0, what, hk, wk))
                         want = st[(tag, k, 0)]
                         scale = max(1.0, float(np.abs(want).max()))
@@ -50,6 +57,7 @@ def test_stage_dumps_vs_oracle(gpu_engine, oracle):
                     assert np.abs(got - want).max() <= 2e-4, (k, it)
     finally:
         gpu_engine.debug_truncate(-1, -1)
+        gpu_engine.debug_fuse(True)
 
 
 def test_batch_ragged_and_strided(gpu_engine, oracle):
