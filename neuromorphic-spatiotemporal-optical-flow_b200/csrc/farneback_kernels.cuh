@@ -853,9 +853,10 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
     float *dst = J.I + (size_t)img * J.pitch * J.h;
     const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
     const int twn = nsof_imin(TW, J.w - tx0), thn = nsof_imin(TH, J.h - ty0);
-    const int SWp = (SWmax + 3) & ~3;
+    const int SWp = (SWmax + 32 + 15) & ~15;
     NSOF_DYN_SMEM(smem_raw);
-    int *cols = (int *)smem_raw, *rows = cols + 2 * TW;
+    nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
+    int *cols = (int *)(smem_raw + 16), *rows = cols + 2 * TW;
     float *ax = (float *)(rows + 2 * TH), *ay = ax + TW, *sg = ay + TH;  // sg: r + 1 taps
     float *sB = sg + ((r + 1 + 3) & ~3);
     float *sHb = sB + 2 * TH * 2 * TW;
@@ -877,21 +878,37 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
             sg[i - TW - TH] = gk[i - TW - TH];
         }
     }
+    if (NSOF_TID == 0) nsof_mbar_init(bar, 1);
     NSOF_SYNC();
     const int Xmin = cols[0] - r, Ymin = rows[0] - r;
     const int swn = nsof_imin(cols[2 * twn - 1] + r - Xmin + 1, SWmax), shn = nsof_imin(rows[2 * thn - 1] + r - Ymin + 1, SHmax);
-    for (int sy = warp; sy < shn; sy += nw) {
-        const uint8_t *row = src + (size_t)nsof_reflect101(Ymin + sy, J.sh) * sp;
-        for (int sx = lane; sx < swn; sx += NSOF_WARP) sS[sy * SWp + sx] = NSOF_LDG(row + nsof_reflect101(Xmin + sx, J.sw));
+    // interior tiles: one bulk asynchronous copy per window row (16-byte aligned superset); border tiles: per-pixel
+    // loads with BORDER_REFLECT_101
+    const bool bulk = Xmin >= 16 && Xmin + swn + 16 <= J.sw && Ymin >= 0 && Ymin + shn <= J.sh && (sp & 15) == 0;
+    int shift = 0;
+    if (bulk) {
+        const uint8_t *a0 = src + (size_t)Ymin * sp + Xmin;
+        shift = (int)((uintptr_t)a0 & 15);
+        const unsigned row_bytes = (unsigned)((shift + swn + 15) & ~15);
+        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, row_bytes * (unsigned)shn);
+        NSOF_SYNC();
+        for (int sy = NSOF_TID; sy < shn; sy += NSOF_NT) nsof_bulk_g2s(sS + sy * SWp, a0 - shift + (size_t)sy * sp, row_bytes, bar);
+        nsof_mbar_wait(bar, 0);
+    } else {
+        for (int sy = warp; sy < shn; sy += nw) {
+            const uint8_t *row = src + (size_t)nsof_reflect101(Ymin + sy, J.sh) * sp;
+            for (int sx = lane; sx < swn; sx += NSOF_WARP) sS[sy * SWp + sx] = NSOF_LDG(row + nsof_reflect101(Xmin + sx, J.sw));
+        }
+        NSOF_SYNC();
     }
-    NSOF_SYNC();
     const float g0 = sg[0];
     for (int sy = warp; sy < shn; sy += nw) {
-        const uint8_t *row = sS + sy * SWp;
+        const uint8_t *row = sS + sy * SWp + shift;
         for (int ci = lane; ci < 2 * twn; ci += NSOF_WARP) {
             const uint8_t *c = row + (cols[ci] - Xmin);
             float acc = g0 * (float)c[0];
-            for (int i = 1; i <= r; i++) acc = acc + sg[i] * ((float)c[-i] + (float)c[i]);
+            // the two taps at distance i are added as integers (exact) and converted once
+            for (int i = 1; i <= r; i++) acc = acc + sg[i] * (float)((int)c[-i] + (int)c[i]);
             sHb[sy * 2 * TW + ci] = acc;
         }
     }
@@ -926,7 +943,7 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
 
 static inline size_t fb_ps_smem(int r, int SWmax, int SHmax)
 {
-    const size_t SWp = (SWmax + 3) & ~3;
-    return (2 * FB_PS_TW + 2 * FB_PS_TH) * sizeof(int) + (FB_PS_TW + FB_PS_TH + ((r + 1 + 3) & ~3)) * sizeof(float) +
+    const size_t SWp = (SWmax + 32 + 15) & ~15;
+    return 16 + (2 * FB_PS_TW + 2 * FB_PS_TH) * sizeof(int) + (FB_PS_TW + FB_PS_TH + ((r + 1 + 3) & ~3)) * sizeof(float) +
            (size_t)2 * FB_PS_TH * 2 * FB_PS_TW * sizeof(float) + (size_t)SHmax * 2 * FB_PS_TW * sizeof(float) + SWp * SHmax;
 }
