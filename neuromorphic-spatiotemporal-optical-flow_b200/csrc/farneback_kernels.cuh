@@ -275,9 +275,23 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
 // First UpdateMatrices of a level; the initial flow is zero (coarsest level) or the coarser
 // level's flow upsampled on the fly (S2-f: resize INTER_LINEAR, times f32(1/pyr_scale)); the
 // upsampled field itself is never written (UpdateFlow_Blur overwrites flow entirely).
-#define FB_UM_TW 64
-#define FB_UM_TH 4
+#define FB_UM_TW 128
+#define FB_UM_TH 8
 
+NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
+{
+    int x0, x1, y0, y1;
+    float ax, ay;
+    fb_lin_coord(x, J.fsx, J.cw, &x0, &x1, &ax);
+    fb_lin_coord(y, J.fsy, J.ch, &y0, &y1, &ay);
+    const float2 f00 = NSOF_LDG(J.cflow + (size_t)y0 * J.cpitch + x0), f01 = NSOF_LDG(J.cflow + (size_t)y0 * J.cpitch + x1);
+    const float2 f10 = NSOF_LDG(J.cflow + (size_t)y1 * J.cpitch + x0), f11 = NSOF_LDG(J.cflow + (size_t)y1 * J.cpitch + x1);
+    const float a0 = 1.f - ax, b0 = 1.f - ay;
+    return make_float2(((f00.x * a0 + f01.x * ax) * b0 + (f10.x * a0 + f11.x * ax) * ay) * flow_mul,
+                       ((f00.y * a0 + f01.y * ax) * b0 + (f10.y * a0 + f11.y * ax) * ay) * flow_mul);
+}
+
+// 4 pixels per thread: float4 loads of R0, float4 stores of M, 80 independent R1 gathers in flight per thread.
 NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
@@ -285,26 +299,37 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const size_t plane = (size_t)J.pitch * J.h;
     const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = (NSOF_BX / tiles_x) * FB_UM_TH;
-    for (int i = NSOF_TID; i < FB_UM_TW * FB_UM_TH; i += NSOF_NT) {
-        const int x = tx0 + i % FB_UM_TW, y = ty0 + i / FB_UM_TW;
+    constexpr int GW = FB_UM_TW / 4;
+    for (int i = NSOF_TID; i < GW * FB_UM_TH; i += NSOF_NT) {
+        const int x = tx0 + (i % GW) * 4, y = ty0 + i / GW;
         if (x >= J.w || y >= J.h) continue;
-        float dx = 0.f, dy = 0.f;
-        if (J.ch > 0) {
-            int x0, x1, y0, y1;
-            float ax, ay;
-            fb_lin_coord(x, J.fsx, J.cw, &x0, &x1, &ax);
-            fb_lin_coord(y, J.fsy, J.ch, &y0, &y1, &ay);
-            const float2 f00 = NSOF_LDG(J.cflow + (size_t)y0 * J.cpitch + x0), f01 = NSOF_LDG(J.cflow + (size_t)y0 * J.cpitch + x1);
-            const float2 f10 = NSOF_LDG(J.cflow + (size_t)y1 * J.cpitch + x0), f11 = NSOF_LDG(J.cflow + (size_t)y1 * J.cpitch + x1);
-            const float a0 = 1.f - ax, b0 = 1.f - ay;
-            dx = ((f00.x * a0 + f01.x * ax) * b0 + (f10.x * a0 + f11.x * ax) * ay) * flow_mul;
-            dy = ((f00.y * a0 + f01.y * ax) * b0 + (f10.y * a0 + f11.y * ax) * ay) * flow_mul;
-        }
         const size_t o = (size_t)y * J.pitch + x;
-        float r0v[5], m[5];
-        for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(J.R + c * plane + o);
-        fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x, y, dx, dy, r0v, m);
-        for (int c = 0; c < 5; c++) J.Ma[c * plane + o] = m[c];
+        float r0[5][4];
+#pragma unroll
+        for (int c = 0; c < 5; c++) {
+            const float4 t = NSOF_LDG((const float4 *)(J.R + c * plane + o));
+            r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
+        }
+        float mo[5][4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            float r0v[5], mm[5];
+            if (x + q < J.w) {
+                float2 d = make_float2(0.f, 0.f);
+                if (J.ch > 0) d = fb_upsampled_flow(J, x + q, y, flow_mul);
+#pragma unroll
+                for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
+                fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, d.x, d.y, r0v, mm);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 5; c++) mm[c] = 0.f;
+            }
+#pragma unroll
+            for (int c = 0; c < 5; c++) mo[c][q] = mm[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 5; c++)
+            *(float4 *)(J.Ma + c * plane + o) = make_float4(mo[c][0], mo[c][1], mo[c][2], mo[c][3]);
     }
 }
 
@@ -456,6 +481,12 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
     float *sM = (float *)(smem_raw + 16);
 
     // ---- phase 1
+#ifdef FB_BS_TIMING
+    long long tstamp[6];
+#endif
+#ifdef FB_BS_TIMING
+    if (NSOF_TID == 0) tstamp[0] = clock64();
+#endif
     const int gx0 = tx0 - ML;                                         // global x of shared column 0
     const int cx0 = nsof_imax(gx0, 0), cx1 = nsof_imin(tx0 + TW + ML, J.pitch);  // copied run, multiples of 4
     const unsigned row_bytes = (unsigned)(cx1 - cx0) * 4u;
@@ -470,7 +501,13 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
         const int gy = nsof_clampi(ty0 - M + ly, 0, J.h - 1);
         nsof_bulk_g2s(sM + c * SP + ly * PW + (cx0 - gx0), Min + c * plane + (size_t)gy * J.pitch + cx0, row_bytes, bar);
     }
-    nsof_mbar_wait(bar, 0);
+    // one warp polls the mbarrier; the others sleep in the block barrier (a try_wait spin in every warp
+    // steals issue slots from the co-resident CTAs: 32 % of all executed instructions in the first profile)
+    if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);
+    NSOF_SYNC();
+#ifdef FB_BS_TIMING
+    if (NSOF_TID == 0) tstamp[1] = clock64();
+#endif
     if (tx0 - M < 0 || tx0 + TW + M > J.w) {  // replicate the first / last image column into the halo
         const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
         const int s_first = -gx0, s_last = J.w - 1 - gx0;  // shared columns of image x = 0 and x = w - 1
@@ -488,33 +525,34 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
         }
     }
     NSOF_SYNC();
+
+#ifdef FB_BS_TIMING
+    if (NSOF_TID == 0) tstamp[2] = clock64();
+#endif
     // ---- phase 2
     for (int col = NSOF_TID; col < 5 * LW; col += NSOF_NT) {
         const int c = col / LW;
         float *p = sM + c * SP + (ML - M) + (col - c * LW);
-#ifdef FB_BS_FLOAT_V
-        float s = 0.f;
+        // prefix sums in double, fully unrolled: every element is loaded and converted once, the window sum of
+        // output row y is P[y + 2M + 1] - P[y]; the 2M + 2 live prefixes sit in a statically indexed register ring
+        constexpr int RING = 2 * M + 2;
+        double ring[RING];
+        double run = 0.;
+        ring[0] = 0.;
 #pragma unroll
-        for (int j = 0; j <= 2 * M; j++) s += p[j * PW];
-#pragma unroll 4
-        for (int y = 0; y < TH; y++) {
-            const float old = p[y * PW];
-            p[y * PW] = s;
-            if (y + 1 < TH) s += p[(y + 2 * M + 1) * PW] - old;
+        for (int j = 0; j < LH; j++) {
+            run += (double)p[j * PW];
+            if (j >= 2 * M) {  // rows 0 .. j are summed: output row y = j - 2M is complete
+                const int y = j - 2 * M;
+                p[y * PW] = (float)(run - ring[y % RING]);  // row y of the column is dead (already summed)
+            }
+            ring[(j + 1) % RING] = run;
         }
-#else
-        double s = 0.;
-#pragma unroll
-        for (int j = 0; j <= 2 * M; j++) s += (double)p[j * PW];
-#pragma unroll 4
-        for (int y = 0; y < TH; y++) {
-            const float old = p[y * PW];
-            p[y * PW] = (float)s;
-            if (y + 1 < TH) s += (double)p[(y + 2 * M + 1) * PW] - (double)old;
-        }
-#endif
     }
     NSOF_SYNC();
+#ifdef FB_BS_TIMING
+    if (NSOF_TID == 0) tstamp[3] = clock64();
+#endif
     // ---- phase 3
     constexpr int GW = TW / 4;
     for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
@@ -584,6 +622,11 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
                 *(float4 *)(Mout + c * plane + o) = make_float4(mo[c][0], mo[c][1], mo[c][2], mo[c][3]);
         }
     }
+#ifdef FB_BS_TIMING
+    __syncthreads();
+    if (NSOF_TID == 0 && NSOF_BY == 0 && (NSOF_BX % 97) == 5)
+        printf("bs tile %d last %d: load %lld fix %lld vert %lld horiz+um %lld\n", NSOF_BX, last, tstamp[1] - tstamp[0], tstamp[2] - tstamp[1], tstamp[3] - tstamp[2], clock64() - tstamp[3]);
+#endif
 }
 
 // a plain function-pointer name: template commas do not survive nested launch macros
