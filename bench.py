@@ -244,7 +244,7 @@ def ncu_traffic(kernel):
     """Per-launch DRAM traffic of `kernel` from the committed ncu --set full summary, if one exists."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            return json.load(f).get(kernel)
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
     except Exception:
         return None
 
@@ -277,12 +277,14 @@ def finish(args, L):
         return rows, cls
 
     kernels, stats = kernel_tables(lambda: pipe.step(frames))
-    dom = max(stats, key=lambda k: stats[k]["ms"])
-    ach = stats[dom]["algorithmic_bytes"] / (stats[dom]["ms"] * 1e-3) / 1e9
+    # dominant kernel = the (class, pyramid level) row with the most device time in the step
+    dom = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    drow = kernels[dom]
+    ach = drow["algorithmic_MB_per_step"] * 1e6 / (drow["ms_per_step"] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": ncu_traffic(dom), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": stats[dom]["algorithmic_bytes"] / stats[dom]["launches"],
-                "avg_launch_ms": stats[dom]["ms"] / stats[dom]["launches"]}
+                "algorithmic_bytes_per_launch": drow["algorithmic_MB_per_step"] * 1e6 / drow["launches"],
+                "avg_launch_ms": drow["ms_per_step"] / drow["launches"]}
     fb_bytes = sum(s["algorithmic_bytes"] for k, s in stats.items() if k.startswith("fb_")) / 2
     fb_ms = sum(s["ms"] for k, s in stats.items() if k.startswith("fb_")) / 2
     extras["stage2_all_kernels"] = {"algorithmic_GB_per_step": fb_bytes / 1e9, "ms_per_step": fb_ms,
