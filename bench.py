@@ -164,16 +164,13 @@ def gpu_arm(args):
     import torch
     import torch.distributed as dist
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    par = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.parallel")
+    rank, world, local = par.rank_info()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; libnsof has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+    par.init("nccl", dev)  # plumbing only: barrier + max-over-ranks of the time; clips shard with no collective
 
     nsof = importlib.import_module("nsof_b200")
     syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
@@ -184,8 +181,8 @@ def gpu_arm(args):
 
     # synthetic clips, generated on the device, layout [F][C][H][W]
     frames = torch.empty((F, Cn, H, W), dtype=torch.uint8, device=dev)
-    for c in range(Cn):
-        frames[:, c] = syn.make_clip(1234 + rank * Cn + c, H, W, F, dev)
+    for i, c in enumerate(par.weak_scaling_clips(Cn, rank, world)):  # clip c -> GPU c mod G
+        frames[:, i] = syn.make_clip(par.clip_seed(c), H, W, F, dev)
     torch.cuda.synchronize()
 
     def barrier():
