@@ -26,7 +26,8 @@ from .engine import PARAMS, Engine, RoiConfig, _fb_params, _synapse_params, u8_t
 
 class SequencePipeline:
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 sim=dict(dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, vds=1.0), full_frame: bool = False):
+                 sim=dict(dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, vds=1.0), full_frame: bool = False,
+                 packed: bool = False):
         import torch
         self.torch = torch
         self.eng, self.lib, self.h = engine, engine.lib, engine.handle
@@ -48,7 +49,17 @@ class SequencePipeline:
         self.memimg = torch.zeros((self.n_pairs, self.Hc, self.Wc), dtype=torch.uint8, device=self.dev)
         self.rects_host = torch.zeros((self.n_pairs, 4), dtype=i32).pin_memory()
         self.n_rects_host = torch.zeros((self.n_pairs,), dtype=i32).pin_memory()
-        self.flow = torch.zeros((self.F - 1, self.C, self.H, self.W, 2), dtype=torch.float32, device=self.dev)
+        # output: full flow frames (zero outside each ROI, the reference's paste semantics) or, for the host path,
+        # the ROI crops packed back to back (outside its rectangle a pair's flow is zero by definition)
+        self.packed_mode = bool(packed)
+        if packed:
+            cap = self.n_pairs * self.H * self.W * 2 // (1 if full_frame else 3)
+            self.packed = torch.empty((cap,), dtype=torch.float32, device=self.dev)
+            self.flow = None
+        else:
+            self.flow = torch.zeros((self.F - 1, self.C, self.H, self.W, 2), dtype=torch.float32, device=self.dev)
+        self.offsets = [-1] * self.n_pairs
+        self.packed_floats = 0
         self.sp = _synapse_params(PARAMS)
         self.fsp = FrameSimParams(float(sim["th1"]), float(sim["th2"]), float(sim["dt"]), int(sim["nSubSteps"]),
                                   float(sim["vds"]))
@@ -91,9 +102,11 @@ class SequencePipeline:
     def build_descs(self, frames, rects, n_rects):
         """Crop descriptors: views into the resident frames and into the full-frame flow buffers (no copies)."""
         H, W, Cn = self.H, self.W, self.C
-        fbase, obase = frames.data_ptr(), self.flow.data_ptr()
+        fbase = frames.data_ptr()
+        obase = self.packed.data_ptr() if self.packed_mode else self.flow.data_ptr()
         n, px = 0, 0
         for i in range(self.n_pairs):
+            self.offsets[i] = -1
             if self.full_frame:
                 x0, y0, x1, y1 = 0, 0, W, H
             else:
@@ -109,15 +122,24 @@ class SequencePipeline:
             d.next = fbase + (((t + 1) * Cn + c) * H * W + off)
             d.h, d.w = y1 - y0, x1 - x0
             d.prev_pitch = d.next_pitch = W
-            d.flow = obase + ((t * Cn + c) * H * W + off) * 8
-            d.flow_pitch = W * 8
+            if self.packed_mode:
+                if (px + (y1 - y0) * (x1 - x0)) * 2 > self.packed.numel():
+                    raise MemoryError("packed flow buffer too small for this step's ROIs")
+                self.offsets[i] = px * 2
+                d.flow = obase + px * 8
+                d.flow_pitch = (x1 - x0) * 8
+            else:
+                d.flow = obase + ((t * Cn + c) * H * W + off) * 8
+                d.flow_pitch = W * 8
             n += 1
             px += (y1 - y0) * (x1 - x0)
         self.last_crop_pixels = px
+        self.packed_floats = px * 2
         return n
 
     def stage2(self, n_items):
-        self.flow.zero_()  # S2-g: the reference pastes every crop's flow into a zero frame
+        if not self.packed_mode:
+            self.flow.zero_()  # S2-g: the reference pastes every crop's flow into a zero frame
         self.lib.check(self.lib.nsof_farneback_batch(self.h, self.descs, n_items, C.byref(self.fb), self._stream()),
                        "farneback_batch")
 
@@ -133,40 +155,91 @@ class SequencePipeline:
         self.stage2(n)
         return n
 
-    # ---- host-buffer entry (the e2e leg) ---------------------------------------------------------------
-    def alloc_host(self):
-        """Pinned host buffers: frames in, packed ROI flow crops + rectangles out."""
-        t = self.torch
-        self.frames_dev = t.empty((self.F, self.C, self.H, self.W), dtype=t.uint8, device=self.dev)
-        self.crop_host = t.empty((self.n_pairs * self.H * self.W * 2 // (1 if self.full_frame else 3),),
-                                 dtype=t.float32).pin_memory()
-        self.crop_dev = t.empty_like(self.crop_host, device=self.dev)
 
-    def step_host(self, frames_host):
-        """frames_host: pinned uint8 [F][C][H][W].  H2D of the frames, the device step, D2H of the rectangles and of
-        every ROI's flow (packed float32 crops; outside its rectangle a pair's flow is zero by definition).
-        Returns (rects, n_rects, offsets, packed flow host tensor)."""
+
+class HostPipeline:
+    """Host-buffer entry of the sequence path (bench.py's e2e leg): pinned uint8 clips in, per pair its rectangle
+    and its ROI flow crop (float32, packed) out, host<->device copies included.
+
+    Clips are independent, so the work is software-pipelined over `slots` streams, one clip per stage:
+    H2D of clip k+1 overlaps stage 1 / stage 2 of clip k and the D2H of clip k-1 (both copy engines and the SMs
+    busy at once).  Every slot owns a libnsof handle (one handle per (GPU, stream)), its device frames and its
+    packed output buffer; the only host synchronisation per clip is the event that its rectangles have arrived.
+    """
+
+    def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
+                 slots: int = 4, full_frame: bool = False, lib=None):
+        import torch
+        self.torch = torch
+        self.dev = torch.device(f"cuda:{device}")
+        self.C, self.F, self.H, self.W = int(clips), int(frames), int(H), int(W)
+        self.slots = []
+        for _ in range(max(1, min(slots, self.C))):
+            eng = Engine(device, lib=lib)
+            pipe = SequencePipeline(eng, 1, frames, H, W, cfg, full_frame=full_frame, packed=True)
+            self.slots.append(dict(eng=eng, pipe=pipe, stream=torch.cuda.Stream(self.dev),
+                                   frames=torch.empty((frames, 1, H, W), dtype=torch.uint8, device=self.dev),
+                                   ev_rects=torch.cuda.Event(), ev_done=torch.cuda.Event(), busy=False))
+        per_clip = self.slots[0]["pipe"].packed.numel()
+        # host outputs: one packed flow buffer and one rectangle table per clip
+        self.flow_host = [torch.empty((per_clip,), dtype=torch.float32).pin_memory() for _ in range(self.C)]
+        self.rects_out = [None] * self.C
+        self.offsets_out = [None] * self.C
+        self.h2d_bytes = self.d2h_bytes = 0
+
+    def launch_count(self) -> int:
+        return sum(s["eng"].launch_count() for s in self.slots)
+
+    def _front(self, k, clip_host):
+        """H2D + stage 1 + rectangles D2H of clip k on its slot's stream (asynchronous)."""
         t = self.torch
-        self.frames_dev.copy_(frames_host, non_blocking=True)
-        n = self.step(self.frames_dev)
-        # gather the ROI windows of the full-frame flow buffers into one packed buffer, then one D2H
-        offs, o = [], 0
-        flow = self.flow.view(self.n_pairs, self.H, self.W, 2)
-        rects, n_rects = (None, None) if self.full_frame else self.last_rects
-        for i in range(self.n_pairs):
-            if self.full_frame:
-                x0, y0, x1, y1 = 0, 0, self.W, self.H
-            elif n_rects[i] == 0:
-                offs.append(-1)
-                continue
-            else:
-                x0, y0, x1, y1 = (int(v) for v in rects[i])
-            sz = (y1 - y0) * (x1 - x0) * 2
-            self.crop_dev[o:o + sz].view(y1 - y0, x1 - x0, 2).copy_(flow[i, y0:y1, x0:x1])
-            offs.append(o)
-            o += sz
-        self.crop_host[:o].copy_(self.crop_dev[:o], non_blocking=True)
-        t.cuda.current_stream(self.dev).synchronize()
-        self.last_d2h_bytes = o * 4 + self.n_pairs * 20
-        self.last_h2d_bytes = frames_host.numel()
-        return rects, n_rects, offs, self.crop_host
+        s = self.slots[k % len(self.slots)]
+        if s["busy"]:
+            s["ev_done"].synchronize()  # the slot's previous clip has left the device
+        with t.cuda.stream(s["stream"]):
+            s["frames"][:, 0].copy_(clip_host, non_blocking=True)
+            p = s["pipe"]
+            if not p.full_frame:
+                p.stage1(s["frames"])
+                p.rects_host.copy_(p.rects[:, 0, :], non_blocking=True)
+                p.n_rects_host.copy_(p.n_rects, non_blocking=True)
+            s["ev_rects"].record()
+        s["busy"] = True
+        self.h2d_bytes += clip_host.numel()
+
+    def _back(self, k):
+        """Wait for clip k's rectangles, then enqueue its Farneback batch and the D2H of the packed crops."""
+        t = self.torch
+        s = self.slots[k % len(self.slots)]
+        p = s["pipe"]
+        s["ev_rects"].synchronize()
+        if p.full_frame:
+            rects, n_rects = None, None
+        else:
+            rects, n_rects = p.rects_host.numpy().copy(), p.n_rects_host.numpy().copy()
+        n = p.build_descs(s["frames"], rects, n_rects)
+        with t.cuda.stream(s["stream"]):
+            p.stage2(n)
+            nf = p.packed_floats
+            self.flow_host[k][:nf].copy_(p.packed[:nf], non_blocking=True)
+            s["ev_done"].record()
+        self.rects_out[k] = (rects, n_rects)
+        self.offsets_out[k] = list(p.offsets)
+        self.d2h_bytes += nf * 4 + p.n_pairs * 20
+
+    def run(self, clips_host):
+        """clips_host: sequence of C pinned uint8 tensors (F, H, W).  Returns per clip (rects, n_rects, offsets,
+        packed float32 host tensor); pair t's flow crop is packed[offsets[t] : offsets[t] + 2 h w].view(h, w, 2)."""
+        assert len(clips_host) == self.C
+        self.h2d_bytes = self.d2h_bytes = 0
+        depth = len(self.slots) - 1  # clips in flight ahead of the one being finished
+        for k in range(self.C):
+            self._front(k, clips_host[k])
+            if k >= depth:
+                self._back(k - depth)
+        for k in range(max(0, self.C - depth), self.C):
+            self._back(k)
+        for s in self.slots:
+            s["ev_done"].synchronize()
+            s["busy"] = False
+        return [(self.rects_out[k][0], self.rects_out[k][1], self.offsets_out[k], self.flow_host[k]) for k in range(self.C)]

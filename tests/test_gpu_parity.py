@@ -272,3 +272,83 @@ def test_frame_mode_1080p_mask_bit_exact(gpu_engine, nsof):
     cfg = nsof.RoiConfig()
     r = gpu_engine.roi_from_currents(cur, (1080, 1920), cfg=cfg)
     assert np.array_equal(r["memimg"], s1.current_to_u8(cur_o))
+
+
+# ------------------------------------------------------------------------------------------- whole clips
+def _small_clips(n, F=6, H=400, W=560):
+    import importlib
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    return [syn.make_clip(100 + c, H, W, F, "cpu", velocity=(4.0, -2.0)) for c in range(n)]
+
+
+def test_sequence_pipeline_vs_cpu_reference(gpu_engine, nsof, oracle):
+    """Stage 1 + ROI + batched Farneback over whole clips (device-resident step) against the reference CPU path
+    (numpy stage 1 + cv2/oracle Farneback on the crop): rectangles identical, flow within tolerance, zero outside."""
+    import importlib
+
+    import torch
+    from oracle import cpu_reference as ref
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    clips = _small_clips(2)
+    F, H, W = clips[0].shape
+    frames = torch.stack(clips, dim=1).cuda().contiguous()  # [F][C][H][W]
+    pipe = pm.SequencePipeline(gpu_engine, 2, F, H, W)
+    n = pipe.step(frames)
+    torch.cuda.synchronize()
+    flow = pipe.flow.cpu().numpy()
+    n_ref = 0
+    for c in range(2):
+        _, _, rects, flows = ref.process_clip(clips[c].numpy(), keep_flow=True)
+        for t in range(F - 1):
+            got_rect = tuple(int(v) for v in pipe.last_rects[0][t * 2 + c]) if pipe.last_rects[1][t * 2 + c] else None
+            assert got_rect == rects[t], (c, t, got_rect, rects[t])
+            if rects[t] is None:
+                assert not flow[t, c].any()
+                continue
+            n_ref += 1
+            x0, y0, x1, y1 = rects[t]
+            # Against cv2 itself these clips (smooth background: near-singular 2x2 systems) are ill-conditioned per
+            # pixel: the scalar C oracle itself differs from cv2 (SIMD blur, 1 ulp of I) by mean 5e-5 / q99.9 1.4e-2 /
+            # max 3e-2 px on these crops, so the per-pixel bounds are loose; the mean stays 20x under BASELINE's
+            # 0.01 px bar.  Well-conditioned (textured) inputs are held to 1e-3 max in test_full_frame_vs_oracle.
+            d = helpers.flow_err(flow[t, c, y0:y1, x0:x1], flows[t][y0:y1, x0:x1].astype(np.float32))
+            assert d.mean() <= 5e-4 and np.quantile(d, 0.999) <= 5e-2 and d.max() <= 0.25, (d.mean(), d.max())
+            if c == 0 and t < 2:  # ... and strictly against the oracle on the same crop
+                want = oracle.farneback(np.ascontiguousarray(clips[c][t, y0:y1, x0:x1].numpy()),
+                                        np.ascontiguousarray(clips[c][t + 1, y0:y1, x0:x1].numpy()), **helpers.PARAM_SETS["grasp"])
+                do = helpers.flow_err(flow[t, c, y0:y1, x0:x1], want)  # FMA contraction vs the oracle's separate roundings
+                assert do.mean() <= 1e-5 and np.quantile(do, 0.999) <= 1e-3 and do.max() <= 1e-2, (do.mean(), do.max())
+            outside = np.ones((H, W), bool)
+            outside[y0:y1, x0:x1] = False
+            assert not flow[t, c][outside].any()
+    assert n == n_ref and n_ref >= 4  # the gate opens on most pairs of these clips
+
+
+def test_host_pipeline_matches_device_step(gpu_engine, nsof):
+    """The multi-stream host path returns, per pair, the same rectangle and bit-identical flow crops as the
+    device-resident step."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    clips = _small_clips(5)
+    F, H, W = clips[0].shape
+    frames = torch.stack(clips, dim=1).cuda().contiguous()
+    pipe = pm.SequencePipeline(gpu_engine, 5, F, H, W)
+    pipe.step(frames)
+    torch.cuda.synchronize()
+    flow = pipe.flow.cpu().numpy()
+    hp = pm.HostPipeline(0, 5, F, H, W, slots=3)
+    for _ in range(2):  # twice: slot reuse
+        out = hp.run([c.pin_memory() for c in clips])
+    for c, (rects, n_rects, offs, packed) in enumerate(out):
+        for t in range(F - 1):
+            i = t * 5 + c
+            assert bool(n_rects[t]) == bool(pipe.last_rects[1][i])
+            if not n_rects[t]:
+                assert offs[t] == -1
+                continue
+            assert tuple(rects[t]) == tuple(pipe.last_rects[0][i])
+            x0, y0, x1, y1 = (int(v) for v in rects[t])
+            crop = packed[offs[t]:offs[t] + 2 * (y1 - y0) * (x1 - x0)].numpy().reshape(y1 - y0, x1 - x0, 2)
+            assert np.array_equal(crop, flow[t, c, y0:y1, x0:x1])
