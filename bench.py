@@ -119,7 +119,7 @@ def cpu_baseline_leg(clip_np):
     return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": ref.KIND,
             "sample": f"1 clip x {clip_np.shape[0]} frames ({n} pairs) of the same synthetic workload, one process, "
                       f"numpy stage 1 + {'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback "
-                      f"on the ROI crop; host has {os.cpu_count()} cores",
+                      f"on the ROI crop; host has {len(os.sched_getaffinity(0))} usable cores",
             "full_frame_value": nf / dtf}
 
 
@@ -129,7 +129,7 @@ def reference_arm(args):
     if rank != 0:
         return 0
     from oracle import cpu_reference as ref
-    cores = os.cpu_count() or 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     workers = max(1, cores)
     ref_frames = 5  # 4 pairs per clip and task: bounded sample
     clips = host_clips(min(workers, 16), ref_frames)
@@ -170,6 +170,7 @@ def gpu_arm(args):
         raise SystemExit("bench.py: no CUDA device; libnsof has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
+    os.environ["NCCL_DEBUG"] = os.environ.get("NSOF_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
     par.init("nccl", dev)  # plumbing only: barrier + max-over-ranks of the time; clips shard with no collective
 
     nsof = importlib.import_module("nsof_b200")

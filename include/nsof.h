@@ -196,6 +196,12 @@ NSOF_API int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const int1
 NSOF_API int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n, const nsof_synapse_params *p,
                                      double *R, void *cuda_stream);
 
+/* Event-mode ROI glue (builder-defined; the reference never thresholds the eventsim state):
+ * currents[cy][cx] = max over the memsize_h x memsize_w pixels of cell (cy, cx) of 1 / resistance_exp(w)
+ * (Hc = H / memsize_h, Wc = W / memsize_w, floor), double, ready for nsof_roi_from_state_f64. */
+NSOF_API int nsof_event_cell_currents_f32(nsof_handle *h, const float *w, int H, int W, int memsize_h, int memsize_w,
+                                          const nsof_synapse_params *p, double *currents, void *cuda_stream);
+
 /* Frame-mode simulator (simulation/simulationcode_v4_transistor_vehicle.m:111-121, 146-236, 306-321):
  * one step of simulate_memristor_array for `n` clips at once.
  *   cells_prev/cells_next: device double [n][Hc][Wc], the Lanczos-3 compressed frames in [0,1]

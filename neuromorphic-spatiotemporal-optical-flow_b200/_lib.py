@@ -99,6 +99,8 @@ _SIGNATURES = {
                                          C.c_void_p]),
     "nsof_resistance_exp_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, _P(SynapseParams), C.c_void_p,
                                           C.c_void_p]),
+    "nsof_event_cell_currents_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                               _P(SynapseParams), C.c_void_p, C.c_void_p]),
     "nsof_frame_sim_step_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                           C.c_int, C.c_int, _P(SynapseParams), _P(FrameSimParams), C.c_void_p]),
     "nsof_frame_sim_run_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,

@@ -108,6 +108,20 @@ extern "C" int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n,
     return NSOF_OK;
 }
 
+extern "C" int nsof_event_cell_currents_f32(nsof_handle *h, const float *w, int H, int W, int memsize_h, int memsize_w,
+                                            const nsof_synapse_params *p, double *currents, void *cuda_stream)
+{
+    if (!h || !w || !p || !currents || H < 1 || W < 1 || memsize_h < 1 || memsize_w < 1 || memsize_h > H || memsize_w > W)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "event_cell_currents: bad argument");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const int Hc = H / memsize_h, Wc = W / memsize_w;
+    const double lam = log(p->Roff / p->Ron);
+    NSOF_KLAUNCH(h, NSOF_K_RESISTANCE, 4. * Hc * memsize_h * Wc * memsize_w, k_s1_cell_current_from_w, Hc * Wc, 1, 1, 128,
+                 128 * sizeof(float), (cudaStream_t)cuda_stream, w, W, memsize_h, memsize_w, Wc, p->Ron, lam, currents);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
 // ------------------------------------------------------------------------------ frame mode
 // MATLAB imresize 'lanczos3' contributions for one dimension (antialiased when shrinking):
 //   scale = out/in; kernel width 6 (/scale when scale < 1); u = x/scale + 0.5*(1 - 1/scale), x = 1..out;

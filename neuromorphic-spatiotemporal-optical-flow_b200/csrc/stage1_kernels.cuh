@@ -137,6 +137,29 @@ NSOF_GLOBAL k_s1_resistance_exp(const float *NSOF_RESTRICT w, size_t n, double R
     }
 }
 
+// Event-mode ROI glue (builder-defined, SURVEY.md 8(d) config 3: the reference never thresholds the eventsim
+// state): one current per MEMSIZE x MEMSIZE cell = the largest pixel current 1 / resistance_exp(w) inside it.
+// The map w -> current is increasing, so the cell current is the current of the cell's largest w: a float max
+// (exact) followed by the same double arithmetic numpy applies to that element.  One block per cell.
+NSOF_GLOBAL k_s1_cell_current_from_w(const float *NSOF_RESTRICT w, int W, int memsize_h, int memsize_w, int Wc, double Ron,
+                                     double lam, double *NSOF_RESTRICT currents)
+{
+    const int cell = NSOF_BX, cx = cell % Wc, cy = cell / Wc;
+    NSOF_DYN_SMEM(smem_raw);
+    float *red = (float *)smem_raw;
+    float m = -1.f;
+    for (int i = NSOF_TID; i < memsize_h * memsize_w; i += NSOF_NT) {
+        const int ly = i / memsize_w, lx = i - ly * memsize_w;
+        m = fmaxf(m, w[(size_t)(cy * memsize_h + ly) * W + cx * memsize_w + lx]);
+    }
+    red[NSOF_TID] = m;
+    NSOF_SYNC();
+    if (NSOF_TID == 0) {
+        for (int i = 1; i < NSOF_NT; i++) m = fmaxf(m, red[i]);
+        currents[cell] = 1.0 / (Ron / exp(-lam * (double)(1.0f - m)));
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Frame mode.  compress_image = im2double + imresize(.,'lanczos3') with antialiasing is a separable
 // linear map: cells = Wy * (img / 255) * Wx^T with DENSE per-axis matrices Wy [Hc][H], Wx [Wc][W]

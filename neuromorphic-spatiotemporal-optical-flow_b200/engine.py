@@ -479,6 +479,19 @@ class Engine:
         self.lib.check(rc, "event_scheme1")
         return dw.cpu().numpy()
 
+    def event_cell_currents(self, w, memsize, p=PARAMS):
+        """Event-mode ROI glue: float32 state (H, W) -> float64 cell currents (H // memsize, W // memsize), the
+        largest pixel current 1 / resistance_exp(w) of every cell (feeds roi_from_currents)."""
+        import torch
+        w32 = np.ascontiguousarray(w, dtype=np.float32)
+        H, W = w32.shape
+        (dw,) = self._dev_roundtrip([w32])
+        out = torch.empty((H // memsize, W // memsize), dtype=torch.float64, device=dw.device)
+        sp = _synapse_params(p)
+        self.lib.check(self.lib.nsof_event_cell_currents_f32(self.handle, dw.data_ptr(), H, W, memsize, memsize,
+                                                             C.byref(sp), out.data_ptr(), self._stream()))
+        return out.cpu().numpy()
+
     def compress_images(self, frames_u8, m, n):
         """compress_image (vehicle.m:111-121) for a stack of grey uint8 frames (T, H, W) -> float64 (T, H//n, W//m)."""
         import torch

@@ -274,3 +274,12 @@ def simulate_memristor_array_vec(compressed, dt=5e-4, nSubSteps=1000, th1=2.0, t
         w[off], w[on] = w_off, w_on
         cur.append(vds / R(w))
     return w, np.stack(cur)
+
+
+def event_cell_currents(w, memsize, p=PARAMS):
+    """Event-mode ROI glue (builder-defined): per-pixel current 1 / resistance_exp(w),
+    block-max pooled to memsize x memsize cells."""
+    H, W = w.shape
+    Hc, Wc = H // memsize, W // memsize
+    cur = 1.0 / resistance_exp(w, p)
+    return cur[:Hc * memsize, :Wc * memsize].reshape(Hc, memsize, Wc, memsize).max(axis=(1, 3))

@@ -167,3 +167,18 @@ def test_emu_frame_mode_vs_oracle(emu_engine):
     assert np.allclose(w, w_o, rtol=0, atol=1e-12) and np.allclose(cur, cur_o, rtol=1e-11)
     w2, cur2 = emu_engine.simulate_memristor_array_stepwise(seq, nSubSteps=20)
     assert np.allclose(w2, w_o, rtol=0, atol=1e-12) and np.allclose(cur2, cur_o, rtol=1e-11)
+
+
+def test_emu_event_roi_glue_vs_oracle(emu_engine, nsof, golden):
+    """Config 3 glue: event state -> cell currents (block max) -> uint8 map -> mask -> rectangles, bit-exact."""
+    ev = golden.ev
+    H, W = int(ev["H"]), int(ev["W"])
+    w = ev["w_decay64"]
+    cur = emu_engine.event_cell_currents(w, 20)
+    want = s1.event_cell_currents(w, 20)
+    assert cur.shape == (12, 16) and np.array_equal(cur, want)
+    cfg = nsof.RoiConfig(MEMSIZE=20, THRES=250, EXTEND_WIDTH_LEFT=8, EXTEND_WIDTH_RIGHT=8, EXTEND_HEIGHT_UPPER=8,
+                         EXTEND_HEIGHT_LOWER=8, FLAG=2)
+    r = emu_engine.roi_from_currents(cur, (H, W), cfg=cfg)
+    n, labels, stats, rects = s1.roi_from_memimg(s1.current_to_u8(want), (H, W), 20, 20, 250, (8, 8, 8, 8), 2)
+    assert r["rects"] == rects and len(rects) == 1 and np.array_equal(r["labels"], labels)

@@ -352,3 +352,26 @@ def test_host_pipeline_matches_device_step(gpu_engine, nsof):
             x0, y0, x1, y1 = (int(v) for v in rects[t])
             crop = packed[offs[t]:offs[t] + 2 * (y1 - y0) * (x1 - x0)].numpy().reshape(y1 - y0, x1 - x0, 2)
             assert np.array_equal(crop, flow[t, c, y0:y1, x0:x1])
+
+
+def test_event_stream_to_roi_gated_flow(gpu_engine, nsof, golden, oracle):
+    """BASELINE configs[2] end to end on the device: event stream -> scheme-1 memory decay -> cell currents -> ROI
+    rectangle (bit-exact vs the numpy restatement on the reference's own float32 state) -> Farneback on the crop."""
+    ev = golden.ev
+    H, W = int(ev["H"]), int(ev["W"])
+    b = ev["slice_bounds"]
+    w = gpu_engine.simulate_scheme1(ev["x"][:b[64]], ev["y"][:b[64]], ev["t"][:b[64]], H, W, 1000, silent_v=0.5)
+    cur = gpu_engine.event_cell_currents(w, 20)
+    assert np.array_equal(gpu_engine.event_cell_currents(ev["w_decay64"], 20), s1.event_cell_currents(ev["w_decay64"], 20))
+    cfg = nsof.RoiConfig(MEMSIZE=20, THRES=250, EXTEND_WIDTH_LEFT=8, EXTEND_WIDTH_RIGHT=8, EXTEND_HEIGHT_UPPER=8,
+                         EXTEND_HEIGHT_LOWER=8, FLAG=2)
+    r = gpu_engine.roi_from_currents(cur, (H, W), cfg=cfg)
+    _, _, _, rects = s1.roi_from_memimg(s1.current_to_u8(s1.event_cell_currents(ev["w_decay64"], 20)), (H, W), 20, 20, 250,
+                                        (8, 8, 8, 8), 2)
+    assert r["rects"] == rects and len(rects) == 1  # the device's float32 state differs by ulps; the mask does not
+    a, bb = helpers.textured_pair(41, H, W, dx=2.0, dy=0.5)
+    flow, _, _, _, info = gpu_engine.opticalFlow3D(r["memimg"], r["memimg"], a, bb, 20, 20, cfg)
+    assert info == rects[0]
+    x0, y0, x1, y1 = info
+    want = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(bb[y0:y1, x0:x1]), **cfg.farneback_params)
+    helpers.assert_flow_close(flow[y0:y1, x0:x1].astype(np.float32), want, "grasp", "event ROI crop")
