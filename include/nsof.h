@@ -109,6 +109,17 @@ NSOF_API int nsof_farneback_u8_host(nsof_handle *h, const uint8_t *prev, const u
                                     int width, ptrdiff_t prev_pitch, ptrdiff_t next_pitch,
                                     const nsof_fb_params *params, float *flow, ptrdiff_t flow_pitch);
 
+/* S2-g, the reference's paste into `flow = np.zeros((h, w, 2))` (optical_flow_seg.py:215, 204): zero the flow
+ * rectangles of `n` crops (only .h, .w, .flow, .flow_pitch of each item are read) in ONE launch.  A sequence
+ * driver that owns its flow frames clears the previous step's rectangles with this instead of re-zeroing whole
+ * frames: outside the rectangles the frames are still zero. */
+NSOF_API int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int n, void *cuda_stream);
+/* Strided host<->device copy of `rows` runs of `row_bytes` (cudaMemcpy2DAsync; kind 1 = host to device,
+ * 2 = device to host), used by the host-buffer sequence path to land a clip's frames in the time-major device
+ * layout.  Pinned host memory keeps it asynchronous. */
+NSOF_API int nsof_copy_2d_async(void *dst, ptrdiff_t dst_pitch, const void *src, ptrdiff_t src_pitch,
+                                size_t row_bytes, size_t rows, int kind, void *cuda_stream);
+
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
 NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,
@@ -124,6 +135,9 @@ NSOF_API double nsof_fb_algorithmic_bytes(int height, int width, const nsof_fb_p
 NSOF_API int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iters);
 /* enable = 0 forces the unfused pyramid + PolyExp kernels, which write I to the workspace (what = 0, 1). */
 NSOF_API int nsof_debug_fuse(nsof_handle *h, int enable);
+/* enable = 0 keeps every launch of nsof_farneback_batch on the caller's stream (default: the pyramid + PolyExp
+ * launches of the finer levels run on internal streams beside the coarse-level iterations). */
+NSOF_API int nsof_debug_fork(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w);
 
 /* ---- stage 1: synaptic temporal memory -> ROI ------------------------------------------- */

@@ -79,11 +79,15 @@ _SIGNATURES = {
     "nsof_farneback_batch_host": (C.c_int, [C.c_void_p, _P(CropDesc), C.c_int, _P(FbParams)]),
     "nsof_farneback_u8_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t,
                                          C.c_ssize_t, _P(FbParams), C.c_void_p, C.c_ssize_t]),
+    "nsof_flow_clear": (C.c_int, [C.c_void_p, _P(CropDesc), C.c_int, C.c_void_p]),
+    "nsof_copy_2d_async": (C.c_int, [C.c_void_p, C.c_ssize_t, C.c_void_p, C.c_ssize_t, C.c_size_t, C.c_size_t, C.c_int,
+                                     C.c_void_p]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),
     "nsof_debug_truncate": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "nsof_debug_fuse": (C.c_int, [C.c_void_p, C.c_int]),
+    "nsof_debug_fork": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, _P(C.c_int), _P(C.c_int)]),
     "nsof_roi_from_state_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _P(RoiParams), C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

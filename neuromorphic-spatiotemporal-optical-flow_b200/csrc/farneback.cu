@@ -69,7 +69,8 @@ int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **out)
 struct FbItemPlan {
     int scales;
     int hk[64], wk[64], pitch[64];
-    size_t off_I, off_R, off_Ma, off_Mb, off_fA, off_fB;  // floats from arena base
+    size_t off_I[64], off_R[64];                  // per level: the levels' pyramids are built concurrently
+    size_t off_Ma, off_Mb, off_fA, off_fB;        // shared by the levels (serial chain); floats from arena base
     nsof_crop_desc d;
 };
 
@@ -100,6 +101,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
     cudaDeviceSynchronize();
     h->arena.release();
     h->tables.release();
+    h->clear_tab.release();
     h->io.release();
     h->s1.release();
     h->lz.release();
@@ -108,6 +110,10 @@ extern "C" int nsof_destroy(nsof_handle *h)
         if (s.done) cudaEventDestroy(s.done);
     }
     for (auto e : h->prof_pool) cudaEventDestroy(e);
+    for (auto e : h->ev_level) cudaEventDestroy(e);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    for (auto &a : h->aux)
+        if (a) cudaStreamDestroy(a);
     delete h->last_plan;
     delete h;
     return NSOF_OK;
@@ -121,7 +127,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 // ------------------------------------------------------------------------------ launch accounting
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
-    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance"};
+    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 
@@ -389,8 +395,9 @@ extern "C" int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_it
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_reserve: NULL handle");
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    // 26 floats per padded level-0 pixel (I 2, R 10, Ma 5, Mb 5, coarse flow 2x2); padding <= 31 px per row
-    const size_t floats = (total_crop_pixels + (size_t)max_items * 32 * 8192) * 26;
+    // per padded level-0 pixel: I 2 + R 10 on every level (x 4/3 for pyr_scale 0.5; x 2 bounds any scale <= 0.7),
+    // Ma 5, Mb 5, coarse flow 2 x 2 / 4; padding <= 31 px per row
+    const size_t floats = (total_crop_pixels + (size_t)max_items * 32 * 8192) * 36;
     int rc = h->arena.ensure(floats * sizeof(float));
     if (rc) return rc;
     return h->tables.ensure((size_t)max_items * 8 * sizeof(FbJob) + 65536);
@@ -421,8 +428,11 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
         FbItemPlan &pl = plan[i];
         const size_t n0 = (size_t)pl.pitch[0] * pl.hk[0];
         const size_t n1 = pl.scales > 1 ? (size_t)pl.pitch[1] * pl.hk[1] : 0;
-        pl.off_I = arena_floats;  arena_floats += 2 * n0;
-        pl.off_R = arena_floats;  arena_floats += 10 * n0;
+        for (int k = 0; k < pl.scales; k++) {
+            const size_t nk = (size_t)pl.pitch[k] * pl.hk[k];
+            pl.off_I[k] = arena_floats;  arena_floats += 2 * nk;
+            pl.off_R[k] = arena_floats;  arena_floats += 10 * nk;
+        }
         pl.off_Ma = arena_floats; arena_floats += 5 * n0;
         pl.off_Mb = arena_floats; arena_floats += 5 * n0;
         pl.off_fA = arena_floats; arena_floats += 2 * n1;
@@ -512,7 +522,7 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             path_n[3 * k + J.fast] += 1;
             path_N[3 * k + J.fast] += (double)J.h * J.w;
             path_N0[3 * k + J.fast] += (double)J.sh * J.sw;
-            J.I = base + pl.off_I; J.R = base + pl.off_R; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
+            J.I = base + pl.off_I[k]; J.R = base + pl.off_R[k]; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
             // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
             float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
             float *fl_coarse = (k & 1) ? base + pl.off_fB : base + pl.off_fA;
@@ -546,19 +556,12 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     const float flow_mul = (float)(1. / params->pyr_scale);
     const float bscale = (float)(1. / ((double)params->winsize * params->winsize));
 
-    // ---- level loop, coarse to fine (A.1)
-    for (int k = max_scales - 1; k >= stop_level; k--) {
+    // S2-b + S2-c of level k on stream `st` (independent of the flow: needs the sources and the tables only)
+    auto launch_pyramid = [&](int k, cudaStream_t st) -> int {
         const FbJob *jobs = (const FbJob *)(ds + job_off[k]);
         const float *gk = (const float *)ds + gk_off[k];
         const int na = n_active[k];
-        int iters = params->iterations;
-        if (k == stop_level && h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
-        // algorithmic bytes per launch: the per-level terms of nsof_fb_algorithmic_bytes, summed over the batch;
-        // items that have no level k keep the coarse-flow term at zero via sumN of the items that do
-        double Nc = 0.;
-        for (int i = 0; i < n; i++)
-            if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
-        const double Nk = sumN[k];
+        cudaStream_t stream = st;  // the launches below name it `stream`
         h->prof_level = k;
         if (path_n[3 * k + 1])
             NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * path_N0[3 * k + 1] + 40 * path_N[3 * k + 1], FB_PYR_POLYEXP_M0,
@@ -577,6 +580,54 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * path_N[3 * k], k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream,
                          jobs, pc);
         }
+        NSOF_CUDA_TRY(cudaGetLastError());
+        return NSOF_OK;
+    };
+    // fork: every level but the coarsest builds its R0, R1 on an internal stream while the caller's stream iterates
+    // on the coarser levels (small, latency-bound launches); joined per level by an event before its first
+    // UpdateMatrices.  Serial when profiling (one event pair per launch must not overlap another).
+    const int top = max_scales - 1;
+    const bool fork = !h->prof_on && !h->no_fork && top > stop_level;
+    if (fork) {
+        for (auto &a : h->aux)
+            if (!a) NSOF_CUDA_TRY(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+        if (!h->ev_fork) NSOF_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+        while ((int)h->ev_level.size() < max_scales) {
+            cudaEvent_t e = nullptr;
+            NSOF_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            h->ev_level.push_back(e);
+        }
+        NSOF_CUDA_TRY(cudaEventRecord(h->ev_fork, stream));  // tables uploaded, previous batch's readers of R done
+        rc = launch_pyramid(top, stream);
+        if (rc) return rc;
+        for (int k = top - 1; k >= stop_level; k--) {
+            cudaStream_t a = h->aux[k & 1];
+            NSOF_CUDA_TRY(cudaStreamWaitEvent(a, h->ev_fork, 0));
+            rc = launch_pyramid(k, a);
+            if (rc) return rc;
+            NSOF_CUDA_TRY(cudaEventRecord(h->ev_level[k], a));
+        }
+    }
+
+    // ---- level loop, coarse to fine (A.1)
+    for (int k = max_scales - 1; k >= stop_level; k--) {
+        const FbJob *jobs = (const FbJob *)(ds + job_off[k]);
+        const int na = n_active[k];
+        int iters = params->iterations;
+        if (k == stop_level && h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
+        // algorithmic bytes per launch: the per-level terms of nsof_fb_algorithmic_bytes, summed over the batch;
+        // items that have no level k keep the coarse-flow term at zero via sumN of the items that do
+        double Nc = 0.;
+        for (int i = 0; i < n; i++)
+            if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
+        const double Nk = sumN[k];
+        if (!fork) {
+            rc = launch_pyramid(k, stream);
+            if (rc) return rc;
+        } else if (k < top) {
+            NSOF_CUDA_TRY(cudaStreamWaitEvent(stream, h->ev_level[k], 0));
+        }
+        h->prof_level = k;
         if (params->iterations == 0) {
             NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * Nc + 8 * Nk, k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
                          flow_mul);
@@ -667,12 +718,85 @@ extern "C" int nsof_farneback_u8_host(nsof_handle *h, const uint8_t *prev, const
     return nsof_farneback_batch_host(h, &d, 1, params);
 }
 
+// ------------------------------------------------------------------------------ S2-g helpers
+struct FbClearJob {
+    float2 *p;
+    int h, w, fpitch;  // fpitch in float2
+};
+
+// grid (row groups, items): 8 rows per block, one warp per row, float2 stores (crops are only 8-byte aligned)
+NSOF_GLOBAL k_fb_flow_clear(const FbClearJob *NSOF_RESTRICT jobs)
+{
+    const FbClearJob J = jobs[NSOF_BY];
+    const int nw = nsof_imax(NSOF_NT / NSOF_WARP, 1), warp = NSOF_TID / NSOF_WARP, lane = NSOF_LANE;
+    for (int y = NSOF_BX * nw + warp; y < J.h; y += nsof_grid_x() * nw) {
+        float2 *row = J.p + (size_t)y * J.fpitch;
+        for (int x = lane; x < J.w; x += NSOF_WARP) row[x] = make_float2(0.f, 0.f);
+    }
+}
+
+extern "C" int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int n, void *cuda_stream)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "flow_clear: NULL handle");
+    if (n < 0 || (n > 0 && !items)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "flow_clear: bad item list");
+    if (n == 0) return NSOF_OK;
+    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "flow_clear: at most 65535 items per call");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)n * sizeof(FbClearJob);
+    NsofStageSlot *slot;
+    int rc = nsof_stage_acquire(h, bytes, &slot);
+    if (rc) return rc;
+    rc = h->clear_tab.ensure(bytes);
+    if (rc) return rc;
+    FbClearJob *hj = (FbClearJob *)slot->host;
+    int max_h = 0;
+    double px = 0.;
+    for (int i = 0; i < n; i++) {
+        const nsof_crop_desc &d = items[i];
+        if (!d.flow || d.h < 1 || d.w < 1 || d.flow_pitch < (ptrdiff_t)d.w * 8 || d.flow_pitch % 8 || (uintptr_t)d.flow % 8)
+            NSOF_FAIL(NSOF_ERR_BAD_ARG, "flow_clear: item %d is malformed", i);
+        hj[i].p = (float2 *)d.flow;
+        hj[i].h = d.h;
+        hj[i].w = d.w;
+        hj[i].fpitch = (int)(d.flow_pitch / 8);
+        max_h = std::max(max_h, d.h);
+        px += (double)d.h * d.w;
+    }
+    NSOF_CUDA_TRY(cudaMemcpyAsync(h->clear_tab.p, hj, bytes, cudaMemcpyHostToDevice, stream));
+    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
+    slot->pending = true;
+    NSOF_KLAUNCH(h, NSOF_K_FLOW_CLEAR, 8 * px, k_fb_flow_clear, std::min((max_h + 7) / 8, 64), n, 1, 256, 0, stream,
+                 (const FbClearJob *)h->clear_tab.p);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+extern "C" int nsof_copy_2d_async(void *dst, ptrdiff_t dst_pitch, const void *src, ptrdiff_t src_pitch, size_t row_bytes,
+                                  size_t rows, int kind, void *cuda_stream)
+{
+    if (!dst || !src) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_2d: NULL pointer");
+    if (kind != 1 && kind != 2) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_2d: kind must be 1 (H2D) or 2 (D2H)");
+    if (dst_pitch < (ptrdiff_t)row_bytes || src_pitch < (ptrdiff_t)row_bytes) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_2d: bad pitch");
+    if (!row_bytes || !rows) return NSOF_OK;
+    NSOF_CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)dst_pitch, src, (size_t)src_pitch, row_bytes, rows,
+                                    kind == 1 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    return NSOF_OK;
+}
+
 // ------------------------------------------------------------------------------ test hooks
 extern "C" int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iters)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     h->dbg_level = stop_level;
     h->dbg_iters = stop_iters;
+    return NSOF_OK;
+}
+
+extern "C" int nsof_debug_fork(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->no_fork = !enable;
     return NSOF_OK;
 }
 
@@ -703,10 +827,10 @@ extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, 
     if (what <= 1 && !h->dbg_no_fuse)
         NSOF_FAIL(NSOF_ERR_BAD_ARG, "debug_fetch: I is not materialised by the fused pyramid kernels; call nsof_debug_fuse(h, 0) first");
     switch (what) {
-    case 0: src = base + pl.off_I; ch = 1; break;
-    case 1: src = base + pl.off_I + plane; ch = 1; break;
-    case 2: src = base + pl.off_R; ch = 5; break;
-    case 3: src = base + pl.off_R + 5 * plane; ch = 5; break;
+    case 0: src = base + pl.off_I[k]; ch = 1; break;
+    case 1: src = base + pl.off_I[k] + plane; ch = 1; break;
+    case 2: src = base + pl.off_R[k]; ch = 5; break;
+    case 3: src = base + pl.off_R[k] + 5 * plane; ch = 5; break;
     case 4: {
         // M currently valid: Ma after um_first, then the iterations alternate a->b->a ...
         int iters = h->last_params.iterations;

@@ -50,7 +50,7 @@ struct FbItemPlan;  // farneback.cu
 enum NsofKernelClass {
     NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_PYR_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
     NSOF_K_LANCZOS, NSOF_K_FRAME_SIM, NSOF_K_ROI, NSOF_K_EVENT_HIST, NSOF_K_EVENT_REPLAY, NSOF_K_SYNAPSE_STEP,
-    NSOF_K_RESISTANCE, NSOF_K_CLASSES
+    NSOF_K_RESISTANCE, NSOF_K_FLOW_CLEAR, NSOF_K_CLASSES
 };
 extern const char *const nsof_kernel_class_names[NSOF_K_CLASSES];
 
@@ -64,6 +64,7 @@ struct nsof_handle {
     int device = 0;
     NsofDevBuf arena;      // I, R, M, coarse flow of every item of the current batch
     NsofDevBuf tables;     // job tables + Gaussian taps on the device
+    NsofDevBuf clear_tab;  // rectangle table of nsof_flow_clear
     NsofDevBuf io;         // device staging of the *_host entry points (crops in, flow out)
     NsofDevBuf s1;         // stage-1 scratch
     NsofDevBuf lz;         // Lanczos-3 weight/index tables (device), cached for lz_key
@@ -80,6 +81,12 @@ struct nsof_handle {
     int last_stop_level = 0;
     nsof_fb_params last_params = {};
     bool smem_configured = false;
+    // fork-join inside nsof_farneback_batch: the pyramid + PolyExp launches of every level but the coarsest do not
+    // depend on the flow, so they run on internal streams beside the (latency-bound) coarse-level iterations
+    cudaStream_t aux[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr;
+    std::vector<cudaEvent_t> ev_level;
+    bool no_fork = false;  // nsof_debug_fork(h, 0): everything on the caller's stream
     // launch accounting
     unsigned long long launches = 0;
     bool prof_on = false;

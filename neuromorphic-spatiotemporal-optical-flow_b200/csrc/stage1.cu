@@ -247,12 +247,12 @@ extern "C" int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, 
     double *part = (double *)h->s1.p;
     if (!h->lz_smem_set) {
         NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_lanczos_cols, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_lanczos_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         h->lz_smem_set = true;
     }
-    const int nt = 128, ngroups = (W + 3) / 4;
-    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, (double)n * H * W, k_s1_lanczos_rows, (ngroups + nt - 1) / nt, n_seg, n, nt,
-                 (size_t)LZ_MAXC * seg_rows * sizeof(double), st, frames, pitch, frame_stride, H, W, Hc, d_Dy, d_cbase,
-                 seg_rows, n_seg, part);
+    const size_t rows_smem = 64 + (size_t)LZ_MAXC * seg_rows * sizeof(double) + (size_t)seg_rows * LZ_TILE_W;
+    NSOF_KLAUNCH(h, NSOF_K_LANCZOS, (double)n * H * W, k_s1_lanczos_rows, (W + LZ_TILE_W - 1) / LZ_TILE_W, n_seg, n,
+                 LZ_TILE_W / 4, rows_smem, st, frames, pitch, frame_stride, H, W, Hc, d_Dy, d_cbase, seg_rows, n_seg, part);
     NSOF_KLAUNCH(h, NSOF_K_LANCZOS, 0., k_s1_lanczos_cols, Hc, n, 1, S1_NT, (size_t)W * sizeof(double), st, part, W, Hc, Wc,
                  d_Dx, d_xband, d_cbase, n_seg, cells);
     NSOF_CUDA_TRY(cudaGetLastError());

@@ -176,44 +176,70 @@ NSOF_GLOBAL k_s1_cell_current_from_w(const float *NSOF_RESTRICT w, int W, int me
 //   (deterministic), then one warp per cell column reduces its tap band with a fixed-order shuffle tree.
 // ---------------------------------------------------------------------------------------------
 #define LZ_MAXC 8
+#define LZ_TILE_W 512   // source columns per block: 128 threads x uchar4
+#define LZ_STAGES 3     // the segment's rows arrive in 3 groups, each on its own mbarrier
 
+// dynamic smem: 64 B (mbarriers) + LZ_MAXC * seg_rows doubles + seg_rows * LZ_TILE_W bytes.
+// The block's seg_rows x LZ_TILE_W source window is fetched by bulk asynchronous row copies (cp.async.bulk, SASS
+// UBLKCP): ~48 KB in flight per block with no register staging (per-thread loads left the kernel latency-bound at
+// 0.4 TB/s); the FP64 accumulation starts as soon as the first third of the rows has landed.
 NSOF_GLOBAL k_s1_lanczos_rows(const uint8_t *NSOF_RESTRICT frames, ptrdiff_t pitch, ptrdiff_t frame_stride, int H, int W,
                               int Hc, const double *NSOF_RESTRICT Wy, const int *NSOF_RESTRICT cbase, int seg_rows,
                               int n_seg, double *NSOF_RESTRICT part)
 {
     const int seg = NSOF_BY, f = NSOF_BZ;
-    const int y0 = seg * seg_rows, y1 = nsof_imin(y0 + seg_rows, H);
+    const int y0 = seg * seg_rows, y1 = nsof_imin(y0 + seg_rows, H), rows = y1 - y0;
     const int cb = cbase[seg];
+    const int x0 = NSOF_BX * LZ_TILE_W, tw = nsof_imin(LZ_TILE_W, W - x0);
     NSOF_DYN_SMEM(smem_raw);
-    double *sw = (double *)smem_raw;
+    nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
+    double *sw = (double *)(smem_raw + 64);
+    uint8_t *tile = smem_raw + 64 + (size_t)LZ_MAXC * seg_rows * sizeof(double);
+    const uint8_t *src = frames + (size_t)f * frame_stride + (size_t)y0 * pitch + x0;
+    const bool bulk = ((uintptr_t)src & 15) == 0 && (pitch & 15) == 0 && (tw & 15) == 0;
+    const int per_stage = (rows + LZ_STAGES - 1) / LZ_STAGES;
+    if (bulk && NSOF_TID == 0) {
+        for (int sg = 0; sg < LZ_STAGES; sg++) {
+            const int r0 = sg * per_stage, r1 = nsof_imin(rows, r0 + per_stage);
+            nsof_mbar_init(bar + sg, 1);
+            nsof_mbar_expect_tx(bar + sg, (unsigned)(nsof_imax(r1 - r0, 0) * tw));
+        }
+    }
     for (int i = NSOF_TID; i < LZ_MAXC * seg_rows; i += NSOF_NT) {
         const int j = i / seg_rows, r = i % seg_rows;
         const int cy = cb + j, y = y0 + r;
         sw[i] = (cy < Hc && y < y1) ? Wy[(size_t)cy * H + y] : 0.;
     }
     NSOF_SYNC();
-    const uint8_t *src = frames + (size_t)f * frame_stride;
-    const int ngroups = (W + 3) / 4;
-    for (int g = NSOF_BX * NSOF_NT + NSOF_TID; g < ngroups; g += NSOF_NT * nsof_grid_x()) {
-        const int x = g * 4;
+    if (bulk)
+        for (int r = NSOF_TID; r < rows; r += NSOF_NT)
+            nsof_bulk_g2s(tile + (size_t)r * LZ_TILE_W, src + (size_t)r * pitch, (unsigned)tw, bar + r / per_stage);
+    const int ngroups = (tw + 3) / 4;
+    for (int g = NSOF_TID; g < ngroups; g += NSOF_NT) {
+        const int x = x0 + g * 4;
         double acc[LZ_MAXC][4];
-        for (int j = 0; j < LZ_MAXC; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.;
-        const bool vec = (x + 3 < W) && ((((uintptr_t)src + x) & 3) == 0) && ((pitch & 3) == 0);
-        for (int y = y0; y < y1; y++) {
-            const uint8_t *row = src + (size_t)y * pitch + x;
-            double v[4];
-            if (vec) {
-                const uint32_t u = NSOF_LDG((const uint32_t *)row);
-                v[0] = (double)(u & 255u); v[1] = (double)((u >> 8) & 255u);
-                v[2] = (double)((u >> 16) & 255u); v[3] = (double)(u >> 24);
-            } else {
-                for (int q = 0; q < 4; q++) v[q] = x + q < W ? (double)NSOF_LDG(row + q) : 0.;
-            }
-            const double *wr = sw + (y - y0);
 #pragma unroll
-            for (int j = 0; j < LZ_MAXC; j++) {
-                const double wj = wr[j * seg_rows];
-                acc[j][0] += wj * v[0]; acc[j][1] += wj * v[1]; acc[j][2] += wj * v[2]; acc[j][3] += wj * v[3];
+        for (int j = 0; j < LZ_MAXC; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.;
+        for (int sg = 0; sg < LZ_STAGES; sg++) {
+            const int r0 = sg * per_stage, r1 = nsof_imin(rows, r0 + per_stage);
+            if (bulk) nsof_mbar_wait(bar + sg, 0);
+#pragma unroll 4
+            for (int r = r0; r < r1; r++) {
+                double v[4];
+                if (bulk) {
+                    const uint32_t u = *(const uint32_t *)(tile + (size_t)r * LZ_TILE_W + g * 4);
+                    v[0] = (double)(u & 255u); v[1] = (double)((u >> 8) & 255u);
+                    v[2] = (double)((u >> 16) & 255u); v[3] = (double)(u >> 24);
+                } else {
+                    const uint8_t *row = src + (size_t)r * pitch + g * 4;
+                    for (int q = 0; q < 4; q++) v[q] = x + q < W ? (double)NSOF_LDG(row + q) : 0.;
+                }
+                const double *wr = sw + r;
+#pragma unroll
+                for (int j = 0; j < LZ_MAXC; j++) {
+                    const double wj = wr[j * seg_rows];
+                    acc[j][0] += wj * v[0]; acc[j][1] += wj * v[1]; acc[j][2] += wj * v[2]; acc[j][3] += wj * v[3];
+                }
             }
         }
         for (int j = 0; j < LZ_MAXC; j++) {
@@ -301,13 +327,16 @@ NSOF_GLOBAL k_s1_frame_step(const double *NSOF_RESTRICT a, const double *NSOF_RE
 // inside; cells[t] is [n_cells] at stride `stride_t` doubles; current_out[t] = state after the pair (t, t+1).
 //
 // The nsub Euler sub-steps of a frame are a chain of dependent x^b evaluations: pure latency (a few thousand
-// cells, one warp per block).  Two things shorten the chain without changing the recurrence
-//     w <- clip(w + g * (1 - s w)^b * dt_sub, 0, 1):
-//  * exact evaluations use exp(b * log(x)) (CUDA's double pow() is ~3x deeper);
-//  * between exact evaluations y = u^b is carried forward multiplicatively: u' = u (1 + d) with |d| <= 2e-3, so
-//    y' = y (1 + d)^b and 1/u' = (1/u) / (1 + d) by 6-term binomial series (truncation < 1e-17, Estrin form,
-//    depth ~5 instead of ~45 dependent operations).  y is re-evaluated exactly every 32 sub-steps, whenever |d| is
-//    larger, which bounds the accumulated rounding to ~1e-14 relative.
+// cells, one warp per block).  The chain is shortened without changing the recurrence
+//     w <- clip(w + c * (1 - s w)^b, 0, 1),   c = g * dt_sub:
+//  * the state is carried as u = 1 - s w (in [1 - s, 1]) and z = u^(b-1).  One Euler step is then
+//        u' = u (1 + d),  d = -s c z          (because u' - u = -s (w' - w) = -s c u^b = u * (-s c z))
+//    and the clip of w to [0, 1] is the clip of u' to [1 - s, 1], where z is a constant (1, or (1-s)^(b-1));
+//  * z is carried forward multiplicatively, z' = z (1 + d)^(b-1), by a 6-term binomial series (|d| <= 2e-3:
+//    truncation ~1e-16, Estrin form), so the loop-carried dependency is z -> d -> series -> z: 5 dependent FP64
+//    operations instead of an exp(log) pair (~45);
+//  * z is re-evaluated exactly, exp((b-1) log u), every 64 sub-steps and whenever |d| is larger, which bounds the
+//    accumulated rounding to ~1e-14 relative.
 NSOF_DEV double s1_pow_pos(double x, double b) { return x > 0. ? exp(b * log(x)) : pow(x, b); }
 
 struct S1Binom { double a1, a2, a3, a4, a5, a6; };
@@ -323,31 +352,31 @@ NSOF_DEV S1Binom s1_binom(double b)
     return c;
 }
 
-// nsub sub-steps of w <- clip(w + c * (1 - s w)^b) with c = g * dt_sub
+// nsub sub-steps of w <- clip(w + c * (1 - s w)^b, 0, 1) with c = g * dt_sub, 0 < s < 1
 NSOF_DEV double s1_euler_chain(double wv, double c, double s, double b, int nsub)
 {
-    const S1Binom k = s1_binom(b);
+    if (c == 0.) return wv;
+    const double e = b - 1.;
+    const S1Binom k = s1_binom(e);
+    const double kap = -s * c;
+    const double u_lo = 1. - s, z_lo = s1_pow_pos(u_lo, e);  // w = 1
     double u = 1. - wv * s;
-    double y = s1_pow_pos(u, b), v = 1. / u;
+    double z = s1_pow_pos(u, e);
     for (int i = 0; i < nsub; i++) {
-        double wn = wv + c * y;
-        wn = fmax(0., fmin(wn, 1.));
-        const double un = 1. - wn * s;
-        const double d = (un - u) * v;  // u' = u (1 + d) holds whether or not the clip acted
-        if (fabs(d) > 2e-3 || (i & 31) == 31) {
-            y = s1_pow_pos(un, b);
-            v = 1. / un;
-        } else {
+        const double d = kap * z;
+        double un = u + u * d;
+        if (un >= 1.) { un = 1.; z = 1.; }                 // w clipped at 0
+        else if (un <= u_lo) { un = u_lo; z = z_lo; }      // w clipped at 1
+        else if (fabs(d) > 2e-3 || (i & 63) == 63) z = s1_pow_pos(un, e);
+        else {
             const double d2 = d * d, d3 = d2 * d;
-            const double py = (1. + d * (k.a1 + k.a2 * d)) + d3 * ((k.a3 + k.a4 * d) + d2 * (k.a5 + k.a6 * d));
-            const double pv = (1. - d * (1. - d)) - d3 * ((1. - d) + d2 * (1. - d));
-            y *= py;
-            v *= pv;
+            z *= (1. + d * (k.a1 + k.a2 * d)) + d3 * ((k.a3 + k.a4 * d) + d2 * (k.a5 + k.a6 * d));
         }
-        wv = wn;
         u = un;
     }
-    return wv;
+    if (u >= 1.) return 0.;
+    if (u <= u_lo) return 1.;
+    return fmax(0., fmin((1. - u) / s, 1.));
 }
 
 NSOF_GLOBAL k_s1_frame_run(const double *NSOF_RESTRICT cells, size_t stride_t, int n_frames, double *NSOF_RESTRICT w,

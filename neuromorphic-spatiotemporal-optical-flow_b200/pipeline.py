@@ -3,31 +3,51 @@ with stage 1 taken from the frame-mode simulator (simulation/simulationcode_v4_t
 instead of a pre-computed .mat, everything resident on one GPU.
 
 For a rank's `C` clips of `F` grey frames (layout [F][C][H][W] uint8, so that time slice t of every clip is one
-contiguous block) one `step` is:
+contiguous block) one `step` is, per chunk of consecutive frame pairs:
 
-  1. compress_image for all F*C frames                       nsof_lanczos3_compress_u8   (1 B / source pixel)
-  2. simulate_memristor_array, all F-1 pairs in one launch   nsof_frame_sim_run_f64      (cells only)
+  1. compress_image for the chunk's frames                   nsof_lanczos3_compress_u8   (1 B / source pixel)
+  2. simulate_memristor_array over the chunk's pairs         nsof_frame_sim_run_f64      (cells only)
   3. current -> u8 -> transition_pic -> CC -> rectangles     nsof_roi_from_state_f64     (cells only)
-  4. rectangles D2H (the one host sync of the step), crop descriptors
-  5. zero the flow frames, ROI-gated Farneback on every crop nsof_farneback_batch        (DESIGN.md byte model)
+  4. rectangles D2H (one host wait per chunk), crop descriptors
+  5. ROI-gated Farneback on the chunk's crops                nsof_farneback_batch        (DESIGN.md byte model)
 
-torch is used for device memory, streams and pinned host buffers only.
+Stage 1 is a recurrence in time (1000 dependent Euler sub-steps per pair): latency-bound, a handful of warps.
+Stage 2 is the bandwidth-bound part.  The pairs are therefore processed in a few time chunks: steps 1-4 of
+ALL chunks are enqueued on a side stream (its own libnsof handle: one handle per stream), step 5 of chunk j is
+enqueued on the caller's stream as soon as chunk j's rectangles have arrived, so the Euler chains of the later
+chunks run underneath the Farneback kernels of the earlier ones.
+
+torch is used for device memory, streams, events and pinned host buffers only.
 """
 from __future__ import annotations
 
 import ctypes as C
+import time
 
 import numpy as np
 
 from . import _lib
-from ._lib import FrameSimParams, RoiParams
+from ._lib import CropDesc, FrameSimParams, RoiParams
 from .engine import PARAMS, Engine, RoiConfig, _fb_params, _synapse_params, u8_threshold_table
+
+_DESC_SIZE = C.sizeof(CropDesc)
+
+
+def chunk_schedule(n_pairs: int, first: int = 1, grow: int = 2, cap: int = 8):
+    """Pair ranges [p0, p1) of a step: a short first chunk (stage 2 starts early), then growing ones (fewer,
+    larger Farneback batches).  (15 pairs -> 1, 2, 4, 8.)"""
+    out, p, n = [], 0, max(1, int(first))
+    while p < n_pairs:
+        q = min(n_pairs, p + n)
+        out.append((p, q))
+        p, n = q, min(max(1, int(cap)), n * max(1, int(grow)))
+    return out
 
 
 class SequencePipeline:
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
                  sim=dict(dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, vds=1.0), full_frame: bool = False,
-                 packed: bool = False):
+                 packed: bool = False, chunks=None, overlap: bool = True, s2_streams: int = 2):
         import torch
         self.torch = torch
         self.eng, self.lib, self.h = engine, engine.lib, engine.handle
@@ -38,6 +58,19 @@ class SequencePipeline:
         M = self.cfg.MEMSIZE
         self.Hc, self.Wc = self.H // M, self.W // M
         self.n_pairs = self.C * (self.F - 1)
+        self.chunks = list(chunks) if chunks is not None else chunk_schedule(self.F - 1)
+        assert self.chunks[0][0] == 0 and self.chunks[-1][1] == self.F - 1
+        # stage 1 runs on a side stream with its own handle (one handle per (GPU, stream)); overlap=False keeps
+        # everything on the caller's stream and handle (per-kernel profiling, debugging)
+        self.overlap = bool(overlap) and not self.full_frame
+        self.s1_eng = Engine(engine.device, lib=engine.lib) if self.overlap else engine
+        self.side = torch.cuda.Stream(self.dev) if self.overlap else None
+        self.ev_chunk = [torch.cuda.Event(enable_timing=True) for _ in self.chunks]
+        # stage 2 of successive chunks alternates between the caller's stream and `s2_streams - 1` extra streams (own
+        # handles): the small coarse-level launches of one batch run beside the large fine-level ones of another
+        n_extra = max(0, int(s2_streams) - 1) if self.overlap else 0
+        self.s2_extra = [(Engine(engine.device, lib=engine.lib), torch.cuda.Stream(self.dev)) for _ in range(n_extra)]
+        self.ev_s2 = [torch.cuda.Event(enable_timing=True) for _ in self.chunks]
         f64, i32 = torch.float64, torch.int32
         self.cells = torch.empty((self.F, self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
         self.w = torch.empty((self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
@@ -67,45 +100,62 @@ class SequencePipeline:
         self.rp = RoiParams(self.Hc, self.Wc, self.H, self.W, M, M, c.EXTEND_WIDTH_LEFT, c.EXTEND_WIDTH_RIGHT,
                             c.EXTEND_HEIGHT_UPPER, c.EXTEND_HEIGHT_LOWER, 2, c.THRES, c.MAP_A, c.MAP_B)
         self.fb = _fb_params(**c.farneback_params)
-        self.descs = (_lib.CropDesc * self.n_pairs)()
+        self.descs = (CropDesc * self.n_pairs)()
+        self.n_items = 0          # descriptors of the current step
+        self.n_dirty = 0          # descriptors whose flow rectangles are non-zero in self.flow (previous step)
         self.last_rects = None
         self.last_crop_pixels = 0
-        engine.reserve(self.n_pairs * self.H * self.W if full_frame else self.n_pairs * self.H * self.W // 3,
-                       self.n_pairs)
+        biggest = max(q - p for p, q in self.chunks) * self.C if not full_frame else self.n_pairs
+        for e in [engine] + [e for e, _ in self.s2_extra]:
+            e.reserve(biggest * self.H * self.W if full_frame else biggest * self.H * self.W // 3, biggest)
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.dev).cuda_stream)
 
-    # ---- stage 1 ---------------------------------------------------------------------------------------
-    def stage1(self, frames):
-        """frames: uint8 device tensor [F][C][H][W].  Leaves rectangles in self.rects / self.n_rects (device)."""
-        lib, h, st = self.lib, self.h, self._stream()
-        F, Cn, H, W = self.F, self.C, self.H, self.W
-        lib.check(lib.nsof_lanczos3_compress_u8(h, frames.data_ptr(), F * Cn, H, W, W, H * W, self.Hc, self.Wc,
-                                                self.cells.data_ptr(), st), "lanczos3_compress")
-        self.w.fill_(float(PARAMS["wini"]))
-        lib.check(lib.nsof_frame_sim_run_f64(h, self.cells.data_ptr(), F, Cn, self.Hc, self.Wc, self.w.data_ptr(),
-                                             self.currents.data_ptr(), C.byref(self.sp), C.byref(self.fsp), st),
-                  "frame_sim_run")
-        lib.check(lib.nsof_roi_from_state_f64(h, self.currents.data_ptr(), self.n_pairs, C.byref(self.rp),
-                                              self.thr.data_ptr(), self.memimg.data_ptr(), None, None,
-                                              self.n_rects.data_ptr(), self.rects.data_ptr(), None, st), "roi")
+    def launch_count(self) -> int:
+        n = self.eng.launch_count() + sum(e.launch_count() for e, _ in self.s2_extra)
+        return n + (self.s1_eng.launch_count() if self.s1_eng is not self.eng else 0)
 
-    def fetch_rects(self):
-        """The step's one host synchronisation: merged rectangle (FLAG 2) of every pair -> host."""
-        self.rects_host.copy_(self.rects[:, 0, :], non_blocking=True)
-        self.n_rects_host.copy_(self.n_rects, non_blocking=True)
-        self.torch.cuda.current_stream(self.dev).synchronize()
-        return self.rects_host.numpy(), self.n_rects_host.numpy()
+    # ---- stage 1 ---------------------------------------------------------------------------------------
+    def stage1_chunk(self, frames, j, eng=None):
+        """Steps 1-3 for chunk j on the current stream: leaves the chunk's rectangles in self.rects / n_rects."""
+        eng = eng or self.s1_eng
+        lib, h, st = self.lib, eng.handle, self._stream()
+        Cn, H, W = self.C, self.H, self.W
+        p0, p1 = self.chunks[j]
+        f0 = 0 if j == 0 else p0 + 1      # frames not compressed yet
+        ncell = self.Hc * self.Wc
+        lib.check(lib.nsof_lanczos3_compress_u8(h, frames.data_ptr() + f0 * Cn * H * W, (p1 + 1 - f0) * Cn, H, W, W,
+                                                H * W, self.Hc, self.Wc, self.cells.data_ptr() + f0 * Cn * ncell * 8,
+                                                st), "lanczos3_compress")
+        if j == 0:
+            self.w.fill_(float(PARAMS["wini"]))
+        lib.check(lib.nsof_frame_sim_run_f64(h, self.cells.data_ptr() + p0 * Cn * ncell * 8, p1 - p0 + 1, Cn, self.Hc,
+                                             self.Wc, self.w.data_ptr(), self.currents.data_ptr() + p0 * Cn * ncell * 8,
+                                             C.byref(self.sp), C.byref(self.fsp), st), "frame_sim_run")
+        i0, n = p0 * Cn, (p1 - p0) * Cn
+        lib.check(lib.nsof_roi_from_state_f64(h, self.currents.data_ptr() + i0 * ncell * 8, n, C.byref(self.rp),
+                                              self.thr.data_ptr(), self.memimg.data_ptr() + i0 * ncell, None, None,
+                                              self.n_rects.data_ptr() + i0 * 4,
+                                              self.rects.data_ptr() + i0 * _lib.NSOF_MAX_RECTS * 16, None, st), "roi")
+        self.rects_host[i0:i0 + n].copy_(self.rects[i0:i0 + n, 0, :], non_blocking=True)
+        self.n_rects_host[i0:i0 + n].copy_(self.n_rects[i0:i0 + n], non_blocking=True)
+
+    def stage1(self, frames):
+        """All chunks back to back on the current stream (tests, debugging)."""
+        for j in range(len(self.chunks)):
+            self.stage1_chunk(frames, j, self.s1_eng if not self.overlap else self.eng)
 
     # ---- stage 2 ---------------------------------------------------------------------------------------
-    def build_descs(self, frames, rects, n_rects):
-        """Crop descriptors: views into the resident frames and into the full-frame flow buffers (no copies)."""
+    def build_descs(self, frames, rects, n_rects, pairs=None, n0=0, px0=0):
+        """Crop descriptors of the pairs `pairs` = (p0, p1) appended at self.descs[n0:]: views into the resident
+        frames and into the flow frames (or the packed buffer from pixel px0 on) -- no copies."""
         H, W, Cn = self.H, self.W, self.C
         fbase = frames.data_ptr()
         obase = self.packed.data_ptr() if self.packed_mode else self.flow.data_ptr()
-        n, px = 0, 0
-        for i in range(self.n_pairs):
+        p0, p1 = pairs if pairs is not None else (0, self.F - 1)
+        n, px = n0, px0
+        for i in range(p0 * Cn, p1 * Cn):
             self.offsets[i] = -1
             if self.full_frame:
                 x0, y0, x1, y1 = 0, 0, W, H
@@ -133,113 +183,198 @@ class SequencePipeline:
                 d.flow_pitch = W * 8
             n += 1
             px += (y1 - y0) * (x1 - x0)
-        self.last_crop_pixels = px
-        self.packed_floats = px * 2
-        return n
+        return n, px
 
-    def stage2(self, n_items):
-        if not self.packed_mode:
-            self.flow.zero_()  # S2-g: the reference pastes every crop's flow into a zero frame
-        self.lib.check(self.lib.nsof_farneback_batch(self.h, self.descs, n_items, C.byref(self.fb), self._stream()),
-                       "farneback_batch")
+    def _descs_at(self, n0):
+        return C.cast(C.byref(self.descs, n0 * _DESC_SIZE), C.POINTER(CropDesc))
+
+    def clear_previous(self):
+        """S2-g: the reference pastes every crop's flow into a zero frame.  The flow frames belong to this object
+        and only stage 2 writes them, so zeroing the previous step's rectangles restores all-zero frames."""
+        if self.packed_mode or not self.n_dirty:
+            return
+        self.lib.check(self.lib.nsof_flow_clear(self.h, self.descs, self.n_dirty, self._stream()), "flow_clear")
+        self.n_dirty = 0
+
+    def stage2(self, n0, n1, eng=None):
+        if n1 > n0:
+            self.lib.check(self.lib.nsof_farneback_batch((eng or self.eng).handle, self._descs_at(n0), n1 - n0,
+                                                         C.byref(self.fb), self._stream()), "farneback_batch")
+
+    def stage2_chunk(self, j, n0, n1, cur):
+        """Farneback batch of chunk j on its stream (chunk j -> stream j mod s2_streams, 0 = the caller's);
+        records self.ev_s2[j] there."""
+        k = j % (1 + len(self.s2_extra))
+        if k == 0:
+            self.stage2(n0, n1)
+            self.ev_s2[j].record(cur)
+        else:
+            eng, st = self.s2_extra[k - 1]
+            with self.torch.cuda.stream(st):
+                self.stage2(n0, n1, eng)
+                self.ev_s2[j].record(st)
 
     def step(self, frames):
         """One pass of the hot path over the rank's clips, inputs and outputs resident in HBM."""
+        t = self.torch
+        self.clear_previous()
         if self.full_frame:
-            n = self.build_descs(frames, None, None)
+            n, px = self.build_descs(frames, None, None)
+            self.stage2(0, n)
         else:
-            self.stage1(frames)
-            rects, n_rects = self.fetch_rects()
-            self.last_rects = (rects.copy(), n_rects.copy())
-            n = self.build_descs(frames, rects, n_rects)
-        self.stage2(n)
+            cur = t.cuda.current_stream(self.dev)
+            if self.overlap:
+                self.side.wait_stream(cur)  # frames (and the previous step) are ordered before stage 1
+                for _, st in self.s2_extra:
+                    st.wait_stream(cur)     # ... and before stage 2 on the extra streams (flow_clear included)
+                with t.cuda.stream(self.side):
+                    for j in range(len(self.chunks)):
+                        self.stage1_chunk(frames, j)
+                        self.ev_chunk[j].record(self.side)
+            n = px = 0
+            for j, pr in enumerate(self.chunks):
+                if self.overlap:
+                    self.ev_chunk[j].synchronize()  # the chunk's rectangles are on the host
+                else:
+                    self.stage1_chunk(frames, j, self.eng)
+                    cur.synchronize()
+                n1, px = self.build_descs(frames, self.rects_host.numpy(), self.n_rects_host.numpy(), pr, n, px)
+                self.stage2_chunk(j, n, n1, cur)
+                n = n1
+            for j in range(len(self.chunks)):  # the caller's stream ends the step after every batch
+                if j % (1 + len(self.s2_extra)):
+                    cur.wait_event(self.ev_s2[j])
+            self.last_rects = (self.rects_host.numpy().copy(), self.n_rects_host.numpy().copy())
+        self.n_items = n
+        self.n_dirty = 0 if self.packed_mode else n
+        self.last_crop_pixels = px
+        self.packed_floats = px * 2
         return n
-
 
 
 class HostPipeline:
     """Host-buffer entry of the sequence path (bench.py's e2e leg): pinned uint8 clips in, per pair its rectangle
     and its ROI flow crop (float32, packed) out, host<->device copies included.
 
-    Clips are independent, so the work is software-pipelined over `slots` streams, one clip per stage:
-    H2D of clip k+1 overlaps stage 1 / stage 2 of clip k and the D2H of clip k-1 (both copy engines and the SMs
-    busy at once).  Every slot owns a libnsof handle (one handle per (GPU, stream)), its device frames and its
-    packed output buffer; the only host synchronisation per clip is the event that its rectangles have arrived.
+    The same time-chunked schedule as `SequencePipeline.step`, with a copy stream on either side:
+
+        in    : H2D of chunk j's frames of every clip (strided into the time-major device layout)
+        side  : stage 1 of chunk j  (waits for in[j])  -> rectangles D2H
+        main  : Farneback batch of chunk j (host waits for the rectangles, enqueues)
+        out   : D2H of chunk j's packed flow crops (waits for main[j])
+
+    so both copy engines and the SMs are busy at once and the latency-bound synapse chains hide under stage 2.
     """
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 slots: int = 4, full_frame: bool = False, lib=None):
+                 slots: int | None = None, full_frame: bool = False, lib=None, chunks=None):
         import torch
         self.torch = torch
         self.dev = torch.device(f"cuda:{device}")
         self.C, self.F, self.H, self.W = int(clips), int(frames), int(H), int(W)
-        self.slots = []
-        for _ in range(max(1, min(slots, self.C))):
-            eng = Engine(device, lib=lib)
-            pipe = SequencePipeline(eng, 1, frames, H, W, cfg, full_frame=full_frame, packed=True)
-            self.slots.append(dict(eng=eng, pipe=pipe, stream=torch.cuda.Stream(self.dev),
-                                   frames=torch.empty((frames, 1, H, W), dtype=torch.uint8, device=self.dev),
-                                   ev_rects=torch.cuda.Event(), ev_done=torch.cuda.Event(), busy=False))
-        per_clip = self.slots[0]["pipe"].packed.numel()
-        # host outputs: one packed flow buffer and one rectangle table per clip
-        self.flow_host = [torch.empty((per_clip,), dtype=torch.float32).pin_memory() for _ in range(self.C)]
-        self.rects_out = [None] * self.C
-        self.offsets_out = [None] * self.C
+        self.eng = Engine(device, lib=lib)
+        with torch.cuda.device(self.dev):
+            self.main = torch.cuda.Stream(self.dev)
+            self.s_in = torch.cuda.Stream(self.dev)
+            self.s_out = torch.cuda.Stream(self.dev)
+            if chunks is None:
+                chunks = chunk_schedule(self.F - 1, first=1, grow=2, cap=4)
+            self.pipe = SequencePipeline(self.eng, clips, frames, H, W, cfg, full_frame=full_frame, packed=True,
+                                         chunks=chunks, overlap=True)
+            if full_frame:  # no stage 1: the side stream/handle of the pipe is unused
+                self.pipe.side = None
+            self.frames = torch.empty((self.F, self.C, H, W), dtype=torch.uint8, device=self.dev)
+            nchunk = len(self.pipe.chunks)
+            self.ev_in = [torch.cuda.Event(enable_timing=True) for _ in range(nchunk)]
+            self.ev_d2h = [torch.cuda.Event(enable_timing=True) for _ in range(nchunk)]
+            self.ev_start = torch.cuda.Event(enable_timing=True)
+            self.ev_out = torch.cuda.Event()
+        self.flow_host = torch.empty((self.pipe.packed.numel(),), dtype=torch.float32).pin_memory()
+        self.slots = ([self.main, self.s_in, self.s_out] + ([self.pipe.side] if self.pipe.side is not None else [])
+                      + [st for _, st in self.pipe.s2_extra])
         self.h2d_bytes = self.d2h_bytes = 0
 
     def launch_count(self) -> int:
-        return sum(s["eng"].launch_count() for s in self.slots)
+        return self.pipe.launch_count()
 
-    def _front(self, k, clip_host):
-        """H2D + stage 1 + rectangles D2H of clip k on its slot's stream (asynchronous)."""
-        t = self.torch
-        s = self.slots[k % len(self.slots)]
-        if s["busy"]:
-            s["ev_done"].synchronize()  # the slot's previous clip has left the device
-        with t.cuda.stream(s["stream"]):
-            s["frames"][:, 0].copy_(clip_host, non_blocking=True)
-            p = s["pipe"]
-            if not p.full_frame:
-                p.stage1(s["frames"])
-                p.rects_host.copy_(p.rects[:, 0, :], non_blocking=True)
-                p.n_rects_host.copy_(p.n_rects, non_blocking=True)
-            s["ev_rects"].record()
-        s["busy"] = True
-        self.h2d_bytes += clip_host.numel()
+    def timeline(self):
+        """Device-side completion times (ms after the start of the last run) of every chunk's H2D, stage 1
+        (rectangles on the host), stage 2 and D2H, plus the host clock when each chunk's stage 2 was enqueued."""
+        rows = []
+        for j, pr in enumerate(self.pipe.chunks):
+            g = lambda e: round(self.ev_start.elapsed_time(e), 3)
+            rows.append(dict(chunk=pr, h2d=g(self.ev_in[j]), stage1=None if self.pipe.full_frame else g(self.pipe.ev_chunk[j]),
+                             stage2=g(self.pipe.ev_s2[j]), d2h=g(self.ev_d2h[j]),
+                             host_enqueued=round((self.host_marks[j + 1] - self.host_marks[0]) * 1e3, 3)))
+        return rows
 
-    def _back(self, k):
-        """Wait for clip k's rectangles, then enqueue its Farneback batch and the D2H of the packed crops."""
-        t = self.torch
-        s = self.slots[k % len(self.slots)]
-        p = s["pipe"]
-        s["ev_rects"].synchronize()
-        if p.full_frame:
-            rects, n_rects = None, None
-        else:
-            rects, n_rects = p.rects_host.numpy().copy(), p.n_rects_host.numpy().copy()
-        n = p.build_descs(s["frames"], rects, n_rects)
-        with t.cuda.stream(s["stream"]):
-            p.stage2(n)
-            nf = p.packed_floats
-            self.flow_host[k][:nf].copy_(p.packed[:nf], non_blocking=True)
-            s["ev_done"].record()
-        self.rects_out[k] = (rects, n_rects)
-        self.offsets_out[k] = list(p.offsets)
-        self.d2h_bytes += nf * 4 + p.n_pairs * 20
+    def _ptr(self, stream):
+        return C.c_void_p(stream.cuda_stream)
 
     def run(self, clips_host):
         """clips_host: sequence of C pinned uint8 tensors (F, H, W).  Returns per clip (rects, n_rects, offsets,
-        packed float32 host tensor); pair t's flow crop is packed[offsets[t] : offsets[t] + 2 h w].view(h, w, 2)."""
+        packed float32 host tensor); pair t's flow crop is packed[offsets[t] : offsets[t] + 2 h w].view(h, w, 2).
+        The packed tensor is shared by all clips of the step.  Synchronous: results are on the host on return."""
         assert len(clips_host) == self.C
+        t, p, lib = self.torch, self.pipe, self.eng.lib
+        Cn, F, H, W = self.C, self.F, self.H, self.W
+        fsz = H * W
         self.h2d_bytes = self.d2h_bytes = 0
-        depth = len(self.slots) - 1  # clips in flight ahead of the one being finished
-        for k in range(self.C):
-            self._front(k, clips_host[k])
-            if k >= depth:
-                self._back(k - depth)
-        for k in range(max(0, self.C - depth), self.C):
-            self._back(k)
-        for s in self.slots:
-            s["ev_done"].synchronize()
-            s["busy"] = False
-        return [(self.rects_out[k][0], self.rects_out[k][1], self.offsets_out[k], self.flow_host[k]) for k in range(self.C)]
+        with t.cuda.device(self.dev):
+            self.ev_start.record(self.s_in)
+            self.host_marks = [time.perf_counter()]
+            # ---- in: all H2D copies, chunk by chunk
+            for j, (p0, p1) in enumerate(p.chunks):
+                f0 = 0 if j == 0 else p0 + 1
+                nf = p1 + 1 - f0
+                for c in range(Cn):
+                    src = clips_host[c]
+                    assert src.dtype == t.uint8 and tuple(src.shape) == (F, H, W) and src.is_contiguous()
+                    lib.check(lib.nsof_copy_2d_async(self.frames.data_ptr() + (f0 * Cn + c) * fsz, Cn * fsz,
+                                                     src.data_ptr() + f0 * fsz, fsz, fsz, nf, 1, self._ptr(self.s_in)),
+                              "copy_2d H2D")
+                self.ev_in[j].record(self.s_in)
+                self.h2d_bytes += nf * Cn * fsz
+            # ---- side: stage 1 of every chunk
+            if not p.full_frame:
+                with t.cuda.stream(p.side):
+                    for j in range(len(p.chunks)):
+                        p.side.wait_event(self.ev_in[j])
+                        p.stage1_chunk(self.frames, j)
+                        p.ev_chunk[j].record(p.side)
+            # ---- main + out
+            n = px = 0
+            for j, pr in enumerate(p.chunks):
+                if p.full_frame:
+                    rects = n_rects = None
+                    self.main.wait_event(self.ev_in[j])
+                else:
+                    p.ev_chunk[j].synchronize()
+                    rects, n_rects = p.rects_host.numpy(), p.n_rects_host.numpy()
+                n1, px1 = p.build_descs(self.frames, rects, n_rects, pr, n, px)
+                with t.cuda.stream(self.main):
+                    p.stage2_chunk(j, n, n1, self.main)
+                if px1 > px:
+                    self.s_out.wait_event(p.ev_s2[j])
+                    with t.cuda.stream(self.s_out):
+                        self.flow_host[2 * px:2 * px1].copy_(p.packed[2 * px:2 * px1], non_blocking=True)
+                self.ev_d2h[j].record(self.s_out)
+                self.host_marks.append(time.perf_counter())
+                n, px = n1, px1
+            self.ev_out.record(self.s_out)
+            self.ev_out.synchronize()
+            self.main.synchronize()
+            for _, st in p.s2_extra:
+                st.synchronize()
+        p.n_items, p.last_crop_pixels, p.packed_floats = n, px, 2 * px
+        self.d2h_bytes = px * 8 + (0 if p.full_frame else p.n_pairs * 20)
+        out = []
+        if p.full_frame:
+            for c in range(Cn):
+                out.append((None, None, [p.offsets[tt * Cn + c] for tt in range(F - 1)], self.flow_host))
+        else:
+            R, N = p.rects_host.numpy().reshape(F - 1, Cn, 4), p.n_rects_host.numpy().reshape(F - 1, Cn)
+            for c in range(Cn):
+                out.append((R[:, c].copy(), N[:, c].copy(), [p.offsets[tt * Cn + c] for tt in range(F - 1)],
+                            self.flow_host))
+        return out

@@ -161,12 +161,27 @@ def test_emu_frame_mode_vs_oracle(emu_engine):
     cells = emu_engine.compress_images(frames, 40, 40)
     for i in range(3):
         assert np.allclose(cells[i], s1.compress_image(frames[i], 40, 40), rtol=0, atol=1e-13)
+    # width a multiple of 16: the row pass takes its bulk-copied shared-memory window (two column tiles: 512 + 48)
+    frames = rng.integers(0, 256, (2, 170, 560), dtype=np.uint8)
+    cells = emu_engine.compress_images(frames, 40, 40)
+    for i in range(2):
+        assert np.allclose(cells[i], s1.compress_image(frames[i], 40, 40), rtol=0, atol=1e-13)
     seq = np.clip(0.5 + 0.02 * rng.standard_normal((4, 3, 5)), 0, 1)
     w, cur = emu_engine.simulate_memristor_array(seq, nSubSteps=20)
     w_o, cur_o = s1.simulate_memristor_array(seq, nSubSteps=20)
     assert np.allclose(w, w_o, rtol=0, atol=1e-12) and np.allclose(cur, cur_o, rtol=1e-11)
     w2, cur2 = emu_engine.simulate_memristor_array_stepwise(seq, nSubSteps=20)
     assert np.allclose(w2, w_o, rtol=0, atol=1e-12) and np.allclose(cur2, cur_o, rtol=1e-11)
+    # the carried-power chain at the reference's nSubSteps, through decay, potentiation and both clips of w
+    T = 24
+    seq = np.zeros((T, 2, 3))
+    seq[::2, 0, :] = 1.0
+    seq[:, 1, :] = np.linspace(0, 1, T)[:, None] * np.array([0.0, 0.6, 1.0])
+    w, cur = emu_engine.simulate_memristor_array(seq, nSubSteps=1000)
+    w_o, cur_o = s1.simulate_memristor_array(seq, nSubSteps=1000)
+    assert (w_o == 1.0).any() and (w_o == 0.0).any()
+    assert np.array_equal(w == 1.0, w_o == 1.0) and np.array_equal(w == 0.0, w_o == 0.0)
+    assert np.allclose(w, w_o, rtol=0, atol=1e-12) and np.allclose(cur, cur_o, rtol=1e-11)
 
 
 def test_emu_event_roi_glue_vs_oracle(emu_engine, nsof, golden):

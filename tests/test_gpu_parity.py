@@ -354,6 +354,31 @@ def test_host_pipeline_matches_device_step(gpu_engine, nsof):
             assert np.array_equal(crop, flow[t, c, y0:y1, x0:x1])
 
 
+def test_sequence_step_repeat_and_serial_schedule(gpu_engine, nsof):
+    """The flow frames are zeroed by clearing the previous step's rectangles only (nsof_flow_clear): a second step on
+    DIFFERENT clips must equal a fresh pipeline's result bit for bit, and the overlapped chunk schedule must equal the
+    serial single-stream one."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    a = torch.stack(_small_clips(3), dim=1).cuda().contiguous()
+    b = torch.stack([syn.make_clip(300 + c, 400, 560, 6, "cpu", velocity=(-3.0, 2.5)) for c in range(3)], dim=1).cuda().contiguous()
+    F, _, H, W = a.shape
+    pipe = pm.SequencePipeline(gpu_engine, 3, F, H, W)
+    pipe.step(a)
+    pipe.step(b)
+    torch.cuda.synchronize()
+    fresh = pm.SequencePipeline(gpu_engine, 3, F, H, W, overlap=False, chunks=[(0, F - 1)])
+    n = fresh.step(b)
+    torch.cuda.synchronize()
+    assert n >= 6 and pipe.n_items == n
+    assert np.array_equal(pipe.last_rects[0][pipe.last_rects[1] > 0], fresh.last_rects[0][fresh.last_rects[1] > 0])
+    assert torch.equal(pipe.flow, fresh.flow)
+    assert pipe.launch_count() > 0
+
+
 def test_event_stream_to_roi_gated_flow(gpu_engine, nsof, golden, oracle):
     """BASELINE configs[2] end to end on the device: event stream -> scheme-1 memory decay -> cell currents -> ROI
     rectangle (bit-exact vs the numpy restatement on the reference's own float32 state) -> Farneback on the crop."""
