@@ -366,6 +366,7 @@ static int configure_smem(nsof_handle *h)
     if (h->smem_configured) return NSOF_OK;
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7S, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7S_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(1)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -489,6 +490,8 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
     std::vector<int> max_tiles_pyr(max_scales, 0), max_tiles_pe(max_scales, 0), max_tiles_um(max_scales, 0),
         max_tiles_bs(max_scales, 0);
+    std::vector<int> max_tiles_bss(max_scales, 0);
+    std::vector<long long> sum_tiles_bs(max_scales, 0);
     const int m = params->winsize / 2;
     int BTW = 0, BTH = 0;
     size_t bs_smem = 0;
@@ -543,6 +546,10 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             }
             max_tiles_um[k] = std::max(max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH));
             if (BTW) max_tiles_bs[k] = std::max(max_tiles_bs[k], tiles(BTW, BTH));
+            if (bs_m7) {
+                max_tiles_bss[k] = std::max(max_tiles_bss[k], tiles(FB_BS7S_TW, FB_BS7S_TH));
+                sum_tiles_bs[k] += tiles(BTW, BTH);
+            }
         }
     }
     NSOF_CUDA_TRY(cudaMemcpyAsync(ds, hs, table_bytes, cudaMemcpyHostToDevice, stream));
@@ -636,7 +643,12 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
                          flow_mul);
             for (int it = 0; it < iters; it++) {
                 const bool last = it == iters - 1;
-                if (bs_m7)
+                // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the
+                // 32x16 tile (4x the CTAs, each a quarter of the serial work)
+                if (bs_m7 && sum_tiles_bs[k] < 2 * 148 * 3 && !h->dbg_big_tiles)
+                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S,
+                                 max_tiles_bss[k], na, 1, FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, bscale, (it & 1) == 0, last);
+                else if (bs_m7)
                     NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7,
                                  max_tiles_bs[k], na, 1, FB_BS7_NT, bs_smem, stream, jobs, bscale, (it & 1) == 0, last);
                 else
@@ -790,6 +802,13 @@ extern "C" int nsof_debug_truncate(nsof_handle *h, int stop_level, int stop_iter
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     h->dbg_level = stop_level;
     h->dbg_iters = stop_iters;
+    return NSOF_OK;
+}
+
+extern "C" int nsof_debug_big_tiles(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_big_tiles = enable != 0;
     return NSOF_OK;
 }
 

@@ -26,12 +26,6 @@
 #ifndef FB_BS7_TH
 #define FB_BS7_TH 32
 #endif
-#ifndef FB_BS7_NT
-#define FB_BS7_NT 256
-#endif
-#ifndef FB_BS7_MINB
-#define FB_BS7_MINB 3
-#endif
 
 
 struct FbJob {
@@ -451,7 +445,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
 }
 
 // ---------------------------------------------------------------------------------------------
-// S2-e (+ S2-d fused), tuned variant for a compile-time window radius M and tile TW x TH.
+// S2-e (+ S2-d fused), tuned variant for a compile-time window radius M, tile TW x TH and NT threads.
 // Same arithmetic, same order of operations per pixel as k_fb_blur_solve (results are bit-identical);
 // what changes is how the work is laid out:
 //   phase 1  the M tile + halo (5 planes x (TH+2M) rows) arrives by bulk asynchronous row copies
@@ -459,16 +453,24 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
 //            no register staging, every row in flight at once.  Rows are 16-byte aligned runs starting at
 //            tx0 - ML (ML = M rounded up to 4); replicate borders are patched in shared memory afterwards
 //            (border tiles only).
-//   phase 2  vertical running sums in double, one thread per (plane, column)
-//   phase 3  4 pixels per thread: aligned float4 shared-memory reads of the 2M+4 window columns,
-//            float4 loads of R0, float4 stores of M'
+//   phase 2  vertical running sums in double, one thread per (plane, column), written in place over rows
+//            0 .. TH-1 of the tile; rows TH .. TH+2M-1 of every plane are dead from here on
+//   phase 3a 4 pixels per thread: aligned float4 shared-memory reads of the 2M+4 window columns, 2x2 solve.
+//            Last iteration: flow -> HBM.  Otherwise the flow tile goes to shared memory (into the dead rows)
+//   phase 3b UpdateMatrices with ONE PIXEL PER LANE, consecutive lanes on consecutive x: the 20 bilinear R1
+//            gathers of a warp instruction then fall into one or two 128-byte lines (with 4 pixels per thread
+//            the lanes of one load sat 16 B apart: 4+ lines per instruction, and L1 was the busiest unit of the
+//            kernel at 68 %); R0 loads and M' stores are 128 B per warp instruction.
 // dynamic smem: 16 B (mbarrier) + 5 * (TH+2M) * (TW+2ML) floats.
 // ---------------------------------------------------------------------------------------------
-template <int M, int TW, int TH>
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
+template <int M, int TW, int TH, int NT, int MINB>
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
 {
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, LW = TW + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
+    constexpr int RPP = (2 * M * PW) / (2 * TW);        // flow rows (TW float2) that fit the dead rows of one plane
+    static_assert(5 * RPP >= TH, "the flow tile must fit the dead halo rows");
+    static_assert((TH * PW) % 4 == 0 && (2 * TW) % 4 == 0, "flow rows must stay 16-byte aligned");
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
@@ -481,12 +483,6 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
     float *sM = (float *)(smem_raw + 16);
 
     // ---- phase 1
-#ifdef FB_BS_TIMING
-    long long tstamp[6];
-#endif
-#ifdef FB_BS_TIMING
-    if (NSOF_TID == 0) tstamp[0] = clock64();
-#endif
     const int gx0 = tx0 - ML;                                         // global x of shared column 0
     const int cx0 = nsof_imax(gx0, 0), cx1 = nsof_imin(tx0 + TW + ML, J.pitch);  // copied run, multiples of 4
     const unsigned row_bytes = (unsigned)(cx1 - cx0) * 4u;
@@ -505,9 +501,6 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
     // steals issue slots from the co-resident CTAs: 32 % of all executed instructions in the first profile)
     if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);
     NSOF_SYNC();
-#ifdef FB_BS_TIMING
-    if (NSOF_TID == 0) tstamp[1] = clock64();
-#endif
     if (tx0 - M < 0 || tx0 + TW + M > J.w) {  // replicate the first / last image column into the halo
         const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
         const int s_first = -gx0, s_last = J.w - 1 - gx0;  // shared columns of image x = 0 and x = w - 1
@@ -523,12 +516,9 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
                 for (int sx = s_last + 1 + lane; sx < ML + TW + M; sx += NSOF_WARP) row[sx] = v;
             }
         }
+        NSOF_SYNC();
     }
-    NSOF_SYNC();
 
-#ifdef FB_BS_TIMING
-    if (NSOF_TID == 0) tstamp[2] = clock64();
-#endif
     // ---- phase 2
     for (int col = NSOF_TID; col < 5 * LW; col += NSOF_NT) {
         const int c = col / LW;
@@ -550,10 +540,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
         }
     }
     NSOF_SYNC();
-#ifdef FB_BS_TIMING
-    if (NSOF_TID == 0) tstamp[3] = clock64();
-#endif
-    // ---- phase 3
+    // ---- phase 3a
     constexpr int GW = TW / 4;
     for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
         const int lx = (i % GW) * 4, ly = i / GW;
@@ -595,43 +582,40 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(FB_BS7_NT, FB_BS7_MINB) k_fb_blur_solve_t(const F
             for (int q = 0; q < 4; q++)
                 if (x + q < J.w) fo[q] = make_float2(fxv[q], fyv[q]);
         } else {
-            const size_t o = (size_t)y * J.pitch + x;
-            float r0[5][4];
-#pragma unroll
-            for (int c = 0; c < 5; c++) {
-                const float4 t = NSOF_LDG((const float4 *)(J.R + c * plane + o));
-                r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
-            }
-            float mo[5][4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                float r0v[5], mm[5];
-                if (x + q < J.w) {
-#pragma unroll
-                    for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
-                    fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, fxv[q], fyv[q], r0v, mm);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 5; c++) mm[c] = 0.f;
-                }
-#pragma unroll
-                for (int c = 0; c < 5; c++) mo[c][q] = mm[c];
-            }
-#pragma unroll
-            for (int c = 0; c < 5; c++)
-                *(float4 *)(Mout + c * plane + o) = make_float4(mo[c][0], mo[c][1], mo[c][2], mo[c][3]);
+            float4 *fo = (float4 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+            fo[0] = make_float4(fxv[0], fyv[0], fxv[1], fyv[1]);
+            fo[1] = make_float4(fxv[2], fyv[2], fxv[3], fyv[3]);
         }
     }
-#ifdef FB_BS_TIMING
-    __syncthreads();
-    if (NSOF_TID == 0 && NSOF_BY == 0 && (NSOF_BX % 97) == 5)
-        printf("bs tile %d last %d: load %lld fix %lld vert %lld horiz+um %lld\n", NSOF_BX, last, tstamp[1] - tstamp[0], tstamp[2] - tstamp[1], tstamp[3] - tstamp[2], clock64() - tstamp[3]);
-#endif
+    if (last) return;
+    NSOF_SYNC();
+    // ---- phase 3b
+    const float *R0 = J.R, *R1 = J.R + 5 * plane;
+#pragma unroll 2
+    for (int i = NSOF_TID; i < TW * TH; i += NSOF_NT) {
+        const int lx = i % TW, ly = i / TW;
+        const int x = tx0 + lx, y = ty0 + ly;
+        if (x >= J.w || y >= J.h) continue;
+        const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+        const size_t o = (size_t)y * J.pitch + x;
+        float r0v[5], mm[5];
+#pragma unroll
+        for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(R0 + c * plane + o);
+        fb_um_pixel(R1, plane, J.pitch, J.h, J.w, x, y, f.x, f.y, r0v, mm);
+#pragma unroll
+        for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c];
+    }
 }
 
 // a plain function-pointer name: template commas do not survive nested launch macros
-static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH>;
+#define FB_BS7_NT 256
+#define FB_BS7S_TW 32   // small tile: coarse levels / small batches are latency-bound, more and shorter CTAs
+#define FB_BS7S_TH 16
+#define FB_BS7S_NT 128
+static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, 3>;
+static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
 #define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
+#define FB_BS7S_SMEM (16 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
 
 // ---------------------------------------------------------------------------------------------
 // S2-b + S2-c fused for the two pyramid shapes every BASELINE.json config spends its time in:
@@ -925,18 +909,50 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
     NSOF_SYNC();
     const int Xmin = cols[0] - r, Ymin = rows[0] - r;
     const int swn = nsof_imin(cols[2 * twn - 1] + r - Xmin + 1, SWmax), shn = nsof_imin(rows[2 * thn - 1] + r - Ymin + 1, SHmax);
-    // interior tiles: one bulk asynchronous copy per window row (16-byte aligned superset); border tiles: per-pixel
-    // loads with BORDER_REFLECT_101
-    const bool bulk = Xmin >= 16 && Xmin + swn + 16 <= J.sw && Ymin >= 0 && Ymin + shn <= J.sh && (sp & 15) == 0;
+    // The in-image part of the window arrives by one bulk asynchronous copy per row (16-byte aligned superset of
+    // the row; the last source row only when the superset stays inside it); BORDER_REFLECT_101 is then applied in
+    // shared memory (single bounce: the mirrored sample is always inside the window).  Images narrower than the
+    // kernel radius, or with an unaligned pitch, take per-pixel loads.
+    const int xs0 = nsof_imax(Xmin, 0), xs1 = nsof_imin(Xmin + swn, J.sw);
+    const int ys0 = nsof_imax(Ymin, 0), ys1 = nsof_imin(Ymin + shn, J.sh);
+    const bool bulk = J.sw > r && J.sh > r && (sp & 15) == 0 && xs1 > xs0 && ys1 > ys0;
     int shift = 0;
     if (bulk) {
-        const uint8_t *a0 = src + (size_t)Ymin * sp + Xmin;
-        shift = (int)((uintptr_t)a0 & 15);
-        const unsigned row_bytes = (unsigned)((shift + swn + 15) & ~15);
-        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, row_bytes * (unsigned)shn);
+        const uint8_t *a0 = src + (size_t)ys0 * sp + xs0;
+        const int mis = (int)((uintptr_t)a0 & 15);
+        shift = (mis - (xs0 - Xmin)) & 15;                     // window column sx lives at byte shift + sx of its row
+        const unsigned row_bytes = (unsigned)((mis + (xs1 - xs0) + 15) & ~15);
+        const bool last_safe = xs0 - mis + (int)row_bytes <= J.sw;  // the over-read of the last source row stays in it
+        const int yb1 = (ys1 == J.sh && !last_safe) ? ys1 - 1 : ys1;
+        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(yb1 - ys0));
         NSOF_SYNC();
-        for (int sy = NSOF_TID; sy < shn; sy += NSOF_NT) nsof_bulk_g2s(sS + sy * SWp, a0 - shift + (size_t)sy * sp, row_bytes, bar);
+        for (int y = ys0 + NSOF_TID; y < yb1; y += NSOF_NT)
+            nsof_bulk_g2s(sS + (y - Ymin) * SWp + shift + (xs0 - Xmin) - mis, a0 - mis + (size_t)(y - ys0) * sp, row_bytes, bar);
+        if (yb1 < ys1) {
+            const uint8_t *row = src + (size_t)yb1 * sp;
+            for (int x = xs0 + NSOF_TID; x < xs1; x += NSOF_NT) sS[(yb1 - Ymin) * SWp + shift + (x - Xmin)] = NSOF_LDG(row + x);
+        }
         nsof_mbar_wait(bar, 0);
+        NSOF_SYNC();
+        if (xs0 > Xmin || xs1 < Xmin + swn) {  // left / right reflection, in-image rows
+            const int nl = xs0 - Xmin, nr = Xmin + swn - xs1;
+            for (int i = NSOF_TID; i < (ys1 - ys0) * (nl + nr); i += NSOF_NT) {
+                const int y = ys0 + i / (nl + nr), q = i % (nl + nr);
+                const int X = q < nl ? Xmin + q : xs1 + (q - nl);
+                uint8_t *row = sS + (y - Ymin) * SWp + shift;
+                row[X - Xmin] = row[nsof_reflect101(X, J.sw) - Xmin];
+            }
+            NSOF_SYNC();
+        }
+        if (ys0 > Ymin || ys1 < Ymin + shn) {  // top / bottom reflection, whole window rows
+            const int nt = ys0 - Ymin, nb = Ymin + shn - ys1;
+            for (int i = NSOF_TID; i < (nt + nb) * swn; i += NSOF_NT) {
+                const int q = i / swn, sx = i % swn;
+                const int Y = q < nt ? Ymin + q : ys1 + (q - nt);
+                sS[(Y - Ymin) * SWp + shift + sx] = sS[(nsof_reflect101(Y, J.sh) - Ymin) * SWp + shift + sx];
+            }
+            NSOF_SYNC();
+        }
     } else {
         for (int sy = warp; sy < shn; sy += nw) {
             const uint8_t *row = src + (size_t)nsof_reflect101(Ymin + sy, J.sh) * sp;

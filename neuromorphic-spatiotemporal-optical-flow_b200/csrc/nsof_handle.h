@@ -86,6 +86,7 @@ struct nsof_handle {
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr;
     std::vector<cudaEvent_t> ev_level;
+    bool dbg_big_tiles = false;  // keep the 64x32 blur tile on every level (tests)
     bool no_fork = false;  // nsof_debug_fork(h, 0): everything on the caller's stream
     // launch accounting
     unsigned long long launches = 0;

@@ -333,8 +333,7 @@ NSOF_GLOBAL k_s1_frame_step(const double *NSOF_RESTRICT a, const double *NSOF_RE
 //        u' = u (1 + d),  d = -s c z          (because u' - u = -s (w' - w) = -s c u^b = u * (-s c z))
 //    and the clip of w to [0, 1] is the clip of u' to [1 - s, 1], where z is a constant (1, or (1-s)^(b-1));
 //  * z is carried forward multiplicatively, z' = z (1 + d)^(b-1), by a 6-term binomial series (|d| <= 2e-3:
-//    truncation ~1e-16, Estrin form), so the loop-carried dependency is z -> d -> series -> z: 5 dependent FP64
-//    operations instead of an exp(log) pair (~45);
+//    truncation ~1e-16, Estrin form) instead of an exp(log) pair (~45 dependent operations);
 //  * z is re-evaluated exactly, exp((b-1) log u), every 64 sub-steps and whenever |d| is larger, which bounds the
 //    accumulated rounding to ~1e-14 relative.
 NSOF_DEV double s1_pow_pos(double x, double b) { return x > 0. ? exp(b * log(x)) : pow(x, b); }
@@ -352,7 +351,10 @@ NSOF_DEV S1Binom s1_binom(double b)
     return c;
 }
 
-// nsub sub-steps of w <- clip(w + c * (1 - s w)^b, 0, 1) with c = g * dt_sub, 0 < s < 1
+// nsub sub-steps of w <- clip(w + c * (1 - s w)^b, 0, 1) with c = g * dt_sub, 0 < s < 1.
+// The loop carries d = -s c z itself (d' = d (1 + d)^(b-1)): the dependency is d -> series -> d, three FP64 levels.
+// The series is evaluated unconditionally and ONE predicate (no clip, |d| small, not a re-evaluation step), ready
+// before the series is, guards the rare path: a branch per test would serialise the in-order pipeline on each.
 NSOF_DEV double s1_euler_chain(double wv, double c, double s, double b, int nsub)
 {
     if (c == 0.) return wv;
@@ -361,18 +363,20 @@ NSOF_DEV double s1_euler_chain(double wv, double c, double s, double b, int nsub
     const double kap = -s * c;
     const double u_lo = 1. - s, z_lo = s1_pow_pos(u_lo, e);  // w = 1
     double u = 1. - wv * s;
-    double z = s1_pow_pos(u, e);
+    double d = kap * s1_pow_pos(u, e);
     for (int i = 0; i < nsub; i++) {
-        const double d = kap * z;
+        // d (1 + a1 d + ... + a6 d^6) = (d + d^2 (a1 + a2 d)) + d^4 ((a3 + a4 d) + d^2 (a5 + a6 d)): three levels
+        const double d2 = d * d, d4 = d2 * d2;
+        double dn = (d + d2 * (k.a1 + k.a2 * d)) + d4 * ((k.a3 + k.a4 * d) + d2 * (k.a5 + k.a6 * d));
         double un = u + u * d;
-        if (un >= 1.) { un = 1.; z = 1.; }                 // w clipped at 0
-        else if (un <= u_lo) { un = u_lo; z = z_lo; }      // w clipped at 1
-        else if (fabs(d) > 2e-3 || (i & 63) == 63) z = s1_pow_pos(un, e);
-        else {
-            const double d2 = d * d, d3 = d2 * d;
-            z *= (1. + d * (k.a1 + k.a2 * d)) + d3 * ((k.a3 + k.a4 * d) + d2 * (k.a5 + k.a6 * d));
+        const bool fast = (un < 1.) & (un > u_lo) & (fabs(d) <= 2e-3) & ((i & 63) != 63);
+        if (!fast) {
+            if (un >= 1.) { un = 1.; dn = kap; }                 // w clipped at 0: z = 1
+            else if (un <= u_lo) { un = u_lo; dn = kap * z_lo; }  // w clipped at 1
+            else dn = kap * s1_pow_pos(un, e);                   // exact re-evaluation
         }
         u = un;
+        d = dn;
     }
     if (u >= 1.) return 0.;
     if (u <= u_lo) return 1.;

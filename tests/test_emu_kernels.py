@@ -16,6 +16,14 @@ def test_emu_farneback_vs_golden(emu_engine, golden, pname):
         prev, nxt = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"]
         got = emu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
         helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"emu vs cv2 {case}")
+    if pname == "grasp":  # both tiles of the tuned blur+solve kernel: small inputs take the 32x16 one by default
+        emu_engine.lib.check(emu_engine.lib.nsof_debug_big_tiles(emu_engine.handle, 1))
+        try:
+            for case in golden.fb["cases"]:
+                got = emu_engine.calcOpticalFlowFarneback(golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"], None, **p)
+                helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"emu (64x32 tile) vs cv2 {case}")
+        finally:
+            emu_engine.lib.check(emu_engine.lib.nsof_debug_big_tiles(emu_engine.handle, 0))
 
 
 @pytest.mark.parametrize("hw,fuse", [((150, 203), False), ((152, 204), True), ((150, 203), True)])

@@ -25,6 +25,14 @@ def test_farneback_vs_cv2_golden(gpu_engine, golden, pname):
         prev, nxt = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"]
         got = gpu_engine.calcOpticalFlowFarneback(prev, nxt, None, **p)
         helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"gpu vs cv2 {case}")
+    if pname == "grasp":  # both tiles of the tuned blur+solve kernel: small inputs take the 32x16 one by default
+        gpu_engine.lib.check(gpu_engine.lib.nsof_debug_big_tiles(gpu_engine.handle, 1))
+        try:
+            for case in golden.fb["cases"]:
+                got = gpu_engine.calcOpticalFlowFarneback(golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"], None, **p)
+                helpers.assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"gpu (64x32 tile) vs cv2 {case}")
+        finally:
+            gpu_engine.lib.check(gpu_engine.lib.nsof_debug_big_tiles(gpu_engine.handle, 0))
 
 
 @pytest.mark.parametrize("hw,fuse", [((150, 203), False), ((152, 204), True), ((150, 203), True)])
