@@ -225,26 +225,26 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
     float r2, r3, r4, r5, r6;
     fx -= (float)x1;
     fy -= (float)y1;
-    if ((unsigned)x1 < (unsigned)(w - 1) && (unsigned)y1 < (unsigned)(h - 1)) {
+    // The 20 loads are issued unconditionally (from a clamped, always valid address) and the two cases are
+    // selected afterwards: without a branch around them the loads of several pixels can be in flight at once.
+    const bool inb = (unsigned)x1 < (unsigned)(w - 1) && (unsigned)y1 < (unsigned)(h - 1);
+    {
         const float a00 = (1.f - fx) * (1.f - fy), a01 = fx * (1.f - fy), a10 = (1.f - fx) * fy, a11 = fx * fy;
-        const float *p = R1 + (size_t)y1 * pitch + x1;
-        r2 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float *p = R1 + (inb ? (size_t)y1 * pitch + x1 : (size_t)0);
+        const float q2 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
         p += plane;
-        r3 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q3 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
         p += plane;
-        r4 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q4 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
         p += plane;
-        r5 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q5 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
         p += plane;
-        r6 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
-        r4 = (r0v[2] + r4) * 0.5f;
-        r5 = (r0v[3] + r5) * 0.5f;
-        r6 = (r0v[4] + r6) * 0.25f;
-    } else {
-        r2 = r3 = 0.f;
-        r4 = r0v[2];
-        r5 = r0v[3];
-        r6 = r0v[4] * 0.5f;
+        const float q6 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        r2 = inb ? q2 : 0.f;
+        r3 = inb ? q3 : 0.f;
+        r4 = inb ? (r0v[2] + q4) * 0.5f : r0v[2];
+        r5 = inb ? (r0v[3] + q5) * 0.5f : r0v[3];
+        r6 = inb ? (r0v[4] + q6) * 0.25f : r0v[4] * 0.5f;
     }
     r2 = (r0v[0] - r2) * 0.5f;
     r3 = (r0v[1] - r3) * 0.5f;
@@ -446,14 +446,14 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
 
 // ---------------------------------------------------------------------------------------------
 // S2-e (+ S2-d fused), tuned variant for a compile-time window radius M, tile TW x TH and NT threads.
-// Same arithmetic, same order of operations per pixel as k_fb_blur_solve (results are bit-identical);
+// Same arithmetic as k_fb_blur_solve except for the vertical window sums (float tree, see phase 2);
 // what changes is how the work is laid out:
 //   phase 1  the M tile + halo (5 planes x (TH+2M) rows) arrives by bulk asynchronous row copies
 //            (cp.async.bulk global->shared on an mbarrier, SASS UBLKCP): no per-element index arithmetic,
 //            no register staging, every row in flight at once.  Rows are 16-byte aligned runs starting at
 //            tx0 - ML (ML = M rounded up to 4); replicate borders are patched in shared memory afterwards
 //            (border tiles only).
-//   phase 2  vertical running sums in double, one thread per (plane, column), written in place over rows
+//   phase 2  vertical window sums (float tree), one thread per (plane, column pair), written in place over rows
 //            0 .. TH-1 of the tile; rows TH .. TH+2M-1 of every plane are dead from here on
 //   phase 3a 4 pixels per thread: aligned float4 shared-memory reads of the 2M+4 window columns, 2x2 solve.
 //            Last iteration: flow -> HBM.  Otherwise the flow tile goes to shared memory (into the dead rows)
@@ -466,7 +466,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
 template <int M, int TW, int TH, int NT, int MINB>
 NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
 {
-    constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, LW = TW + 2 * M, SP = LH * PW;
+    constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
     constexpr int RPP = (2 * M * PW) / (2 * TW);        // flow rows (TW float2) that fit the dead rows of one plane
     static_assert(5 * RPP >= TH, "the flow tile must fit the dead halo rows");
@@ -497,6 +497,19 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         const int gy = nsof_clampi(ty0 - M + ly, 0, J.h - 1);
         nsof_bulk_g2s(sM + c * SP + ly * PW + (cx0 - gx0), Min + c * plane + (size_t)gy * J.pitch + cx0, row_bytes, bar);
     }
+    // phase 3b reads R0 and gathers R1 around this tile: start pulling those rows into L2 now (bulk prefetch, one
+    // instruction per row; R1 with a margin of ML columns / M rows for the displacement), so that the dependent
+    // loads two phases later find them there instead of paying DRAM latency at 35 % occupancy
+    if (!last) {
+        const int px0 = nsof_imax(tx0 - ML, 0), px1 = nsof_imin(tx0 + TW + ML, J.pitch);
+        const int py0 = nsof_imax(ty0 - M, 0), py1 = nsof_imin(ty0 + TH + M, J.h);
+        const int t0 = nsof_imin(tx0 + TW, J.pitch);
+        for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
+            const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
+            nsof_prefetch_l2(J.R + (5 + c) * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
+            if (gy >= ty0 && gy < ty0 + TH) nsof_prefetch_l2(J.R + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(t0 - tx0) * 4u);
+        }
+    }
     // one warp polls the mbarrier; the others sleep in the block barrier (a try_wait spin in every warp
     // steals issue slots from the co-resident CTAs: 32 % of all executed instructions in the first profile)
     if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);
@@ -519,24 +532,29 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         NSOF_SYNC();
     }
 
-    // ---- phase 2
-    for (int col = NSOF_TID; col < 5 * LW; col += NSOF_NT) {
-        const int c = col / LW;
-        float *p = sM + c * SP + (ML - M) + (col - c * LW);
-        // prefix sums in double, fully unrolled: every element is loaded and converted once, the window sum of
-        // output row y is P[y + 2M + 1] - P[y]; the 2M + 2 live prefixes sit in a statically indexed register ring
-        constexpr int RING = 2 * M + 2;
-        double ring[RING];
-        double run = 0.;
-        ring[0] = 0.;
+    // ---- phase 2: vertical 15-row window sums, one thread per (plane, pair of columns), all LH rows unrolled.
+    // Each window is summed as a fixed tree  (v[y..y+7] + v[y+8..y+11]) + (v[y+12..y+13] + v[y+14])  built from
+    // shared pair / quad / octet sums: 7 float additions per output instead of 14, depth 4, and no loop-carried
+    // dependency.  (OpenCV keeps running sums in double; a running float sum would let rounding of large
+    // neighbours leak into small windows, a direct tree does not: relative error <= 4 ulp of sum |v|.  The double
+    // version cost 2 x 46 dependent FP64 additions per column and a float<->double conversion per element on
+    // the quarter-rate XU pipe, which ncu showed as the busiest pipe of the kernel.)
+    static_assert(M == 7, "the window tree is written for 2M+1 = 15 = 8 + 4 + 2 + 1 rows");
+    for (int it = NSOF_TID; it < 5 * (PW / 2); it += NSOF_NT) {
+        const int c = it / (PW / 2);
+        float2 *p = (float2 *)(sM + c * SP) + (it - c * (PW / 2));
+        float2 v[LH], p2[LH], p4[LH], p8[LH];
 #pragma unroll
         for (int j = 0; j < LH; j++) {
-            run += (double)p[j * PW];
-            if (j >= 2 * M) {  // rows 0 .. j are summed: output row y = j - 2M is complete
-                const int y = j - 2 * M;
-                p[y * PW] = (float)(run - ring[y % RING]);  // row y of the column is dead (already summed)
+            v[j] = p[j * (PW / 2)];
+            if (j >= 1) p2[j - 1] = make_float2(v[j - 1].x + v[j].x, v[j - 1].y + v[j].y);
+            if (j >= 3) p4[j - 3] = make_float2(p2[j - 3].x + p2[j - 1].x, p2[j - 3].y + p2[j - 1].y);
+            if (j >= 7) p8[j - 7] = make_float2(p4[j - 7].x + p4[j - 3].x, p4[j - 7].y + p4[j - 3].y);
+            if (j >= 14) {
+                const int y = j - 14;  // row y of the column pair is dead (already loaded)
+                p[y * (PW / 2)] = make_float2((p8[y].x + p4[y + 8].x) + (p2[y + 12].x + v[j].x),
+                                              (p8[y].y + p4[y + 8].y) + (p2[y + 12].y + v[j].y));
             }
-            ring[(j + 1) % RING] = run;
         }
     }
     NSOF_SYNC();

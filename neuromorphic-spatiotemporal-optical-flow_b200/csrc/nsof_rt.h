@@ -107,6 +107,7 @@ static inline void nsof_mbar_init(nsof_mbar_t *, int) {}
 static inline void nsof_mbar_expect_tx(nsof_mbar_t *, unsigned) {}
 static inline void nsof_bulk_g2s(void *dst, const void *src, unsigned bytes, nsof_mbar_t *) { memcpy(dst, src, bytes); }
 static inline void nsof_mbar_wait(nsof_mbar_t *, unsigned) {}
+static inline void nsof_prefetch_l2(const void *, unsigned) {}
 #define NSOF_LANE 0
 #define NSOF_SYNCWARP() ((void)0)
 #else
@@ -141,6 +142,11 @@ __device__ __forceinline__ void nsof_mbar_wait(nsof_mbar_t *bar, unsigned parity
         "}\n" ::"r"(nsof_smem_u32(bar)),
         "r"(parity)
         : "memory");
+}
+// bulk L2 prefetch of a 16-byte aligned run (cp.async.bulk.prefetch: no register, no LSU slot, no completion)
+__device__ __forceinline__ void nsof_prefetch_l2(const void *src, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 #define NSOF_LANE ((int)(threadIdx.x & 31))
 #define NSOF_SYNCWARP() __syncwarp()
