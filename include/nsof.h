@@ -120,6 +120,40 @@ NSOF_API int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int n,
 NSOF_API int nsof_copy_2d_async(void *dst, ptrdiff_t dst_pitch, const void *src, ptrdiff_t src_pitch,
                                 size_t row_bytes, size_t rows, int kind, void *cuda_stream);
 
+/* ---- stage 2 split by rows over several GPUs (BASELINE.json configs[4]: 8K frames, halo-row exchange) -------
+ * The reference has no multi-GPU path; this is the B200 design for frames too large to be worth one GPU each.
+ * Every rank calls nsof_fb_tiled_begin with the SAME full-frame crop descriptors (its own device pointers; only
+ * the source rows its band's stencils reach are read, and only its band of `flow` is written) and then drives the
+ * level loop of FarnebackOpticalFlowImpl::calc (A.1) stage by stage:
+ *     for level = levels-1 .. 0:
+ *         stage 0 (pyramid + PolyExp of the band)      -> exchange `halo_r1` rows of R1 (what = 0) with both
+ *                                                          neighbours, and (level < top) 4 rows of the coarser
+ *                                                          level's flow (what = 3, level + 1)
+ *         stage 1 (first UpdateMatrices)               -> exchange winsize/2 rows of Ma (what = 1)
+ *         stage 2, it = 0 .. iterations-1              -> after every iteration but the last: exchange winsize/2
+ *                                                          rows of the M buffer just written (Mb, Ma, Mb, ...)
+ * Rank r owns rows [r*h_k/world, (r+1)*h_k/world) of level k (nsof_tiled_buf.y_lo / y_hi).  An exchange sends the
+ * first / last rows of the band to the upper / lower neighbour and receives theirs into the rows just outside the
+ * band, in place (the workspace is full size on every rank).  parallel.TiledFarneback does this over NCCL. */
+typedef struct nsof_tiled_buf {
+    void *ptr;             /* device pointer of row 0 of plane 0 (rows of the WHOLE level, not of the band) */
+    size_t row_floats;     /* floats per row */
+    size_t plane_floats;   /* floats between planes */
+    int planes;
+    int h, w;              /* the level's size */
+    int y_lo, y_hi;        /* this rank's band of rows */
+} nsof_tiled_buf;
+NSOF_API int nsof_fb_tiled_begin(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params,
+                                 int rank, int world, int halo_r1, void *cuda_stream);
+NSOF_API int nsof_fb_tiled_levels(const nsof_handle *h);
+/* stage: 0 pyramid + PolyExp, 1 first UpdateMatrices, 2 blur + solve iteration `it` (ignored otherwise). */
+NSOF_API int nsof_fb_tiled_stage(nsof_handle *h, int level, int stage, int it, void *cuda_stream);
+/* what: 0 R1, 1 Ma, 2 Mb, 3 flow of `level` (level 0: the caller's flow buffer). */
+NSOF_API int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what, nsof_tiled_buf *out);
+/* *tripped = 1 when an UpdateMatrices gather reached R1 rows beyond the received halo (result invalid: rerun with
+ * a larger halo_r1).  Synchronises the stream. */
+NSOF_API int nsof_fb_tiled_guard(nsof_handle *h, int *tripped, void *cuda_stream);
+
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
 NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,

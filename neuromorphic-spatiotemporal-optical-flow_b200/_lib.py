@@ -57,6 +57,11 @@ class FrameSimParams(C.Structure):
                 ("vds", C.c_double)]
 
 
+class TiledBuf(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("row_floats", C.c_size_t), ("plane_floats", C.c_size_t), ("planes", C.c_int),
+                ("h", C.c_int), ("w", C.c_int), ("y_lo", C.c_int), ("y_hi", C.c_int)]
+
+
 class KernelStat(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("launches", C.c_int), ("ms", C.c_double), ("algorithmic_bytes", C.c_double)]
 
@@ -82,6 +87,12 @@ _SIGNATURES = {
     "nsof_flow_clear": (C.c_int, [C.c_void_p, _P(CropDesc), C.c_int, C.c_void_p]),
     "nsof_copy_2d_async": (C.c_int, [C.c_void_p, C.c_ssize_t, C.c_void_p, C.c_ssize_t, C.c_size_t, C.c_size_t, C.c_int,
                                      C.c_void_p]),
+    "nsof_fb_tiled_begin": (C.c_int, [C.c_void_p, _P(CropDesc), C.c_int, _P(FbParams), C.c_int, C.c_int, C.c_int,
+                                      C.c_void_p]),
+    "nsof_fb_tiled_levels": (C.c_int, [C.c_void_p]),
+    "nsof_fb_tiled_stage": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "nsof_fb_tiled_query": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _P(TiledBuf)]),
+    "nsof_fb_tiled_guard": (C.c_int, [C.c_void_p, _P(C.c_int), C.c_void_p]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),

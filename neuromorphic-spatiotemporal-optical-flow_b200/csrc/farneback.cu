@@ -74,6 +74,8 @@ struct FbItemPlan {
     nsof_crop_desc d;
 };
 
+static void fb_ctx_free(nsof_handle *h);  // defined with FbBatchCtx
+
 extern "C" int nsof_create(int device, nsof_handle **out)
 {
     if (!out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_create: out is NULL");
@@ -102,6 +104,8 @@ extern "C" int nsof_destroy(nsof_handle *h)
     h->arena.release();
     h->tables.release();
     h->clear_tab.release();
+    h->guard_buf.release();
+    fb_ctx_free(h);
     h->io.release();
     h->s1.release();
     h->lz.release();
@@ -404,19 +408,60 @@ extern "C" int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_it
     return h->tables.ensure((size_t)max_items * 8 * sizeof(FbJob) + 65536);
 }
 
-extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params,
-                                    void *cuda_stream)
+// Everything one batch needs between planning and the last launch.  nsof_farneback_batch fills it and runs all
+// stages; the spatially tiled entry points (nsof_fb_tiled_*) fill it once and run one stage per call, with the
+// caller exchanging halo rows in between.
+struct FbTiling {
+    int rank, world;   // this rank owns rows [rank * h_k / world, (rank + 1) * h_k / world) of every level k
+    int halo_r1;       // R1 rows received from each neighbour per level (reach of the UpdateMatrices gather)
+    int *guard;        // device flag, see FbJob::guard
+};
+
+struct FbBatchCtx {
+    bool valid = false;
+    int n = 0, max_scales = 0, stop_level = 0, m = 0;
+    nsof_fb_params params = {};
+    bool tiled = false;
+    FbTiling tiling = {0, 1, 0, nullptr};
+    int ksize[64];
+    std::vector<size_t> gk_off, job_off;
+    std::vector<int> n_active, path_n, max_tiles_pp, max_tiles_ps, ps_sw, ps_sh, max_tiles_pyr, max_tiles_pe,
+        max_tiles_um, max_tiles_bs, max_tiles_bss;
+    std::vector<long long> sum_tiles_bs;
+    std::vector<double> sumN, sumNc, path_N, path_N0;
+    int BTW = 0, BTH = 0;
+    size_t bs_smem = 0, pe_smem = 0;
+    bool bs_m7 = false;
+    PolyConst pc;
+    float flow_mul = 0.f, bscale = 0.f;
+    unsigned char *ds = nullptr;  // device tables
+};
+
+static void fb_ctx_free(nsof_handle *h)
 {
-    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: NULL handle");
-    if (n < 0 || (n > 0 && !items)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: bad item list");
-    int rc = validate_params(params);
+    delete h->ctx;
+    h->ctx = nullptr;
+}
+
+// rows [lo, hi) of a level of height hk owned by `rank` of `world`
+static inline void band_rows(int hk, int rank, int world, int *lo, int *hi)
+{
+    *lo = (int)((long long)rank * hk / world);
+    *hi = (int)((long long)(rank + 1) * hk / world);
+}
+
+static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params,
+                      const FbTiling *tiling, cudaStream_t stream)
+{
+    if (!h->ctx) h->ctx = new FbBatchCtx();
+    FbBatchCtx &X = *h->ctx;
+    X.valid = false;
+    int rc = configure_smem(h);
     if (rc) return rc;
-    if (n == 0) return NSOF_OK;
-    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: at most 65535 items per batch");
-    cudaStream_t stream = (cudaStream_t)cuda_stream;
-    NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    rc = configure_smem(h);
-    if (rc) return rc;
+    X.n = n;
+    X.params = *params;
+    X.tiled = tiling != nullptr;
+    if (tiling) X.tiling = *tiling;
 
     // ---- plan: geometry + arena offsets
     std::vector<FbItemPlan> &plan = *h->last_plan;
@@ -444,36 +489,37 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     rc = h->arena.ensure(arena_floats * sizeof(float));
     if (rc) return rc;
     float *base = (float *)h->arena.p;
+    X.max_scales = max_scales;
 
-    int ksize[64];
     double sigma[64];
     {
         // ksize/sigma depend on the level index only; take them from a geometry with all levels present
         double scale = 1;
         for (int k = 0; k < max_scales; k++) {
             sigma[k] = (1. / scale - 1) * 0.5;
-            ksize[k] = std::max(cv_round(sigma[k] * 5) | 1, 3);
+            X.ksize[k] = std::max(cv_round(sigma[k] * 5) | 1, 3);
             scale *= params->pyr_scale;
         }
     }
-    const int stop_level = (h->dbg_level >= 0 && h->dbg_level < max_scales) ? h->dbg_level : 0;
-    h->last_stop_level = stop_level;
+    X.stop_level = (h->dbg_level >= 0 && h->dbg_level < max_scales) ? h->dbg_level : 0;
+    h->last_stop_level = X.stop_level;
     h->last_params = *params;
 
     // ---- job tables for every level + Gaussian taps, one upload
     size_t gk_floats = 0;
-    std::vector<size_t> gk_off(max_scales), job_off(max_scales);
-    std::vector<int> n_active(max_scales, 0);
+    X.gk_off.assign(max_scales, 0);
+    X.job_off.assign(max_scales, 0);
+    X.n_active.assign(max_scales, 0);
     for (int k = 0; k < max_scales; k++) {
-        if (ksize[k] / 2 > 4096) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: pyramid blur ksize %d too large", ksize[k]);
-        gk_off[k] = gk_floats;
-        gk_floats += round_up(ksize[k] / 2 + 1, 4);
-        for (int i = 0; i < n; i++) n_active[k] += plan[i].scales > k;
+        if (X.ksize[k] / 2 > 4096) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: pyramid blur ksize %d too large", X.ksize[k]);
+        X.gk_off[k] = gk_floats;
+        gk_floats += round_up(X.ksize[k] / 2 + 1, 4);
+        for (int i = 0; i < n; i++) X.n_active[k] += plan[i].scales > k;
     }
     size_t table_bytes = round_up(gk_floats * sizeof(float), 16);
     for (int k = 0; k < max_scales; k++) {
-        job_off[k] = table_bytes;
-        table_bytes += round_up((size_t)n_active[k] * sizeof(FbJob), 16);
+        X.job_off[k] = table_bytes;
+        table_bytes += round_up((size_t)X.n_active[k] * sizeof(FbJob), 16);
     }
     NsofStageSlot *slot;
     rc = nsof_stage_acquire(h, table_bytes, &slot);
@@ -481,27 +527,30 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
     rc = h->tables.ensure(table_bytes);
     if (rc) return rc;
     unsigned char *hs = (unsigned char *)slot->host;
-    unsigned char *ds = (unsigned char *)h->tables.p;
-    std::vector<double> sumN(max_scales + 1, 0.), sumN0(max_scales, 0.);
+    X.ds = (unsigned char *)h->tables.p;
+    X.sumN.assign(max_scales, 0.);
+    X.sumNc.assign(max_scales, 0.);
     // per level and pyramid path (0 generic, 1 fused level-0 shape, 2 fused exact-2x shape): items, pixels, source pixels
-    std::vector<int> path_n(3 * max_scales, 0), max_tiles_pp(max_scales, 0), max_tiles_ps(max_scales, 0);
-    std::vector<int> ps_sw(max_scales, 0), ps_sh(max_scales, 0);  // largest source window of a k_fb_pyr_sep tile
-    std::vector<double> path_N(3 * max_scales, 0.), path_N0(3 * max_scales, 0.);
+    X.path_n.assign(3 * max_scales, 0);
+    X.path_N.assign(3 * max_scales, 0.);
+    X.path_N0.assign(3 * max_scales, 0.);
+    for (auto *v : {&X.max_tiles_pp, &X.max_tiles_ps, &X.ps_sw, &X.ps_sh, &X.max_tiles_pyr, &X.max_tiles_pe, &X.max_tiles_um,
+                    &X.max_tiles_bs, &X.max_tiles_bss})
+        v->assign(max_scales, 0);
+    X.sum_tiles_bs.assign(max_scales, 0);
     const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
-    std::vector<int> max_tiles_pyr(max_scales, 0), max_tiles_pe(max_scales, 0), max_tiles_um(max_scales, 0),
-        max_tiles_bs(max_scales, 0);
-    std::vector<int> max_tiles_bss(max_scales, 0);
-    std::vector<long long> sum_tiles_bs(max_scales, 0);
     const int m = params->winsize / 2;
-    int BTW = 0, BTH = 0;
-    size_t bs_smem = 0;
-    const bool bs_m7 = (m == 7);  // winsize 14/15: the tuned kernel (every BASELINE.json config)
-    if (bs_m7) { BTW = FB_BS7_TW; BTH = FB_BS7_TH; bs_smem = FB_BS7_SMEM; }
-    else if (params->iterations > 0 && !pick_blur_tile(m, &BTW, &BTH, &bs_smem))
+    X.m = m;
+    X.BTW = X.BTH = 0;
+    X.bs_smem = 0;
+    X.bs_m7 = (m == 7);  // winsize 14/15: the tuned kernel (every BASELINE.json config)
+    if (X.bs_m7) { X.BTW = FB_BS7_TW; X.BTH = FB_BS7_TH; X.bs_smem = FB_BS7_SMEM; }
+    else if (params->iterations > 0 && !pick_blur_tile(m, &X.BTW, &X.BTH, &X.bs_smem))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
+    const int pn = params->poly_n;
     for (int k = 0; k < max_scales; k++) {
-        gaussian_half_kernel(ksize[k], sigma[k], (float *)hs + gk_off[k]);
-        FbJob *jobs = (FbJob *)(hs + job_off[k]);
+        gaussian_half_kernel(X.ksize[k], sigma[k], (float *)hs + X.gk_off[k]);
+        FbJob *jobs = (FbJob *)(hs + X.job_off[k]);
         int a = 0;
         for (int i = 0; i < n; i++) {
             const FbItemPlan &pl = plan[i];
@@ -521,10 +570,21 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             else if (J.sh == 2 * J.h && J.sw == 2 * J.w) J.resize_mode = 1;  // cv::resize takes INTER_AREA at exact 2x
             else J.resize_mode = 2;
             J.sx = (double)J.sw / J.w; J.sy = (double)J.sh / J.h;
-            J.fast = (may_fuse && ksize[k] == 3 && J.resize_mode < 2) ? J.resize_mode + 1 : 0;
-            path_n[3 * k + J.fast] += 1;
-            path_N[3 * k + J.fast] += (double)J.h * J.w;
-            path_N0[3 * k + J.fast] += (double)J.sh * J.sw;
+            J.fast = (may_fuse && X.ksize[k] == 3 && J.resize_mode < 2) ? J.resize_mode + 1 : 0;
+            // row window
+            J.y_lo = 0; J.y_hi = J.h; J.gy_lo = 0; J.gy_hi = J.h; J.guard = nullptr;
+            if (tiling) {
+                band_rows(J.h, tiling->rank, tiling->world, &J.y_lo, &J.y_hi);
+                J.gy_lo = std::max(0, J.y_lo - tiling->halo_r1);
+                J.gy_hi = std::min(J.h, J.y_hi + tiling->halo_r1);
+                J.guard = tiling->guard;
+            }
+            J.iy_lo = std::max(0, J.y_lo - pn); J.iy_hi = std::min(J.h, J.y_hi + pn);
+            const int rows = J.y_hi - J.y_lo, irows = J.iy_hi - J.iy_lo;
+            const double frac = (double)rows / J.h;  // share of the level this rank computes (1 when untiled)
+            X.path_n[3 * k + J.fast] += 1;
+            X.path_N[3 * k + J.fast] += (double)rows * J.w;
+            X.path_N0[3 * k + J.fast] += (double)J.sh * J.sw * frac;
             J.I = base + pl.off_I[k]; J.R = base + pl.off_R[k]; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
             // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
             float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
@@ -533,63 +593,134 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             else { J.flow = (float2 *)fl_this; J.fpitch = J.pitch; }
             J.cflow = (const float2 *)fl_coarse;
             jobs[a++] = J;
-            sumN[k] += (double)J.h * J.w;
-            sumN0[k] += (double)J.sh * J.sw;
-            auto tiles = [&](int tw, int th) { return ((J.w + tw - 1) / tw) * ((J.h + th - 1) / th); };
-            max_tiles_pyr[k] = std::max(max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH));
-            max_tiles_pe[k] = std::max(max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH));
-            max_tiles_pp[k] = std::max(max_tiles_pp[k], tiles(FB_PP_TW, FB_PP_TH));
+            X.sumN[k] += (double)rows * J.w;
+            if (!coarsest) X.sumNc[k] += (double)J.ch * J.cw * frac;
+            auto tiles = [&](int tw, int th, int nrows) { return ((J.w + tw - 1) / tw) * ((nrows + th - 1) / th); };
+            X.max_tiles_pyr[k] = std::max(X.max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH, irows));
+            X.max_tiles_pe[k] = std::max(X.max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH, rows));
+            X.max_tiles_pp[k] = std::max(X.max_tiles_pp[k], tiles(FB_PP_TW, FB_PP_TH, rows));
             if (!J.fast) {
-                max_tiles_ps[k] = std::max(max_tiles_ps[k], tiles(FB_PS_TW, FB_PS_TH));
-                ps_sw[k] = std::max(ps_sw[k], (int)ceil(FB_PS_TW * J.sx) + 2 * (ksize[k] / 2) + 4);
-                ps_sh[k] = std::max(ps_sh[k], (int)ceil(FB_PS_TH * J.sy) + 2 * (ksize[k] / 2) + 4);
+                X.max_tiles_ps[k] = std::max(X.max_tiles_ps[k], tiles(FB_PS_TW, FB_PS_TH, irows));
+                X.ps_sw[k] = std::max(X.ps_sw[k], (int)ceil(FB_PS_TW * J.sx) + 2 * (X.ksize[k] / 2) + 4);
+                X.ps_sh[k] = std::max(X.ps_sh[k], (int)ceil(FB_PS_TH * J.sy) + 2 * (X.ksize[k] / 2) + 4);
             }
-            max_tiles_um[k] = std::max(max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH));
-            if (BTW) max_tiles_bs[k] = std::max(max_tiles_bs[k], tiles(BTW, BTH));
-            if (bs_m7) {
-                max_tiles_bss[k] = std::max(max_tiles_bss[k], tiles(FB_BS7S_TW, FB_BS7S_TH));
-                sum_tiles_bs[k] += tiles(BTW, BTH);
+            X.max_tiles_um[k] = std::max(X.max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH, rows));
+            if (X.BTW) X.max_tiles_bs[k] = std::max(X.max_tiles_bs[k], tiles(X.BTW, X.BTH, rows));
+            if (X.bs_m7) {
+                X.max_tiles_bss[k] = std::max(X.max_tiles_bss[k], tiles(FB_BS7S_TW, FB_BS7S_TH, rows));
+                X.sum_tiles_bs[k] += tiles(X.BTW, X.BTH, rows);
             }
         }
     }
-    NSOF_CUDA_TRY(cudaMemcpyAsync(ds, hs, table_bytes, cudaMemcpyHostToDevice, stream));
+    NSOF_CUDA_TRY(cudaMemcpyAsync(X.ds, hs, table_bytes, cudaMemcpyHostToDevice, stream));
     NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
     slot->pending = true;
 
-    PolyConst pc;
-    prepare_poly(params->poly_n, params->poly_sigma, &pc);
-    const int pn = params->poly_n;
-    const size_t pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
-    const float flow_mul = (float)(1. / params->pyr_scale);
-    const float bscale = (float)(1. / ((double)params->winsize * params->winsize));
+    prepare_poly(params->poly_n, params->poly_sigma, &X.pc);
+    X.pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
+    X.flow_mul = (float)(1. / params->pyr_scale);
+    X.bscale = (float)(1. / ((double)params->winsize * params->winsize));
+    X.valid = true;
+    return NSOF_OK;
+}
 
-    // S2-b + S2-c of level k on stream `st` (independent of the flow: needs the sources and the tables only)
-    auto launch_pyramid = [&](int k, cudaStream_t st) -> int {
-        const FbJob *jobs = (const FbJob *)(ds + job_off[k]);
-        const float *gk = (const float *)ds + gk_off[k];
-        const int na = n_active[k];
-        cudaStream_t stream = st;  // the launches below name it `stream`
-        h->prof_level = k;
-        if (path_n[3 * k + 1])
-            NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * path_N0[3 * k + 1] + 40 * path_N[3 * k + 1], FB_PYR_POLYEXP_M0,
-                         max_tiles_pp[k], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
-        if (path_n[3 * k + 2])
-            NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * path_N0[3 * k + 2] + 40 * path_N[3 * k + 2], FB_PYR_POLYEXP_M1,
-                         max_tiles_pp[k], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
-        if (path_n[3 * k]) {
-            const size_t ps_smem = fb_ps_smem(ksize[k] / 2, ps_sw[k], ps_sh[k]);
-            if (ps_smem <= 100 * 1024)  // two CTAs per SM; larger windows (extreme ratios) take the direct kernel
-                NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * path_N0[3 * k], k_fb_pyr_sep, max_tiles_ps[k], na, 2, 256, ps_smem, stream, jobs,
-                             gk, ksize[k] / 2, ps_sw[k], ps_sh[k]);
-            else
-                NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * path_N0[3 * k], k_fb_pyr, max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk,
-                             ksize[k] / 2);
-            NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * path_N[3 * k], k_fb_polyexp, max_tiles_pe[k], na, 2, 256, pe_smem, stream,
-                         jobs, pc);
-        }
-        NSOF_CUDA_TRY(cudaGetLastError());
-        return NSOF_OK;
-    };
+// S2-b + S2-c of level k on `stream` (independent of the flow: needs the sources and the tables only)
+static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream)
+{
+    FbBatchCtx &X = *h->ctx;
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
+    const float *gk = (const float *)X.ds + X.gk_off[k];
+    const int na = X.n_active[k];
+    const PolyConst &pc = X.pc;
+    h->prof_level = k;
+    if (X.path_n[3 * k + 1])
+        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * k + 1] + 40 * X.path_N[3 * k + 1], FB_PYR_POLYEXP_M0,
+                     X.max_tiles_pp[k], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
+    if (X.path_n[3 * k + 2])
+        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * k + 2] + 40 * X.path_N[3 * k + 2], FB_PYR_POLYEXP_M1,
+                     X.max_tiles_pp[k], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
+    if (X.path_n[3 * k]) {
+        const int r = X.ksize[k] / 2;
+        const size_t ps_smem = fb_ps_smem(r, X.ps_sw[k], X.ps_sh[k]);
+        if (ps_smem <= 100 * 1024)  // two CTAs per SM; larger windows (extreme ratios) take the direct kernel
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * k], k_fb_pyr_sep, X.max_tiles_ps[k], na, 2, 256, ps_smem, stream, jobs,
+                         gk, r, X.ps_sw[k], X.ps_sh[k]);
+        else
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * k], k_fb_pyr, X.max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, r);
+        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * k], k_fb_polyexp, X.max_tiles_pe[k], na, 2, 256, X.pe_smem, stream,
+                     jobs, pc);
+    }
+    NSOF_CUDA_TRY(cudaGetLastError());
+    h->prof_level = -1;
+    return NSOF_OK;
+}
+
+// S2-f + first S2-d of level k (or the flow initialisation of a level with zero iterations)
+static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream)
+{
+    FbBatchCtx &X = *h->ctx;
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
+    const int na = X.n_active[k];
+    h->prof_level = k;
+    if (X.params.iterations == 0)
+        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[k] + 8 * X.sumN[k], k_fb_flow_init, X.max_tiles_um[k], na, 1, 256, 0, stream,
+                     jobs, X.flow_mul);
+    else
+        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[k] + 8 * X.sumNc[k], k_fb_um_first, X.max_tiles_um[k], na, 1, 256, 0, stream,
+                     jobs, X.flow_mul);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    h->prof_level = -1;
+    return NSOF_OK;
+}
+
+// iteration `it` of S2-e on level k: blur + solve, then UpdateMatrices (it < iters - 1) or the flow write
+static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t stream)
+{
+    FbBatchCtx &X = *h->ctx;
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
+    const int na = X.n_active[k];
+    const bool last = it == iters - 1;
+    const double Nk = X.sumN[k];
+    h->prof_level = k;
+    // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the
+    // 32x16 tile (4x the CTAs, each a quarter of the serial work)
+    if (X.bs_m7 && X.sum_tiles_bs[k] < 2 * 148 * 3 && !h->dbg_big_tiles)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, X.max_tiles_bss[k], na, 1,
+                     FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, X.bscale, (it & 1) == 0, last);
+    else if (X.bs_m7)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, X.max_tiles_bs[k], na, 1,
+                     FB_BS7_NT, X.bs_smem, stream, jobs, X.bscale, (it & 1) == 0, last);
+    else
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[k], na, 1,
+                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    h->prof_level = -1;
+    return NSOF_OK;
+}
+
+static int fb_check_batch_args(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: NULL handle");
+    if (n < 0 || (n > 0 && !items)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: bad item list");
+    int rc = validate_params(params);
+    if (rc) return rc;
+    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: at most 65535 items per batch");
+    return NSOF_OK;
+}
+
+extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params,
+                                    void *cuda_stream)
+{
+    int rc = fb_check_batch_args(h, items, n, params);
+    if (rc) return rc;
+    if (n == 0) return NSOF_OK;
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    rc = fb_prepare(h, items, n, params, nullptr, stream);
+    if (rc) return rc;
+    FbBatchCtx &X = *h->ctx;
+    const int max_scales = X.max_scales, stop_level = X.stop_level;
+
     // fork: every level but the coarsest builds its R0, R1 on an internal stream while the caller's stream iterates
     // on the coarser levels (small, latency-bound launches); joined per level by an event before its first
     // UpdateMatrices.  Serial when profiling (one event pair per launch must not overlap another).
@@ -605,12 +736,12 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
             h->ev_level.push_back(e);
         }
         NSOF_CUDA_TRY(cudaEventRecord(h->ev_fork, stream));  // tables uploaded, previous batch's readers of R done
-        rc = launch_pyramid(top, stream);
+        rc = fb_launch_pyramid(h, top, stream);
         if (rc) return rc;
         for (int k = top - 1; k >= stop_level; k--) {
             cudaStream_t a = h->aux[k & 1];
             NSOF_CUDA_TRY(cudaStreamWaitEvent(a, h->ev_fork, 0));
-            rc = launch_pyramid(k, a);
+            rc = fb_launch_pyramid(h, k, a);
             if (rc) return rc;
             NSOF_CUDA_TRY(cudaEventRecord(h->ev_level[k], a));
         }
@@ -618,47 +749,120 @@ extern "C" int nsof_farneback_batch(nsof_handle *h, const nsof_crop_desc *items,
 
     // ---- level loop, coarse to fine (A.1)
     for (int k = max_scales - 1; k >= stop_level; k--) {
-        const FbJob *jobs = (const FbJob *)(ds + job_off[k]);
-        const int na = n_active[k];
         int iters = params->iterations;
         if (k == stop_level && h->dbg_level >= 0 && h->dbg_iters >= 0) iters = std::min(iters, h->dbg_iters);
-        // algorithmic bytes per launch: the per-level terms of nsof_fb_algorithmic_bytes, summed over the batch;
-        // items that have no level k keep the coarse-flow term at zero via sumN of the items that do
-        double Nc = 0.;
-        for (int i = 0; i < n; i++)
-            if (plan[i].scales > k + 1) Nc += (double)plan[i].hk[k + 1] * plan[i].wk[k + 1];
-        const double Nk = sumN[k];
         if (!fork) {
-            rc = launch_pyramid(k, stream);
+            rc = fb_launch_pyramid(h, k, stream);
             if (rc) return rc;
         } else if (k < top) {
             NSOF_CUDA_TRY(cudaStreamWaitEvent(stream, h->ev_level[k], 0));
         }
-        h->prof_level = k;
-        if (params->iterations == 0) {
-            NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * Nc + 8 * Nk, k_fb_flow_init, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
-                         flow_mul);
-        } else {
-            NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * Nk + 8 * Nc, k_fb_um_first, max_tiles_um[k], na, 1, 256, 0, stream, jobs,
-                         flow_mul);
+        rc = fb_launch_um_first(h, k, stream);
+        if (rc) return rc;
+        if (params->iterations > 0)
             for (int it = 0; it < iters; it++) {
-                const bool last = it == iters - 1;
-                // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the
-                // 32x16 tile (4x the CTAs, each a quarter of the serial work)
-                if (bs_m7 && sum_tiles_bs[k] < 2 * 148 * 3 && !h->dbg_big_tiles)
-                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S,
-                                 max_tiles_bss[k], na, 1, FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, bscale, (it & 1) == 0, last);
-                else if (bs_m7)
-                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7,
-                                 max_tiles_bs[k], na, 1, FB_BS7_NT, bs_smem, stream, jobs, bscale, (it & 1) == 0, last);
-                else
-                    NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve,
-                                 max_tiles_bs[k], na, 1, 256, bs_smem, stream, jobs, BTW, BTH, m, bscale, (it & 1) == 0, last);
+                rc = fb_launch_blur(h, k, it, iters, stream);
+                if (rc) return rc;
             }
-        }
-        NSOF_CUDA_TRY(cudaGetLastError());
     }
-    h->prof_level = -1;
+    return NSOF_OK;
+}
+
+// ------------------------------------------------------------------------------ spatial tiling
+// One frame pair (or a batch of pairs) split by rows over `world` GPUs.  Every rank plans the WHOLE problem (full-size
+// workspace: addressing, borders and resize geometry stay those of the whole frame) but computes only its band of
+// rows of every level; rows a stencil or gather reads beyond the band are halo rows the caller exchanges between
+// the stage calls (NCCL send/recv between row neighbours, parallel.py).  Buffers are reported by nsof_fb_tiled_query.
+extern "C" int nsof_fb_tiled_begin(nsof_handle *h, const nsof_crop_desc *items, int n, const nsof_fb_params *params, int rank,
+                                   int world, int halo_r1, void *cuda_stream)
+{
+    int rc = fb_check_batch_args(h, items, n, params);
+    if (rc) return rc;
+    if (n < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_begin: no items");
+    if (world < 1 || rank < 0 || rank >= world || halo_r1 < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_begin: bad rank/world/halo");
+    if (params->iterations < 1) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_begin: iterations >= 1 required");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    rc = h->guard_buf.ensure(sizeof(int));
+    if (rc) return rc;
+    NSOF_CUDA_TRY(cudaMemsetAsync(h->guard_buf.p, 0, sizeof(int), stream));
+    FbTiling t = {rank, world, halo_r1, (int *)h->guard_buf.p};
+    rc = fb_prepare(h, items, n, params, &t, stream);
+    if (rc) return rc;
+    // every item must have every level, with a band of at least the blur radius on every rank
+    const std::vector<FbItemPlan> &plan = *h->last_plan;
+    for (int i = 0; i < n; i++) {
+        if (plan[i].scales != h->ctx->max_scales) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_begin: items must share the level count");
+        const int hk = plan[i].hk[plan[i].scales - 1];
+        if (hk / world < params->winsize / 2 + 1 || hk / world < halo_r1)
+            NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_begin: the coarsest level (%d rows) is too small for %d ranks", hk, world);
+    }
+    return NSOF_OK;
+}
+
+extern "C" int nsof_fb_tiled_levels(const nsof_handle *h)
+{
+    return (h && h->ctx && h->ctx->valid && h->ctx->tiled) ? h->ctx->max_scales : 0;
+}
+
+// stage: 0 pyramid + PolyExp, 1 first UpdateMatrices, 2 blur + solve iteration `it`
+extern "C" int nsof_fb_tiled_stage(nsof_handle *h, int level, int stage, int it, void *cuda_stream)
+{
+    if (!h || !h->ctx || !h->ctx->valid || !h->ctx->tiled) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: no tiled batch (call nsof_fb_tiled_begin)");
+    FbBatchCtx &X = *h->ctx;
+    if (level < 0 || level >= X.max_scales) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: level %d", level);
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    switch (stage) {
+    case 0: return fb_launch_pyramid(h, level, stream);
+    case 1: return fb_launch_um_first(h, level, stream);
+    case 2:
+        if (it < 0 || it >= X.params.iterations) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: iteration %d", it);
+        return fb_launch_blur(h, level, it, X.params.iterations, stream);
+    default: NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: stage %d", stage);
+    }
+}
+
+// Buffer `what` of item `item` on `level`: 0 R1 (5 planes), 1 Ma, 2 Mb (5 planes), 3 the level's flow (float2 rows).
+// M written by UpdateMatrices number u of a level (u = 0 first, then one per non-last iteration) is Ma for even u.
+extern "C" int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what, nsof_tiled_buf *out)
+{
+    if (!h || !out || !h->ctx || !h->ctx->valid || !h->ctx->tiled) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_query: no tiled batch");
+    FbBatchCtx &X = *h->ctx;
+    const std::vector<FbItemPlan> &plan = *h->last_plan;
+    if (item < 0 || item >= X.n || level < 0 || level >= X.max_scales) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_query: item/level");
+    const FbItemPlan &pl = plan[item];
+    float *base = (float *)h->arena.p;
+    const size_t planef = (size_t)pl.pitch[level] * pl.hk[level];
+    memset(out, 0, sizeof(*out));
+    out->h = pl.hk[level];
+    out->w = pl.wk[level];
+    band_rows(out->h, X.tiling.rank, X.tiling.world, &out->y_lo, &out->y_hi);
+    switch (what) {
+    case 0: out->ptr = base + pl.off_R[level] + 5 * planef; out->planes = 5; out->row_floats = pl.pitch[level]; out->plane_floats = planef; break;
+    case 1: out->ptr = base + pl.off_Ma; out->planes = 5; out->row_floats = pl.pitch[level]; out->plane_floats = planef; break;
+    case 2: out->ptr = base + pl.off_Mb; out->planes = 5; out->row_floats = pl.pitch[level]; out->plane_floats = planef; break;
+    case 3:
+        out->planes = 1;
+        if (level == 0) { out->ptr = pl.d.flow; out->row_floats = (size_t)(pl.d.flow_pitch / 4); }
+        else { out->ptr = (level & 1) ? base + pl.off_fA : base + pl.off_fB; out->row_floats = 2 * (size_t)pl.pitch[level]; }
+        out->plane_floats = out->row_floats * out->h;
+        break;
+    default: NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_query: what=%d", what);
+    }
+    return NSOF_OK;
+}
+
+// 1 when an UpdateMatrices gather of the tiled batch reached R1 rows outside the received halo (the result is then
+// invalid: rerun with a larger halo_r1).  Synchronises the stream.
+extern "C" int nsof_fb_tiled_guard(nsof_handle *h, int *tripped, void *cuda_stream)
+{
+    if (!h || !tripped || !h->guard_buf.p) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_guard: no tiled batch");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    int v = 0;
+    NSOF_CUDA_TRY(cudaMemcpyAsync(&v, h->guard_buf.p, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    NSOF_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+    *tripped = v;
     return NSOF_OK;
 }
 

@@ -36,6 +36,13 @@ struct FbJob {
     int fpitch;            // pitch of `flow`, float2 units
     int resize_mode;       // 0 identity, 1 exact 2x (2x2 mean), 2 bilinear
     int fast;              // 0: generic k_fb_pyr + k_fb_polyexp; 1 / 2: fused k_fb_pyr_polyexp_t<MODE 0 / 1>
+    // Row window (spatial tiling across GPUs, nsof_fb_tiled_*): the kernels compute rows [y_lo, y_hi) of this level
+    // (the generic pyramid kernels rows [iy_lo, iy_hi) of I) but keep addressing, borders and resize geometry of
+    // the whole h x w level; rows outside the window are read where a stencil / gather reaches them (exchanged
+    // halo rows).  Untiled: [0, h).
+    int y_lo, y_hi, iy_lo, iy_hi;
+    int gy_lo, gy_hi;      // rows of R1 that are valid on this rank (own + received halo); checked when guard != 0
+    int *guard;            // device flag set when an UpdateMatrices gather leaves [gy_lo, gy_hi) (NULL: unchecked)
     double sx, sy;         // src/dst ratio of the pyramid resize
     double fsx, fsy;       // coarse/this ratio of the flow upsample
     const uint8_t *src0, *src1;
@@ -103,16 +110,16 @@ NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT
 {
     const FbJob J = jobs[NSOF_BY];
     if (J.fast) return;
-    const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW, tiles_y = (J.h + FB_PYR_TH - 1) / FB_PYR_TH;
+    const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW, tiles_y = (J.iy_hi - J.iy_lo + FB_PYR_TH - 1) / FB_PYR_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_PYR_TW, ty0 = (NSOF_BX / tiles_x) * FB_PYR_TH;
+    const int tx0 = (NSOF_BX % tiles_x) * FB_PYR_TW, ty0 = J.iy_lo + (NSOF_BX / tiles_x) * FB_PYR_TH;
     for (int i = NSOF_TID; i < FB_PYR_TW * FB_PYR_TH; i += NSOF_NT) {
         const int x = tx0 + i % FB_PYR_TW, y = ty0 + i / FB_PYR_TW;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.iy_hi) continue;
         float v;
         if (J.resize_mode == 0) {
             v = fb_blur_at(src, sp, J.sh, J.sw, x, y, gk, r);
@@ -151,13 +158,13 @@ NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, PolyConst pc)
 {
     const FbJob J = jobs[NSOF_BY];
     if (J.fast) return;
-    const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW, tiles_y = (J.h + FB_PE_TH - 1) / FB_PE_TH;
+    const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW, tiles_y = (J.y_hi - J.y_lo + FB_PE_TH - 1) / FB_PE_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *I = J.I + img * plane;
     float *R = J.R + (size_t)img * 5 * plane;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_PE_TW, ty0 = (NSOF_BX / tiles_x) * FB_PE_TH;
+    const int tx0 = (NSOF_BX % tiles_x) * FB_PE_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_PE_TH;
     const int n = pc.n, IW = FB_PE_TW + 2 * n, IH = FB_PE_TH + 2 * n;
     NSOF_DYN_SMEM(smem_raw);
     float *sI = (float *)smem_raw;
@@ -189,7 +196,7 @@ NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, PolyConst pc)
     for (int i = NSOF_TID; i < FB_PE_TW * FB_PE_TH; i += NSOF_NT) {
         const int lx = i % FB_PE_TW, ly = i / FB_PE_TW;
         const int x = tx0 + lx, y = ty0 + ly;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         const float *q0 = sr + ly * IW + lx + n, *q1 = q0 + SRP, *q2 = q1 + SRP;
         const float g0 = pc.g[0];
         float b1 = q0[0] * g0, b2 = 0.f, b3 = q1[0] * g0, b4 = 0.f, b5 = q2[0] * g0, b6 = 0.f;
@@ -272,6 +279,13 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
 #define FB_UM_TW 128
 #define FB_UM_TH 8
 
+// tiled runs: flag a gather that reaches R1 rows this rank neither owns nor received
+NSOF_DEV void fb_um_guard(const FbJob &J, int y, float dy)
+{
+    const int y1 = (int)floorf((float)y + dy);
+    if ((unsigned)y1 < (unsigned)(J.h - 1) && (y1 < J.gy_lo || y1 + 1 >= J.gy_hi)) *J.guard = 1;
+}
+
 NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 {
     int x0, x1, y0, y1;
@@ -289,14 +303,14 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.h + FB_UM_TH - 1) / FB_UM_TH;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const size_t plane = (size_t)J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = (NSOF_BX / tiles_x) * FB_UM_TH;
+    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;
     constexpr int GW = FB_UM_TW / 4;
     for (int i = NSOF_TID; i < GW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + (i % GW) * 4, y = ty0 + i / GW;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         const size_t o = (size_t)y * J.pitch + x;
         float r0[5][4];
 #pragma unroll
@@ -313,6 +327,7 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
                 if (J.ch > 0) d = fb_upsampled_flow(J, x + q, y, flow_mul);
 #pragma unroll
                 for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
+                if (J.guard) fb_um_guard(J, y, d.y);
                 fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, d.x, d.y, r0v, mm);
             } else {
 #pragma unroll
@@ -331,12 +346,12 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 NSOF_GLOBAL k_fb_flow_init(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.h + FB_UM_TH - 1) / FB_UM_TH;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = (NSOF_BX / tiles_x) * FB_UM_TH;
+    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;
     for (int i = NSOF_TID; i < FB_UM_TW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + i % FB_UM_TW, y = ty0 + i / FB_UM_TW;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         float dx = 0.f, dy = 0.f;
         if (J.ch > 0) {
             int x0, x1, y0, y1;
@@ -368,12 +383,12 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
                             int last)
 {
     const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *Min = src_is_a ? J.Ma : J.Mb;
     float *Mout = src_is_a ? J.Mb : J.Ma;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
     const int LW = TW + 2 * m, LH = TH + 2 * m, PW = (LW + 3) & ~3;
     const int SP = LH * PW;  // smem plane
     NSOF_DYN_SMEM(smem_raw);
@@ -400,7 +415,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
     for (int i = NSOF_TID; i < gw * TH; i += NSOF_NT) {
         const int lx = (i % gw) * 4, ly = i / gw;
         const int x = tx0 + lx, y = ty0 + ly;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         float s[5][4];
         for (int c = 0; c < 5; c++) {
             const float *v = sM + c * SP + ly * PW + lx;
@@ -432,6 +447,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
                 float r0v[5], mm[5];
                 if (x + q < J.w) {
                     for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(J.R + c * plane + o + q);
+                    if (J.guard) fb_um_guard(J, y, fyv[q]);
                     fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, fxv[q], fyv[q], r0v, mm);
                 } else {
                     for (int c = 0; c < 5; c++) mm[c] = 0.f;
@@ -472,12 +488,12 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     static_assert(5 * RPP >= TH, "the flow tile must fit the dead halo rows");
     static_assert((TH * PW) % 4 == 0 && (2 * TW) % 4 == 0, "flow rows must stay 16-byte aligned");
     const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *Min = src_is_a ? J.Ma : J.Mb;
     float *Mout = src_is_a ? J.Mb : J.Ma;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
     float *sM = (float *)(smem_raw + 16);
@@ -563,7 +579,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
         const int lx = (i % GW) * 4, ly = i / GW;
         const int x = tx0 + lx, y = ty0 + ly;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         float s[5][4];
 #pragma unroll
         for (int c = 0; c < 5; c++) {
@@ -613,12 +629,13 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     for (int i = NSOF_TID; i < TW * TH; i += NSOF_NT) {
         const int lx = i % TW, ly = i / TW;
         const int x = tx0 + lx, y = ty0 + ly;
-        if (x >= J.w || y >= J.h) continue;
+        if (x >= J.w || y >= J.y_hi) continue;
         const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
         const size_t o = (size_t)y * J.pitch + x;
         float r0v[5], mm[5];
 #pragma unroll
         for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(R0 + c * plane + o);
+        if (J.guard) fb_um_guard(J, y, f.y);
         fb_um_pixel(R1, plane, J.pitch, J.h, J.w, x, y, f.x, f.y, r0v, mm);
 #pragma unroll
         for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c];
@@ -660,14 +677,14 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_REST
     static_assert(A_BYTES % 16 == 0 && B_BYTES % 16 == 0, "shared regions must stay 16-byte aligned");
     const FbJob J = jobs[NSOF_BY];
     if (J.fast != MODE + 1) return;
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     const size_t plane = (size_t)J.pitch * J.h;
     float *R = J.R + (size_t)img * 5 * plane;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
     float *sS = (float *)(smem_raw + 16);                 // phases A2/B
@@ -812,7 +829,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_REST
         for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
             const int lx = (i % GW) * 4, ly = i / GW;
             const int x = tx0 + lx, y = ty0 + ly;
-            if (x >= J.w || y >= J.h) continue;
+            if (x >= J.w || y >= J.y_hi) continue;
             float q[3][NV * 4];
 #pragma unroll
             for (int p = 0; p < 3; p++) {
@@ -890,14 +907,14 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
     constexpr int TW = FB_PS_TW, TH = FB_PS_TH;
     const FbJob J = jobs[NSOF_BY];
     if (J.fast) return;
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.h + TH - 1) / TH;
+    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.iy_hi - J.iy_lo + TH - 1) / TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = (NSOF_BX / tiles_x) * TH;
-    const int twn = nsof_imin(TW, J.w - tx0), thn = nsof_imin(TH, J.h - ty0);
+    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.iy_lo + (NSOF_BX / tiles_x) * TH;
+    const int twn = nsof_imin(TW, J.w - tx0), thn = nsof_imin(TH, J.iy_hi - ty0);
     const int SWp = (SWmax + 32 + 15) & ~15;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;

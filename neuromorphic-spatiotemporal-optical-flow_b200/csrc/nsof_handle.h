@@ -45,6 +45,7 @@ struct NsofStageSlot {
 };
 
 struct FbItemPlan;  // farneback.cu
+struct FbBatchCtx;  // farneback.cu
 
 // Kernel classes for the launch counter and the optional per-launch event timing (nsof_profile*).
 enum NsofKernelClass {
@@ -65,6 +66,8 @@ struct nsof_handle {
     NsofDevBuf arena;      // I, R, M, coarse flow of every item of the current batch
     NsofDevBuf tables;     // job tables + Gaussian taps on the device
     NsofDevBuf clear_tab;  // rectangle table of nsof_flow_clear
+    NsofDevBuf guard_buf;  // halo guard flag of a tiled batch
+    FbBatchCtx *ctx = nullptr;  // plan, tables and launch geometry of the current batch
     NsofDevBuf io;         // device staging of the *_host entry points (crops in, flow out)
     NsofDevBuf s1;         // stage-1 scratch
     NsofDevBuf lz;         // Lanczos-3 weight/index tables (device), cached for lz_key

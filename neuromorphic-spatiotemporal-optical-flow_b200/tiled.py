@@ -1,0 +1,146 @@
+"""Spatially tiled Farneback: one frame pair (or a batch of pairs) split by ROWS over the GPUs of one box
+(BASELINE.json configs[4]: 8K frames, NCCL halo-row exchange per pyramid level).
+
+The reference has no multi-GPU path (its Farneback is cv2's single-threaded CPU code, optical_flow_seg.py:494);
+this is the B200 design for frames too large to be worth one GPU each.  One process per GPU.  Every rank plans the
+WHOLE frame (full-size workspace, so addressing, image borders and resize geometry are those of the whole frame)
+but computes only its band of rows of every pyramid level (`nsof_fb_tiled_*`, include/nsof.h).  What a stencil or
+a gather reads beyond the band arrives from the row neighbours, in place, between the stages:
+
+    per level, coarse to fine                                      rows per neighbour      bytes at 8K level 0
+      pyramid + PolyExp of the band (local: the source frames are read with their own overlap)
+      R1 halo                      <- UpdateMatrices gathers at y + dy    halo_r1 (32) x 5 planes    4.9 MB
+      coarse flow halo             <- bilinear flow upsampling            4 rows x float2
+      first UpdateMatrices
+      M halo                       <- 15 x 15 box window                  winsize/2 (7) x 5 planes   1.1 MB
+      iterations x [blur + solve + UpdateMatrices ; M halo]
+
+Messages are contiguous row blocks of the planar buffers: no packing kernels.  They go through
+torch.distributed point-to-point operations (NCCL send/recv over NVLink between row neighbours; gloo in the CPU
+tests, where the same driver runs on the block-emulator build of the kernels).  The result is bit-identical to the
+single-GPU result: per-pixel arithmetic does not depend on the tile decomposition.
+
+A displacement larger than `halo_r1` rows at some level would gather rows that were never received; the kernels
+flag that (nsof_fb_tiled_guard) and `run` raises instead of returning a wrong field.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._lib import CropDesc, TiledBuf
+from .engine import FARNEBACK_PARAMS, Engine, _fb_params
+
+WHAT_R1, WHAT_MA, WHAT_MB, WHAT_FLOW = 0, 1, 2, 3
+FLOW_HALO_ROWS = 4
+
+
+def band_rows(h: int, rank: int, world: int):
+    """Rows [lo, hi) of a level of height h owned by `rank` (the same split the library uses)."""
+    return rank * h // world, (rank + 1) * h // world
+
+
+class _DevArray:
+    """float32 view of foreign device memory for torch.as_tensor (CUDA array interface v2)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class TiledFarneback:
+    def __init__(self, engine: Engine, rank: int, world: int, halo_r1: int = 32, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.eng, self.lib, self.h = engine, engine.lib, engine.handle
+        self.rank, self.world, self.halo_r1 = int(rank), int(world), int(halo_r1)
+        self.group = group
+        self.emulated = bool(getattr(engine, "_emulated", False))
+        self.messages = 0       # point-to-point operations of the last run (sends + receives of this rank)
+        self.bytes_sent = 0
+
+    # ---- plumbing ----------------------------------------------------------------------------------------
+    def _stream(self):
+        if self.emulated:
+            return C.c_void_p(0)
+        return C.c_void_p(self.torch.cuda.current_stream(self.eng.device).cuda_stream)
+
+    def _tensor(self, ptr: int, n: int):
+        if self.emulated:
+            return self.torch.from_numpy(np.ctypeslib.as_array((C.c_float * n).from_address(ptr)))
+        return self.torch.as_tensor(_DevArray(ptr, n), device=f"cuda:{self.eng.device}")
+
+    def _query(self, item, level, what) -> TiledBuf:
+        b = TiledBuf()
+        self.lib.check(self.lib.nsof_fb_tiled_query(self.h, item, level, what, C.byref(b)), "fb_tiled_query")
+        return b
+
+    def _exchange(self, n_items, level, what, rows):
+        """Send the first / last `rows` rows of the band to the upper / lower neighbour, receive theirs into the
+        rows just outside the band.  One grouped call for all items and planes."""
+        if self.world == 1:
+            return
+        dist = self.dist
+        ops = []
+        for item in range(n_items):
+            b = self._query(item, level, what)
+            r = min(rows, b.y_hi - b.y_lo)
+            for p in range(b.planes):
+                base = b.ptr + 4 * p * b.plane_floats
+                blk = lambda y0, y1: self._tensor(base + 4 * y0 * b.row_floats, (y1 - y0) * b.row_floats)
+                if self.rank > 0:
+                    ops.append(dist.P2POp(dist.isend, blk(b.y_lo, b.y_lo + r), self.rank - 1, self.group))
+                    ops.append(dist.P2POp(dist.irecv, blk(b.y_lo - r, b.y_lo), self.rank - 1, self.group))
+                    self.bytes_sent += 4 * r * b.row_floats
+                if self.rank < self.world - 1:
+                    ops.append(dist.P2POp(dist.isend, blk(b.y_hi - r, b.y_hi), self.rank + 1, self.group))
+                    ops.append(dist.P2POp(dist.irecv, blk(b.y_hi, b.y_hi + r), self.rank + 1, self.group))
+                    self.bytes_sent += 4 * r * b.row_floats
+        self.messages += len(ops)
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+    # ---- the level loop of FarnebackOpticalFlowImpl::calc, stage by stage -----------------------------------
+    def run(self, crops, **farneback_params):
+        """`crops`: list of (prev_ptr, next_ptr, h, w, prev_pitch, next_pitch, flow_ptr, flow_pitch) with raw
+        device addresses of FULL frames (all pairs the same size).  On return (asynchronous on the current
+        stream, apart from the guard check) rows band_rows(h, rank, world) of every flow buffer hold this rank's
+        share of the flow."""
+        kw = dict(FARNEBACK_PARAMS)
+        kw.update(farneback_params)
+        fb = _fb_params(**kw)
+        n = len(crops)
+        descs = (CropDesc * max(n, 1))()
+        for i, c in enumerate(crops):
+            descs[i] = CropDesc(*c)
+        lib, h, st = self.lib, self.h, self._stream()
+        self.messages = self.bytes_sent = 0
+        lib.check(lib.nsof_fb_tiled_begin(h, descs, n, C.byref(fb), self.rank, self.world, self.halo_r1, st),
+                  "fb_tiled_begin")
+        levels = lib.nsof_fb_tiled_levels(h)
+        m, T = kw["winsize"] // 2, kw["iterations"]
+        stage = lambda k, s, it=0: lib.check(lib.nsof_fb_tiled_stage(h, k, s, it, st), "fb_tiled_stage")
+        for k in range(levels - 1, -1, -1):
+            stage(k, 0)
+            self._exchange(n, k, WHAT_R1, self.halo_r1)
+            if k < levels - 1:
+                self._exchange(n, k + 1, WHAT_FLOW, FLOW_HALO_ROWS)
+            stage(k, 1)
+            self._exchange(n, k, WHAT_MA, m)
+            for it in range(T):
+                stage(k, 2, it)
+                if it < T - 1:
+                    self._exchange(n, k, WHAT_MB if it % 2 == 0 else WHAT_MA, m)
+        tripped = C.c_int(0)
+        lib.check(lib.nsof_fb_tiled_guard(h, C.byref(tripped), st), "fb_tiled_guard")
+        flag = int(tripped.value)
+        if self.world > 1:  # every rank must reach the same verdict
+            t = self.torch.tensor([flag], dtype=self.torch.int32,
+                                  device="cpu" if self.emulated else f"cuda:{self.eng.device}")
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+            flag = int(t.item())
+        if flag:
+            raise RuntimeError(f"tiled Farneback: a displacement exceeded the R1 halo of {self.halo_r1} rows on some "
+                               f"rank; rerun with a larger halo_r1")
+        return levels

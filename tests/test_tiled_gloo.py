@@ -1,0 +1,80 @@
+"""Spatial tiling (BASELINE.json configs[4]) on CPU: 2 and 3 gloo ranks run the row-tiled Farneback driver
+(tiled.py + nsof_fb_tiled_*) over the block-emulator build of the kernels, exchange halo rows, and together reproduce
+the untiled result bit for bit."""
+import importlib
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import helpers  # noqa: E402
+
+H, W = 384, 328
+PARAMS = dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _pairs():
+    return [helpers.textured_pair(7, H, W, dx=2.5, dy=-3.0), helpers.textured_pair(8, H, W, dx=-1.0, dy=4.5)]
+
+
+def _worker(rank, world, port, out_dir, halo):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    nsof = importlib.import_module("nsof_b200")
+    tiled = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.tiled")
+    par = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.parallel")
+    par.init("gloo")
+    eng = nsof.Engine(0, lib=nsof.Library(helpers.build_emu()), _emulated=True)
+    pairs = _pairs()
+    flows = [np.full((H, W, 2), np.nan, dtype=np.float32) for _ in pairs]
+    crops = [(a.ctypes.data, b.ctypes.data, H, W, a.strides[0], b.strides[0], f.ctypes.data, f.strides[0])
+             for (a, b), f in zip(pairs, flows)]
+    tf = tiled.TiledFarneback(eng, rank, world, halo_r1=halo)
+    status = "ok"
+    try:
+        tf.run(crops, **PARAMS)
+    except RuntimeError as e:
+        status = "guard" if "halo" in str(e) else "error: " + str(e)
+    lo, hi = tiled.band_rows(H, rank, world)
+    np.savez(os.path.join(out_dir, f"r{rank}.npz"), lo=lo, hi=hi, status=status, messages=tf.messages,
+             **{f"flow{i}": f for i, f in enumerate(flows)})
+    torch.distributed.destroy_process_group()
+    eng.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_tiled_ranks_reproduce_the_untiled_flow(tmp_path, emu_engine, world):
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), 12), nprocs=world, join=True)
+    want = [emu_engine.calcOpticalFlowFarneback(a, b, None, **PARAMS) for a, b in _pairs()]
+    covered = 0
+    for r in range(world):
+        z = np.load(tmp_path / f"r{r}.npz")
+        assert str(z["status"]) == "ok"
+        lo, hi = int(z["lo"]), int(z["hi"])
+        covered += hi - lo
+        for i, wnt in enumerate(want):
+            got = z[f"flow{i}"]
+            assert np.array_equal(got[lo:hi], wnt[lo:hi]), (world, r, i, np.abs(got[lo:hi] - wnt[lo:hi]).max())
+            outside = np.ones(H, bool)
+            outside[lo:hi] = False
+            assert np.isnan(got[outside]).all()  # a rank writes its band only
+        assert int(z["messages"]) > 0
+    assert covered == H
+
+
+def test_tiled_guard_trips_when_the_halo_is_too_small(tmp_path):
+    """dy = 4.5 px at full resolution needs R1 rows the 1-row halo does not bring: every rank must raise."""
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), 1), nprocs=2, join=True)
+    for r in range(2):
+        assert str(np.load(tmp_path / f"r{r}.npz")["status"]) == "guard"
