@@ -154,6 +154,15 @@ NSOF_API int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what, 
  * a larger halo_r1).  Synchronises the stream. */
 NSOF_API int nsof_fb_tiled_guard(nsof_handle *h, int *tripped, void *cuda_stream);
 
+/* Device-to-device copy of `n` byte blocks in ONE launch (halo rows <-> contiguous message buffers of the tiled
+ * path: one NCCL message per neighbour instead of one per plane and pair). */
+typedef struct nsof_copy_block {
+    void *dst;
+    const void *src;
+    size_t bytes;
+} nsof_copy_block;
+NSOF_API int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, int n, void *cuda_stream);
+
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
 NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,

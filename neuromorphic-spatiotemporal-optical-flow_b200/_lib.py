@@ -62,6 +62,10 @@ class TiledBuf(C.Structure):
                 ("h", C.c_int), ("w", C.c_int), ("y_lo", C.c_int), ("y_hi", C.c_int)]
 
 
+class CopyBlock(C.Structure):
+    _fields_ = [("dst", C.c_void_p), ("src", C.c_void_p), ("bytes", C.c_size_t)]
+
+
 class KernelStat(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("launches", C.c_int), ("ms", C.c_double), ("algorithmic_bytes", C.c_double)]
 
@@ -93,6 +97,7 @@ _SIGNATURES = {
     "nsof_fb_tiled_stage": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "nsof_fb_tiled_query": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _P(TiledBuf)]),
     "nsof_fb_tiled_guard": (C.c_int, [C.c_void_p, _P(C.c_int), C.c_void_p]),
+    "nsof_copy_blocks": (C.c_int, [C.c_void_p, _P(CopyBlock), C.c_int, C.c_void_p]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),

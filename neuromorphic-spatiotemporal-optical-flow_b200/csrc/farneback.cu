@@ -131,7 +131,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 // ------------------------------------------------------------------------------ launch accounting
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
-    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear"};
+    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 
@@ -984,6 +984,53 @@ extern "C" int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int 
     slot->pending = true;
     NSOF_KLAUNCH(h, NSOF_K_FLOW_CLEAR, 8 * px, k_fb_flow_clear, std::min((max_h + 7) / 8, 64), n, 1, 256, 0, stream,
                  (const FbClearJob *)h->clear_tab.p);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+// grid (chunks, blocks): every block of bytes is copied by up to 64 CTAs, 16 bytes per thread where aligned
+NSOF_GLOBAL k_copy_blocks(const nsof_copy_block *NSOF_RESTRICT blocks)
+{
+    const nsof_copy_block B = blocks[NSOF_BY];
+    const size_t stride = (size_t)nsof_grid_x() * NSOF_NT;
+    if ((((uintptr_t)B.dst | (uintptr_t)B.src | B.bytes) & 15) == 0) {
+        const float4 *s4 = (const float4 *)B.src;
+        float4 *d4 = (float4 *)B.dst;
+        for (size_t i = (size_t)NSOF_BX * NSOF_NT + NSOF_TID; i < B.bytes / 16; i += stride) d4[i] = s4[i];
+    } else {
+        const unsigned char *s1 = (const unsigned char *)B.src;
+        unsigned char *d1 = (unsigned char *)B.dst;
+        for (size_t i = (size_t)NSOF_BX * NSOF_NT + NSOF_TID; i < B.bytes; i += stride) d1[i] = s1[i];
+    }
+}
+
+extern "C" int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, int n, void *cuda_stream)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_blocks: NULL handle");
+    if (n < 0 || (n > 0 && !blocks)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_blocks: bad block list");
+    if (n == 0) return NSOF_OK;
+    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "copy_blocks: at most 65535 blocks per call");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)n * sizeof(nsof_copy_block);
+    NsofStageSlot *slot;
+    int rc = nsof_stage_acquire(h, bytes, &slot);
+    if (rc) return rc;
+    rc = h->clear_tab.ensure(bytes);
+    if (rc) return rc;
+    size_t biggest = 0;
+    double total = 0.;
+    for (int i = 0; i < n; i++) {
+        if (!blocks[i].dst || !blocks[i].src) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_blocks: block %d has a NULL pointer", i);
+        biggest = std::max(biggest, blocks[i].bytes);
+        total += (double)blocks[i].bytes;
+    }
+    memcpy(slot->host, blocks, bytes);
+    NSOF_CUDA_TRY(cudaMemcpyAsync(h->clear_tab.p, slot->host, bytes, cudaMemcpyHostToDevice, stream));
+    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
+    slot->pending = true;
+    const int chunks = (int)std::min<size_t>(64, std::max<size_t>(1, biggest / (16 * 256 * 4)));
+    NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total, k_copy_blocks, chunks, n, 1, 256, 0, stream, (const nsof_copy_block *)h->clear_tab.p);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
 }

@@ -15,7 +15,8 @@ a gather reads beyond the band arrives from the row neighbours, in place, betwee
       M halo                       <- 15 x 15 box window                  winsize/2 (7) x 5 planes   1.1 MB
       iterations x [blur + solve + UpdateMatrices ; M halo]
 
-Messages are contiguous row blocks of the planar buffers: no packing kernels.  They go through
+The halo rows of all pairs and planes of one exchange travel as ONE message per neighbour (gathered and scattered
+by a copy kernel on either side: per-plane messages made the path latency-bound on operation count).  They go through
 torch.distributed point-to-point operations (NCCL send/recv over NVLink between row neighbours; gloo in the CPU
 tests, where the same driver runs on the block-emulator build of the kernels).  The result is bit-identical to the
 single-GPU result: per-pixel arithmetic does not depend on the tile decomposition.
@@ -29,7 +30,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import CropDesc, TiledBuf
+from ._lib import CopyBlock, CropDesc, TiledBuf
 from .engine import FARNEBACK_PARAMS, Engine, _fb_params
 
 WHAT_R1, WHAT_MA, WHAT_MB, WHAT_FLOW = 0, 1, 2, 3
@@ -59,6 +60,7 @@ class TiledFarneback:
         self.emulated = bool(getattr(engine, "_emulated", False))
         self.messages = 0       # point-to-point operations of the last run (sends + receives of this rank)
         self.bytes_sent = 0
+        self._ops: dict = {}    # (exchange, workspace layout) -> (operation list, bytes sent)
 
     # ---- plumbing ----------------------------------------------------------------------------------------
     def _stream(self):
@@ -78,28 +80,61 @@ class TiledFarneback:
 
     def _exchange(self, n_items, level, what, rows):
         """Send the first / last `rows` rows of the band to the upper / lower neighbour, receive theirs into the
-        rows just outside the band.  One grouped call for all items and planes."""
+        rows just outside the band.  The row blocks of all items and planes are gathered into ONE message per
+        neighbour by one copy kernel (nsof_copy_blocks), exchanged with a single grouped send/recv, and scattered
+        into the halo rows by a second copy kernel.  The plan of an exchange (block tables, message buffers,
+        operation list) is built once per workspace layout."""
         if self.world == 1:
             return
-        dist = self.dist
-        ops = []
-        for item in range(n_items):
-            b = self._query(item, level, what)
-            r = min(rows, b.y_hi - b.y_lo)
-            for p in range(b.planes):
-                base = b.ptr + 4 * p * b.plane_floats
-                blk = lambda y0, y1: self._tensor(base + 4 * y0 * b.row_floats, (y1 - y0) * b.row_floats)
-                if self.rank > 0:
-                    ops.append(dist.P2POp(dist.isend, blk(b.y_lo, b.y_lo + r), self.rank - 1, self.group))
-                    ops.append(dist.P2POp(dist.irecv, blk(b.y_lo - r, b.y_lo), self.rank - 1, self.group))
-                    self.bytes_sent += 4 * r * b.row_floats
-                if self.rank < self.world - 1:
-                    ops.append(dist.P2POp(dist.isend, blk(b.y_hi - r, b.y_hi), self.rank + 1, self.group))
-                    ops.append(dist.P2POp(dist.irecv, blk(b.y_hi, b.y_hi + r), self.rank + 1, self.group))
-                    self.bytes_sent += 4 * r * b.row_floats
-        self.messages += len(ops)
+        dist, torch = self.dist, self.torch
+        first = self._query(0, level, what)
+        key = (n_items, level, what, rows, first.ptr, first.h, first.w)
+        plan = self._ops.get(key)
+        if plan is None:
+            up, dn = self.rank > 0, self.rank < self.world - 1
+            per_dir = 0
+            blocks = []  # (band rows to send up, halo rows above, band rows to send down, halo rows below, bytes)
+            for item in range(n_items):
+                b = self._query(item, level, what)
+                r = min(rows, b.y_hi - b.y_lo)
+                nbytes = 4 * r * b.row_floats
+                for p in range(b.planes):
+                    row = lambda y: b.ptr + 4 * (p * b.plane_floats + y * b.row_floats)
+                    blocks.append((row(b.y_lo), row(b.y_lo - r), row(b.y_hi - r), row(b.y_hi), nbytes))
+                    per_dir += nbytes
+            mk = lambda: (np.zeros(per_dir // 4, dtype=np.float32) if self.emulated
+                          else torch.empty(per_dir // 4, dtype=torch.float32, device=f"cuda:{self.eng.device}"))
+            bufs = {k: mk() for k, use in (("su", up), ("ru", up), ("sd", dn), ("rd", dn)) if use}
+            addr = lambda t: t.ctypes.data if self.emulated else t.data_ptr()
+            as_t = lambda t: torch.from_numpy(t) if self.emulated else t
+            pack, unpack, off = [], [], 0
+            for s_up, h_up, s_dn, h_dn, nbytes in blocks:
+                if up:
+                    pack.append((addr(bufs["su"]) + off, s_up, nbytes))
+                    unpack.append((h_up, addr(bufs["ru"]) + off, nbytes))
+                if dn:
+                    pack.append((addr(bufs["sd"]) + off, s_dn, nbytes))
+                    unpack.append((h_dn, addr(bufs["rd"]) + off, nbytes))
+                off += nbytes
+            tab = lambda rows_: (CopyBlock * len(rows_))(*[CopyBlock(*r) for r in rows_])
+            ops = []
+            if up:
+                ops += [dist.P2POp(dist.isend, as_t(bufs["su"]), self.rank - 1, self.group),
+                        dist.P2POp(dist.irecv, as_t(bufs["ru"]), self.rank - 1, self.group)]
+            if dn:
+                ops += [dist.P2POp(dist.isend, as_t(bufs["sd"]), self.rank + 1, self.group),
+                        dist.P2POp(dist.irecv, as_t(bufs["rd"]), self.rank + 1, self.group)]
+            if len(self._ops) > 256:
+                self._ops.clear()
+            plan = self._ops[key] = (tab(pack), len(pack), tab(unpack), len(unpack), ops, per_dir * (int(up) + int(dn)), bufs)
+        pack, n_pack, unpack, n_unpack, ops, sent, _ = plan
+        st = self._stream()
+        self.lib.check(self.lib.nsof_copy_blocks(self.h, pack, n_pack, st), "copy_blocks (pack)")
         for req in dist.batch_isend_irecv(ops):
             req.wait()
+        self.lib.check(self.lib.nsof_copy_blocks(self.h, unpack, n_unpack, st), "copy_blocks (unpack)")
+        self.messages += len(ops)
+        self.bytes_sent += sent
 
     # ---- the level loop of FarnebackOpticalFlowImpl::calc, stage by stage -----------------------------------
     def run(self, crops, **farneback_params):
