@@ -49,7 +49,8 @@ if args.check:
     H, W = 1080, 1920
     frames = syn.make_clip(4321, H, W, 3, dev, velocity=(5.0, -4.0))  # same seed on every rank: the same frames
     flow = torch.full((2, H, W, 2), float("nan"), dtype=torch.float32, device=dev)
-    tf.run(crops_of(frames, flow), **P)
+    tfc = tiled.TiledFarneback(eng, rank, world, halo_r1=min(args.halo, (H // 8) // world))  # 135 coarsest rows
+    tfc.run(crops_of(frames, flow), **P)
     torch.cuda.synchronize()
     lo, hi = tiled.band_rows(H, rank, world)
     ref = torch.empty((2, H, W, 2), dtype=torch.float32, device=dev)
@@ -62,9 +63,9 @@ if args.check:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"# check 1080p x{world}: bands bit-identical to the untiled flow on every rank: {bool(ok.item())}; "
-              f"{tf.messages} p2p ops, {tf.bytes_sent / 1e6:.1f} MB sent by rank 0", flush=True)
+              f"{tfc.messages} p2p ops, {tfc.bytes_sent / 1e6:.1f} MB sent by rank 0", flush=True)
     assert ok.item() == 1
-    del frames, flow, ref
+    del frames, flow, ref, tfc
 
 H, W, NP = args.height, args.width, args.pairs
 frames = syn.make_clip(999, H, W, NP + 1, dev, velocity=(6.0, -3.0))
