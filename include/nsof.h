@@ -250,6 +250,18 @@ NSOF_API int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const int1
                                     const int64_t *slice_begin, int n_slices, int H, int W, int theta,
                                     float active_v, float silent_v, const nsof_synapse_params *p, double dt,
                                     float *w, void *cuda_stream);
+/* Scheme 2 of simulate() (eventsim/event_mem_sim.py:231-286): DC bias + event overlay with a per-pixel refractory
+ * period, for a run of `n_slices` consecutive time windows.  Per slice and array: V = bias_v; pixels with a matching
+ * event in the slice whose next_ok <= t[first event of the slice] get V = bias_v + active_v and
+ * next_ok = t[last event of the slice] + refractory_us (REFRACTORY_US = 800, :34); w = update_state(w, V).
+ * magnitude = 0 ('split'): ON events (pol == 1) drive (w_a, next_ok_a), OFF events (pol == 0) drive (w_b, next_ok_b);
+ * magnitude = 1: every event drives array A and the B pointers may be NULL.  pol: int8 per event; t: int64 us;
+ * next_ok_*: device int64[H*W], zero before the first call, carried between calls. */
+NSOF_API int nsof_event_scheme2_f32(nsof_handle *h, const int16_t *x, const int16_t *y, const int8_t *pol,
+                                    const int64_t *t, const int64_t *slice_begin, int n_slices, int H, int W,
+                                    int magnitude, float active_v, float bias_v, long long refractory_us,
+                                    const nsof_synapse_params *p, double dt, float *w_a, float *w_b,
+                                    int64_t *next_ok_a, int64_t *next_ok_b, void *cuda_stream);
 /* resistance_exp (eventsim/event_mem_sim.py:60-63): R = Ron / exp(-ln(Roff/Ron) * (1 - w)) for float32 w.
  * The result is float64, as in numpy (np.log returns a float64 scalar, which promotes the array). */
 NSOF_API int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n, const nsof_synapse_params *p,

@@ -118,6 +118,9 @@ _SIGNATURES = {
     "nsof_event_scheme1_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                          C.c_int, C.c_float, C.c_float, _P(SynapseParams), C.c_double, C.c_void_p,
                                          C.c_void_p]),
+    "nsof_event_scheme2_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                         C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_longlong, _P(SynapseParams),
+                                         C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "nsof_resistance_exp_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, _P(SynapseParams), C.c_void_p,
                                           C.c_void_p]),
     "nsof_event_cell_currents_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -95,6 +95,48 @@ extern "C" int nsof_event_scheme1_f32(nsof_handle *h, const int16_t *x, const in
     return NSOF_OK;
 }
 
+extern "C" int nsof_event_scheme2_f32(nsof_handle *h, const int16_t *x, const int16_t *y, const int8_t *pol, const int64_t *t,
+                                      const int64_t *slice_begin, int n_slices, int H, int W, int magnitude, float active_v,
+                                      float bias_v, long long refractory_us, const nsof_synapse_params *p, double dt, float *w_a,
+                                      float *w_b, int64_t *next_ok_a, int64_t *next_ok_b, void *cuda_stream)
+{
+    if (!h || !x || !y || !pol || !t || !slice_begin || !p || !w_a || !next_ok_a || n_slices < 0 || H < 1 || W < 1)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "event_scheme2: bad argument");
+    if (!magnitude && (!w_b || !next_ok_b)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "event_scheme2: split polarity needs the B arrays");
+    if (n_slices == 0) return NSOF_OK;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t npx = (size_t)H * W;
+    // scratch: two hit-mask planes + first/last event time of the 32 slices of a chunk
+    int rc = h->s1.ensure(npx * 8 + 64 * sizeof(int64_t));
+    if (rc) return rc;
+    uint32_t *bits_a = (uint32_t *)h->s1.p, *bits_b = bits_a + npx;
+    int64_t *t_first = (int64_t *)(bits_b + npx), *t_last = t_first + 32;
+    const SynF32 sp = syn_f32(p, dt);
+    std::vector<int64_t> sb(n_slices + 1);
+    NSOF_CUDA_TRY(cudaMemcpyAsync(sb.data(), slice_begin, sizeof(int64_t) * (n_slices + 1), cudaMemcpyDeviceToHost, st));
+    NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+    NSOF_CUDA_TRY(cudaMemsetAsync(bits_a, 0, npx * 8, st));
+    const bool bias_is_idle = !(bias_v < sp.voff) && !(bias_v > sp.von);
+    for (int s0 = 0; s0 < n_slices; s0 += 32) {
+        const int ns = std::min(32, n_slices - s0);
+        const int64_t ne = sb[s0 + ns] - sb[s0];
+        if (ne == 0 && bias_is_idle) continue;
+        if (ne > 0) {
+            NSOF_KLAUNCH(h, NSOF_K_EVENT_HIST, 5. * ne, k_s2_slice_bits, blocks_for((size_t)ne, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, x, y, pol,
+                         slice_begin + s0, ns, H, W, magnitude, bits_a, bits_b, S1_PER_BLOCK);
+            NSOF_KLAUNCH(h, NSOF_K_EVENT_HIST, 16. * ns, k_s2_slice_times, 1, 1, 1, 32, 0, st, t, slice_begin + s0, ns, t_first, t_last);
+        }
+        NSOF_KLAUNCH(h, NSOF_K_EVENT_REPLAY, 24. * npx, k_s2_replay_bits, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w_a, bits_a,
+                     next_ok_a, npx, ns, t_first, t_last, (int64_t)refractory_us, active_v, bias_v, sp, S1_PER_BLOCK);
+        if (!magnitude)
+            NSOF_KLAUNCH(h, NSOF_K_EVENT_REPLAY, 24. * npx, k_s2_replay_bits, blocks_for(npx, S1_PER_BLOCK), 1, 1, S1_NT, 0, st, w_b, bits_b,
+                         next_ok_b, npx, ns, t_first, t_last, (int64_t)refractory_us, active_v, bias_v, sp, S1_PER_BLOCK);
+    }
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
 extern "C" int nsof_resistance_exp_f32(nsof_handle *h, const float *w, size_t n, const nsof_synapse_params *p, double *R,
                                        void *cuda_stream)
 {

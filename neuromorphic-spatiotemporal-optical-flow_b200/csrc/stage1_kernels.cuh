@@ -115,6 +115,79 @@ NSOF_GLOBAL k_s1_replay_bits(float *NSOF_RESTRICT w, uint32_t *NSOF_RESTRICT bit
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scheme 2 (eventsim/event_mem_sim.py:231-286): DC bias everywhere, bias + active_v on the pixels that saw a
+// matching event in the slice AND whose refractory stamp next_ok <= t_us[sl.start]; those pixels get
+// next_ok = t_us[sl.stop - 1] + REFRACTORY_US.  'split': ON events (p == 1) drive array A, OFF events (p == 0)
+// array B (any other polarity value is ignored, as in the reference -- its synthetic generator writes -1 for
+// OFF); 'magnitude': every event drives array A.  Same two passes as scheme 1, chunks of <= 32 slices.
+// ---------------------------------------------------------------------------------------------
+NSOF_GLOBAL k_s2_slice_bits(const int16_t *NSOF_RESTRICT x, const int16_t *NSOF_RESTRICT y, const int8_t *NSOF_RESTRICT pol,
+                            const int64_t *NSOF_RESTRICT slice_begin, int n_slices, int H, int W, int magnitude,
+                            uint32_t *bits_a, uint32_t *bits_b, int per_block)
+{
+    const int64_t e0 = slice_begin[0], e1 = slice_begin[n_slices];
+    const int64_t base = e0 + (int64_t)NSOF_BX * per_block;
+    for (int i = NSOF_TID; i < per_block; i += NSOF_NT) {
+        const int64_t e = base + i;
+        if (e >= e1) continue;
+        int lo = 0, hi = n_slices - 1;  // slice of event e: last s with slice_begin[s] <= e
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (slice_begin[mid] <= e) lo = mid; else hi = mid - 1;
+        }
+        const int xx = x[e], yy = y[e], pp = pol[e];
+        uint32_t *bits = magnitude ? bits_a : (pp == 1 ? bits_a : (pp == 0 ? bits_b : nullptr));
+        if (bits && (unsigned)xx < (unsigned)W && (unsigned)yy < (unsigned)H) {
+#ifdef NSOF_EMU
+            bits[(size_t)yy * W + xx] |= 1u << lo;
+#else
+            atomicOr(bits + (size_t)yy * W + xx, 1u << lo);
+#endif
+        }
+    }
+}
+
+// first / last event time of every slice of the chunk (t_first is what every pixel's refractory test reads)
+NSOF_GLOBAL k_s2_slice_times(const int64_t *NSOF_RESTRICT t, const int64_t *NSOF_RESTRICT slice_begin, int n_slices,
+                             int64_t *NSOF_RESTRICT t_first, int64_t *NSOF_RESTRICT t_last)
+{
+    for (int s = NSOF_TID; s < n_slices; s += NSOF_NT) {
+        const int64_t a = slice_begin[s], b = slice_begin[s + 1];
+        t_first[s] = b > a ? t[a] : 0;
+        t_last[s] = b > a ? t[b - 1] : 0;
+    }
+}
+
+NSOF_GLOBAL k_s2_replay_bits(float *NSOF_RESTRICT w, uint32_t *NSOF_RESTRICT bits, int64_t *NSOF_RESTRICT next_ok, size_t n,
+                             int n_slices, const int64_t *NSOF_RESTRICT t_first, const int64_t *NSOF_RESTRICT t_last,
+                             int64_t refractory, float active_v, float bias_v, SynF32 p, int per_block)
+{
+    const size_t base = (size_t)NSOF_BX * per_block;
+    const bool bias_is_idle = !(bias_v < p.voff) && !(bias_v > p.von);
+    const float v_on = bias_v + active_v;  // Va[ys_ok, xs_ok] += active_v on a float32 map
+    for (int i = NSOF_TID; i < per_block; i += NSOF_NT) {
+        const size_t e = base + i;
+        if (e >= n) continue;
+        const uint32_t b = bits[e];
+        bits[e] = 0;  // leave the scratch clean for the next chunk
+        if (bias_is_idle && b == 0) continue;
+        float wv = w[e];
+        int64_t nk = next_ok[e];
+        for (int s = 0; s < n_slices; s++) {
+            bool hit = (b >> s) & 1u;
+            if (hit) {
+                hit = nk <= t_first[s];
+                if (hit) nk = t_last[s] + refractory;
+            }
+            if (!hit && bias_is_idle) continue;
+            wv = s1_update_state_f32(wv, hit ? v_on : bias_v, p);
+        }
+        w[e] = wv;
+        next_ok[e] = nk;
+    }
+}
+
 // General theta: one slice at a time from an int32 histogram.
 NSOF_GLOBAL k_s1_step_from_counts(float *NSOF_RESTRICT w, const int32_t *NSOF_RESTRICT counts, size_t n, int theta,
                                   float active_v, float silent_v, SynF32 p, int per_block)

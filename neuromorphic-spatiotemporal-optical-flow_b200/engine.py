@@ -479,6 +479,29 @@ class Engine:
         self.lib.check(rc, "event_scheme1")
         return dw.cpu().numpy()
 
+    def simulate_scheme2(self, x, y, pol, t, H, W, slice_us, active_v=-6.0, silent_v=0.0, polarity="split", p=PARAMS, dt=DT):
+        """Scheme 2 of simulate() (eventsim/event_mem_sim.py:231-286) over the whole stream: DC bias + event overlay
+        with the per-pixel refractory period.  Returns (w_a, w_b) -- w_b is None for polarity='magnitude'."""
+        assert polarity in ("split", "magnitude"), "polarity must be 'split' or 'magnitude'"
+        t = np.asarray(t)
+        bounds = slice_bounds(t, slice_us)
+        arrs = [np.ascontiguousarray(x, dtype=np.int16), np.ascontiguousarray(y, dtype=np.int16),
+                np.ascontiguousarray(pol, dtype=np.int8), np.ascontiguousarray(t, dtype=np.int64), bounds.astype(np.int64)]
+        dx, dy, dp, dt_, db = self._dev_roundtrip(arrs)
+        two = polarity == "split"
+        w0 = np.full((H, W), p["wini"], dtype=np.float32)
+        nk0 = np.zeros((H, W), dtype=np.int64)
+        dwa, dna = self._dev_roundtrip([w0, nk0])
+        dwb, dnb = self._dev_roundtrip([w0, nk0]) if two else (None, None)
+        sp = _synapse_params(p)
+        rc = self.lib.nsof_event_scheme2_f32(self.handle, dx.data_ptr(), dy.data_ptr(), dp.data_ptr(), dt_.data_ptr(),
+                                             db.data_ptr(), len(bounds) - 1, H, W, 0 if two else 1, float(active_v),
+                                             float(silent_v), int(REFRACTORY_US), C.byref(sp), float(dt), dwa.data_ptr(),
+                                             dwb.data_ptr() if two else None, dna.data_ptr(),
+                                             dnb.data_ptr() if two else None, self._stream())
+        self.lib.check(rc, "event_scheme2")
+        return dwa.cpu().numpy(), (dwb.cpu().numpy() if two else None)
+
     def event_cell_currents(self, w, memsize, p=PARAMS):
         """Event-mode ROI glue: float32 state (H, W) -> float64 cell currents (H // memsize, W // memsize), the
         largest pixel current 1 / resistance_exp(w) of every cell (feeds roi_from_currents)."""

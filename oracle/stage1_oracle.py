@@ -154,6 +154,45 @@ def scheme1(x, y, t, H, W, slice_us, active_v=-6.0, silent_v=0.0, n_slices=None,
     return w
 
 
+REFRACTORY_US = 800  # eventsim/event_mem_sim.py:34
+
+
+def scheme2(x, y, pol, t, H, W, slice_us, active_v=-6.0, silent_v=0.0, polarity="split", p=PARAMS):
+    """Scheme-2 loop of simulate() (eventsim/event_mem_sim.py:231-286): DC bias + event overlay with a per-pixel
+    refractory period.  polarity 'split': ON events (pol == 1) drive array A, OFF events (pol == 0) array B;
+    'magnitude': every event drives array A.  Returns (w_a, w_b or None)."""
+    idx = slice_bounds(t, slice_us)
+    two = polarity == "split"
+    w_a = p["wini"] * np.ones((H, W), dtype=np.float32)
+    w_b = w_a.copy() if two else None
+    next_a = np.zeros((H, W), dtype=np.int64)
+    next_b = np.zeros((H, W), dtype=np.int64)
+
+    def overlay(V, next_ok, xs, ys, t_start, t_last):
+        if xs.size == 0:
+            return
+        ok = next_ok[ys, xs] <= t_start
+        if np.any(ok):
+            V[ys[ok], xs[ok]] += active_v  # duplicates apply once (numpy fancy-index semantics)
+            next_ok[ys[ok], xs[ok]] = t_last + REFRACTORY_US
+
+    for i in range(len(idx) - 1):
+        a, b = idx[i], idx[i + 1]
+        Va = np.full((H, W), float(silent_v), dtype=np.float32)
+        Vb = np.full((H, W), float(silent_v), dtype=np.float32) if two else None
+        if b > a:
+            xs, ys, ps = x[a:b], y[a:b], pol[a:b]
+            if two:
+                overlay(Va, next_a, xs[ps == 1], ys[ps == 1], t[a], t[b - 1])
+                overlay(Vb, next_b, xs[ps == 0], ys[ps == 0], t[a], t[b - 1])
+            else:
+                overlay(Va, next_a, xs, ys, t[a], t[b - 1])
+        w_a = update_state(w_a, Va, p)
+        if two:
+            w_b = update_state(w_b, Vb, p)
+    return w_a, w_b
+
+
 # ----------------------------------------------------------------------------- frame mode (unpinned)
 def _lanczos3(x):
     """MATLAB imresize.m lanczos3 kernel."""

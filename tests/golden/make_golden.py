@@ -205,7 +205,42 @@ def make_events():
     print("events_reference.npz", len(x), "events", len(slices), "slices")
 
 
+def make_events_scheme2():
+    """Scheme 2 (DC bias + event overlay with a per-pixel refractory period) by running the reference's own
+    simulate() (event_mem_sim.py:164-322) with load_events patched to hand it the synthetic stream."""
+    import tempfile
+    from pathlib import Path
+    sys.modules.setdefault("h5py", types.ModuleType("h5py"))
+    sys.path.insert(0, f"{REF}/eventsim")
+    import event_mem_sim as ems
+    x, y, p, t = ems.generate_synthetic_events()
+    H, W = 240, 320
+    p01 = np.where(p > 0, 1, 0)  # a Prophesee file stores OFF as 0; the synthetic generator writes -1
+    cases = {  # name: (polarity array, slice_us, active_v, silent_v (bias), polarity mode, number of events used)
+        "split_pm1": (p, 1000, -6.0, 0.0, "split", len(x)),
+        "split_01_decay": (p01, 500, -6.0, 0.3, "split", 12000),
+        "magnitude": (p01, 700, -6.0, 0.3, "magnitude", 12000),
+    }
+    out = dict(x=x.astype(np.int16), y=y.astype(np.int16), t=t.astype(np.int64), p_pm1=p.astype(np.int8),
+               p_01=p01.astype(np.int8), H=H, W=W, cases=np.array(list(cases)))
+    for name, (pp, slice_us, av, sv, mode, n) in cases.items():
+        ems.load_events = lambda path, pp=pp, n=n: (x[:n], y[:n], pp[:n].astype(int), t[:n], H, W)
+        with tempfile.TemporaryDirectory() as d:
+            h5 = Path(d) / "ev.hdf5"
+            ems.simulate(h5, version=2, slice_us=slice_us, active_v=av, silent_v=sv, save_video=False, polarity=mode)
+            out[f"{name}__w_a"] = np.load(h5.with_suffix(".V2.npz"))["w_final"]
+            if mode == "split":
+                out[f"{name}__w_b"] = np.load(h5.with_suffix(".V2_b.npz"))["w_final"]
+        out[f"{name}__args"] = np.array([slice_us, av, sv, n, 0 if mode == "split" else 1], dtype=np.float64)
+        print(name, "w_a range", out[f"{name}__w_a"].min(), out[f"{name}__w_a"].max())
+    np.savez_compressed(os.path.join(OUT, "events_scheme2_reference.npz"), **out)
+    print("events_scheme2_reference.npz")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "scheme2":
+        make_events_scheme2()
+        sys.exit(0)
     make_farneback()
     make_roi()
     make_events()

@@ -86,6 +86,19 @@ class Golden:
         self.fb = np.load(os.path.join(GOLDEN, "farneback_cv2.npz"))
         self.roi = np.load(os.path.join(GOLDEN, "roi_reference.npz"))
         self.ev = np.load(os.path.join(GOLDEN, "events_reference.npz"))
+        self.ev2 = np.load(os.path.join(GOLDEN, "events_scheme2_reference.npz"))
+
+
+def scheme2_cases(ev2):
+    """(name, kwargs for scheme2 / simulate_scheme2, golden w_a, golden w_b or None) of events_scheme2_reference.npz."""
+    for name in [str(c) for c in ev2["cases"]]:
+        slice_us, av, sv, n, mode = ev2[f"{name}__args"]
+        n = int(n)
+        pol = ev2["p_pm1"] if name == "split_pm1" else ev2["p_01"]
+        kw = dict(x=ev2["x"][:n], y=ev2["y"][:n], pol=pol[:n], t=ev2["t"][:n], H=int(ev2["H"]), W=int(ev2["W"]),
+                  slice_us=int(slice_us), active_v=float(av), silent_v=float(sv),
+                  polarity="split" if mode == 0 else "magnitude")
+        yield name, kw, ev2[f"{name}__w_a"], (ev2[f"{name}__w_b"] if mode == 0 else None)
 
 
 def textured_pair(seed, h, w, dx=3.0, dy=-1.5):

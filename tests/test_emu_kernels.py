@@ -205,3 +205,20 @@ def test_emu_event_roi_glue_vs_oracle(emu_engine, nsof, golden):
     r = emu_engine.roi_from_currents(cur, (H, W), cfg=cfg)
     n, labels, stats, rects = s1.roi_from_memimg(s1.current_to_u8(want), (H, W), 20, 20, 250, (8, 8, 8, 8), 2)
     assert r["rects"] == rects and len(rects) == 1 and np.array_equal(r["labels"], labels)
+
+
+def test_emu_event_scheme2_vs_reference(emu_engine, golden):
+    """Scheme 2 (DC bias + event overlay, per-pixel refractory period; eventsim/event_mem_sim.py:231-286) against
+    w_final of the reference's own simulate(): the set of pixels at the clip values and every hit / refractory decision
+    must agree (a wrong decision moves w by >= 1e-3); float32 powf differs from numpy's by ulps per step."""
+    for name, kw, w_a, w_b in helpers.scheme2_cases(golden.ev2):
+        kw = dict(kw)
+        got_a, got_b = emu_engine.simulate_scheme2(kw.pop("x"), kw.pop("y"), kw.pop("pol"), kw.pop("t"), kw.pop("H"), kw.pop("W"),
+                                               kw.pop("slice_us"), **kw)
+        for got, want in ((got_a, w_a), (got_b, w_b)):
+            assert (got is None) == (want is None), name
+            if want is None:
+                continue
+            assert got.dtype == np.float32 and got.shape == want.shape
+            assert np.array_equal(got == 0, want == 0) and np.array_equal(got == 1, want == 1), name
+            assert np.abs(got - want).max() <= 2e-5, (name, np.abs(got - want).max())

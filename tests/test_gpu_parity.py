@@ -411,3 +411,20 @@ def test_event_stream_to_roi_gated_flow(gpu_engine, nsof, golden, oracle):
     x0, y0, x1, y1 = info
     want = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(bb[y0:y1, x0:x1]), **cfg.farneback_params)
     helpers.assert_flow_close(flow[y0:y1, x0:x1].astype(np.float32), want, "grasp", "event ROI crop")
+
+
+def test_event_scheme2_vs_reference(gpu_engine, golden):
+    """Scheme 2 (DC bias + event overlay, per-pixel refractory period; eventsim/event_mem_sim.py:231-286) against
+    w_final of the reference's own simulate(): the set of pixels at the clip values and every hit / refractory decision
+    must agree (a wrong decision moves w by >= 1e-3); float32 powf differs from numpy's by ulps per step."""
+    for name, kw, w_a, w_b in helpers.scheme2_cases(golden.ev2):
+        kw = dict(kw)
+        got_a, got_b = gpu_engine.simulate_scheme2(kw.pop("x"), kw.pop("y"), kw.pop("pol"), kw.pop("t"), kw.pop("H"), kw.pop("W"),
+                                               kw.pop("slice_us"), **kw)
+        for got, want in ((got_a, w_a), (got_b, w_b)):
+            assert (got is None) == (want is None), name
+            if want is None:
+                continue
+            assert got.dtype == np.float32 and got.shape == want.shape
+            assert np.array_equal(got == 0, want == 0) and np.array_equal(got == 1, want == 1), name
+            assert np.abs(got - want).max() <= 2e-5, (name, np.abs(got - want).max())

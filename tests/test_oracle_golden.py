@@ -77,3 +77,14 @@ def test_frame_mode_oracle_sanity():
     cells = np.full((3, 2, 2), 0.5)
     w, cur = s1.simulate_memristor_array(cells, nSubSteps=50)
     assert (w < 0.5).all() and np.allclose(cur[0], 1 / (163305 / np.exp(-np.log(2104377 / 163305) * 0.5)))
+
+
+def test_event_scheme2_oracle_matches_reference(golden):
+    """The numpy restatement of the scheme-2 loop against w_final of the reference's own simulate() (split with the
+    generator's +/-1 polarities, split with 0/1 polarities and a decaying bias, magnitude mode): bit for bit."""
+    for name, kw, w_a, w_b in helpers.scheme2_cases(golden.ev2):
+        got_a, got_b = s1.scheme2(**kw)
+        assert np.array_equal(got_a, w_a), name
+        assert (got_b is None) == (w_b is None)
+        if w_b is not None:
+            assert np.array_equal(got_b, w_b), name
