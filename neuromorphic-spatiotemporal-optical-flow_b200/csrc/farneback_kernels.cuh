@@ -701,20 +701,52 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_REST
     // source window: shared (sy, sx) <-> source (Ylo + sy, Xlo + sx), BORDER_REFLECT_101 outside the source
     const int Xlo = (MODE ? 2 * cx_lo : cx_lo) - 1, Ylo = (MODE ? 2 * cy_lo : cy_lo) - 1;
 
-    // ---- A: stage the window.  Interior tiles: one bulk asynchronous copy per row (16-byte aligned superset of
-    // the row), then uint8 -> float once per source pixel.  Border tiles: per-pixel loads with reflection.
-    const bool bulk = Xlo >= 16 && Xlo + SWN + 16 <= J.sw && Ylo >= 0 && Ylo + SHN <= J.sh && (sp & 15) == 0;
+    // ---- A: stage the window.  The in-image part arrives by one bulk asynchronous copy per row (16-byte aligned
+    // superset of the row; the last source row only when the superset stays inside it), BORDER_REFLECT_101 is applied
+    // to the raw bytes in shared memory (single bounce: the blur radius is 1), then uint8 -> float once per source
+    // pixel.  Degenerate images (a side < 2) or an unaligned pitch take per-pixel loads.
+    const int xs0 = nsof_imax(Xlo, 0), xs1 = nsof_imin(Xlo + SWN, J.sw);
+    const int ys0 = nsof_imax(Ylo, 0), ys1 = nsof_imin(Ylo + SHN, J.sh);
+    const bool bulk = J.sw > 1 && J.sh > 1 && (sp & 15) == 0 && xs1 > xs0 && ys1 > ys0;
     if (bulk) {
-        const uint8_t *a0 = src + (size_t)Ylo * sp + Xlo;
-        const int shift = (int)((uintptr_t)a0 & 15);
-        const unsigned row_bytes = (unsigned)((shift + SWN + 15) & ~15);
+        const uint8_t *a0 = src + (size_t)ys0 * sp + xs0;
+        const int mis = (int)((uintptr_t)a0 & 15);
+        const int shift = (mis - (xs0 - Xlo)) & 15;              // window column sx lives at byte shift + sx of its row
+        const unsigned row_bytes = (unsigned)((mis + (xs1 - xs0) + 15) & ~15);
+        const bool last_safe = xs0 - mis + (int)row_bytes <= J.sw;  // the over-read of the last source row stays in it
+        const int yb1 = (ys1 == J.sh && !last_safe) ? ys1 - 1 : ys1;
         if (NSOF_TID == 0) {
             nsof_mbar_init(bar, 1);
-            nsof_mbar_expect_tx(bar, row_bytes * (unsigned)SHN);
+            nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(yb1 - ys0));
         }
         NSOF_SYNC();
-        for (int r = NSOF_TID; r < SHN; r += NSOF_NT) nsof_bulk_g2s(sraw + r * RP, a0 - shift + (size_t)r * sp, row_bytes, bar);
-        nsof_mbar_wait(bar, 0);
+        for (int y = ys0 + NSOF_TID; y < yb1; y += NSOF_NT)
+            nsof_bulk_g2s(sraw + (y - Ylo) * RP + shift + (xs0 - Xlo) - mis, a0 - mis + (size_t)(y - ys0) * sp, row_bytes, bar);
+        if (yb1 < ys1) {
+            const uint8_t *row = src + (size_t)yb1 * sp;
+            for (int x = xs0 + NSOF_TID; x < xs1; x += NSOF_NT) sraw[(yb1 - Ylo) * RP + shift + (x - Xlo)] = NSOF_LDG(row + x);
+        }
+        if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);  // one warp polls, the others sleep in the block barrier
+        NSOF_SYNC();
+        if (xs0 > Xlo || xs1 < Xlo + SWN) {  // left / right reflection, in-image rows
+            const int nl = xs0 - Xlo, nr = Xlo + SWN - xs1;
+            for (int i = NSOF_TID; i < (ys1 - ys0) * (nl + nr); i += NSOF_NT) {
+                const int y = ys0 + i / (nl + nr), q = i % (nl + nr);
+                const int X = q < nl ? Xlo + q : xs1 + (q - nl);
+                uint8_t *row = sraw + (y - Ylo) * RP + shift;
+                row[X - Xlo] = row[nsof_reflect101(X, J.sw) - Xlo];
+            }
+            NSOF_SYNC();
+        }
+        if (ys0 > Ylo || ys1 < Ylo + SHN) {  // top / bottom reflection, whole window rows
+            const int nt = ys0 - Ylo, nb = Ylo + SHN - ys1;
+            for (int i = NSOF_TID; i < (nt + nb) * SWN; i += NSOF_NT) {
+                const int q = i / SWN, sx = i % SWN;
+                const int Y = q < nt ? Ylo + q : ys1 + (q - nt);
+                sraw[(Y - Ylo) * RP + shift + sx] = sraw[(nsof_reflect101(Y, J.sh) - Ylo) * RP + shift + sx];
+            }
+            NSOF_SYNC();
+        }
         // A2: 4 source pixels per thread: two aligned words, funnel shift by the misalignment, 4 conversions
         constexpr int G = SW / 4;
         for (int i = NSOF_TID; i < SHN * G; i += NSOF_NT) {
@@ -967,7 +999,7 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
             const uint8_t *row = src + (size_t)yb1 * sp;
             for (int x = xs0 + NSOF_TID; x < xs1; x += NSOF_NT) sS[(yb1 - Ymin) * SWp + shift + (x - Xmin)] = NSOF_LDG(row + x);
         }
-        nsof_mbar_wait(bar, 0);
+        if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);  // one warp polls, the others sleep in the block barrier
         NSOF_SYNC();
         if (xs0 > Xmin || xs1 < Xmin + swn) {  // left / right reflection, in-image rows
             const int nl = xs0 - Xmin, nr = Xmin + swn - xs1;
