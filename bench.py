@@ -45,7 +45,9 @@ def workload_config(args, n_gpus):
             "pairs_per_step_per_gpu": args.clips * (args.frames - 1), "clips_total": args.clips * n_gpus,
             "roi": "synapse-array gate (MEMSIZE 80, THRES 250, EXT 20, FLAG 2)",
             "farneback": [0.5, 3, 15, 3, 5, 1.2, 0], "stage1": "frame mode, nSubSteps 1000",
-            "l2": "inputs exceed L2 (frames + flow frames per step >> 126 MB)"}
+            "l2": "inputs exceed L2 (frames + flow frames per step >> 126 MB)",
+            "schedule": "pairs in time chunks 1,2,4,4,4 x all clips: stage 1 on a high-priority side stream, Farneback "
+                        "batches alternating between two streams (pipeline.py)"}
 
 
 # ------------------------------------------------------------------------------------------- clocks

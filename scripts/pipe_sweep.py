@@ -38,10 +38,19 @@ P = F - 1
 scheds = {k: v for k, v in {"1": [(0, P)], "1,2,4,8": pm.chunk_schedule(P), "1,2,4,4,4": pm.chunk_schedule(P, 1, 2, 4),
           "2,4,9": [(0, 2), (2, 6), (6, P)], "1,3,11": [(0, 1), (1, 4), (4, P)], "3x5": [(0, 5), (5, 10), (10, P)],
           "1,2,3,3,3,3": [(0, 1), (1, 3), (3, 6), (6, 9), (9, 12), (12, P)], "2,13": [(0, 2), (2, P)]}.items() if not os.environ.get("NSOF_SCHEDS") or k in os.environ["NSOF_SCHEDS"].split(";")}
+for spec in os.environ.get("NSOF_SCHEDS", "").split(";"):  # sizes not in the table: "1,2,4,4,2,1,1"
+    if spec and spec not in scheds and spec != "1":
+        sizes, pos, ch = [int(v) for v in spec.split(",")], 0, []
+        for n_ in sizes:
+            ch.append((pos, min(P, pos + n_)))
+            pos += n_
+        if pos == P:
+            scheds[spec] = ch
+step_streams = [int(v) for v in os.environ.get("NSOF_S2", "1,2,3").split(",") if v]
 for name, ch in scheds.items():
     if ch[-1][1] != P:
         continue
-    for ns in (1, 2, 3):
+    for ns in step_streams:
         eng = nsof.Engine(0)
         pipe = pm.SequencePipeline(eng, Cn, F, H, W, chunks=ch, s2_streams=ns)
         ms = t_step(pipe)
