@@ -307,6 +307,16 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const size_t plane = (size_t)J.pitch * J.h;
     const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;
+    // The R1 gather addresses depend on the coarse-flow loads: start pulling the tile's R1 rows (+- 4 rows for the
+    // displacement) into L2 now, so that the second, dependent round of loads does not pay DRAM latency again.
+    {
+        const int py0 = nsof_imax(ty0 - 4, 0), py1 = nsof_imin(ty0 + FB_UM_TH + 4, J.h);
+        const int px1 = nsof_imin(tx0 + FB_UM_TW, J.pitch);
+        for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
+            const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
+            nsof_prefetch_l2(J.R + (5 + c) * plane + (size_t)gy * J.pitch + tx0, (unsigned)(px1 - tx0) * 4u);
+        }
+    }
     constexpr int GW = FB_UM_TW / 4;
     for (int i = NSOF_TID; i < GW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + (i % GW) * 4, y = ty0 + i / GW;

@@ -33,6 +33,8 @@ def build_oracle():
 
 
 def build_emu():
+    if os.environ.get("NSOF_EMU_LIB"):  # e.g. the AddressSanitizer build (make -C .../csrc emu-asan)
+        return os.path.abspath(os.environ["NSOF_EMU_LIB"])
     path = os.path.join(ROOT, "tests", "emu", "_build", "libnsof_emu.so")
     csrc = os.path.join(ROOT, "neuromorphic-spatiotemporal-optical-flow_b200", "csrc")
     subprocess.run(["make", "-s", "-C", csrc, "emu"], check=True)
