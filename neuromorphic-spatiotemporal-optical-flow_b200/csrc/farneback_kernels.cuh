@@ -541,19 +541,18 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);
     NSOF_SYNC();
     if (tx0 - M < 0 || tx0 + TW + M > J.w) {  // replicate the first / last image column into the halo
-        const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
+        // one element per thread; on the right only the M columns past the last image column are ever read by a
+        // valid output (a tile that is mostly outside the image used to fill all of them: 10 % of the kernel's
+        // instructions on ROI-sized crops)
         const int s_first = -gx0, s_last = J.w - 1 - gx0;  // shared columns of image x = 0 and x = w - 1
-        for (int r = warp; r < 5 * LH; r += nw) {
+        const int n_l = tx0 - M < 0 ? s_first - (ML - M) : 0;
+        const int n_r = tx0 + TW + M > J.w ? nsof_imin(M, ML + TW + M - (s_last + 1)) : 0;
+        const int per_row = n_l + n_r;
+        for (int i = NSOF_TID; i < 5 * LH * per_row; i += NSOF_NT) {
+            const int r = i / per_row, k = i - r * per_row;
             float *row = sM + (r / LH) * SP + (r % LH) * PW;
-            if (tx0 - M < 0) {
-                const float v = row[s_first];
-                for (int sx = ML - M + lane; sx < s_first; sx += NSOF_WARP) row[sx] = v;
-            }
-            if (tx0 + TW + M > J.w) {
-                const float v = row[s_last];
-                NSOF_SYNCWARP();
-                for (int sx = s_last + 1 + lane; sx < ML + TW + M; sx += NSOF_WARP) row[sx] = v;
-            }
+            if (k < n_l) row[ML - M + k] = row[s_first];
+            else row[s_last + 1 + (k - n_l)] = row[s_last];
         }
         NSOF_SYNC();
     }
@@ -635,7 +634,11 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     NSOF_SYNC();
     // ---- phase 3b
     const float *R0 = J.R, *R1 = J.R + 5 * plane;
-#pragma unroll 2
+#ifndef FB_BS_UNROLL
+#define FB_BS_UNROLL 2
+#endif
+    constexpr int UNR3B = FB_BS_UNROLL;
+#pragma unroll UNR3B
     for (int i = NSOF_TID; i < TW * TH; i += NSOF_NT) {
         const int lx = i % TW, ly = i / TW;
         const int x = tx0 + lx, y = ty0 + ly;
