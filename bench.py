@@ -223,7 +223,7 @@ def gpu_arm(args):
     crop_px_step = pipe.last_crop_pixels
 
     # ---- e2e: pinned host clips in, rectangles + packed ROI flow crops out, copies inside the timed region
-    hp = pipe_mod.HostPipeline(local, Cn, F, H, W)
+    hp = pipe_mod.HostStream(local, Cn, F, H, W, depth=3)
     clips_host = [torch.empty((F, H, W), dtype=torch.uint8).pin_memory() for _ in range(Cn)]
     for c in range(Cn):
         clips_host[c].copy_(frames[:, c])
@@ -231,24 +231,31 @@ def gpu_arm(args):
 
     def timed_host(steps, warmup):
         for _ in range(warmup):
-            hp.run(clips_host)
+            hp.submit(clips_host)
+        hp.drain()
+        torch.cuda.synchronize()
         barrier()
         t0 = time.perf_counter()  # several streams: wall clock between device-wide synchronisations
-        for _ in range(steps):
-            hp.run(clips_host)
+        got = 0
+        for _ in range(steps):    # every step: H2D of its clips, D2H of its rectangles + flow crops, results collected
+            got += hp.submit(clips_host) is not None
+        got += len(hp.drain())    # pipeline fill and drain are inside the timed region
         torch.cuda.synchronize()
+        assert got == steps
         ms_ = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
         barrier()
         if world > 1:
             dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
         return float(ms_.item())
 
-    ms_e2e = timed_host(args.steps, 2)
+    ms_e2e = timed_host(args.steps, 3)
+    s0 = hp.slots[0]
     e2e = {"value": pairs_step * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": int(hp.h2d_bytes), "d2h_bytes_per_step": int(hp.d2h_bytes),
-           "api": "HostPipeline.run (pinned uint8 clips -> rectangles + packed float32 ROI flow), "
-                  f"{len(hp.slots)} streams (H2D / stage 1 / stage 2 / D2H), {len(hp.pipe.chunks)} time chunks, "
-                  "timed by host clock between device synchronisations"}
+           "api": "HostStream.submit/drain (pinned uint8 clips -> rectangles + packed float32 ROI flow on the host), "
+                  f"{len(hp.slots)} steps in flight, each on {len(s0.slots)} streams (H2D / stage 1 / stage 2 / D2H) "
+                  f"in {len(s0.pipe.chunks)} time chunks; all {args.steps} steps submitted and drained inside the "
+                  "timed region, host clock between device synchronisations"}
     del hp
     return finish(args, locals())
 
@@ -257,7 +264,8 @@ def gpu_arm(args):
 KERNEL_FUNCTION = {"fb_blur_um": "k_fb_blur_solve_t", "fb_blur_flow": "k_fb_blur_solve_t",
                    "fb_pyr_polyexp": "k_fb_pyr_polyexp_t", "fb_um_first": "k_fb_um_first", "fb_pyr": "k_fb_pyr_sep",
                    "fb_polyexp": "k_fb_polyexp", "s1_frame_sim": "k_s1_frame_run", "s1_lanczos": "k_s1_lanczos_rows+cols",
-                   "s1_roi": "k_s1_roi", "fb_flow_clear": "k_fb_flow_clear"}
+                   "s1_roi": "k_s1_roi", "fb_flow_clear": "k_fb_flow_clear", "table_upload": "k_table_upload",
+                   "halo_copy": "k_copy_blocks"}
 
 
 def measured_peak():

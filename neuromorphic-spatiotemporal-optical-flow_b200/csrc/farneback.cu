@@ -55,7 +55,7 @@ int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **out)
         s.pending = false;
     }
     if (!s.done) NSOF_CUDA_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-    if (s.bytes < bytes) {
+    if (s.bytes < bytes + 16) {  // uploads read whole 16-byte words
         if (s.host) NSOF_CUDA_TRY(cudaFreeHost(s.host));
         s.host = nullptr;
         s.bytes = 0;
@@ -63,6 +63,27 @@ int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **out)
         s.bytes = bytes + bytes / 4 + 4096;
     }
     *out = &s;
+    return NSOF_OK;
+}
+
+// Job tables reach the device through a kernel that reads the pinned staging slot over PCIe, not through
+// cudaMemcpyAsync: a host-to-device copy queues on the copy engine behind every frame copy already submitted (5 ms
+// of them per step in the host pipeline) and the batch's first kernel would sit behind all of them.
+NSOF_GLOBAL k_table_upload(float4 *NSOF_RESTRICT dst, const float4 *NSOF_RESTRICT src, size_t n16)
+{
+    for (size_t i = (size_t)NSOF_BX * NSOF_NT + NSOF_TID; i < n16; i += (size_t)nsof_grid_x() * NSOF_NT) dst[i] = src[i];
+}
+
+// `dst` (NsofDevBuf memory) and the slot are both allocated with >= 16 bytes of slack past `bytes`.
+static int nsof_table_upload(nsof_handle *h, void *dst, NsofStageSlot *slot, size_t bytes, cudaStream_t stream)
+{
+    const size_t n16 = (bytes + 15) / 16;
+    const int grid = (int)std::min<size_t>(32, std::max<size_t>(1, n16 / 256));
+    NSOF_KLAUNCH(h, NSOF_K_TABLE_UPLOAD, 2.0 * (double)bytes, k_table_upload, grid, 1, 1, 256, 0, stream, (float4 *)dst,
+                 (const float4 *)slot->host, n16);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
+    slot->pending = true;
     return NSOF_OK;
 }
 
@@ -131,7 +152,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 // ------------------------------------------------------------------------------ launch accounting
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
-    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy"};
+    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 
@@ -524,7 +545,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     NsofStageSlot *slot;
     rc = nsof_stage_acquire(h, table_bytes, &slot);
     if (rc) return rc;
-    rc = h->tables.ensure(table_bytes);
+    rc = h->tables.ensure(table_bytes + 16);
     if (rc) return rc;
     unsigned char *hs = (unsigned char *)slot->host;
     X.ds = (unsigned char *)h->tables.p;
@@ -612,9 +633,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             }
         }
     }
-    NSOF_CUDA_TRY(cudaMemcpyAsync(X.ds, hs, table_bytes, cudaMemcpyHostToDevice, stream));
-    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
-    slot->pending = true;
+    { int rc_up = nsof_table_upload(h, X.ds, slot, table_bytes, stream); if (rc_up) return rc_up; }
 
     prepare_poly(params->poly_n, params->poly_sigma, &X.pc);
     X.pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
@@ -963,7 +982,7 @@ extern "C" int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int 
     NsofStageSlot *slot;
     int rc = nsof_stage_acquire(h, bytes, &slot);
     if (rc) return rc;
-    rc = h->clear_tab.ensure(bytes);
+    rc = h->clear_tab.ensure(bytes + 16);
     if (rc) return rc;
     FbClearJob *hj = (FbClearJob *)slot->host;
     int max_h = 0;
@@ -979,9 +998,8 @@ extern "C" int nsof_flow_clear(nsof_handle *h, const nsof_crop_desc *items, int 
         max_h = std::max(max_h, d.h);
         px += (double)d.h * d.w;
     }
-    NSOF_CUDA_TRY(cudaMemcpyAsync(h->clear_tab.p, hj, bytes, cudaMemcpyHostToDevice, stream));
-    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
-    slot->pending = true;
+    rc = nsof_table_upload(h, h->clear_tab.p, slot, bytes, stream);
+    if (rc) return rc;
     NSOF_KLAUNCH(h, NSOF_K_FLOW_CLEAR, 8 * px, k_fb_flow_clear, std::min((max_h + 7) / 8, 64), n, 1, 256, 0, stream,
                  (const FbClearJob *)h->clear_tab.p);
     NSOF_CUDA_TRY(cudaGetLastError());
@@ -1016,7 +1034,7 @@ extern "C" int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, i
     NsofStageSlot *slot;
     int rc = nsof_stage_acquire(h, bytes, &slot);
     if (rc) return rc;
-    rc = h->clear_tab.ensure(bytes);
+    rc = h->clear_tab.ensure(bytes + 16);
     if (rc) return rc;
     size_t biggest = 0;
     double total = 0.;
@@ -1026,9 +1044,8 @@ extern "C" int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, i
         total += (double)blocks[i].bytes;
     }
     memcpy(slot->host, blocks, bytes);
-    NSOF_CUDA_TRY(cudaMemcpyAsync(h->clear_tab.p, slot->host, bytes, cudaMemcpyHostToDevice, stream));
-    NSOF_CUDA_TRY(cudaEventRecord(slot->done, stream));
-    slot->pending = true;
+    rc = nsof_table_upload(h, h->clear_tab.p, slot, bytes, stream);
+    if (rc) return rc;
     const int chunks = (int)std::min<size_t>(64, std::max<size_t>(1, biggest / (16 * 256 * 4)));
     NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total, k_copy_blocks, chunks, n, 1, 256, 0, stream, (const nsof_copy_block *)h->clear_tab.p);
     NSOF_CUDA_TRY(cudaGetLastError());

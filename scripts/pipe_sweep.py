@@ -94,3 +94,25 @@ for name, ch in scheds.items():
             print("     ", r, flush=True)
     del hp
     torch.cuda.empty_cache()
+
+# steps overlapped through HostStream (depth = steps in flight)
+for depth in [int(v) for v in os.environ.get("NSOF_DEPTHS", "2,3,4").split(",") if v]:
+    for name, ch in scheds.items():
+        if ch[-1][1] != P:
+            continue
+        hs = pm.HostStream(0, Cn, F, H, W, depth=depth, chunks=ch)
+        for _ in range(depth + 1):
+            hs.submit(clips_host)
+        hs.drain()
+        torch.cuda.synchronize()
+        for K in (5, 20):
+            t0 = time.perf_counter()
+            for _ in range(K):
+                hs.submit(clips_host)
+            hs.drain()
+            torch.cuda.synchronize()
+            ms = (time.perf_counter() - t0) / K * 1e3
+            print(f"stream depth {depth} chunks {name:12s} K={K:2d}: {ms:7.3f} ms/step  {hs.slots[0].pipe.n_pairs / ms * 1e3:9.0f} pairs/s",
+                  flush=True)
+        del hs
+        torch.cuda.empty_cache()

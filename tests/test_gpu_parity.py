@@ -346,7 +346,7 @@ def test_host_pipeline_matches_device_step(gpu_engine, nsof):
     pipe.step(frames)
     torch.cuda.synchronize()
     flow = pipe.flow.cpu().numpy()
-    hp = pm.HostPipeline(0, 5, F, H, W, slots=3)
+    hp = pm.HostPipeline(0, 5, F, H, W)
     for _ in range(2):  # twice: slot reuse
         out = hp.run([c.pin_memory() for c in clips])
     for c, (rects, n_rects, offs, packed) in enumerate(out):
@@ -360,6 +360,47 @@ def test_host_pipeline_matches_device_step(gpu_engine, nsof):
             x0, y0, x1, y1 = (int(v) for v in rects[t])
             crop = packed[offs[t]:offs[t] + 2 * (y1 - y0) * (x1 - x0)].numpy().reshape(y1 - y0, x1 - x0, 2)
             assert np.array_equal(crop, flow[t, c, y0:y1, x0:x1])
+
+
+def test_host_stream_matches_synchronous_runs(nsof):
+    """Five steps on DIFFERENT clips through a 3-deep HostStream (steps overlap on the device, slots are reused)
+    hand out, in order, exactly what one synchronous HostPipeline.run per step returns."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    steps = []
+    for k in range(5):
+        steps.append([syn.make_clip(700 + 10 * k + c, 400, 560, 6, "cpu",
+                                    velocity=(2.0 + k, -1.5 + 0.5 * c)).pin_memory() for c in range(3)])
+    F, H, W = steps[0][0].shape
+
+    def snapshot(out):  # the packed host tensor is reused by later steps of the same slot: copy what is compared
+        return [(r.copy(), n.copy(), list(o), pk.clone()) for r, n, o, pk in out]
+
+    hp = pm.HostPipeline(0, 3, F, H, W)
+    want = [snapshot(hp.run(s)) for s in steps]
+    hs = pm.HostStream(0, 3, F, H, W, depth=3)
+    got = []
+    for s in steps:
+        out = hs.submit(s)
+        if out is not None:
+            got.append(snapshot(out))
+    assert len(got) == 2  # steps 0 and 1 came back when steps 3 and 4 took over their slots
+    got += [snapshot(o) for o in hs.drain()]
+    assert len(got) == 5 and hs.h2d_bytes == 3 * F * H * W
+    opened = 0
+    for g, w in zip(got, want):
+        for (gr, gn, go, gp), (wr, wn, wo, wp) in zip(g, w):
+            assert np.array_equal(gn, wn) and np.array_equal(gr[gn > 0], wr[wn > 0]) and go == wo
+            opened += int((gn > 0).sum())
+            for t in range(F - 1):
+                if gn[t]:
+                    x0, y0, x1, y1 = (int(v) for v in gr[t])
+                    m = 2 * (y1 - y0) * (x1 - x0)
+                    assert torch.equal(gp[go[t]:go[t] + m], wp[wo[t]:wo[t] + m])
+    assert opened >= 30
 
 
 def test_sequence_step_repeat_and_serial_schedule(gpu_engine, nsof):
