@@ -303,6 +303,46 @@ NSOF_API int nsof_lanczos3_compress_u8(nsof_handle *h, const uint8_t *frames, in
                                        ptrdiff_t pitch, ptrdiff_t frame_stride, int Hc, int Wc, double *cells,
                                        void *cuda_stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Next row of the path: the motion-segmentation post-process that consumes the flow.
+ *
+ * Replaces, per region, `mag, ang = cv2.cartToPolar(flow_region[..., 0], flow_region[..., 1])` followed by
+ * `process_flow_region(mag, ang)` (optical_flow_seg.py:285-287, 308-311, 322-357; same code in optical_flow_yolo.py)
+ * and the paste `motion_binary[y_min:y_max, x_min:x_max] = ...` (:287).  What that function returns depends only on
+ *     motion_mask = 255 where mag > SEG_TH            (:345-346; the HSV / BGR / grey / `binary` images are dead code)
+ *     5 x [ dilate, erode ] with getStructuringElement(MORPH_ELLIPSE, (10, 10))   (:349-352)
+ *     threshold(., 1, 255, THRESH_BINARY)             (:355)
+ * The reference's flow is float64 there (pasted into np.zeros, negated, :215, :461) but holds float32 values, and
+ * cv2.cartToPolar computes in float32 regardless: mag = sqrtf(fmaf(x, x, y*y)), compared with mag_thresh in double
+ * (pinned by the golden masks of the reference's own function).  Morphology follows cv2: anchor = kernel
+ * centre (ksize / 2), pixels outside the image do not take part (dilate ignores them, erode ignores them).
+ * Masks are bit-exact.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct nsof_seg_params {
+    double mag_thresh;  /* SEG_TH (optical_flow_seg.py:49) */
+    int shape;          /* cv2.MORPH_RECT 0, MORPH_CROSS 1, MORPH_ELLIPSE 2 (getStructuringElement) */
+    int ksize_w, ksize_h; /* 1..32 each; (10, 10) in the reference */
+    int iterations;     /* dilate + erode rounds, 5 in the reference; 0 = threshold only */
+} nsof_seg_params;
+typedef struct nsof_seg_desc {
+    const float *flow;    /* device, h x w x 2 float32 (dx, dy), row pitch flow_pitch BYTES */
+    ptrdiff_t flow_pitch;
+    int h, w;
+    uint8_t *mask;        /* device, h x w uint8 (0 / 255), row pitch mask_pitch BYTES: the region of motion_binary */
+    ptrdiff_t mask_pitch;
+} nsof_seg_desc;
+/* All `n` regions in 2 + 2 * iterations launches (threshold + pack to bit planes, one launch per morphological pass
+ * over all regions, unpack).  Asynchronous on `cuda_stream`. */
+NSOF_API int nsof_flow_segment_batch(nsof_handle *h, const nsof_seg_desc *items, int n, const nsof_seg_params *params,
+                                     void *cuda_stream);
+/* One region with HOST pointers (flow in, mask out), synchronous: the call a `process_flow_region` drop-in makes
+ * for numpy arrays. */
+NSOF_API int nsof_flow_segment_host(nsof_handle *h, const float *flow, ptrdiff_t flow_pitch, int height, int width,
+                                    const nsof_seg_params *params, uint8_t *mask, ptrdiff_t mask_pitch);
+/* cv2.getStructuringElement(shape, (ksize_w, ksize_h)) as uint8 [ksize_h][ksize_w] (host), for tests and callers
+ * that want to look at the element the passes use. */
+NSOF_API int nsof_structuring_element(int shape, int ksize_w, int ksize_h, uint8_t *out);
+
 #ifdef __cplusplus
 }
 #endif

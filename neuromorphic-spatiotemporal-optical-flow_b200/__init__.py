@@ -8,7 +8,7 @@ Module-level functions mirror the reference's call sites and run on a lazily cre
     flow = nsof.calcOpticalFlowFarneback(prev_region, next_region, None, **nsof.FARNEBACK_PARAMS)
 """
 from ._lib import DEFAULT_LIB_PATH, EXPORTED_SYMBOLS, Library, error  # noqa: F401
-from .engine import (DT, FARNEBACK_PARAMS, PARAMS, REFRACTORY_US, THETA_EVENTS, Engine, RoiConfig,  # noqa: F401
+from .engine import (DT, FARNEBACK_PARAMS, PARAMS, REFRACTORY_US, SEG_TH, THETA_EVENTS, Engine, RoiConfig,  # noqa: F401
                      current_to_u8_reference_formula, slice_bounds, slice_indices, u8_threshold_table)
 
 _engines: dict = {}
@@ -34,6 +34,21 @@ def opticalFlow3D(memimg1, memimg2, rgbimg1, rgbimg2, pixel_width, pixel_height)
 def update_transition_pic(prev_memristor, transition_pic, thres):
     """optical_flow_seg.py:116."""
     return default_engine().update_transition_pic(prev_memristor, transition_pic, thres)
+
+
+def process_flow_region(mag, ang=None, flow_region=None):
+    """optical_flow_seg.py:322 drop-in.  The reference's result depends on `mag > SEG_TH` only, and `mag` is
+    cv2.cartToPolar of the flow region: pass `flow_region=` (h, w, 2) to have the magnitude test evaluated on the
+    device exactly as cv2.cartToPolar does (float32 arithmetic).  With `mag` alone the region (mag, 0) is
+    segmented; a float64 magnitude is rounded to float32 without moving it across SEG_TH."""
+    import numpy as np
+    if flow_region is None:
+        m = np.asarray(mag)
+        m32 = m.astype(np.float32)
+        th32 = np.float32(SEG_TH)
+        m32 = np.where((m > SEG_TH) & (m32 <= th32), np.nextafter(th32, np.float32(np.inf)), m32)
+        flow_region = np.stack([m32, np.zeros_like(m32)], axis=-1)
+    return default_engine().segment_flow(flow_region)
 
 
 def update_state(w, V, p=PARAMS, dt=DT):

@@ -66,6 +66,16 @@ class CopyBlock(C.Structure):
     _fields_ = [("dst", C.c_void_p), ("src", C.c_void_p), ("bytes", C.c_size_t)]
 
 
+class SegParams(C.Structure):  # nsof_seg_params
+    _fields_ = [("mag_thresh", C.c_double), ("shape", C.c_int), ("ksize_w", C.c_int), ("ksize_h", C.c_int),
+                ("iterations", C.c_int)]
+
+
+class SegDesc(C.Structure):  # nsof_seg_desc
+    _fields_ = [("flow", C.c_void_p), ("flow_pitch", C.c_ssize_t), ("h", C.c_int), ("w", C.c_int),
+                ("mask", C.c_void_p), ("mask_pitch", C.c_ssize_t)]
+
+
 class KernelStat(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("launches", C.c_int), ("ms", C.c_double), ("algorithmic_bytes", C.c_double)]
 
@@ -98,6 +108,10 @@ _SIGNATURES = {
     "nsof_fb_tiled_query": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _P(TiledBuf)]),
     "nsof_fb_tiled_guard": (C.c_int, [C.c_void_p, _P(C.c_int), C.c_void_p]),
     "nsof_copy_blocks": (C.c_int, [C.c_void_p, _P(CopyBlock), C.c_int, C.c_void_p]),
+    "nsof_flow_segment_batch": (C.c_int, [C.c_void_p, _P(SegDesc), C.c_int, _P(SegParams), C.c_void_p]),
+    "nsof_flow_segment_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, _P(SegParams),
+                                         C.c_void_p, C.c_ssize_t]),
+    "nsof_structuring_element": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),

@@ -75,7 +75,7 @@ NSOF_GLOBAL k_table_upload(float4 *NSOF_RESTRICT dst, const float4 *NSOF_RESTRIC
 }
 
 // `dst` (NsofDevBuf memory) and the slot are both allocated with >= 16 bytes of slack past `bytes`.
-static int nsof_table_upload(nsof_handle *h, void *dst, NsofStageSlot *slot, size_t bytes, cudaStream_t stream)
+int nsof_table_upload(nsof_handle *h, void *dst, NsofStageSlot *slot, size_t bytes, cudaStream_t stream)
 {
     const size_t n16 = (bytes + 15) / 16;
     const int grid = (int)std::min<size_t>(32, std::max<size_t>(1, n16 / 256));
@@ -129,6 +129,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
     fb_ctx_free(h);
     h->io.release();
     h->s1.release();
+    h->seg.release();
     h->lz.release();
     for (auto &s : h->stage) {
         if (s.host) cudaFreeHost(s.host);
@@ -152,7 +153,8 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 // ------------------------------------------------------------------------------ launch accounting
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
-    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload"};
+    "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload",
+    "seg_pack", "seg_morph", "seg_unpack"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 

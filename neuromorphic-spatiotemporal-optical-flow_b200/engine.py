@@ -22,7 +22,8 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _lib
-from ._lib import CropDesc, FbParams, FrameSimParams, Library, Rect, RoiParams, SynapseParams, error
+from ._lib import (CropDesc, FbParams, FrameSimParams, Library, Rect, RoiParams, SegDesc, SegParams, SynapseParams,
+                   error)
 
 # PARAMS of eventsim/event_mem_sim.py:20-27 == simulation/simulationcode_v4_transistor_vehicle.m:26-33
 PARAMS = dict(alphaoff=1, alphaon=1, voff=-0.2, von=0.1, koff=51.03, kon=-2.91, son=0.2, soff=0.8, bon=-5.12,
@@ -30,6 +31,7 @@ PARAMS = dict(alphaoff=1, alphaon=1, voff=-0.2, von=0.1, koff=51.03, kon=-2.91, 
 DT = 5e-4            # eventsim/event_mem_sim.py:30
 THETA_EVENTS = 1     # eventsim/event_mem_sim.py:33
 REFRACTORY_US = 800  # eventsim/event_mem_sim.py:34
+SEG_TH = 1           # optical_flow_seg.py:49, optical_flow_yolo.py:80
 
 # farneback_params of optical_flow_seg.py:73-81 (also optical_flow_yolo.py:114-122)
 FARNEBACK_PARAMS = dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0)
@@ -364,6 +366,59 @@ class Engine:
             flow[y0:y1, x0:x1] = self.calcOpticalFlowFarneback(prev_region, next_region, None, **fp)
             self.mem_velocity_times.append(time.time() - t0)
         return flow, self.mem_cal_times, self.mem_velocity_times, region_list, (x0, y0, x1, y1)
+
+    # ------------------------------------------------------------------ flow -> motion mask
+    def segment_flow(self, flow, seg_th=SEG_TH, ksize=(10, 10), iterations=5, shape=2):
+        """cv2.cartToPolar + process_flow_region (optical_flow_seg.py:308-311, 322-357) on a numpy flow region
+        (h, w, 2), float32 or the reference's float64 holding float32 values -> uint8 (h, w) mask, 0 / 255."""
+        f = np.asarray(flow)
+        if f.ndim != 3 or f.shape[2] != 2 or f.shape[0] < 1 or f.shape[1] < 1:
+            raise error("flow region must be a non-empty (h, w, 2) array")
+        f32 = np.ascontiguousarray(f, dtype=np.float32)
+        if f.dtype != np.float32 and not np.array_equal(f32.astype(f.dtype), f, equal_nan=True):
+            raise error("flow region holds values that are not float32-representable")
+        h, w = f32.shape[:2]
+        out = np.empty((h, w), dtype=np.uint8)
+        p = SegParams(float(seg_th), int(shape), int(ksize[0]), int(ksize[1]), int(iterations))
+        self.lib.check(self.lib.nsof_flow_segment_host(self.handle, f32.ctypes.data, f32.strides[0], h, w, C.byref(p),
+                                                       out.ctypes.data, out.strides[0]), "segment_flow")
+        return out
+
+    def segment_flow_device(self, regions, stream_ptr: int = 0, seg_th=SEG_TH, ksize=(10, 10), iterations=5, shape=2):
+        """`regions`: list of (flow_ptr, flow_pitch_bytes, h, w, mask_ptr, mask_pitch_bytes) with raw device
+        addresses; all regions in 2 + 2 * iterations launches, asynchronous on the stream."""
+        n = len(regions)
+        descs = (SegDesc * max(n, 1))()
+        for i, r in enumerate(regions):
+            descs[i] = SegDesc(*r)
+        p = SegParams(float(seg_th), int(shape), int(ksize[0]), int(ksize[1]), int(iterations))
+        self.lib.check(self.lib.nsof_flow_segment_batch(self.handle, descs, n, C.byref(p), C.c_void_p(stream_ptr)),
+                       "segment_flow_device")
+
+    def task_results(self, prev_frame, next_frame, flow, num_labels, regions_info, EST_FLAG=2, MERGE_FLAG=True,
+                     padding=0, seg_th=SEG_TH):
+        """optical_flow_seg.py:255-320: motion_binary of one frame pair from the pasted flow and the region(s)."""
+        h, w = prev_frame.shape[:2]
+        motion_binary = np.zeros((h, w), dtype=np.uint8)
+        if num_labels > 1:
+            if EST_FLAG == 1 and MERGE_FLAG:
+                boxes = [(max(0, min(r[0] for r in regions_info) - padding), max(0, min(r[1] for r in regions_info) - padding),
+                          min(w, max(r[2] for r in regions_info) + padding), min(h, max(r[3] for r in regions_info) + padding))]
+            elif EST_FLAG == 1:
+                boxes = [tuple(r) for r in regions_info]
+            else:
+                boxes = [tuple(regions_info)]
+            for x0, y0, x1, y1 in boxes:
+                if y1 > y0 and x1 > x0:
+                    motion_binary[y0:y1, x0:x1] = self.segment_flow(flow[y0:y1, x0:x1], seg_th)
+        return motion_binary
+
+    def structuring_element(self, shape, ksize):
+        """cv2.getStructuringElement(shape, ksize) as the segmentation passes build it."""
+        out = np.zeros((int(ksize[1]), int(ksize[0])), dtype=np.uint8)
+        self.lib.check(self.lib.nsof_structuring_element(int(shape), int(ksize[0]), int(ksize[1]), out.ctypes.data),
+                       "structuring_element")
+        return out
 
     def process_separate_regions(self, rects, rgbimg1, rgbimg2, flow, farneback_params=None):
         """FLAG=1 (optical_flow_seg.py:123-166): every region's crop pair goes into ONE batched launch sequence."""

@@ -27,8 +27,8 @@ import time
 import numpy as np
 
 from . import _lib
-from ._lib import CropDesc, FrameSimParams, RoiParams
-from .engine import PARAMS, Engine, RoiConfig, _fb_params, _synapse_params, u8_threshold_table
+from ._lib import CropDesc, FrameSimParams, RoiParams, SegDesc, SegParams
+from .engine import PARAMS, SEG_TH, Engine, RoiConfig, _fb_params, _synapse_params, u8_threshold_table
 
 _DESC_SIZE = C.sizeof(CropDesc)
 
@@ -47,10 +47,11 @@ def chunk_schedule(n_pairs: int, first: int = 1, grow: int = 2, cap: int = 8):
 class SequencePipeline:
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
                  sim=dict(dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, vds=1.0), full_frame: bool = False,
-                 packed: bool = False, chunks=None, overlap: bool = True, s2_streams: int = 2):
+                 packed: bool = False, chunks=None, overlap: bool = True, s2_streams: int = 2, segment: bool = False):
         import torch
         self.torch = torch
         self.eng, self.lib, self.h = engine, engine.lib, engine.handle
+        self.segment = bool(segment)  # also run task_results / process_flow_region on every ROI flow (8(f) rank 1)
         self.C, self.F, self.H, self.W = int(clips), int(frames), int(H), int(W)
         self.cfg = cfg or RoiConfig()
         self.full_frame = bool(full_frame)  # ROI = 100 %: skip the gate, run Farneback on whole frames
@@ -96,6 +97,16 @@ class SequencePipeline:
             self.flow = torch.zeros((self.F - 1, self.C, self.H, self.W, 2), dtype=torch.float32, device=self.dev)
         self.offsets = [-1] * self.n_pairs
         self.packed_floats = 0
+        # motion_binary (optical_flow_seg.py:262): uint8 frames, zero outside the ROI; packed mode: the crops' masks
+        # back to back, pair i's mask at packed_mask[offsets[i] // 2 :][: h * w]
+        self.motion = self.packed_mask = None
+        if self.segment:
+            if packed:
+                self.packed_mask = torch.empty((self.packed.numel() // 2,), dtype=torch.uint8, device=self.dev)
+            else:
+                self.motion = torch.zeros((self.F - 1, self.C, self.H, self.W), dtype=torch.uint8, device=self.dev)
+            self.seg_descs = (SegDesc * self.n_pairs)()
+            self.seg_params = SegParams(float(SEG_TH), 2, 10, 10, 5)  # optical_flow_seg.py:49, 349-351
         self.sp = _synapse_params(PARAMS)
         self.fsp = FrameSimParams(float(sim["th1"]), float(sim["th2"]), float(sim["dt"]), int(sim["nSubSteps"]),
                                   float(sim["vds"]))
@@ -184,6 +195,13 @@ class SequencePipeline:
             else:
                 d.flow = obase + ((t * Cn + c) * H * W + off) * 8
                 d.flow_pitch = W * 8
+            if self.segment:
+                g = self.seg_descs[n]
+                g.flow, g.flow_pitch, g.h, g.w = d.flow, d.flow_pitch, d.h, d.w
+                if self.packed_mode:
+                    g.mask, g.mask_pitch = self.packed_mask.data_ptr() + px, x1 - x0
+                else:
+                    g.mask, g.mask_pitch = self.motion.data_ptr() + ((t * Cn + c) * H * W + off), W
             n += 1
             px += (y1 - y0) * (x1 - x0)
         return n, px
@@ -197,12 +215,18 @@ class SequencePipeline:
         if self.packed_mode or not self.n_dirty:
             return
         self.lib.check(self.lib.nsof_flow_clear(self.h, self.descs, self.n_dirty, self._stream()), "flow_clear")
+        if self.segment:
+            self.motion.zero_()  # 1 byte per frame pixel; the flow frames are 8
         self.n_dirty = 0
 
     def stage2(self, n0, n1, eng=None):
         if n1 > n0:
             self.lib.check(self.lib.nsof_farneback_batch((eng or self.eng).handle, self._descs_at(n0), n1 - n0,
                                                          C.byref(self.fb), self._stream()), "farneback_batch")
+            if self.segment:
+                segs = C.cast(C.byref(self.seg_descs, n0 * C.sizeof(SegDesc)), C.POINTER(SegDesc))
+                self.lib.check(self.lib.nsof_flow_segment_batch((eng or self.eng).handle, segs, n1 - n0,
+                                                                C.byref(self.seg_params), self._stream()), "flow_segment")
 
     def stage2_chunk(self, j, n0, n1, cur):
         """Farneback batch of chunk j on its stream (chunk j -> stream j mod s2_streams, 0 = the caller's);
@@ -270,7 +294,8 @@ class HostPipeline:
     """
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 slots: int | None = None, full_frame: bool = False, lib=None, chunks=None, copy_streams=None):
+                 slots: int | None = None, full_frame: bool = False, lib=None, chunks=None, copy_streams=None,
+                 segment: bool = False):
         import torch
         self.torch = torch
         self.dev = torch.device(f"cuda:{device}")
@@ -285,7 +310,7 @@ class HostPipeline:
             if chunks is None:
                 chunks = chunk_schedule(self.F - 1, first=1, grow=2, cap=4)
             self.pipe = SequencePipeline(self.eng, clips, frames, H, W, cfg, full_frame=full_frame, packed=True,
-                                         chunks=chunks, overlap=True)
+                                         chunks=chunks, overlap=True, segment=segment)
             if full_frame:  # no stage 1: the side stream/handle of the pipe is unused
                 self.pipe.side = None
             self.frames = torch.empty((self.F, self.C, H, W), dtype=torch.uint8, device=self.dev)
@@ -295,6 +320,8 @@ class HostPipeline:
             self.ev_start = torch.cuda.Event(enable_timing=True)
             self.ev_out = torch.cuda.Event()
         self.flow_host = torch.empty((self.pipe.packed.numel(),), dtype=torch.float32).pin_memory()
+        self.mask_host = (torch.empty((self.pipe.packed_mask.numel(),), dtype=torch.uint8).pin_memory()
+                          if segment else None)
         self.slots = ([self.main, self.s_in, self.s_out] + ([self.pipe.side] if self.pipe.side is not None else [])
                       + [st for _, st in self.pipe.s2_extra])
         self.h2d_bytes = self.d2h_bytes = 0
@@ -319,7 +346,9 @@ class HostPipeline:
     def run(self, clips_host):
         """clips_host: sequence of C pinned uint8 tensors (F, H, W).  Returns per clip (rects, n_rects, offsets,
         packed float32 host tensor); pair t's flow crop is packed[offsets[t] : offsets[t] + 2 h w].view(h, w, 2).
-        The packed tensor is shared by all clips of the step.  Synchronous: results are on the host on return."""
+        With segment=True a fifth entry, the packed uint8 motion masks: pair t's is
+        masks[offsets[t] // 2 : offsets[t] // 2 + h w].view(h, w).  The packed tensors are shared by all clips of
+        the step.  Synchronous: results are on the host on return."""
         self.enqueue_input(clips_host)
         self.enqueue_flow()
         return self.collect()
@@ -374,6 +403,8 @@ class HostPipeline:
                     self.s_out.wait_event(p.ev_s2[j])
                     with t.cuda.stream(self.s_out):
                         self.flow_host[2 * px:2 * px1].copy_(p.packed[2 * px:2 * px1], non_blocking=True)
+                        if p.segment:
+                            self.mask_host[px:px1].copy_(p.packed_mask[px:px1], non_blocking=True)
                 self.ev_d2h[j].record(self.s_out)
                 self.host_marks.append(time.perf_counter())
                 n, px = n1, px1
@@ -391,16 +422,17 @@ class HostPipeline:
             for _, st in p.s2_extra:
                 st.synchronize()
         p.n_items, p.last_crop_pixels, p.packed_floats = n, px, 2 * px
-        self.d2h_bytes = px * 8 + (0 if p.full_frame else p.n_pairs * 20)
+        self.d2h_bytes = px * (9 if p.segment else 8) + (0 if p.full_frame else p.n_pairs * 20)
         out = []
         if p.full_frame:
             for c in range(Cn):
-                out.append((None, None, [p.offsets[tt * Cn + c] for tt in range(F - 1)], self.flow_host))
+                out.append((None, None, [p.offsets[tt * Cn + c] for tt in range(F - 1)], self.flow_host)
+                           + ((self.mask_host,) if p.segment else ()))
         else:
             R, N = p.rects_host.numpy().reshape(F - 1, Cn, 4), p.n_rects_host.numpy().reshape(F - 1, Cn)
             for c in range(Cn):
                 out.append((R[:, c].copy(), N[:, c].copy(), [p.offsets[tt * Cn + c] for tt in range(F - 1)],
-                            self.flow_host))
+                            self.flow_host) + ((self.mask_host,) if p.segment else ()))
         return out
 
 
@@ -419,7 +451,7 @@ class HostStream:
     """
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 depth: int = 3, full_frame: bool = False, lib=None, chunks=None):
+                 depth: int = 3, full_frame: bool = False, lib=None, chunks=None, segment: bool = False):
         assert depth >= 2
         import torch
         dev = torch.device(f"cuda:{device}")
@@ -431,7 +463,7 @@ class HostStream:
             chunks = [(n * i // parts, n * (i + 1) // parts) for i in range(parts)]
         self.copy_streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
         self.slots = [HostPipeline(device, clips, frames, H, W, cfg, full_frame=full_frame, lib=lib, chunks=chunks,
-                                   copy_streams=self.copy_streams) for _ in range(depth)]
+                                   copy_streams=self.copy_streams, segment=segment) for _ in range(depth)]
         self.k = 0            # steps submitted
         self.flowed = 0       # steps whose Farneback batches are queued
         self.collected = 0    # steps handed out

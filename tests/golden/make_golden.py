@@ -237,10 +237,84 @@ def make_events_scheme2():
     print("events_scheme2_reference.npz")
 
 
+def make_segment():
+    """Masks of the reference's own `process_flow_region` (optical_flow_seg.py:322-357, source-sliced) on
+    `cv2.cartToPolar` of float64 flow regions, exactly as `task_results` calls it (:308-311): the flow is a float64
+    array holding negated float32 Farneback output (:215, :461)."""
+    src = open(os.path.join(REF, "optical_flow_seg.py"), encoding="utf-8").read()
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "process_flow_region"]
+    ns = dict(cv2=cv2, np=np, SEG_TH=1)  # SEG_TH: optical_flow_seg.py:49
+    exec(compile(ast.Module(body=body, type_ignores=[]), "optical_flow_seg.py", "exec"), ns)
+    ref = ns["process_flow_region"]
+    rng = np.random.default_rng(77)
+    cases = {}
+    # (1) real Farneback flow of a moving textured patch: a compact blob with a ragged rim around |flow| = 1
+    a, b = synth_pair(rng, 150, 200, dx=0.0, dy=0.0)
+    patch = rng.integers(0, 256, (60, 80)).astype(np.float32)
+    patch = cv2.GaussianBlur(patch, (0, 0), 1.5)
+    patch = ((patch - patch.min()) / (patch.max() - patch.min()) * 255).astype(np.uint8)
+    a = a.copy(); b = b.copy()
+    a[40:100, 50:130] = patch
+    b[42:102, 53:133] = patch
+    cases["farneback_patch"] = cv2.calcOpticalFlowFarneback(a, b, None, **PARAM_SETS["grasp"])
+    # (2) smooth random fields, about 12 % of the pixels above the threshold (components, holes, gaps narrower and
+    # wider than the element), quantised to multiples of 1/32 (stored as int8; plenty of magnitudes exactly 1)
+    for name, (h, w, sig) in {"noise_97x131": (97, 131, 4.0), "noise_64x64": (64, 64, 2.0), "noise_33x65": (33, 65, 3.0),
+                              "noise_200x31": (200, 31, 2.5), "noise_7x9": (7, 9, 1.0), "noise_1x40": (1, 40, 1.0),
+                              "noise_40x1": (40, 1, 1.0), "noise_1x1": (1, 1, 1.0), "noise_420x560": (420, 560, 6.0)}.items():
+        f = rng.standard_normal((h + 40, w + 40, 2)).astype(np.float32)
+        f = cv2.GaussianBlur(f, (0, 0), sig)[20:20 + h, 20:20 + w].reshape(h, w, 2)
+        f = f / (np.abs(f).mean() + 1e-9) * 0.39
+        q = np.clip(np.rint(f * 32), -128, 127).astype(np.int8)
+        cases[name] = q
+    # (3) magnitudes exactly at and next to the threshold, isolated pixels at the corners and edges, NaN / Inf
+    f = np.zeros((50, 70, 2), np.float32)
+    f[0, 0] = (1.0, 0.0)                                   # == 1: not set
+    f[0, 69] = (np.nextafter(np.float32(1), np.float32(2)), 0.0)
+    f[49, 0] = (0.6, 0.8)                                  # float32(0.6)^2 + float32(0.8)^2 in double
+    f[49, 69] = (-3.0, 4.0)
+    f[25, 35] = (0.0, -1.0000001)
+    f[10, 20] = (np.nan, 5.0)
+    f[12, 40] = (np.inf, 0.0)
+    f[30, 5:64] = (0.70710677, 0.70710677)                 # float32(sqrt(.5)): squares sum to just below / above 1
+    f[31, 5:64] = (0.7071068, 0.7071068)
+    cases["edge_values"] = f
+    out = {"cases": np.array(sorted(cases))}
+    for name, stored in cases.items():
+        f32 = stored.astype(np.float32) / 32 if stored.dtype == np.int8 else stored
+        flow = -np.asarray(f32, dtype=np.float64)          # the reference's float64 flow after `flow = -flow`
+        mag, ang = cv2.cartToPolar(flow[..., 0], flow[..., 1])
+        m = ref(mag, ang)
+        assert m.dtype == np.uint8 and m.shape == f32.shape[:2] and set(np.unique(m)) <= {0, 255}
+        out[f"{name}__flow"] = stored                       # int8: flow = stored / 32
+        out[f"{name}__mask"] = np.packbits(m > 0, axis=1)
+        out[f"{name}__mag_gt"] = np.packbits(mag > 1, axis=1)
+    ks = [(10, 10), (3, 3), (5, 7), (7, 5), (1, 1), (2, 2), (4, 9), (32, 32), (31, 17), (15, 15)]
+    for shape in (0, 1, 2):
+        for kw, kh in ks:
+            out[f"element__{shape}_{kw}_{kh}"] = cv2.getStructuringElement(shape, (kw, kh))
+    # dilate / erode alone (one pass each) with other elements, on the noise field
+    base = (np.sqrt(((cases["noise_97x131"].astype(np.float64) / 32) ** 2).sum(-1)) > 1).astype(np.uint8) * 255
+    for shape, (kw, kh) in [(2, (10, 10)), (0, (3, 5)), (1, (7, 7)), (2, (4, 9)), (2, (31, 17)), (0, (32, 32))]:
+        el = cv2.getStructuringElement(shape, (kw, kh))
+        out[f"dilate__{shape}_{kw}_{kh}"] = np.packbits(cv2.dilate(base, el) > 0, axis=1)
+        out[f"erode__{shape}_{kw}_{kh}"] = np.packbits(cv2.erode(base, el) > 0, axis=1)
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(OUT, "segment_reference.npz"), **out)
+    print("segment_reference.npz", {k: (int(np.unpackbits(out[f"{k}__mag_gt"]).sum()), int(np.unpackbits(out[f"{k}__mask"]).sum()),
+                                          cases[k].shape[0] * cases[k].shape[1]) for k in cases})
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "scheme2":
         make_events_scheme2()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "segment":
+        make_segment()
+        sys.exit(0)
     make_farneback()
     make_roi()
     make_events()
+    make_events_scheme2()
+    make_segment()

@@ -89,6 +89,17 @@ class Golden:
         self.roi = np.load(os.path.join(GOLDEN, "roi_reference.npz"))
         self.ev = np.load(os.path.join(GOLDEN, "events_reference.npz"))
         self.ev2 = np.load(os.path.join(GOLDEN, "events_scheme2_reference.npz"))
+        self.seg = np.load(os.path.join(GOLDEN, "segment_reference.npz"))
+
+
+def segment_cases(seg):
+    """(name, float32 flow region, golden mask bool, golden `mag > SEG_TH` bool) of segment_reference.npz."""
+    for name in [str(c) for c in seg["cases"]]:
+        stored = seg[f"{name}__flow"]
+        flow = stored.astype(np.float32) / 32 if stored.dtype == np.int8 else stored
+        h, w = flow.shape[:2]
+        unpack = lambda a: np.unpackbits(a, axis=1)[:, :w].astype(bool)
+        yield name, flow, unpack(seg[f"{name}__mask"]), unpack(seg[f"{name}__mag_gt"])
 
 
 def scheme2_cases(ev2):

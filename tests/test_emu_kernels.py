@@ -222,3 +222,34 @@ def test_emu_event_scheme2_vs_reference(emu_engine, golden):
             assert got.dtype == np.float32 and got.shape == want.shape
             assert np.array_equal(got == 0, want == 0) and np.array_equal(got == 1, want == 1), name
             assert np.abs(got - want).max() <= 2e-5, (name, np.abs(got - want).max())
+
+
+def test_emu_segment_vs_reference_and_oracle(emu_engine, golden):
+    """Bit-plane segmentation kernels (emulator build): masks of the reference's process_flow_region bit for bit;
+    threshold-only mode; other elements / iteration counts vs the (pinned) numpy restatement; the cv2 elements."""
+    from oracle import seg_oracle as so
+    for name, flow, mask, mag_gt in helpers.segment_cases(golden.seg):
+        if flow.shape[0] * flow.shape[1] > 40000:
+            continue  # the emulator is slow; the GPU test runs the ROI-sized case
+        assert np.array_equal(emu_engine.segment_flow(flow, iterations=0) > 0, mag_gt), name
+        got = emu_engine.segment_flow(flow)
+        assert got.dtype == np.uint8 and set(np.unique(got)) <= {0, 255}
+        assert np.array_equal(got > 0, mask), name
+        assert np.array_equal(emu_engine.segment_flow(-flow.astype(np.float64)) > 0, mask), name
+    flow = next(f for n, f, _, _ in helpers.segment_cases(golden.seg) if n == "noise_97x131")
+    for shape, ksize, its in [(0, (3, 5), 1), (1, (7, 7), 2), (2, (4, 9), 3), (2, (31, 17), 1), (0, (32, 32), 1), (2, (1, 1), 2),
+                              (2, (10, 10), 1), (2, (15, 15), 2), (0, (2, 2), 4)]:
+        want = so.process_flow_region(flow, 0.7, ksize, its, shape)
+        got = emu_engine.segment_flow(flow, 0.7, ksize, its, shape)
+        assert np.array_equal(got, want), (shape, ksize, its)
+        assert np.array_equal(emu_engine.structuring_element(shape, ksize), so.structuring_element(shape, ksize))
+    for bad in (dict(ksize=(33, 3)), dict(ksize=(0, 3)), dict(shape=3), dict(iterations=-1)):
+        with pytest.raises(Exception):
+            emu_engine.segment_flow(flow, **bad)
+    with pytest.raises(Exception):
+        emu_engine.segment_flow(np.zeros((0, 4, 2), np.float32))
+    # negative threshold: every pixel passes; NaN magnitude never does
+    f = np.zeros((5, 40, 2), np.float32)
+    f[2, 7] = np.nan
+    m = emu_engine.segment_flow(f, seg_th=-1.0, iterations=0)
+    assert m[2, 7] == 0 and (m > 0).sum() == 5 * 40 - 1

@@ -403,6 +403,70 @@ def test_host_stream_matches_synchronous_runs(nsof):
     assert opened >= 30
 
 
+def test_segment_vs_reference(gpu_engine, golden):
+    """Flow -> motion mask: masks of the reference's own process_flow_region on
+    cv2.cartToPolar of the same flow, bit for bit; threshold-only mode; other elements vs the pinned restatement."""
+    from oracle import seg_oracle as so
+    for name, flow, mask, mag_gt in helpers.segment_cases(golden.seg):
+        assert np.array_equal(gpu_engine.segment_flow(flow, iterations=0) > 0, mag_gt), name
+        got = gpu_engine.segment_flow(flow)
+        assert got.dtype == np.uint8 and set(np.unique(got)) <= {0, 255}
+        assert np.array_equal(got > 0, mask), name
+        assert np.array_equal(gpu_engine.segment_flow(-flow.astype(np.float64)) > 0, mask), name
+    # a full 1080p region vs the pinned restatement
+    rng = np.random.default_rng(5)
+    coarse = rng.standard_normal((1080 // 8 + 3, 1920 // 8 + 3, 2)).astype(np.float32)
+    big = np.ascontiguousarray(np.kron(coarse, np.ones((8, 8, 1), np.float32))[3:1083, 5:1925] * 0.4
+                               + rng.standard_normal((1080, 1920, 2)).astype(np.float32) * 0.2)
+    want = so.process_flow_region(big)
+    assert 0.02 < (want > 0).mean() < 0.98
+    assert np.array_equal(gpu_engine.segment_flow(big), want)
+    flow = next(f for n, f, _, _ in helpers.segment_cases(golden.seg) if n == "noise_97x131")
+    for shape, ksize, its in [(0, (3, 5), 1), (1, (7, 7), 2), (2, (4, 9), 3), (2, (31, 17), 1), (0, (32, 32), 1), (2, (1, 1), 2),
+                              (2, (15, 15), 2), (0, (2, 2), 4)]:
+        assert np.array_equal(gpu_engine.segment_flow(flow, 0.7, ksize, its, shape),
+                              so.process_flow_region(flow, 0.7, ksize, its, shape)), (shape, ksize, its)
+    with pytest.raises(Exception):
+        gpu_engine.segment_flow(flow, ksize=(33, 3))
+
+
+def test_sequence_step_with_segmentation(gpu_engine, nsof):
+    """segment=True: the motion_binary frames of the device-resident step equal task_results of the step's own flow
+    frames (restatement pinned to the reference), zero outside the rectangles, also after a second step on other
+    clips; the host path returns the same masks, packed."""
+    import importlib
+
+    import torch
+    from oracle import seg_oracle as so
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    other = torch.stack([syn.make_clip(500 + c, 400, 560, 6, "cpu", velocity=(-2.0, 3.0)) for c in range(3)], dim=1).cuda().contiguous()
+    clips = _small_clips(3)
+    frames = torch.stack(clips, dim=1).cuda().contiguous()
+    F, _, H, W = frames.shape
+    pipe = pm.SequencePipeline(gpu_engine, 3, F, H, W, segment=True)
+    pipe.step(other)
+    n = pipe.step(frames)
+    torch.cuda.synchronize()
+    flow, motion = pipe.flow.cpu().numpy(), pipe.motion.cpu().numpy()
+    rects, n_rects = pipe.last_rects
+    set_px = 0
+    for i in range(pipe.n_pairs):
+        t, c = divmod(i, 3)
+        want = so.task_results((H, W), flow[t, c], tuple(int(v) for v in rects[i])) if n_rects[i] else np.zeros((H, W), np.uint8)
+        assert np.array_equal(motion[t, c], want), (t, c)
+        set_px += int((want > 0).sum())
+    assert n >= 6 and set_px > 1000  # the moving object shows up in the masks
+    hp = pm.HostPipeline(0, 3, F, H, W, segment=True)
+    out = hp.run([c.pin_memory() for c in clips])
+    for c, (r, nr, offs, packed, masks) in enumerate(out):
+        for t in range(F - 1):
+            if nr[t]:
+                x0, y0, x1, y1 = (int(v) for v in r[t])
+                m = masks[offs[t] // 2:offs[t] // 2 + (y1 - y0) * (x1 - x0)].numpy().reshape(y1 - y0, x1 - x0)
+                assert np.array_equal(m, motion[t, c, y0:y1, x0:x1]), (t, c)
+
+
 def test_sequence_step_repeat_and_serial_schedule(gpu_engine, nsof):
     """The flow frames are zeroed by clearing the previous step's rectangles only (nsof_flow_clear): a second step on
     DIFFERENT clips must equal a fresh pipeline's result bit for bit, and the overlapped chunk schedule must equal the

@@ -88,3 +88,29 @@ def test_event_scheme2_oracle_matches_reference(golden):
         assert (got_b is None) == (w_b is None)
         if w_b is not None:
             assert np.array_equal(got_b, w_b), name
+
+
+def test_segment_oracle_matches_reference(golden):
+    """oracle/seg_oracle.py vs masks of the reference's own process_flow_region (cv2 cartToPolar / dilate / erode),
+    the cv2 structuring elements and single cv2 dilate / erode passes: bit for bit."""
+    from oracle import seg_oracle as so
+    seg = golden.seg
+    for name, flow, mask, mag_gt in helpers.segment_cases(seg):
+        assert np.array_equal(so.process_flow_region(flow, iterations=0) > 0, mag_gt), name
+        assert np.array_equal(so.process_flow_region(flow) > 0, mask), name
+        assert np.array_equal(so.process_flow_region(-flow.astype(np.float64)) > 0, mask), name  # sign, dtype of :461
+    base = None
+    for key in seg.files:
+        if key.startswith("element__"):
+            shape, kw, kh = (int(v) for v in key.split("__")[1].split("_"))
+            assert np.array_equal(so.structuring_element(shape, (kw, kh)), seg[key]), key
+        elif key.startswith(("dilate__", "erode__")):
+            if base is None:
+                base = next(m for n, _, _, m in helpers.segment_cases(seg) if n == "noise_97x131")
+            shape, kw, kh = (int(v) for v in key.split("__")[1].split("_"))
+            got = so._morph(base, so.structuring_element(shape, (kw, kh)), erode=key.startswith("erode"))
+            assert np.array_equal(got, np.unpackbits(seg[key], axis=1)[:, :base.shape[1]].astype(bool)), key
+    frame = np.zeros((60, 80, 2), np.float32)
+    frame[10:43, 5:70] = next(f for n, f, _, _ in helpers.segment_cases(seg) if n == "noise_33x65")
+    mb = so.task_results((60, 80), frame, (5, 10, 70, 43))
+    assert mb[10:43, 5:70].any() and not mb[:10].any() and not mb[:, 70:].any()
