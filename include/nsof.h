@@ -148,6 +148,10 @@ NSOF_API int nsof_fb_tiled_begin(nsof_handle *h, const nsof_crop_desc *items, in
 NSOF_API int nsof_fb_tiled_levels(const nsof_handle *h);
 /* stage: 0 pyramid + PolyExp, 1 first UpdateMatrices, 2 blur + solve iteration `it` (ignored otherwise). */
 NSOF_API int nsof_fb_tiled_stage(nsof_handle *h, int level, int stage, int it, void *cuda_stream);
+/* The same stage on a sub-window of the band: part 0 = the whole band, 1 / 2 = its top / bottom `halo_r1` rows (all a
+ * row neighbour waits for), 3 = the rows in between.  Parts 1 + 2 + 3 write exactly what part 0 writes: start the halo
+ * exchange after the edges, compute the interior while the rows travel (tiled.py, overlap=True). */
+NSOF_API int nsof_fb_tiled_stage_rows(nsof_handle *h, int level, int stage, int it, int part, void *cuda_stream);
 /* what: 0 R1, 1 Ma, 2 Mb, 3 flow of `level` (level 0: the caller's flow buffer). */
 NSOF_API int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what, nsof_tiled_buf *out);
 /* *tripped = 1 when an UpdateMatrices gather reached R1 rows beyond the received halo (result invalid: rerun with
@@ -162,6 +166,10 @@ typedef struct nsof_copy_block {
     size_t bytes;
 } nsof_copy_block;
 NSOF_API int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, int n, void *cuda_stream);
+/* The same with the block table already resident in DEVICE memory (uploaded once by the caller; `biggest_block` and
+ * `total_bytes` describe it): no staging slot and no upload kernel per call. */
+NSOF_API int nsof_copy_blocks_resident(nsof_handle *h, const nsof_copy_block *device_blocks, int n, size_t biggest_block,
+                                       double total_bytes, void *cuda_stream);
 
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */

@@ -105,9 +105,11 @@ _SIGNATURES = {
                                       C.c_void_p]),
     "nsof_fb_tiled_levels": (C.c_int, [C.c_void_p]),
     "nsof_fb_tiled_stage": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "nsof_fb_tiled_stage_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "nsof_fb_tiled_query": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _P(TiledBuf)]),
     "nsof_fb_tiled_guard": (C.c_int, [C.c_void_p, _P(C.c_int), C.c_void_p]),
     "nsof_copy_blocks": (C.c_int, [C.c_void_p, _P(CopyBlock), C.c_int, C.c_void_p]),
+    "nsof_copy_blocks_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_double, C.c_void_p]),
     "nsof_flow_segment_batch": (C.c_int, [C.c_void_p, _P(SegDesc), C.c_int, _P(SegParams), C.c_void_p]),
     "nsof_flow_segment_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, _P(SegParams),
                                          C.c_void_p, C.c_ssize_t]),

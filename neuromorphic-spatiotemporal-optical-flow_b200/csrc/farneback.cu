@@ -447,6 +447,10 @@ struct FbBatchCtx {
     bool tiled = false;
     FbTiling tiling = {0, 1, 0, nullptr};
     int ksize[64];
+    // tiled batches keep 4 job tables per level: 0 the rank's band, 1 / 2 its top / bottom `edge` rows (what the row
+    // neighbours wait for), 3 the rows in between; every per-level vector below except gk_off is indexed
+    // [variant * max_scales + level]
+    int n_variants = 1, edge = 0;
     std::vector<size_t> gk_off, job_off;
     std::vector<int> n_active, path_n, max_tiles_pp, max_tiles_ps, ps_sw, ps_sh, max_tiles_pyr, max_tiles_pe,
         max_tiles_um, max_tiles_bs, max_tiles_bss;
@@ -530,19 +534,23 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
 
     // ---- job tables for every level + Gaussian taps, one upload
     size_t gk_floats = 0;
+    const int NV = tiling ? 4 : 1, LV = NV * max_scales;
+    X.n_variants = NV;
+    X.edge = tiling ? tiling->halo_r1 : 0;
     X.gk_off.assign(max_scales, 0);
-    X.job_off.assign(max_scales, 0);
-    X.n_active.assign(max_scales, 0);
+    X.job_off.assign(LV, 0);
+    X.n_active.assign(LV, 0);
     for (int k = 0; k < max_scales; k++) {
         if (X.ksize[k] / 2 > 4096) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: pyramid blur ksize %d too large", X.ksize[k]);
         X.gk_off[k] = gk_floats;
         gk_floats += round_up(X.ksize[k] / 2 + 1, 4);
         for (int i = 0; i < n; i++) X.n_active[k] += plan[i].scales > k;
+        for (int v = 1; v < NV; v++) X.n_active[v * max_scales + k] = X.n_active[k];
     }
     size_t table_bytes = round_up(gk_floats * sizeof(float), 16);
-    for (int k = 0; k < max_scales; k++) {
-        X.job_off[k] = table_bytes;
-        table_bytes += round_up((size_t)X.n_active[k] * sizeof(FbJob), 16);
+    for (int kk = 0; kk < LV; kk++) {
+        X.job_off[kk] = table_bytes;
+        table_bytes += round_up((size_t)X.n_active[kk] * sizeof(FbJob), 16);
     }
     NsofStageSlot *slot;
     rc = nsof_stage_acquire(h, table_bytes, &slot);
@@ -551,16 +559,16 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     if (rc) return rc;
     unsigned char *hs = (unsigned char *)slot->host;
     X.ds = (unsigned char *)h->tables.p;
-    X.sumN.assign(max_scales, 0.);
-    X.sumNc.assign(max_scales, 0.);
+    X.sumN.assign(LV, 0.);
+    X.sumNc.assign(LV, 0.);
     // per level and pyramid path (0 generic, 1 fused level-0 shape, 2 fused exact-2x shape): items, pixels, source pixels
-    X.path_n.assign(3 * max_scales, 0);
-    X.path_N.assign(3 * max_scales, 0.);
-    X.path_N0.assign(3 * max_scales, 0.);
+    X.path_n.assign(3 * LV, 0);
+    X.path_N.assign(3 * LV, 0.);
+    X.path_N0.assign(3 * LV, 0.);
     for (auto *v : {&X.max_tiles_pp, &X.max_tiles_ps, &X.ps_sw, &X.ps_sh, &X.max_tiles_pyr, &X.max_tiles_pe, &X.max_tiles_um,
                     &X.max_tiles_bs, &X.max_tiles_bss})
-        v->assign(max_scales, 0);
-    X.sum_tiles_bs.assign(max_scales, 0);
+        v->assign(LV, 0);
+    X.sum_tiles_bs.assign(LV, 0);
     const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
     const int m = params->winsize / 2;
     X.m = m;
@@ -571,9 +579,10 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     else if (params->iterations > 0 && !pick_blur_tile(m, &X.BTW, &X.BTH, &X.bs_smem))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
     const int pn = params->poly_n;
-    for (int k = 0; k < max_scales; k++) {
-        gaussian_half_kernel(X.ksize[k], sigma[k], (float *)hs + X.gk_off[k]);
-        FbJob *jobs = (FbJob *)(hs + X.job_off[k]);
+    for (int kk = 0; kk < LV; kk++) {
+        const int k = kk % max_scales, variant = kk / max_scales;
+        if (variant == 0) gaussian_half_kernel(X.ksize[k], sigma[k], (float *)hs + X.gk_off[k]);
+        FbJob *jobs = (FbJob *)(hs + X.job_off[kk]);
         int a = 0;
         for (int i = 0; i < n; i++) {
             const FbItemPlan &pl = plan[i];
@@ -601,13 +610,19 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
                 J.gy_lo = std::max(0, J.y_lo - tiling->halo_r1);
                 J.gy_hi = std::min(J.h, J.y_hi + tiling->halo_r1);
                 J.guard = tiling->guard;
+                // sub-windows of the band (empty when the band is shorter than two edges)
+                const int e = std::min(X.edge, (J.y_hi - J.y_lo) / 2);
+                if (variant == 1) J.y_hi = J.y_lo + e;
+                else if (variant == 2) J.y_lo = J.y_hi - e;
+                else if (variant == 3) { J.y_lo += e; J.y_hi -= e; }
             }
             J.iy_lo = std::max(0, J.y_lo - pn); J.iy_hi = std::min(J.h, J.y_hi + pn);
+            if (J.y_hi <= J.y_lo) J.iy_hi = J.iy_lo;
             const int rows = J.y_hi - J.y_lo, irows = J.iy_hi - J.iy_lo;
             const double frac = (double)rows / J.h;  // share of the level this rank computes (1 when untiled)
-            X.path_n[3 * k + J.fast] += 1;
-            X.path_N[3 * k + J.fast] += (double)rows * J.w;
-            X.path_N0[3 * k + J.fast] += (double)J.sh * J.sw * frac;
+            X.path_n[3 * kk + J.fast] += 1;
+            X.path_N[3 * kk + J.fast] += (double)rows * J.w;
+            X.path_N0[3 * kk + J.fast] += (double)J.sh * J.sw * frac;
             J.I = base + pl.off_I[k]; J.R = base + pl.off_R[k]; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
             // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
             float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
@@ -616,22 +631,22 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             else { J.flow = (float2 *)fl_this; J.fpitch = J.pitch; }
             J.cflow = (const float2 *)fl_coarse;
             jobs[a++] = J;
-            X.sumN[k] += (double)rows * J.w;
-            if (!coarsest) X.sumNc[k] += (double)J.ch * J.cw * frac;
+            X.sumN[kk] += (double)rows * J.w;
+            if (!coarsest) X.sumNc[kk] += (double)J.ch * J.cw * frac;
             auto tiles = [&](int tw, int th, int nrows) { return ((J.w + tw - 1) / tw) * ((nrows + th - 1) / th); };
-            X.max_tiles_pyr[k] = std::max(X.max_tiles_pyr[k], tiles(FB_PYR_TW, FB_PYR_TH, irows));
-            X.max_tiles_pe[k] = std::max(X.max_tiles_pe[k], tiles(FB_PE_TW, FB_PE_TH, rows));
-            X.max_tiles_pp[k] = std::max(X.max_tiles_pp[k], tiles(FB_PP_TW, FB_PP_TH, rows));
+            X.max_tiles_pyr[kk] = std::max(X.max_tiles_pyr[kk], tiles(FB_PYR_TW, FB_PYR_TH, irows));
+            X.max_tiles_pe[kk] = std::max(X.max_tiles_pe[kk], tiles(FB_PE_TW, FB_PE_TH, rows));
+            X.max_tiles_pp[kk] = std::max(X.max_tiles_pp[kk], tiles(FB_PP_TW, FB_PP_TH, rows));
             if (!J.fast) {
-                X.max_tiles_ps[k] = std::max(X.max_tiles_ps[k], tiles(FB_PS_TW, FB_PS_TH, irows));
-                X.ps_sw[k] = std::max(X.ps_sw[k], (int)ceil(FB_PS_TW * J.sx) + 2 * (X.ksize[k] / 2) + 4);
-                X.ps_sh[k] = std::max(X.ps_sh[k], (int)ceil(FB_PS_TH * J.sy) + 2 * (X.ksize[k] / 2) + 4);
+                X.max_tiles_ps[kk] = std::max(X.max_tiles_ps[kk], tiles(FB_PS_TW, FB_PS_TH, irows));
+                X.ps_sw[kk] = std::max(X.ps_sw[kk], (int)ceil(FB_PS_TW * J.sx) + 2 * (X.ksize[k] / 2) + 4);
+                X.ps_sh[kk] = std::max(X.ps_sh[kk], (int)ceil(FB_PS_TH * J.sy) + 2 * (X.ksize[k] / 2) + 4);
             }
-            X.max_tiles_um[k] = std::max(X.max_tiles_um[k], tiles(FB_UM_TW, FB_UM_TH, rows));
-            if (X.BTW) X.max_tiles_bs[k] = std::max(X.max_tiles_bs[k], tiles(X.BTW, X.BTH, rows));
+            X.max_tiles_um[kk] = std::max(X.max_tiles_um[kk], tiles(FB_UM_TW, FB_UM_TH, rows));
+            if (X.BTW) X.max_tiles_bs[kk] = std::max(X.max_tiles_bs[kk], tiles(X.BTW, X.BTH, rows));
             if (X.bs_m7) {
-                X.max_tiles_bss[k] = std::max(X.max_tiles_bss[k], tiles(FB_BS7S_TW, FB_BS7S_TH, rows));
-                X.sum_tiles_bs[k] += tiles(X.BTW, X.BTH, rows);
+                X.max_tiles_bss[kk] = std::max(X.max_tiles_bss[kk], tiles(FB_BS7S_TW, FB_BS7S_TH, rows));
+                X.sum_tiles_bs[kk] += tiles(X.BTW, X.BTH, rows);
             }
         }
     }
@@ -646,29 +661,30 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
 }
 
 // S2-b + S2-c of level k on `stream` (independent of the flow: needs the sources and the tables only)
-static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream)
+static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream, int variant = 0)
 {
     FbBatchCtx &X = *h->ctx;
-    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
+    const int kk = variant * X.max_scales + k;  // job table / geometry of the band (0) or one of its sub-windows
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[kk]);
     const float *gk = (const float *)X.ds + X.gk_off[k];
-    const int na = X.n_active[k];
+    const int na = X.n_active[kk];
     const PolyConst &pc = X.pc;
     h->prof_level = k;
-    if (X.path_n[3 * k + 1])
-        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * k + 1] + 40 * X.path_N[3 * k + 1], FB_PYR_POLYEXP_M0,
-                     X.max_tiles_pp[k], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
-    if (X.path_n[3 * k + 2])
-        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * k + 2] + 40 * X.path_N[3 * k + 2], FB_PYR_POLYEXP_M1,
-                     X.max_tiles_pp[k], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
-    if (X.path_n[3 * k]) {
+    if (X.path_n[3 * kk + 1] && X.max_tiles_pp[kk])
+        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 1] + 40 * X.path_N[3 * kk + 1], FB_PYR_POLYEXP_M0,
+                     X.max_tiles_pp[kk], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
+    if (X.path_n[3 * kk + 2] && X.max_tiles_pp[kk])
+        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 2] + 40 * X.path_N[3 * kk + 2], FB_PYR_POLYEXP_M1,
+                     X.max_tiles_pp[kk], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
+    if (X.path_n[3 * kk] && X.max_tiles_pe[kk]) {
         const int r = X.ksize[k] / 2;
-        const size_t ps_smem = fb_ps_smem(r, X.ps_sw[k], X.ps_sh[k]);
+        const size_t ps_smem = fb_ps_smem(r, X.ps_sw[kk], X.ps_sh[kk]);
         if (ps_smem <= 100 * 1024)  // two CTAs per SM; larger windows (extreme ratios) take the direct kernel
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * k], k_fb_pyr_sep, X.max_tiles_ps[k], na, 2, 256, ps_smem, stream, jobs,
-                         gk, r, X.ps_sw[k], X.ps_sh[k]);
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, X.max_tiles_ps[kk], na, 2, 256, ps_smem, stream, jobs,
+                         gk, r, X.ps_sw[kk], X.ps_sh[kk]);
         else
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * k], k_fb_pyr, X.max_tiles_pyr[k], na, 2, 256, 0, stream, jobs, gk, r);
-        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * k], k_fb_polyexp, X.max_tiles_pe[k], na, 2, 256, X.pe_smem, stream,
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, X.max_tiles_pyr[kk], na, 2, 256, 0, stream, jobs, gk, r);
+        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, X.max_tiles_pe[kk], na, 2, 256, X.pe_smem, stream,
                      jobs, pc);
     }
     NSOF_CUDA_TRY(cudaGetLastError());
@@ -677,17 +693,19 @@ static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream)
 }
 
 // S2-f + first S2-d of level k (or the flow initialisation of a level with zero iterations)
-static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream)
+static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream, int variant = 0)
 {
     FbBatchCtx &X = *h->ctx;
-    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
-    const int na = X.n_active[k];
+    const int kk = variant * X.max_scales + k;
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[kk]);
+    const int na = X.n_active[kk];
     h->prof_level = k;
+    if (!X.max_tiles_um[kk]) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
     if (X.params.iterations == 0)
-        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[k] + 8 * X.sumN[k], k_fb_flow_init, X.max_tiles_um[k], na, 1, 256, 0, stream,
+        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
                      jobs, X.flow_mul);
     else
-        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[k] + 8 * X.sumNc[k], k_fb_um_first, X.max_tiles_um[k], na, 1, 256, 0, stream,
+        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first, X.max_tiles_um[kk], na, 1, 256, 0, stream,
                      jobs, X.flow_mul);
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
@@ -695,24 +713,26 @@ static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream)
 }
 
 // iteration `it` of S2-e on level k: blur + solve, then UpdateMatrices (it < iters - 1) or the flow write
-static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t stream)
+static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t stream, int variant = 0)
 {
     FbBatchCtx &X = *h->ctx;
-    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[k]);
-    const int na = X.n_active[k];
+    const int kk = variant * X.max_scales + k;
+    const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[kk]);
+    const int na = X.n_active[kk];
     const bool last = it == iters - 1;
-    const double Nk = X.sumN[k];
+    const double Nk = X.sumN[kk];
     h->prof_level = k;
+    if (!X.max_tiles_bs[kk]) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
     // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the
     // 32x16 tile (4x the CTAs, each a quarter of the serial work)
-    if (X.bs_m7 && X.sum_tiles_bs[k] < 2 * 148 * 3 && !h->dbg_big_tiles)
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, X.max_tiles_bss[k], na, 1,
+    if (X.bs_m7 && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, X.max_tiles_bss[kk], na, 1,
                      FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, X.bscale, (it & 1) == 0, last);
     else if (X.bs_m7)
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, X.max_tiles_bs[k], na, 1,
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, X.max_tiles_bs[kk], na, 1,
                      FB_BS7_NT, X.bs_smem, stream, jobs, X.bscale, (it & 1) == 0, last);
     else
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[k], na, 1,
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[kk], na, 1,
                      256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last);
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
@@ -829,17 +849,26 @@ extern "C" int nsof_fb_tiled_levels(const nsof_handle *h)
 // stage: 0 pyramid + PolyExp, 1 first UpdateMatrices, 2 blur + solve iteration `it`
 extern "C" int nsof_fb_tiled_stage(nsof_handle *h, int level, int stage, int it, void *cuda_stream)
 {
+    return nsof_fb_tiled_stage_rows(h, level, stage, it, 0, cuda_stream);
+}
+
+// The same stage on a sub-window of the band: part 0 the whole band, 1 / 2 its top / bottom `halo_r1` rows (everything
+// a row neighbour waits for), 3 the rows in between.  Parts 1 + 2 + 3 write exactly what part 0 writes, so a caller
+// can start the halo exchange after the edges and compute the interior while the rows travel.
+extern "C" int nsof_fb_tiled_stage_rows(nsof_handle *h, int level, int stage, int it, int part, void *cuda_stream)
+{
     if (!h || !h->ctx || !h->ctx->valid || !h->ctx->tiled) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: no tiled batch (call nsof_fb_tiled_begin)");
     FbBatchCtx &X = *h->ctx;
     if (level < 0 || level >= X.max_scales) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: level %d", level);
+    if (part < 0 || part >= X.n_variants) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: part %d", part);
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     switch (stage) {
-    case 0: return fb_launch_pyramid(h, level, stream);
-    case 1: return fb_launch_um_first(h, level, stream);
+    case 0: return fb_launch_pyramid(h, level, stream, part);
+    case 1: return fb_launch_um_first(h, level, stream, part);
     case 2:
         if (it < 0 || it >= X.params.iterations) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: iteration %d", it);
-        return fb_launch_blur(h, level, it, X.params.iterations, stream);
+        return fb_launch_blur(h, level, it, X.params.iterations, stream, part);
     default: NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_stage: stage %d", stage);
     }
 }
@@ -882,6 +911,8 @@ extern "C" int nsof_fb_tiled_guard(nsof_handle *h, int *tripped, void *cuda_stre
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     int v = 0;
     NSOF_CUDA_TRY(cudaMemcpyAsync(&v, h->guard_buf.p, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    // read and clear
+    NSOF_CUDA_TRY(cudaMemsetAsync(h->guard_buf.p, 0, sizeof(int), (cudaStream_t)cuda_stream));
     NSOF_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)cuda_stream));
     *tripped = v;
     return NSOF_OK;
@@ -1050,6 +1081,23 @@ extern "C" int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, i
     if (rc) return rc;
     const int chunks = (int)std::min<size_t>(64, std::max<size_t>(1, biggest / (16 * 256 * 4)));
     NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total, k_copy_blocks, chunks, n, 1, 256, 0, stream, (const nsof_copy_block *)h->clear_tab.p);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+// The same copy with the block table already RESIDENT in device memory (uploaded once by the caller, tiled.py keeps one
+// per exchange plan): no staging slot and no upload kernel per call.
+extern "C" int nsof_copy_blocks_resident(nsof_handle *h, const nsof_copy_block *device_blocks, int n, size_t biggest_block,
+                                         double total_bytes, void *cuda_stream)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_blocks_resident: NULL handle");
+    if (n < 0 || (n > 0 && !device_blocks)) NSOF_FAIL(NSOF_ERR_BAD_ARG, "copy_blocks_resident: bad block list");
+    if (n == 0) return NSOF_OK;
+    if (n > 65535) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "copy_blocks_resident: at most 65535 blocks per call");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const int chunks = (int)std::min<size_t>(64, std::max<size_t>(1, biggest_block / (16 * 256 * 4)));
+    NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total_bytes, k_copy_blocks, chunks, n, 1, 256, 0, stream, device_blocks);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;
 }

@@ -50,7 +50,7 @@ class _DevArray:
 
 
 class TiledFarneback:
-    def __init__(self, engine: Engine, rank: int, world: int, halo_r1: int = 32, group=None):
+    def __init__(self, engine: Engine, rank: int, world: int, halo_r1: int = 32, group=None, overlap: bool = False):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -61,6 +61,14 @@ class TiledFarneback:
         self.messages = 0       # point-to-point operations of the last run (sends + receives of this rank)
         self.bytes_sent = 0
         self._ops: dict = {}    # (exchange, workspace layout) -> (operation list, bytes sent)
+        # overlap: on levels whose band is at least 4 edges high every stage runs as edges -> [exchange on a second
+        # stream || interior]; the rows travel while the bulk of the band is computed (nsof_fb_tiled_stage_rows).
+        # Bit-identical, but measured no faster on 2 and 8 B200 (8K, 8 pairs: 1 117 vs 1 182 pairs/s at 8 GPUs): the
+        # step is bound by the HOST submitting ~190 launches and 20 exchange rounds, not by the rows in flight, and
+        # the split triples the launches.  Off by default.
+        self.overlap = bool(overlap)
+        self.comm = None if self.emulated else torch.cuda.Stream(torch.device(f"cuda:{engine.device}"))
+        self.split_levels = 0   # levels of the last run that took the overlapped schedule
 
     # ---- plumbing ----------------------------------------------------------------------------------------
     def _stream(self):
@@ -116,7 +124,14 @@ class TiledFarneback:
                     pack.append((addr(bufs["sd"]) + off, s_dn, nbytes))
                     unpack.append((h_dn, addr(bufs["rd"]) + off, nbytes))
                 off += nbytes
-            tab = lambda rows_: (CopyBlock * len(rows_))(*[CopyBlock(*r) for r in rows_])
+            def tab(rows_):
+                """Block table of one copy kernel: host array in the emulator, resident device tensor on CUDA
+                (uploaded once: no staging copy and no upload kernel per exchange)."""
+                arr = (CopyBlock * len(rows_))(*[CopyBlock(*r) for r in rows_])
+                if self.emulated or not rows_:
+                    return arr, None
+                host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+                return arr, host.to(f"cuda:{self.eng.device}")
             ops = []
             if up:
                 ops += [dist.P2POp(dist.isend, as_t(bufs["su"]), self.rank - 1, self.group),
@@ -126,13 +141,22 @@ class TiledFarneback:
                         dist.P2POp(dist.irecv, as_t(bufs["rd"]), self.rank + 1, self.group)]
             if len(self._ops) > 256:
                 self._ops.clear()
-            plan = self._ops[key] = (tab(pack), len(pack), tab(unpack), len(unpack), ops, per_dir * (int(up) + int(dn)), bufs)
-        pack, n_pack, unpack, n_unpack, ops, sent, _ = plan
+            big = max((b[2] for b in pack), default=0)
+            plan = self._ops[key] = (tab(pack), len(pack), tab(unpack), len(unpack), ops, per_dir * (int(up) + int(dn)), bufs,
+                                     big, float(sum(b[2] for b in pack)))
+        (pack, pack_dev), n_pack, (unpack, unpack_dev), n_unpack, ops, sent, _, big, total = plan
         st = self._stream()
-        self.lib.check(self.lib.nsof_copy_blocks(self.h, pack, n_pack, st), "copy_blocks (pack)")
+
+        def copy(host_tab, dev_tab, cnt, what_):
+            if dev_tab is None:
+                self.lib.check(self.lib.nsof_copy_blocks(self.h, host_tab, cnt, st), what_)
+            else:
+                self.lib.check(self.lib.nsof_copy_blocks_resident(self.h, dev_tab.data_ptr(), cnt, big, total, st), what_)
+
+        copy(pack, pack_dev, n_pack, "copy_blocks (pack)")
         for req in dist.batch_isend_irecv(ops):
             req.wait()
-        self.lib.check(self.lib.nsof_copy_blocks(self.h, unpack, n_unpack, st), "copy_blocks (unpack)")
+        copy(unpack, unpack_dev, n_unpack, "copy_blocks (unpack)")
         self.messages += len(ops)
         self.bytes_sent += sent
 
@@ -150,23 +174,73 @@ class TiledFarneback:
         for i, c in enumerate(crops):
             descs[i] = CropDesc(*c)
         lib, h, st = self.lib, self.h, self._stream()
-        self.messages = self.bytes_sent = 0
         lib.check(lib.nsof_fb_tiled_begin(h, descs, n, C.byref(fb), self.rank, self.world, self.halo_r1, st),
                   "fb_tiled_begin")
+        self._n, self._kw = n, kw
+        levels = self._stages()
+        self._check_guard()
+        return levels
+
+    def _stages(self):
+        """Every stage and exchange of the batch planned by the last nsof_fb_tiled_begin, on the current stream."""
+        lib, h = self.lib, self.h
+        n, kw = self._n, self._kw
+        self.messages = self.bytes_sent = 0
         levels = lib.nsof_fb_tiled_levels(h)
         m, T = kw["winsize"] // 2, kw["iterations"]
-        stage = lambda k, s, it=0: lib.check(lib.nsof_fb_tiled_stage(h, k, s, it, st), "fb_tiled_stage")
+        torch = self.torch
+        main = None if self.emulated else torch.cuda.current_stream(self.eng.device)
+        pending = [None]  # event of the last exchange queued on the second stream
+
+        def wait_halo():
+            if pending[0] is not None:
+                main.wait_event(pending[0])
+                pending[0] = None
+
+        def stage(k, s, it, exchanges, split):
+            """One stage of level k followed by its halo exchanges [(level, what, rows), ...]."""
+            run = lambda part: lib.check(lib.nsof_fb_tiled_stage_rows(h, k, s, it, part, self._stream()), "fb_tiled_stage")
+            wait_halo()
+            if not split:
+                run(0)
+                for lv, what, rows in exchanges:
+                    self._exchange(n, lv, what, rows)
+                return
+            run(1)
+            run(2)
+            if self.emulated or not exchanges:
+                for lv, what, rows in exchanges:
+                    self._exchange(n, lv, what, rows)
+            else:
+                ev = torch.cuda.Event()
+                ev.record(main)
+                with torch.cuda.stream(self.comm):
+                    self.comm.wait_event(ev)
+                    for lv, what, rows in exchanges:
+                        self._exchange(n, lv, what, rows)
+                    done = torch.cuda.Event()
+                    done.record(self.comm)
+                pending[0] = done
+            run(3)
+
+        self.split_levels = 0
         for k in range(levels - 1, -1, -1):
-            stage(k, 0)
-            self._exchange(n, k, WHAT_R1, self.halo_r1)
-            if k < levels - 1:
-                self._exchange(n, k + 1, WHAT_FLOW, FLOW_HALO_ROWS)
-            stage(k, 1)
-            self._exchange(n, k, WHAT_MA, m)
+            split = self.overlap and self.world > 1 and all(
+                (lambda b: b.y_hi - b.y_lo >= 4 * self.halo_r1)(self._query(i, k, WHAT_R1)) for i in range(n))
+            self.split_levels += int(split)
+            stage(k, 0, 0, [(k, WHAT_R1, self.halo_r1)], split)
+            stage(k, 1, 0, [(k, WHAT_MA, m)], split)
             for it in range(T):
-                stage(k, 2, it)
                 if it < T - 1:
-                    self._exchange(n, k, WHAT_MB if it % 2 == 0 else WHAT_MA, m)
+                    ex = [(k, WHAT_MB if it % 2 == 0 else WHAT_MA, m)]
+                else:  # the level's flow: the next finer level upsamples it (bilinear: rows beyond the band)
+                    ex = [(k, WHAT_FLOW, FLOW_HALO_ROWS)] if k > 0 else []
+                stage(k, 2, it, ex, split)
+        wait_halo()
+        return levels
+
+    def _check_guard(self):
+        lib, h, st = self.lib, self.h, self._stream()
         tripped = C.c_int(0)
         lib.check(lib.nsof_fb_tiled_guard(h, C.byref(tripped), st), "fb_tiled_guard")
         flag = int(tripped.value)
@@ -178,4 +252,3 @@ class TiledFarneback:
         if flag:
             raise RuntimeError(f"tiled Farneback: a displacement exceeded the R1 halo of {self.halo_r1} rows on some "
                                f"rank; rerun with a larger halo_r1")
-        return levels

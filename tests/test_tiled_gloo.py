@@ -28,7 +28,7 @@ def _pairs():
     return [helpers.textured_pair(7, H, W, dx=2.5, dy=-3.0), helpers.textured_pair(8, H, W, dx=-1.0, dy=4.5)]
 
 
-def _worker(rank, world, port, out_dir, halo):
+def _worker(rank, world, port, out_dir, halo, overlap=True):
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
                       MASTER_PORT=str(port))
     nsof = importlib.import_module("nsof_b200")
@@ -40,14 +40,14 @@ def _worker(rank, world, port, out_dir, halo):
     flows = [np.full((H, W, 2), np.nan, dtype=np.float32) for _ in pairs]
     crops = [(a.ctypes.data, b.ctypes.data, H, W, a.strides[0], b.strides[0], f.ctypes.data, f.strides[0])
              for (a, b), f in zip(pairs, flows)]
-    tf = tiled.TiledFarneback(eng, rank, world, halo_r1=halo)
+    tf = tiled.TiledFarneback(eng, rank, world, halo_r1=halo, overlap=overlap)
     status = "ok"
     try:
         tf.run(crops, **PARAMS)
     except RuntimeError as e:
         status = "guard" if "halo" in str(e) else "error: " + str(e)
     lo, hi = tiled.band_rows(H, rank, world)
-    np.savez(os.path.join(out_dir, f"r{rank}.npz"), lo=lo, hi=hi, status=status, messages=tf.messages,
+    np.savez(os.path.join(out_dir, f"r{rank}.npz"), lo=lo, hi=hi, status=status, messages=tf.messages, split=tf.split_levels,
              **{f"flow{i}": f for i, f in enumerate(flows)})
     torch.distributed.destroy_process_group()
     eng.close()
@@ -70,6 +70,8 @@ def test_tiled_ranks_reproduce_the_untiled_flow(tmp_path, emu_engine, world):
             outside[lo:hi] = False
             assert np.isnan(got[outside]).all()  # a rank writes its band only
         assert int(z["messages"]) > 0
+        # levels with a band of >= 4 halos ran as edges -> exchange -> interior (nsof_fb_tiled_stage_rows), the rest whole
+        assert int(z["split"]) == (3 if world == 2 else 2)
     assert covered == H
 
 
