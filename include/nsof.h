@@ -351,6 +351,36 @@ NSOF_API int nsof_flow_segment_host(nsof_handle *h, const float *flow, ptrdiff_t
  * that want to look at the element the passes use. */
 NSOF_API int nsof_structuring_element(int shape, int ksize_w, int ksize_h, uint8_t *out);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Frame-side neighbours of the path.
+ *
+ * nsof_rgb2gray_u8 replaces `cv2.cvtColor(frame, cv2.COLOR_RGB2GRAY)` on the decoded 3-channel frame
+ * (optical_flow_seg.py:442-443; same lines in _ob / _prediction / _yolo): OpenCV's 8-bit formula
+ * (c0 * 9798 + c1 * 19235 + c2 * 3735 + 16384) >> 15 on the channels AS STORED (the scripts pass a BGR array).
+ * `n` frames of H x W x 3 (row pitch / frame stride in bytes) -> n frames of H x W; device pointers, asynchronous.
+ * Decoding (cv2.imread) stays on the host.  Bit-exact.
+ * ------------------------------------------------------------------------------------------------------------- */
+NSOF_API int nsof_rgb2gray_u8(nsof_handle *h, const uint8_t *src, ptrdiff_t src_pitch, ptrdiff_t src_frame_stride, int n,
+                              int H, int W, uint8_t *dst, ptrdiff_t dst_pitch, ptrdiff_t dst_frame_stride, void *cuda_stream);
+NSOF_API int nsof_rgb2gray_u8_host(nsof_handle *h, const uint8_t *src, ptrdiff_t src_pitch, int H, int W, uint8_t *dst,
+                                   ptrdiff_t dst_pitch);
+/* The prediction task (optical_flow_prediction.py:281-352, 257-361): per region
+ *     flow_map = (x, y) + flow_region  (formed in double, stored float32)
+ *     new_frame[y0:y1, x0:x1, c] = cv2.remap(next_frame[:, :, c], map_x, map_y, INTER_LINEAR, borderMode=BORDER_REPLICATE)
+ * with OpenCV's 8-bit fixed-point bilinear (coordinates rounded to 1/32 px, 15-bit weights, taps clamped).
+ * `frame` is the whole source image (H x W x channels, interleaved), `flow` the region's flow (h x w x 2 float32),
+ * `out` the region of the destination image; flow_sign -1 applies the reference's `flow = -flow` first.  Bit-exact. */
+typedef struct nsof_warp_desc {
+    const uint8_t *frame; ptrdiff_t frame_pitch; int H, W, channels;
+    const float *flow; ptrdiff_t flow_pitch;
+    int x0, y0, h, w;
+    uint8_t *out; ptrdiff_t out_pitch;
+} nsof_warp_desc;
+NSOF_API int nsof_remap_flow_batch(nsof_handle *h, const nsof_warp_desc *items, int n, int flow_sign, void *cuda_stream);
+NSOF_API int nsof_remap_flow_host(nsof_handle *h, const uint8_t *frame, ptrdiff_t frame_pitch, int H, int W, int channels,
+                                  const float *flow, ptrdiff_t flow_pitch, int x0, int y0, int height, int width,
+                                  int flow_sign, uint8_t *out, ptrdiff_t out_pitch);
+
 #ifdef __cplusplus
 }
 #endif

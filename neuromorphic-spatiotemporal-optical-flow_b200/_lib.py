@@ -76,6 +76,12 @@ class SegDesc(C.Structure):  # nsof_seg_desc
                 ("mask", C.c_void_p), ("mask_pitch", C.c_ssize_t)]
 
 
+class WarpDesc(C.Structure):  # nsof_warp_desc
+    _fields_ = [("frame", C.c_void_p), ("frame_pitch", C.c_ssize_t), ("H", C.c_int), ("W", C.c_int), ("channels", C.c_int),
+                ("flow", C.c_void_p), ("flow_pitch", C.c_ssize_t), ("x0", C.c_int), ("y0", C.c_int), ("h", C.c_int),
+                ("w", C.c_int), ("out", C.c_void_p), ("out_pitch", C.c_ssize_t)]
+
+
 class KernelStat(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("launches", C.c_int), ("ms", C.c_double), ("algorithmic_bytes", C.c_double)]
 
@@ -114,6 +120,12 @@ _SIGNATURES = {
     "nsof_flow_segment_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, _P(SegParams),
                                          C.c_void_p, C.c_ssize_t]),
     "nsof_structuring_element": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "nsof_rgb2gray_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                   C.c_ssize_t, C.c_ssize_t, C.c_void_p]),
+    "nsof_rgb2gray_u8_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_void_p, C.c_ssize_t]),
+    "nsof_remap_flow_batch": (C.c_int, [C.c_void_p, _P(WarpDesc), C.c_int, C.c_int, C.c_void_p]),
+    "nsof_remap_flow_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                       C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_ssize_t]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),

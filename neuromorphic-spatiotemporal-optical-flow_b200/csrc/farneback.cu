@@ -130,6 +130,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
     h->io.release();
     h->s1.release();
     h->seg.release();
+    h->warp_tab.release();
     h->lz.release();
     for (auto &s : h->stage) {
         if (s.host) cudaFreeHost(s.host);
@@ -154,7 +155,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
     "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload",
-    "seg_pack", "seg_morph", "seg_unpack"};
+    "seg_pack", "seg_morph", "seg_unpack", "rgb2gray", "remap_flow"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 

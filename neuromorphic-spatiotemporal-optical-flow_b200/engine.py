@@ -23,7 +23,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (CropDesc, FbParams, FrameSimParams, Library, Rect, RoiParams, SegDesc, SegParams, SynapseParams,
-                   error)
+                   WarpDesc, error)
 
 # PARAMS of eventsim/event_mem_sim.py:20-27 == simulation/simulationcode_v4_transistor_vehicle.m:26-33
 PARAMS = dict(alphaoff=1, alphaon=1, voff=-0.2, von=0.1, koff=51.03, kon=-2.91, son=0.2, soff=0.8, bon=-5.12,
@@ -412,6 +412,70 @@ class Engine:
                 if y1 > y0 and x1 > x0:
                     motion_binary[y0:y1, x0:x1] = self.segment_flow(flow[y0:y1, x0:x1], seg_th)
         return motion_binary
+
+    # ------------------------------------------------------------------ frames either side of the path (8(f) 2, 3)
+    def cvtColor_rgb2gray(self, frame):
+        """cv2.cvtColor(frame, cv2.COLOR_RGB2GRAY) for a uint8 (H, W, 3) array, channels as stored
+        (optical_flow_seg.py:442-443 passes the BGR frame of cv2.imread)."""
+        f = np.asarray(frame)
+        if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3 or f.shape[0] < 1 or f.shape[1] < 1:
+            raise error("frame must be a non-empty uint8 (H, W, 3) array")
+        if f.strides[1:] != (3, 1):
+            f = np.ascontiguousarray(f)
+        H, W = f.shape[:2]
+        out = np.empty((H, W), dtype=np.uint8)
+        self.lib.check(self.lib.nsof_rgb2gray_u8_host(self.handle, f.ctypes.data, f.strides[0], H, W, out.ctypes.data,
+                                                      out.strides[0]), "cvtColor_rgb2gray")
+        return out
+
+    def remap_flow(self, next_frame, flow_region, x_min, y_min, flow_sign=1):
+        """optical_flow_prediction.py:281-297 for one region: flow_map = (x, y) + flow_region as float32, every channel
+        of `next_frame` (uint8 (H, W) or (H, W, C)) remapped with INTER_LINEAR / BORDER_REPLICATE -> uint8 region."""
+        img = np.asarray(next_frame)
+        if img.dtype != np.uint8 or img.ndim not in (2, 3) or img.size == 0:
+            raise error("next_frame must be a non-empty uint8 (H, W[, C]) array")
+        img3 = np.ascontiguousarray(img.reshape(img.shape[0], img.shape[1], -1))
+        fl = np.asarray(flow_region)
+        if fl.ndim != 3 or fl.shape[2] != 2 or fl.shape[0] < 1 or fl.shape[1] < 1:
+            raise error("flow region must be a non-empty (h, w, 2) array")
+        f32 = np.ascontiguousarray(fl, dtype=np.float32)
+        if fl.dtype != np.float32 and not np.array_equal(f32.astype(fl.dtype), fl, equal_nan=True):
+            raise error("flow region holds values that are not float32-representable")
+        H, W, ch = img3.shape
+        h, w = f32.shape[:2]
+        out = np.empty((h, w, ch), dtype=np.uint8)
+        self.lib.check(self.lib.nsof_remap_flow_host(self.handle, img3.ctypes.data, img3.strides[0], H, W, ch, f32.ctypes.data,
+                                                     f32.strides[0], int(x_min), int(y_min), h, w, int(flow_sign),
+                                                     out.ctypes.data, out.strides[0]), "remap_flow")
+        return out if img.ndim == 3 else out[..., 0]
+
+    def remap_flow_device(self, regions, stream_ptr: int = 0, flow_sign=1):
+        """`regions`: list of WarpDesc field tuples (frame_ptr, frame_pitch, H, W, channels, flow_ptr, flow_pitch, x0, y0,
+        h, w, out_ptr, out_pitch) with raw device addresses; one launch, asynchronous on the stream."""
+        n = len(regions)
+        descs = (WarpDesc * max(n, 1))()
+        for i, r in enumerate(regions):
+            descs[i] = WarpDesc(*r)
+        self.lib.check(self.lib.nsof_remap_flow_batch(self.handle, descs, n, int(flow_sign), C.c_void_p(stream_ptr)),
+                       "remap_flow_device")
+
+    def predict_frame(self, prev_frame, next_frame, flow, num_labels, regions_info, EST_FLAG=2, MERGE_FLAG=True, padding=0):
+        """task_results of optical_flow_prediction.py:257-361: next_frame with every region replaced by its
+        flow-extrapolated version."""
+        h, w = prev_frame.shape[:2]
+        new_frame = np.array(next_frame, copy=True)
+        if num_labels > 1:
+            if EST_FLAG == 1 and MERGE_FLAG:
+                boxes = [(max(0, min(r[0] for r in regions_info) - padding), max(0, min(r[1] for r in regions_info) - padding),
+                          min(w, max(r[2] for r in regions_info) + padding), min(h, max(r[3] for r in regions_info) + padding))]
+            elif EST_FLAG == 1:
+                boxes = [tuple(r) for r in regions_info]
+            else:
+                boxes = [tuple(regions_info)]
+            for x0, y0, x1, y1 in boxes:
+                if y1 > y0 and x1 > x0:
+                    new_frame[y0:y1, x0:x1] = self.remap_flow(next_frame, flow[y0:y1, x0:x1], x0, y0)
+        return new_frame
 
     def structuring_element(self, shape, ksize):
         """cv2.getStructuringElement(shape, ksize) as the segmentation passes build it."""

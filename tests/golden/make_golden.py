@@ -306,7 +306,58 @@ def make_segment():
                                           cases[k].shape[0] * cases[k].shape[1]) for k in cases})
 
 
+def make_frames():
+    """cv2.cvtColor(COLOR_RGB2GRAY) as the scripts call it (optical_flow_seg.py:439-443) on crops of real frames, and
+    the reference's own prediction `task_results` (optical_flow_prediction.py:257-361, source-sliced) on flow fields."""
+    import glob
+    import time
+    src = open(os.path.join(REF, "optical_flow_prediction.py"), encoding="utf-8").read()
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "task_results"]
+    ns = dict(cv2=cv2, np=np, time=time, PADDING=10, mem_combination_times=[], mem_task_times=[])
+    exec(compile(ast.Module(body=body, type_ignores=[]), "optical_flow_prediction.py", "exec"), ns)
+    ref_task = ns["task_results"]
+    rng = np.random.default_rng(99)
+    out = {}
+    files = sorted(glob.glob(os.path.join(REF, "data", "grasp", "RGB", "*.jpg")))[:2]
+    frames = [cv2.imread(f) for f in files]
+    # grey: two real crops + a random frame with odd width (every residue of the 4-pixel groups)
+    greys = {"grasp_a": frames[0][300:420, 200:457], "grasp_b": frames[1][800:899, 500:763],
+             "random": rng.integers(0, 256, (37, 131, 3), dtype=np.uint8)}
+    for k, f in greys.items():
+        f = np.ascontiguousarray(f)
+        out[f"grey__{k}__in"] = f
+        out[f"grey__{k}__out"] = cv2.cvtColor(f, cv2.COLOR_RGB2GRAY)
+    # prediction: a real frame crop as next_frame, smooth + noisy flow, regions touching the borders (replicate)
+    nf = np.ascontiguousarray(frames[1][600:840, 300:620])      # 240 x 320 x 3
+    H, W = nf.shape[:2]
+    smooth = cv2.GaussianBlur(rng.standard_normal((H, W, 2)).astype(np.float32) * 40, (0, 0), 9)
+    flow = (smooth + rng.standard_normal((H, W, 2)).astype(np.float32) * 0.5).astype(np.float32)
+    flow[5, 7] = (0.5, -0.5)          # ties of the 1/32 rounding
+    flow[6, 8] = (1.0 / 64, 3.0 / 64)
+    flow[0, 0] = (-30.0, -30.0)       # far outside: replicate
+    flow[H - 1, W - 1] = (1e4, 1e4)
+    out["pred__next"] = nf
+    out["pred__flow"] = flow
+    rects = {"whole": (0, 0, W, H), "inner": (37, 21, 250, 190), "corner": (200, 150, W, H), "thin": (10, 100, 11, 180)}
+    for k, r in rects.items():
+        got = ref_task(nf, nf, flow, 2, r, 2, True)
+        assert got.shape == nf.shape and got.dtype == np.uint8
+        out[f"pred__{k}__rect"] = np.array(r)
+        out[f"pred__{k}__out"] = got
+    # EST_FLAG 1, merged, PADDING 10 (optical_flow_prediction.py:269-300)
+    regs = [(60, 40, 120, 90), (150, 100, 230, 170)]
+    out["pred__merge__regions"] = np.array(regs)
+    out["pred__merge__out"] = ref_task(nf, nf, flow, 3, regs, 1, True)
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(OUT, "frames_reference.npz"), **out)
+    print("frames_reference.npz", {k: v.shape for k, v in out.items() if hasattr(v, "shape") and v.ndim >= 2})
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "frames":
+        make_frames()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "scheme2":
         make_events_scheme2()
         sys.exit(0)
@@ -318,3 +369,4 @@ if __name__ == "__main__":
     make_events()
     make_events_scheme2()
     make_segment()
+    make_frames()

@@ -90,6 +90,7 @@ class Golden:
         self.ev = np.load(os.path.join(GOLDEN, "events_reference.npz"))
         self.ev2 = np.load(os.path.join(GOLDEN, "events_scheme2_reference.npz"))
         self.seg = np.load(os.path.join(GOLDEN, "segment_reference.npz"))
+        self.frames = np.load(os.path.join(GOLDEN, "frames_reference.npz"))
 
 
 def segment_cases(seg):
@@ -152,3 +153,25 @@ def assert_flow_close(got, want, pname, what=""):
 
 def planar_to_aos(p):
     return np.ascontiguousarray(np.moveaxis(p, 0, -1))
+
+
+def check_frames_against_golden(fr, rgb2gray, remap_flow, predict_frame):
+    """Shared by the oracle, emulator and GPU tests: `fr` = frames_reference.npz; the three callables are the
+    implementation under test.  Everything bit-exact."""
+    for k in ("grasp_a", "grasp_b", "random"):
+        assert np.array_equal(rgb2gray(fr[f"grey__{k}__in"]), fr[f"grey__{k}__out"]), k
+    nf, flow = fr["pred__next"], fr["pred__flow"]
+    for k in ("whole", "inner", "corner", "thin"):
+        x0, y0, x1, y1 = (int(v) for v in fr[f"pred__{k}__rect"])
+        want = fr[f"pred__{k}__out"]
+        got = remap_flow(nf, flow[y0:y1, x0:x1], x0, y0)
+        assert np.array_equal(got, want[y0:y1, x0:x1]), k
+        full = predict_frame(nf, nf, flow, 2, (x0, y0, x1, y1), 2, True)
+        assert np.array_equal(full, want), k
+    if predict_frame is not None:
+        regs = [tuple(int(v) for v in r) for r in fr["pred__merge__regions"]]
+        assert np.array_equal(predict_frame(nf, nf, flow, 3, regs, 1, True, 10), fr["pred__merge__out"])
+    # a single channel, the reference's float64 flow dtype
+    x0, y0, x1, y1 = (int(v) for v in fr["pred__inner__rect"])
+    got = remap_flow(np.ascontiguousarray(nf[:, :, 1]), flow[y0:y1, x0:x1].astype(np.float64), x0, y0)
+    assert np.array_equal(got, fr["pred__inner__out"][y0:y1, x0:x1, 1])

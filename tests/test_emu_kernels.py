@@ -253,3 +253,17 @@ def test_emu_segment_vs_reference_and_oracle(emu_engine, golden):
     f[2, 7] = np.nan
     m = emu_engine.segment_flow(f, seg_th=-1.0, iterations=0)
     assert m[2, 7] == 0 and (m > 0).sum() == 5 * 40 - 1
+
+
+def test_emu_frames_vs_reference(emu_engine, golden):
+    """Grey conversion and flow-extrapolation kernels (emulator build) vs cv2 / the reference's task_results."""
+    helpers.check_frames_against_golden(golden.frames, emu_engine.cvtColor_rgb2gray, emu_engine.remap_flow,
+                                        emu_engine.predict_frame)
+    with pytest.raises(Exception):
+        emu_engine.cvtColor_rgb2gray(np.zeros((4, 4), np.uint8))
+    with pytest.raises(Exception):
+        emu_engine.remap_flow(np.zeros((4, 4, 3), np.uint8), np.zeros((0, 3, 2), np.float32), 0, 0)
+    # flow_sign -1 == the reference's `flow = -flow` applied first
+    nf, flow = golden.frames["pred__next"], golden.frames["pred__flow"]
+    assert np.array_equal(emu_engine.remap_flow(nf, -flow[20:60, 30:90], 30, 20, flow_sign=-1),
+                          emu_engine.remap_flow(nf, flow[20:60, 30:90], 30, 20))

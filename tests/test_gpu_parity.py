@@ -430,6 +430,37 @@ def test_segment_vs_reference(gpu_engine, golden):
         gpu_engine.segment_flow(flow, ksize=(33, 3))
 
 
+def test_frames_vs_reference(gpu_engine, golden):
+    """grey conversion and the prediction warp vs cv2 / the reference's own task_results, bit
+    for bit; the device batch entry points on strided frames."""
+    import torch
+    from oracle import frames_oracle as fo
+    helpers.check_frames_against_golden(golden.frames, gpu_engine.cvtColor_rgb2gray, gpu_engine.remap_flow,
+                                        gpu_engine.predict_frame)
+    rng = np.random.default_rng(3)
+    bgr = rng.integers(0, 256, (5, 270, 481, 3), dtype=np.uint8)
+    d_bgr = torch.from_numpy(bgr).cuda()
+    d_grey = torch.zeros((5, 270, 512), dtype=torch.uint8, device="cuda")  # pitched destination
+    gpu_engine.lib.check(gpu_engine.lib.nsof_rgb2gray_u8(gpu_engine.handle, d_bgr.data_ptr(), 481 * 3, 270 * 481 * 3, 5, 270, 481,
+                                                         d_grey.data_ptr(), 512, 270 * 512,
+                                                         torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    got = d_grey.cpu().numpy()
+    assert np.array_equal(got[:, :, :481], np.stack([fo.rgb2gray(f) for f in bgr])) and not got[:, :, 481:].any()
+    # two regions of two different frames in one launch, written into copies of the frames
+    flow = (rng.standard_normal((2, 270, 481, 2)) * 5).astype(np.float32)
+    d_flow, d_out = torch.from_numpy(flow).cuda(), d_bgr[:2].clone()
+    rects = [(11, 7, 300, 200), (100, 50, 481, 270)]
+    regions = []
+    for i, (x0, y0, x1, y1) in enumerate(rects):
+        regions.append((d_bgr[i].data_ptr(), 481 * 3, 270, 481, 3, d_flow[i].data_ptr() + (y0 * 481 + x0) * 8, 481 * 8, x0, y0,
+                        y1 - y0, x1 - x0, d_out[i].data_ptr() + (y0 * 481 + x0) * 3, 481 * 3))
+    gpu_engine.remap_flow_device(regions, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for i, r in enumerate(rects):
+        assert np.array_equal(d_out[i].cpu().numpy(), fo.task_results(bgr[i], bgr[i], flow[i], r)), i
+
+
 def test_sequence_step_with_segmentation(gpu_engine, nsof):
     """segment=True: the motion_binary frames of the device-resident step equal task_results of the step's own flow
     frames (restatement pinned to the reference), zero outside the rectangles, also after a second step on other

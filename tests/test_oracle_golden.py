@@ -114,3 +114,19 @@ def test_segment_oracle_matches_reference(golden):
     frame[10:43, 5:70] = next(f for n, f, _, _ in helpers.segment_cases(seg) if n == "noise_33x65")
     mb = so.task_results((60, 80), frame, (5, 10, 70, 43))
     assert mb[10:43, 5:70].any() and not mb[:10].any() and not mb[:, 70:].any()
+
+
+def test_frames_oracle_matches_reference(golden):
+    """oracle/frames_oracle.py vs cv2.cvtColor(RGB2GRAY) on real frames and the reference's own prediction
+    task_results (cv2.remap INTER_LINEAR / BORDER_REPLICATE per channel): bit for bit."""
+    from oracle import frames_oracle as fo
+
+    def predict(prev, nxt, flow, num_labels, regions, est, merge, padding=0):
+        if est == 2:
+            return fo.task_results(prev, nxt, flow, regions)
+        h, w = prev.shape[:2]
+        r = (max(0, min(q[0] for q in regions) - padding), max(0, min(q[1] for q in regions) - padding),
+             min(w, max(q[2] for q in regions) + padding), min(h, max(q[3] for q in regions) + padding))
+        return fo.task_results(prev, nxt, flow, r)
+
+    helpers.check_frames_against_golden(golden.frames, fo.rgb2gray, fo.remap_flow, predict)
