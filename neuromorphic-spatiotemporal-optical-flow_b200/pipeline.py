@@ -243,21 +243,33 @@ class SequencePipeline:
 
     def step(self, frames):
         """One pass of the hot path over the rank's clips, inputs and outputs resident in HBM."""
+        self.begin(frames)
+        return self.finish(frames)
+
+    def begin(self, frames):
+        """First half of a step, no host wait: clear the previous step's flow rectangles and queue stage 1 of every
+        chunk on the side stream (overlap=True).  `DeviceStream` calls this for step k before it finishes step k-1."""
         t = self.torch
         self.clear_previous()
+        if self.full_frame or not self.overlap:
+            return
+        cur = t.cuda.current_stream(self.dev)
+        self.side.wait_stream(cur)  # frames (and everything queued so far) are ordered before stage 1
+        for _, st in self.s2_extra:
+            st.wait_stream(cur)     # ... and before stage 2 on the extra streams (flow_clear included)
+        with t.cuda.stream(self.side):
+            for j in range(len(self.chunks)):
+                self.stage1_chunk(frames, j)
+                self.ev_chunk[j].record(self.side)
+
+    def finish(self, frames):
+        """Second half: per chunk, wait for its rectangles on the host and queue its Farneback batch."""
+        t = self.torch
         if self.full_frame:
             n, px = self.build_descs(frames, None, None)
             self.stage2(0, n)
         else:
             cur = t.cuda.current_stream(self.dev)
-            if self.overlap:
-                self.side.wait_stream(cur)  # frames (and the previous step) are ordered before stage 1
-                for _, st in self.s2_extra:
-                    st.wait_stream(cur)     # ... and before stage 2 on the extra streams (flow_clear included)
-                with t.cuda.stream(self.side):
-                    for j in range(len(self.chunks)):
-                        self.stage1_chunk(frames, j)
-                        self.ev_chunk[j].record(self.side)
             n = px = 0
             for j, pr in enumerate(self.chunks):
                 if self.overlap:
@@ -277,6 +289,54 @@ class SequencePipeline:
         self.last_crop_pixels = px
         self.packed_floats = px * 2
         return n
+
+
+class DeviceStream:
+    """A stream of device-resident steps through `depth` SequencePipeline slots, ONE Farneback batch per step.
+
+    `SequencePipeline.step` hides the latency-bound synapse chains of stage 1 under stage 2 of the SAME step, which
+    forces the step into small time chunks (a Farneback batch needs its rectangles) and the coarse pyramid levels of a
+    small batch do not fill the machine.  Here stage 1 of step k runs under the Farneback batch of step k-1 instead:
+    every step is one batch of all its pairs (measured 4.0 ms against 4.9 ms chunked for 120 pairs), and the host
+    waits for rectangles that have been ready for a whole step.
+
+        submit(frames) -> the pipeline slot holding the results (.flow, .last_rects, .motion) of the PREVIOUS step,
+                          valid until `depth - 1` more submits; None for the first
+        drain()        -> finishes the step still in flight and returns its slot
+    """
+
+    def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
+                 depth: int = 2, segment: bool = False, full_frame: bool = False):
+        assert depth >= 2
+        one = [(0, int(frames) - 1)]
+        self.slots = [SequencePipeline(engine if i == 0 else Engine(engine.device, lib=engine.lib), clips, frames, H, W, cfg,
+                                       chunks=one, overlap=True, s2_streams=1, segment=segment, full_frame=full_frame)
+                      for i in range(depth)]
+        self.k = 0
+        self.pending = None  # (slot, frames) of the step whose stage 1 is queued
+
+    @property
+    def n_pairs(self):
+        return self.slots[0].n_pairs
+
+    def launch_count(self) -> int:
+        return sum(s.launch_count() for s in self.slots)
+
+    def submit(self, frames):
+        slot = self.slots[self.k % len(self.slots)]
+        self.k += 1
+        slot.begin(frames)          # stage 1 of this step: side stream, behind everything queued so far
+        done = self.drain()         # Farneback batch of the previous step: runs beside it
+        self.pending = (slot, frames)
+        return done
+
+    def drain(self):
+        if self.pending is None:
+            return None
+        slot, frames = self.pending
+        self.pending = None
+        slot.finish(frames)
+        return slot
 
 
 class HostPipeline:

@@ -498,6 +498,40 @@ def test_sequence_step_with_segmentation(gpu_engine, nsof):
                 assert np.array_equal(m, motion[t, c, y0:y1, x0:x1]), (t, c)
 
 
+def test_device_stream_matches_synchronous_steps(gpu_engine, nsof):
+    """Four steps on different clips through DeviceStream (stage 1 of step k under the Farneback batch of step k-1,
+    two slots reused) return, one submit later, exactly the flow frames and rectangles of synchronous steps."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    steps = [torch.stack([syn.make_clip(900 + 7 * k + c, 400, 560, 6, "cpu", velocity=(3.0 - k, 1.0 + 0.5 * c))
+                          for c in range(3)], dim=1).cuda().contiguous() for k in range(4)]
+    F, _, H, W = steps[0].shape
+    ref = pm.SequencePipeline(gpu_engine, 3, F, H, W, overlap=False, chunks=[(0, F - 1)])
+    want = []
+    for fr in steps:
+        ref.step(fr)
+        torch.cuda.synchronize()
+        want.append((ref.flow.clone(), ref.last_rects[0].copy(), ref.last_rects[1].copy()))
+    ds = pm.DeviceStream(gpu_engine, 3, F, H, W, depth=2)
+    got = []
+    for fr in steps:
+        done = ds.submit(fr)
+        if done is not None:
+            torch.cuda.synchronize()
+            got.append((done.flow.clone(), done.last_rects[0].copy(), done.last_rects[1].copy()))
+    done = ds.drain()
+    torch.cuda.synchronize()
+    got.append((done.flow.clone(), done.last_rects[0].copy(), done.last_rects[1].copy()))
+    assert len(got) == 4 and ds.drain() is None
+    for k, ((gf, gr, gn), (wf, wr, wn)) in enumerate(zip(got, want)):
+        assert np.array_equal(gn, wn) and np.array_equal(gr[gn > 0], wr[wn > 0]), k
+        assert torch.equal(gf, wf), k
+        assert int((gn > 0).sum()) >= 6
+
+
 def test_sequence_step_repeat_and_serial_schedule(gpu_engine, nsof):
     """The flow frames are zeroed by clearing the previous step's rectangles only (nsof_flow_clear): a second step on
     DIFFERENT clips must equal a fresh pipeline's result bit for bit, and the overlapped chunk schedule must equal the
