@@ -1041,24 +1041,56 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_REST
         NSOF_SYNC();
     }
     const float g0 = sg[0];
-    for (int sy = warp; sy < shn; sy += nw) {
-        const uint8_t *row = sS + sy * SWp + shift;
-        for (int ci = lane; ci < 2 * twn; ci += NSOF_WARP) {
-            const uint8_t *c = row + (cols[ci] - Xmin);
-            float acc = g0 * (float)c[0];
+    // Each output is a serial chain of r dependent FMAs (the order of the sum is OpenCV's), and a CTA runs at 8 warps:
+    // every thread carries FOUR independent chains (2 rows x 2 columns) through the tap loop so the chains hide each
+    // other's latency.  Outputs outside the tile are computed on clamped addresses and not stored.
+    for (int sy = 2 * warp; sy < shn; sy += 2 * nw) {
+        const bool rb = sy + 1 < shn;
+        const uint8_t *row0 = sS + sy * SWp + shift, *row1 = sS + (rb ? sy + 1 : sy) * SWp + shift;
+        for (int ci = lane; ci < 2 * twn; ci += 2 * NSOF_WARP) {
+            const bool cb = ci + NSOF_WARP < 2 * twn;
+            const int o0 = cols[ci] - Xmin, o1 = cols[cb ? ci + NSOF_WARP : ci] - Xmin;
+            const uint8_t *c00 = row0 + o0, *c01 = row0 + o1, *c10 = row1 + o0, *c11 = row1 + o1;
+            float a00 = g0 * (float)c00[0], a01 = g0 * (float)c01[0], a10 = g0 * (float)c10[0], a11 = g0 * (float)c11[0];
             // the two taps at distance i are added as integers (exact) and converted once
-            for (int i = 1; i <= r; i++) acc = acc + sg[i] * (float)((int)c[-i] + (int)c[i]);
-            sHb[sy * 2 * TW + ci] = acc;
+            for (int i = 1; i <= r; i++) {
+                const float g = sg[i];
+                a00 = a00 + g * (float)((int)c00[-i] + (int)c00[i]);
+                a01 = a01 + g * (float)((int)c01[-i] + (int)c01[i]);
+                a10 = a10 + g * (float)((int)c10[-i] + (int)c10[i]);
+                a11 = a11 + g * (float)((int)c11[-i] + (int)c11[i]);
+            }
+            sHb[sy * 2 * TW + ci] = a00;
+            if (cb) sHb[sy * 2 * TW + ci + NSOF_WARP] = a01;
+            if (rb) {
+                sHb[(sy + 1) * 2 * TW + ci] = a10;
+                if (cb) sHb[(sy + 1) * 2 * TW + ci + NSOF_WARP] = a11;
+            }
         }
     }
     NSOF_SYNC();
-    for (int ri = warp; ri < 2 * thn; ri += nw) {
-        const float *rowc = sHb + (rows[ri] - Ymin) * 2 * TW;
-        for (int ci = lane; ci < 2 * twn; ci += NSOF_WARP) {
-            const float *c = rowc + ci;
-            float acc = g0 * c[0];
-            for (int i = 1; i <= r; i++) acc = acc + sg[i] * (c[-i * 2 * TW] + c[i * 2 * TW]);
-            sB[ri * 2 * TW + ci] = acc;
+    for (int ri = 2 * warp; ri < 2 * thn; ri += 2 * nw) {
+        const bool rb = ri + 1 < 2 * thn;
+        const float *rowc0 = sHb + (rows[ri] - Ymin) * 2 * TW, *rowc1 = sHb + (rows[rb ? ri + 1 : ri] - Ymin) * 2 * TW;
+        for (int ci = lane; ci < 2 * twn; ci += 2 * NSOF_WARP) {
+            const bool cb = ci + NSOF_WARP < 2 * twn;
+            const int c1 = cb ? ci + NSOF_WARP : ci;
+            const float *c00 = rowc0 + ci, *c01 = rowc0 + c1, *c10 = rowc1 + ci, *c11 = rowc1 + c1;
+            float a00 = g0 * c00[0], a01 = g0 * c01[0], a10 = g0 * c10[0], a11 = g0 * c11[0];
+            for (int i = 1; i <= r; i++) {
+                const float g = sg[i];
+                const int d = i * 2 * TW;
+                a00 = a00 + g * (c00[-d] + c00[d]);
+                a01 = a01 + g * (c01[-d] + c01[d]);
+                a10 = a10 + g * (c10[-d] + c10[d]);
+                a11 = a11 + g * (c11[-d] + c11[d]);
+            }
+            sB[ri * 2 * TW + ci] = a00;
+            if (cb) sB[ri * 2 * TW + c1] = a01;
+            if (rb) {
+                sB[(ri + 1) * 2 * TW + ci] = a10;
+                if (cb) sB[(ri + 1) * 2 * TW + c1] = a11;
+            }
         }
     }
     NSOF_SYNC();
