@@ -343,6 +343,9 @@ typedef struct nsof_seg_desc {
  * over all regions, unpack).  Asynchronous on `cuda_stream`. */
 NSOF_API int nsof_flow_segment_batch(nsof_handle *h, const nsof_seg_desc *items, int n, const nsof_seg_params *params,
                                      void *cuda_stream);
+/* `motion_binary = np.zeros((h, w))` of the next frame pair (optical_flow_seg.py:262) for a driver that owns its mask
+ * frames: zero the mask rectangles of `n` regions (only .mask, .mask_pitch, .h, .w are read) in one launch. */
+NSOF_API int nsof_mask_clear(nsof_handle *h, const nsof_seg_desc *items, int n, void *cuda_stream);
 /* One region with HOST pointers (flow in, mask out), synchronous: the call a `process_flow_region` drop-in makes
  * for numpy arrays. */
 NSOF_API int nsof_flow_segment_host(nsof_handle *h, const float *flow, ptrdiff_t flow_pitch, int height, int width,

@@ -117,6 +117,7 @@ _SIGNATURES = {
     "nsof_copy_blocks": (C.c_int, [C.c_void_p, _P(CopyBlock), C.c_int, C.c_void_p]),
     "nsof_copy_blocks_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_double, C.c_void_p]),
     "nsof_flow_segment_batch": (C.c_int, [C.c_void_p, _P(SegDesc), C.c_int, _P(SegParams), C.c_void_p]),
+    "nsof_mask_clear": (C.c_int, [C.c_void_p, _P(SegDesc), C.c_int, C.c_void_p]),
     "nsof_flow_segment_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, _P(SegParams),
                                          C.c_void_p, C.c_ssize_t]),
     "nsof_structuring_element": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p]),

@@ -72,29 +72,51 @@ NSOF_HD int frames_cv_round(float v)
 #endif
 }
 
-// grid (chunks, regions): one output pixel (all channels) per thread
+// one output pixel: fixed-point coordinates, four clamped taps per channel
+NSOF_DEV void remap_pixel(const WarpJob &J, int x, int y, float sign, uint8_t *px)
+{
+    const float2 f = *(const float2 *)(J.flow + (size_t)y * J.flow_pitch + 2 * x);
+    // flow_map = (coords + flow).astype(float32): the sum is formed in double (int64 + float promote to float64)
+    const float mx = (float)((double)(J.x0 + x) + (double)(sign * f.x));
+    const float my = (float)((double)(J.y0 + y) + (double)(sign * f.y));
+    const int sx = frames_cv_round(mx * 32.f), sy = frames_cv_round(my * 32.f);
+    const int ax = sx & 31, ay = sy & 31;
+    const int ix = nsof_clampi(sx >> 5, -32768, 32767), iy = nsof_clampi(sy >> 5, -32768, 32767);  // saturate_cast<short>
+    const int xa = nsof_clampi(ix, 0, J.W - 1), xb = nsof_clampi(ix + 1, 0, J.W - 1);
+    const int ya = nsof_clampi(iy, 0, J.H - 1), yb = nsof_clampi(iy + 1, 0, J.H - 1);
+    const int w00 = (32 - ax) * (32 - ay) * 32, w01 = ax * (32 - ay) * 32, w10 = (32 - ax) * ay * 32, w11 = ax * ay * 32;
+    const uint8_t *ra = J.frame + (size_t)ya * J.fpitch_bytes, *rb = J.frame + (size_t)yb * J.fpitch_bytes;
+    for (int c = 0; c < J.ch; c++) {
+        const int v = (int)NSOF_LDG(ra + xa * J.ch + c) * w00 + (int)NSOF_LDG(ra + xb * J.ch + c) * w01 +
+                      (int)NSOF_LDG(rb + xa * J.ch + c) * w10 + (int)NSOF_LDG(rb + xb * J.ch + c) * w11;
+        px[c] = (uint8_t)((v + 16384) >> 15);
+    }
+}
+
+// grid (chunks, regions): four output pixels (all channels) per thread; for 3-channel images whose output rows are
+// 4-byte aligned the 12 bytes leave as three words
 NSOF_GLOBAL k_remap_flow(const WarpJob *NSOF_RESTRICT jobs, float sign)
 {
     const WarpJob J = jobs[NSOF_BY];
-    const int total = J.h * J.w;
+    const int qw = (J.w + 3) / 4, total = J.h * qw;
     for (int idx = NSOF_BX * NSOF_NT + NSOF_TID; idx < total; idx += nsof_grid_x() * NSOF_NT) {
-        const int y = idx / J.w, x = idx - y * J.w;
-        const float2 f = *(const float2 *)(J.flow + (size_t)y * J.flow_pitch + 2 * x);
-        // flow_map = (coords + flow).astype(float32): the sum is formed in double (int64 + float promote to float64)
-        const float mx = (float)((double)(J.x0 + x) + (double)(sign * f.x));
-        const float my = (float)((double)(J.y0 + y) + (double)(sign * f.y));
-        const int sx = frames_cv_round(mx * 32.f), sy = frames_cv_round(my * 32.f);
-        const int ax = sx & 31, ay = sy & 31;
-        const int ix = nsof_clampi(sx >> 5, -32768, 32767), iy = nsof_clampi(sy >> 5, -32768, 32767);  // saturate_cast<short>
-        const int xa = nsof_clampi(ix, 0, J.W - 1), xb = nsof_clampi(ix + 1, 0, J.W - 1);
-        const int ya = nsof_clampi(iy, 0, J.H - 1), yb = nsof_clampi(iy + 1, 0, J.H - 1);
-        const int w00 = (32 - ax) * (32 - ay) * 32, w01 = ax * (32 - ay) * 32, w10 = (32 - ax) * ay * 32, w11 = ax * ay * 32;
-        const uint8_t *ra = J.frame + (size_t)ya * J.fpitch_bytes, *rb = J.frame + (size_t)yb * J.fpitch_bytes;
+        const int y = idx / qw, x = (idx - y * qw) * 4;
         uint8_t *o = J.out + (size_t)y * J.opitch + (size_t)x * J.ch;
-        for (int c = 0; c < J.ch; c++) {
-            const int v = (int)NSOF_LDG(ra + xa * J.ch + c) * w00 + (int)NSOF_LDG(ra + xb * J.ch + c) * w01 +
-                          (int)NSOF_LDG(rb + xa * J.ch + c) * w10 + (int)NSOF_LDG(rb + xb * J.ch + c) * w11;
-            o[c] = (uint8_t)((v + 16384) >> 15);
+        const int nq = nsof_imin(4, J.w - x);
+        if (J.ch == 3 && nq == 4 && (((uintptr_t)o) & 3) == 0) {
+            uint8_t b[12];
+#pragma unroll
+            for (int q = 0; q < 4; q++) remap_pixel(J, x + q, y, sign, b + 3 * q);
+            uint32_t *o4 = (uint32_t *)o;
+#pragma unroll
+            for (int k = 0; k < 3; k++)
+                o4[k] = (uint32_t)b[4 * k] | ((uint32_t)b[4 * k + 1] << 8) | ((uint32_t)b[4 * k + 2] << 16) | ((uint32_t)b[4 * k + 3] << 24);
+        } else {
+            for (int q = 0; q < nq; q++) {
+                uint8_t b[4];
+                remap_pixel(J, x + q, y, sign, b);
+                for (int c = 0; c < J.ch; c++) o[q * J.ch + c] = b[c];
+            }
         }
     }
 }
@@ -168,7 +190,7 @@ extern "C" int nsof_remap_flow_batch(nsof_handle *h, const nsof_warp_desc *items
     }
     rc = nsof_table_upload(h, h->warp_tab.p, slot, bytes, stream);
     if (rc) return rc;
-    const int gx = std::max(1, std::min((max_px + 255) / 256, 2048));
+    const int gx = std::max(1, std::min((max_px / 4 + 255) / 256, 2048));
     NSOF_KLAUNCH(h, NSOF_K_REMAP, px, k_remap_flow, gx, n, 1, 256, 0, stream, (const WarpJob *)h->warp_tab.p, (float)flow_sign);
     NSOF_CUDA_TRY(cudaGetLastError());
     return NSOF_OK;

@@ -37,6 +37,18 @@ for seg in (False, True):
     res[seg] = t_step(pipe)
     print(f"step segment={seg}: {res[seg]:.3f} ms  ({pipe.n_pairs / res[seg] * 1e3:.0f} pairs/s)", flush=True)
     if seg:
+        for label, chunks in (("time chunks 1,2,4,4,4", None), ("one batch per step", [(0, F - 1)])):
+            ser = pm.SequencePipeline(nsof.Engine(0), Cn, F, H, W, segment=True, overlap=False, chunks=chunks)
+            ser.step(frames)
+            torch.cuda.synchronize()
+            ser.eng.profile(True)
+            ser.step(frames)
+            torch.cuda.synchronize()
+            rows = [dict(name=k, **v) for k, v in ser.eng.profile_read().items() if k.startswith("seg_")]
+            ser.eng.profile(False)
+            print(f"   {label}: " + ", ".join(f"{r['name']} {r['launches']} x {r['ms'] / r['launches'] * 1e3:.1f} us" for r in rows)
+                  + f" = {sum(r['ms'] for r in rows):.3f} ms per step", flush=True)
+            del ser
         ser = pm.SequencePipeline(nsof.Engine(0), Cn, F, H, W, segment=True, overlap=False)
         ser.step(frames)
         torch.cuda.synchronize()
@@ -71,3 +83,22 @@ for seg in (False, True):
         print(f"   cv2 on the host (threshold + 5 x dilate/erode only): {dt / px * pipe.last_crop_pixels * 1e3:.1f} ms per step "
               f"equivalent ({px / dt / 1e6:.1f} Mpx/s)", flush=True)
 print(f"segmentation adds {res[True] - res[False]:.3f} ms per step ({(res[True] / res[False] - 1) * 100:.1f} %)")
+# one Farneback batch per step (DeviceStream, the bench's value leg): 12 segmentation launches per step
+ds_ms = {}
+for seg in (False, True):
+    ds = pm.DeviceStream(nsof.Engine(0), Cn, F, H, W, segment=seg)
+    for _ in range(3):
+        ds.submit(frames)
+    ds.drain()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(8):
+        ds.submit(frames)
+    ds.drain()
+    e1.record()
+    torch.cuda.synchronize()
+    ds_ms[seg] = e0.elapsed_time(e1) / 8
+    del ds
+    torch.cuda.empty_cache()
+print(f"DeviceStream (8 steps): {ds_ms[False]:.3f} ms per step, with segmentation {ds_ms[True]:.3f} ms (+{(ds_ms[True] / ds_ms[False] - 1) * 100:.1f} %)")

@@ -236,6 +236,11 @@ def test_emu_segment_vs_reference_and_oracle(emu_engine, golden):
         assert got.dtype == np.uint8 and set(np.unique(got)) <= {0, 255}
         assert np.array_equal(got > 0, mask), name
         assert np.array_equal(emu_engine.segment_flow(-flow.astype(np.float64)) > 0, mask), name
+        emu_engine.debug_fuse(False)  # the per-word pass instead of the tiled one
+        try:
+            assert np.array_equal(emu_engine.segment_flow(flow) > 0, mask), name
+        finally:
+            emu_engine.debug_fuse(True)
     flow = next(f for n, f, _, _ in helpers.segment_cases(golden.seg) if n == "noise_97x131")
     for shape, ksize, its in [(0, (3, 5), 1), (1, (7, 7), 2), (2, (4, 9), 3), (2, (31, 17), 1), (0, (32, 32), 1), (2, (1, 1), 2),
                               (2, (10, 10), 1), (2, (15, 15), 2), (0, (2, 2), 4)]:

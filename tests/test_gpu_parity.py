@@ -413,6 +413,11 @@ def test_segment_vs_reference(gpu_engine, golden):
         assert got.dtype == np.uint8 and set(np.unique(got)) <= {0, 255}
         assert np.array_equal(got > 0, mask), name
         assert np.array_equal(gpu_engine.segment_flow(-flow.astype(np.float64)) > 0, mask), name
+        gpu_engine.debug_fuse(False)  # the per-word pass instead of the tiled one
+        try:
+            assert np.array_equal(gpu_engine.segment_flow(flow) > 0, mask), name
+        finally:
+            gpu_engine.debug_fuse(True)
     # a full 1080p region vs the pinned restatement
     rng = np.random.default_rng(5)
     coarse = rng.standard_normal((1080 // 8 + 3, 1920 // 8 + 3, 2)).astype(np.float32)
