@@ -29,7 +29,7 @@ H, W = 1080, 1920
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="nsof", choices=["nsof", "reference"])
     ap.add_argument("--clips", type=int, default=8, help="clips per GPU")
