@@ -28,11 +28,14 @@ extern "C" {
 
 #define NSOF_OK 0
 #define NSOF_ERR_BAD_ARG (-1)     /* what cv2 reports as cv2.error -215 (empty input, size mismatch, pyr_scale >= 1) */
-#define NSOF_ERR_UNSUPPORTED (-2) /* legal for OpenCV but outside this library (flags != 0, poly_n > 31, ...) */
+#define NSOF_ERR_UNSUPPORTED (-2) /* legal for OpenCV but outside this library (OPTFLOW_USE_INITIAL_FLOW, poly_n > 31, ...) */
 #define NSOF_ERR_CUDA (-3)
 #define NSOF_ERR_NOMEM (-4)
 
 typedef struct nsof_handle nsof_handle;
+
+/* cv2.OPTFLOW_FARNEBACK_GAUSSIAN: Gaussian winsize x winsize window instead of the box (SURVEY.md 8(a) S2-e') */
+#define NSOF_FB_GAUSSIAN 256
 
 /* The kwargs of `farneback_params` (optical_flow_seg.py:73-81), same names and meaning as
  * cv2.calcOpticalFlowFarneback(prev, next, flow, pyr_scale, levels, winsize, iterations, poly_n,
@@ -44,7 +47,7 @@ typedef struct nsof_fb_params {
     int iterations;
     int poly_n;
     double poly_sigma;
-    int flags; /* only 0 is implemented; the reference never passes anything else */
+    int flags; /* 0 (every call site of the reference) or NSOF_FB_GAUSSIAN; OPTFLOW_USE_INITIAL_FLOW (4) is refused */
 } nsof_fb_params;
 
 /* One crop pair = one independent Farneback problem (the `prev_region` / `next_region` views of

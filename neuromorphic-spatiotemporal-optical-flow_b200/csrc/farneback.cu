@@ -340,10 +340,13 @@ static int validate_params(const nsof_fb_params *p)
                   "column 0 to every 1x1 window there; see oracle/farneback_oracle.c A.7)");
     if (p->poly_n < 1 || p->poly_n > NSOF_MAX_POLY_N)
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: poly_n must be in 1..%d", NSOF_MAX_POLY_N);
-    if (p->flags != 0)
+    if (p->flags & ~NSOF_FB_GAUSSIAN)
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED,
-                  "farneback: flags=%d; only 0 is implemented (OPTFLOW_USE_INITIAL_FLOW / "
-                  "OPTFLOW_FARNEBACK_GAUSSIAN are never selected by the reference)", p->flags);
+                  "farneback: flags=%d; 0 and OPTFLOW_FARNEBACK_GAUSSIAN (256) are implemented "
+                  "(OPTFLOW_USE_INITIAL_FLOW is never selected by the reference: every call site passes flow=None)",
+                  p->flags);
+    if ((p->flags & NSOF_FB_GAUSSIAN) && p->winsize / 2 > FB_MAX_WIN_M)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: Gaussian window radius %d > %d", p->winsize / 2, FB_MAX_WIN_M);
     return NSOF_OK;
 }
 
@@ -462,6 +465,7 @@ struct FbBatchCtx {
     bool bs_m7 = false;
     PolyConst pc;
     float flow_mul = 0.f, bscale = 0.f;
+    FbGaussWin gwin;  // S2-e': weights of the Gaussian window (flags & NSOF_FB_GAUSSIAN)
     unsigned char *ds = nullptr;  // device tables
 };
 
@@ -575,7 +579,8 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     X.m = m;
     X.BTW = X.BTH = 0;
     X.bs_smem = 0;
-    X.bs_m7 = (m == 7);  // winsize 14/15: the tuned kernel (every BASELINE.json config)
+    // winsize 14/15 with the box window: the tuned kernel (every BASELINE.json config)
+    X.bs_m7 = (m == 7) && !(params->flags & NSOF_FB_GAUSSIAN);
     if (X.bs_m7) { X.BTW = FB_BS7_TW; X.BTH = FB_BS7_TH; X.bs_smem = FB_BS7_SMEM; }
     else if (params->iterations > 0 && !pick_blur_tile(m, &X.BTW, &X.BTH, &X.bs_smem))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
@@ -657,6 +662,22 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     X.pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
     X.flow_mul = (float)(1. / params->pyr_scale);
     X.bscale = (float)(1. / ((double)params->winsize * params->winsize));
+    memset(&X.gwin, 0, sizeof(X.gwin));
+    if (params->flags & NSOF_FB_GAUSSIAN) {
+        // FarnebackUpdateFlow_GaussianBlur: sigma = 0.3 m; k[0] = 1, k[i] = f32(exp(-i^2 / 2 sigma^2)); normalised in double
+        const double gs = m * 0.3;
+        double sum = 1.;
+        X.gwin.on = 1;
+        X.gwin.k[0] = 1.f;
+        for (int i = 1; i <= m; i++) {
+            const float t = (float)exp(-i * i / (2 * gs * gs));
+            X.gwin.k[i] = t;
+            sum += t * 2;
+        }
+        sum = 1. / sum;
+        for (int i = 0; i <= m; i++) X.gwin.k[i] = (float)(X.gwin.k[i] * sum);
+        X.bscale = 1.f;  // the Gaussian sums are used as they are
+    }
     X.valid = true;
     return NSOF_OK;
 }
@@ -734,7 +755,7 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
                      FB_BS7_NT, X.bs_smem, stream, jobs, X.bscale, (it & 1) == 0, last);
     else
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[kk], na, 1,
-                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last);
+                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
     return NSOF_OK;

@@ -388,9 +388,19 @@ NSOF_GLOBAL k_fb_flow_init(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 //              otherwise      : UpdateMatrices with the new flow in registers -> M_out
 //            so flow never touches HBM between iterations.
 // dynamic smem: 5 * (TH+2m) * PW floats, PW = roundup4(TW+2m).   TW % 4 == 0, m >= 1.
+//
+// S2-e' (OPTFLOW_FARNEBACK_GAUSSIAN, FarnebackUpdateFlow_GaussianBlur): same tile, gwin.on != 0.  The window is the
+// separable float kernel gwin.k[0..m] (sigma = 0.3 m, normalised), both passes accumulate in float in OpenCV's order
+// (centre tap first, then symmetric pairs outwards) and the sums are used unscaled.
 // ---------------------------------------------------------------------------------------------
+#define FB_MAX_WIN_M 63
+struct FbGaussWin {
+    int on;
+    float k[FB_MAX_WIN_M + 1];
+};
+
 NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int m, float scale, int src_is_a,
-                            int last)
+                            int last, const FbGaussWin gwin)
 {
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
@@ -410,6 +420,18 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
         sM[c * SP + ly * PW + lx] = NSOF_LDG(Min + c * plane + (size_t)gy * J.pitch + gx);
     }
     NSOF_SYNC();
+    if (gwin.on) {
+        // in place: output row y overwrites input row y, the oldest row of its own window [y, y + 2m]
+        for (int i = NSOF_TID; i < 5 * LW; i += NSOF_NT) {
+            float *col = sM + (i / LW) * SP + (i % LW);
+            for (int y = 0; y < TH; y++) {
+                const float *c0 = col + (y + m) * PW;
+                float s = c0[0] * gwin.k[0];
+                for (int j = 1; j <= m; j++) s += (c0[j * PW] + c0[-j * PW]) * gwin.k[j];
+                col[y * PW] = s;
+            }
+        }
+    } else
     for (int i = NSOF_TID; i < 5 * LW; i += NSOF_NT) {
         float *col = sM + (i / LW) * SP + (i % LW);
         double s = 0.;
@@ -427,6 +449,16 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
         const int x = tx0 + lx, y = ty0 + ly;
         if (x >= J.w || y >= J.y_hi) continue;
         float s[5][4];
+        if (gwin.on) {
+            for (int c = 0; c < 5; c++) {
+                const float *v = sM + c * SP + ly * PW + lx + m;
+                for (int q = 0; q < 4; q++) {
+                    float a = v[q] * gwin.k[0];
+                    for (int j = 1; j <= m; j++) a += gwin.k[j] * (v[q - j] + v[q + j]);
+                    s[c][q] = a;
+                }
+            }
+        } else
         for (int c = 0; c < 5; c++) {
             const float *v = sM + c * SP + ly * PW + lx;
             // common part: taps 3 .. 2m (shared by the four windows; empty when m == 1), then 3 private taps each

@@ -359,6 +359,61 @@ NSOF_ORACLE_API int nsof_oracle_update_flow_blur(const float *M, int h, int w, i
     return 0;
 }
 
+/* ---- A.7': FarnebackUpdateFlow_GaussianBlur (OPTFLOW_FARNEBACK_GAUSSIAN = 256) ---- */
+/* OpenCV optflowgf.cpp, FarnebackUpdateFlow_GaussianBlur: m = winsize/2, sigma = 0.3 m, float kernel
+ * k[0] = 1, k[i] = f32(exp(-i^2 / (2 sigma^2))), normalised by s = 1 / (1 + 2 sum k[i]) in double and stored
+ * float.  Vertical pass (float): v = M(y)*k[0]; v += (M(y+i) + M(y-i)) * k[i], rows clamped.  Horizontal pass
+ * (float): s = v(x)*k[0]; s += k[i] * (v(x-i) + v(x+i)), columns clamped.  Solve: the products g11*g22 etc.
+ * are FLOAT products (the g's are float variables), only "+ 1e-3", the reciprocal and the final product are
+ * double.  Never selected by the reference's scripts ('flags': 0 everywhere); pinned against cv2 with flags=256. */
+NSOF_ORACLE_API int nsof_oracle_gaussian_window(int winsize, float *k /* m+1 floats */)
+{
+    int m = winsize / 2;
+    double sigma = m * 0.3, s = 1.;
+    k[0] = 1.f;
+    for (int i = 1; i <= m; i++) {
+        float t = (float)exp(-i * i / (2 * sigma * sigma));
+        k[i] = t;
+        s += t * 2;
+    }
+    s = 1. / s;
+    for (int i = 0; i <= m; i++) k[i] = (float)(k[i] * s);
+    return m;
+}
+
+NSOF_ORACLE_API int nsof_oracle_update_flow_gaussian(const float *M, int h, int w, int winsize, float *flow)
+{
+    int m = winsize / 2;
+    float *k = (float *)malloc(sizeof(float) * (size_t)(m + 1));
+    float *vsum = (float *)malloc(sizeof(float) * (size_t)w * 5);
+    if (!k || !vsum) return -2;
+    nsof_oracle_gaussian_window(winsize, k);
+    for (int y = 0; y < h; y++) {
+        const float *r0 = M + (size_t)y * w * 5;
+        for (int i = 0; i < w * 5; i++) vsum[i] = r0[i] * k[0];
+        for (int j = 1; j <= m; j++) {
+            const float *ra = M + (size_t)imax(y - j, 0) * w * 5;
+            const float *rb = M + (size_t)imin(y + j, h - 1) * w * 5;
+            for (int i = 0; i < w * 5; i++) vsum[i] += (rb[i] + ra[i]) * k[j];
+        }
+        for (int x = 0; x < w; x++) {
+            float s[5];
+            for (int c = 0; c < 5; c++) s[c] = vsum[(size_t)x * 5 + c] * k[0];
+            for (int j = 1; j <= m; j++) {
+                const float *va = vsum + (size_t)imax(x - j, 0) * 5, *vb = vsum + (size_t)imin(x + j, w - 1) * 5;
+                for (int c = 0; c < 5; c++) s[c] += k[j] * (va[c] + vb[c]);
+            }
+            float g11 = s[0], g12 = s[1], g22 = s[2], h1 = s[3], h2 = s[4];
+            double idet = 1. / (g11 * g22 - g12 * g12 + 1e-3);
+            flow[((size_t)y * w + x) * 2] = (float)((g11 * h2 - g12 * h1) * idet);
+            flow[((size_t)y * w + x) * 2 + 1] = (float)((g22 * h1 - g12 * h2) * idet);
+        }
+    }
+    free(vsum);
+    free(k);
+    return 0;
+}
+
 /* ---- A.1/A.3: inter-level flow upsample: resize(LINEAR) * (1/pyr_scale) --- */
 NSOF_ORACLE_API void nsof_oracle_upsample_flow(const float *src, int hs, int ws, int hd, int wd,
                                                double pyr_scale, float *dst)
@@ -415,7 +470,7 @@ NSOF_ORACLE_API int nsof_oracle_level_geometry(int h, int w, double pyr_scale, i
     return cropped + 1;
 }
 
-/* ---- A.1: the whole call, flags = 0, flow = None -------------------------- */
+/* ---- A.1: the whole call, flags = 0 or OPTFLOW_FARNEBACK_GAUSSIAN (256), flow = None ---- */
 /* stage_dump (optional, may be NULL): called after every stage with a tag so tests can
  * compare device intermediates; tag: 0=I(img0) 1=I(img1) 2=R0 3=R1 4=M(after first
  * UpdateMatrices) 5=flow(after iteration `it`), level k. */
@@ -429,7 +484,7 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
 {
     if (!prev || !next || h < 1 || w < 1) return -1;
     if (!(pyr_scale < 1.) || pyr_scale <= 0 || levels < 0 || winsize < 1 || iterations < 0 || poly_n < 1) return -1;
-    if (flags != 0) return -3; /* USE_INITIAL_FLOW / GAUSSIAN are never selected by the reference */
+    if (flags & ~256) return -3; /* OPTFLOW_USE_INITIAL_FLOW (4) is not restated: no call site passes a flow */
     int hk[64], wk[64], ks[64];
     double sg[64];
     if (levels > 62) return -1;
@@ -458,7 +513,8 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
         nsof_oracle_update_matrices(R0, R1, flow, H, W, M);
         if (dump) dump(user, 4, k, 0, M, H, W, 5);
         for (int it = 0; it < iterations; it++) {
-            int rc = nsof_oracle_update_flow_blur(M, H, W, winsize, flow);
+            int rc = (flags & 256) ? nsof_oracle_update_flow_gaussian(M, H, W, winsize, flow)
+                                   : nsof_oracle_update_flow_blur(M, H, W, winsize, flow);
             if (rc) return rc;
             if (dump) dump(user, 5, k, it, flow, H, W, 2);
             if (it < iterations - 1) nsof_oracle_update_matrices(R0, R1, flow, H, W, M);

@@ -31,6 +31,11 @@ PARAM_SETS = {
     "grasp": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0),
     "autodriving_txt": dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3, poly_n=10, poly_sigma=1.05, flags=0),
     "tabletennis": dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2, poly_n=1, poly_sigma=1.05, flags=0),
+    # OPTFLOW_FARNEBACK_GAUSSIAN (SURVEY.md 8(a) S2-e'): no script selects it; pinned so the drop-in covers the flag
+    "grasp_gaussian": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2,
+                           flags=cv2.OPTFLOW_FARNEBACK_GAUSSIAN),
+    "gaussian_w10": dict(pyr_scale=0.6, levels=2, winsize=10, iterations=2, poly_n=7, poly_sigma=1.5,
+                         flags=cv2.OPTFLOW_FARNEBACK_GAUSSIAN),
 }
 
 
@@ -355,6 +360,9 @@ def make_frames():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "farneback":
+        make_farneback()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "frames":
         make_frames()
         sys.exit(0)

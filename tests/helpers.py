@@ -13,6 +13,9 @@ PARAM_SETS = {
     "grasp": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=0),
     "autodriving_txt": dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3, poly_n=10, poly_sigma=1.05, flags=0),
     "tabletennis": dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2, poly_n=1, poly_sigma=1.05, flags=0),
+    # OPTFLOW_FARNEBACK_GAUSSIAN = 256 (SURVEY.md 8(a) S2-e'): never selected by the scripts, covered for the drop-in
+    "grasp_gaussian": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=256),
+    "gaussian_w10": dict(pyr_scale=0.6, levels=2, winsize=10, iterations=2, poly_n=7, poly_sigma=1.5, flags=256),
 }
 # Flow tolerances vs OpenCV's float Farneback (BASELINE.json bar: EPE <= 0.01 px).  Pixels whose 2x2 system is
 # near-singular (aperture problem inside a tiny window: winsize 3/4) amplify 1-ulp differences of ANY
@@ -23,6 +26,8 @@ TOL = {
     "grasp": dict(epe_mean=1e-4, q=1.0, qmax=1e-3),
     "autodriving_txt": dict(epe_mean=1e-3, q=0.99, qmax=1e-2),
     "tabletennis": dict(epe_mean=1e-3, q=0.99, qmax=1e-2),
+    "grasp_gaussian": dict(epe_mean=1e-4, q=1.0, qmax=1e-3),
+    "gaussian_w10": dict(epe_mean=1e-4, q=1.0, qmax=1e-3),
 }
 
 

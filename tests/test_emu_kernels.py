@@ -83,7 +83,7 @@ def test_emu_errors_mirror_cv2(emu_engine, nsof):
     with pytest.raises(nsof.error):
         emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
     with pytest.raises(NotImplementedError):
-        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=256))
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=4))  # OPTFLOW_USE_INITIAL_FLOW
     with pytest.raises(NotImplementedError):
         emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, winsize=1))
     z = emu_engine.calcOpticalFlowFarneback(a, a, None, **p)

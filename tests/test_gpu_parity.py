@@ -146,7 +146,7 @@ def test_errors_mirror_cv2(gpu_engine, nsof):
     with pytest.raises(nsof.error):
         gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
     with pytest.raises(NotImplementedError):
-        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=256))
+        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=4))  # OPTFLOW_USE_INITIAL_FLOW
     z = gpu_engine.calcOpticalFlowFarneback(a, a, None, **p)
     assert z.shape == (40, 40, 2) and z.dtype == np.float32 and not z.any()
 
