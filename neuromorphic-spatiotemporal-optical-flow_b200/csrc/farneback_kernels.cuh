@@ -300,6 +300,8 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 }
 
 // 4 pixels per thread: float4 loads of R0, float4 stores of M, 80 independent R1 gathers in flight per thread.
+// (no launch bounds: 64 registers / 4 CTAs per SM as ptxas picks them; __launch_bounds__(256, 1) measured 2.35 -> 2.95 ms
+// per full-frame step, (256, 5) with its 60-byte spill 2.51 ms)
 NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
@@ -317,6 +319,9 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
             nsof_prefetch_l2(J.R + (5 + c) * plane + (size_t)gy * J.pitch + tx0, (unsigned)(px1 - tx0) * 4u);
         }
     }
+    // (one pixel per lane, as in phase 3b of the blur+solve kernel, was measured here and is SLOWER: 2.35 -> 2.60 ms per
+    // full-frame step; this kernel has no shared-memory phase to overlap with, and 80 independent gathers per thread
+    // hide more latency than the narrower L1 footprint saves)
     constexpr int GW = FB_UM_TW / 4;
     for (int i = NSOF_TID; i < GW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + (i % GW) * 4, y = ty0 + i / GW;
@@ -709,7 +714,12 @@ static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, float, int, int) = k_fb_bl
 // static smem: max(3*TH*IP*4, SH*SW) + IH*IP*4 bytes  (IP = roundup4(TW+2N)).
 // ---------------------------------------------------------------------------------------------
 template <int MODE, int N, int TW, int TH>
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk,
+// 4 CTAs per SM (64 registers, no spill) hide the block barriers between the phases better than 3 (76 registers):
+// 2.89 -> 2.60 ms per full-frame step; 5 and 6 CTAs (48 / 40 registers, spilling) measured 2.71 / 2.58 ms
+#ifndef FB_PP_MINB
+#define FB_PP_MINB 4
+#endif
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk,
                                                          PolyConst pc)
 {
     constexpr int IW = TW + 2 * N, IH = TH + 2 * N, IP = (IW + 3) & ~3;
@@ -718,7 +728,13 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_REST
     constexpr int RP = (SWN + 32 + 15) & ~15;                                       // pitch of the raw uint8 window
     constexpr int A_BYTES = (3 * TH * IP * 4 > SHN * SW * 4 ? 3 * TH * IP * 4 : SHN * SW * 4);  // S (float) | sr
     constexpr int B_BYTES = (IH * IP * 4 > SHN * RP ? IH * IP * 4 : SHN * RP);                  // raw u8 | sI
-    constexpr int BSTRIP = 14, BNS = (IH + BSTRIP - 1) / BSTRIP;
+#ifndef FB_PP_BSTRIP
+#define FB_PP_BSTRIP 14
+#endif
+#ifndef FB_PP_STRIP
+#define FB_PP_STRIP 8
+#endif
+    constexpr int BSTRIP = FB_PP_BSTRIP, BNS = (IH + BSTRIP - 1) / BSTRIP;
     static_assert(A_BYTES % 16 == 0 && B_BYTES % 16 == 0, "shared regions must stay 16-byte aligned");
     const FbJob J = jobs[NSOF_BY];
     if (J.fast != MODE + 1) return;
@@ -875,7 +891,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_fb_pyr_polyexp_t(const FbJob *NSOF_REST
     }
     // ---- C: vertical moments, one thread per (column, strip of 8 rows), the column window kept in registers
     {
-        constexpr int STRIP = 8, NS = TH / STRIP;
+        constexpr int STRIP = FB_PP_STRIP, NS = TH / STRIP;
         for (int i = NSOF_TID; i < IW * NS; i += NSOF_NT) {
             const int lx = i % IW, st = i / IW;
             float col[STRIP + 2 * N];
