@@ -396,6 +396,7 @@ static int configure_smem(nsof_handle *h)
 {
     if (h->smem_configured) return NSOF_OK;
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve_gauss, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7S, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7S_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
@@ -753,6 +754,9 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
     else if (X.bs_m7)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, X.max_tiles_bs[kk], na, 1,
                      FB_BS7_NT, X.bs_smem, stream, jobs, X.bscale, (it & 1) == 0, last);
+    else if (X.gwin.on)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve_gauss, X.max_tiles_bs[kk], na, 1,
+                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
     else
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[kk], na, 1,
                      256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);

@@ -404,8 +404,9 @@ struct FbGaussWin {
     float k[FB_MAX_WIN_M + 1];
 };
 
-NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int m, float scale, int src_is_a,
-                            int last, const FbGaussWin gwin)
+template <int GAUSS>  // compile-time: the box instantiation must not pay for the indexed weight table
+NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int m, float scale, int src_is_a,
+                              int last, const FbGaussWin gwin)
 {
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
@@ -425,7 +426,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
         sM[c * SP + ly * PW + lx] = NSOF_LDG(Min + c * plane + (size_t)gy * J.pitch + gx);
     }
     NSOF_SYNC();
-    if (gwin.on) {
+    if (GAUSS) {
         // in place: output row y overwrites input row y, the oldest row of its own window [y, y + 2m]
         for (int i = NSOF_TID; i < 5 * LW; i += NSOF_NT) {
             float *col = sM + (i / LW) * SP + (i % LW);
@@ -454,7 +455,7 @@ NSOF_GLOBAL k_fb_blur_solve(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int
         const int x = tx0 + lx, y = ty0 + ly;
         if (x >= J.w || y >= J.y_hi) continue;
         float s[5][4];
-        if (gwin.on) {
+        if (GAUSS) {
             for (int c = 0; c < 5; c++) {
                 const float *v = sM + c * SP + ly * PW + lx + m;
                 for (int q = 0; q < 4; q++) {
@@ -692,8 +693,12 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     }
 }
 
+static void (*const k_fb_blur_solve)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<0>;
+static void (*const k_fb_blur_solve_gauss)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<1>;
 // a plain function-pointer name: template commas do not survive nested launch macros
+#ifndef FB_BS7_NT
 #define FB_BS7_NT 256
+#endif
 #define FB_BS7S_TW 32   // small tile: coarse levels / small batches are latency-bound, more and shorter CTAs
 #define FB_BS7S_TH 16
 #define FB_BS7S_NT 128
