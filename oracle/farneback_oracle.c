@@ -445,6 +445,78 @@ NSOF_ORACLE_API void nsof_oracle_upsample_flow(const float *src, int hs, int ws,
     }
 }
 
+/* ---- A.8: OPTFLOW_USE_INITIAL_FLOW (4): cv::resize(flow0, INTER_AREA) of a 2-channel float image ---- */
+/* Restated from OpenCV imgproc/resize.cpp and pinned bit for bit against cv2.resize (tests/test_oracle_golden.py).
+ * scale = src/dst per axis (>= 1 here).  Both scales integer ("area fast"): plain sum of the ix*iy source pixels in
+ * row-major order, accumulated four at a time as sum += ((a+b)+c)+d (ResizeAreaFastNoVec's unrolled loop), times
+ * f32(1/area).  Otherwise the DecimateAlpha tables (computeResizeAreaTab): per destination cell the partially covered
+ * first source pixel, the fully covered ones (weight 1/cellWidth) and the partially covered last one; rows are combined
+ * as sum = beta_0*buf_0 + beta_1*buf_1 + ... with buf = horizontal weighted sum, all float. */
+static int area_tab(int ssize, int dsize, int dx, int *si, float *alpha /* room for (int)scale + 3 */)
+{
+    double scale = (double)ssize / dsize;
+    double fsx1 = dx * scale, fsx2 = fsx1 + scale;
+    double cell = scale < ssize - fsx1 ? scale : ssize - fsx1;
+    int sx1 = (int)ceil(fsx1), sx2 = (int)floor(fsx2), k = 0;
+    sx2 = imin(sx2, ssize - 1);
+    sx1 = imin(sx1, sx2);
+    if (sx1 - fsx1 > 1e-3) { si[k] = sx1 - 1; alpha[k++] = (float)((sx1 - fsx1) / cell); }
+    for (int sx = sx1; sx < sx2; sx++) { si[k] = sx; alpha[k++] = (float)(1.0 / cell); }
+    if (fsx2 - sx2 > 1e-3) {
+        double t = fsx2 - sx2;
+        if (t > 1.) t = 1.;
+        if (t > cell) t = cell;
+        si[k] = sx2;
+        alpha[k++] = (float)(t / cell);
+    }
+    return k;
+}
+
+NSOF_ORACLE_API int nsof_oracle_resize_area_c2(const float *src, int hs, int ws, int hd, int wd, float *dst)
+{
+    if (hd > hs || wd > ws || hd < 1 || wd < 1) return -1;
+    if (hs % hd == 0 && ws % wd == 0) {
+        int iy = hs / hd, ix = ws / wd, area = ix * iy;
+        float sc = 1.f / area;
+        for (int dy = 0; dy < hd; dy++)
+            for (int dx = 0; dx < wd; dx++)
+                for (int c = 0; c < 2; c++) {
+#define AV(k) src[(((size_t)dy * iy + (k) / ix) * ws + (size_t)dx * ix + (k) % ix) * 2 + c]
+                    float sum = 0.f;
+                    int k = 0;
+                    for (; k <= area - 4; k += 4) sum += AV(k) + AV(k + 1) + AV(k + 2) + AV(k + 3);
+                    for (; k < area; k++) sum += AV(k);
+#undef AV
+                    dst[((size_t)dy * wd + dx) * 2 + c] = sum * sc;
+                }
+        return 0;
+    }
+    int nx = ws / wd + 3, ny = hs / hd + 3;
+    int *xi = (int *)malloc(sizeof(int) * (size_t)(nx + ny));
+    float *xa = (float *)malloc(sizeof(float) * (size_t)(nx + ny));
+    if (!xi || !xa) return -2;
+    int *yi = xi + nx;
+    float *ya = xa + nx;
+    for (int dy = 0; dy < hd; dy++) {
+        int ky = area_tab(hs, hd, dy, yi, ya);
+        for (int dx = 0; dx < wd; dx++) {
+            int kx = area_tab(ws, wd, dx, xi, xa);
+            for (int c = 0; c < 2; c++) {
+                float sum = 0.f;
+                for (int j = 0; j < ky; j++) {
+                    float buf = 0.f;
+                    for (int i = 0; i < kx; i++) buf = buf + src[((size_t)yi[j] * ws + xi[i]) * 2 + c] * xa[i];
+                    sum = j == 0 ? ya[j] * buf : sum + ya[j] * buf;
+                }
+                dst[((size_t)dy * wd + dx) * 2 + c] = sum;
+            }
+        }
+    }
+    free(xi);
+    free(xa);
+    return 0;
+}
+
 /* ---- A.1: level geometry (shared by tests to address stage dumps) -------- */
 /* Returns the number of scales (levels_eff + 1); fills hk/wk/ksize/sigma for k = 0..levels_eff. */
 NSOF_ORACLE_API int nsof_oracle_level_geometry(int h, int w, double pyr_scale, int levels,
@@ -484,7 +556,9 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
 {
     if (!prev || !next || h < 1 || w < 1) return -1;
     if (!(pyr_scale < 1.) || pyr_scale <= 0 || levels < 0 || winsize < 1 || iterations < 0 || poly_n < 1) return -1;
-    if (flags & ~256) return -3; /* OPTFLOW_USE_INITIAL_FLOW (4) is not restated: no call site passes a flow */
+    if (flags & ~(256 | 4)) return -3;
+    /* flags & 4 (OPTFLOW_USE_INITIAL_FLOW): flow_out holds the initial flow on entry (no call site of the reference
+     * passes one; restated for the drop-in signature and pinned against cv2) */
     int hk[64], wk[64], ks[64];
     double sg[64];
     if (levels > 62) return -1;
@@ -500,7 +574,16 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
         float *R1 = (float *)malloc(sizeof(float) * N * 5);
         float *M = (float *)malloc(sizeof(float) * N * 5);
         if (!flow || !I || !R0 || !R1 || !M) return -2;
-        if (!prev_flow) memset(flow, 0, sizeof(float) * N * 2);
+        if (!prev_flow && (flags & 4)) {
+            /* resize(flow0, INTER_AREA) then flow *= scale (Mat *= double: f32(v * f32(scale))) */
+            double sc = 1;
+            for (int i = 0; i < k; i++) sc *= pyr_scale;
+            if (k > 0) {
+                int rc = nsof_oracle_resize_area_c2(flow_out, h, w, H, W, flow);
+                if (rc) return rc;
+            }
+            for (size_t i = 0; i < N * 2; i++) flow[i] = flow[i] * (float)sc;
+        } else if (!prev_flow) memset(flow, 0, sizeof(float) * N * 2);
         else nsof_oracle_upsample_flow(prev_flow, ph, pw, H, W, pyr_scale, flow);
         for (int i = 0; i < 2; i++) {
             int rc = nsof_oracle_pyr_level(i ? next : prev, h, w, i ? pitch1 : pitch0, ks[k], sg[k], H, W, I);

@@ -55,13 +55,15 @@ class Oracle:
         self.lib.nsof_oracle_farneback_dump.argtypes = [
             C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_ssize_t, C.c_double, C.c_int, C.c_int, C.c_int,
             C.c_int, C.c_double, C.c_int, C.c_void_p, DUMP_FN, C.c_void_p]
+        self.lib.nsof_oracle_resize_area_c2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         self.lib.nsof_oracle_level_geometry.argtypes = [C.c_int, C.c_int, C.c_double, C.c_int] + [C.c_void_p] * 4
 
-    def farneback(self, prev, nxt, pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags=0, dump=False):
+    def farneback(self, prev, nxt, pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags=0, dump=False,
+                  flow=None):
         prev = np.ascontiguousarray(prev)
         nxt = np.ascontiguousarray(nxt)
         h, w = prev.shape
-        out = np.zeros((h, w, 2), np.float32)
+        out = np.zeros((h, w, 2), np.float32) if flow is None else np.ascontiguousarray(flow, np.float32).copy()
         stages = {}
 
         def cb(user, tag, k, it, data, hh, ww, ch):
@@ -74,6 +76,12 @@ class Oracle:
                                                  None)
         assert rc == 0, rc
         return (out, stages) if dump else out
+
+    def resize_area(self, src, hd, wd):
+        src = np.ascontiguousarray(src, np.float32)
+        out = np.empty((hd, wd, 2), np.float32)
+        assert self.lib.nsof_oracle_resize_area_c2(src.ctypes.data, src.shape[0], src.shape[1], hd, wd, out.ctypes.data) == 0
+        return out
 
     def level_geometry(self, h, w, pyr_scale, levels):
         hk = (C.c_int * 64)()
