@@ -28,7 +28,7 @@ extern "C" {
 
 #define NSOF_OK 0
 #define NSOF_ERR_BAD_ARG (-1)     /* what cv2 reports as cv2.error -215 (empty input, size mismatch, pyr_scale >= 1) */
-#define NSOF_ERR_UNSUPPORTED (-2) /* legal for OpenCV but outside this library (OPTFLOW_USE_INITIAL_FLOW, poly_n > 31, ...) */
+#define NSOF_ERR_UNSUPPORTED (-2) /* legal for OpenCV but outside this library (winsize 1, poly_n > 31, ...) */
 #define NSOF_ERR_CUDA (-3)
 #define NSOF_ERR_NOMEM (-4)
 
@@ -36,6 +36,9 @@ typedef struct nsof_handle nsof_handle;
 
 /* cv2.OPTFLOW_FARNEBACK_GAUSSIAN: Gaussian winsize x winsize window instead of the box (SURVEY.md 8(a) S2-e') */
 #define NSOF_FB_GAUSSIAN 256
+/* cv2.OPTFLOW_USE_INITIAL_FLOW: `flow` is in/out; the coarsest level starts from resize(flow, INTER_AREA) * scale
+ * instead of zero (no call site of the reference passes a flow; implemented for the drop-in signature) */
+#define NSOF_FB_USE_INITIAL_FLOW 4
 
 /* The kwargs of `farneback_params` (optical_flow_seg.py:73-81), same names and meaning as
  * cv2.calcOpticalFlowFarneback(prev, next, flow, pyr_scale, levels, winsize, iterations, poly_n,
@@ -47,7 +50,7 @@ typedef struct nsof_fb_params {
     int iterations;
     int poly_n;
     double poly_sigma;
-    int flags; /* 0 (every call site of the reference) or NSOF_FB_GAUSSIAN; OPTFLOW_USE_INITIAL_FLOW (4) is refused */
+    int flags; /* 0 (every call site of the reference), NSOF_FB_GAUSSIAN, NSOF_FB_USE_INITIAL_FLOW or both */
 } nsof_fb_params;
 
 /* One crop pair = one independent Farneback problem (the `prev_region` / `next_region` views of

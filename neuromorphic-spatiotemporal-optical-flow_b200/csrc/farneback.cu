@@ -340,11 +340,10 @@ static int validate_params(const nsof_fb_params *p)
                   "column 0 to every 1x1 window there; see oracle/farneback_oracle.c A.7)");
     if (p->poly_n < 1 || p->poly_n > NSOF_MAX_POLY_N)
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: poly_n must be in 1..%d", NSOF_MAX_POLY_N);
-    if (p->flags & ~NSOF_FB_GAUSSIAN)
+    if (p->flags & ~(NSOF_FB_GAUSSIAN | NSOF_FB_USE_INITIAL_FLOW))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED,
-                  "farneback: flags=%d; 0 and OPTFLOW_FARNEBACK_GAUSSIAN (256) are implemented "
-                  "(OPTFLOW_USE_INITIAL_FLOW is never selected by the reference: every call site passes flow=None)",
-                  p->flags);
+                  "farneback: flags=%d; OPTFLOW_USE_INITIAL_FLOW (4) and OPTFLOW_FARNEBACK_GAUSSIAN (256) are the flags "
+                  "cv2 defines", p->flags);
     if ((p->flags & NSOF_FB_GAUSSIAN) && p->winsize / 2 > FB_MAX_WIN_M)
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: Gaussian window radius %d > %d", p->winsize / 2, FB_MAX_WIN_M);
     return NSOF_OK;
@@ -460,6 +459,7 @@ struct FbBatchCtx {
     std::vector<int> n_active, path_n, max_tiles_pp, max_tiles_ps, ps_sw, ps_sh, max_tiles_pyr, max_tiles_pe,
         max_tiles_um, max_tiles_bs, max_tiles_bss;
     std::vector<long long> sum_tiles_bs;
+    std::vector<int> n_init;  // per level: items whose coarsest level it is and that take an initial flow (k > 0)
     std::vector<double> sumN, sumNc, path_N, path_N0;
     int BTW = 0, BTH = 0;
     size_t bs_smem = 0, pe_smem = 0;
@@ -575,6 +575,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
                     &X.max_tiles_bs, &X.max_tiles_bss})
         v->assign(LV, 0);
     X.sum_tiles_bs.assign(LV, 0);
+    X.n_init.assign(LV, 0);
     const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
     const int m = params->winsize / 2;
     X.m = m;
@@ -637,6 +638,17 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             if (k == 0) { J.flow = (float2 *)pl.d.flow; J.fpitch = (int)(pl.d.flow_pitch / 8); }
             else { J.flow = (float2 *)fl_this; J.fpitch = J.pitch; }
             J.cflow = (const float2 *)fl_coarse;
+            if (coarsest && (params->flags & NSOF_FB_USE_INITIAL_FLOW)) {
+                double sc = 1;  // pyr_scale^k by repeated multiplication, as the level geometry
+                for (int i2 = 0; i2 < k; i2++) sc *= params->pyr_scale;
+                J.init = k == 0 ? 2 : 1;
+                J.init_mul = (float)sc;
+                J.flow0 = (const float2 *)pl.d.flow;
+                J.f0pitch = (int)(pl.d.flow_pitch / 8);
+                J.cflow = J.flow;  // the level's own buffer, read as it is by the first UpdateMatrices
+                J.cpitch = J.fpitch;
+                if (k > 0) X.n_init[kk] += 1;
+            }
             jobs[a++] = J;
             X.sumN[kk] += (double)rows * J.w;
             if (!coarsest) X.sumNc[kk] += (double)J.ch * J.cw * frac;
@@ -724,6 +736,8 @@ static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream, int va
     const int na = X.n_active[kk];
     h->prof_level = k;
     if (!X.max_tiles_um[kk]) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
+    if (X.n_init[kk])  // OPTFLOW_USE_INITIAL_FLOW: items whose coarsest level this is
+        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumN[kk], k_fb_area_init, X.max_tiles_um[kk], na, 1, 256, 0, stream, jobs);
     if (X.params.iterations == 0)
         NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
                      jobs, X.flow_mul);
@@ -848,6 +862,8 @@ extern "C" int nsof_fb_tiled_begin(nsof_handle *h, const nsof_crop_desc *items, 
     if (n < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_begin: no items");
     if (world < 1 || rank < 0 || rank >= world || halo_r1 < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_begin: bad rank/world/halo");
     if (params->iterations < 1) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_begin: iterations >= 1 required");
+    if (params->flags & NSOF_FB_USE_INITIAL_FLOW)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_begin: OPTFLOW_USE_INITIAL_FLOW is not available in the row-tiled mode");
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     rc = h->guard_buf.ensure(sizeof(int));
@@ -992,6 +1008,9 @@ extern "C" int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *i
         dev[i].prev_pitch = dev[i].next_pitch = (ptrdiff_t)ipitch[i];
         dev[i].flow = (float *)(io + off_flow[i]);
         dev[i].flow_pitch = (ptrdiff_t)d.w * 8;
+        if (params->flags & NSOF_FB_USE_INITIAL_FLOW)  // flow is in/out, as cv2's InputOutputArray
+            NSOF_CUDA_TRY(cudaMemcpy2DAsync(dev[i].flow, dev[i].flow_pitch, d.flow, d.flow_pitch, (size_t)d.w * 8, d.h,
+                                            cudaMemcpyHostToDevice, stream));
     }
     rc = nsof_farneback_batch(h, dev.data(), n, params, stream);
     if (rc) return rc;

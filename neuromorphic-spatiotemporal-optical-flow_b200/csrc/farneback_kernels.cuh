@@ -51,6 +51,13 @@ struct FbJob {
     float *Ma, *Mb;
     const float2 *cflow;
     float2 *flow;
+    // OPTFLOW_USE_INITIAL_FLOW, coarsest level of the item only.  init: 0 no; 1 the level's flow buffer holds
+    // resize(flow0, INTER_AREA) * init_mul (k_fb_area_init); 2 level 0 is the coarsest: the caller's flow, in place.
+    // cflow / cpitch then name the level's OWN flow buffer, read as it is.
+    int init;
+    float init_mul;
+    const float2 *flow0;  // the caller's full-resolution flow (sh x sw, f0pitch in float2)
+    int f0pitch;
 };
 
 struct PolyConst {
@@ -339,7 +346,8 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
             float r0v[5], mm[5];
             if (x + q < J.w) {
                 float2 d = make_float2(0.f, 0.f);
-                if (J.ch > 0) d = fb_upsampled_flow(J, x + q, y, flow_mul);
+                if (J.init) d = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q);
+                else if (J.ch > 0) d = fb_upsampled_flow(J, x + q, y, flow_mul);
 #pragma unroll
                 for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
                 if (J.guard) fb_um_guard(J, y, d.y);
@@ -357,10 +365,105 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// OPTFLOW_USE_INITIAL_FLOW (A.8): flow_coarsest = resize(flow0, (w_k, h_k), INTER_AREA) * f32(scale_k), two-channel
+// float.  OpenCV's two INTER_AREA paths, restated in oracle/farneback_oracle.c (bit-exact against cv2.resize there):
+// both ratios integer -> sum of the ix*iy source pixels, row-major, accumulated four at a time as
+// sum += ((a+b)+c)+d, times f32(1/area); otherwise the DecimateAlpha taps per axis (partially covered first pixel,
+// fully covered ones at 1/cellWidth, partially covered last one), rows combined as sum = b0*buf0 + b1*buf1 + ...
+// One thread per output pixel: the coarsest level is at most a few thousand pixels.
+// ---------------------------------------------------------------------------------------------
+struct FbAreaAxis {
+    int s1, s2, has0, has1;
+    float a0, am, a1;
+};
+NSOF_DEV FbAreaAxis fb_area_axis(int ssize, int dsize, int d)
+{
+    const double scale = (double)ssize / dsize;
+    const double f1 = d * scale, f2 = f1 + scale;
+    const double cell = fmin(scale, ssize - f1);
+    int s1 = (int)ceil(f1), s2 = (int)floor(f2);
+    s2 = nsof_imin(s2, ssize - 1);
+    s1 = nsof_imin(s1, s2);
+    FbAreaAxis A;
+    A.s1 = s1; A.s2 = s2;
+    A.has0 = (s1 - f1 > 1e-3) ? 1 : 0;
+    A.has1 = (f2 - s2 > 1e-3) ? 1 : 0;
+    A.a0 = (float)((s1 - f1) / cell);
+    A.am = (float)(1.0 / cell);
+    A.a1 = (float)(fmin(fmin(f2 - s2, 1.), cell) / cell);
+    return A;
+}
+// tap i of an axis: source index and weight
+NSOF_DEV void fb_area_tap(const FbAreaAxis &A, int i, int *si, float *a)
+{
+    const int j = i - A.has0;
+    if (j < 0) { *si = A.s1 - 1; *a = A.a0; }
+    else if (j < A.s2 - A.s1) { *si = A.s1 + j; *a = A.am; }
+    else { *si = A.s2; *a = A.a1; }
+}
+
+NSOF_GLOBAL k_fb_area_init(const FbJob *NSOF_RESTRICT jobs)
+{
+    const FbJob J = jobs[NSOF_BY];
+    if (J.init != 1) return;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.h + FB_UM_TH - 1) / FB_UM_TH;
+    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = (NSOF_BX / tiles_x) * FB_UM_TH;
+    const bool fastp = J.sh % J.h == 0 && J.sw % J.w == 0;
+    for (int i = NSOF_TID; i < FB_UM_TW * FB_UM_TH; i += NSOF_NT) {
+        const int x = tx0 + i % FB_UM_TW, y = ty0 + i / FB_UM_TW;
+        if (x >= J.w || y >= J.h) continue;
+        float sx = 0.f, sy = 0.f;
+        if (fastp) {
+            const int iy = J.sh / J.h, ix = J.sw / J.w, area = ix * iy;
+            const float2 *base = J.flow0 + (size_t)y * iy * J.f0pitch + (size_t)x * ix;
+#define FB_AV(k) NSOF_LDG(base + (size_t)((k) / ix) * J.f0pitch + (k) % ix)
+            int k = 0;
+            for (; k <= area - 4; k += 4) {
+                const float2 a = FB_AV(k), b = FB_AV(k + 1), c = FB_AV(k + 2), d = FB_AV(k + 3);
+                sx += ((a.x + b.x) + c.x) + d.x;
+                sy += ((a.y + b.y) + c.y) + d.y;
+            }
+            for (; k < area; k++) {
+                const float2 a = FB_AV(k);
+                sx += a.x;
+                sy += a.y;
+            }
+#undef FB_AV
+            const float sc = 1.f / (float)area;
+            sx *= sc;
+            sy *= sc;
+        } else {
+            const FbAreaAxis AX = fb_area_axis(J.sw, J.w, x), AY = fb_area_axis(J.sh, J.h, y);
+            const int nx = AX.has0 + (AX.s2 - AX.s1) + AX.has1, ny = AY.has0 + (AY.s2 - AY.s1) + AY.has1;
+            for (int j = 0; j < ny; j++) {
+                int yy;
+                float beta;
+                fb_area_tap(AY, j, &yy, &beta);
+                const float2 *row = J.flow0 + (size_t)yy * J.f0pitch;
+                float bx = 0.f, by = 0.f;
+                for (int t = 0; t < nx; t++) {
+                    int xx;
+                    float al;
+                    fb_area_tap(AX, t, &xx, &al);
+                    const float2 v = NSOF_LDG(row + xx);
+                    bx = bx + v.x * al;
+                    by = by + v.y * al;
+                }
+                sx = j == 0 ? beta * bx : sx + beta * bx;
+                sy = j == 0 ? beta * by : sy + beta * by;
+            }
+        }
+        J.flow[(size_t)y * J.fpitch + x] = make_float2(sx * J.init_mul, sy * J.init_mul);
+    }
+}
+
 // Level with zero iterations: flow is just the (scaled) upsampled coarse flow, or zero.
 NSOF_GLOBAL k_fb_flow_init(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
+    if (J.init) return;  // the initial flow is already in place
     const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
     if (NSOF_BX >= tiles_x * tiles_y) return;
     const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;

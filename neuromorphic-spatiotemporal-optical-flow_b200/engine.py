@@ -148,6 +148,8 @@ class Engine:
         prev, next = self._check_pair(prev, next)
         h, w = prev.shape
         if flow is None:
+            if int(flags) & 4:  # cv2: assertion on the size / type of the initial flow
+                raise error("(-215:Assertion failed) OPTFLOW_USE_INITIAL_FLOW needs a float32 (h, w, 2) flow")
             out = np.empty((h, w, 2), dtype=np.float32)
         else:
             out = flow

@@ -92,6 +92,31 @@ def make_farneback():
     print("farneback_cv2.npz", len(names), "cases")
 
 
+def make_farneback_initflow():
+    """OPTFLOW_USE_INITIAL_FLOW (cv2 flag 4; no script passes a flow): cv2 itself on the pairs of farneback_cv2.npz with
+    a seeded smooth initial flow.  96x128 takes INTER_AREA's integer-ratio path (1/8), 75x101 the general one,
+    40x33 has a single scale (the initial flow is used in place)."""
+    fb = np.load(os.path.join(OUT, "farneback_cv2.npz"))
+    rng = np.random.default_rng(20261105)
+    out = {}
+    sets = {
+        "grasp_init": dict(PARAM_SETS["grasp"], flags=4, iterations=1),
+        "gaussian_init": dict(PARAM_SETS["gaussian_w10"], flags=4 | 256),
+    }
+    names = ["synth_96x128", "synth_75x101", "synth_40x33"]
+    for name in names:
+        a, b = fb[f"{name}__prev"], fb[f"{name}__next"]
+        f0 = rng.normal(size=a.shape + (2,)).astype(np.float32) * 2
+        f0 = cv2.GaussianBlur(f0, (0, 0), 5) * 4 + np.float32([2.0, -1.0])
+        out[f"{name}__flow0"] = f0.astype(np.float32)
+        for pname, p in sets.items():
+            out[f"{name}__{pname}"] = cv2.calcOpticalFlowFarneback(a, b, f0.astype(np.float32).copy(), **p)
+    out["cases"] = np.array(names)
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(OUT, "farneback_initflow_cv2.npz"), **out)
+    print("farneback_initflow_cv2.npz", len(names), "cases")
+
+
 def make_roi():
     out = {}
     for ds, script, consts, frame_hw in [
@@ -362,6 +387,10 @@ def make_frames():
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "farneback":
         make_farneback()
+        make_farneback_initflow()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "initflow":
+        make_farneback_initflow()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "frames":
         make_frames()
@@ -373,6 +402,7 @@ if __name__ == "__main__":
         make_segment()
         sys.exit(0)
     make_farneback()
+    make_farneback_initflow()
     make_roi()
     make_events()
     make_events_scheme2()

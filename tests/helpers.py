@@ -17,6 +17,29 @@ PARAM_SETS = {
     "grasp_gaussian": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2, flags=256),
     "gaussian_w10": dict(pyr_scale=0.6, levels=2, winsize=10, iterations=2, poly_n=7, poly_sigma=1.5, flags=256),
 }
+# OPTFLOW_USE_INITIAL_FLOW (flag 4) sets of tests/golden/farneback_initflow_cv2.npz: one iteration, so that the result
+# still depends on the initial flow (three iterations converge to the flags=0 answer within 1e-5 px)
+INIT_PARAM_SETS = {
+    "grasp_init": dict(pyr_scale=0.5, levels=3, winsize=15, iterations=1, poly_n=5, poly_sigma=1.2, flags=4),
+    "gaussian_init": dict(pyr_scale=0.6, levels=2, winsize=10, iterations=2, poly_n=7, poly_sigma=1.5, flags=4 | 256),
+}
+
+
+def check_initial_flow(golden, farneback, what):
+    """Shared by the oracle, emulator and GPU tests: `farneback(prev, next, flow0, **params)` -> flow, against cv2's
+    result with the same initial flow, and (sanity of the fixture) NOT equal to the result without it."""
+    g = golden.fb_init
+    for case in [str(c) for c in g["cases"]]:
+        prev, nxt, f0 = golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"], g[f"{case}__flow0"]
+        for pname, p in INIT_PARAM_SETS.items():
+            want = g[f"{case}__{pname}"]
+            got = farneback(prev, nxt, f0.copy(), **p)
+            d = flow_err(got, want)
+            assert d.mean() <= 1e-4 and d.max() <= 1e-3, f"{what} {case} {pname}: EPE mean {d.mean():.3e} max {d.max():.3e}"
+            zero = farneback(prev, nxt, np.zeros_like(f0), **p)
+            assert flow_err(zero, want).max() > 1e-2, f"{what} {case} {pname}: fixture does not depend on the initial flow"
+
+
 # Flow tolerances vs OpenCV's float Farneback (BASELINE.json bar: EPE <= 0.01 px).  Pixels whose 2x2 system is
 # near-singular (aperture problem inside a tiny window: winsize 3/4) amplify 1-ulp differences of ANY
 # implementation -- the C oracle itself differs from cv2 by up to 0.6 px on 0.003 % of such pixels of a 1080p
@@ -99,6 +122,7 @@ def load_oracle():
 class Golden:
     def __init__(self):
         self.fb = np.load(os.path.join(GOLDEN, "farneback_cv2.npz"))
+        self.fb_init = np.load(os.path.join(GOLDEN, "farneback_initflow_cv2.npz"))
         self.roi = np.load(os.path.join(GOLDEN, "roi_reference.npz"))
         self.ev = np.load(os.path.join(GOLDEN, "events_reference.npz"))
         self.ev2 = np.load(os.path.join(GOLDEN, "events_scheme2_reference.npz"))

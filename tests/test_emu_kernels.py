@@ -26,6 +26,14 @@ def test_emu_farneback_vs_golden(emu_engine, golden, pname):
             emu_engine.lib.check(emu_engine.lib.nsof_debug_big_tiles(emu_engine.handle, 0))
 
 
+def test_emu_farneback_initial_flow_vs_golden(emu_engine, golden, nsof):
+    """OPTFLOW_USE_INITIAL_FLOW through the C ABI (flow is in/out): cv2 goldens; flow=None with the flag raises."""
+    helpers.check_initial_flow(golden, lambda a, b, f0, **p: emu_engine.calcOpticalFlowFarneback(a, b, f0, **p), "emu vs cv2")
+    a = golden.fb["synth_40x33__prev"]
+    with pytest.raises(nsof.error):
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **helpers.INIT_PARAM_SETS["grasp_init"])
+
+
 @pytest.mark.parametrize("hw,fuse", [((150, 203), False), ((152, 204), True), ((150, 203), True)])
 def test_emu_stage_dumps_vs_oracle(emu_engine, oracle, hw, fuse):
     """Every intermediate (I, R0, R1, M, per-iteration flow) of every level against the oracle's dump, through the
@@ -83,7 +91,7 @@ def test_emu_errors_mirror_cv2(emu_engine, nsof):
     with pytest.raises(nsof.error):
         emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
     with pytest.raises(NotImplementedError):
-        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=4))  # OPTFLOW_USE_INITIAL_FLOW
+        emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=8))  # not a cv2 flag
     with pytest.raises(NotImplementedError):
         emu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, winsize=1))
     z = emu_engine.calcOpticalFlowFarneback(a, a, None, **p)

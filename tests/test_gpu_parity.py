@@ -18,6 +18,14 @@ def test_gpu_library_is_the_cuda_build(gpu_engine, nsof):
 
 
 # ------------------------------------------------------------------------------------------- stage 2
+def test_farneback_initial_flow_vs_cv2_golden(gpu_engine, golden, nsof):
+    """OPTFLOW_USE_INITIAL_FLOW through the C ABI (flow is in/out): cv2 goldens; flow=None with the flag raises."""
+    helpers.check_initial_flow(golden, lambda a, b, f0, **p: gpu_engine.calcOpticalFlowFarneback(a, b, f0, **p), "gpu vs cv2")
+    a = golden.fb["synth_40x33__prev"]
+    with pytest.raises(nsof.error):
+        gpu_engine.calcOpticalFlowFarneback(a, a, None, **helpers.INIT_PARAM_SETS["grasp_init"])
+
+
 @pytest.mark.parametrize("pname", list(helpers.PARAM_SETS))
 def test_farneback_vs_cv2_golden(gpu_engine, golden, pname):
     p = helpers.PARAM_SETS[pname]
@@ -146,7 +154,7 @@ def test_errors_mirror_cv2(gpu_engine, nsof):
     with pytest.raises(nsof.error):
         gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, pyr_scale=1.0))
     with pytest.raises(NotImplementedError):
-        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=4))  # OPTFLOW_USE_INITIAL_FLOW
+        gpu_engine.calcOpticalFlowFarneback(a, a, None, **dict(p, flags=8))  # not a cv2 flag
     z = gpu_engine.calcOpticalFlowFarneback(a, a, None, **p)
     assert z.shape == (40, 40, 2) and z.dtype == np.float32 and not z.any()
 

@@ -17,6 +17,23 @@ def test_farneback_oracle_matches_cv2_golden(oracle, golden, pname):
         helpers.assert_flow_close(got, want, pname, f"oracle vs cv2 {case}")
 
 
+def test_farneback_oracle_initial_flow_matches_cv2(oracle, golden):
+    helpers.check_initial_flow(golden, lambda a, b, f0, **p: oracle.farneback(a, b, flow=f0, **p), "oracle vs cv2")
+
+
+def test_resize_area_oracle_matches_cv2():
+    """INTER_AREA of a 2-channel float image (the initial-flow downscale), bit for bit against cv2.resize: integer
+    ratios (the unrolled fast path), fractional ratios (DecimateAlpha tables), identity."""
+    import cv2
+    o = helpers.load_oracle()
+    rng = np.random.default_rng(7)
+    for hs, ws, hd, wd in [(101, 75, 13, 9), (96, 128, 12, 16), (96, 128, 48, 64), (75, 101, 27, 36), (40, 33, 40, 33),
+                           (100, 130, 36, 47), (90, 120, 30, 40), (421, 523, 53, 65), (64, 64, 8, 64)]:
+        src = (rng.normal(size=(hs, ws, 2)) * 5).astype(np.float32)
+        want = cv2.resize(src, (wd, hd), interpolation=cv2.INTER_AREA)
+        assert np.array_equal(o.resize_area(src, hd, wd), want), (hs, ws, hd, wd)
+
+
 def test_level_geometry_matches_spec(oracle):
     # SURVEY.md section 8: 1080x1920 at (0.5, 3) -> 4 scales, ksize 3,3,9,19
     g = oracle.level_geometry(1080, 1920, 0.5, 3)
