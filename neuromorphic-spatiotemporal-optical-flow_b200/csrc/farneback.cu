@@ -741,6 +741,9 @@ static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream, int va
     if (X.params.iterations == 0)
         NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
                      jobs, X.flow_mul);
+    else if (X.params.flags & NSOF_FB_USE_INITIAL_FLOW)
+        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
+                     jobs, X.flow_mul);
     else
         NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first, X.max_tiles_um[kk], na, 1, 256, 0, stream,
                      jobs, X.flow_mul);

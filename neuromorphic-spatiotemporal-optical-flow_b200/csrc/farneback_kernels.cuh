@@ -309,7 +309,10 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 // 4 pixels per thread: float4 loads of R0, float4 stores of M, 80 independent R1 gathers in flight per thread.
 // (no launch bounds: 64 registers / 4 CTAs per SM as ptxas picks them; __launch_bounds__(256, 1) measured 2.35 -> 2.95 ms
 // per full-frame step, (256, 5) with its 60-byte spill 2.51 ms)
-NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
+// INIT = 1: the batch carries OPTFLOW_USE_INITIAL_FLOW items (J.init); a separate instantiation because the extra
+// branch costs the hot path 6 registers and with them the fourth CTA per SM (2.35 -> 2.62 ms per full-frame step)
+template <int INIT>
+NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
@@ -346,7 +349,7 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
             float r0v[5], mm[5];
             if (x + q < J.w) {
                 float2 d = make_float2(0.f, 0.f);
-                if (J.init) d = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q);
+                if (INIT && J.init) d = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q);
                 else if (J.ch > 0) d = fb_upsampled_flow(J, x + q, y, flow_mul);
 #pragma unroll
                 for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
@@ -364,6 +367,9 @@ NSOF_GLOBAL k_fb_um_first(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
             *(float4 *)(J.Ma + c * plane + o) = make_float4(mo[c][0], mo[c][1], mo[c][2], mo[c][3]);
     }
 }
+
+static void (*const k_fb_um_first)(const FbJob *, float) = k_fb_um_first_g<0>;
+static void (*const k_fb_um_first_init)(const FbJob *, float) = k_fb_um_first_g<1>;
 
 // ---------------------------------------------------------------------------------------------
 // OPTFLOW_USE_INITIAL_FLOW (A.8): flow_coarsest = resize(flow0, (w_k, h_k), INTER_AREA) * f32(scale_k), two-channel
@@ -799,13 +805,16 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 static void (*const k_fb_blur_solve)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<0>;
 static void (*const k_fb_blur_solve_gauss)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<1>;
 // a plain function-pointer name: template commas do not survive nested launch macros
+#ifndef FB_BS7_MINB
+#define FB_BS7_MINB 3
+#endif
 #ifndef FB_BS7_NT
 #define FB_BS7_NT 256
 #endif
 #define FB_BS7S_TW 32   // small tile: coarse levels / small batches are latency-bound, more and shorter CTAs
 #define FB_BS7S_TH 16
 #define FB_BS7S_NT 128
-static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, 3>;
+static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
 static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
 #define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
 #define FB_BS7S_SMEM (16 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
