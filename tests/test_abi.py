@@ -36,3 +36,30 @@ def test_no_cpu_fallback_without_a_device(nsof):
     a = np.zeros((40, 40), np.uint8)
     with pytest.raises(Exception):
         nsof.calcOpticalFlowFarneback(a, a, None, **nsof.FARNEBACK_PARAMS)
+
+
+# Register budgets of the hot kernels = the CTAs per SM their measured times depend on (65 536 registers per SM).  A
+# branch added to k_fb_um_first once cost it 6 registers, the fourth CTA per SM and 11 % of its time without any test
+# noticing (profiles/r1v12_variant_ab.txt); this reads the budgets back from the product build.
+REG_BUDGET = {
+    r"k_fb_um_first_gILi0E": 64,                      # 4 CTAs x 256 threads
+    r"k_fb_pyr_polyexp_tILi0ELi5ELi64ELi32E": 64,     # __launch_bounds__(256, 4)
+    r"k_fb_pyr_polyexp_tILi1ELi5ELi64ELi32E": 64,
+    r"k_fb_blur_solve_tILi7ELi64ELi32ELi256ELi3E": 80,  # 3 CTAs x 256 threads (shared memory allows no more)
+    r"k_fb_blur_solve_gILi0E": 72,                    # box window of the generic kernel
+}
+
+
+def test_hot_kernels_keep_their_register_budget(nsof):
+    import shutil
+    import subprocess
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(tool):
+        pytest.skip("cuobjdump not found")
+    out = subprocess.run([tool, "--dump-resource-usage", nsof.DEFAULT_LIB_PATH], capture_output=True, text=True).stdout
+    usage = dict(re.findall(r"Function (\S+):\s*\n\s*REG:(\d+)", out))
+    for pat, budget in REG_BUDGET.items():
+        hits = {k: int(v) for k, v in usage.items() if pat in k}
+        assert hits, f"kernel {pat} not found in libnsof.so"
+        for name, regs in hits.items():
+            assert regs <= budget, f"{name}: {regs} registers > budget {budget} (occupancy regression)"
