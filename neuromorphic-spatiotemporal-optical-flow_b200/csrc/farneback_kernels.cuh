@@ -719,13 +719,13 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #pragma unroll
         for (int j = 0; j < LH; j++) {
             v[j] = p[j * (PW / 2)];
-            if (j >= 1) p2[j - 1] = make_float2(v[j - 1].x + v[j].x, v[j - 1].y + v[j].y);
-            if (j >= 3) p4[j - 3] = make_float2(p2[j - 3].x + p2[j - 1].x, p2[j - 3].y + p2[j - 1].y);
-            if (j >= 7) p8[j - 7] = make_float2(p4[j - 7].x + p4[j - 3].x, p4[j - 7].y + p4[j - 3].y);
+            // the column pair is a natural operand of the packed FP32 add (FADD2): half the issue slots of this phase
+            if (j >= 1) p2[j - 1] = nsof_add2(v[j - 1], v[j]);
+            if (j >= 3) p4[j - 3] = nsof_add2(p2[j - 3], p2[j - 1]);
+            if (j >= 7) p8[j - 7] = nsof_add2(p4[j - 7], p4[j - 3]);
             if (j >= 14) {
                 const int y = j - 14;  // row y of the column pair is dead (already loaded)
-                p[y * (PW / 2)] = make_float2((p8[y].x + p4[y + 8].x) + (p2[y + 12].x + v[j].x),
-                                              (p8[y].y + p4[y + 8].y) + (p2[y + 12].y + v[j].y));
+                p[y * (PW / 2)] = nsof_add2(nsof_add2(p8[y], p4[y + 8]), nsof_add2(p2[y + 12], v[j]));
             }
         }
     }

@@ -110,6 +110,7 @@ static inline void nsof_mbar_wait(nsof_mbar_t *, unsigned) {}
 static inline void nsof_prefetch_l2(const void *, unsigned) {}
 #define NSOF_LANE 0
 #define NSOF_SYNCWARP() ((void)0)
+static inline float2 nsof_add2(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 #else
 typedef unsigned long long nsof_mbar_t;
 __device__ __forceinline__ unsigned nsof_smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -150,4 +151,17 @@ __device__ __forceinline__ void nsof_prefetch_l2(const void *src, unsigned bytes
 }
 #define NSOF_LANE ((int)(threadIdx.x & 31))
 #define NSOF_SYNCWARP() __syncwarp()
+// Packed FP32 add of Blackwell (add.rn.f32x2 -> SASS FADD2): two IEEE round-to-nearest additions in one issue slot,
+// per component identical to a scalar FADD.  For kernels that are bound by instruction issue, not by the FP32 pipe.
+#ifndef NSOF_PACKED_F32
+#define NSOF_PACKED_F32 1
+#endif
+__device__ __forceinline__ float2 nsof_add2(float2 a, float2 b)
+{
+#if NSOF_PACKED_F32
+    return __fadd2_rn(a, b);
+#else
+    return make_float2(a.x + b.x, a.y + b.y);
+#endif
+}
 #endif
