@@ -280,6 +280,71 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
     out[4] = r6 * r2 + r5 * r3;
 }
 
+// Two pixels at once with the packed FP32 instructions of Blackwell (FMUL2 / FFMA2 / FADD2): the same operations as
+// fb_um_pixel in the same order, the two pixels in the two halves of every operand, so the ~60 FP32 instructions per
+// pixel of UpdateMatrices take half the issue slots.  The 2 x 20 gathers stay scalar loads (data-dependent addresses).
+NSOF_DEV float nsof_um_border_scale(int x, int y, int w, int h)
+{
+    if ((unsigned)(x - 5) < (unsigned)(w - 10) && (unsigned)(y - 5) < (unsigned)(h - 10)) return 1.f;
+    const int xr = w - 1 - x, yb = h - 1 - y;
+    float scale = (x < 2 ? 0.14f : (x < 5 ? 0.4472f : 1.f));
+    scale *= (xr < 2 ? 0.14f : (xr < 5 ? 0.4472f : 1.f));
+    scale *= (y < 2 ? 0.14f : (y < 5 ? 0.4472f : 1.f));
+    scale *= (yb < 2 ? 0.14f : (yb < 5 ? 0.4472f : 1.f));
+    return scale;
+}
+
+NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int h, int w, int xa, int ya, int xb,
+                           int yb, float2 dx, float2 dy, const float2 r0v[5], float2 out[5])
+{
+    float2 fx = nsof_add2(make_float2((float)xa, (float)xb), dx), fy = nsof_add2(make_float2((float)ya, (float)yb), dy);
+    const int x1a = (int)floorf(fx.x), y1a = (int)floorf(fy.x), x1b = (int)floorf(fx.y), y1b = (int)floorf(fy.y);
+    fx = nsof_add2(fx, make_float2(-(float)x1a, -(float)x1b));
+    fy = nsof_add2(fy, make_float2(-(float)y1a, -(float)y1b));
+    const bool ina = (unsigned)x1a < (unsigned)(w - 1) && (unsigned)y1a < (unsigned)(h - 1);
+    const bool inb = (unsigned)x1b < (unsigned)(w - 1) && (unsigned)y1b < (unsigned)(h - 1);
+    const float2 one = make_float2(1.f, 1.f), mone = make_float2(-1.f, -1.f);
+    const float2 ox = nsof_fma2(fx, mone, one), oy = nsof_fma2(fy, mone, one);  // 1 - fx, 1 - fy (one rounding each)
+    const float2 a00 = nsof_mul2(ox, oy), a01 = nsof_mul2(fx, oy), a10 = nsof_mul2(ox, fy), a11 = nsof_mul2(fx, fy);
+    const float *pa = R1 + (ina ? (size_t)y1a * pitch + x1a : (size_t)0);
+    const float *pb = R1 + (inb ? (size_t)y1b * pitch + x1b : (size_t)0);
+    float2 q[5];
+#pragma unroll
+    for (int c = 0; c < 5; c++) {
+        const float2 v00 = make_float2(NSOF_LDG(pa), NSOF_LDG(pb)), v01 = make_float2(NSOF_LDG(pa + 1), NSOF_LDG(pb + 1));
+        const float2 v10 = make_float2(NSOF_LDG(pa + pitch), NSOF_LDG(pb + pitch));
+        const float2 v11 = make_float2(NSOF_LDG(pa + pitch + 1), NSOF_LDG(pb + pitch + 1));
+        q[c] = nsof_fma2(a11, v11, nsof_fma2(a10, v10, nsof_fma2(a01, v01, nsof_mul2(a00, v00))));
+        pa += plane;
+        pb += plane;
+    }
+    const float2 half = make_float2(0.5f, 0.5f), mhalf = make_float2(-0.5f, -0.5f), quarter = make_float2(0.25f, 0.25f);
+    const float2 t4 = nsof_mul2(nsof_add2(r0v[2], q[2]), half), t5 = nsof_mul2(nsof_add2(r0v[3], q[3]), half);
+    const float2 t6 = nsof_mul2(nsof_add2(r0v[4], q[4]), quarter), u6 = nsof_mul2(r0v[4], half);
+    float2 r2 = make_float2(ina ? q[0].x : 0.f, inb ? q[0].y : 0.f);
+    float2 r3 = make_float2(ina ? q[1].x : 0.f, inb ? q[1].y : 0.f);
+    float2 r4 = make_float2(ina ? t4.x : r0v[2].x, inb ? t4.y : r0v[2].y);
+    float2 r5 = make_float2(ina ? t5.x : r0v[3].x, inb ? t5.y : r0v[3].y);
+    float2 r6 = make_float2(ina ? t6.x : u6.x, inb ? t6.y : u6.y);
+    // (r0 - r) * 0.5 == fma(r, -0.5, r0 * 0.5): scaling by a power of two commutes with the rounding
+    r2 = nsof_fma2(r2, mhalf, nsof_mul2(r0v[0], half));
+    r3 = nsof_fma2(r3, mhalf, nsof_mul2(r0v[1], half));
+    r2 = nsof_add2(r2, nsof_fma2(r6, dx, nsof_mul2(r4, dy)));
+    r3 = nsof_add2(r3, nsof_fma2(r5, dx, nsof_mul2(r6, dy)));
+    const bool bord = (unsigned)(xa - 5) >= (unsigned)(w - 10) || (unsigned)(ya - 5) >= (unsigned)(h - 10) ||
+                      (unsigned)(xb - 5) >= (unsigned)(w - 10) || (unsigned)(yb - 5) >= (unsigned)(h - 10);
+    if (bord) {
+        const float2 sc = make_float2(nsof_um_border_scale(xa, ya, w, h), nsof_um_border_scale(xb, yb, w, h));
+        r2 = nsof_mul2(r2, sc); r3 = nsof_mul2(r3, sc); r4 = nsof_mul2(r4, sc); r5 = nsof_mul2(r5, sc); r6 = nsof_mul2(r6, sc);
+    }
+    const float2 r66 = nsof_mul2(r6, r6);
+    out[0] = nsof_fma2(r4, r4, r66);
+    out[1] = nsof_mul2(nsof_add2(r4, r5), r6);
+    out[2] = nsof_fma2(r5, r5, r66);
+    out[3] = nsof_fma2(r4, r2, nsof_mul2(r6, r3));
+    out[4] = nsof_fma2(r6, r2, nsof_mul2(r5, r3));
+}
+
 // First UpdateMatrices of a level; the initial flow is zero (coarsest level) or the coarser
 // level's flow upsampled on the fly (S2-f: resize INTER_LINEAR, times f32(1/pyr_scale)); the
 // upsampled field itself is never written (UpdateFlow_Blur overwrites flow entirely).
@@ -312,7 +377,12 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 // INIT = 1: the batch carries OPTFLOW_USE_INITIAL_FLOW items (J.init); a separate instantiation because the extra
 // branch costs the hot path 6 registers and with them the fourth CTA per SM (2.35 -> 2.62 ms per full-frame step)
 template <int INIT>
-NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
+#ifdef FB_UM_MINB
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(
+#else
+NSOF_GLOBAL k_fb_um_first_g(
+#endif
+    const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
@@ -344,6 +414,32 @@ NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
             r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
         }
         float mo[5][4];
+#ifndef FB_UM_PAIR
+#define FB_UM_PAIR 0
+#endif
+#if FB_UM_PAIR
+        if (x + 3 < J.w) {  // whole group inside the image: two pixel pairs through the packed FP32 path (fb_um_pixel2)
+#pragma unroll
+            for (int q = 0; q < 4; q += 2) {
+                float2 da = make_float2(0.f, 0.f), db = make_float2(0.f, 0.f);
+                if (INIT && J.init) {
+                    da = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q);
+                    db = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q + 1);
+                } else if (J.ch > 0) {
+                    da = fb_upsampled_flow(J, x + q, y, flow_mul);
+                    db = fb_upsampled_flow(J, x + q + 1, y, flow_mul);
+                }
+                if (J.guard) { fb_um_guard(J, y, da.y); fb_um_guard(J, y, db.y); }
+                float2 r0p[5], mp[5];
+#pragma unroll
+                for (int c = 0; c < 5; c++) r0p[c] = make_float2(r0[c][q], r0[c][q + 1]);
+                fb_um_pixel2(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, x + q + 1, y, make_float2(da.x, db.x),
+                             make_float2(da.y, db.y), r0p, mp);
+#pragma unroll
+                for (int c = 0; c < 5; c++) { mo[c][q] = mp[c].x; mo[c][q + 1] = mp[c].y; }
+            }
+        } else
+#endif
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             float r0v[5], mm[5];
@@ -784,6 +880,42 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #ifndef FB_BS_UNROLL
 #define FB_BS_UNROLL 2
 #endif
+#ifndef FB_BS_PAIR
+#define FB_BS_PAIR 1
+#endif
+#if FB_BS_PAIR
+    // two pixels per thread and iteration (i and i + NT: same column, NT / TW rows apart when NT is a multiple of TW), in
+    // the two halves of packed FP32 operands (fb_um_pixel2)
+    for (int i = NSOF_TID; i < TW * TH; i += 2 * NSOF_NT) {
+        const int ib = i + NSOF_NT;
+        const int lxa = i % TW, lya = i / TW, lxb = ib % TW, lyb = ib / TW;
+        const int xa = tx0 + lxa, ya = ty0 + lya, xb = tx0 + lxb, yb = ty0 + lyb;
+        const bool va = xa < J.w && ya < J.y_hi, vb = ib < TW * TH && xb < J.w && yb < J.y_hi;
+        if (va && vb) {
+            const float2 fa = *(const float2 *)(sM + (lya / RPP) * SP + TH * PW + (lya % RPP) * (2 * TW) + 2 * lxa);
+            const float2 fb = *(const float2 *)(sM + (lyb / RPP) * SP + TH * PW + (lyb % RPP) * (2 * TW) + 2 * lxb);
+            const size_t oa = (size_t)ya * J.pitch + xa, ob = (size_t)yb * J.pitch + xb;
+            float2 r0v[5], mm[5];
+#pragma unroll
+            for (int c = 0; c < 5; c++) r0v[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
+            if (J.guard) { fb_um_guard(J, ya, fa.y); fb_um_guard(J, yb, fb.y); }
+            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, xa, ya, xb, yb, make_float2(fa.x, fb.x), make_float2(fa.y, fb.y), r0v, mm);
+#pragma unroll
+            for (int c = 0; c < 5; c++) { Mout[c * plane + oa] = mm[c].x; Mout[c * plane + ob] = mm[c].y; }
+        } else if (va || vb) {
+            const int lx = va ? lxa : lxb, ly = va ? lya : lyb, x = va ? xa : xb, y = va ? ya : yb;
+            const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+            const size_t o = (size_t)y * J.pitch + x;
+            float r0v[5], mm[5];
+#pragma unroll
+            for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(R0 + c * plane + o);
+            if (J.guard) fb_um_guard(J, y, f.y);
+            fb_um_pixel(R1, plane, J.pitch, J.h, J.w, x, y, f.x, f.y, r0v, mm);
+#pragma unroll
+            for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c];
+        }
+    }
+#else
     constexpr int UNR3B = FB_BS_UNROLL;
 #pragma unroll UNR3B
     for (int i = NSOF_TID; i < TW * TH; i += NSOF_NT) {
@@ -800,6 +932,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #pragma unroll
         for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c];
     }
+#endif
 }
 
 static void (*const k_fb_blur_solve)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<0>;

@@ -111,6 +111,8 @@ static inline void nsof_prefetch_l2(const void *, unsigned) {}
 #define NSOF_LANE 0
 #define NSOF_SYNCWARP() ((void)0)
 static inline float2 nsof_add2(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+static inline float2 nsof_mul2(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+static inline float2 nsof_fma2(float2 a, float2 b, float2 c) { return make_float2(a.x * b.x + c.x, a.y * b.y + c.y); }
 #else
 typedef unsigned long long nsof_mbar_t;
 __device__ __forceinline__ unsigned nsof_smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -162,6 +164,23 @@ __device__ __forceinline__ float2 nsof_add2(float2 a, float2 b)
     return __fadd2_rn(a, b);
 #else
     return make_float2(a.x + b.x, a.y + b.y);
+#endif
+}
+// FMUL2 / FFMA2: per component the same as __fmul_rn / __fmaf_rn
+__device__ __forceinline__ float2 nsof_mul2(float2 a, float2 b)
+{
+#if NSOF_PACKED_F32
+    return __fmul2_rn(a, b);
+#else
+    return make_float2(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y));
+#endif
+}
+__device__ __forceinline__ float2 nsof_fma2(float2 a, float2 b, float2 c)
+{
+#if NSOF_PACKED_F32
+    return __ffma2_rn(a, b, c);
+#else
+    return make_float2(__fmaf_rn(a.x, b.x, c.x), __fmaf_rn(a.y, b.y, c.y));
 #endif
 }
 #endif
