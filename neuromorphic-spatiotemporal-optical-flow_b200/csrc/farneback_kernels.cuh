@@ -377,12 +377,7 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 // INIT = 1: the batch carries OPTFLOW_USE_INITIAL_FLOW items (J.init); a separate instantiation because the extra
 // branch costs the hot path 6 registers and with them the fourth CTA per SM (2.35 -> 2.62 ms per full-frame step)
 template <int INIT>
-#ifdef FB_UM_MINB
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(
-#else
-NSOF_GLOBAL k_fb_um_first_g(
-#endif
-    const FbJob *NSOF_RESTRICT jobs, float flow_mul)
+NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
 {
     const FbJob J = jobs[NSOF_BY];
     const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
@@ -414,32 +409,8 @@ NSOF_GLOBAL k_fb_um_first_g(
             r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
         }
         float mo[5][4];
-#ifndef FB_UM_PAIR
-#define FB_UM_PAIR 0
-#endif
-#if FB_UM_PAIR
-        if (x + 3 < J.w) {  // whole group inside the image: two pixel pairs through the packed FP32 path (fb_um_pixel2)
-#pragma unroll
-            for (int q = 0; q < 4; q += 2) {
-                float2 da = make_float2(0.f, 0.f), db = make_float2(0.f, 0.f);
-                if (INIT && J.init) {
-                    da = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q);
-                    db = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x + q + 1);
-                } else if (J.ch > 0) {
-                    da = fb_upsampled_flow(J, x + q, y, flow_mul);
-                    db = fb_upsampled_flow(J, x + q + 1, y, flow_mul);
-                }
-                if (J.guard) { fb_um_guard(J, y, da.y); fb_um_guard(J, y, db.y); }
-                float2 r0p[5], mp[5];
-#pragma unroll
-                for (int c = 0; c < 5; c++) r0p[c] = make_float2(r0[c][q], r0[c][q + 1]);
-                fb_um_pixel2(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, x + q + 1, y, make_float2(da.x, db.x),
-                             make_float2(da.y, db.y), r0p, mp);
-#pragma unroll
-                for (int c = 0; c < 5; c++) { mo[c][q] = mp[c].x; mo[c][q + 1] = mp[c].y; }
-            }
-        } else
-#endif
+        // (pixel pairs through fb_um_pixel2, as in phase 3b of the blur+solve kernel, need 90 registers here: 2.36 -> 2.97 ms
+        // per full-frame step, 2.71 / 2.63 ms when held to 80 / 64 registers by launch bounds; left scalar)
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             float r0v[5], mm[5];
@@ -833,6 +804,46 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         const int x = tx0 + lx, y = ty0 + ly;
         if (x >= J.w || y >= J.y_hi) continue;
         float s[5][4];
+#ifndef FB_BS_PACK3A
+#define FB_BS_PACK3A 1
+#endif
+#if FB_BS_PACK3A
+        static_assert(M == 7 && ML - M == 1 && NV == 5, "the packed window sums are written for columns v[1..18] of 20");
+#pragma unroll
+        for (int c = 0; c < 5; c++) {
+            // window of output q = v[1+q .. 15+q].  v[4..15] is common to the four windows: it arrives as six aligned
+            // pairs (halves of the float4 reads) and is summed as a tree of packed adds (5 FADD2 + 1 FADD instead of 11
+            // FADD); the three private columns on either side are added with two shared partial sums.
+            const float4 *q = (const float4 *)(sM + c * SP + ly * PW + lx);
+            const float4 t0 = q[0], t1 = q[1], t2 = q[2], t3 = q[3], t4 = q[4];
+            const float2 c2 = nsof_add2(nsof_add2(nsof_add2(make_float2(t1.x, t1.y), make_float2(t1.z, t1.w)),
+                                                  nsof_add2(make_float2(t2.x, t2.y), make_float2(t2.z, t2.w))),
+                                        nsof_add2(make_float2(t3.x, t3.y), make_float2(t3.z, t3.w)));
+            const float common = c2.x + c2.y;
+            const float a23 = t0.z + t0.w, b12 = t4.x + t4.y;  // v2 + v3, v16 + v17
+            s[c][0] = common + (t0.y + a23);
+            s[c][1] = common + (a23 + t4.x);
+            s[c][2] = common + (t0.w + b12);
+            s[c][3] = common + (b12 + t4.z);
+        }
+        float fxv[4], fyv[4];
+        {
+            // 2x2 solve of two pixels per packed instruction (same operations as the scalar form below)
+            const float2 sc = make_float2(scale, scale), nsc = make_float2(-scale, -scale), eps = make_float2(1e-3f, 1e-3f);
+#pragma unroll
+            for (int q = 0; q < 4; q += 2) {
+                const float2 g11 = nsof_mul2(make_float2(s[0][q], s[0][q + 1]), sc), g12 = nsof_mul2(make_float2(s[1][q], s[1][q + 1]), sc);
+                const float2 n12 = nsof_mul2(make_float2(s[1][q], s[1][q + 1]), nsc), g22 = nsof_mul2(make_float2(s[2][q], s[2][q + 1]), sc);
+                const float2 h1 = nsof_mul2(make_float2(s[3][q], s[3][q + 1]), sc), h2 = nsof_mul2(make_float2(s[4][q], s[4][q + 1]), sc);
+                const float2 det = nsof_fma2(n12, g12, nsof_fma2(g11, g22, eps));
+                const float2 idet = make_float2(1.f / det.x, 1.f / det.y);
+                const float2 fx2 = nsof_mul2(nsof_fma2(n12, h1, nsof_mul2(g11, h2)), idet);
+                const float2 fy2 = nsof_mul2(nsof_fma2(n12, h2, nsof_mul2(g22, h1)), idet);
+                fxv[q] = fx2.x; fxv[q + 1] = fx2.y;
+                fyv[q] = fy2.x; fyv[q + 1] = fy2.y;
+            }
+        }
+#else
 #pragma unroll
         for (int c = 0; c < 5; c++) {
             float v[NV * 4];
@@ -862,6 +873,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             fxv[q] = (g11 * h2 - g12 * h1) * idet;
             fyv[q] = (g22 * h1 - g12 * h2) * idet;
         }
+#endif
         if (last) {
             float2 *fo = J.flow + (size_t)y * J.fpitch + x;
 #pragma unroll
