@@ -10,7 +10,10 @@
  * modules/video/src/optflowgf.cpp, FarnebackOpticalFlowImpl::calc.  This file
  * restates that published algorithm and is PINNED
  * against cv2 4.13.0 outputs generated in the build container
- * (tests/golden/make_golden.py -> tests/golden/ npz files).
+ * (tests/golden/make_golden.py -> tests/golden/ npz files): flags = 0 with the three
+ * parameter sets the reference ships, OPTFLOW_FARNEBACK_GAUSSIAN (farneback_cv2.npz),
+ * OPTFLOW_USE_INITIAL_FLOW (farneback_initflow_cv2.npz; its INTER_AREA downscale is
+ * bit-exact against cv2.resize, tests/test_oracle_golden.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs may load this library.  The product path never does.
