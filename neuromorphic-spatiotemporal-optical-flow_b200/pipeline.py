@@ -47,13 +47,28 @@ def chunk_schedule(n_pairs: int, first: int = 1, grow: int = 2, cap: int = 8):
 class SequencePipeline:
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
                  sim=dict(dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, vds=1.0), full_frame: bool = False,
-                 packed: bool = False, chunks=None, overlap: bool = True, s2_streams: int = 2, segment: bool = False):
+                 packed: bool = False, chunks=None, overlap: bool = True, s2_streams: int = 2, segment: bool = False,
+                 roi_state: str = "scripts", stage1: str = "simulate"):
+        """roi_state: which array state gates pair (t, t+1).  "scripts" (default): the state BEFORE the
+        pair -- all four scripts overwrite memimg2 with memimg1 (optical_flow_seg.py:435), so pair i reads slice
+        OFFSET + i of constructed3DMatrix (the initial state for pair 0: every cell above THRES, ROI = the whole cell
+        grid).  "notebook": the state AFTER the pair, slice OFFSET + i + 1, the un-bugged form of demo.ipynb cell 11.
+        stage1: "simulate" (frame-mode simulator on the clip's frames) or "given" (the caller fills `self.currents`
+        [F][C][Hc][Wc] with pre-computed array states, slice t = constructed3DMatrix[:, :, OFFSET + t], as the
+        scripts read them from the .mat: steps 1-2 are skipped)."""
         import torch
         self.torch = torch
         self.eng, self.lib, self.h = engine, engine.lib, engine.handle
         self.segment = bool(segment)  # also run task_results / process_flow_region on every ROI flow (8(f) rank 1)
         self.C, self.F, self.H, self.W = int(clips), int(frames), int(H), int(W)
         self.cfg = cfg or RoiConfig()
+        if self.cfg.FLAG != 2:
+            raise NotImplementedError("the sequence pipelines batch the merged region (FLAG 2, what every script ships "
+                                      "with); FLAG 1 (process_separate_regions) is served by Engine.opticalFlow3D")
+        if roi_state not in ("scripts", "notebook") or stage1 not in ("simulate", "given"):
+            raise ValueError("roi_state must be 'scripts' or 'notebook', stage1 'simulate' or 'given'")
+        self.roi_state, self.stage1_mode = roi_state, stage1
+        self.roi_shift = 0 if roi_state == "scripts" else 1
         self.full_frame = bool(full_frame)  # ROI = 100 %: skip the gate, run Farneback on whole frames
         self.dev = torch.device(f"cuda:{engine.device}")
         M = self.cfg.MEMSIZE
@@ -77,8 +92,11 @@ class SequencePipeline:
         f64, i32 = torch.float64, torch.int32
         self.cells = torch.empty((self.F, self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
         self.w = torch.empty((self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
-        # currents[t] = array state after the pair (t, t+1): slice t of constructed3DMatrix
-        self.currents = torch.empty((self.F - 1, self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
+        # currents[t] = slice t of constructed3DMatrix: [0] the initial state (w = wini), [t + 1] the
+        # array state after the pair (t, t+1).  Pair t is gated by slice t + roi_shift.
+        self.currents = torch.empty((self.F, self.C, self.Hc, self.Wc), dtype=f64, device=self.dev)
+        lam = np.log(PARAMS["Roff"] / PARAMS["Ron"])    # calculate_resistances_exp (vehicle.m:233-236), vds / R
+        self.currents[0] = float(sim["vds"]) / (PARAMS["Ron"] / np.exp(-lam * (1.0 - PARAMS["wini"])))
         self.thr = torch.from_numpy(u8_threshold_table(self.cfg.MAP_A, self.cfg.MAP_B)).to(self.dev)
         self.memimg = torch.zeros((self.n_pairs, self.Hc, self.Wc), dtype=torch.uint8, device=self.dev)
         # the ROI kernel stores its rectangles straight into pinned host memory (device-addressable under unified
@@ -90,7 +108,10 @@ class SequencePipeline:
         # the ROI crops packed back to back (outside its rectangle a pair's flow is zero by definition)
         self.packed_mode = bool(packed)
         if packed:
-            cap = self.n_pairs * self.H * self.W * 2 // (1 if full_frame else 3)
+            # ROI crops: about a third of the frames' pixels plus, in the scripts' form, one whole frame per clip (the
+            # initial state opens every cell); a step that needs more raises MemoryError in build_descs
+            cap = (self.n_pairs * self.H * self.W * 2 if full_frame
+                   else (self.n_pairs * self.H * self.W // 3 + self.C * self.H * self.W) * 2)
             self.packed = torch.empty((cap,), dtype=torch.float32, device=self.dev)
             self.flow = None
         else:
@@ -140,16 +161,19 @@ class SequencePipeline:
         p0, p1 = self.chunks[j]
         f0 = 0 if j == 0 else p0 + 1      # frames not compressed yet
         ncell = self.Hc * self.Wc
-        lib.check(lib.nsof_lanczos3_compress_u8(h, frames.data_ptr() + f0 * Cn * H * W, (p1 + 1 - f0) * Cn, H, W, W,
-                                                H * W, self.Hc, self.Wc, self.cells.data_ptr() + f0 * Cn * ncell * 8,
-                                                st), "lanczos3_compress")
-        if j == 0:
-            self.w.fill_(float(PARAMS["wini"]))
-        lib.check(lib.nsof_frame_sim_run_f64(h, self.cells.data_ptr() + p0 * Cn * ncell * 8, p1 - p0 + 1, Cn, self.Hc,
-                                             self.Wc, self.w.data_ptr(), self.currents.data_ptr() + p0 * Cn * ncell * 8,
-                                             C.byref(self.sp), C.byref(self.fsp), st), "frame_sim_run")
+        if self.stage1_mode == "simulate":
+            lib.check(lib.nsof_lanczos3_compress_u8(h, frames.data_ptr() + f0 * Cn * H * W, (p1 + 1 - f0) * Cn, H, W, W,
+                                                    H * W, self.Hc, self.Wc, self.cells.data_ptr() + f0 * Cn * ncell * 8,
+                                                    st), "lanczos3_compress")
+            if j == 0:
+                self.w.fill_(float(PARAMS["wini"]))
+            lib.check(lib.nsof_frame_sim_run_f64(h, self.cells.data_ptr() + p0 * Cn * ncell * 8, p1 - p0 + 1, Cn, self.Hc,
+                                                 self.Wc, self.w.data_ptr(),
+                                                 self.currents.data_ptr() + (p0 + 1) * Cn * ncell * 8,
+                                                 C.byref(self.sp), C.byref(self.fsp), st), "frame_sim_run")
         i0, n = p0 * Cn, (p1 - p0) * Cn
-        lib.check(lib.nsof_roi_from_state_f64(h, self.currents.data_ptr() + i0 * ncell * 8, n, C.byref(self.rp),
+        lib.check(lib.nsof_roi_from_state_f64(h, self.currents.data_ptr() + (i0 + self.roi_shift * Cn) * ncell * 8, n,
+                                              C.byref(self.rp),
                                               self.thr.data_ptr(), self.memimg.data_ptr() + i0 * ncell, None, None,
                                               self.n_rects_host.data_ptr() + i0 * 4,
                                               self.rects_pinned.data_ptr() + i0 * _lib.NSOF_MAX_RECTS * 16, None, st),
@@ -306,11 +330,12 @@ class DeviceStream:
     """
 
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 depth: int = 2, segment: bool = False, full_frame: bool = False):
+                 depth: int = 2, segment: bool = False, full_frame: bool = False, roi_state: str = "scripts"):
         assert depth >= 2
         one = [(0, int(frames) - 1)]
         self.slots = [SequencePipeline(engine if i == 0 else Engine(engine.device, lib=engine.lib), clips, frames, H, W, cfg,
-                                       chunks=one, overlap=True, s2_streams=1, segment=segment, full_frame=full_frame)
+                                       chunks=one, overlap=True, s2_streams=1, segment=segment, full_frame=full_frame,
+                                       roi_state=roi_state)
                       for i in range(depth)]
         self.k = 0
         self.pending = None  # (slot, frames) of the step whose stage 1 is queued
@@ -355,7 +380,7 @@ class HostPipeline:
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
                  slots: int | None = None, full_frame: bool = False, lib=None, chunks=None, copy_streams=None,
-                 segment: bool = False):
+                 segment: bool = False, roi_state: str = "scripts"):
         import torch
         self.torch = torch
         self.dev = torch.device(f"cuda:{device}")
@@ -370,7 +395,7 @@ class HostPipeline:
             if chunks is None:
                 chunks = chunk_schedule(self.F - 1, first=1, grow=2, cap=4)
             self.pipe = SequencePipeline(self.eng, clips, frames, H, W, cfg, full_frame=full_frame, packed=True,
-                                         chunks=chunks, overlap=True, segment=segment)
+                                         chunks=chunks, overlap=True, segment=segment, roi_state=roi_state)
             if full_frame:  # no stage 1: the side stream/handle of the pipe is unused
                 self.pipe.side = None
             self.frames = torch.empty((self.F, self.C, H, W), dtype=torch.uint8, device=self.dev)
@@ -511,7 +536,8 @@ class HostStream:
     """
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 depth: int = 3, full_frame: bool = False, lib=None, chunks=None, segment: bool = False):
+                 depth: int = 3, full_frame: bool = False, lib=None, chunks=None, segment: bool = False,
+                 roi_state: str = "scripts"):
         assert depth >= 2
         import torch
         dev = torch.device(f"cuda:{device}")
@@ -524,7 +550,8 @@ class HostStream:
             chunks = [((n * i + parts - 1) // parts, (n * (i + 1) + parts - 1) // parts) for i in range(parts)]
         self.copy_streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
         self.slots = [HostPipeline(device, clips, frames, H, W, cfg, full_frame=full_frame, lib=lib, chunks=chunks,
-                                   copy_streams=self.copy_streams, segment=segment) for _ in range(depth)]
+                                   copy_streams=self.copy_streams, segment=segment, roi_state=roi_state)
+                      for _ in range(depth)]
         self.k = 0            # steps submitted
         self.flowed = 0       # steps whose Farneback batches are queued
         self.collected = 0    # steps handed out

@@ -43,14 +43,18 @@ def farneback(prev, nxt, **p):
     return _oracle.farneback(np.ascontiguousarray(prev), np.ascontiguousarray(nxt), **p)
 
 
-def clip_rects(frames, cfg=GRASP, sim=None):
-    """Stage 1 for one clip (F, H, W) uint8 -> (memimg (F-1, Hc, Wc), rects list of (x0,y0,x1,y1) or None)."""
+def clip_rects(frames, cfg=GRASP, sim=None, roi_state="scripts"):
+    """Stage 1 for one clip (F, H, W) uint8 -> (memimg (F-1, Hc, Wc), rects list of (x0,y0,x1,y1) or None).
+    roi_state "scripts": pair t is gated by the array state BEFORE it (slice OFFSET + t of constructed3DMatrix; all
+    four scripts overwrite memimg2 with memimg1, optical_flow_seg.py:435); "notebook": by the state after it
+    (slice OFFSET + t + 1, demo.ipynb cell 11).  SURVEY.md 3.5."""
+    assert roi_state in ("scripts", "notebook")
     sim = sim or {}
     M = cfg["MEMSIZE"]
     H, W = frames.shape[1:]
     cells = np.stack([s1.compress_image(f, M, M) for f in frames])
     _, cur = s1.simulate_memristor_array_vec(cells, **sim)
-    memimg = s1.current_to_u8(cur[1:])  # slice t = state after pair (t, t+1)
+    memimg = s1.current_to_u8(cur[:-1] if roi_state == "scripts" else cur[1:])  # cur[0] = the initial state
     rects = []
     for t in range(len(frames) - 1):
         n, _, _, r = s1.roi_from_memimg(memimg[t], (H, W), M, M, cfg["THRES"], cfg["ext"], 2)
@@ -58,7 +62,8 @@ def clip_rects(frames, cfg=GRASP, sim=None):
     return memimg, rects
 
 
-def process_clip(frames, cfg=GRASP, params=FARNEBACK_PARAMS, full_frame=False, keep_flow=False, sim=None):
+def process_clip(frames, cfg=GRASP, params=FARNEBACK_PARAMS, full_frame=False, keep_flow=False, sim=None,
+                 roi_state="scripts"):
     """The reference path over one clip.  Returns (pairs, seconds, rects, flows or None)."""
     t0 = time.perf_counter()
     F, H, W = frames.shape
@@ -66,7 +71,7 @@ def process_clip(frames, cfg=GRASP, params=FARNEBACK_PARAMS, full_frame=False, k
     if full_frame:
         rects = [(0, 0, W, H)] * (F - 1)
     else:
-        _, rects = clip_rects(frames, cfg, sim)
+        _, rects = clip_rects(frames, cfg, sim, roi_state)
     for t in range(F - 1):
         flow = np.zeros((H, W, 2))  # optical_flow_seg.py:215
         r = rects[t]

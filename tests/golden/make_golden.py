@@ -384,7 +384,153 @@ def make_frames():
     print("frames_reference.npz", {k: v.shape for k, v in out.items() if hasattr(v, "shape") and v.ndim >= 2})
 
 
+def _script_namespace(script, names, consts):
+    """Top-level functions `names` of a reference script (source-sliced, unmodified) in one namespace together with
+    the script's module-level constants `consts` and its timing-list globals."""
+    import time
+    from numba import njit
+    src = open(os.path.join(REF, script), encoding="utf-8").read()
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert {n.name for n in body} == set(names), (script, names)
+    ns = dict(cv2=cv2, np=np, time=time, njit=njit, print=lambda *a, **k: None, mem_cal_times=[], mem_velocity_times=[],
+              mem_opticalflow_times=[], mem_task_times=[], mem_combination_times=[])
+    ns.update(consts)
+    exec(compile(ast.Module(body=body, type_ignores=[]), script, "exec"), ns)
+    return ns
+
+
+REALDATA = {
+    # dataset: (script, constants of that script, pairs kept with their crops, pairs kept with FULL frames)
+    "grasp": ("optical_flow_seg.py",
+              dict(MEMSIZE=80, OFFSET=0, EXTEND_HEIGHT_UPPER=20, EXTEND_HEIGHT_LOWER=20, EXTEND_WIDTH_LEFT=20,
+                   EXTEND_WIDTH_RIGHT=20, THRES=250, CONNECT=4, FLAG=2, PADDING=20, SEG_TH=1,
+                   farneback_params=PARAM_SETS["grasp"]), "12 consecutive", 1),
+    "autodriving": ("optical_flow_yolo.py",
+                    dict(MEMSIZE=200, OFFSET=15, EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, EXTEND_WIDTH_LEFT=60,
+                         EXTEND_WIDTH_RIGHT=60, THRES=114, CONNECT=4, FLAG=2, PADDING=60, SEG_TH=1,
+                         farneback_params=PARAM_SETS["grasp"]), "all non-empty", 2),
+}
+
+
+def make_realdata(which=("grasp", "autodriving")):
+    """configs[0] / configs[1] end to end: the body of the scripts' main loop (optical_flow_seg.py:413-545,
+    optical_flow_yolo.py:752-797 + the segmentation task the yolo script shares with the seg script) driven over the
+    shipped sequences with the reference's OWN functions (source-sliced: opticalFlow3D, process_merged_region,
+    update_transition_pic, task_results, process_flow_region, calculate_pixel_accuracy).  The only changes against the
+    scripts: the Windows-only sort key (`x.split('\\')`, optical_flow_seg.py:402) becomes os.path.basename, nothing is
+    written to disk, and YOLO (absent weights) is skipped.  The `mem_state2 = mem_state1` line (:435) is kept, so pair
+    i is gated by slice OFFSET + i.
+
+    Per dataset -> tests/golden/realdata_<ds>.npz:
+      all pairs   : rects, accuracy1 ("our method"), accuracy2 (full-frame baseline), dataset averages
+      kept pairs  : memimg, rectangle, the grey frames cropped to the rectangles that read them (the flow inside a
+                    rectangle depends on nothing else), cv2's flow of the crop at every 8th pixel of every 8th row
+                    (+ |flow| checksum; the GPU box has cv2 and compares every pixel live), the reference's motion_binary
+                    (bit-packed), the ground-truth mask (bit-packed), accuracy1
+      full pairs  : both whole grey frames, the baseline's motion_binary1 and accuracy2 (full-frame Farneback path,
+                    optical_flow_seg.py:492-545)
+    """
+    for ds in which:
+        script, consts, _, n_full = REALDATA[ds]
+        ns = _script_namespace(script, ["update_transition_pic", "process_separate_regions", "process_merged_region",
+                                        "opticalFlow3D", "task_results", "process_flow_region",
+                                        "calculate_pixel_accuracy"], consts)
+        base = f"{REF}/data/{ds}"
+        imgs = open(f"{base}/imgs.txt").read().splitlines()
+        mem_state = scipy.io.loadmat(f"{base}/constructed_3D_matrix.mat")["constructed3DMatrix"]
+        rgbimages = sorted([os.path.join(base, "RGB", i) for i in imgs],
+                           key=lambda x: int(os.path.basename(x).split(".")[0]))
+        M, OFFSET = consts["MEMSIZE"], consts["OFFSET"]
+        n_pairs = len(imgs) - 2
+        rects = np.zeros((n_pairs, 4), np.int32)
+        acc1 = np.zeros(n_pairs)
+        acc2 = np.zeros(n_pairs)
+        per_pair = {}
+        kernel = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (10, 10))
+        for i in range(n_pairs):
+            mem_state1 = mem_state[:, :, OFFSET + i].astype(np.double)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                mem_state1 = -3366 / np.log10(mem_state1) - 306
+            mem_state1 = np.clip(mem_state1, 0, 255).astype(np.uint8)
+            memimg1 = memimg2 = mem_state1.astype(np.uint8)          # optical_flow_seg.py:435
+            prev_frame, next_frame = cv2.imread(rgbimages[i]), cv2.imread(rgbimages[i + 1])
+            prev_gray = cv2.cvtColor(prev_frame, cv2.COLOR_RGB2GRAY)
+            next_gray = cv2.cvtColor(next_frame, cv2.COLOR_RGB2GRAY)
+            image = cv2.imread(f"{base}/gtmask/{imgs[i + 1]}")
+            gray_image = cv2.cvtColor(image, cv2.COLOR_BGR2GRAY)
+            _, binary_image = cv2.threshold(gray_image, 127, 256, cv2.THRESH_BINARY)
+            for k in ("mem_cal_times", "mem_velocity_times", "mem_opticalflow_times", "mem_task_times",
+                      "mem_combination_times"):
+                ns[k].clear()
+            flow, _, _, _, (x0, y0, x1, y1) = ns["opticalFlow3D"](memimg1, memimg2, prev_gray, next_gray, M, M)
+            flow = -flow
+            num_labels = 1 if (x0, y0, x1, y1) == (0, 0, 0, 0) else 2
+            motion_binary = ns["task_results"](prev_frame, next_frame, flow, num_labels, (x0, y0, x1, y1),
+                                               EST_FLAG=2, MERGE_FLAG=True)
+            # baseline block (optical_flow_seg.py:492-539): only what reaches motion_binary1
+            flow1 = -cv2.calcOpticalFlowFarneback(prev_gray, next_gray, None, **consts["farneback_params"])
+            mag, _ = cv2.cartToPolar(flow1[..., 0], flow1[..., 1])
+            mm = np.zeros(prev_frame.shape, np.uint8)
+            mm[mag > consts["SEG_TH"]] = 255
+            for _ in range(5):
+                mm = cv2.erode(cv2.dilate(mm, kernel), kernel)
+            _, motion_binary1 = cv2.threshold(cv2.cvtColor(mm, cv2.COLOR_BGR2GRAY), 1, 255, cv2.THRESH_BINARY)
+            rects[i] = (x0, y0, x1, y1)
+            acc1[i] = ns["calculate_pixel_accuracy"](motion_binary, binary_image)
+            acc2[i] = ns["calculate_pixel_accuracy"](motion_binary1, binary_image)
+            per_pair[i] = dict(memimg=memimg2, prev_gray=prev_gray, next_gray=next_gray, gt=binary_image,
+                               motion=motion_binary, motion1=motion_binary1, flow=-flow)
+            if ds == "grasp" and i >= 60:   # keep memory bounded: only the candidates below are used
+                per_pair[i] = None
+            print(ds, i, rects[i], f"{acc1[i]:.6f} {acc2[i]:.6f}", flush=True)
+        area = (rects[:, 2] - rects[:, 0]) * (rects[:, 3] - rects[:, 1])
+        if ds == "grasp":
+            keep = list(range(40, 52))                               # 12 consecutive pairs, 41.jpg .. 53.jpg
+        else:
+            keep = [i for i in range(n_pairs) if area[i] > 0]        # every pair with a non-empty ROI
+        full = keep[:n_full]
+        H, W = per_pair[keep[0]]["prev_gray"].shape
+        out = dict(frame_hw=np.array([H, W]), rects=rects, acc1=acc1, acc2=acc2, acc1_mean=acc1.mean(),
+                   acc2_mean=acc2.mean(), keep=np.array(keep), full=np.array(full), cv2_version=np.array(cv2.__version__))
+        # grey frames: frame t serves pair t-1 (as next) and pair t (as prev); stored once, cropped to the union of the
+        # rectangles that read it (outside them nothing reaches the ROI path)
+        boxes = {}
+        for i in keep:
+            for t in (i, i + 1):
+                b = boxes.get(t)
+                r = rects[i]
+                boxes[t] = tuple(r) if b is None else (min(b[0], r[0]), min(b[1], r[1]), max(b[2], r[2]), max(b[3], r[3]))
+        for t, (bx0, by0, bx1, by1) in boxes.items():
+            src = per_pair[t]["prev_gray"] if per_pair.get(t) else per_pair[t - 1]["next_gray"]
+            out[f"frame__{t}"] = np.ascontiguousarray(src[by0:by1, bx0:bx1])
+            out[f"fbox__{t}"] = np.array([bx0, by0, bx1, by1], np.int32)
+        for i in keep:
+            d = per_pair[i]
+            x0, y0, x1, y1 = (int(v) for v in rects[i])
+            fl = d["flow"][y0:y1, x0:x1].astype(np.float32)          # cv2's float32 crop flow (pasted into float64)
+            assert np.array_equal(fl.astype(np.float64), d["flow"][y0:y1, x0:x1])
+            out[f"memimg__{i}"] = d["memimg"]
+            out[f"flow8__{i}"] = np.ascontiguousarray(fl[::8, ::8])
+            out[f"flowsum__{i}"] = np.array([np.abs(fl.astype(np.float64)).sum(), float(np.abs(fl).max())])
+            out[f"motion__{i}"] = np.packbits(d["motion"] > 0, axis=1)
+            out[f"gt__{i}"] = np.packbits(d["gt"] > 0, axis=1)
+            assert set(np.unique(d["gt"])) <= {0, 255} and set(np.unique(d["motion"])) <= {0, 255}
+        for i in full:
+            d = per_pair[i]
+            out[f"fullprev__{i}"] = d["prev_gray"]
+            out[f"fullnext__{i}"] = d["next_gray"]
+            out[f"motion1__{i}"] = np.packbits(d["motion1"] > 0, axis=1)
+        path = os.path.join(OUT, f"realdata_{ds}.npz")
+        np.savez_compressed(path, **out)
+        print(f"realdata_{ds}.npz: {len(keep)} pairs kept, {len(full)} with full frames, {os.path.getsize(path) / 1e6:.1f} MB; "
+              f"our method average accuracy {acc1.mean()!r}, original {acc2.mean()!r}")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "realdata":
+        make_realdata(tuple(sys.argv[2:]) or ("grasp", "autodriving"))
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "farneback":
         make_farneback()
         make_farneback_initflow()
@@ -408,3 +554,4 @@ if __name__ == "__main__":
     make_events_scheme2()
     make_segment()
     make_frames()
+    make_realdata()

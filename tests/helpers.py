@@ -212,3 +212,49 @@ def check_frames_against_golden(fr, rgb2gray, remap_flow, predict_frame):
     x0, y0, x1, y1 = (int(v) for v in fr["pred__inner__rect"])
     got = remap_flow(np.ascontiguousarray(nf[:, :, 1]), flow[y0:y1, x0:x1].astype(np.float64), x0, y0)
     assert np.array_equal(got, fr["pred__inner__out"][y0:y1, x0:x1, 1])
+
+
+class RealData:
+    """tests/golden/realdata_<ds>.npz (make_golden.make_realdata): the scripts' main-loop body run with the reference's own
+    functions over the shipped data/grasp and data/autodriving sequences."""
+
+    def __init__(self, ds):
+        self.ds = ds
+        self.g = np.load(os.path.join(GOLDEN, f"realdata_{ds}.npz"))
+        self.H, self.W = (int(v) for v in self.g["frame_hw"])
+        self.keep = [int(i) for i in self.g["keep"]]
+        self.full = [int(i) for i in self.g["full"]]
+
+    def rect(self, i):
+        return tuple(int(v) for v in self.g["rects"][i])
+
+    def frame(self, t):
+        """Grey frame t: zero outside the stored box (nothing outside the pair's rectangle reaches the ROI path)."""
+        x0, y0, x1, y1 = (int(v) for v in self.g[f"fbox__{t}"])
+        f = np.zeros((self.H, self.W), np.uint8)
+        f[y0:y1, x0:x1] = self.g[f"frame__{t}"]
+        return f
+
+    def pair(self, i):
+        return self.frame(i), self.frame(i + 1)
+
+    def full_pair(self, i):
+        return self.g[f"fullprev__{i}"], self.g[f"fullnext__{i}"]
+
+    def unpack(self, key):
+        return np.unpackbits(self.g[key], axis=1)[:, :self.W].astype(bool)
+
+    def check_flow(self, i, crop_flow, what, mean_tol=1e-4, max_tol=1e-3):
+        """crop_flow: float32 (h, w, 2) of pair i's rectangle vs cv2's flow at every 8th pixel + the |flow| checksum."""
+        want = self.g[f"flow8__{i}"]
+        d = flow_err(crop_flow[::8, ::8], want)
+        assert d.mean() <= mean_tol and d.max() <= max_tol, f"{what} {self.ds} pair {i}: EPE mean {d.mean():.3e} max {d.max():.3e}"
+        s, m = self.g[f"flowsum__{i}"]
+        got = np.abs(crop_flow.astype(np.float64)).sum()
+        assert abs(got - s) <= mean_tol * 2 * crop_flow.shape[0] * crop_flow.shape[1], (what, i, got, s)
+        return d.mean(), d.max()
+
+
+def pixel_accuracy(a, b):
+    """calculate_pixel_accuracy (optical_flow_seg.py:384-388)."""
+    return np.sum(a == b) / a.size * 100

@@ -280,3 +280,20 @@ def test_emu_frames_vs_reference(emu_engine, golden):
     nf, flow = golden.frames["pred__next"], golden.frames["pred__flow"]
     assert np.array_equal(emu_engine.remap_flow(nf, -flow[20:60, 30:90], 30, 20, flow_sign=-1),
                           emu_engine.remap_flow(nf, flow[20:60, 30:90], 30, 20))
+
+
+def test_emu_realdata_pair_end_to_end(emu_engine, nsof):
+    """One real grasp pair (configs[0]) through the reference-shaped host seam on the emulator build:
+    opticalFlow3D -> -flow -> task_results -> pixel accuracy, against the reference's own outputs."""
+    rd = helpers.RealData("grasp")
+    cfg = nsof.RoiConfig.grasp()
+    i = rd.keep[1]
+    a, b = rd.pair(i)
+    memimg = rd.g[f"memimg__{i}"]
+    flow, _, _, _, info = emu_engine.opticalFlow3D(memimg, memimg, a, b, cfg.MEMSIZE, cfg.MEMSIZE, cfg)
+    assert info == rd.rect(i)
+    x0, y0, x1, y1 = info
+    rd.check_flow(i, flow[y0:y1, x0:x1].astype(np.float32), "emu vs cv2")
+    motion = emu_engine.task_results(a, b, -flow, 2, info)
+    assert np.array_equal(motion > 0, rd.unpack(f"motion__{i}"))
+    assert helpers.pixel_accuracy(motion > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]

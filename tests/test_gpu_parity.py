@@ -103,6 +103,114 @@ def test_full_frame_vs_oracle(gpu_engine, oracle, hw):
     assert abs(med[0] - 3.0) < 0.15 and abs(med[1] + 1.5) < 0.15, med
 
 
+@pytest.mark.parametrize("hw", [(1080, 1920), (1920, 1080), (801, 801)])
+def test_full_frame_vs_cv2(gpu_engine, hw):
+    """The same BASELINE.json sizes against cv2.calcOpticalFlowFarneback ITSELF (cv2 is on the GPU box; the C oracle
+    is only the stand-in when it is not): well-conditioned textured frames, mean EPE <= 1e-4 px, max <= 1e-3 px."""
+    cv2 = pytest.importorskip("cv2")
+    p = helpers.PARAM_SETS["grasp"]
+    a, b = helpers.textured_pair(21, *hw)
+    got = gpu_engine.calcOpticalFlowFarneback(a, b, None, **p)
+    want = cv2.calcOpticalFlowFarneback(a, b, None, **p)
+    helpers.assert_flow_close(got, want, "grasp", f"gpu vs cv2 {hw}")
+
+
+REALDATA_CFG = {"grasp": "grasp", "autodriving": "autodriving"}
+
+
+@pytest.mark.parametrize("ds", ["grasp", "autodriving"])
+def test_realdata_end_to_end(gpu_engine, nsof, ds):
+    """BASELINE configs[0] / configs[1] through the reference-shaped host seam, on the shipped sequences (12 consecutive
+    grasp pairs, all 23 autodriving pairs with a non-empty ROI; tests/golden/realdata_<ds>.npz holds what the reference's
+    own functions produced): Engine.opticalFlow3D -> `flow = -flow` -> task_results -> calculate_pixel_accuracy.
+    Rectangles equal; flow within mean 1e-4 / max 1e-3 px of cv2's at every 8th pixel (and of cv2 itself, live, at
+    every pixel when cv2 imports); motion masks bit for bit; accuracy to the last digit."""
+    try:
+        import cv2
+    except Exception:
+        cv2 = None
+    rd = helpers.RealData(ds)
+    cfg = getattr(nsof.RoiConfig, REALDATA_CFG[ds])()
+    acc = []
+    for i in rd.keep:
+        a, b = rd.pair(i)
+        memimg = rd.g[f"memimg__{i}"]
+        flow, _, _, region_list, info = gpu_engine.opticalFlow3D(memimg, memimg, a, b, cfg.MEMSIZE, cfg.MEMSIZE, cfg)
+        assert info == rd.rect(i), (ds, i)
+        x0, y0, x1, y1 = info
+        crop = flow[y0:y1, x0:x1].astype(np.float32)
+        rd.check_flow(i, crop, "gpu vs cv2 golden")
+        if cv2 is not None:
+            want = cv2.calcOpticalFlowFarneback(a[y0:y1, x0:x1], b[y0:y1, x0:x1], None, **cfg.farneback_params)
+            d = helpers.flow_err(crop, want)
+            assert d.mean() <= 1e-4 and d.max() <= 1e-3, (ds, i, d.mean(), d.max())
+        outside = np.ones((rd.H, rd.W), bool)
+        outside[y0:y1, x0:x1] = False
+        assert not flow[outside].any()
+        motion = gpu_engine.task_results(a, b, -flow, 2, info)   # optical_flow_seg.py:461, 479-487
+        assert np.array_equal(motion > 0, rd.unpack(f"motion__{i}")), (ds, i)
+        acc.append(helpers.pixel_accuracy(motion > 0, rd.unpack(f"gt__{i}")))
+        assert acc[-1] == rd.g["acc1"][i], (ds, i, acc[-1], rd.g["acc1"][i])
+    assert np.mean(acc) == np.mean(rd.g["acc1"][rd.keep])
+    # pairs the gate leaves closed (autodriving: 75 of 98): zero flow, (0, 0, 0, 0), accuracy of an all-zero mask
+    closed = [i for i in range(len(rd.g["rects"])) if not rd.g["rects"][i].any()][:1]
+    for i in closed:
+        blank = np.zeros((rd.H, rd.W), np.uint8)
+        cells = np.zeros(((rd.H // cfg.MEMSIZE), (rd.W // cfg.MEMSIZE)), np.uint8)
+        res = gpu_engine.opticalFlow3D(cells, cells, blank, blank, cfg.MEMSIZE, cfg.MEMSIZE, cfg)
+        assert not res[0].any() and res[4] == (0, 0, 0, 0)
+
+
+@pytest.mark.parametrize("ds", ["grasp", "autodriving"])
+def test_realdata_full_frame_baseline(gpu_engine, ds):
+    """The scripts' baseline block (optical_flow_seg.py:492-545) on whole real frames: full-frame Farneback ->
+    -flow -> threshold + 5 x (dilate, erode) -> motion_binary1 -> accuracy2, against the reference run."""
+    rd = helpers.RealData(ds)
+    for i in rd.full:
+        a, b = rd.full_pair(i)
+        flow1 = -gpu_engine.calcOpticalFlowFarneback(a, b, None, **helpers.PARAM_SETS["grasp"])
+        motion1 = gpu_engine.segment_flow(flow1)
+        assert np.array_equal(motion1 > 0, rd.unpack(f"motion1__{i}")), (ds, i)
+        assert helpers.pixel_accuracy(motion1 > 0, rd.unpack(f"gt__{i}")) == rd.g["acc2"][i]
+
+
+@pytest.mark.parametrize("roi_state", ["scripts", "notebook"])
+def test_realdata_sequence_from_mat(gpu_engine, nsof, golden, roi_state):
+    """configs[0] as the scripts run it -- array states read from constructed_3D_matrix.mat, not simulated -- through the
+    device-resident SequencePipeline (stage1="given", segment=True) over the 12 consecutive grasp pairs: rectangles,
+    flow and motion masks of every pair against the reference run ("scripts": slice OFFSET + i, the shipped form;
+    "notebook": slice OFFSET + i + 1, checked against the numpy restatement's rectangles)."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    rd = helpers.RealData("grasp")
+    i0, n = rd.keep[0], len(rd.keep)
+    assert rd.keep == list(range(i0, i0 + n))
+    frames = np.stack([rd.frame(t) for t in range(i0, i0 + n + 1)])[:, None]           # [F][1][H][W]
+    cur = golden.roi["grasp__currents"][i0:i0 + n + 1][:, None]                         # slice t -> frame i0 + t
+    pipe = pm.SequencePipeline(gpu_engine, 1, n + 1, rd.H, rd.W, nsof.RoiConfig.grasp(), stage1="given", segment=True,
+                               roi_state=roi_state, overlap=False, chunks=[(0, n)])
+    pipe.currents.copy_(torch.from_numpy(np.ascontiguousarray(cur)))
+    d_frames = torch.from_numpy(frames).cuda().contiguous()
+    pipe.step(d_frames)
+    torch.cuda.synchronize()
+    rects, n_rects = pipe.last_rects
+    flow, motion = pipe.flow.cpu().numpy(), pipe.motion.cpu().numpy()
+    shift = 0 if roi_state == "scripts" else 1
+    memimg = s1.current_to_u8(golden.roi["grasp__currents"])
+    for k in range(n):
+        _, _, _, want = s1.roi_from_memimg(memimg[i0 + k + shift], (rd.H, rd.W), 80, 80, 250, (20, 20, 20, 20), 2)
+        assert n_rects[k] == len(want) and tuple(int(v) for v in rects[k]) == want[0]
+        if roi_state == "scripts":
+            i = i0 + k
+            assert want[0] == rd.rect(i)
+            x0, y0, x1, y1 = want[0]
+            rd.check_flow(i, flow[k, 0, y0:y1, x0:x1], "pipeline vs cv2 golden")
+            assert np.array_equal(motion[k, 0] > 0, rd.unpack(f"motion__{i}")), i
+            assert helpers.pixel_accuracy(motion[k, 0] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
+
+
 def test_full_size_properties(gpu_engine):
     """Size-independent properties at 1080p: a constant frame pair -> exactly zero flow (identical TEXTURED frames do
     not: OpenCV's UpdateMatrices takes r2 = R0/2 on the last row/column, cv2 itself returns up to 0.09 px there);
@@ -297,9 +405,12 @@ def _small_clips(n, F=6, H=400, W=560):
     return [syn.make_clip(100 + c, H, W, F, "cpu", velocity=(4.0, -2.0)) for c in range(n)]
 
 
-def test_sequence_pipeline_vs_cpu_reference(gpu_engine, nsof, oracle):
+@pytest.mark.parametrize("roi_state", ["scripts", "notebook"])
+def test_sequence_pipeline_vs_cpu_reference(gpu_engine, nsof, oracle, roi_state):
     """Stage 1 + ROI + batched Farneback over whole clips (device-resident step) against the reference CPU path
-    (numpy stage 1 + cv2/oracle Farneback on the crop): rectangles identical, flow within tolerance, zero outside."""
+    (numpy stage 1 + cv2/oracle Farneback on the crop): rectangles identical, flow within tolerance, zero outside.
+    Both gating forms of SURVEY.md 3.5: "scripts" (pair t gated by the state before it; pair 0 by the initial state =
+    the whole cell grid) and "notebook" (the state after it)."""
     import importlib
 
     import torch
@@ -308,13 +419,15 @@ def test_sequence_pipeline_vs_cpu_reference(gpu_engine, nsof, oracle):
     clips = _small_clips(2)
     F, H, W = clips[0].shape
     frames = torch.stack(clips, dim=1).cuda().contiguous()  # [F][C][H][W]
-    pipe = pm.SequencePipeline(gpu_engine, 2, F, H, W)
+    pipe = pm.SequencePipeline(gpu_engine, 2, F, H, W, roi_state=roi_state)
     n = pipe.step(frames)
     torch.cuda.synchronize()
     flow = pipe.flow.cpu().numpy()
     n_ref = 0
     for c in range(2):
-        _, _, rects, flows = ref.process_clip(clips[c].numpy(), keep_flow=True)
+        _, _, rects, flows = ref.process_clip(clips[c].numpy(), keep_flow=True, roi_state=roi_state)
+        if roi_state == "scripts":
+            assert rects[0] == (0, 0, W, H)  # 400 x 560 at MEMSIZE 80: 5 x 7 cells + EXT 20 cover the frame
         for t in range(F - 1):
             got_rect = tuple(int(v) for v in pipe.last_rects[0][t * 2 + c]) if pipe.last_rects[1][t * 2 + c] else None
             assert got_rect == rects[t], (c, t, got_rect, rects[t])

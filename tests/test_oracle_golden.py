@@ -147,3 +147,44 @@ def test_frames_oracle_matches_reference(golden):
         return fo.task_results(prev, nxt, flow, r)
 
     helpers.check_frames_against_golden(golden.frames, fo.rgb2gray, fo.remap_flow, predict)
+
+
+REALDATA_CFG = {"grasp": dict(MEMSIZE=80, OFFSET=0, THRES=250, ext=(20, 20, 20, 20)),
+                "autodriving": dict(MEMSIZE=200, OFFSET=15, THRES=114, ext=(60, 60, 60, 60))}
+
+
+@pytest.mark.parametrize("ds", ["grasp", "autodriving"])
+def test_realdata_oracle_end_to_end(oracle, golden, ds):
+    """BASELINE configs[0] / configs[1]: the oracle chain (ROI tail -> C Farneback on the crop -> -flow -> motion mask ->
+    pixel accuracy) against what the reference's own functions produced on the shipped sequences
+    (tests/golden/realdata_<ds>.npz).  Rectangles of EVERY pair of the sequence (slice OFFSET + i: the scripts'
+    `mem_state2 = mem_state1` form); flow, mask and accuracy on the kept pairs -- masks bit for bit, accuracy to the
+    last digit."""
+    from oracle import seg_oracle as so
+    rd = helpers.RealData(ds)
+    c = REALDATA_CFG[ds]
+    M = c["MEMSIZE"]
+    memimg_all = s1.current_to_u8(golden.roi[f"{ds}__currents"])
+    rects_all = rd.g["rects"]
+    for i in range(len(rects_all)):
+        _, _, _, r = s1.roi_from_memimg(memimg_all[c["OFFSET"] + i], (rd.H, rd.W), M, M, c["THRES"], c["ext"], 2)
+        assert (r[0] if r else (0, 0, 0, 0)) == tuple(int(v) for v in rects_all[i]), (ds, i)
+    worst = 0.0
+    for i in rd.keep[::2]:   # every other kept pair keeps the CPU suite short; the GPU tests run all of them
+        assert np.array_equal(memimg_all[c["OFFSET"] + i], rd.g[f"memimg__{i}"])
+        a, b = rd.pair(i)
+        x0, y0, x1, y1 = rd.rect(i)
+        f = oracle.farneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(b[y0:y1, x0:x1]),
+                             **helpers.PARAM_SETS["grasp"])
+        _, mx = rd.check_flow(i, f, "oracle vs cv2")
+        worst = max(worst, mx)
+        flow = np.zeros((rd.H, rd.W, 2))
+        flow[y0:y1, x0:x1] = f
+        mb = so.task_results((rd.H, rd.W), -flow, (x0, y0, x1, y1)) > 0
+        assert np.array_equal(mb, rd.unpack(f"motion__{i}")), (ds, i)
+        assert helpers.pixel_accuracy(mb, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i], (ds, i)
+    assert worst <= 1e-3
+    # the dataset averages the scripts print (optical_flow_seg.py:619-620; BASELINE.md section 2 for grasp)
+    if ds == "grasp":
+        assert abs(float(rd.g["acc1_mean"]) - 99.02812363605189) < 1e-9
+        assert abs(float(rd.g["acc2_mean"]) - 98.71762912691729) < 1e-9
