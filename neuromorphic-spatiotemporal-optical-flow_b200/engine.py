@@ -651,15 +651,22 @@ class Engine:
         self.lib.check(rc, "lanczos3_compress")
         return out.cpu().numpy()
 
+    def _w_init(self, w0, Hc, Wc, p, device):
+        import torch
+        if w0 is None:
+            return torch.full((Hc, Wc), float(p["wini"]), dtype=torch.float64, device=device)
+        w0 = np.ascontiguousarray(np.broadcast_to(np.asarray(w0, dtype=np.float64), (Hc, Wc)))
+        return self._dev_roundtrip([w0])[0]
+
     def simulate_memristor_array_stepwise(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS,
-                                          vds=1.0):
+                                          vds=1.0, w0=None):
         """Same as simulate_memristor_array through the per-pair entry point nsof_frame_sim_step_f64 (streaming use:
-        one call per arriving frame)."""
+        one call per arriving frame).  `w0`: initial state per cell instead of wini (resuming a sequence)."""
         import torch
         cells = np.ascontiguousarray(compressed_images, dtype=np.float64)
         T, Hc, Wc = cells.shape
         (d,) = self._dev_roundtrip([cells])
-        w = torch.full((Hc, Wc), float(p["wini"]), dtype=torch.float64, device=d.device)
+        w = self._w_init(w0, Hc, Wc, p, d.device)
         cur = torch.empty((T, Hc, Wc), dtype=torch.float64, device=d.device)
         sp = _synapse_params(p)
         lam = np.log(p["Roff"] / p["Ron"])
@@ -672,14 +679,16 @@ class Engine:
             self.lib.check(rc, "frame_sim_step")
         return w.cpu().numpy(), cur.cpu().numpy()
 
-    def simulate_memristor_array(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS, vds=1.0):
+    def simulate_memristor_array(self, compressed_images, dt=5e-4, nSubSteps=1000, th1=2.0, th2=1.5, p=PARAMS, vds=1.0,
+                                 w0=None):
         """simulate_memristor_array (vehicle.m:187-227): returns (w_array, currents (T, Hc, Wc) with slice 0 the
-        initial state -- the layout of constructed3DMatrix = vds / resistances_over_time)."""
+        initial state -- the layout of constructed3DMatrix = vds / resistances_over_time).  `w0`: initial state per
+        cell instead of wini."""
         import torch
         cells = np.ascontiguousarray(compressed_images, dtype=np.float64)
         T, Hc, Wc = cells.shape
         (d,) = self._dev_roundtrip([cells])
-        w = torch.full((Hc, Wc), float(p["wini"]), dtype=torch.float64, device=d.device)
+        w = self._w_init(w0, Hc, Wc, p, d.device)
         cur = torch.empty((T, Hc, Wc), dtype=torch.float64, device=d.device)
         sp = _synapse_params(p)
         lam = np.log(p["Roff"] / p["Ron"])

@@ -258,3 +258,62 @@ class RealData:
 def pixel_accuracy(a, b):
     """calculate_pixel_accuracy (optical_flow_seg.py:384-388)."""
     return np.sum(a == b) / a.size * 100
+
+
+def external_image(H, W, seed=20261105):
+    """Seeded uint8 test image of tests/golden/make_stage1_external.py (noise with a vertical brightness ramp, so that
+    the cells of a Lanczos reduction differ by far more than the comparison tolerance)."""
+    rng = np.random.default_rng(seed + H * 10000 + W)
+    img = rng.integers(0, 256, (H, W), dtype=np.uint8)
+    return (0.5 * img + 0.5 * np.roll(img, 37, 1) * (np.arange(H)[:, None] / H)).astype(np.uint8)
+
+
+class Stage1External:
+    """tests/golden/stage1_external.npz (make_stage1_external.py): frame-mode fixtures from an independent 50-digit
+    derivation -- Lanczos-3 contribution matrices, Pillow's resize as a loose cross-check, exact-arithmetic Euler
+    trajectories of update_state."""
+
+    def __init__(self):
+        self.g = np.load(os.path.join(GOLDEN, "stage1_external.npz"))
+
+    def check_compress(self, compress, what, tol=1e-13):
+        """compress(img uint8 (H, W), m, n) -> cells; vs  W_y (img / 255) W_x^T  with the external matrices."""
+        for H, W, M in [(1080, 1920, 80), (801, 801, 200)]:
+            img = external_image(H, W)
+            assert int(img.astype(np.int64).sum()) == int(self.g[f"pillow__{H}x{W}__imgsum"])
+            want = self.g[f"lanczos__{H}_{H // M}"] @ (img / 255.0) @ self.g[f"lanczos__{W}_{W // M}"].T
+            got = compress(img, M, M)
+            assert got.shape == want.shape and np.abs(got - want).max() <= tol, (what, H, W, np.abs(got - want).max())
+            if H == 1080:  # cells whose 6-cell support stays inside the image: Pillow's edge rule does not matter
+                pil = self.g[f"pillow__{H}x{W}__cells"]
+                assert np.abs(got - pil)[3:-3, 3:-3].max() <= 1e-6, what
+        for n_in, n_out, m in [(161, 4, 40), (160, 4, 40), (600, 15, 40)]:   # uav / tabletennis / uavnew2 geometry
+            img = external_image(n_in, n_in)
+            Wm = self.g[f"lanczos__{n_in}_{n_out}"]
+            got = compress(img, m, m)
+            assert np.abs(got - Wm @ (img / 255.0) @ Wm.T).max() <= tol, (what, n_in)
+
+    def euler_groups(self):
+        """-> [(th1, th2, w0 (n,), delta (n,), want (n, 3))] -- one simulator call per threshold pair."""
+        pts, W = self.g["euler__points"], self.g["euler__w"]
+        out = []
+        for th in sorted({(a, b) for _, _, a, b in pts}):
+            sel = [i for i, q in enumerate(pts) if (q[2], q[3]) == th]
+            out.append((th[0], th[1], pts[sel, 0], pts[sel, 1], W[sel]))
+        return out
+
+    def check_euler(self, simulate, what, tol):
+        """simulate(cells (4, 1, n), w0 (1, n), th1, th2) -> currents or (w, currents); the state after each of the 3
+        frames is recovered from the current (vds / R(w)) and compared with the 50-digit Euler recurrence."""
+        lam = np.log(2104377 / 163305)
+        worst = 0.0
+        for th1, th2, w0, d, want in self.euler_groups():
+            cells = np.zeros((4, 1, len(d)))
+            cells[1::2, 0, :] = d / 256.0           # |256 a - 256 b| = d for every consecutive pair
+            w_fin, cur = simulate(cells, w0[None, :], th1, th2)
+            w_of = 1.0 + np.log(cur[1:, 0, :] * 163305.0) / lam       # invert I = exp(-lam (1 - w)) / Ron
+            err = max(np.abs(w_fin[0] - want[:, 2]).max(), np.abs(w_of.T - want).max())
+            worst = max(worst, err)
+            assert np.array_equal(w_fin[0] == 0, want[:, 2] == 0) and np.array_equal(w_fin[0] == 1, want[:, 2] == 1), what
+        assert worst <= tol, (what, worst)
+        return worst

@@ -297,3 +297,14 @@ def test_emu_realdata_pair_end_to_end(emu_engine, nsof):
     motion = emu_engine.task_results(a, b, -flow, 2, info)
     assert np.array_equal(motion > 0, rd.unpack(f"motion__{i}"))
     assert helpers.pixel_accuracy(motion > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
+
+
+def test_emu_frame_mode_vs_external_fixtures(emu_engine):
+    """The stage-1 frame-mode kernels (dense Lanczos matrices; Euler chain with the binomial-series carry between exact
+    re-evaluations) against the independent 50-digit fixtures of tests/golden/make_stage1_external.py."""
+    ext = helpers.Stage1External()
+    ext.check_compress(lambda img, m, n: emu_engine.compress_images(img, m, n)[0], "emu kernels")
+    sim = lambda cells, w0, th1, th2: emu_engine.simulate_memristor_array(cells, th1=th1, th2=th2, w0=w0)
+    ext.check_euler(sim, "emu kernels (run)", tol=1e-10)
+    sim2 = lambda cells, w0, th1, th2: emu_engine.simulate_memristor_array_stepwise(cells, th1=th1, th2=th2, w0=w0)
+    ext.check_euler(sim2, "emu kernels (stepwise)", tol=1e-10)

@@ -398,6 +398,45 @@ def test_frame_mode_1080p_mask_bit_exact(gpu_engine, nsof):
     assert np.array_equal(r["memimg"], s1.current_to_u8(cur_o))
 
 
+def test_frame_mode_vs_external_fixtures(gpu_engine):
+    """Frame mode is parity-unpinned against the reference (no MATLAB): the kernels are held to the independent
+    50-digit fixtures instead (tests/golden/make_stage1_external.py) -- Lanczos cells <= 1e-13 of W_y img W_x^T with
+    the externally derived matrices (all config ratios), Pillow on interior cells, and the Euler chain (binomial-
+    series carry, exact re-evaluation every 64 sub-steps) <= 1e-10 of the exact-arithmetic recurrence for 64
+    (w0, delta) points incl. the dead zone and both clips, through both entry points."""
+    ext = helpers.Stage1External()
+    ext.check_compress(lambda img, m, n: gpu_engine.compress_images(img, m, n)[0], "gpu kernels")
+    ext.check_euler(lambda c, w0, a, b: gpu_engine.simulate_memristor_array(c, th1=a, th2=b, w0=w0), "gpu run", 1e-10)
+    ext.check_euler(lambda c, w0, a, b: gpu_engine.simulate_memristor_array_stepwise(c, th1=a, th2=b, w0=w0),
+                    "gpu stepwise", 1e-10)
+
+
+def test_bench_clips_gate_bit_exact_1080p(gpu_engine, nsof):
+    """The gate of the bench workload itself: two of bench.py's clips (seeds 1234, 1235; 1080p, 8 frames) through the
+    device pipeline's stage 1 vs the numpy restatement -- uint8 maps and rectangles identical, both gating forms."""
+    import importlib
+
+    import torch
+    from oracle import cpu_reference as ref
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    clips = [syn.make_clip(1234 + c, 1080, 1920, 8, "cpu") for c in range(2)]
+    frames = torch.stack(clips, dim=1).cuda().contiguous()
+    for roi_state in ("scripts", "notebook"):
+        pipe = pm.SequencePipeline(gpu_engine, 2, 8, 1080, 1920, roi_state=roi_state, overlap=False, chunks=[(0, 7)])
+        pipe.stage1(frames)
+        torch.cuda.synchronize()
+        memimg = pipe.memimg.cpu().numpy().reshape(7, 2, 13, 24)
+        rects, n_rects = pipe.rects_host.numpy().reshape(7, 2, 4), pipe.n_rects_host.numpy().reshape(7, 2)
+        for c in range(2):
+            want_mem, want_rects = ref.clip_rects(clips[c].numpy(), roi_state=roi_state)
+            assert np.array_equal(memimg[:, c], want_mem), (roi_state, c)
+            for t in range(7):
+                got = tuple(int(v) for v in rects[t, c]) if n_rects[t, c] else None
+                assert got == want_rects[t], (roi_state, c, t)
+        del pipe
+
+
 # ------------------------------------------------------------------------------------------- whole clips
 def _small_clips(n, F=6, H=400, W=560):
     import importlib
