@@ -33,22 +33,32 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="nsof", choices=["nsof", "reference"])
     ap.add_argument("--clips", type=int, default=8, help="clips per GPU")
-    ap.add_argument("--frames", type=int, default=16, help="frames per clip")
+    ap.add_argument("--frames", type=int, default=32, help="frames per clip")
+    ap.add_argument("--roi-state", default="scripts", choices=["scripts", "notebook"],
+                    help="which array state gates a pair (SURVEY.md 3.5): before it, as the scripts do, or after it")
+    ap.add_argument("--min-seconds", type=float, default=1.0,
+                    help="repeat the timed block of exactly --steps steps until the device-resident leg has run this long")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the full-frame and per-kernel legs")
     return ap.parse_args()
 
 
 def workload_config(args, n_gpus):
-    return {"workload": "configs[3]: synthetic 1920x1080 clips, sequence-parallel (no collective)",
+    """Identical in both arms (`--impl nsof` and `--impl reference`): it names the workload, not how an arm runs it."""
+    return {"workload": "configs[3]: synthetic 1920x1080 clips of 32 frames, sequence-parallel (no collective); 64 clips "
+                        "over 8 GPUs = 8 clips per GPU, weak-scaled (per-GPU work fixed: 8 clips at every N)",
             "frame": [H, W], "clips_per_gpu": args.clips, "frames_per_clip": args.frames,
             "pairs_per_step_per_gpu": args.clips * (args.frames - 1), "clips_total": args.clips * n_gpus,
-            "roi": "synapse-array gate (MEMSIZE 80, THRES 250, EXT 20, FLAG 2)",
-            "farneback": [0.5, 3, 15, 3, 5, 1.2, 0], "stage1": "frame mode, nSubSteps 1000",
+            "roi": "synapse-array gate (MEMSIZE 80, THRES 250, EXT 20, FLAG 2)", "roi_state": args.roi_state,
+            "farneback": [0.5, 3, 15, 3, 5, 1.2, 0],
+            "stage1": "frame mode, nSubSteps 1000 (parity unpinned: no MATLAB; held to independent 50-digit fixtures)",
             "l2": "inputs exceed L2 (frames + flow frames per step >> 126 MB)",
-            "schedule": "DeviceStream (pipeline.py): one Farneback batch of all pairs per step on the caller's stream; stage 1 "
-                        "of step k+1 on a high-priority side stream beside it; all K steps submitted and drained "
-                        "inside the timed region"}
+            "parallelism": f"sequence-parallel x{n_gpus}"}
+
+
+GPU_SCHEDULE = ("DeviceStream (pipeline.py): one Farneback batch of all pairs per step on the caller's stream; stage 1 of "
+                "step k+1 on a high-priority side stream beside it; every timed block = exactly K steps submitted and "
+                "drained between two events")
 
 
 # ------------------------------------------------------------------------------------------- clocks
@@ -112,53 +122,62 @@ def host_clips(n_clips, frames, seed0=1234):
     return [syn.make_clip(seed0 + c, H, W, frames, "cpu").numpy() for c in range(n_clips)]
 
 
-def cpu_baseline_leg(clip_np):
-    """Bounded sample on rank 0: the reference CPU path on all host cores (one process per core, one clip per task --
-    OpenCV's Farneback core is single-threaded), plus the same path in ONE process for the per-core figure."""
-    from oracle import cpu_reference as ref
+def _host_workers():
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    workers = max(1, cores)
-    clips = host_clips(min(workers, 16), 5)
+    return max(1, cores)
+
+
+def _ref_what(ref):
+    return f"numpy stage 1 + {'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback on the ROI crop"
+
+
+def cpu_baseline_leg(args, clip_np):
+    """Bounded sample on rank 0: the reference CPU path on all host cores (one persistent process per core, one clip of
+    the workload's own length per task -- OpenCV's Farneback core is single-threaded), plus the same path in ONE
+    process for the per-core figure."""
+    from oracle import cpu_reference as ref
+    workers = _host_workers()
+    clips = host_clips(min(workers, 16), args.frames)
     clips = [clips[i % len(clips)] for i in range(workers)]
-    ref.process_clips_parallel(clips, workers)  # warm-up (pool start, page-in)
-    t0, pairs = time.perf_counter(), 0
-    for _ in range(3):
-        n, _ = ref.process_clips_parallel(clips, workers)
-        pairs += n
-    dt_all = time.perf_counter() - t0
-    ref.process_clip(clip_np[:3])
-    n1, dt1, _, _ = ref.process_clip(clip_np)
-    nf, dtf, _, _ = ref.process_clip(clip_np[:3], full_frame=True)
-    what = f"numpy stage 1 + {'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback on the ROI crop"
+    pool = ref.ClipPool(clips, workers, args.roi_state)  # created (and warmed) before the timed pass
+    pool.run()
+    pairs, dt_all = pool.run()
+    pool.close()
+    short = clip_np[:min(len(clip_np), 6)]
+    ref.process_clip(short[:3], roi_state=args.roi_state)
+    n1, dt1, _, _ = ref.process_clip(short, roi_state=args.roi_state)
+    nf, dtf, _, _ = ref.process_clip(short[:3], full_frame=True)
     return {"value": pairs / dt_all, "unit": UNIT, "cores": workers, "kind": ref.KIND,
-            "sample": f"3 x ({workers} clips x 5 frames = {workers * 4} pairs) of the same synthetic 1080p workload, one process "
-                      f"per host core, {what}",
-            "single_process_value": n1 / dt1, "single_process_full_frame_value": nf / dtf}
+            "sample": f"one pass over {workers} clips x {args.frames} frames = {pairs} pairs of the same synthetic 1080p "
+                      f"workload (roi_state {args.roi_state}), one persistent process per host core, {_ref_what(ref)}",
+            "single_process_value": n1 / dt1, "single_process_sample": f"{n1} pairs (first {len(short)} frames of clip 0)",
+            "single_process_full_frame_value": nf / dtf}
 
 
 def reference_arm(args):
-    """--impl reference: the reference CPU path on all host cores (one process per core, one clip per task)."""
+    """--impl reference: the reference CPU path on all host cores, on the GPU arm's config.  One step = one pass over
+    one clip (of the workload's own `--frames`) per host core; the process pool is persistent and created before the
+    timed loop."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     from oracle import cpu_reference as ref
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    workers = max(1, cores)
-    ref_frames = 5  # 4 pairs per clip and task: bounded sample
-    clips = host_clips(min(workers, 16), ref_frames)
+    workers = _host_workers()
+    clips = host_clips(min(workers, 16), args.frames)
     clips = [clips[i % len(clips)] for i in range(workers)]
+    pool = ref.ClipPool(clips, workers, args.roi_state)
     for _ in range(max(1, min(args.warmup, 1))):
-        ref.process_clips_parallel(clips, workers)
+        pool.run()
     t0 = time.perf_counter()
     pairs = 0
     for _ in range(args.steps):
-        n, _ = ref.process_clips_parallel(clips, workers)
+        n, _ = pool.run()
         pairs += n
     dt = time.perf_counter() - t0
+    pool.close()
     val = pairs / dt
-    sample = (f"each step = {workers} clips x {ref_frames} frames ({workers * (ref_frames - 1)} pairs) of the same "
-              f"synthetic 1080p workload, one process per host core, numpy stage 1 + "
-              f"{'cv2 ' + ref.cv2.__version__ if ref.cv2 is not None else 'C oracle'} Farneback on the ROI crop")
+    sample = (f"each step = {workers} clips x {args.frames} frames ({workers * (args.frames - 1)} pairs) of the same "
+              f"synthetic 1080p workload (roi_state {args.roi_state}), one persistent process per host core, {_ref_what(ref)}")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -168,6 +187,27 @@ def reference_arm(args):
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+def parity_check(args, clip_u8, rects, n_rects, flow_of_pair, n_pairs=8):
+    """Outside every timed region: the first `n_pairs` pairs of clip 0 of the timed workload through the reference CPU
+    path (stage 1 is a recurrence from frame 0, so a prefix of the clip reproduces the prefix of the rectangles) against
+    what the timed GPU step left in HBM."""
+    import numpy as np
+    from oracle import cpu_reference as ref
+    F = min(len(clip_u8), n_pairs + 1)
+    _, _, want_rects, flows = ref.process_clip(clip_u8[:F], keep_flow=True, roi_state=args.roi_state)
+    ok, epe_sum, epe_max, px = True, 0.0, 0.0, 0
+    for t in range(F - 1):
+        got = tuple(int(v) for v in rects[t]) if n_rects[t] else None
+        ok = ok and (got == want_rects[t])
+        if got is None or got != want_rects[t]:
+            continue
+        x0, y0, x1, y1 = got
+        d = np.sqrt(((flow_of_pair(t)[y0:y1, x0:x1].astype(np.float64) - flows[t][y0:y1, x0:x1]) ** 2).sum(-1))
+        epe_sum, epe_max, px = epe_sum + d.sum(), max(epe_max, float(d.max())), px + d.size
+    return {"pairs": F - 1, "rects_equal": bool(ok), "epe_mean": epe_sum / max(px, 1), "epe_max": epe_max,
+            "against": _ref_what(ref), "bar": "BASELINE.json: EPE <= 0.01 px, masks bit-exact"}
 
 
 # ------------------------------------------------------------------------------------------- GPU arm
@@ -183,7 +223,9 @@ def gpu_arm(args):
         raise SystemExit("bench.py: no CUDA device; libnsof has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
-    os.environ["NCCL_DEBUG"] = os.environ.get("NSOF_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
+    # stdout carries the one JSON line: NCCL's log (whatever level the environment asks for) goes to stderr
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     par.init("nccl", dev)  # plumbing only: barrier + max-over-ranks of the time; clips shard with no collective
 
     nsof = importlib.import_module("nsof_b200")
@@ -191,7 +233,7 @@ def gpu_arm(args):
     pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
     eng = nsof.Engine(local)
     Cn, F = args.clips, args.frames
-    pipe = pipe_mod.DeviceStream(eng, Cn, F, H, W, depth=2)
+    pipe = pipe_mod.DeviceStream(eng, Cn, F, H, W, depth=2, roi_state=args.roi_state)
 
     # synthetic clips, generated on the device, layout [F][C][H][W]
     frames = torch.empty((F, Cn, H, W), dtype=torch.uint8, device=dev)
@@ -233,24 +275,41 @@ def gpu_arm(args):
         pipe.drain()
 
     run_steps(args.warmup)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = pipe.launch_count()
-    e0.record()                # stage 1 of the first step is ordered behind this event (side stream waits for it)
-    run_steps(args.steps)      # exactly K steps, every Farneback batch on this stream
-    e1.record()
-    barrier()
-    launches = pipe.launch_count() - l0
-    ms_t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
-    ms = float(ms_t.item())
+    # the timed block is EXACTLY K steps between two events; it is repeated back to back (each block its own barrier +
+    # synchronize on both sides) until the leg has run --min-seconds, so the clock record has samples under load.
+    # value = pairs of all blocks / summed max-over-ranks block times; ms_per_step = that time / (blocks x K).
+    block_ms, launches = [], 0
+    while True:
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = pipe.launch_count()
+        e0.record()                # stage 1 of the first step is ordered behind this event (side stream waits for it)
+        run_steps(args.steps)      # exactly K steps, every Farneback batch on this stream
+        e1.record()
+        barrier()
+        if not block_ms:
+            launches = pipe.launch_count() - l0
+        ms_t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+        block_ms.append(float(ms_t.item()))
+        if sum(block_ms) >= args.min_seconds * 1e3 or len(block_ms) >= 200:   # every rank sees the same reduced times
+            break
+    ms = sum(block_ms) / len(block_ms)     # mean K-step block
     value = pairs_step * world * args.steps / (ms * 1e-3)
     roi_frac = pipe.slots[0].last_crop_pixels / (pairs_step * H * W)
     crop_px_step = pipe.slots[0].last_crop_pixels
 
     # ---- e2e: pinned host clips in, rectangles + packed ROI flow crops out, copies inside the timed region
-    hp = pipe_mod.HostStream(local, Cn, F, H, W, depth=3)
+    # parity of what was just timed, outside the timed region (rank 0): first pairs of clip 0 vs the reference CPU path
+    parity = None
+    if rank == 0:
+        sl = pipe.slots[(pipe.k - 1) % len(pipe.slots)]
+        torch.cuda.synchronize()
+        r_all, n_all = sl.last_rects
+        parity = parity_check(args, frames[:, 0].cpu().numpy(), r_all.reshape(F - 1, Cn, 4)[:, 0],
+                              n_all.reshape(F - 1, Cn)[:, 0], lambda t: sl.flow[t, 0].cpu().numpy())
+    hp = pipe_mod.HostStream(local, Cn, F, H, W, depth=3, roi_state=args.roi_state)
     clips_host = [torch.empty((F, H, W), dtype=torch.uint8).pin_memory() for _ in range(Cn)]
     for c in range(Cn):
         clips_host[c].copy_(frames[:, c])
@@ -342,7 +401,8 @@ def finish(args, L):
 
     # per-kernel leg on a serialised copy of the step (stage 1 on the same stream: no overlap between the event pairs)
     pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
-    pipe_ser = pipe_mod.SequencePipeline(eng, Cn, F, H, W, overlap=False, chunks=[(0, F - 1)])  # one batch per step, as timed
+    pipe_ser = pipe_mod.SequencePipeline(eng, Cn, F, H, W, overlap=False, chunks=[(0, F - 1)],
+                                         roi_state=args.roi_state)  # one batch per step, as timed
     pipe_ser.step(frames)
     kernels, stats = kernel_tables(lambda: pipe_ser.step(frames))
     del pipe_ser
@@ -390,10 +450,11 @@ def finish(args, L):
             "warmup": args.warmup, "ms_per_step": L["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
             "clocks": L["clocks"], "e2e": L["e2e"], "gpu_launches": int(L["launches"]), "roofline": roofline,
+            "timed_blocks": len(L["block_ms"]), "block_ms_min_max": [min(L["block_ms"]), max(L["block_ms"])],
+            "schedule": GPU_SCHEDULE, "parity_check": L["parity"],
             "roi_fraction_of_frame": L["roi_frac"], "kernels": kernels, **extras}
-    line["config"]["parallelism"] = f"sequence-parallel x{world}"
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline_leg(frames[:, 0].cpu().numpy())
+        line["cpu_baseline"] = cpu_baseline_leg(args, frames[:, 0].cpu().numpy())
     print(json.dumps(line), flush=True)
     return 0
 

@@ -427,9 +427,11 @@ extern "C" int nsof_reserve(nsof_handle *h, size_t total_crop_pixels, int max_it
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "nsof_reserve: NULL handle");
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    // per padded level-0 pixel: I 2 + R 10 on every level (x 4/3 for pyr_scale 0.5; x 2 bounds any scale <= 0.7),
-    // Ma 5, Mb 5, coarse flow 2 x 2 / 4; padding <= 31 px per row
-    const size_t floats = (total_crop_pixels + (size_t)max_items * 32 * 8192) * 36;
+    // what fb_prepare's plan asks for, per level-0 pixel: (I 2 + R 10) on every level (x 4/3 for pyr_scale 0.5),
+    // Ma 5 + Mb 5, coarse flow 2 x 2 / 4  ->  27 floats (28 with slack); rows are padded to 32 floats: <= 31 floats on
+    // each of ~4/3 h rows per item (budgeted for crops up to ~1150 rows).  A hint only: fb_prepare sizes every batch
+    // exactly and grows the arena when a batch needs more (other pyr_scale, taller crops).
+    const size_t floats = total_crop_pixels * 28 + (size_t)max_items * 31 * 1536 * 28;
     int rc = h->arena.ensure(floats * sizeof(float));
     if (rc) return rc;
     return h->tables.ensure((size_t)max_items * 8 * sizeof(FbJob) + 65536);

@@ -77,6 +77,7 @@ struct nsof_handle {
     int lz_key[4] = {0, 0, 0, 0};
     int lz_P[2] = {0, 0};  // seg_rows, n_seg of the cached Lanczos geometry
     bool lz_smem_set = false;
+    bool roi_smem_set = false;  // k_s1_roi opted into > 48 KB of dynamic shared memory on this handle's device
     NsofStageSlot stage[4];
     int stage_next = 0;
     // debug truncation (tests only)

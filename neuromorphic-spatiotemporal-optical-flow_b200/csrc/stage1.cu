@@ -356,8 +356,6 @@ static int validate_roi(const nsof_roi_params *p)
     return NSOF_OK;
 }
 
-static bool g_roi_smem_set = false;
-
 extern "C" int nsof_roi_from_state_f64(nsof_handle *h, const double *currents, int n, const nsof_roi_params *p,
                                        const double *thr_table, uint8_t *memimg, int32_t *labels, int32_t *n_components,
                                        int32_t *n_rects, nsof_rect *rects, int32_t *stats, void *cuda_stream)
@@ -368,9 +366,9 @@ extern "C" int nsof_roi_from_state_f64(nsof_handle *h, const double *currents, i
     if (n == 0) return NSOF_OK;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     const size_t smem = ((size_t)p->cells_h * p->cells_w + 1 + 5 * NSOF_MAX_RECTS) * sizeof(int);
-    if (!g_roi_smem_set) {
+    if (!h->roi_smem_set) {  // the attribute is per device: kept per handle, like lz_smem_set
         NSOF_CUDA_TRY(cudaFuncSetAttribute(k_s1_roi, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        g_roi_smem_set = true;
+        h->roi_smem_set = true;
     }
     NSOF_KLAUNCH(h, NSOF_K_ROI, (double)n * p->cells_h * p->cells_w * 13., k_s1_roi, n, 1, 1, 128, smem, (cudaStream_t)cuda_stream, currents, *p, thr_table, memimg, labels,
                 n_components, n_rects, rects, stats);

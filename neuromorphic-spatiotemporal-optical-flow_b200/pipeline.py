@@ -140,9 +140,12 @@ class SequencePipeline:
         self.n_dirty = 0          # descriptors whose flow rectangles are non-zero in self.flow (previous step)
         self.last_rects = None
         self.last_crop_pixels = 0
+        # workspace hint for the largest Farneback batch of a step: ROI crops of about a fifth of the frame plus, in the
+        # scripts' form, one whole frame per clip; a batch that needs more grows the arena (nsof_farneback_batch)
         biggest = max(q - p for p, q in self.chunks) * self.C if not full_frame else self.n_pairs
         for e in [engine] + [e for e, _ in self.s2_extra]:
-            e.reserve(biggest * self.H * self.W if full_frame else biggest * self.H * self.W // 3, biggest)
+            e.reserve(biggest * self.H * self.W if full_frame
+                      else biggest * self.H * self.W // 5 + self.C * self.H * self.W, biggest)
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.dev).cuda_stream)

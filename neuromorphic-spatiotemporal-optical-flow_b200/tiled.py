@@ -95,8 +95,9 @@ class TiledFarneback:
         if self.world == 1:
             return
         dist, torch = self.dist, self.torch
-        first = self._query(0, level, what)
-        key = (n_items, level, what, rows, first.ptr, first.h, first.w)
+        # the cached block tables hold absolute addresses of EVERY item: key the plan on all of them
+        key = (n_items, level, what, rows) + tuple((q.ptr, q.h, q.w, q.row_floats) for q in
+                                                   (self._query(i, level, what) for i in range(n_items)))
         plan = self._ops.get(key)
         if plan is None:
             up, dn = self.rank > 0, self.rank < self.world - 1
