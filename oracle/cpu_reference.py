@@ -85,41 +85,59 @@ def process_clip(frames, cfg=GRASP, params=FARNEBACK_PARAMS, full_frame=False, k
     return F - 1, time.perf_counter() - t0, rects, (flows if keep_flow else None)
 
 
-_POOL_CLIPS = None   # clips of the persistent pool: set before the fork, so workers inherit them (no pickling per task)
+_POOL_CLIPS = None   # per worker process: the clips, memory-mapped from the pool's scratch directory
+
+
+def _pool_init(paths):
+    global _POOL_CLIPS
+    if cv2 is not None:
+        cv2.setNumThreads(1)
+    _POOL_CLIPS = [np.load(p, mmap_mode="r") for p in paths]
 
 
 def _worker(args):
     idx, full_frame, roi_state = args
-    if cv2 is not None:
-        cv2.setNumThreads(1)
-    n, dt, _, _ = process_clip(_POOL_CLIPS[idx], full_frame=full_frame, roi_state=roi_state)
+    n, dt, _, _ = process_clip(np.asarray(_POOL_CLIPS[idx]), full_frame=full_frame, roi_state=roi_state)
     return n
 
 
 class ClipPool:
-    """ONE persistent fork pool of `workers` processes over a fixed list of clips ((F, H, W) uint8 arrays), one clip
-    per task -- OpenCV's Farneback core is single-threaded, so this is the CPU path's best case.  Created BEFORE any
-    timed region; `run()` is what gets timed."""
+    """ONE persistent pool of `workers` processes over a fixed list of clips ((F, H, W) uint8 arrays), one clip per
+    task -- OpenCV's Farneback core is single-threaded, so this is the CPU path's best case.  Created BEFORE any timed
+    region; `run()` is what gets timed.  The workers are SPAWNED (fresh interpreters importing numpy / cv2 only), never
+    forked: bench.py's GPU arm calls this from a process that holds a CUDA context and thread pools, and forked
+    children of such a process deadlocked in their first cv2 / BLAS call.  The clips reach the workers through .npy files
+    in a scratch directory (memory-mapped once per worker, at pool start)."""
 
     def __init__(self, clips, workers, roi_state="scripts"):
         import multiprocessing as mp
-        global _POOL_CLIPS
-        _POOL_CLIPS = list(clips)
-        self.n, self.workers, self.roi_state = len(_POOL_CLIPS), max(1, int(workers)), roi_state
-        self.pool = mp.get_context("fork").Pool(self.workers) if self.workers > 1 else None
+        import tempfile
+        self.n, self.workers, self.roi_state = len(clips), max(1, int(workers)), roi_state
+        base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+        self.dir = tempfile.mkdtemp(prefix="nsof_clips_", dir=base)
+        self.paths = []
+        seen = {}
+        for i, c in enumerate(clips):
+            if id(c) not in seen:       # the same array listed twice is stored once
+                seen[id(c)] = os.path.join(self.dir, f"clip{i}.npy")
+                np.save(seen[id(c)], np.ascontiguousarray(c))
+            self.paths.append(seen[id(c)])
+        self.pool = mp.get_context("spawn").Pool(self.workers, initializer=_pool_init, initargs=(self.paths,))
 
     def run(self, full_frame=False):
         """-> (pairs processed, wall seconds) for one pass over all clips."""
         t0 = time.perf_counter()
         tasks = [(i, full_frame, self.roi_state) for i in range(self.n)]
-        n = sum(self.pool.map(_worker, tasks, chunksize=1)) if self.pool else sum(_worker(t) for t in tasks)
+        n = sum(self.pool.map(_worker, tasks, chunksize=1))
         return n, time.perf_counter() - t0
 
     def close(self):
+        import shutil
         if self.pool is not None:
             self.pool.close()
             self.pool.join()
             self.pool = None
+        shutil.rmtree(self.dir, ignore_errors=True)
 
 
 def process_clips_parallel(clips, workers, full_frame=False, roi_state="scripts"):
