@@ -123,6 +123,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     h->arena.release();
+    h->tile_buf.release();
     h->tables.release();
     h->clear_tab.release();
     h->guard_buf.release();
@@ -155,7 +156,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
     "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload",
-    "seg_pack", "seg_morph", "seg_unpack", "rgb2gray", "remap_flow"};
+    "seg_pack", "seg_morph", "seg_unpack", "rgb2gray", "remap_flow", "fb_tile_list"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 
@@ -446,6 +447,14 @@ struct FbTiling {
     int *guard;        // device flag, see FbJob::guard
 };
 
+// Tile lists of a level: which items they hold and the tile geometry
+//   PP0 / PP1  fused pyramid + PolyExp, items with fast == 1 / 2       64 x 32 over rows [y_lo, y_hi)
+//   PYR        generic pyramid, items with fast == 0                    32 x 16 (separable) or 32 x 8 (direct) over I rows
+//   PE         generic PolyExp, items with fast == 0                    32 x 32
+//   UM         first UpdateMatrices / flow initialisation, all items    128 x 8
+//   BS         blur + solve, all items                                  BTW x BTH, or 32 x 16 on latency-bound levels
+enum { FB_L_PP0 = 0, FB_L_PP1, FB_L_PYR, FB_L_PE, FB_L_UM, FB_L_BS, FB_NLISTS };
+
 struct FbBatchCtx {
     bool valid = false;
     int n = 0, max_scales = 0, stop_level = 0, m = 0;
@@ -458,9 +467,12 @@ struct FbBatchCtx {
     // [variant * max_scales + level]
     int n_variants = 1, edge = 0;
     std::vector<size_t> gk_off, job_off;
-    std::vector<int> n_active, path_n, max_tiles_pp, max_tiles_ps, ps_sw, ps_sh, max_tiles_pyr, max_tiles_pe,
-        max_tiles_um, max_tiles_bs, max_tiles_bss;
+    std::vector<int> n_active, path_n, ps_sw, ps_sh;
     std::vector<long long> sum_tiles_bs;
+    // flat tile lists (one CTA per entry), per [kk * FB_NLISTS + list]: first entry and entry count in h->tile_buf
+    std::vector<unsigned> list_off, list_n;
+    std::vector<char> bs_small, pyr_sep;  // per kk: geometry of FB_L_BS (32x16 instead of 64x32) / FB_L_PYR (separable)
+    const uint2 *dtiles = nullptr;
     std::vector<int> n_init;  // per level: items whose coarsest level it is and that take an initial flow (k > 0)
     std::vector<double> sumN, sumNc, path_N, path_N0;
     int BTW = 0, BTH = 0;
@@ -560,6 +572,13 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
         X.job_off[kk] = table_bytes;
         table_bytes += round_up((size_t)X.n_active[kk] * sizeof(FbJob), 16);
     }
+    // runs of the flat tile lists: at most one per (level, list, item); only the used part is uploaded
+    const size_t runs_off = table_bytes;
+    {
+        size_t max_runs = 0;
+        for (int kk = 0; kk < LV; kk++) max_runs += (size_t)X.n_active[kk] * FB_NLISTS;
+        table_bytes += round_up(max_runs * sizeof(FbTileRun), 16);
+    }
     NsofStageSlot *slot;
     rc = nsof_stage_acquire(h, table_bytes, &slot);
     if (rc) return rc;
@@ -573,9 +592,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     X.path_n.assign(3 * LV, 0);
     X.path_N.assign(3 * LV, 0.);
     X.path_N0.assign(3 * LV, 0.);
-    for (auto *v : {&X.max_tiles_pp, &X.max_tiles_ps, &X.ps_sw, &X.ps_sh, &X.max_tiles_pyr, &X.max_tiles_pe, &X.max_tiles_um,
-                    &X.max_tiles_bs, &X.max_tiles_bss})
-        v->assign(LV, 0);
+    for (auto *v : {&X.ps_sw, &X.ps_sh}) v->assign(LV, 0);
     X.sum_tiles_bs.assign(LV, 0);
     X.n_init.assign(LV, 0);
     const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
@@ -654,24 +671,67 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             jobs[a++] = J;
             X.sumN[kk] += (double)rows * J.w;
             if (!coarsest) X.sumNc[kk] += (double)J.ch * J.cw * frac;
-            auto tiles = [&](int tw, int th, int nrows) { return ((J.w + tw - 1) / tw) * ((nrows + th - 1) / th); };
-            X.max_tiles_pyr[kk] = std::max(X.max_tiles_pyr[kk], tiles(FB_PYR_TW, FB_PYR_TH, irows));
-            X.max_tiles_pe[kk] = std::max(X.max_tiles_pe[kk], tiles(FB_PE_TW, FB_PE_TH, rows));
-            X.max_tiles_pp[kk] = std::max(X.max_tiles_pp[kk], tiles(FB_PP_TW, FB_PP_TH, rows));
             if (!J.fast) {
-                X.max_tiles_ps[kk] = std::max(X.max_tiles_ps[kk], tiles(FB_PS_TW, FB_PS_TH, irows));
                 X.ps_sw[kk] = std::max(X.ps_sw[kk], (int)ceil(FB_PS_TW * J.sx) + 2 * (X.ksize[k] / 2) + 4);
                 X.ps_sh[kk] = std::max(X.ps_sh[kk], (int)ceil(FB_PS_TH * J.sy) + 2 * (X.ksize[k] / 2) + 4);
             }
-            X.max_tiles_um[kk] = std::max(X.max_tiles_um[kk], tiles(FB_UM_TW, FB_UM_TH, rows));
-            if (X.BTW) X.max_tiles_bs[kk] = std::max(X.max_tiles_bs[kk], tiles(X.BTW, X.BTH, rows));
-            if (X.bs_m7) {
-                X.max_tiles_bss[kk] = std::max(X.max_tiles_bss[kk], tiles(FB_BS7S_TW, FB_BS7S_TH, rows));
-                X.sum_tiles_bs[kk] += tiles(X.BTW, X.BTH, rows);
-            }
+            if (X.bs_m7) X.sum_tiles_bs[kk] += (long long)((J.w + X.BTW - 1) / X.BTW) * ((rows + X.BTH - 1) / X.BTH);
+            (void)irows;
         }
     }
-    { int rc_up = nsof_table_upload(h, X.ds, slot, table_bytes, stream); if (rc_up) return rc_up; }
+    // ---- flat tile lists: per (level, list) the runs (item, tile count) of the items it holds, in item order
+    X.list_off.assign((size_t)LV * FB_NLISTS, 0);
+    X.list_n.assign((size_t)LV * FB_NLISTS, 0);
+    X.bs_small.assign(LV, 0);
+    X.pyr_sep.assign(LV, 0);
+    FbTileRun *runs = (FbTileRun *)(hs + runs_off);
+    size_t n_runs = 0;
+    unsigned n_tiles = 0;
+    for (int kk = 0; kk < LV; kk++) {
+        const int k = kk % max_scales;
+        // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the 32x16
+        // tile (4x the CTAs, each a quarter of the serial work)
+        X.bs_small[kk] = X.bs_m7 && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles;
+        // two CTAs per SM; larger windows (extreme resize ratios) take the direct pyramid kernel
+        X.pyr_sep[kk] = fb_ps_smem(X.ksize[k] / 2, X.ps_sw[kk], X.ps_sh[kk]) <= 100 * 1024;
+        const FbJob *jobs = (const FbJob *)(hs + X.job_off[kk]);
+        for (int l = 0; l < FB_NLISTS; l++) {
+            X.list_off[(size_t)kk * FB_NLISTS + l] = n_tiles;
+            for (int a = 0; a < X.n_active[kk]; a++) {
+                const FbJob &J = jobs[a];
+                const int rows = J.y_hi - J.y_lo, irows = J.iy_hi - J.iy_lo;
+                int tw = 0, th = 0, nr = rows;
+                switch (l) {
+                case FB_L_PP0: if (J.fast == 1) { tw = FB_PP_TW; th = FB_PP_TH; } break;
+                case FB_L_PP1: if (J.fast == 2) { tw = FB_PP_TW; th = FB_PP_TH; } break;
+                case FB_L_PYR:
+                    if (!J.fast) { tw = X.pyr_sep[kk] ? FB_PS_TW : FB_PYR_TW; th = X.pyr_sep[kk] ? FB_PS_TH : FB_PYR_TH; nr = irows; }
+                    break;
+                case FB_L_PE: if (!J.fast) { tw = FB_PE_TW; th = FB_PE_TH; } break;
+                case FB_L_UM: tw = FB_UM_TW; th = FB_UM_TH; break;
+                case FB_L_BS:
+                    if (X.BTW) { tw = X.bs_small[kk] ? FB_BS7S_TW : X.BTW; th = X.bs_small[kk] ? FB_BS7S_TH : X.BTH; }
+                    break;
+                }
+                if (!tw || nr <= 0) continue;
+                const unsigned cnt = (unsigned)(((J.w + tw - 1) / tw) * ((nr + th - 1) / th));
+                if (!cnt) continue;
+                FbTileRun r = {n_tiles, (unsigned)a, cnt, 0u};
+                runs[n_runs++] = r;
+                n_tiles += cnt;
+            }
+            X.list_n[(size_t)kk * FB_NLISTS + l] = n_tiles - X.list_off[(size_t)kk * FB_NLISTS + l];
+        }
+    }
+    rc = h->tile_buf.ensure((size_t)std::max(n_tiles, 1u) * sizeof(uint2));
+    if (rc) return rc;
+    X.dtiles = (const uint2 *)h->tile_buf.p;
+    { int rc_up = nsof_table_upload(h, X.ds, slot, runs_off + n_runs * sizeof(FbTileRun), stream); if (rc_up) return rc_up; }
+    if (n_runs) {
+        NSOF_KLAUNCH(h, NSOF_K_TILE_LIST, (double)n_runs * sizeof(FbTileRun) + (double)n_tiles * sizeof(uint2), k_fb_build_tiles,
+                     (int)n_runs, 1, 1, 128, 0, stream, (const FbTileRun *)(X.ds + runs_off), (uint2 *)h->tile_buf.p);
+        NSOF_CUDA_TRY(cudaGetLastError());
+    }
 
     prepare_poly(params->poly_n, params->poly_sigma, &X.pc);
     X.pe_smem = ((size_t)(FB_PE_TH + 2 * pn) * (FB_PE_TW + 2 * pn) + 3 * (size_t)FB_PE_TH * (FB_PE_TW + 2 * pn)) * sizeof(float);
@@ -707,22 +767,24 @@ static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream, int var
     const int na = X.n_active[kk];
     const PolyConst &pc = X.pc;
     h->prof_level = k;
-    if (X.path_n[3 * kk + 1] && X.max_tiles_pp[kk])
+    const auto ln = [&](int l) { return (int)X.list_n[(size_t)kk * FB_NLISTS + l]; };
+    const auto lp = [&](int l) { return X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + l]; };
+    (void)na;
+    if (ln(FB_L_PP0))
         NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 1] + 40 * X.path_N[3 * kk + 1], FB_PYR_POLYEXP_M0,
-                     X.max_tiles_pp[kk], na, 2, 256, fb_pp_smem(0), stream, jobs, gk, pc);
-    if (X.path_n[3 * kk + 2] && X.max_tiles_pp[kk])
+                     ln(FB_L_PP0), 1, 2, 256, fb_pp_smem(0), stream, jobs, lp(FB_L_PP0), gk, pc);
+    if (ln(FB_L_PP1))
         NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 2] + 40 * X.path_N[3 * kk + 2], FB_PYR_POLYEXP_M1,
-                     X.max_tiles_pp[kk], na, 2, 256, fb_pp_smem(1), stream, jobs, gk, pc);
-    if (X.path_n[3 * kk] && X.max_tiles_pe[kk]) {
+                     ln(FB_L_PP1), 1, 2, 256, fb_pp_smem(1), stream, jobs, lp(FB_L_PP1), gk, pc);
+    if (ln(FB_L_PYR) && ln(FB_L_PE)) {
         const int r = X.ksize[k] / 2;
-        const size_t ps_smem = fb_ps_smem(r, X.ps_sw[kk], X.ps_sh[kk]);
-        if (ps_smem <= 100 * 1024)  // two CTAs per SM; larger windows (extreme ratios) take the direct kernel
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, X.max_tiles_ps[kk], na, 2, 256, ps_smem, stream, jobs,
-                         gk, r, X.ps_sw[kk], X.ps_sh[kk]);
+        if (X.pyr_sep[kk])
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, ln(FB_L_PYR), 1, 2, 256,
+                         fb_ps_smem(r, X.ps_sw[kk], X.ps_sh[kk]), stream, jobs, lp(FB_L_PYR), gk, r, X.ps_sw[kk], X.ps_sh[kk]);
         else
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, X.max_tiles_pyr[kk], na, 2, 256, 0, stream, jobs, gk, r);
-        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, X.max_tiles_pe[kk], na, 2, 256, X.pe_smem, stream,
-                     jobs, pc);
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, ln(FB_L_PYR), 1, 2, 256, 0, stream, jobs, lp(FB_L_PYR), gk, r);
+        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, ln(FB_L_PE), 1, 2, 256, X.pe_smem, stream,
+                     jobs, lp(FB_L_PE), pc);
     }
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
@@ -737,18 +799,21 @@ static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream, int va
     const FbJob *jobs = (const FbJob *)(X.ds + X.job_off[kk]);
     const int na = X.n_active[kk];
     h->prof_level = k;
-    if (!X.max_tiles_um[kk]) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
+    const int n_um = (int)X.list_n[(size_t)kk * FB_NLISTS + FB_L_UM];
+    const uint2 *tl_um = X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + FB_L_UM];
+    (void)na;
+    if (!n_um) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
     if (X.n_init[kk])  // OPTFLOW_USE_INITIAL_FLOW: items whose coarsest level this is
-        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumN[kk], k_fb_area_init, X.max_tiles_um[kk], na, 1, 256, 0, stream, jobs);
+        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumN[kk], k_fb_area_init, n_um, 1, 1, 256, 0, stream, jobs, tl_um);
     if (X.params.iterations == 0)
-        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
-                     jobs, X.flow_mul);
+        NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, n_um, 1, 1, 256, 0, stream,
+                     jobs, tl_um, X.flow_mul);
     else if (X.params.flags & NSOF_FB_USE_INITIAL_FLOW)
-        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_init, X.max_tiles_um[kk], na, 1, 256, 0, stream,
-                     jobs, X.flow_mul);
+        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_init, n_um, 1, 1, 256, 0, stream,
+                     jobs, tl_um, X.flow_mul);
     else
-        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first, X.max_tiles_um[kk], na, 1, 256, 0, stream,
-                     jobs, X.flow_mul);
+        NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first, n_um, 1, 1, 256, 0, stream,
+                     jobs, tl_um, X.flow_mul);
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
     return NSOF_OK;
@@ -764,21 +829,22 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
     const bool last = it == iters - 1;
     const double Nk = X.sumN[kk];
     h->prof_level = k;
-    if (!X.max_tiles_bs[kk]) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
-    // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the
-    // 32x16 tile (4x the CTAs, each a quarter of the serial work)
-    if (X.bs_m7 && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles)
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, X.max_tiles_bss[kk], na, 1,
-                     FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, X.bscale, (it & 1) == 0, last);
+    const int n_bs = (int)X.list_n[(size_t)kk * FB_NLISTS + FB_L_BS];
+    const uint2 *tl_bs = X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + FB_L_BS];
+    (void)na;
+    if (!n_bs) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
+    if (X.bs_m7 && X.bs_small[kk])  // latency-bound level: the 32x16 tile (see fb_prepare)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, n_bs, 1, 1,
+                     FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, last);
     else if (X.bs_m7)
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, X.max_tiles_bs[kk], na, 1,
-                     FB_BS7_NT, X.bs_smem, stream, jobs, X.bscale, (it & 1) == 0, last);
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, n_bs, 1, 1,
+                     FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, last);
     else if (X.gwin.on)
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve_gauss, X.max_tiles_bs[kk], na, 1,
-                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve_gauss, n_bs, 1, 1,
+                     256, X.bs_smem, stream, jobs, tl_bs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
     else
-        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, X.max_tiles_bs[kk], na, 1,
-                     256, X.bs_smem, stream, jobs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve, n_bs, 1, 1,
+                     256, X.bs_smem, stream, jobs, tl_bs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
     NSOF_CUDA_TRY(cudaGetLastError());
     h->prof_level = -1;
     return NSOF_OK;

@@ -15,8 +15,10 @@
 // accesses at x % 4 == 0 are aligned.  Planar (SoA) instead of OpenCV's AoS-5 keeps every
 // warp access a run of consecutive 4-byte words; byte counts are identical.
 //
-// All kernels take a device table of per-item jobs and run as grid (max_tiles, n_items[, 2]):
-// blocks past an item's tile count exit at once, which is how ragged ROI crops batch.
+// All kernels take a device table of per-item jobs and a FLAT TILE LIST (one uint2 = (item, tile of that item) per
+// CTA, built on the device by k_fb_build_tiles from per-item runs) and run as grid (n_tiles_of_all_items[, 1, 2]):
+// ragged ROI crops batch into exactly as many CTAs as there are tiles.  (Round 1 ran grid (max tiles, items) with
+// early exits: one whole-frame item among 250 small crops made 90 % of the CTAs of every launch empty.)
 #pragma once
 #include "nsof_rt.h"
 #include <algorithm>
@@ -28,7 +30,7 @@
 #endif
 
 
-struct FbJob {
+struct alignas(16) FbJob {
     int h, w, pitch;       // this level
     int ch, cw, cpitch;    // coarser level (flow source), ch == 0 -> zero initial flow; cpitch in float2
     int sh, sw;            // full-resolution source
@@ -59,6 +61,17 @@ struct FbJob {
     const float2 *flow0;  // the caller's full-resolution flow (sh x sw, f0pitch in float2)
     int f0pitch;
 };
+
+// One run of a flat tile list: `count` consecutive entries (item, 0), (item, 1), ... starting at entry `off`.
+struct FbTileRun {
+    unsigned off, item, count, pad;
+};
+
+NSOF_GLOBAL k_fb_build_tiles(const FbTileRun *NSOF_RESTRICT runs, uint2 *NSOF_RESTRICT tiles)
+{
+    const FbTileRun r = runs[NSOF_BX];
+    for (unsigned t = (unsigned)NSOF_TID; t < r.count; t += (unsigned)NSOF_NT) tiles[r.off + t] = make_uint2(r.item, t);
+}
 
 struct PolyConst {
     int n;
@@ -113,17 +126,17 @@ NSOF_DEV void fb_lin_coord(int d, double ratio, int len, int *i0, int *i1, float
 #define FB_PYR_TW 32
 #define FB_PYR_TH 8
 
-NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk, int r)
+NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, const float *NSOF_RESTRICT gk, int r)
 {
-    const FbJob J = jobs[NSOF_BY];
-    if (J.fast) return;
-    const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW, tiles_y = (J.iy_hi - J.iy_lo + FB_PYR_TH - 1) / FB_PYR_TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_PYR_TW, ty0 = J.iy_lo + (NSOF_BX / tiles_x) * FB_PYR_TH;
+    const int tx0 = (tile % tiles_x) * FB_PYR_TW, ty0 = J.iy_lo + (tile / tiles_x) * FB_PYR_TH;
     for (int i = NSOF_TID; i < FB_PYR_TW * FB_PYR_TH; i += NSOF_NT) {
         const int x = tx0 + i % FB_PYR_TW, y = ty0 + i / FB_PYR_TW;
         if (x >= J.w || y >= J.iy_hi) continue;
@@ -161,17 +174,17 @@ NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT
 #define FB_PE_TW 32
 #define FB_PE_TH 32
 
-NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, PolyConst pc)
+NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, PolyConst pc)
 {
-    const FbJob J = jobs[NSOF_BY];
-    if (J.fast) return;
-    const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW, tiles_y = (J.y_hi - J.y_lo + FB_PE_TH - 1) / FB_PE_TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW;
     const int img = NSOF_BZ;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *I = J.I + img * plane;
     float *R = J.R + (size_t)img * 5 * plane;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_PE_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_PE_TH;
+    const int tx0 = (tile % tiles_x) * FB_PE_TW, ty0 = J.y_lo + (tile / tiles_x) * FB_PE_TH;
     const int n = pc.n, IW = FB_PE_TW + 2 * n, IH = FB_PE_TH + 2 * n;
     NSOF_DYN_SMEM(smem_raw);
     float *sI = (float *)smem_raw;
@@ -376,14 +389,19 @@ NSOF_DEV float2 fb_upsampled_flow(const FbJob &J, int x, int y, float flow_mul)
 // per full-frame step, (256, 5) with its 60-byte spill 2.51 ms)
 // INIT = 1: the batch carries OPTFLOW_USE_INITIAL_FLOW items (J.init); a separate instantiation because the extra
 // branch costs the hot path 6 registers and with them the fourth CTA per SM (2.35 -> 2.62 ms per full-frame step)
+// Flat tile lists (round 2): 72 registers without a bound, 64 + a 12-byte spill with (256, 4): the fourth CTA per SM is kept
+#ifndef FB_UM_MINB
+#define FB_UM_MINB 4
+#endif
 template <int INIT>
-NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float flow_mul)
 {
-    const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW;
     const size_t plane = (size_t)J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;
+    const int tx0 = (tile % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (tile / tiles_x) * FB_UM_TH;
     // The R1 gather addresses depend on the coarse-flow loads: start pulling the tile's R1 rows (+- 4 rows for the
     // displacement) into L2 now, so that the second, dependent round of loads does not pay DRAM latency again.
     {
@@ -435,8 +453,8 @@ NSOF_GLOBAL k_fb_um_first_g(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
     }
 }
 
-static void (*const k_fb_um_first)(const FbJob *, float) = k_fb_um_first_g<0>;
-static void (*const k_fb_um_first_init)(const FbJob *, float) = k_fb_um_first_g<1>;
+static void (*const k_fb_um_first)(const FbJob *, const uint2 *, float) = k_fb_um_first_g<0>;
+static void (*const k_fb_um_first_init)(const FbJob *, const uint2 *, float) = k_fb_um_first_g<1>;
 
 // ---------------------------------------------------------------------------------------------
 // OPTFLOW_USE_INITIAL_FLOW (A.8): flow_coarsest = resize(flow0, (w_k, h_k), INTER_AREA) * f32(scale_k), two-channel
@@ -476,13 +494,15 @@ NSOF_DEV void fb_area_tap(const FbAreaAxis &A, int i, int *si, float *a)
     else { *si = A.s2; *a = A.a1; }
 }
 
-NSOF_GLOBAL k_fb_area_init(const FbJob *NSOF_RESTRICT jobs)
+NSOF_GLOBAL k_fb_area_init(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl)
 {
-    const FbJob J = jobs[NSOF_BY];
+    // runs on the UM tile list (initial flow is refused in the row-tiled mode, so [y_lo, y_hi) is the whole level)
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
     if (J.init != 1) return;
-    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.h + FB_UM_TH - 1) / FB_UM_TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = (NSOF_BX / tiles_x) * FB_UM_TH;
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW;
+    const int tx0 = (tile % tiles_x) * FB_UM_TW, ty0 = (tile / tiles_x) * FB_UM_TH;
     const bool fastp = J.sh % J.h == 0 && J.sw % J.w == 0;
     for (int i = NSOF_TID; i < FB_UM_TW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + i % FB_UM_TW, y = ty0 + i / FB_UM_TW;
@@ -533,13 +553,14 @@ NSOF_GLOBAL k_fb_area_init(const FbJob *NSOF_RESTRICT jobs)
 }
 
 // Level with zero iterations: flow is just the (scaled) upsampled coarse flow, or zero.
-NSOF_GLOBAL k_fb_flow_init(const FbJob *NSOF_RESTRICT jobs, float flow_mul)
+NSOF_GLOBAL k_fb_flow_init(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float flow_mul)
 {
-    const FbJob J = jobs[NSOF_BY];
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
     if (J.init) return;  // the initial flow is already in place
-    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW, tiles_y = (J.y_hi - J.y_lo + FB_UM_TH - 1) / FB_UM_TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
-    const int tx0 = (NSOF_BX % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * FB_UM_TH;
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + FB_UM_TW - 1) / FB_UM_TW;
+    const int tx0 = (tile % tiles_x) * FB_UM_TW, ty0 = J.y_lo + (tile / tiles_x) * FB_UM_TH;
     for (int i = NSOF_TID; i < FB_UM_TW * FB_UM_TH; i += NSOF_NT) {
         const int x = tx0 + i % FB_UM_TW, y = ty0 + i / FB_UM_TW;
         if (x >= J.w || y >= J.y_hi) continue;
@@ -581,16 +602,17 @@ struct FbGaussWin {
 };
 
 template <int GAUSS>  // compile-time: the box instantiation must not pay for the indexed weight table
-NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, int m, float scale, int src_is_a,
-                              int last, const FbGaussWin gwin)
+NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, int TW, int TH, int m, float scale,
+                              int src_is_a, int last, const FbGaussWin gwin)
 {
-    const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + TW - 1) / TW;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *Min = src_is_a ? J.Ma : J.Mb;
     float *Mout = src_is_a ? J.Mb : J.Ma;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
     const int LW = TW + 2 * m, LH = TH + 2 * m, PW = (LW + 3) & ~3;
     const int SP = LH * PW;  // smem plane
     NSOF_DYN_SMEM(smem_raw);
@@ -704,20 +726,22 @@ NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, int TW, int TH, i
 // dynamic smem: 16 B (mbarrier) + 5 * (TH+2M) * (TW+2ML) floats.
 // ---------------------------------------------------------------------------------------------
 template <int M, int TW, int TH, int NT, int MINB>
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, float scale, int src_is_a, int last)
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float scale,
+                                                           int src_is_a, int last)
 {
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
     constexpr int RPP = (2 * M * PW) / (2 * TW);        // flow rows (TW float2) that fit the dead rows of one plane
     static_assert(5 * RPP >= TH, "the flow tile must fit the dead halo rows");
     static_assert((TH * PW) % 4 == 0 && (2 * TW) % 4 == 0, "flow rows must stay 16-byte aligned");
-    const FbJob J = jobs[NSOF_BY];
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + TW - 1) / TW;
     const size_t plane = (size_t)J.pitch * J.h;
     const float *Min = src_is_a ? J.Ma : J.Mb;
     float *Mout = src_is_a ? J.Mb : J.Ma;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
     float *sM = (float *)(smem_raw + 16);
@@ -947,8 +971,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #endif
 }
 
-static void (*const k_fb_blur_solve)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<0>;
-static void (*const k_fb_blur_solve_gauss)(const FbJob *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<1>;
+static void (*const k_fb_blur_solve)(const FbJob *, const uint2 *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<0>;
+static void (*const k_fb_blur_solve_gauss)(const FbJob *, const uint2 *, int, int, int, float, int, int, FbGaussWin) = k_fb_blur_solve_g<1>;
 // a plain function-pointer name: template commas do not survive nested launch macros
 #ifndef FB_BS7_MINB
 #define FB_BS7_MINB 3
@@ -959,8 +983,8 @@ static void (*const k_fb_blur_solve_gauss)(const FbJob *, int, int, int, float, 
 #define FB_BS7S_TW 32   // small tile: coarse levels / small batches are latency-bound, more and shorter CTAs
 #define FB_BS7S_TH 16
 #define FB_BS7S_NT 128
-static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
-static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
+static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, const uint2 *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
+static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
 #define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
 #define FB_BS7S_SMEM (16 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
 
@@ -981,8 +1005,8 @@ template <int MODE, int N, int TW, int TH>
 #ifndef FB_PP_MINB
 #define FB_PP_MINB 4
 #endif
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk,
-                                                         PolyConst pc)
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl,
+                                                         const float *NSOF_RESTRICT gk, PolyConst pc)
 {
     constexpr int IW = TW + 2 * N, IH = TH + 2 * N, IP = (IW + 3) & ~3;
     constexpr int SWN = (MODE ? 2 * IW : IW) + 2, SHN = (MODE ? 2 * IH : IH) + 2;  // source window actually needed
@@ -998,16 +1022,16 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
 #endif
     constexpr int BSTRIP = FB_PP_BSTRIP, BNS = (IH + BSTRIP - 1) / BSTRIP;
     static_assert(A_BYTES % 16 == 0 && B_BYTES % 16 == 0, "shared regions must stay 16-byte aligned");
-    const FbJob J = jobs[NSOF_BY];
-    if (J.fast != MODE + 1) return;
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.y_hi - J.y_lo + TH - 1) / TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];  // the list holds items with fast == MODE + 1 only
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + TW - 1) / TW;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     const size_t plane = (size_t)J.pitch * J.h;
     float *R = J.R + (size_t)img * 5 * plane;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.y_lo + (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
     float *sS = (float *)(smem_raw + 16);                 // phases A2/B
@@ -1233,8 +1257,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
 #define FB_PP_TW 64
 #define FB_PP_TH 32
 #define FB_PP_N 5
-static void (*const FB_PYR_POLYEXP_M0)(const FbJob *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, FB_PP_N, FB_PP_TW, FB_PP_TH>;
-static void (*const FB_PYR_POLYEXP_M1)(const FbJob *, const float *, PolyConst) = k_fb_pyr_polyexp_t<1, FB_PP_N, FB_PP_TW, FB_PP_TH>;
+static void (*const FB_PYR_POLYEXP_M0)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, FB_PP_N, FB_PP_TW, FB_PP_TH>;
+static void (*const FB_PYR_POLYEXP_M1)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<1, FB_PP_N, FB_PP_TW, FB_PP_TH>;
 static inline size_t fb_pp_smem(int mode)
 {
     const int IW = FB_PP_TW + 2 * FB_PP_N, IH = FB_PP_TH + 2 * FB_PP_N, IP = (IW + 3) & ~3;
@@ -1257,18 +1281,19 @@ static inline size_t fb_pp_smem(int mode)
 #define FB_PS_TW 32
 #define FB_PS_TH 16
 
-NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const float *NSOF_RESTRICT gk, int r, int SWmax, int SHmax)
+NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, const float *NSOF_RESTRICT gk, int r,
+                         int SWmax, int SHmax)
 {
     constexpr int TW = FB_PS_TW, TH = FB_PS_TH;
-    const FbJob J = jobs[NSOF_BY];
-    if (J.fast) return;
-    const int tiles_x = (J.w + TW - 1) / TW, tiles_y = (J.iy_hi - J.iy_lo + TH - 1) / TH;
-    if (NSOF_BX >= tiles_x * tiles_y) return;
+    const uint2 te = tl[NSOF_BX];  // the list holds the generic-path items (fast == 0) only
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + TW - 1) / TW;
     const int img = NSOF_BZ;
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
-    const int tx0 = (NSOF_BX % tiles_x) * TW, ty0 = J.iy_lo + (NSOF_BX / tiles_x) * TH;
+    const int tx0 = (tile % tiles_x) * TW, ty0 = J.iy_lo + (tile / tiles_x) * TH;
     const int twn = nsof_imin(TW, J.w - tx0), thn = nsof_imin(TH, J.iy_hi - ty0);
     const int SWp = (SWmax + 32 + 15) & ~15;
     NSOF_DYN_SMEM(smem_raw);

@@ -52,7 +52,7 @@ enum NsofKernelClass {
     NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_PYR_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
     NSOF_K_LANCZOS, NSOF_K_FRAME_SIM, NSOF_K_ROI, NSOF_K_EVENT_HIST, NSOF_K_EVENT_REPLAY, NSOF_K_SYNAPSE_STEP,
     NSOF_K_RESISTANCE, NSOF_K_FLOW_CLEAR, NSOF_K_HALO_COPY, NSOF_K_TABLE_UPLOAD, NSOF_K_SEG_PACK, NSOF_K_SEG_MORPH,
-    NSOF_K_SEG_UNPACK, NSOF_K_RGB2GRAY, NSOF_K_REMAP, NSOF_K_CLASSES
+    NSOF_K_SEG_UNPACK, NSOF_K_RGB2GRAY, NSOF_K_REMAP, NSOF_K_TILE_LIST, NSOF_K_CLASSES
 };
 extern const char *const nsof_kernel_class_names[NSOF_K_CLASSES];
 
@@ -66,6 +66,7 @@ struct nsof_handle {
     int device = 0;
     NsofDevBuf arena;      // I, R, M, coarse flow of every item of the current batch
     NsofDevBuf tables;     // job tables + Gaussian taps on the device
+    NsofDevBuf tile_buf;   // flat tile lists of the current batch (uint2 = item, tile), built by k_fb_build_tiles
     NsofDevBuf clear_tab;  // rectangle table of nsof_flow_clear
     NsofDevBuf guard_buf;  // halo guard flag of a tiled batch
     FbBatchCtx *ctx = nullptr;  // plan, tables and launch geometry of the current batch

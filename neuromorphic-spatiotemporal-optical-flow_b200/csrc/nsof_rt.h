@@ -22,6 +22,8 @@
 #include <vector>
 struct float2 { float x, y; };
 struct float4 { float x, y, z, w; };
+struct uint2 { unsigned x, y; };
+static inline uint2 make_uint2(unsigned x, unsigned y) { uint2 r = {x, y}; return r; }
 static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r; }
 static inline float4 make_float4(float x, float y, float z, float w) { float4 r = {x, y, z, w}; return r; }
 namespace nsof_emu {
@@ -82,6 +84,24 @@ __device__ __forceinline__ double nsof_warp_sum_f64(double v)
 #define NSOF_LAUNCH(kern, gx, gy, gz, nt, smem_bytes, stream, ...) \
     kern<<<dim3((gx), (gy), (gz)), dim3(nt), (smem_bytes), (stream)>>>(__VA_ARGS__)
 #define NSOF_LAUNCH_BOUNDS(nt, minb) __launch_bounds__(nt, minb)
+#endif
+
+// The CTA's job descriptor, staged once in shared memory.  With flat tile lists the descriptor's address depends on a
+// loaded index (not on blockIdx), so a by-value copy read lazily from global memory pins the address and the live fields
+// in registers for the whole kernel (k_fb_um_first: 64 -> 72 registers, its fourth CTA per SM); shared-memory fields
+// have a constant address and can be re-read wherever they are needed.  T: 16-byte aligned, sizeof(T) % 16 == 0.
+#ifdef NSOF_EMU
+#define NSOF_JOB_TO_SMEM(T, J, src) \
+    const T J##_copy = *(src);      \
+    const T &J = J##_copy
+#else
+#define NSOF_JOB_TO_SMEM(T, J, src)                                                                             \
+    __shared__ __align__(16) T J##_s;                                                                           \
+    static_assert(sizeof(T) % 16 == 0, "job descriptors are copied as 16-byte words");                          \
+    for (int i_ = (int)threadIdx.x; i_ < (int)(sizeof(T) / 16); i_ += (int)blockDim.x)                          \
+        ((int4 *)&J##_s)[i_] = __ldg((const int4 *)(src) + i_);                                                 \
+    __syncthreads();                                                                                            \
+    const T &J = J##_s
 #endif
 
 NSOF_HD int nsof_imin(int a, int b) { return a < b ? a : b; }
