@@ -350,13 +350,16 @@ static int validate_params(const nsof_fb_params *p)
     return NSOF_OK;
 }
 
+// opt-in limit of dynamic shared memory per CTA: 227 KB minus the static part (the job descriptor, NSOF_JOB_TO_SMEM)
+#define FB_MAX_DYN_SMEM (227 * 1024 - 512)
+
 // Tile of k_fb_blur_solve for a window radius m: largest candidate that keeps >= 3 CTAs per SM,
 // else anything that fits the 227 KB opt-in limit.
 static bool pick_blur_tile(int m, int *TW, int *TH, size_t *smem)
 {
     static const int cand[][2] = {{64, 32}, {64, 16}, {32, 32}, {32, 16}, {16, 16}, {16, 8}, {8, 8}, {4, 4}};
     for (int pass = 0; pass < 2; pass++) {
-        const size_t limit = pass == 0 ? 75 * 1024 : 227 * 1024;
+        const size_t limit = pass == 0 ? 75 * 1024 : FB_MAX_DYN_SMEM;
         for (auto &c : cand) {
             const size_t pw = round_up(c[0] + 2 * m, 4);
             const size_t b = 5 * (size_t)(c[1] + 2 * m) * pw * sizeof(float);
@@ -395,14 +398,14 @@ extern "C" double nsof_fb_algorithmic_bytes(int h, int w, const nsof_fb_params *
 static int configure_smem(nsof_handle *h)
 {
     if (h->smem_configured) return NSOF_OK;
-    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve_gauss, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve_gauss, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7S, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7S_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(1)));
-    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
     h->smem_configured = true;
     return NSOF_OK;
 }
