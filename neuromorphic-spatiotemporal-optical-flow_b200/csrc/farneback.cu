@@ -320,6 +320,11 @@ static void prepare_poly(int n, double sigma, PolyConst *pc)
         pc->xg[k] = xg[n + k];
         pc->xxg[k] = xxg[n + k];
     }
+    for (int k = 0; k <= n && k < 8; k++) {
+        pc->g2[k] = make_float2(pc->g[k], pc->g[k]);
+        pc->xg2[k] = make_float2(pc->xg[k], pc->xg[k]);
+        pc->xxg2[k] = make_float2(pc->xxg[k], pc->xxg[k]);
+    }
     pc->ig11 = (float)inv[1][1];
     pc->ig03 = (float)inv[0][3];
     pc->ig33 = (float)inv[3][3];

@@ -77,6 +77,8 @@ struct PolyConst {
     int n;
     float g[NSOF_MAX_POLY_N + 1], xg[NSOF_MAX_POLY_N + 1], xxg[NSOF_MAX_POLY_N + 1];
     float ig11, ig03, ig33, ig55;
+    // taps 0 .. 7 once more as (t, t) pairs: operands of the packed FP32 instructions of k_fb_pyr_polyexp_t
+    float2 g2[8], xg2[8], xxg2[8];
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -1013,7 +1015,22 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
     constexpr int SW = (SWN + 3) & ~3;                                              // pitch of the float window
     constexpr int RP = (SWN + 32 + 15) & ~15;                                       // pitch of the raw uint8 window
     constexpr int A_BYTES = (3 * TH * IP * 4 > SHN * SW * 4 ? 3 * TH * IP * 4 : SHN * SW * 4);  // S (float) | sr
-    constexpr int B_BYTES = (IH * IP * 4 > SHN * RP ? IH * IP * 4 : SHN * RP);                  // raw u8 | sI
+#ifndef FB_PP_PACKED
+#define FB_PP_PACKED 1
+#endif
+#if FB_PP_PACKED
+    // Packed FP32 (FADD2 / FMUL2 / FFMA2) for the two moment passes: tile rows y and y + TH/2 travel in the two halves of
+    // every operand.  For the halves to be an aligned register pair after a plain shared-memory load, I and the three
+    // moment planes are stored ROW-PAIR INTERLEAVED: element (row r, column x) of I sits in float2 [r][x].x for
+    // r < PR and in [r - HALF][x].y for r >= HALF (rows HALF .. PR-1 twice: they belong to the windows of both halves);
+    // moment planes: float2 [y][x] = (row y, row y + HALF), y < HALF.
+    constexpr int HALF = TH / 2, PR = IH - HALF;
+    static_assert(TH % 8 == 0 && PR >= HALF && N <= 7, "row-pair layout");
+    constexpr int SI_BYTES = PR * IP * 8;
+#else
+    constexpr int SI_BYTES = IH * IP * 4;
+#endif
+    constexpr int B_BYTES = (SI_BYTES > SHN * RP ? SI_BYTES : SHN * RP);                        // raw u8 | sI
 #ifndef FB_PP_BSTRIP
 #define FB_PP_BSTRIP 14
 #endif
@@ -1039,6 +1056,18 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
     uint8_t *sraw = smem_raw + 16 + A_BYTES;              // phase A
     float *sI = (float *)(smem_raw + 16 + A_BYTES);       // phases B/C (aliases sraw)
     const int lane = NSOF_LANE, warp = NSOF_TID / NSOF_WARP, nw = nsof_imax(NSOF_NT / NSOF_WARP, 1);
+#if FB_PP_PACKED
+#define FB_SI_ST(ly, lx, v)                                                          \
+    {                                                                                \
+        const float v_ = (v);                                                        \
+        if ((ly) < PR) sI[(((ly)) * IP + (lx)) * 2] = v_;                            \
+        if ((ly) >= HALF) sI[(((ly) - HALF) * IP + (lx)) * 2 + 1] = v_;              \
+    }
+#define FB_SI_LD(ly, lx) ((ly) < PR ? sI[((ly) * IP + (lx)) * 2] : sI[(((ly) - HALF) * IP + (lx)) * 2 + 1])
+#else
+#define FB_SI_ST(ly, lx, v) sI[(ly) * IP + (lx)] = (v)
+#define FB_SI_LD(ly, lx) sI[(ly) * IP + (lx)]
+#endif
 
     // I positions of the tile + halo that lie inside the level image: lx in [lx_lo, lx_hi), ly in [ly_lo, ly_hi).
     // Positions outside are PolyExp's replicate border and are filled from these after phase B.
@@ -1132,7 +1161,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
                     rbp = rbp + g1 * (c[-1] + c[1]);
                     float acc = g0 * rb0;
                     acc = acc + g1 * (rbm + rbp);
-                    sI[ly * IP + lx] = acc;
+                    FB_SI_ST(ly, lx, acc);
                     rbm = rb0;
                     rb0 = rbp;
                 }
@@ -1156,7 +1185,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
                     float s01 = g0 * h1[1]; s01 = s01 + g1 * (h0[1] + h2[1]);
                     float s10 = g0 * h2[0]; s10 = s10 + g1 * (h1[0] + h3[0]);
                     float s11 = g0 * h2[1]; s11 = s11 + g1 * (h1[1] + h3[1]);
-                    sI[ly * IP + lx] = (s00 + s01 + s10 + s11) * 0.25f;
+                    FB_SI_ST(ly, lx, (s00 + s01 + s10 + s11) * 0.25f);
                     h0[0] = h2[0]; h0[1] = h2[1]; h1[0] = h3[0]; h1[1] = h3[1];
                     c += 2 * SW;
                 }
@@ -1170,11 +1199,116 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
             const int sy = nsof_clampi(ly, ly_lo, ly_hi - 1);
             for (int lx = lane; lx < IW; lx += NSOF_WARP) {
                 const int sx = nsof_clampi(lx, lx_lo, lx_hi - 1);
-                if (sx != lx || sy != ly) sI[ly * IP + lx] = sI[sy * IP + sx];
+                if (sx != lx || sy != ly) FB_SI_ST(ly, lx, FB_SI_LD(sy, sx));
             }
         }
         NSOF_SYNC();
     }
+#if FB_PP_PACKED
+    // ---- C (packed): vertical moments of rows y and y + HALF at once, one thread per (column, strip of 4 row pairs)
+    {
+        constexpr int STRIP = 4, NS = HALF / STRIP, PLANE = HALF * IP * 2;
+        const float2 mone = make_float2(-1.f, -1.f);
+        for (int i = NSOF_TID; i < IW * NS; i += NSOF_NT) {
+            const int lx = i % IW, st = i / IW;
+            float2 col[STRIP + 2 * N];
+#pragma unroll
+            for (int j = 0; j < STRIP + 2 * N; j++) col[j] = *(const float2 *)(sI + ((st * STRIP + j) * IP + lx) * 2);
+#pragma unroll
+            for (int y = 0; y < STRIP; y++) {
+                float2 r0 = nsof_mul2(col[y + N], pc.g2[0]), r1 = make_float2(0.f, 0.f), r2 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float2 a = col[y + N - k], b = col[y + N + k];
+                    const float2 p = nsof_add2(a, b), d = nsof_fma2(a, mone, b);  // b - a, one rounding
+                    r0 = nsof_fma2(pc.g2[k], p, r0);
+                    r1 = nsof_fma2(pc.xg2[k], d, r1);
+                    r2 = nsof_fma2(pc.xxg2[k], p, r2);
+                }
+                const int o = ((st * STRIP + y) * IP + lx) * 2;
+                *(float2 *)(sr + o) = r0;
+                *(float2 *)(sr + PLANE + o) = r1;
+                *(float2 *)(sr + 2 * PLANE + o) = r2;
+            }
+        }
+    }
+    NSOF_SYNC();
+    // ---- D (packed): horizontal pass, 2 columns x (row y, row y + HALF) per thread, one moment plane at a time (the
+    // window of a plane is 2 + 2N float2 registers); the five outputs are finished in scalar arithmetic so that they
+    // land in consecutive registers for the 8-byte stores
+    {
+        constexpr int CP = TW / 2, NQ = 2 + 2 * N, PLANE = HALF * IP * 2;
+        static_assert(NQ % 2 == 0, "window loads are float4 = two float2");
+        const float2 mone = make_float2(-1.f, -1.f);
+        for (int i = NSOF_TID; i < CP * HALF; i += NSOF_NT) {
+            const int lx = (i % CP) * 2, ly = i / CP;
+            const int x = tx0 + lx, ya = ty0 + ly, yb = ya + HALF;
+            if (x >= J.w || ya >= J.y_hi) continue;
+            float2 q[NQ], b1[2], b2[2], b3[2], b4[2], b5[2], b6[2];
+#define FB_PP_LOADQ(p)                                                                        \
+    {                                                                                         \
+        const float4 *s4 = (const float4 *)(sr + (p) * PLANE + (ly * IP + lx) * 2);           \
+        _Pragma("unroll") for (int k = 0; k < NQ / 2; k++) {                                  \
+            const float4 t = s4[k];                                                           \
+            q[2 * k] = make_float2(t.x, t.y);                                                 \
+            q[2 * k + 1] = make_float2(t.z, t.w);                                             \
+        }                                                                                     \
+    }
+            FB_PP_LOADQ(0);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int ctr = e + N;
+                b1[e] = nsof_mul2(q[ctr], pc.g2[0]);
+                b2[e] = make_float2(0.f, 0.f);
+                b4[e] = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float2 tg = nsof_add2(q[ctr + k], q[ctr - k]), d = nsof_fma2(q[ctr - k], mone, q[ctr + k]);
+                    b1[e] = nsof_fma2(tg, pc.g2[k], b1[e]);
+                    b4[e] = nsof_fma2(tg, pc.xxg2[k], b4[e]);
+                    b2[e] = nsof_fma2(d, pc.xg2[k], b2[e]);
+                }
+            }
+            FB_PP_LOADQ(1);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int ctr = e + N;
+                b3[e] = nsof_mul2(q[ctr], pc.g2[0]);
+                b6[e] = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    b3[e] = nsof_fma2(nsof_add2(q[ctr + k], q[ctr - k]), pc.g2[k], b3[e]);
+                    b6[e] = nsof_fma2(nsof_fma2(q[ctr - k], mone, q[ctr + k]), pc.xg2[k], b6[e]);
+                }
+            }
+            FB_PP_LOADQ(2);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int ctr = e + N;
+                b5[e] = nsof_mul2(q[ctr], pc.g2[0]);
+#pragma unroll
+                for (int k = 1; k <= N; k++) b5[e] = nsof_fma2(nsof_add2(q[ctr + k], q[ctr - k]), pc.g2[k], b5[e]);
+            }
+#undef FB_PP_LOADQ
+            {
+                const size_t o = (size_t)ya * J.pitch + x;
+                *(float2 *)(R + o) = make_float2(b3[0].x * pc.ig11, b3[1].x * pc.ig11);
+                *(float2 *)(R + plane + o) = make_float2(b2[0].x * pc.ig11, b2[1].x * pc.ig11);
+                *(float2 *)(R + 2 * plane + o) = make_float2(b1[0].x * pc.ig03 + b5[0].x * pc.ig33, b1[1].x * pc.ig03 + b5[1].x * pc.ig33);
+                *(float2 *)(R + 3 * plane + o) = make_float2(b1[0].x * pc.ig03 + b4[0].x * pc.ig33, b1[1].x * pc.ig03 + b4[1].x * pc.ig33);
+                *(float2 *)(R + 4 * plane + o) = make_float2(b6[0].x * pc.ig55, b6[1].x * pc.ig55);
+            }
+            if (yb < J.y_hi) {
+                const size_t o = (size_t)yb * J.pitch + x;
+                *(float2 *)(R + o) = make_float2(b3[0].y * pc.ig11, b3[1].y * pc.ig11);
+                *(float2 *)(R + plane + o) = make_float2(b2[0].y * pc.ig11, b2[1].y * pc.ig11);
+                *(float2 *)(R + 2 * plane + o) = make_float2(b1[0].y * pc.ig03 + b5[0].y * pc.ig33, b1[1].y * pc.ig03 + b5[1].y * pc.ig33);
+                *(float2 *)(R + 3 * plane + o) = make_float2(b1[0].y * pc.ig03 + b4[0].y * pc.ig33, b1[1].y * pc.ig03 + b4[1].y * pc.ig33);
+                *(float2 *)(R + 4 * plane + o) = make_float2(b6[0].y * pc.ig55, b6[1].y * pc.ig55);
+            }
+        }
+    }
+#else
     // ---- C: vertical moments, one thread per (column, strip of 8 rows), the column window kept in registers
     {
         constexpr int STRIP = FB_PP_STRIP, NS = TH / STRIP;
@@ -1252,6 +1386,9 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
             *(float4 *)(R + 4 * plane + o) = make_float4(o4[0], o4[1], o4[2], o4[3]);
         }
     }
+#endif
+#undef FB_SI_ST
+#undef FB_SI_LD
 }
 
 #define FB_PP_TW 64
@@ -1263,7 +1400,12 @@ static inline size_t fb_pp_smem(int mode)
 {
     const int IW = FB_PP_TW + 2 * FB_PP_N, IH = FB_PP_TH + 2 * FB_PP_N, IP = (IW + 3) & ~3;
     const int SWN = (mode ? 2 * IW : IW) + 2, SHN = (mode ? 2 * IH : IH) + 2, SW = (SWN + 3) & ~3, RP = (SWN + 32 + 15) & ~15;
-    const int a = std::max(3 * FB_PP_TH * IP * 4, SHN * SW * 4), b = std::max(IH * IP * 4, SHN * RP);
+#if FB_PP_PACKED
+    const int si_bytes = (IH - FB_PP_TH / 2) * IP * 8;
+#else
+    const int si_bytes = IH * IP * 4;
+#endif
+    const int a = std::max(3 * FB_PP_TH * IP * 4, SHN * SW * 4), b = std::max(si_bytes, SHN * RP);
     return 16 + (size_t)a + (size_t)b;
 }
 
