@@ -1001,6 +1001,14 @@ static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int,
 // grid (tiles, items, 2 images); items whose FbJob.fast != MODE + 1 exit (they take the generic kernels).
 // static smem: max(3*TH*IP*4, SH*SW) + IH*IP*4 bytes  (IP = roundup4(TW+2N)).
 // ---------------------------------------------------------------------------------------------
+// FB_PP_PACKED = 1 builds the moment passes (phases C / D) in packed FP32 on row pairs.  Measured on B200 (round 2,
+// profiles/r2_pyr_polyexp_packed_ab.txt): 25 % fewer executed instructions (FFMA2 takes its tap pairs straight from
+// uniform registers, no MOVs) and 6 % MORE time (full-frame level 0: 35.6 vs 33.6 us per pair) -- the kernel is bound by
+// its block barriers (stall `barrier` 4.1 cycles per issue: the wait for the bulk copy and the phase imbalance), not by
+// issue slots or the FMA pipe, and the plane-at-a-time horizontal pass has less memory-level parallelism.  Off.
+#ifndef FB_PP_PACKED
+#define FB_PP_PACKED 0
+#endif
 template <int MODE, int N, int TW, int TH>
 // 4 CTAs per SM (64 registers, no spill) hide the block barriers between the phases better than 3 (76 registers):
 // 2.89 -> 2.60 ms per full-frame step; 5 and 6 CTAs (48 / 40 registers, spilling) measured 2.71 / 2.58 ms
@@ -1015,9 +1023,6 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
     constexpr int SW = (SWN + 3) & ~3;                                              // pitch of the float window
     constexpr int RP = (SWN + 32 + 15) & ~15;                                       // pitch of the raw uint8 window
     constexpr int A_BYTES = (3 * TH * IP * 4 > SHN * SW * 4 ? 3 * TH * IP * 4 : SHN * SW * 4);  // S (float) | sr
-#ifndef FB_PP_PACKED
-#define FB_PP_PACKED 1
-#endif
 #if FB_PP_PACKED
     // Packed FP32 (FADD2 / FMUL2 / FFMA2) for the two moment passes: tile rows y and y + TH/2 travel in the two halves of
     // every operand.  For the halves to be an aligned register pair after a plain shared-memory load, I and the three
