@@ -363,6 +363,72 @@ def gpu_arm(args):
     return finish(args, locals())
 
 
+def tiled_8k_leg(args, rank, world, local, dev, barrier, steps=20, pairs=8, halo=32):
+    """extras["tiled_8k"]: BASELINE.json configs[4] -- synthetic 8K (7680 x 4320) frame pairs, each split by rows over
+    ALL ranks (strong scaling), the level loop in one library call per batch with the halo rows stored straight into
+    the row neighbours' workspaces over NVLink peer memory (tiled.TiledFarneback.run_linked).  Before timing, rank
+    0 runs the same pairs untiled on its own GPU and every rank compares its band bit for bit."""
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+    nsof = importlib.import_module("nsof_b200")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    tiled = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.tiled")
+    H8, W8 = 4320, 7680
+    P = nsof.FARNEBACK_PARAMS
+    eng = nsof.Engine(local)
+    frames = syn.make_clip(999, H8, W8, pairs + 1, dev, velocity=(6.0, -3.0))   # the same frames on every rank
+    flow = torch.zeros((pairs, H8, W8, 2), dtype=torch.float32, device=dev)
+    crops = lambda out: [(frames[t].data_ptr(), frames[t + 1].data_ptr(), H8, W8, W8, W8, out[t].data_ptr(), W8 * 8)
+                         for t in range(min(pairs, out.shape[0]))]
+    tf = tiled.TiledFarneback(eng, rank, world, halo_r1=halo)
+    tf.run_linked(crops(flow), **P)
+    torch.cuda.synchronize()
+    # bit-identity of every rank's band against an untiled run (two pairs are enough to hold 8K workspaces twice)
+    lo, hi = tiled.band_rows(H8, rank, world)
+    ref_eng = nsof.Engine(local)
+    ref = torch.empty((2, H8, W8, 2), dtype=torch.float32, device=dev)
+    ref_eng.farneback_batch_device(crops(ref), torch.cuda.current_stream().cuda_stream, **P)
+    torch.cuda.synchronize()
+    ok = torch.tensor([int(torch.equal(flow[:2, lo:hi], ref[:, lo:hi]))], device=dev)
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    ref_eng.close()
+    del ref
+    torch.cuda.empty_cache()
+    for _ in range(2):
+        tf.run_linked(crops(flow), check_guard=False, **P)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = eng.launch_count()
+    e0.record()
+    for _ in range(steps):
+        tf.run_linked(crops(flow), check_guard=False, **P)
+    e1.record()
+    barrier()
+    launches = eng.launch_count() - l0
+    tf._check_guard()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms.item()) / steps
+    bytes_pair = eng.algorithmic_bytes(H8, W8)
+    peak, _ = measured_peak()
+    out = {"metric": "tiled_farneback_frame_pairs_per_sec_8k", "value": pairs / (ms_step * 1e-3), "unit": UNIT,
+           "n_gpus": world, "scaling": "strong", "steps": steps, "ms_per_step": ms_step, "pairs_per_step": pairs,
+           "frame": [H8, W8], "halo_r1": halo, "bands_bit_identical_to_untiled": bool(ok.item()),
+           "launches_per_step": launches // steps,
+           "algorithmic_GBps_per_gpu": pairs * bytes_pair / world / (ms_step * 1e-3) / 1e9,
+           "frac_of_hbm_peak_per_gpu": pairs * bytes_pair / world / (ms_step * 1e-3) / 1e9 / peak,
+           "exchange": "one store-to-peer kernel + one flag-wait kernel per stage (NVLink peer memory, CUDA IPC); no NCCL "
+                       "on the data path, one host call per batch" if world > 1 else "none (one GPU)"}
+    eng.close()
+    del frames, flow
+    torch.cuda.empty_cache()
+    return out
+
+
 # kernel class (nsof_profile rows) -> __global__ function
 KERNEL_FUNCTION = {"fb_blur_um": "k_fb_blur_solve_t", "fb_blur_flow": "k_fb_blur_solve_t",
                    "fb_pyr_polyexp": "k_fb_pyr_polyexp_t", "fb_um_first": "k_fb_um_first", "fb_pyr": "k_fb_pyr_sep",
@@ -461,6 +527,14 @@ def finish(args, L):
                                 "frac_of_peak": n_ff * bytes_pair / (ms_ff * 1e-3) / 1e9 / peak,
                                 "pairs_per_step_per_gpu": pf.n_pairs}
         extras["full_frame"]["kernels"] = kernel_tables(lambda: pf.step(ff_frames))[0]
+    if not args.no_extras:
+        for sl in pipe.slots:   # release the device-resident pipelines before the 8K workspaces are built
+            for e in [sl.eng, sl.s1_eng] + [e for e, _ in sl.s2_extra]:
+                e.close()
+        del pf
+        torch.cuda.empty_cache()
+        note("tiled 8K leg")
+        extras["tiled_8k"] = tiled_8k_leg(args, rank, world, L["local"], dev, L["barrier"])
     if rank != 0:
         return 0
     line = {"metric": METRIC, "value": L["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,

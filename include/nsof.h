@@ -164,6 +164,24 @@ NSOF_API int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what, 
  * a larger halo_r1).  Synchronises the stream. */
 NSOF_API int nsof_fb_tiled_guard(nsof_handle *h, int *tripped, void *cuda_stream);
 
+/* ---- the same row tiling over PEER MEMORY (NVLink), the whole level loop in one host call -----------------------
+ * Every rank plans the whole frame from the same descriptors, so a row of any workspace buffer has the same offset
+ * from the workspace base on every rank.  After nsof_fb_tiled_begin a rank exports its workspace and its flag buffer
+ * (nsof_fb_tiled_link_export: CUDA IPC handles for ranks in other processes, raw addresses for ranks in this one),
+ * the driver hands every rank its row neighbours' exports (nsof_fb_tiled_link_attach), and nsof_fb_tiled_run
+ * enqueues every stage of the batch with, after each, ONE kernel that stores the band's edge rows straight into
+ * the neighbours' halo rows and raises their flags to the exchange's sequence number, and a one-thread kernel
+ * that waits for this rank's own two flags.  No message buffers, no pack / unpack kernels, no library collective and
+ * no host round trip between stages.  Ranks must sit on different devices (a waiting kernel and the kernel it waits
+ * for cannot share a GPU).  Re-export and re-attach when `arena_bytes` changes (a larger batch re-allocated the
+ * workspace).  `first_seq`: the running exchange count, identical on every rank (start at 0, pass *next_seq on). */
+NSOF_API int nsof_fb_tiled_link_export(nsof_handle *h, void *arena_ipc64, void *flags_ipc64, void **arena_ptr,
+                                       void **flags_ptr, size_t *arena_bytes);
+NSOF_API int nsof_fb_tiled_link_attach(nsof_handle *h, const void *up_arena, const void *up_flags, const void *dn_arena,
+                                       const void *dn_flags, int use_ipc);
+NSOF_API int nsof_fb_tiled_run(nsof_handle *h, int halo_flow, unsigned long long first_seq, unsigned long long *next_seq,
+                               void *cuda_stream);
+
 /* Device-to-device copy of `n` byte blocks in ONE launch (halo rows <-> contiguous message buffers of the tiled
  * path: one NCCL message per neighbour instead of one per plane and pair). */
 typedef struct nsof_copy_block {

@@ -114,6 +114,10 @@ _SIGNATURES = {
     "nsof_fb_tiled_stage_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "nsof_fb_tiled_query": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _P(TiledBuf)]),
     "nsof_fb_tiled_guard": (C.c_int, [C.c_void_p, _P(C.c_int), C.c_void_p]),
+    "nsof_fb_tiled_link_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _P(C.c_void_p), _P(C.c_void_p),
+                                            _P(C.c_size_t)]),
+    "nsof_fb_tiled_link_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "nsof_fb_tiled_run": (C.c_int, [C.c_void_p, C.c_int, C.c_ulonglong, _P(C.c_ulonglong), C.c_void_p]),
     "nsof_copy_blocks": (C.c_int, [C.c_void_p, _P(CopyBlock), C.c_int, C.c_void_p]),
     "nsof_copy_blocks_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_double, C.c_void_p]),
     "nsof_flow_segment_batch": (C.c_int, [C.c_void_p, _P(SegDesc), C.c_int, _P(SegParams), C.c_void_p]),

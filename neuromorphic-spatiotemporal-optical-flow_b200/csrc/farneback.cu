@@ -96,6 +96,7 @@ struct FbItemPlan {
 };
 
 static void fb_ctx_free(nsof_handle *h);  // defined with FbBatchCtx
+static void fb_link_close(nsof_handle *h);  // defined with nsof_fb_tiled_run
 
 extern "C" int nsof_create(int device, nsof_handle **out)
 {
@@ -124,6 +125,9 @@ extern "C" int nsof_destroy(nsof_handle *h)
     cudaDeviceSynchronize();
     h->arena.release();
     h->tile_buf.release();
+    fb_link_close(h);
+    h->link_flags.release();
+    h->link_tab.release();
     h->tables.release();
     h->clear_tab.release();
     h->guard_buf.release();
@@ -1021,6 +1025,288 @@ extern "C" int nsof_fb_tiled_query(nsof_handle *h, int item, int level, int what
         break;
     default: NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_query: what=%d", what);
     }
+    return NSOF_OK;
+}
+
+// ---- row tiling over peer memory (NVLink): the whole level loop in ONE host call -------------------------------------
+// Every rank plans the whole frame with the same descriptors, so a row of any workspace buffer has the SAME offset
+// from the arena base on every rank.  With the row neighbours' arenas mapped into this process (CUDA IPC, or plain
+// pointers when the ranks are devices / threads of one process), an exchange is one kernel: k_fb_halo_push stores the
+// band's edge rows of all pairs and planes straight into the neighbour's halo rows at the same offsets and then
+// raises the neighbour's flag to the exchange's sequence number; the consumer's stream carries a one-thread kernel
+// (k_fb_halo_wait) that spins until BOTH of its own flags have reached that number.  No pack / unpack kernels, no
+// message buffers, no library collective, no host round trip between stages.  Producers never wait on consumers, and
+// every overwrite of a halo row is separated from its last reader by a flag wait (tiled_begin demands >= 1 iteration),
+// so ranks cannot deadlock or race however far one runs ahead.  The ranks MUST run on different devices (or, in the
+// emulator, different threads): a spinning kernel and the kernel it waits for cannot share one GPU.
+struct FbPushBlock {
+    void *dst;
+    const void *src;
+    size_t bytes;
+};
+
+NSOF_DEV void nsof_store_release_sys(unsigned long long *p, unsigned long long v)
+{
+#ifdef NSOF_EMU
+    __atomic_store_n(p, v, __ATOMIC_RELEASE);
+#else
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+#endif
+}
+NSOF_DEV unsigned long long nsof_load_acquire_sys(const unsigned long long *p)
+{
+#ifdef NSOF_EMU
+    return __atomic_load_n(p, __ATOMIC_ACQUIRE);
+#else
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+#endif
+}
+
+// grid (chunks, blocks).  `done` counts finished CTAs (local memory, reset by the last one); the last CTA publishes.
+NSOF_GLOBAL k_fb_halo_push(const FbPushBlock *NSOF_RESTRICT blocks, unsigned total_ctas, unsigned *done,
+                           unsigned long long *flag_up, unsigned long long *flag_dn, unsigned long long seq)
+{
+    const FbPushBlock B = blocks[NSOF_BY];
+    const size_t stride = (size_t)nsof_grid_x() * NSOF_NT;
+    const float4 *s4 = (const float4 *)B.src;   // rows of pitch-padded planes: 16-byte aligned multiples of 16 bytes
+    float4 *d4 = (float4 *)B.dst;
+    for (size_t i = (size_t)NSOF_BX * NSOF_NT + NSOF_TID; i < B.bytes / 16; i += stride) d4[i] = s4[i];
+#ifdef NSOF_EMU
+    if (++*done == total_ctas) {
+        *done = 0;
+        if (flag_up) nsof_store_release_sys(flag_up, seq);
+        if (flag_dn) nsof_store_release_sys(flag_dn, seq);
+    }
+#else
+    __threadfence_system();  // this thread's peer stores are performed system-wide before the CTA reports
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned prev = atomicAdd(done, 1u);
+        if (prev + 1 == total_ctas) {
+            *done = 0;
+            __threadfence_system();
+            if (flag_up) nsof_store_release_sys(flag_up, seq);
+            if (flag_dn) nsof_store_release_sys(flag_dn, seq);
+        }
+    }
+#endif
+}
+
+NSOF_GLOBAL k_fb_halo_wait(const unsigned long long *from_up, const unsigned long long *from_dn, unsigned long long seq)
+{
+    if (NSOF_TID != 0) return;
+    if (from_up) while (nsof_load_acquire_sys(from_up) < seq) { }
+    if (from_dn) while (nsof_load_acquire_sys(from_dn) < seq) { }
+}
+
+// flags buffer of a handle (peer-writable): [0] raised by the upper neighbour, [1] by the lower one, [2] CTA counter
+static int fb_link_flags(nsof_handle *h)
+{
+    if (h->link_flags.p) return NSOF_OK;
+    int rc = h->link_flags.ensure(256);
+    if (rc) return rc;
+    NSOF_CUDA_TRY(cudaMemset(h->link_flags.p, 0, 256));
+    return NSOF_OK;
+}
+
+static void fb_link_close(nsof_handle *h)
+{
+#ifndef NSOF_EMU
+    for (void *p : h->link_ipc) cudaIpcCloseMemHandle(p);
+#endif
+    h->link_ipc.clear();
+    h->link_up_arena = h->link_dn_arena = nullptr;
+    h->link_up_flags = h->link_dn_flags = nullptr;
+    h->link_arena_seen = nullptr;
+}
+
+// Export: 64-byte CUDA IPC handles of this rank's arena and flag buffer (call after nsof_fb_tiled_begin: the arena is
+// sized by the plan; `arena_bytes` lets the caller detect a re-allocation), plus their raw addresses for ranks that
+// share a process.
+extern "C" int nsof_fb_tiled_link_export(nsof_handle *h, void *arena_ipc64, void *flags_ipc64, void **arena_ptr, void **flags_ptr,
+                                         size_t *arena_bytes)
+{
+    if (!h || !h->ctx || !h->ctx->valid || !h->ctx->tiled) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_link_export: no tiled batch");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    int rc = fb_link_flags(h);
+    if (rc) return rc;
+#ifndef NSOF_EMU
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handles travel as 64 bytes");
+    if (arena_ipc64) NSOF_CUDA_TRY(cudaIpcGetMemHandle((cudaIpcMemHandle_t *)arena_ipc64, h->arena.p));
+    if (flags_ipc64) NSOF_CUDA_TRY(cudaIpcGetMemHandle((cudaIpcMemHandle_t *)flags_ipc64, h->link_flags.p));
+#else
+    if (arena_ipc64) memset(arena_ipc64, 0, 64);
+    if (flags_ipc64) memset(flags_ipc64, 0, 64);
+#endif
+    if (arena_ptr) *arena_ptr = h->arena.p;
+    if (flags_ptr) *flags_ptr = h->link_flags.p;
+    if (arena_bytes) *arena_bytes = h->arena.bytes;
+    return NSOF_OK;
+}
+
+// Attach the row neighbours.  use_ipc != 0: the four arguments are 64-byte IPC handles of OTHER processes (NULL = no
+// such neighbour) and are opened here; use_ipc == 0: they are device pointers valid in this process.
+extern "C" int nsof_fb_tiled_link_attach(nsof_handle *h, const void *up_arena, const void *up_flags, const void *dn_arena,
+                                         const void *dn_flags, int use_ipc)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_link_attach: NULL handle");
+    if ((up_arena == nullptr) != (up_flags == nullptr) || (dn_arena == nullptr) != (dn_flags == nullptr))
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_link_attach: a neighbour needs both its arena and its flags");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    int rc = fb_link_flags(h);
+    if (rc) return rc;
+    fb_link_close(h);
+    void *p[4] = {nullptr, nullptr, nullptr, nullptr};
+    const void *in[4] = {up_arena, up_flags, dn_arena, dn_flags};
+    for (int i = 0; i < 4; i++) {
+        if (!in[i]) continue;
+        if (use_ipc) {
+#ifndef NSOF_EMU
+            cudaIpcMemHandle_t hd;
+            memcpy(&hd, in[i], sizeof(hd));
+            NSOF_CUDA_TRY(cudaIpcOpenMemHandle(&p[i], hd, cudaIpcMemLazyEnablePeerAccess));
+            h->link_ipc.push_back(p[i]);
+#else
+            NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "fb_tiled_link_attach: no CUDA IPC in the emulator build");
+#endif
+        } else {
+            p[i] = const_cast<void *>(in[i]);
+        }
+    }
+    h->link_up_arena = (float *)p[0];
+    h->link_up_flags = (unsigned long long *)p[1];
+    h->link_dn_arena = (float *)p[2];
+    h->link_dn_flags = (unsigned long long *)p[3];
+    h->link_arena_seen = h->arena.p;
+    return NSOF_OK;
+}
+
+// Edge rows of buffer `what` (nsof_fb_tiled_query numbering) of level k, all items and planes, as push blocks
+static void fb_push_blocks(nsof_handle *h, int k, int what, int rows, std::vector<FbPushBlock> *out, size_t *biggest)
+{
+    FbBatchCtx &X = *h->ctx;
+    const std::vector<FbItemPlan> &plan = *h->last_plan;
+    float *base = (float *)h->arena.p;
+    for (int i = 0; i < X.n; i++) {
+        const FbItemPlan &pl = plan[i];
+        const size_t planef = (size_t)pl.pitch[k] * pl.hk[k];
+        size_t off, row_floats = pl.pitch[k], plane_floats = planef;
+        int planes = 5;
+        switch (what) {
+        case 0: off = pl.off_R[k] + 5 * planef; break;
+        case 1: off = pl.off_Ma; break;
+        case 2: off = pl.off_Mb; break;
+        default: off = (k & 1) ? pl.off_fA : pl.off_fB; planes = 1; row_floats = 2 * (size_t)pl.pitch[k]; plane_floats = row_floats * pl.hk[k]; break;
+        }
+        int y_lo, y_hi;
+        band_rows(pl.hk[k], X.tiling.rank, X.tiling.world, &y_lo, &y_hi);
+        const int r = std::min(rows, y_hi - y_lo);
+        const size_t bytes = (size_t)r * row_floats * sizeof(float);
+        if (!bytes) continue;
+        for (int c = 0; c < planes; c++) {
+            const size_t top = off + c * plane_floats + (size_t)y_lo * row_floats;
+            const size_t bot = off + c * plane_floats + (size_t)(y_hi - r) * row_floats;
+            if (h->link_up_arena) out->push_back({h->link_up_arena + top, base + top, bytes});
+            if (h->link_dn_arena) out->push_back({h->link_dn_arena + bot, base + bot, bytes});
+            *biggest = std::max(*biggest, bytes);
+        }
+    }
+}
+
+// The level loop of the batch planned by nsof_fb_tiled_begin, every stage followed by its halo push and flag wait.
+// `halo_flow` = rows of the coarser flow the bilinear upsampling reaches beyond the band (4).  Asynchronous on the
+// stream; check nsof_fb_tiled_guard afterwards.  `first_seq` = this batch's first exchange number: every rank passes
+// the same, strictly increasing value (the driver keeps the running count and gets the next one back).
+extern "C" int nsof_fb_tiled_run(nsof_handle *h, int halo_flow, unsigned long long first_seq, unsigned long long *next_seq,
+                                 void *cuda_stream)
+{
+    if (!h || !h->ctx || !h->ctx->valid || !h->ctx->tiled) NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_run: no tiled batch (call nsof_fb_tiled_begin)");
+    FbBatchCtx &X = *h->ctx;
+    const int world = X.tiling.world, rank = X.tiling.rank;
+    if (world > 1) {
+        if ((rank > 0 && !h->link_up_arena) || (rank < world - 1 && !h->link_dn_arena))
+            NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_run: row neighbours are not attached (nsof_fb_tiled_link_attach)");
+        if (h->link_arena_seen != h->arena.p)
+            NSOF_FAIL(NSOF_ERR_BAD_ARG, "fb_tiled_run: the workspace was re-allocated after the neighbours were attached; export and attach again");
+    }
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    int rc = fb_link_flags(h);
+    if (rc) return rc;
+    const int T = X.params.iterations, m = X.m;
+    // ---- push tables of every exchange of the batch, one upload
+    struct Ex { int k, what, rows; size_t first, count, biggest; };
+    std::vector<Ex> exs;
+    std::vector<FbPushBlock> blocks;
+    auto add = [&](int k, int what, int rows) {
+        Ex e = {k, what, rows, blocks.size(), 0, 0};
+        if (world > 1) fb_push_blocks(h, k, what, rows, &blocks, &e.biggest);
+        e.count = blocks.size() - e.first;
+        exs.push_back(e);
+    };
+    for (int k = X.max_scales - 1; k >= X.stop_level; k--) {
+        add(k, 0, X.tiling.halo_r1);
+        add(k, 1, m);
+        for (int it = 0; it < T; it++) {
+            if (it < T - 1) add(k, (it % 2 == 0) ? 2 : 1, m);
+            else add(k, 3, k > 0 ? halo_flow : 0);
+        }
+    }
+    const FbPushBlock *dblocks = nullptr;
+    if (!blocks.empty()) {
+        const size_t bytes = blocks.size() * sizeof(FbPushBlock);
+        NsofStageSlot *slot;
+        rc = nsof_stage_acquire(h, bytes, &slot);
+        if (rc) return rc;
+        rc = h->link_tab.ensure(bytes + 16);
+        if (rc) return rc;
+        memcpy(slot->host, blocks.data(), bytes);
+        rc = nsof_table_upload(h, h->link_tab.p, slot, bytes, stream);
+        if (rc) return rc;
+        dblocks = (const FbPushBlock *)h->link_tab.p;
+    }
+    unsigned long long *fl = (unsigned long long *)h->link_flags.p;
+    unsigned long long seq = first_seq;
+    size_t ei = 0;
+    auto exchange = [&]() -> int {
+        const Ex &e = exs[ei++];
+        seq++;
+        if (world == 1 || e.rows <= 0) return NSOF_OK;  // (a skipped exchange still consumes its number on every rank)
+        // peer flags: the UPPER neighbour's "raised by the lower one" slot [1], the LOWER neighbour's slot [0]
+        unsigned long long *f_up = h->link_up_arena ? h->link_up_flags + 1 : nullptr;
+        unsigned long long *f_dn = h->link_dn_arena ? h->link_dn_flags + 0 : nullptr;
+        if (e.count) {
+            double total = 0.;
+            for (size_t b = 0; b < e.count; b++) total += (double)blocks[e.first + b].bytes;
+            const int chunks = (int)std::min<size_t>(32, std::max<size_t>(1, e.biggest / (16 * 256 * 4)));
+            NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total, k_fb_halo_push, chunks, (int)e.count, 1, 256, 0, stream, dblocks + e.first,
+                         (unsigned)(chunks * e.count), (unsigned *)(fl + 2), f_up, f_dn, seq);
+        }
+        NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 0., k_fb_halo_wait, 1, 1, 1, 32, 0, stream,
+                     (const unsigned long long *)(h->link_up_arena ? fl + 0 : nullptr),
+                     (const unsigned long long *)(h->link_dn_arena ? fl + 1 : nullptr), seq);
+        NSOF_CUDA_TRY(cudaGetLastError());
+        return NSOF_OK;
+    };
+    for (int k = X.max_scales - 1; k >= X.stop_level; k--) {
+        rc = fb_launch_pyramid(h, k, stream);
+        if (rc) return rc;
+        rc = exchange();
+        if (rc) return rc;
+        rc = fb_launch_um_first(h, k, stream);
+        if (rc) return rc;
+        rc = exchange();
+        if (rc) return rc;
+        for (int it = 0; it < T; it++) {
+            rc = fb_launch_blur(h, k, it, T, stream);
+            if (rc) return rc;
+            rc = exchange();
+            if (rc) return rc;
+        }
+    }
+    if (next_seq) *next_seq = seq;
     return NSOF_OK;
 }
 

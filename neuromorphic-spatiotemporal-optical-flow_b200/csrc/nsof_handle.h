@@ -67,6 +67,13 @@ struct nsof_handle {
     NsofDevBuf arena;      // I, R, M, coarse flow of every item of the current batch
     NsofDevBuf tables;     // job tables + Gaussian taps on the device
     NsofDevBuf tile_buf;   // flat tile lists of the current batch (uint2 = item, tile), built by k_fb_build_tiles
+    // row tiling over peer memory (nsof_fb_tiled_link_* / nsof_fb_tiled_run)
+    NsofDevBuf link_flags;  // [0] raised by the upper neighbour, [1] by the lower one, [2] CTA counter of k_fb_halo_push
+    NsofDevBuf link_tab;    // push-block tables of the current batch
+    float *link_up_arena = nullptr, *link_dn_arena = nullptr;  // the neighbours' arenas, mapped here
+    unsigned long long *link_up_flags = nullptr, *link_dn_flags = nullptr;
+    void *link_arena_seen = nullptr;  // this rank's arena address when the neighbours were attached
+    std::vector<void *> link_ipc;     // IPC mappings to close
     NsofDevBuf clear_tab;  // rectangle table of nsof_flow_clear
     NsofDevBuf guard_buf;  // halo guard flag of a tiled batch
     FbBatchCtx *ctx = nullptr;  // plan, tables and launch geometry of the current batch

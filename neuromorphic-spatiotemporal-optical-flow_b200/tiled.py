@@ -23,6 +23,13 @@ single-GPU result: per-pixel arithmetic does not depend on the tile decompositio
 
 A displacement larger than `halo_r1` rows at some level would gather rows that were never received; the kernels
 flag that (nsof_fb_tiled_guard) and `run` raises instead of returning a wrong field.
+
+`run_linked` is the same decomposition over PEER MEMORY (NVLink): the row neighbours' workspaces are mapped into
+this process once (CUDA IPC handles exchanged through torch.distributed -- plumbing), and ONE library call
+(nsof_fb_tiled_run) enqueues the whole level loop; after every stage one kernel stores the band's edge rows straight
+into the neighbours' halo rows and raises their flags, and a one-thread kernel waits for this rank's own flags.  No
+message buffers, no pack / unpack kernels, no NCCL point-to-point operations, no host round trips between stages.
+`run` (NCCL / gloo messages) remains as the portable path and as the cross-check.
 """
 from __future__ import annotations
 
@@ -239,6 +246,71 @@ class TiledFarneback:
                 stage(k, 2, it, ex, split)
         wait_halo()
         return levels
+
+    # ---- the same over peer memory ---------------------------------------------------------------------------
+    def _link(self, peers=None):
+        """(Re-)attach the row neighbours when this rank's workspace is new.  `peers`: for ranks that share a process
+        (tests on the emulator, several GPUs driven by one process) a dict rank -> TiledFarneback; otherwise the IPC
+        handles travel through torch.distributed.all_gather_object."""
+        lib, h = self.lib, self.h
+        mine = (self._export[2], self._export[4])
+        if peers is not None:   # one process: raw addresses; every rank re-attaches when ANY workspace is new
+            key = tuple((r, peers[r]._export[2], peers[r]._export[3]) for r in sorted(peers))
+            if getattr(self, "_linked", None) == (mine, key):
+                return
+            up, dn = peers.get(self.rank - 1), peers.get(self.rank + 1)
+            lib.check(lib.nsof_fb_tiled_link_attach(h, up._export[2] if up else None, up._export[3] if up else None,
+                                                    dn._export[2] if dn else None, dn._export[3] if dn else None, 0),
+                      "fb_tiled_link_attach")
+            self._linked = (mine, key)
+            return
+        # several processes: has any rank a new workspace?  (cheap: one small object collective per run)
+        changed = [None] * self.world
+        self.dist.all_gather_object(changed, getattr(self, "_linked", None) != mine, group=self.group)
+        if not any(changed):
+            return
+        table = [None] * self.world
+        self.dist.all_gather_object(table, self._export[:2], group=self.group)
+        up = table[self.rank - 1] if self.rank > 0 else (None, None)
+        dn = table[self.rank + 1] if self.rank < self.world - 1 else (None, None)
+        buf = lambda b: (C.c_ubyte * 64).from_buffer_copy(b) if b is not None else None
+        lib.check(lib.nsof_fb_tiled_link_attach(h, buf(up[0]), buf(up[1]), buf(dn[0]), buf(dn[1]), 1), "fb_tiled_link_attach")
+        self._linked = mine
+
+    def begin_linked(self, crops, **farneback_params):
+        """Plan the batch (nsof_fb_tiled_begin) and export this rank's workspace; `run_linked` = begin + link + go."""
+        kw = dict(FARNEBACK_PARAMS)
+        kw.update(farneback_params)
+        fb = _fb_params(**kw)
+        n = len(crops)
+        descs = (CropDesc * max(n, 1))()
+        for i, c in enumerate(crops):
+            descs[i] = CropDesc(*c)
+        self.lib.check(self.lib.nsof_fb_tiled_begin(self.h, descs, n, C.byref(fb), self.rank, self.world, self.halo_r1,
+                                                    self._stream()), "fb_tiled_begin")
+        self._n, self._kw = n, kw
+        a_ipc, f_ipc = (C.c_ubyte * 64)(), (C.c_ubyte * 64)()
+        a_ptr, f_ptr, nbytes = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        self.lib.check(self.lib.nsof_fb_tiled_link_export(self.h, a_ipc, f_ipc, C.byref(a_ptr), C.byref(f_ptr),
+                                                          C.byref(nbytes)), "fb_tiled_link_export")
+        self._export = (bytes(a_ipc), bytes(f_ipc), a_ptr.value, f_ptr.value, int(nbytes.value))
+
+    def go_linked(self):
+        nxt = C.c_ulonglong(0)
+        self.lib.check(self.lib.nsof_fb_tiled_run(self.h, FLOW_HALO_ROWS, getattr(self, "_seq", 0), C.byref(nxt), self._stream()),
+                       "fb_tiled_run")
+        self._seq = int(nxt.value)
+
+    def run_linked(self, crops, check_guard: bool = True, **farneback_params):
+        """`run` over peer memory: same arguments, same (bit-identical) result, one library call for the level loop.
+        Every rank must call it with the same batch geometry, in the same order."""
+        self.begin_linked(crops, **farneback_params)
+        if self.world > 1:
+            self._link()
+        self.go_linked()
+        if check_guard:
+            self._check_guard()
+        return self.lib.nsof_fb_tiled_levels(self.h)
 
     def _check_guard(self):
         lib, h, st = self.lib, self.h, self._stream()

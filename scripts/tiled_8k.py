@@ -25,6 +25,7 @@ ap.add_argument("--width", type=int, default=7680)
 ap.add_argument("--halo", type=int, default=32)
 ap.add_argument("--check", action="store_true")
 ap.add_argument("--overlap", action="store_true", help="edges -> exchange on a second stream || interior (tiled.py)")
+ap.add_argument("--linked", action="store_true", help="peer-memory path: the level loop in one library call (run_linked)")
 args = ap.parse_args()
 
 nsof = importlib.import_module("nsof_b200")
@@ -51,7 +52,7 @@ if args.check:
     frames = syn.make_clip(4321, H, W, 3, dev, velocity=(5.0, -4.0))  # same seed on every rank: the same frames
     flow = torch.full((2, H, W, 2), float("nan"), dtype=torch.float32, device=dev)
     tfc = tiled.TiledFarneback(eng, rank, world, halo_r1=min(args.halo, (H // 8) // world), overlap=args.overlap)  # 135 coarsest rows
-    tfc.run(crops_of(frames, flow), **P)
+    (tfc.run_linked if args.linked else tfc.run)(crops_of(frames, flow), **P)
     torch.cuda.synchronize()
     lo, hi = tiled.band_rows(H, rank, world)
     ref = torch.empty((2, H, W, 2), dtype=torch.float32, device=dev)
@@ -81,7 +82,7 @@ def barrier():
     torch.cuda.synchronize()
 
 
-step = lambda: tf.run(crops, **P)
+step = (lambda: tf.run_linked(crops, check_guard=False, **P)) if args.linked else (lambda: tf.run(crops, **P))
 for _ in range(args.warmup):
     step()
 barrier()
@@ -101,7 +102,8 @@ if rank == 0:
                       "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "scaling": "strong",
                       "config": {"workload": "configs[4]: synthetic 8K frames, row-tiled over the ranks, NCCL halo rows",
                                  "frame": [H, W], "pairs_per_step": NP, "halo_r1": args.halo,
-                                 "schedule": "whole-band stages, blocking exchanges" if not args.overlap else
+                                 "schedule": "peer memory: store-to-neighbour + flag-wait kernels, one host call per batch" if args.linked else
+                                 "whole-band stages, blocking exchanges" if not args.overlap else
                                  f"edges -> exchange on a second stream || interior on {tf.split_levels} of the levels"},
                       "p2p_ops_per_step_rank0": tf.messages, "MB_sent_per_step_rank0": tf.bytes_sent / 1e6,
                       "algorithmic_GBps_whole_job": NP * bytes_pair / (ms_step * 1e-3) / 1e9}), flush=True)

@@ -29,6 +29,7 @@ static inline cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, s
     return cudaSuccess;
 }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t) { memset(d, v, n); return cudaSuccess; }
+static inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return cudaSuccess; }
 static inline cudaError_t cudaMemset2DAsync(void *d, size_t dp, int v, size_t wbytes, size_t rows, cudaStream_t)
 {
     for (size_t r = 0; r < rows; r++) memset((char *)d + r * dp, v, wbytes);

@@ -80,3 +80,54 @@ def test_tiled_guard_trips_when_the_halo_is_too_small(tmp_path):
     mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), 1), nprocs=2, join=True)
     for r in range(2):
         assert str(np.load(tmp_path / f"r{r}.npz")["status"]) == "guard"
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_tiled_peer_memory_run_reproduces_the_untiled_flow(emu_engine, nsof, world):
+    """nsof_fb_tiled_run (the level loop in one call; halo rows stored straight into the neighbour's workspace, flags
+    instead of messages) with the ranks as THREADS of this process over the emulator build: bands bit-identical to the
+    untiled flow, twice in a row (the exchange sequence numbers carry over between batches)."""
+    import threading
+    tiled = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.tiled")
+    lib = nsof.Library(helpers.build_emu())
+    pairs = _pairs()
+    engs = [nsof.Engine(0, lib=lib, _emulated=True) for _ in range(world)]
+    tfs = {r: tiled.TiledFarneback(engs[r], r, world, halo_r1=12) for r in range(world)}
+    flows = {r: [np.full((H, W, 2), np.nan, dtype=np.float32) for _ in pairs] for r in range(world)}
+    crops = {r: [(a.ctypes.data, b.ctypes.data, H, W, a.strides[0], b.strides[0], f.ctypes.data, f.strides[0])
+                 for (a, b), f in zip(pairs, flows[r])] for r in range(world)}
+    want = [emu_engine.calcOpticalFlowFarneback(a, b, None, **PARAMS) for a, b in pairs]
+    for rep in range(2):
+        for r in range(world):
+            for f in flows[r]:
+                f.fill(np.nan)
+            tfs[r].begin_linked(crops[r], **PARAMS)
+        for r in range(world):
+            tfs[r]._link(peers=tfs)
+        errs = []
+
+        def go(r):
+            try:
+                tfs[r].go_linked()
+            except Exception as e:  # pragma: no cover
+                errs.append((r, e))
+
+        th = [threading.Thread(target=go, args=(r,)) for r in range(world)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join(timeout=300)
+        assert not errs and not any(t.is_alive() for t in th), errs
+        for r in range(world):
+            lo, hi = tiled.band_rows(H, r, world)
+            tripped = __import__("ctypes").c_int(0)
+            lib.check(lib.nsof_fb_tiled_guard(engs[r].handle, __import__("ctypes").byref(tripped), None))
+            assert tripped.value == 0
+            for i, wnt in enumerate(want):
+                assert np.array_equal(flows[r][i][lo:hi], wnt[lo:hi]), (rep, r, i)
+                outside = np.ones(H, bool)
+                outside[lo:hi] = False
+                assert np.isnan(flows[r][i][outside]).all()
+    assert tfs[0]._seq == tfs[world - 1]._seq > 0
+    for e in engs:
+        e.close()
