@@ -944,13 +944,17 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             const int lx = va ? lxa : lxb, ly = va ? lya : lyb, x = va ? xa : xb, y = va ? ya : yb;
             const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
             const size_t o = (size_t)y * J.pitch + x;
-            float r0v[5], mm[5];
+            // a pixel without a partner goes through the SAME packed routine (both halves = this pixel): which pixels
+            // lose their partner depends on where the tiles start, and the scalar routine's compiler-chosen FMA
+            // contraction differs from the packed one in the last bit -- a row-tiled run (tiles start at the band's
+            // first row) must reproduce the untiled flow bit for bit
+            float2 r0v[5], mm[5];
 #pragma unroll
-            for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(R0 + c * plane + o);
+            for (int c = 0; c < 5; c++) { const float t = NSOF_LDG(R0 + c * plane + o); r0v[c] = make_float2(t, t); }
             if (J.guard) fb_um_guard(J, y, f.y);
-            fb_um_pixel(R1, plane, J.pitch, J.h, J.w, x, y, f.x, f.y, r0v, mm);
+            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, x, y, x, y, make_float2(f.x, f.x), make_float2(f.y, f.y), r0v, mm);
 #pragma unroll
-            for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c];
+            for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c].x;
         }
     }
 #else

@@ -767,3 +767,70 @@ def test_event_scheme2_vs_reference(gpu_engine, golden):
             assert got.dtype == np.float32 and got.shape == want.shape
             assert np.array_equal(got == 0, want == 0) and np.array_equal(got == 1, want == 1), name
             assert np.abs(got - want).max() <= 2e-5, (name, np.abs(got - want).max())
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_tiled_lockstep_ranks_bit_identical_on_one_gpu(gpu_engine, nsof, world):
+    """Row tiling (configs[4]) on ONE GPU: the ranks are handles of this process stepped in lockstep, stage by stage,
+    with the halo rows copied between their workspaces by plain device copies (no waiting kernels, no NCCL).  Every
+    band must equal the untiled flow BIT FOR BIT: the per-pixel arithmetic may not depend on where the tiles start
+    (an unpaired pixel of the packed UpdateMatrices once took the scalar routine and differed in the last bit)."""
+    import importlib
+
+    import torch
+    tiled = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.tiled")
+    eng_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.engine")
+    syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+    P = nsof.FARNEBACK_PARAMS
+    H, W = 1080, 1000
+    dev = torch.device("cuda:0")
+    frames = syn.make_clip(4321, H, W, 3, dev, velocity=(5.0, -4.0))
+    st = torch.cuda.current_stream().cuda_stream
+    crops_of = lambda flow: [(frames[t].data_ptr(), frames[t + 1].data_ptr(), H, W, W, W, flow[t].data_ptr(), W * 8) for t in range(2)]
+    ref = torch.empty((2, H, W, 2), dtype=torch.float32, device=dev)
+    gpu_engine.farneback_batch_device(crops_of(ref), st, **P)
+    engs = [nsof.Engine(0) for _ in range(world)]
+    tfs = [tiled.TiledFarneback(engs[r], r, world, halo_r1=min(32, (H // 8) // world)) for r in range(world)]
+    flows = [torch.full((2, H, W, 2), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
+    lib, fb = engs[0].lib, eng_mod._fb_params(**P)
+    for r in range(world):
+        descs = (tiled.CropDesc * 2)(*[tiled.CropDesc(*c) for c in crops_of(flows[r])])
+        lib.check(lib.nsof_fb_tiled_begin(engs[r].handle, descs, 2, C.byref(fb), r, world, tfs[r].halo_r1, C.c_void_p(st)))
+    levels, m, T = lib.nsof_fb_tiled_levels(engs[0].handle), P["winsize"] // 2, P["iterations"]
+
+    def exchange(level, what, rows):
+        for r in range(world):
+            for item in range(2):
+                b = tfs[r]._query(item, level, what)
+                rr = min(rows, b.y_hi - b.y_lo)
+                for nb, y_src in ((r - 1, b.y_lo), (r + 1, b.y_hi - rr)):
+                    if 0 <= nb < world:
+                        q = tfs[nb]._query(item, level, what)
+                        for p in range(b.planes):
+                            n = rr * b.row_floats
+                            tfs[nb]._tensor(q.ptr + 4 * (p * q.plane_floats + y_src * q.row_floats), n).copy_(
+                                tfs[r]._tensor(b.ptr + 4 * (p * b.plane_floats + y_src * b.row_floats), n))
+
+    def stage(k, s, it):
+        for r in range(world):
+            lib.check(lib.nsof_fb_tiled_stage(engs[r].handle, k, s, it, C.c_void_p(st)))
+
+    for k in range(levels - 1, -1, -1):
+        stage(k, 0, 0); exchange(k, 0, tfs[0].halo_r1)
+        stage(k, 1, 0); exchange(k, 1, m)
+        for it in range(T):
+            stage(k, 2, it)
+            if it < T - 1:
+                exchange(k, 2 if it % 2 == 0 else 1, m)
+            elif k > 0:
+                exchange(k, 3, 4)
+    torch.cuda.synchronize()
+    for r in range(world):
+        lo, hi = tiled.band_rows(H, r, world)
+        assert torch.equal(flows[r][:, lo:hi], ref[:, lo:hi]), (world, r)
+        assert bool(torch.isnan(flows[r][:, :lo]).all() and torch.isnan(flows[r][:, hi:]).all())
+        tripped = C.c_int(0)
+        lib.check(lib.nsof_fb_tiled_guard(engs[r].handle, C.byref(tripped), C.c_void_p(st)))
+        assert tripped.value == 0
+    for e in engs:
+        e.close()
