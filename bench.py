@@ -352,8 +352,39 @@ def gpu_arm(args):
     ms_e2e = timed_host(args.steps, 3)
     clocks = clk.stop() if rank == 0 else None  # sampled every 20 ms across both timed regions (value and e2e)
     s0 = hp.slots[0]
+
+    def copy_floor(steps):
+        """The same bytes over the same pinned buffers and copy streams with NO kernels: what the host<->device path of
+        this box allows for the e2e leg (all ranks copy at once, as in the leg itself)."""
+        lib, fsz = eng.lib, H * W
+        px = s0.pipe.last_crop_pixels
+        n_ch = len(s0.pipe.chunks)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            for j, (p0, p1) in enumerate(s0.pipe.chunks):
+                f0 = 0 if j == 0 else p0 + 1
+                for c in range(Cn):
+                    lib.check(lib.nsof_copy_2d_async(s0.frames.data_ptr() + (f0 * Cn + c) * fsz, Cn * fsz,
+                                                     clips_host[c].data_ptr() + f0 * fsz, fsz, fsz, p1 + 1 - f0, 1,
+                                                     s0._ptr(s0.s_in)), "copy floor H2D")
+                a, b = 2 * px * j // n_ch, 2 * px * (j + 1) // n_ch
+                with torch.cuda.stream(s0.s_out):
+                    s0.flow_host[a:b].copy_(s0.pipe.packed[a:b], non_blocking=True)
+        torch.cuda.synchronize()
+        ms_ = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+        barrier()
+        if world > 1:
+            dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
+        return float(ms_.item()) / steps
+
+    copy_floor(2)
+    floor_ms = copy_floor(max(5, args.steps // 2))
     e2e = {"value": pairs_step * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": int(hp.h2d_bytes), "d2h_bytes_per_step": int(hp.d2h_bytes),
+           "ms_per_step": ms_e2e / args.steps, "copy_floor_ms_per_step": floor_ms,
+           "copy_floor_GBps_per_gpu": (hp.h2d_bytes + hp.d2h_bytes) / (floor_ms * 1e-3) / 1e9,
+           "frac_of_copy_floor": floor_ms / (ms_e2e / args.steps),
            "api": "HostStream.submit/drain (pinned uint8 clips -> rectangles + packed float32 ROI flow on the host), "
                   f"{len(hp.slots)} steps in flight, each on {len(s0.slots)} streams (H2D / stage 1 / stage 2 / D2H) "
                   f"in {len(s0.pipe.chunks)} time chunks; all {args.steps} steps submitted and drained inside the "
@@ -361,6 +392,64 @@ def gpu_arm(args):
     del hp
     note(f"e2e leg done: {ms_e2e / args.steps:.3f} ms per step; per-kernel leg")
     return finish(args, locals())
+
+
+def dropin_call_leg(eng):
+    """extras["dropin_call"]: what a maintainer gets after the two-line edit of INTEGRATION.md -- the synchronous
+    per-pair call `calcOpticalFlowFarneback(prev, next, None, **farneback_params)` on numpy arrays (pageable host
+    memory in, a fresh numpy flow out), median of 15 calls, beside cv2's own time on the same arrays."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers
+    nsof = __import__("nsof_b200")
+    try:
+        import cv2
+    except Exception:
+        cv2 = None
+    out = {}
+    for name, (h, w) in (("crop_600x600", (600, 600)), ("frame_1080x1920", (1080, 1920))):
+        a, b = helpers.textured_pair(5, h, w)
+        ts = []
+        for _ in range(18):
+            t0 = time.perf_counter()
+            f = eng.calcOpticalFlowFarneback(a, b, None, **nsof.FARNEBACK_PARAMS)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        row = {"nsof_ms_median": float(np.median(ts[3:])), "nsof_ms_min": float(min(ts[3:]))}
+        if cv2 is not None:
+            tc = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                g = cv2.calcOpticalFlowFarneback(a, b, None, **nsof.FARNEBACK_PARAMS)
+                tc.append((time.perf_counter() - t0) * 1e3)
+            d = np.sqrt(((f.astype(np.float64) - g) ** 2).sum(-1))
+            row.update(cv2_ms_median=float(np.median(tc)), speedup=float(np.median(tc) / row["nsof_ms_median"]),
+                       epe_mean=float(d.mean()), epe_max=float(d.max()))
+        out[name] = row
+    return out
+
+
+def param_sets_leg(eng, frames, timed):
+    """extras["param_sets"]: full-frame 1080p pairs/s and fraction of the HBM peak for the two OTHER parameter sets the
+    reference ships (optical_flow_seg.py:61-112, data/*/Parameters.txt): they run on the generic kernels."""
+    import importlib
+    nsof = importlib.import_module("nsof_b200")
+    pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    peak, _ = measured_peak()
+    out = {}
+    F = 9
+    fr = frames[:F, :1].contiguous()
+    for name, p in (("autodriving_txt", dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3, poly_n=10, poly_sigma=1.05, flags=0)),
+                    ("tabletennis", dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2, poly_n=1, poly_sigma=1.05, flags=0))):
+        cfg = nsof.RoiConfig(farneback_params=p)
+        pf = pipe_mod.SequencePipeline(eng, 1, F, H, W, cfg, full_frame=True)
+        ms, _ = timed(lambda: pf.step(fr), 5, 2)
+        pairs = 5 * pf.n_pairs
+        bytes_pair = eng.algorithmic_bytes(H, W, **p)
+        out[name] = {"params": list(p.values()), "value": pairs / (ms * 1e-3), "unit": UNIT,
+                     "algorithmic_MB_per_pair": bytes_pair / 1e6,
+                     "frac_of_peak": pairs * bytes_pair / (ms * 1e-3) / 1e9 / peak}
+        del pf
+    return out
 
 
 def tiled_8k_leg(args, rank, world, local, dev, barrier, steps=20, pairs=8, halo=32):
@@ -528,6 +617,10 @@ def finish(args, L):
                                 "pairs_per_step_per_gpu": pf.n_pairs}
         extras["full_frame"]["kernels"] = kernel_tables(lambda: pf.step(ff_frames))[0]
     if not args.no_extras:
+        if rank == 0 and world == 1:
+            note("drop-in call and parameter-set legs")
+            extras["dropin_call"] = dropin_call_leg(eng)
+            extras["param_sets"] = param_sets_leg(eng, frames, timed)
         for sl in pipe.slots:   # release the device-resident pipelines before the 8K workspaces are built
             for e in [sl.eng, sl.s1_eng] + [e for e, _ in sl.s2_extra]:
                 e.close()
