@@ -195,6 +195,17 @@ NSOF_API int nsof_copy_blocks(nsof_handle *h, const nsof_copy_block *blocks, int
 NSOF_API int nsof_copy_blocks_resident(nsof_handle *h, const nsof_copy_block *device_blocks, int n, size_t biggest_block,
                                        double total_bytes, void *cuda_stream);
 
+/* ---- SSIM of the prediction task (optical_flow_prediction.py:113-115) --------------------
+ * skimage.metrics.structural_similarity(a, b, data_range=...) with its defaults for 2-D uint8 images: 7 x 7 uniform
+ * window, sample covariance, K1 = 0.01, K2 = 0.03, mean over the image cropped by 3 pixels.  `*_pixel_stride` = bytes
+ * between pixels (3 selects one channel of an interleaved BGR frame, as the script's `[:, :, 2]` does).  The score is a
+ * float64 written to DEVICE memory (`_host`: to host memory, synchronous). */
+NSOF_API int nsof_ssim_u8(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                          ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out_dev,
+                          void *cuda_stream);
+NSOF_API int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                               ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out);
+
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
 NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,

@@ -131,6 +131,10 @@ _SIGNATURES = {
     "nsof_remap_flow_batch": (C.c_int, [C.c_void_p, _P(WarpDesc), C.c_int, C.c_int, C.c_void_p]),
     "nsof_remap_flow_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                        C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_ssize_t]),
+    "nsof_ssim_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int,
+                               C.c_double, C.c_void_p, C.c_void_p]),
+    "nsof_ssim_u8_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int,
+                                    C.c_int, C.c_double, _P(C.c_double)]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),
                                          _P(C.c_int), _P(C.c_double)]),
     "nsof_fb_algorithmic_bytes": (C.c_double, [C.c_int, C.c_int, _P(FbParams)]),

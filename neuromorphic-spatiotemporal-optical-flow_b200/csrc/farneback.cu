@@ -160,7 +160,7 @@ extern "C" size_t nsof_workspace_bytes(const nsof_handle *h)
 const char *const nsof_kernel_class_names[NSOF_K_CLASSES] = {
     "fb_pyr", "fb_polyexp", "fb_pyr_polyexp", "fb_um_first", "fb_blur_um", "fb_blur_flow", "fb_flow_init", "s1_lanczos", "s1_frame_sim",
     "s1_roi", "s1_event_hist", "s1_event_replay", "s1_synapse_step", "s1_resistance", "fb_flow_clear", "halo_copy", "table_upload",
-    "seg_pack", "seg_morph", "seg_unpack", "rgb2gray", "remap_flow", "fb_tile_list"};
+    "seg_pack", "seg_morph", "seg_unpack", "rgb2gray", "remap_flow", "fb_tile_list", "ssim"};
 
 extern "C" unsigned long long nsof_launch_count(const nsof_handle *h) { return h ? h->launches : 0; }
 

@@ -224,3 +224,135 @@ extern "C" int nsof_remap_flow_host(nsof_handle *h, const uint8_t *frame, ptrdif
     NSOF_CUDA_TRY(cudaStreamSynchronize(nullptr));
     return NSOF_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// SSIM of the prediction task (optical_flow_prediction.py:113-115): skimage.metrics.structural_similarity(true[:, :, 2],
+// prediction[:, :, 2], data_range=255.0) with its defaults -- 7 x 7 uniform window, sample covariance (x 49 / 48),
+// K1 = 0.01, K2 = 0.03, mean over the image cropped by 3 pixels on every side (so every window lies inside the
+// image and scipy's boundary mode never matters).  scikit-image is not vendored in the reference (requirements.txt pins
+// scikit-image); restated from its published algorithm, oracle/frames_oracle.py `ssim_u8`.
+// Both inputs are uint8, so the five window sums (x, y, xx, yy, xy) are exact integers; the per-pixel S and the mean are
+// float64.  Partial sums per CTA are reduced in a fixed order by a second launch: the result is deterministic.
+// ---------------------------------------------------------------------------------------------------------------------
+#define SSIM_TW 32
+#define SSIM_TH 32
+struct SsimJob {
+    const uint8_t *a, *b;
+    ptrdiff_t apitch, bpitch;
+    int astride, bstride;  // bytes between pixels (3 for channel 2 of an interleaved BGR frame, 1 for a grey plane)
+    int H, W;
+    double C1, C2;
+    double *partial;  // one per CTA
+};
+
+NSOF_GLOBAL k_ssim_tiles(SsimJob J)
+{
+    constexpr int LW = SSIM_TW + 6, LH = SSIM_TH + 6;
+    const int iw = J.W - 6, ih = J.H - 6;                     // interior (cropped) size
+    const int tiles_x = (iw + SSIM_TW - 1) / SSIM_TW;
+    const int tx0 = (NSOF_BX % tiles_x) * SSIM_TW, ty0 = (NSOF_BX / tiles_x) * SSIM_TH;  // interior coordinates
+    NSOF_DYN_SMEM(smem_raw);
+    int *sa = (int *)smem_raw, *sb = sa + LW * LH;              // pixels
+    int *hs = sb + LW * LH;                                     // horizontal 7-sums: 5 planes of LH x SSIM_TW
+    for (int i = NSOF_TID; i < LW * LH; i += NSOF_NT) {
+        const int lx = i % LW, ly = i / LW;
+        const int x = nsof_imin(tx0 + lx, J.W - 1), y = nsof_imin(ty0 + ly, J.H - 1);  // clamped loads feed unused outputs only
+        sa[i] = NSOF_LDG(J.a + (size_t)y * J.apitch + (size_t)x * J.astride);
+        sb[i] = NSOF_LDG(J.b + (size_t)y * J.bpitch + (size_t)x * J.bstride);
+    }
+    NSOF_SYNC();
+    for (int i = NSOF_TID; i < SSIM_TW * LH; i += NSOF_NT) {
+        const int lx = i % SSIM_TW, ly = i / SSIM_TW;
+        int s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+#pragma unroll
+        for (int k = 0; k < 7; k++) {
+            const int u = sa[ly * LW + lx + k], v = sb[ly * LW + lx + k];
+            s0 += u; s1 += v; s2 += u * u; s3 += v * v; s4 += u * v;
+        }
+        int *o = hs + i;
+        o[0] = s0; o[SSIM_TW * LH] = s1; o[2 * SSIM_TW * LH] = s2; o[3 * SSIM_TW * LH] = s3; o[4 * SSIM_TW * LH] = s4;
+    }
+    NSOF_SYNC();
+    double acc = 0.;
+    for (int i = NSOF_TID; i < SSIM_TW * SSIM_TH; i += NSOF_NT) {
+        const int lx = i % SSIM_TW, ly = i / SSIM_TW;
+        if (tx0 + lx >= iw || ty0 + ly >= ih) continue;
+        int s[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 7; k++)
+#pragma unroll
+            for (int c = 0; c < 5; c++) s[c] += hs[c * SSIM_TW * LH + (ly + k) * SSIM_TW + lx];
+        // uniform_filter means, then skimage's formula (cov_norm = NP / (NP - 1), NP = 49)
+        const double inv = 1. / 49., cn = 49. / 48.;
+        const double ux = s[0] * inv, uy = s[1] * inv, uxx = s[2] * inv, uyy = s[3] * inv, uxy = s[4] * inv;
+        const double vx = cn * (uxx - ux * ux), vy = cn * (uyy - uy * uy), vxy = cn * (uxy - ux * uy);
+        const double A1 = 2 * ux * uy + J.C1, A2 = 2 * vxy + J.C2, B1 = ux * ux + uy * uy + J.C1, B2 = vx + vy + J.C2;
+        acc += (A1 * A2) / (B1 * B2);
+    }
+    // fixed-order block reduction through shared memory (reuses sa: 8-byte aligned)
+    double *red = (double *)smem_raw;
+    NSOF_SYNC();
+    red[NSOF_TID] = acc;
+    NSOF_SYNC();
+    if (NSOF_TID == 0) {
+        double t = 0.;
+        for (int i = 0; i < NSOF_NT; i++) t += red[i];
+        J.partial[NSOF_BX] = t;
+    }
+}
+
+NSOF_GLOBAL k_ssim_finish(const double *partial, int n, double count, double *out)
+{
+    if (NSOF_TID != 0 || NSOF_BX != 0) return;
+    double t = 0.;
+    for (int i = 0; i < n; i++) t += partial[i];
+    *out = t / count;
+}
+
+extern "C" int nsof_ssim_u8(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                            ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out_dev,
+                            void *cuda_stream)
+{
+    if (!h || !a || !b || !out_dev) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: NULL argument");
+    if (height < 7 || width < 7) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: win_size 7 exceeds the image extent (skimage raises ValueError)");
+    if (a_pixel_stride < 1 || b_pixel_stride < 1 || a_pitch < (ptrdiff_t)width * a_pixel_stride || b_pitch < (ptrdiff_t)width * b_pixel_stride)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: bad pitch / pixel stride");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    const int iw = width - 6, ih = height - 6;
+    const int tiles = ((iw + SSIM_TW - 1) / SSIM_TW) * ((ih + SSIM_TH - 1) / SSIM_TH);
+    int rc = h->warp_tab.ensure((size_t)tiles * sizeof(double) + 64);
+    if (rc) return rc;
+    SsimJob J = {a, b, a_pitch, b_pitch, a_pixel_stride, b_pixel_stride, height, width,
+                 (0.01 * data_range) * (0.01 * data_range), (0.03 * data_range) * (0.03 * data_range), (double *)h->warp_tab.p};
+    const size_t smem = (2 * (SSIM_TW + 6) * (SSIM_TH + 6) + 5 * SSIM_TW * (SSIM_TH + 6)) * sizeof(int);
+    NSOF_KLAUNCH(h, NSOF_K_SSIM, 2. * height * width, k_ssim_tiles, tiles, 1, 1, 256, smem, stream, J);
+    NSOF_KLAUNCH(h, NSOF_K_SSIM, 8. * tiles, k_ssim_finish, 1, 1, 1, 32, 0, stream, (const double *)h->warp_tab.p, tiles,
+                 (double)iw * ih, out_dev);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
+
+// host arrays in, the score out (synchronous)
+extern "C" int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                                 ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out)
+{
+    if (!h || !a || !b || !out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: NULL argument");
+    if (height < 1 || width < 1 || a_pixel_stride < 1 || b_pixel_stride < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: bad geometry");
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    const size_t rowa = (size_t)width * a_pixel_stride, rowb = (size_t)width * b_pixel_stride;
+    const size_t pa = (rowa + 255) & ~(size_t)255, pb = (rowb + 255) & ~(size_t)255;
+    int rc = h->io.ensure(pa * height + pb * height + 256);
+    if (rc) return rc;
+    uint8_t *da = (uint8_t *)h->io.p, *db = da + pa * height;
+    double *dout = (double *)(db + pb * height + (256 - (pb * height) % 256) % 256);
+    cudaStream_t stream = nullptr;
+    NSOF_CUDA_TRY(cudaMemcpy2DAsync(da, pa, a, a_pitch, rowa, height, cudaMemcpyHostToDevice, stream));
+    NSOF_CUDA_TRY(cudaMemcpy2DAsync(db, pb, b, b_pitch, rowb, height, cudaMemcpyHostToDevice, stream));
+    rc = nsof_ssim_u8(h, da, (ptrdiff_t)pa, a_pixel_stride, db, (ptrdiff_t)pb, b_pixel_stride, height, width, data_range, dout, stream);
+    if (rc) return rc;
+    NSOF_CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(double), cudaMemcpyDeviceToHost, stream));
+    NSOF_CUDA_TRY(cudaStreamSynchronize(stream));
+    return NSOF_OK;
+}

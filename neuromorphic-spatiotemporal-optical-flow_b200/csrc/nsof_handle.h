@@ -52,7 +52,7 @@ enum NsofKernelClass {
     NSOF_K_PYR = 0, NSOF_K_POLYEXP, NSOF_K_PYR_POLYEXP, NSOF_K_UM_FIRST, NSOF_K_BLUR_UM, NSOF_K_BLUR_FLOW, NSOF_K_FLOW_INIT,
     NSOF_K_LANCZOS, NSOF_K_FRAME_SIM, NSOF_K_ROI, NSOF_K_EVENT_HIST, NSOF_K_EVENT_REPLAY, NSOF_K_SYNAPSE_STEP,
     NSOF_K_RESISTANCE, NSOF_K_FLOW_CLEAR, NSOF_K_HALO_COPY, NSOF_K_TABLE_UPLOAD, NSOF_K_SEG_PACK, NSOF_K_SEG_MORPH,
-    NSOF_K_SEG_UNPACK, NSOF_K_RGB2GRAY, NSOF_K_REMAP, NSOF_K_TILE_LIST, NSOF_K_CLASSES
+    NSOF_K_SEG_UNPACK, NSOF_K_RGB2GRAY, NSOF_K_REMAP, NSOF_K_TILE_LIST, NSOF_K_SSIM, NSOF_K_CLASSES
 };
 extern const char *const nsof_kernel_class_names[NSOF_K_CLASSES];
 

@@ -479,6 +479,29 @@ class Engine:
                     new_frame[y0:y1, x0:x1] = self.remap_flow(next_frame, flow[y0:y1, x0:x1], x0, y0)
         return new_frame
 
+    def structural_similarity(self, im1, im2, data_range=255.0):
+        """skimage.metrics.structural_similarity(im1, im2, data_range=...) for 2-D uint8 arrays with skimage's defaults,
+        as calculateIntegralError calls it on channel 2 of the true and the predicted frame
+        (optical_flow_prediction.py:113-115).  Channel views of interleaved frames (`frame[:, :, 2]`) are read in place."""
+        a, b = np.asarray(im1), np.asarray(im2)
+        if a.shape != b.shape:
+            raise ValueError("Input images must have the same dimensions.")      # skimage's check_shape_equality
+        if a.ndim != 2 or a.dtype != np.uint8 or b.dtype != np.uint8:
+            raise NotImplementedError("structural_similarity: 2-D uint8 images (one channel), as the prediction script passes")
+        if min(a.shape) < 7:
+            raise ValueError("win_size exceeds image extent.")
+        fix = lambda v: v if (v.strides[1] >= 1 and v.strides[0] >= v.shape[1] * v.strides[1]) else np.ascontiguousarray(v)
+        a, b = fix(a), fix(b)
+        out = C.c_double()
+        self.lib.check(self.lib.nsof_ssim_u8_host(self.handle, a.ctypes.data, a.strides[0], a.strides[1], b.ctypes.data,
+                                                  b.strides[0], b.strides[1], a.shape[0], a.shape[1], float(data_range),
+                                                  C.byref(out)), "structural_similarity")
+        return float(out.value)
+
+    def calculateIntegralError(self, prediction, true):
+        """optical_flow_prediction.py:113-115."""
+        return self.structural_similarity(true[:, :, 2], prediction[:, :, 2], data_range=255.0)
+
     def structuring_element(self, shape, ksize):
         """cv2.getStructuringElement(shape, ksize) as the segmentation passes build it."""
         out = np.zeros((int(ksize[1]), int(ksize[0])), dtype=np.uint8)

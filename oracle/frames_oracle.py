@@ -61,3 +61,23 @@ def task_results(prev_frame, next_frame, flow, rect):
     if y1 > y0 and x1 > x0:
         out[y0:y1, x0:x1] = remap_flow(next_frame, flow[y0:y1, x0:x1], x0, y0)
     return out
+
+
+def ssim_u8(im1, im2, data_range=255.0):
+    """skimage.metrics.structural_similarity(im1, im2, data_range=data_range) with its defaults for 2-D images
+    (optical_flow_prediction.py:113-115 passes channel 2 of two uint8 frames): win_size 7, uniform filter
+    (scipy.ndimage.uniform_filter, the call skimage itself makes), use_sample_covariance=True, K1 = 0.01, K2 = 0.03,
+    mean over the result cropped by (win_size - 1) // 2.  scikit-image is not installed in the build container or on
+    the GPU box: PARITY UNPINNED against skimage itself; the restatement follows skimage/metrics/_structural_similarity.py
+    (0.2x) line by line and uses the same scipy primitive."""
+    from scipy.ndimage import uniform_filter
+    x, y = np.asarray(im1).astype(np.float64), np.asarray(im2).astype(np.float64)
+    win, NP = 7, 49
+    cov_norm = NP / (NP - 1)
+    ux, uy = uniform_filter(x, size=win), uniform_filter(y, size=win)
+    uxx, uyy, uxy = uniform_filter(x * x, size=win), uniform_filter(y * y, size=win), uniform_filter(x * y, size=win)
+    vx, vy, vxy = cov_norm * (uxx - ux * ux), cov_norm * (uyy - uy * uy), cov_norm * (uxy - ux * uy)
+    C1, C2 = (0.01 * data_range) ** 2, (0.03 * data_range) ** 2
+    S = ((2 * ux * uy + C1) * (2 * vxy + C2)) / ((ux ** 2 + uy ** 2 + C1) * (vx + vy + C2))
+    pad = (win - 1) // 2
+    return float(S[pad:-pad, pad:-pad].mean(dtype=np.float64))

@@ -317,3 +317,22 @@ class Stage1External:
             assert np.array_equal(w_fin[0] == 0, want[:, 2] == 0) and np.array_equal(w_fin[0] == 1, want[:, 2] == 1), what
         assert worst <= tol, (what, worst)
         return worst
+
+
+def check_ssim(ssim, frames, what, tol=1e-12):
+    """Shared by the oracle, emulator and GPU tests: `ssim(a, b)` for 2-D uint8 arrays (channel views allowed) against
+    known answers and the scipy-based restatement (oracle/frames_oracle.py; skimage itself is not installed)."""
+    from oracle import frames_oracle as fo
+    nf, pred = frames["pred__next"], frames["pred__whole__out"]
+    assert ssim(nf[:, :, 2], nf[:, :, 2]) == 1.0, what                                 # identical images
+    for c1, c2 in ((10, 200), (0, 255), (77, 77)):                                     # constant images: closed form
+        a, b = np.full((40, 50), c1, np.uint8), np.full((40, 50), c2, np.uint8)
+        C1 = (0.01 * 255.0) ** 2
+        assert abs(ssim(a, b) - (2.0 * c1 * c2 + C1) / (c1 * c1 + c2 * c2 + C1)) <= tol, (what, c1, c2)
+    rng = np.random.default_rng(0)
+    cases = [(nf[:, :, 2], pred[:, :, 2]), (nf[:, :, 0], pred[:, :, 1]),               # strided channel views of real frames
+             (rng.integers(0, 256, (37, 45), dtype=np.uint8), rng.integers(0, 256, (37, 45), dtype=np.uint8)),
+             (rng.integers(0, 256, (7, 7), dtype=np.uint8), rng.integers(0, 256, (7, 7), dtype=np.uint8)),
+             (rng.integers(0, 256, (100, 7), dtype=np.uint8), rng.integers(0, 256, (100, 7), dtype=np.uint8))]
+    for a, b in cases:
+        assert abs(ssim(a, b) - fo.ssim_u8(a, b)) <= tol, (what, a.shape)

@@ -308,3 +308,11 @@ def test_emu_frame_mode_vs_external_fixtures(emu_engine):
     ext.check_euler(sim, "emu kernels (run)", tol=1e-10)
     sim2 = lambda cells, w0, th1, th2: emu_engine.simulate_memristor_array_stepwise(cells, th1=th1, th2=th2, w0=w0)
     ext.check_euler(sim2, "emu kernels (stepwise)", tol=1e-10)
+
+
+def test_emu_ssim(emu_engine, golden):
+    helpers.check_ssim(emu_engine.structural_similarity, golden.frames, "emu")
+    with pytest.raises(ValueError):
+        emu_engine.structural_similarity(np.zeros((6, 20), np.uint8), np.zeros((6, 20), np.uint8))
+    with pytest.raises(ValueError):
+        emu_engine.structural_similarity(np.zeros((8, 20), np.uint8), np.zeros((8, 21), np.uint8))

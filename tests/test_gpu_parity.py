@@ -630,6 +630,17 @@ def test_frames_vs_reference(gpu_engine, golden):
         assert np.array_equal(d_out[i].cpu().numpy(), fo.task_results(bgr[i], bgr[i], flow[i], r)), i
 
 
+def test_ssim_vs_oracle(gpu_engine, golden):
+    """calculateIntegralError (optical_flow_prediction.py:113-115) on the device, incl. a 1080p
+    BGR frame pair through the channel-2 view; tolerance 1e-12 (integer window sums are exact, the mean is float64)."""
+    from oracle import frames_oracle as fo
+    helpers.check_ssim(gpu_engine.structural_similarity, golden.frames, "gpu")
+    rng = np.random.default_rng(4)
+    true = rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8)
+    pred = np.clip(true.astype(np.int16) + rng.integers(-20, 21, true.shape), 0, 255).astype(np.uint8)
+    assert abs(gpu_engine.calculateIntegralError(pred, true) - fo.ssim_u8(true[:, :, 2], pred[:, :, 2])) <= 1e-12
+
+
 def test_sequence_step_with_segmentation(gpu_engine, nsof):
     """segment=True: the motion_binary frames of the device-resident step equal task_results of the step's own flow
     frames (restatement pinned to the reference), zero outside the rectangles, also after a second step on other

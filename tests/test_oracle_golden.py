@@ -237,3 +237,13 @@ def test_bench_clip_gate_has_margin():
         margin = min(margin, np.abs(cur / thr - 1.0).min())
         assert np.array_equal(s1.current_to_u8(cur) >= 250, cur >= thr)
     assert margin > 1e-6, margin
+
+
+def test_ssim_oracle_known_answers(golden):
+    """structural_similarity restatement (scikit-image is absent here and on the GPU box: parity unpinned against
+    skimage itself): identical images -> 1, constant images -> the closed form, symmetry."""
+    from oracle import frames_oracle as fo
+    helpers.check_ssim(fo.ssim_u8, golden.frames, "oracle")
+    nf, pred = golden.frames["pred__next"], golden.frames["pred__whole__out"]
+    assert fo.ssim_u8(nf[:, :, 2], pred[:, :, 2]) == fo.ssim_u8(pred[:, :, 2], nf[:, :, 2])
+    assert 0.9 < fo.ssim_u8(nf[:, :, 2], pred[:, :, 2]) < 1.0
