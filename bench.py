@@ -45,6 +45,8 @@ def parse_args():
                     help="which array state gates a pair (SURVEY.md 3.5): before it, as the scripts do, or after it")
     ap.add_argument("--min-seconds", type=float, default=1.0,
                     help="repeat the timed block of exactly --steps steps until the device-resident leg has run this long")
+    ap.add_argument("--chunks", default="", help="pair boundaries of the step's Farneback batches, e.g. 0,12,31 (default: one batch)")
+    ap.add_argument("--s2-streams", type=int, default=1, help="streams the batches of a step alternate over")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the full-frame and per-kernel legs")
     return ap.parse_args()
@@ -245,7 +247,10 @@ def gpu_arm(args):
     pipe_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
     eng = nsof.Engine(local)
     Cn, F = args.clips, args.frames
-    pipe = pipe_mod.DeviceStream(eng, Cn, F, H, W, depth=2, roi_state=args.roi_state)
+    cb = [int(v) for v in args.chunks.split(",")] if args.chunks else [0, F - 1]
+    assert cb[0] == 0 and cb[-1] == F - 1 and cb == sorted(cb), "--chunks must run from 0 to frames - 1"
+    pipe = pipe_mod.DeviceStream(eng, Cn, F, H, W, depth=2, roi_state=args.roi_state,
+                                 chunks=list(zip(cb[:-1], cb[1:])), s2_streams=args.s2_streams)
 
     # synthetic clips, generated on the device, layout [F][C][H][W]
     frames = torch.empty((F, Cn, H, W), dtype=torch.uint8, device=dev)

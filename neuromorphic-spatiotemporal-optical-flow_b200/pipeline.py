@@ -333,12 +333,16 @@ class DeviceStream:
     """
 
     def __init__(self, engine: Engine, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
-                 depth: int = 2, segment: bool = False, full_frame: bool = False, roi_state: str = "scripts"):
+                 depth: int = 2, segment: bool = False, full_frame: bool = False, roi_state: str = "scripts",
+                 chunks=None, s2_streams: int = 1):
+        """chunks / s2_streams: by default a step is ONE Farneback batch on the caller's stream; `chunks` = pair ranges
+        [(p0, p1), ...] splits it into time chunks whose batches alternate over `s2_streams` streams (two half batches
+        side by side fill the tails and the barrier-bound phases of each other)."""
         assert depth >= 2
-        one = [(0, int(frames) - 1)]
+        one = list(chunks) if chunks is not None else [(0, int(frames) - 1)]
         self.slots = [SequencePipeline(engine if i == 0 else Engine(engine.device, lib=engine.lib), clips, frames, H, W, cfg,
-                                       chunks=one, overlap=True, s2_streams=1, segment=segment, full_frame=full_frame,
-                                       roi_state=roi_state)
+                                       chunks=one, overlap=True, s2_streams=s2_streams, segment=segment,
+                                       full_frame=full_frame, roi_state=roi_state)
                       for i in range(depth)]
         self.k = 0
         self.pending = None  # (slot, frames) of the step whose stage 1 is queued
