@@ -7,6 +7,7 @@
 #include "farneback_kernels.cuh"
 #include <float.h>
 #include <algorithm>
+#include <unordered_map>
 
 // ------------------------------------------------------------------------------ error + handle
 static thread_local char g_err[512] = "";
@@ -92,6 +93,7 @@ struct FbItemPlan {
     int hk[64], wk[64], pitch[64];
     size_t off_I[64], off_R[64];                  // per level: the levels' pyramids are built concurrently
     size_t off_Ma, off_Mb, off_fA, off_fB;        // shared by the levels (serial chain); floats from arena base
+    int r0_from;                                  // item whose R[1] serves as this item's R[0] (shared frame), or -1
     nsof_crop_desc d;
 };
 
@@ -545,6 +547,21 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
         arena_floats = round_up(arena_floats, 64);
         max_scales = std::max(max_scales, pl.scales);
     }
+    // Shared frames: item j's `prev` crop that IS item i's `next` crop (same address, size and pitch: consecutive pairs
+    // of a clip under an unchanged ROI rectangle, or whole frames) has the same pyramid and polynomial expansion at
+    // every level -- R[0] of j is R[1] of i, computed once.  (OpenCV expands both images of every call.)
+    {
+        std::unordered_map<const uint8_t *, int> by_next;
+        if (!h->dbg_no_dedup)
+            for (int i = 0; i < n; i++) by_next.emplace(plan[i].d.next, i);
+        for (int j = 0; j < n; j++) {
+            plan[j].r0_from = -1;
+            auto it = by_next.find(plan[j].d.prev);
+            if (it == by_next.end() || it->second == j) continue;
+            const nsof_crop_desc &a = plan[it->second].d, &b = plan[j].d;
+            if (a.h == b.h && a.w == b.w && a.next_pitch == b.prev_pitch) plan[j].r0_from = it->second;
+        }
+    }
     rc = h->arena.ensure(arena_floats * sizeof(float));
     if (rc) return rc;
     float *base = (float *)h->arena.p;
@@ -588,7 +605,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     const size_t runs_off = table_bytes;
     {
         size_t max_runs = 0;
-        for (int kk = 0; kk < LV; kk++) max_runs += (size_t)X.n_active[kk] * FB_NLISTS;
+        for (int kk = 0; kk < LV; kk++) max_runs += (size_t)X.n_active[kk] * (FB_NLISTS + 4);  // pyramid lists: 2 images
         table_bytes += round_up(max_runs * sizeof(FbTileRun), 16);
     }
     NsofStageSlot *slot;
@@ -659,10 +676,15 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             if (J.y_hi <= J.y_lo) J.iy_hi = J.iy_lo;
             const int rows = J.y_hi - J.y_lo, irows = J.iy_hi - J.iy_lo;
             const double frac = (double)rows / J.h;  // share of the level this rank computes (1 when untiled)
+            // (the byte accounting of the pyramid launches counts the images actually expanded: 1 or 2 per item)
+            const double n_img = pl.r0_from >= 0 ? 0.5 : 1.0;
             X.path_n[3 * kk + J.fast] += 1;
-            X.path_N[3 * kk + J.fast] += (double)rows * J.w;
-            X.path_N0[3 * kk + J.fast] += (double)J.sh * J.sw * frac;
-            J.I = base + pl.off_I[k]; J.R = base + pl.off_R[k]; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
+            X.path_N[3 * kk + J.fast] += (double)rows * J.w * n_img;
+            X.path_N0[3 * kk + J.fast] += (double)J.sh * J.sw * frac * n_img;
+            J.I = base + pl.off_I[k]; J.Ma = base + pl.off_Ma; J.Mb = base + pl.off_Mb;
+            J.R[0] = pl.r0_from >= 0 ? base + plan[pl.r0_from].off_R[k] + 5 * (size_t)J.pitch * J.h : base + pl.off_R[k];
+            J.R[1] = base + pl.off_R[k] + 5 * (size_t)J.pitch * J.h;
+            J.share0 = pl.r0_from >= 0;
             // coarse flow ping-pong: level k writes A when k is odd, B when even; level 0 writes the caller's buffer
             float *fl_this = (k & 1) ? base + pl.off_fA : base + pl.off_fB;
             float *fl_coarse = (k & 1) ? base + pl.off_fB : base + pl.off_fA;
@@ -728,9 +750,12 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
                 if (!tw || nr <= 0) continue;
                 const unsigned cnt = (unsigned)(((J.w + tw - 1) / tw) * ((nr + th - 1) / th));
                 if (!cnt) continue;
-                FbTileRun r = {n_tiles, (unsigned)a, cnt, 0u};
-                runs[n_runs++] = r;
-                n_tiles += cnt;
+                const bool per_image = l <= FB_L_PE;  // pyramid / PolyExp lists: one run per image to expand
+                for (int img = per_image && J.share0 ? 1 : 0; img < (per_image ? 2 : 1); img++) {
+                    FbTileRun r = {n_tiles, (unsigned)a | ((unsigned)img << FB_TL_IMG_SHIFT), cnt, 0u};
+                    runs[n_runs++] = r;
+                    n_tiles += cnt;
+                }
             }
             X.list_n[(size_t)kk * FB_NLISTS + l] = n_tiles - X.list_off[(size_t)kk * FB_NLISTS + l];
         }
@@ -784,18 +809,18 @@ static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream, int var
     (void)na;
     if (ln(FB_L_PP0))
         NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 1] + 40 * X.path_N[3 * kk + 1], FB_PYR_POLYEXP_M0,
-                     ln(FB_L_PP0), 1, 2, 256, fb_pp_smem(0), stream, jobs, lp(FB_L_PP0), gk, pc);
+                     ln(FB_L_PP0), 1, 1, 256, fb_pp_smem(0), stream, jobs, lp(FB_L_PP0), gk, pc);
     if (ln(FB_L_PP1))
         NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 2] + 40 * X.path_N[3 * kk + 2], FB_PYR_POLYEXP_M1,
-                     ln(FB_L_PP1), 1, 2, 256, fb_pp_smem(1), stream, jobs, lp(FB_L_PP1), gk, pc);
+                     ln(FB_L_PP1), 1, 1, 256, fb_pp_smem(1), stream, jobs, lp(FB_L_PP1), gk, pc);
     if (ln(FB_L_PYR) && ln(FB_L_PE)) {
         const int r = X.ksize[k] / 2;
         if (X.pyr_sep[kk])
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, ln(FB_L_PYR), 1, 2, 256,
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, ln(FB_L_PYR), 1, 1, 256,
                          fb_ps_smem(r, X.ps_sw[kk], X.ps_sh[kk]), stream, jobs, lp(FB_L_PYR), gk, r, X.ps_sw[kk], X.ps_sh[kk]);
         else
-            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, ln(FB_L_PYR), 1, 2, 256, 0, stream, jobs, lp(FB_L_PYR), gk, r);
-        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, ln(FB_L_PE), 1, 2, 256, X.pe_smem, stream,
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, ln(FB_L_PYR), 1, 1, 256, 0, stream, jobs, lp(FB_L_PYR), gk, r);
+        NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, ln(FB_L_PE), 1, 1, 256, X.pe_smem, stream,
                      jobs, lp(FB_L_PE), pc);
     }
     NSOF_CUDA_TRY(cudaGetLastError());
@@ -1540,6 +1565,14 @@ extern "C" int nsof_debug_big_tiles(nsof_handle *h, int enable)
     return NSOF_OK;
 }
 
+// 0: expand both images of every item even when a frame is shared between two items (tests, A/B)
+extern "C" int nsof_debug_share_frames(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_no_dedup = !enable;
+    return NSOF_OK;
+}
+
 extern "C" int nsof_debug_fork(nsof_handle *h, int enable)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
@@ -1576,7 +1609,7 @@ extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, 
     switch (what) {
     case 0: src = base + pl.off_I[k]; ch = 1; break;
     case 1: src = base + pl.off_I[k] + plane; ch = 1; break;
-    case 2: src = base + pl.off_R[k]; ch = 5; break;
+    case 2: src = pl.r0_from >= 0 ? base + plan[pl.r0_from].off_R[k] + 5 * plane : base + pl.off_R[k]; ch = 5; break;
     case 3: src = base + pl.off_R[k] + 5 * plane; ch = 5; break;
     case 4: {
         // M currently valid: Ma after um_first, then the iterations alternate a->b->a ...

@@ -38,6 +38,7 @@ struct alignas(16) FbJob {
     int fpitch;            // pitch of `flow`, float2 units
     int resize_mode;       // 0 identity, 1 exact 2x (2x2 mean), 2 bilinear
     int fast;              // 0: generic k_fb_pyr + k_fb_polyexp; 1 / 2: fused k_fb_pyr_polyexp_t<MODE 0 / 1>
+    int share0;            // R[0] is another item's R[1] (shared frame): only image 1 of this item is expanded
     // Row window (spatial tiling across GPUs, nsof_fb_tiled_*): the kernels compute rows [y_lo, y_hi) of this level
     // (the generic pyramid kernels rows [iy_lo, iy_hi) of I) but keep addressing, borders and resize geometry of
     // the whole h x w level; rows outside the window are read where a stencil / gather reaches them (exchanged
@@ -49,7 +50,10 @@ struct alignas(16) FbJob {
     double fsx, fsy;       // coarse/this ratio of the flow upsample
     const uint8_t *src0, *src1;
     float *I;
-    float *R;
+    // polynomial expansions of the two images, 5 planes each.  R[0] of an item whose `prev` crop IS another item's
+    // `next` crop (consecutive pairs of a clip under an unchanged ROI rectangle, or whole frames) points at that item's
+    // R[1]: the expansion of a shared frame is computed once per batch (the tile lists carry (item, image) entries).
+    float *R[2];
     float *Ma, *Mb;
     const float2 *cflow;
     float2 *flow;
@@ -61,6 +65,10 @@ struct alignas(16) FbJob {
     const float2 *flow0;  // the caller's full-resolution flow (sh x sw, f0pitch in float2)
     int f0pitch;
 };
+
+// tile-list entry .x = item index (low 24 bits) | image index << 24 (pyramid / PolyExp lists; 0 elsewhere)
+#define FB_TL_ITEM 0xffffffu
+#define FB_TL_IMG_SHIFT 24
 
 // One run of a flat tile list: `count` consecutive entries (item, 0), (item, 1), ... starting at entry `off`.
 struct FbTileRun {
@@ -131,10 +139,10 @@ NSOF_DEV void fb_lin_coord(int d, double ratio, int len, int *i0, int *i1, float
 NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, const float *NSOF_RESTRICT gk, int r)
 {
     const uint2 te = tl[NSOF_BX];
-    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + (te.x & FB_TL_ITEM));
     const int tile = (int)te.y;
     const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW;
-    const int img = NSOF_BZ;
+    const int img = (int)(te.x >> FB_TL_IMG_SHIFT);
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
@@ -179,13 +187,13 @@ NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT
 NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, PolyConst pc)
 {
     const uint2 te = tl[NSOF_BX];
-    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + (te.x & FB_TL_ITEM));
     const int tile = (int)te.y;
     const int tiles_x = (J.w + FB_PE_TW - 1) / FB_PE_TW;
-    const int img = NSOF_BZ;
+    const int img = (int)(te.x >> FB_TL_IMG_SHIFT);
     const size_t plane = (size_t)J.pitch * J.h;
     const float *I = J.I + img * plane;
-    float *R = J.R + (size_t)img * 5 * plane;
+    float *R = J.R[img];
     const int tx0 = (tile % tiles_x) * FB_PE_TW, ty0 = J.y_lo + (tile / tiles_x) * FB_PE_TH;
     const int n = pc.n, IW = FB_PE_TW + 2 * n, IH = FB_PE_TH + 2 * n;
     NSOF_DYN_SMEM(smem_raw);
@@ -411,7 +419,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(const FbJob *NSO
         const int px1 = nsof_imin(tx0 + FB_UM_TW, J.pitch);
         for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
             const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
-            nsof_prefetch_l2(J.R + (5 + c) * plane + (size_t)gy * J.pitch + tx0, (unsigned)(px1 - tx0) * 4u);
+            nsof_prefetch_l2(J.R[1] + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(px1 - tx0) * 4u);
         }
     }
     // (one pixel per lane, as in phase 3b of the blur+solve kernel, was measured here and is SLOWER: 2.35 -> 2.60 ms per
@@ -425,7 +433,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(const FbJob *NSO
         float r0[5][4];
 #pragma unroll
         for (int c = 0; c < 5; c++) {
-            const float4 t = NSOF_LDG((const float4 *)(J.R + c * plane + o));
+            const float4 t = NSOF_LDG((const float4 *)(J.R[0] + c * plane + o));
             r0[c][0] = t.x; r0[c][1] = t.y; r0[c][2] = t.z; r0[c][3] = t.w;
         }
         float mo[5][4];
@@ -441,7 +449,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(const FbJob *NSO
 #pragma unroll
                 for (int c = 0; c < 5; c++) r0v[c] = r0[c][q];
                 if (J.guard) fb_um_guard(J, y, d.y);
-                fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, d.x, d.y, r0v, mm);
+                fb_um_pixel(J.R[1], plane, J.pitch, J.h, J.w, x + q, y, d.x, d.y, r0v, mm);
             } else {
 #pragma unroll
                 for (int c = 0; c < 5; c++) mm[c] = 0.f;
@@ -694,9 +702,9 @@ NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF
             for (int q = 0; q < 4; q++) {
                 float r0v[5], mm[5];
                 if (x + q < J.w) {
-                    for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(J.R + c * plane + o + q);
+                    for (int c = 0; c < 5; c++) r0v[c] = NSOF_LDG(J.R[0] + c * plane + o + q);
                     if (J.guard) fb_um_guard(J, y, fyv[q]);
-                    fb_um_pixel(J.R + 5 * plane, plane, J.pitch, J.h, J.w, x + q, y, fxv[q], fyv[q], r0v, mm);
+                    fb_um_pixel(J.R[1], plane, J.pitch, J.h, J.w, x + q, y, fxv[q], fyv[q], r0v, mm);
                 } else {
                     for (int c = 0; c < 5; c++) mm[c] = 0.f;
                 }
@@ -772,8 +780,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         const int t0 = nsof_imin(tx0 + TW, J.pitch);
         for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
             const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
-            nsof_prefetch_l2(J.R + (5 + c) * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
-            if (gy >= ty0 && gy < ty0 + TH) nsof_prefetch_l2(J.R + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(t0 - tx0) * 4u);
+            nsof_prefetch_l2(J.R[1] + c * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
+            if (gy >= ty0 && gy < ty0 + TH) nsof_prefetch_l2(J.R[0] + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(t0 - tx0) * 4u);
         }
     }
     // one warp polls the mbarrier; the others sleep in the block barrier (a try_wait spin in every warp
@@ -914,7 +922,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     if (last) return;
     NSOF_SYNC();
     // ---- phase 3b
-    const float *R0 = J.R, *R1 = J.R + 5 * plane;
+    const float *R0 = J.R[0], *R1 = J.R[1];
 #ifndef FB_BS_UNROLL
 #define FB_BS_UNROLL 2
 #endif
@@ -1048,15 +1056,15 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
 #endif
     constexpr int BSTRIP = FB_PP_BSTRIP, BNS = (IH + BSTRIP - 1) / BSTRIP;
     static_assert(A_BYTES % 16 == 0 && B_BYTES % 16 == 0, "shared regions must stay 16-byte aligned");
-    const uint2 te = tl[NSOF_BX];  // the list holds items with fast == MODE + 1 only
-    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const uint2 te = tl[NSOF_BX];  // the list holds (item, image) entries of items with fast == MODE + 1 only
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + (te.x & FB_TL_ITEM));
     const int tile = (int)te.y;
     const int tiles_x = (J.w + TW - 1) / TW;
-    const int img = NSOF_BZ;
+    const int img = (int)(te.x >> FB_TL_IMG_SHIFT);
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     const size_t plane = (size_t)J.pitch * J.h;
-    float *R = J.R + (size_t)img * 5 * plane;
+    float *R = J.R[img];
     const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
@@ -1436,11 +1444,11 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_REST
                          int SWmax, int SHmax)
 {
     constexpr int TW = FB_PS_TW, TH = FB_PS_TH;
-    const uint2 te = tl[NSOF_BX];  // the list holds the generic-path items (fast == 0) only
-    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const uint2 te = tl[NSOF_BX];  // the list holds (item, image) entries of the generic-path items (fast == 0) only
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + (te.x & FB_TL_ITEM));
     const int tile = (int)te.y;
     const int tiles_x = (J.w + TW - 1) / TW;
-    const int img = NSOF_BZ;
+    const int img = (int)(te.x >> FB_TL_IMG_SHIFT);
     const uint8_t *src = img ? J.src1 : J.src0;
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;

@@ -90,6 +90,7 @@ struct nsof_handle {
     int stage_next = 0;
     // debug truncation (tests only)
     int dbg_level = -1, dbg_iters = -1;
+    bool dbg_no_dedup = false;  // expand shared frames once per item (nsof_debug_share_frames(h, 0))
     bool dbg_no_fuse = false;  // force the generic pyramid + PolyExp kernels (so that I exists and can be fetched)
     // geometry of the last batch, kept for nsof_debug_fetch
     std::vector<FbItemPlan> *last_plan = nullptr;

@@ -336,3 +336,24 @@ def check_ssim(ssim, frames, what, tol=1e-12):
              (rng.integers(0, 256, (100, 7), dtype=np.uint8), rng.integers(0, 256, (100, 7), dtype=np.uint8))]
     for a, b in cases:
         assert abs(ssim(a, b) - fo.ssim_u8(a, b)) <= tol, (what, a.shape)
+
+
+def check_shared_frames(eng, device_batch=None):
+    """A batch of consecutive pairs of one clip (frames f0..f3, the same crop) shares the expansion of the middle frames
+    between neighbouring items; the flows must equal, BIT FOR BIT, those of single calls and of the batch with the
+    sharing switched off.  Different crops of the same frames must not be shared."""
+    base, _ = textured_pair(51, 260, 330)
+    frames = [np.ascontiguousarray(np.roll(base, (2 * t, -3 * t), axis=(0, 1))) for t in range(4)]
+    p = PARAM_SETS["grasp"]
+    crop = (slice(20, 240), slice(16, 316))
+    other = (slice(20, 240), slice(24, 316))   # another rectangle: its frames start at other addresses
+    pairs = [(frames[t][crop], frames[t + 1][crop]) for t in range(3)] + [(frames[1][other], frames[2][other])]
+    singles = [eng.calcOpticalFlowFarneback(a, b, None, **p) for a, b in pairs]
+    if device_batch is None:   # host batch: the crops are copied to separate device buffers, nothing can be shared
+        return singles
+    got = device_batch(frames, [crop, crop, crop, other], [0, 1, 2, 1], True)
+    off = device_batch(frames, [crop, crop, crop, other], [0, 1, 2, 1], False)
+    for i, want in enumerate(singles):
+        assert np.array_equal(got[i], want), i
+        assert np.array_equal(off[i], want), i
+    return singles

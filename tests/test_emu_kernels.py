@@ -316,3 +316,32 @@ def test_emu_ssim(emu_engine, golden):
         emu_engine.structural_similarity(np.zeros((6, 20), np.uint8), np.zeros((6, 20), np.uint8))
     with pytest.raises(ValueError):
         emu_engine.structural_similarity(np.zeros((8, 20), np.uint8), np.zeros((8, 21), np.uint8))
+
+
+def test_shared_frame_expansion_bit_identical(emu_engine):
+    """Consecutive pairs of a clip under one ROI rectangle: R of the shared frame is computed once per batch."""
+    import ctypes as C
+    eng = emu_engine
+    to_dev = lambda f: f
+    new_out = lambda hw: np.zeros(hw + (2,), np.float32)
+    ptr = lambda a: a.ctypes.data
+    stream = lambda: 0
+    to_host = lambda o: o
+
+    def device_batch(frames, crops, t0s, share):
+        eng.lib.check(eng.lib.nsof_debug_share_frames(eng.handle, 1 if share else 0))
+        try:
+            H, W = frames[0].shape
+            dev = [to_dev(f) for f in frames]
+            outs = [new_out((sl[0].stop - sl[0].start, sl[1].stop - sl[1].start)) for sl in crops]
+            items = []
+            for sl, t, o in zip(crops, t0s, outs):
+                off = sl[0].start * W + sl[1].start
+                h, w = sl[0].stop - sl[0].start, sl[1].stop - sl[1].start
+                items.append((ptr(dev[t]) + off, ptr(dev[t + 1]) + off, h, w, W, W, ptr(o), w * 8))
+            eng.farneback_batch_device(items, stream(), **helpers.PARAM_SETS["grasp"])
+            return [to_host(o) for o in outs]
+        finally:
+            eng.lib.check(eng.lib.nsof_debug_share_frames(eng.handle, 1))
+
+    helpers.check_shared_frames(eng, device_batch)

@@ -845,3 +845,35 @@ def test_tiled_lockstep_ranks_bit_identical_on_one_gpu(gpu_engine, nsof, world):
         assert tripped.value == 0
     for e in engs:
         e.close()
+
+
+def test_shared_frame_expansion_bit_identical(gpu_engine):
+    """Consecutive pairs of a clip under one ROI rectangle: R of the shared frame is computed once per batch."""
+    import ctypes as C
+    eng = gpu_engine
+    import torch
+    to_dev = lambda f: torch.from_numpy(f).cuda()
+    new_out = lambda hw: torch.zeros(hw + (2,), dtype=torch.float32, device="cuda")
+    ptr = lambda t: t.data_ptr()
+    stream = lambda: torch.cuda.current_stream().cuda_stream
+    def to_host(o):
+        torch.cuda.synchronize()
+        return o.cpu().numpy()
+
+    def device_batch(frames, crops, t0s, share):
+        eng.lib.check(eng.lib.nsof_debug_share_frames(eng.handle, 1 if share else 0))
+        try:
+            H, W = frames[0].shape
+            dev = [to_dev(f) for f in frames]
+            outs = [new_out((sl[0].stop - sl[0].start, sl[1].stop - sl[1].start)) for sl in crops]
+            items = []
+            for sl, t, o in zip(crops, t0s, outs):
+                off = sl[0].start * W + sl[1].start
+                h, w = sl[0].stop - sl[0].start, sl[1].stop - sl[1].start
+                items.append((ptr(dev[t]) + off, ptr(dev[t + 1]) + off, h, w, W, W, ptr(o), w * 8))
+            eng.farneback_batch_device(items, stream(), **helpers.PARAM_SETS["grasp"])
+            return [to_host(o) for o in outs]
+        finally:
+            eng.lib.check(eng.lib.nsof_debug_share_frames(eng.handle, 1))
+
+    helpers.check_shared_frames(eng, device_batch)
