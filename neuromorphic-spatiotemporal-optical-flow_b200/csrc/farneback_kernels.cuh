@@ -1353,6 +1353,90 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
         }
     }
     NSOF_SYNC();
+#ifndef FB_PP_D8
+#define FB_PP_D8 1
+#endif
+#if FB_PP_D8
+    // ---- D: horizontal pass, EIGHT outputs per thread, one moment plane at a time (planes 0, 2, 1; the outputs that
+    // depend on planes 0 and 2 are stored before plane 1 is loaded, so at most 32 partial sums are alive).  The kernel's
+    // busiest unit is the shared-memory pipe (ncu: l1tex 72 %); a thread of the 4-output form loaded 15 float4 per 4
+    // outputs, this one loads 15 per 8 -- and the 256 items of a tile are exactly one round of the 256 threads.
+    {
+        constexpr int GW = TW / 8, NV = (8 + 2 * N + 3) / 4;
+        for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
+            // 8 consecutive lanes = 4 column groups x 2 rows: their float4 loads (rows IP = 76 words apart) fall into
+            // disjoint banks; 8 column groups side by side would be 32 bytes apart and conflict 2-way
+            static_assert(GW == 8 && TH % 2 == 0, "lane mapping of phase D");
+            const int j8 = i & 7, q8 = i >> 3;
+            const int lx = ((((q8 & 1) << 2) | (j8 & 3))) * 8, ly = ((q8 >> 1) << 1) | (j8 >> 2);
+            const int x = tx0 + lx, y = ty0 + ly;
+            if (x >= J.w || y >= J.y_hi) continue;
+            float q[NV * 4];
+#define FB_PP_LOADQ(p)                                                                   \
+    {                                                                                    \
+        const float4 *s4 = (const float4 *)(sr + (p) * TH * IP + ly * IP + lx);          \
+        _Pragma("unroll") for (int k = 0; k < NV; k++) {                                 \
+            const float4 t = s4[k];                                                      \
+            q[4 * k] = t.x; q[4 * k + 1] = t.y; q[4 * k + 2] = t.z; q[4 * k + 3] = t.w;  \
+        }                                                                                \
+    }
+            const size_t o = (size_t)y * J.pitch + x;
+            const float g0 = pc.g[0];
+            float b1[8], b2[8], b4[8], b5[8];
+            FB_PP_LOADQ(0);
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const int ctr = e + N;
+                b1[e] = q[ctr] * g0; b2[e] = 0.f; b4[e] = 0.f;
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float p0 = q[ctr + k], m0 = q[ctr - k];
+                    const float tg = p0 + m0;
+                    b1[e] += tg * pc.g[k];
+                    b4[e] += tg * pc.xxg[k];
+                    b2[e] += (p0 - m0) * pc.xg[k];
+                }
+            }
+            FB_PP_LOADQ(2);
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const int ctr = e + N;
+                b5[e] = q[ctr] * g0;
+#pragma unroll
+                for (int k = 1; k <= N; k++) b5[e] += (q[ctr + k] + q[ctr - k]) * pc.g[k];
+            }
+#pragma unroll
+            for (int hq = 0; hq < 2; hq++) {
+                const int e = 4 * hq;
+                *(float4 *)(R + plane + o + e) = make_float4(b2[e] * pc.ig11, b2[e + 1] * pc.ig11, b2[e + 2] * pc.ig11, b2[e + 3] * pc.ig11);
+                *(float4 *)(R + 2 * plane + o + e) = make_float4(b1[e] * pc.ig03 + b5[e] * pc.ig33, b1[e + 1] * pc.ig03 + b5[e + 1] * pc.ig33,
+                                                                 b1[e + 2] * pc.ig03 + b5[e + 2] * pc.ig33, b1[e + 3] * pc.ig03 + b5[e + 3] * pc.ig33);
+                *(float4 *)(R + 3 * plane + o + e) = make_float4(b1[e] * pc.ig03 + b4[e] * pc.ig33, b1[e + 1] * pc.ig03 + b4[e + 1] * pc.ig33,
+                                                                 b1[e + 2] * pc.ig03 + b4[e + 2] * pc.ig33, b1[e + 3] * pc.ig03 + b4[e + 3] * pc.ig33);
+            }
+            FB_PP_LOADQ(1);
+#undef FB_PP_LOADQ
+            float b3[8], b6[8];
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const int ctr = e + N;
+                b3[e] = q[ctr] * g0; b6[e] = 0.f;
+#pragma unroll
+                for (int k = 1; k <= N; k++) {
+                    const float p1 = q[ctr + k], m1 = q[ctr - k];
+                    b3[e] += (p1 + m1) * pc.g[k];
+                    b6[e] += (p1 - m1) * pc.xg[k];
+                }
+            }
+#pragma unroll
+            for (int hq = 0; hq < 2; hq++) {
+                const int e = 4 * hq;
+                *(float4 *)(R + o + e) = make_float4(b3[e] * pc.ig11, b3[e + 1] * pc.ig11, b3[e + 2] * pc.ig11, b3[e + 3] * pc.ig11);
+                *(float4 *)(R + 4 * plane + o + e) = make_float4(b6[e] * pc.ig55, b6[e + 1] * pc.ig55, b6[e + 2] * pc.ig55, b6[e + 3] * pc.ig55);
+            }
+        }
+    }
+#else
     // ---- D: horizontal pass, 4 outputs per thread
     {
         constexpr int GW = TW / 4, NV = (4 + 2 * N + 3) / 4;
@@ -1403,6 +1487,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
             *(float4 *)(R + 4 * plane + o) = make_float4(o4[0], o4[1], o4[2], o4[3]);
         }
     }
+#endif
 #endif
 #undef FB_SI_ST
 #undef FB_SI_LD
