@@ -39,6 +39,10 @@ typedef struct nsof_handle nsof_handle;
 /* cv2.OPTFLOW_USE_INITIAL_FLOW: `flow` is in/out; the coarsest level starts from resize(flow, INTER_AREA) * scale
  * instead of zero (no call site of the reference passes a flow; implemented for the drop-in signature) */
 #define NSOF_FB_USE_INITIAL_FLOW 4
+/* Not a cv2 flag: `prev` / `next` point to FLOAT32 frames (pitches in bytes).  cv2.calcOpticalFlowFarneback accepts
+ * CV_32F images as well as CV_8U (its convertTo(CV_32F) is then the identity); no reference call site passes them.
+ * They take the direct pyramid kernel with typed loads (the tuned kernels stage uint8 source windows). */
+#define NSOF_FB_SRC_F32 0x10000
 
 /* The kwargs of `farneback_params` (optical_flow_seg.py:73-81), same names and meaning as
  * cv2.calcOpticalFlowFarneback(prev, next, flow, pyr_scale, levels, winsize, iterations, poly_n,

@@ -19,6 +19,7 @@ NSOF_ERR_UNSUPPORTED = -2
 NSOF_ERR_CUDA = -3
 NSOF_ERR_NOMEM = -4
 NSOF_MAX_RECTS = 256
+NSOF_FB_SRC_F32 = 0x10000  # prev / next are float32 frames (include/nsof.h)
 
 
 class error(ValueError):

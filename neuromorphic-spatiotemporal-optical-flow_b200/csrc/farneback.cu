@@ -352,7 +352,7 @@ static int validate_params(const nsof_fb_params *p)
                   "column 0 to every 1x1 window there; see oracle/farneback_oracle.c A.7)");
     if (p->poly_n < 1 || p->poly_n > NSOF_MAX_POLY_N)
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: poly_n must be in 1..%d", NSOF_MAX_POLY_N);
-    if (p->flags & ~(NSOF_FB_GAUSSIAN | NSOF_FB_USE_INITIAL_FLOW))
+    if (p->flags & ~(NSOF_FB_GAUSSIAN | NSOF_FB_USE_INITIAL_FLOW | NSOF_FB_SRC_F32))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED,
                   "farneback: flags=%d; OPTFLOW_USE_INITIAL_FLOW (4) and OPTFLOW_FARNEBACK_GAUSSIAN (256) are the flags "
                   "cv2 defines", p->flags);
@@ -426,7 +426,9 @@ static int plan_item(const nsof_crop_desc &d, const nsof_fb_params *p, FbItemPla
     if (!d.prev || !d.next || !d.flow) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a NULL pointer", index);
     if (d.h < 1 || d.w < 1)
         NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d is empty (%dx%d) (cv2: assertion !_src.empty())", index, d.h, d.w);
-    if (d.prev_pitch < d.w || d.next_pitch < d.w || d.flow_pitch < (ptrdiff_t)d.w * 8 || d.flow_pitch % 8)
+    const ptrdiff_t esz = (p->flags & NSOF_FB_SRC_F32) ? 4 : 1;
+    if (d.prev_pitch < d.w * esz || d.next_pitch < d.w * esz || d.flow_pitch < (ptrdiff_t)d.w * 8 || d.flow_pitch % 8 ||
+        (esz == 4 && ((d.prev_pitch | d.next_pitch) % 4 || ((uintptr_t)d.prev | (uintptr_t)d.next) % 4)))
         NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a bad pitch", index);
     if ((uintptr_t)d.flow % 8) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d flow pointer is not 8-byte aligned", index);
     pl->d = d;
@@ -659,6 +661,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             else J.resize_mode = 2;
             J.sx = (double)J.sw / J.w; J.sy = (double)J.sh / J.h;
             J.fast = (may_fuse && X.ksize[k] == 3 && J.resize_mode < 2) ? J.resize_mode + 1 : 0;
+            if (params->flags & NSOF_FB_SRC_F32) J.fast = 0;  // float32 frames: the direct pyramid kernel (typed loads)
             // row window
             J.y_lo = 0; J.y_hi = J.h; J.gy_lo = 0; J.gy_hi = J.h; J.guard = nullptr;
             if (tiling) {
@@ -727,7 +730,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
         // tile (4x the CTAs, each a quarter of the serial work)
         X.bs_small[kk] = X.bs_m7 && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles;
         // two CTAs per SM; larger windows (extreme resize ratios) take the direct pyramid kernel
-        X.pyr_sep[kk] = fb_ps_smem(X.ksize[k] / 2, X.ps_sw[kk], X.ps_sh[kk]) <= 100 * 1024;
+        X.pyr_sep[kk] = fb_ps_smem(X.ksize[k] / 2, X.ps_sw[kk], X.ps_sh[kk]) <= 100 * 1024 && !(params->flags & NSOF_FB_SRC_F32);
         const FbJob *jobs = (const FbJob *)(hs + X.job_off[kk]);
         for (int l = 0; l < FB_NLISTS; l++) {
             X.list_off[(size_t)kk * FB_NLISTS + l] = n_tiles;
@@ -818,6 +821,8 @@ static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream, int var
         if (X.pyr_sep[kk])
             NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr_sep, ln(FB_L_PYR), 1, 1, 256,
                          fb_ps_smem(r, X.ps_sw[kk], X.ps_sh[kk]), stream, jobs, lp(FB_L_PYR), gk, r, X.ps_sw[kk], X.ps_sh[kk]);
+        else if (X.params.flags & NSOF_FB_SRC_F32)
+            NSOF_KLAUNCH(h, NSOF_K_PYR, 8 * X.path_N0[3 * kk], k_fb_pyr_f32, ln(FB_L_PYR), 1, 1, 256, 0, stream, jobs, lp(FB_L_PYR), gk, r);
         else
             NSOF_KLAUNCH(h, NSOF_K_PYR, 2 * X.path_N0[3 * kk], k_fb_pyr, ln(FB_L_PYR), 1, 1, 256, 0, stream, jobs, lp(FB_L_PYR), gk, r);
         NSOF_KLAUNCH(h, NSOF_K_POLYEXP, 40 * X.path_N[3 * kk], k_fb_polyexp, ln(FB_L_PE), 1, 1, 256, X.pe_smem, stream,
@@ -1368,6 +1373,7 @@ extern "C" int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *i
     if (n == 0) return NSOF_OK;
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
     std::vector<nsof_crop_desc> dev(n);
+    const ptrdiff_t esz = (params->flags & NSOF_FB_SRC_F32) ? 4 : 1;  // float32 frames (cv2 accepts them)
     size_t bytes = 0;
     std::vector<size_t> off_img(n), off_flow(n), ipitch(n);
     for (int i = 0; i < n; i++) {
@@ -1375,9 +1381,9 @@ extern "C" int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *i
         if (!d.prev || !d.next || !d.flow) NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a NULL pointer", i);
         if (d.h < 1 || d.w < 1)
             NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d is empty (%dx%d) (cv2: assertion !_src.empty())", i, d.h, d.w);
-        if (d.prev_pitch < d.w || d.next_pitch < d.w || d.flow_pitch < (ptrdiff_t)d.w * 8)
+        if (d.prev_pitch < d.w * esz || d.next_pitch < d.w * esz || d.flow_pitch < (ptrdiff_t)d.w * 8)
             NSOF_FAIL(NSOF_ERR_BAD_ARG, "farneback: item %d has a bad pitch", i);
-        ipitch[i] = round_up(d.w, 128);
+        ipitch[i] = round_up((size_t)d.w * esz, 128);
         off_img[i] = bytes;
         bytes += 2 * ipitch[i] * d.h;
         bytes = round_up(bytes, 256);
@@ -1392,8 +1398,8 @@ extern "C" int nsof_farneback_batch_host(nsof_handle *h, const nsof_crop_desc *i
     for (int i = 0; i < n; i++) {
         const nsof_crop_desc &d = items[i];
         uint8_t *p0 = io + off_img[i], *p1 = p0 + ipitch[i] * d.h;
-        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p0, ipitch[i], d.prev, d.prev_pitch, d.w, d.h, cudaMemcpyHostToDevice, stream));
-        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p1, ipitch[i], d.next, d.next_pitch, d.w, d.h, cudaMemcpyHostToDevice, stream));
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p0, ipitch[i], d.prev, d.prev_pitch, (size_t)d.w * esz, d.h, cudaMemcpyHostToDevice, stream));
+        NSOF_CUDA_TRY(cudaMemcpy2DAsync(p1, ipitch[i], d.next, d.next_pitch, (size_t)d.w * esz, d.h, cudaMemcpyHostToDevice, stream));
         dev[i].prev = p0; dev[i].next = p1; dev[i].h = d.h; dev[i].w = d.w;
         dev[i].prev_pitch = dev[i].next_pitch = (ptrdiff_t)ipitch[i];
         dev[i].flow = (float *)(io + off_flow[i]);

@@ -94,7 +94,9 @@ struct PolyConst {
 // Always evaluated from the full-resolution uint8 source, only at the blurred samples the resize
 // touches.  gk[0] is the centre tap, gk[i] the tap at distance i (symmetric kernel, radius r).
 // ---------------------------------------------------------------------------------------------
-NSOF_DEV float fb_blur_row(const uint8_t *NSOF_RESTRICT row, int X, int w, const float *NSOF_RESTRICT gk, int r)
+// T = uint8_t (the reference's grey frames) or float (cv2 accepts CV_32F frames too: convertTo(CV_32F) is then the identity)
+template <typename T>
+NSOF_DEV float fb_blur_row(const T *NSOF_RESTRICT row, int X, int w, const float *NSOF_RESTRICT gk, int r)
 {
     float acc = gk[0] * (float)NSOF_LDG(row + X);
     if (X - r >= 0 && X + r < w) {
@@ -108,15 +110,19 @@ NSOF_DEV float fb_blur_row(const uint8_t *NSOF_RESTRICT row, int X, int w, const
     return acc;
 }
 
-NSOF_DEV float fb_blur_at(const uint8_t *NSOF_RESTRICT src, int sp, int sh, int sw, int X, int Y,
+// sp: row pitch in BYTES
+template <typename T>
+NSOF_DEV float fb_blur_at(const T *NSOF_RESTRICT src, int sp, int sh, int sw, int X, int Y,
                           const float *NSOF_RESTRICT gk, int r)
 {
-    float acc = gk[0] * fb_blur_row(src + (size_t)Y * sp, X, sw, gk, r);
+#define FB_ROW(y_) ((const T *)((const unsigned char *)src + (size_t)(y_) * sp))
+    float acc = gk[0] * fb_blur_row(FB_ROW(Y), X, sw, gk, r);
     for (int i = 1; i <= r; i++) {
-        float a = fb_blur_row(src + (size_t)nsof_reflect101(Y - i, sh) * sp, X, sw, gk, r);
-        float b = fb_blur_row(src + (size_t)nsof_reflect101(Y + i, sh) * sp, X, sw, gk, r);
+        float a = fb_blur_row(FB_ROW(nsof_reflect101(Y - i, sh)), X, sw, gk, r);
+        float b = fb_blur_row(FB_ROW(nsof_reflect101(Y + i, sh)), X, sw, gk, r);
         acc = acc + gk[i] * (a + b);
     }
+#undef FB_ROW
     return acc;
 }
 
@@ -136,14 +142,15 @@ NSOF_DEV void fb_lin_coord(int d, double ratio, int len, int *i0, int *i1, float
 #define FB_PYR_TW 32
 #define FB_PYR_TH 8
 
-NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, const float *NSOF_RESTRICT gk, int r)
+template <typename T>
+NSOF_GLOBAL k_fb_pyr_g(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, const float *NSOF_RESTRICT gk, int r)
 {
     const uint2 te = tl[NSOF_BX];
     NSOF_JOB_TO_SMEM(FbJob, J, jobs + (te.x & FB_TL_ITEM));
     const int tile = (int)te.y;
     const int tiles_x = (J.w + FB_PYR_TW - 1) / FB_PYR_TW;
     const int img = (int)(te.x >> FB_TL_IMG_SHIFT);
-    const uint8_t *src = img ? J.src1 : J.src0;
+    const T *src = (const T *)(img ? J.src1 : J.src0);
     const int sp = img ? J.spitch1 : J.spitch0;
     float *dst = J.I + (size_t)img * J.pitch * J.h;
     const int tx0 = (tile % tiles_x) * FB_PYR_TW, ty0 = J.iy_lo + (tile / tiles_x) * FB_PYR_TH;
@@ -175,6 +182,9 @@ NSOF_GLOBAL k_fb_pyr(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT
         dst[(size_t)y * J.pitch + x] = v;
     }
 }
+
+static void (*const k_fb_pyr)(const FbJob *, const uint2 *, const float *, int) = k_fb_pyr_g<uint8_t>;
+static void (*const k_fb_pyr_f32)(const FbJob *, const uint2 *, const float *, int) = k_fb_pyr_g<float>;
 
 // ---------------------------------------------------------------------------------------------
 // S2-c: FarnebackPolyExp (A.5).  Tile TW x TH of R from an I tile with an n-pixel replicate halo

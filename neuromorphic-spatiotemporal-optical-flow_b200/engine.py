@@ -156,7 +156,10 @@ class Engine:
             if not (isinstance(out, np.ndarray) and out.dtype == np.float32 and out.shape == (h, w, 2)
                     and out.strides[1:] == (8, 4)):
                 raise error("flow must be None or a float32 (h, w, 2) array")
-        p = _fb_params(pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags)
+        if int(flags) & ~(4 | 256):
+            raise NotImplementedError(f"flags={flags}: cv2 defines OPTFLOW_USE_INITIAL_FLOW (4) and OPTFLOW_FARNEBACK_GAUSSIAN (256)")
+        p = _fb_params(pyr_scale, levels, winsize, iterations, poly_n, poly_sigma,
+                       int(flags) | (_lib.NSOF_FB_SRC_F32 if prev.dtype == np.float32 else 0))
         rc = self.lib.nsof_farneback_u8_host(self.handle, prev.ctypes.data, next.ctypes.data, h, w, prev.strides[0],
                                              next.strides[0], C.byref(p), out.ctypes.data, out.strides[0])
         self.lib.check(rc, "calcOpticalFlowFarneback")
@@ -174,11 +177,14 @@ class Engine:
         if prev.ndim != 2 or next.ndim != 2 or prev.shape != next.shape:
             raise error("(-215:Assertion failed) prev0.size() == next0.size() && prev0.channels() == "
                         "next0.channels() && prev0.channels() == 1")
-        if prev.dtype != np.uint8 or next.dtype != np.uint8:
-            raise NotImplementedError("only uint8 frames are implemented (the reference passes cv2 grey images)")
-        if prev.strides[1] != 1 or prev.strides[0] < prev.shape[1]:
+        if prev.dtype == np.float32 or next.dtype == np.float32:  # cv2 takes CV_32F frames too (no script passes them)
+            prev, next = np.asarray(prev, dtype=np.float32), np.asarray(next, dtype=np.float32)
+        elif prev.dtype != np.uint8 or next.dtype != np.uint8:
+            raise error("(-210:Unsupported format or combination of formats) frames must be uint8 or float32")
+        esz = prev.dtype.itemsize
+        if prev.strides[1] != esz or prev.strides[0] < prev.shape[1] * esz or prev.strides[0] % esz:
             prev = np.ascontiguousarray(prev)
-        if next.strides[1] != 1 or next.strides[0] < next.shape[1]:
+        if next.strides[1] != esz or next.strides[0] < next.shape[1] * esz or next.strides[0] % esz:
             next = np.ascontiguousarray(next)
         return prev, next
 
@@ -193,6 +199,8 @@ class Engine:
         keep, outs = [], []
         for i, (a, b) in enumerate(pairs):
             a, b = self._check_pair(a, b)
+            if a.dtype != np.uint8:
+                raise NotImplementedError("farneback_batch: uint8 crops (float32 frames go through calcOpticalFlowFarneback)")
             out = np.empty(a.shape + (2,), dtype=np.float32)
             keep.append((a, b))
             outs.append(out)

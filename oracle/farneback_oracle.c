@@ -75,8 +75,17 @@ NSOF_ORACLE_API void nsof_oracle_gaussian_kernel(int ksize, double sigma, float 
 }
 
 /* ---- A.2 + A.3: I_k = resize(GaussianBlur(f32(img)), (wk,hk), LINEAR) ---- */
+/* f32 != 0: `img` holds float32 samples (pitch in bytes) -- cv2 accepts CV_32F frames, convertTo(CV_32F) is then the
+ * identity; the reference's call sites pass uint8. */
+NSOF_ORACLE_API int nsof_oracle_pyr_level_ex(const uint8_t *img, int h, int w, ptrdiff_t pitch, int f32,
+                                             int ksize, double sigma, int hk, int wk, float *out);
 NSOF_ORACLE_API int nsof_oracle_pyr_level(const uint8_t *img, int h, int w, ptrdiff_t pitch,
                                           int ksize, double sigma, int hk, int wk, float *out)
+{
+    return nsof_oracle_pyr_level_ex(img, h, w, pitch, 0, ksize, sigma, hk, wk, out);
+}
+NSOF_ORACLE_API int nsof_oracle_pyr_level_ex(const uint8_t *img, int h, int w, ptrdiff_t pitch, int f32,
+                                             int ksize, double sigma, int hk, int wk, float *out)
 {
     if (ksize > 63 || !(ksize & 1)) return -1;
     float kern[64];
@@ -88,15 +97,18 @@ NSOF_ORACLE_API int nsof_oracle_pyr_level(const uint8_t *img, int h, int w, ptrd
     /* row pass (symmetric pairs, float accumulate) */
     for (int y = 0; y < h; y++) {
         const uint8_t *s = img + (ptrdiff_t)y * pitch;
+        const float *sf = (const float *)s;
+#define SRC(x_) (f32 ? sf[x_] : (float)s[x_])
         for (int x = 0; x < w; x++) {
-            float acc = kern[r] * (float)s[x];
+            float acc = kern[r] * SRC(x);
             for (int i = 1; i <= r; i++) {
-                float a = (float)s[reflect101(x - i, w)];
-                float b = (float)s[reflect101(x + i, w)];
+                float a = SRC(reflect101(x - i, w));
+                float b = SRC(reflect101(x + i, w));
                 acc = acc + kern[r + i] * (a + b);
             }
             tmp[(size_t)y * w + x] = acc;
         }
+#undef SRC
     }
     /* column pass */
     for (int y = 0; y < h; y++) {
@@ -559,7 +571,7 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
 {
     if (!prev || !next || h < 1 || w < 1) return -1;
     if (!(pyr_scale < 1.) || pyr_scale <= 0 || levels < 0 || winsize < 1 || iterations < 0 || poly_n < 1) return -1;
-    if (flags & ~(256 | 4)) return -3;
+    if (flags & ~(256 | 4 | 0x10000)) return -3;  /* 0x10000: float32 frames (libnsof's NSOF_FB_SRC_F32) */
     /* flags & 4 (OPTFLOW_USE_INITIAL_FLOW): flow_out holds the initial flow on entry (no call site of the reference
      * passes one; restated for the drop-in signature and pinned against cv2) */
     int hk[64], wk[64], ks[64];
@@ -589,7 +601,7 @@ NSOF_ORACLE_API int nsof_oracle_farneback_dump(const uint8_t *prev, const uint8_
         } else if (!prev_flow) memset(flow, 0, sizeof(float) * N * 2);
         else nsof_oracle_upsample_flow(prev_flow, ph, pw, H, W, pyr_scale, flow);
         for (int i = 0; i < 2; i++) {
-            int rc = nsof_oracle_pyr_level(i ? next : prev, h, w, i ? pitch1 : pitch0, ks[k], sg[k], H, W, I);
+            int rc = nsof_oracle_pyr_level_ex(i ? next : prev, h, w, i ? pitch1 : pitch0, (flags & 0x10000) != 0, ks[k], sg[k], H, W, I);
             if (rc) return rc;
             if (dump) dump(user, i, k, 0, I, H, W, 1);
             rc = nsof_oracle_polyexp(I, H, W, poly_n, poly_sigma, i ? R1 : R0);

@@ -117,6 +117,26 @@ def make_farneback_initflow():
     print("farneback_initflow_cv2.npz", len(names), "cases")
 
 
+def make_farneback_f32():
+    """cv2 accepts CV_32F frames as well as CV_8U (SURVEY.md 8(b) "Input conventions"); no reference call site passes
+    them.  Non-integer grey values so that the float path cannot be served by rounding to uint8."""
+    rng = np.random.default_rng(20261106)
+    out, names = {}, []
+    for (h, w) in [(96, 128), (75, 101)]:
+        a, b = synth_pair(rng, h, w)
+        af = (a.astype(np.float32) + rng.random((h, w)).astype(np.float32) * 0.9).astype(np.float32)
+        bf = (b.astype(np.float32) + rng.random((h, w)).astype(np.float32) * 0.9).astype(np.float32)
+        name = f"f32_{h}x{w}"
+        names.append(name)
+        out[f"{name}__prev"], out[f"{name}__next"] = af, bf
+        for pname in ("grasp", "autodriving_txt"):
+            out[f"{name}__{pname}"] = cv2.calcOpticalFlowFarneback(af, bf, None, **PARAM_SETS[pname])
+    out["cases"] = np.array(names)
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(OUT, "farneback_f32_cv2.npz"), **out)
+    print("farneback_f32_cv2.npz", names)
+
+
 def make_roi():
     out = {}
     for ds, script, consts, frame_hw in [
@@ -528,6 +548,9 @@ def make_realdata(which=("grasp", "autodriving")):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "f32":
+        make_farneback_f32()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "realdata":
         make_realdata(tuple(sys.argv[2:]) or ("grasp", "autodriving"))
         sys.exit(0)
@@ -549,6 +572,7 @@ if __name__ == "__main__":
         sys.exit(0)
     make_farneback()
     make_farneback_initflow()
+    make_farneback_f32()
     make_roi()
     make_events()
     make_events_scheme2()

@@ -86,6 +86,11 @@ class Oracle:
         prev = np.ascontiguousarray(prev)
         nxt = np.ascontiguousarray(nxt)
         h, w = prev.shape
+        if prev.dtype == np.float32:   # cv2 accepts CV_32F frames; the restatement takes them through flag 0x10000
+            assert nxt.dtype == np.float32
+            flags |= 0x10000
+        else:
+            assert prev.dtype == np.uint8 and nxt.dtype == np.uint8
         out = np.zeros((h, w, 2), np.float32) if flow is None else np.ascontiguousarray(flow, np.float32).copy()
         stages = {}
 
@@ -94,7 +99,7 @@ class Oracle:
             stages[(tag, k, it)] = arr
 
         fn = DUMP_FN(cb) if dump else C.cast(None, DUMP_FN)
-        rc = self.lib.nsof_oracle_farneback_dump(prev.ctypes.data, nxt.ctypes.data, h, w, w, w, pyr_scale, levels,
+        rc = self.lib.nsof_oracle_farneback_dump(prev.ctypes.data, nxt.ctypes.data, h, w, prev.strides[0], nxt.strides[0], pyr_scale, levels,
                                                  winsize, iterations, poly_n, poly_sigma, flags, out.ctypes.data, fn,
                                                  None)
         assert rc == 0, rc
@@ -128,6 +133,7 @@ class Golden:
         self.ev2 = np.load(os.path.join(GOLDEN, "events_scheme2_reference.npz"))
         self.seg = np.load(os.path.join(GOLDEN, "segment_reference.npz"))
         self.frames = np.load(os.path.join(GOLDEN, "frames_reference.npz"))
+        self.fb_f32 = np.load(os.path.join(GOLDEN, "farneback_f32_cv2.npz"))
 
 
 def segment_cases(seg):
@@ -357,3 +363,14 @@ def check_shared_frames(eng, device_batch=None):
         assert np.array_equal(got[i], want), i
         assert np.array_equal(off[i], want), i
     return singles
+
+
+def check_float32_frames(golden, farneback, what):
+    """cv2.calcOpticalFlowFarneback on FLOAT32 frames (non-integer grey values; tests/golden/farneback_f32_cv2.npz):
+    `farneback(prev, next, **params)` within the same tolerances as the uint8 cases."""
+    g = golden.fb_f32
+    for case in [str(c) for c in g["cases"]]:
+        prev, nxt = g[f"{case}__prev"], g[f"{case}__next"]
+        assert prev.dtype == np.float32
+        for pname in ("grasp", "autodriving_txt"):
+            assert_flow_close(farneback(prev, nxt, **PARAM_SETS[pname]), g[f"{case}__{pname}"], pname, f"{what} f32 {case}")

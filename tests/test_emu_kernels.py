@@ -345,3 +345,17 @@ def test_shared_frame_expansion_bit_identical(emu_engine):
             eng.lib.check(eng.lib.nsof_debug_share_frames(eng.handle, 1))
 
     helpers.check_shared_frames(eng, device_batch)
+
+
+def test_float32_frames_vs_cv2_golden(emu_engine, golden):
+    """cv2 accepts CV_32F frames; they take the typed direct pyramid kernel.  Strided views included."""
+    eng = emu_engine
+    helpers.check_float32_frames(golden, lambda a, b, **p: eng.calcOpticalFlowFarneback(a, b, None, **p), "emu vs cv2")
+    g = golden.fb_f32
+    a, b = g["f32_96x128__prev"], g["f32_96x128__next"]
+    big_a, big_b = np.zeros((120, 160), np.float32), np.zeros((120, 160), np.float32)
+    big_a[10:106, 20:148], big_b[10:106, 20:148] = a, b
+    got = eng.calcOpticalFlowFarneback(big_a[10:106, 20:148], big_b[10:106, 20:148], None, **helpers.PARAM_SETS["grasp"])
+    assert np.array_equal(got, eng.calcOpticalFlowFarneback(a, b, None, **helpers.PARAM_SETS["grasp"]))
+    mixed = eng.calcOpticalFlowFarneback(a, np.rint(b).astype(np.uint8), None, **helpers.PARAM_SETS["grasp"])  # mixed: both as float32
+    assert mixed.shape == got.shape

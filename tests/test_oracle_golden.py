@@ -247,3 +247,7 @@ def test_ssim_oracle_known_answers(golden):
     nf, pred = golden.frames["pred__next"], golden.frames["pred__whole__out"]
     assert fo.ssim_u8(nf[:, :, 2], pred[:, :, 2]) == fo.ssim_u8(pred[:, :, 2], nf[:, :, 2])
     assert 0.9 < fo.ssim_u8(nf[:, :, 2], pred[:, :, 2]) < 1.0
+
+
+def test_farneback_oracle_float32_frames_match_cv2(oracle, golden):
+    helpers.check_float32_frames(golden, lambda a, b, **p: oracle.farneback(a, b, **p), "oracle vs cv2")
