@@ -116,6 +116,7 @@ extern "C" int nsof_create(int device, nsof_handle **out)
     nsof_handle *h = new nsof_handle();
     h->device = device;
     h->last_plan = new std::vector<FbItemPlan>();
+    if (const char *e = getenv("NSOF_SHARE_FRAMES")) h->dbg_no_dedup = e[0] == '0';  // A/B measurements (default: on)
     *out = h;
     return NSOF_OK;
 }

@@ -1363,8 +1363,11 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
         }
     }
     NSOF_SYNC();
+// FB_PP_D8 = 1: eight outputs per thread, one moment plane at a time (half the shared-memory loads per output, one
+// round of 256 items per tile).  Measured SLOWER than the 4-output form (full-frame step: fb_pyr_polyexp 3.26 vs 2.90 ms,
+// profiles/r2_pyr_polyexp_packed_ab.txt): longer dependent chains per thread and 2 x fewer independent items. Off.
 #ifndef FB_PP_D8
-#define FB_PP_D8 1
+#define FB_PP_D8 0
 #endif
 #if FB_PP_D8
     // ---- D: horizontal pass, EIGHT outputs per thread, one moment plane at a time (planes 0, 2, 1; the outputs that
