@@ -947,25 +947,32 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         const int lxa = i % TW, lya = i / TW, lxb = ib % TW, lyb = ib / TW;
         const int xa = tx0 + lxa, ya = ty0 + lya, xb = tx0 + lxb, yb = ty0 + lyb;
         const bool va = xa < J.w && ya < J.y_hi, vb = ib < TW * TH && xb < J.w && yb < J.y_hi;
-        if (!va && !vb) continue;
-        // ONE code path: a pixel without a partner is paired with itself (both halves of every operand hold it) and only
-        // the valid halves are stored.  Which pixels lose their partner depends on where the tiles start; a separate
-        // scalar routine for them would differ from the packed one in the last bit (compiler-chosen FMA contraction),
-        // and a row-tiled run (tiles start at the band's first row) must reproduce the untiled flow bit for bit.
-        const int lxA = va ? lxa : lxb, lyA = va ? lya : lyb, lxB = vb ? lxb : lxa, lyB = vb ? lyb : lya;
-        const int xA = tx0 + lxA, yA = ty0 + lyA, xB = tx0 + lxB, yB = ty0 + lyB;
-        const float2 fa = *(const float2 *)(sM + (lyA / RPP) * SP + TH * PW + (lyA % RPP) * (2 * TW) + 2 * lxA);
-        const float2 fb = *(const float2 *)(sM + (lyB / RPP) * SP + TH * PW + (lyB % RPP) * (2 * TW) + 2 * lxB);
-        const size_t oa = (size_t)yA * J.pitch + xA, ob = (size_t)yB * J.pitch + xB;
-        float2 r0v[5], mm[5];
+        if (va && vb) {
+            const float2 fa = *(const float2 *)(sM + (lya / RPP) * SP + TH * PW + (lya % RPP) * (2 * TW) + 2 * lxa);
+            const float2 fb = *(const float2 *)(sM + (lyb / RPP) * SP + TH * PW + (lyb % RPP) * (2 * TW) + 2 * lxb);
+            const size_t oa = (size_t)ya * J.pitch + xa, ob = (size_t)yb * J.pitch + xb;
+            float2 r0v[5], mm[5];
 #pragma unroll
-        for (int c = 0; c < 5; c++) r0v[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
-        if (J.guard) { fb_um_guard(J, yA, fa.y); fb_um_guard(J, yB, fb.y); }
-        fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, xA, yA, xB, yB, make_float2(fa.x, fb.x), make_float2(fa.y, fb.y), r0v, mm);
+            for (int c = 0; c < 5; c++) r0v[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
+            if (J.guard) { fb_um_guard(J, ya, fa.y); fb_um_guard(J, yb, fb.y); }
+            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, xa, ya, xb, yb, make_float2(fa.x, fb.x), make_float2(fa.y, fb.y), r0v, mm);
 #pragma unroll
-        for (int c = 0; c < 5; c++) {
-            if (va) Mout[c * plane + oa] = mm[c].x;
-            if (vb) Mout[c * plane + ob] = mm[c].y;
+            for (int c = 0; c < 5; c++) { Mout[c * plane + oa] = mm[c].x; Mout[c * plane + ob] = mm[c].y; }
+        } else if (va || vb) {
+            const int lx = va ? lxa : lxb, ly = va ? lya : lyb, x = va ? xa : xb, y = va ? ya : yb;
+            const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+            const size_t o = (size_t)y * J.pitch + x;
+            // a pixel without a partner goes through the SAME packed routine (both halves = this pixel): which pixels
+            // lose their partner depends on where the tiles start, and the scalar routine's compiler-chosen FMA
+            // contraction differs from the packed one in the last bit -- a row-tiled run (tiles start at the band's
+            // first row) must reproduce the untiled flow bit for bit
+            float2 r0v[5], mm[5];
+#pragma unroll
+            for (int c = 0; c < 5; c++) { const float t = NSOF_LDG(R0 + c * plane + o); r0v[c] = make_float2(t, t); }
+            if (J.guard) fb_um_guard(J, y, f.y);
+            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, x, y, x, y, make_float2(f.x, f.x), make_float2(f.y, f.y), r0v, mm);
+#pragma unroll
+            for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c].x;
         }
     }
 #else
