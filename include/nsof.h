@@ -210,6 +210,17 @@ NSOF_API int nsof_ssim_u8(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, i
 NSOF_API int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
                                ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out);
 
+/* nsof_ssim_u8 for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and
+ * result as nsof_ssim_u8; the per-CTA partial sums live in a file-scope `static __device__` array, so the call makes
+ * no cudaMalloc / cudaFree and touches no growable buffer.  Limit: at most 4096 tiles of 32 x 32 interior pixels
+ * (1080 x 1920 = 2040 tiles, 2048 x 2048 = 4096); larger images return NSOF_ERR_UNSUPPORTED.  The 32 KB array is held
+ * by every GPU that loads the library until exit and is shared by all calls on a device: calls that overlap on the GPU
+ * race (serialise them on one stream); it keeps the last call's contents and needs no clearing. */
+NSOF_API int nsof_ssim_u8_noalloc(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                                  ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range,
+                                  double *out_dev, void *cuda_stream);
+
 /* Pyramid geometry exactly as the driver computes it (A.1): returns the number of scales and
  * fills hk/wk/ksize/sigma[0 .. scales-1] (any pointer may be NULL).  Pure host arithmetic. */
 NSOF_API int nsof_fb_level_geometry(int height, int width, double pyr_scale, int levels, int *hk, int *wk,

@@ -134,6 +134,8 @@ _SIGNATURES = {
                                        C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_ssize_t]),
     "nsof_ssim_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int,
                                C.c_double, C.c_void_p, C.c_void_p]),
+    "nsof_ssim_u8_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int,
+                                       C.c_int, C.c_double, C.c_void_p, C.c_void_p]),
     "nsof_ssim_u8_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int,
                                     C.c_int, C.c_double, _P(C.c_double)]),
     "nsof_fb_level_geometry": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int, _P(C.c_int), _P(C.c_int),

@@ -356,3 +356,70 @@ extern "C" int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_p
     NSOF_CUDA_TRY(cudaStreamSynchronize(stream));
     return NSOF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// nsof_ssim_u8_noalloc: the SSIM above for callers that may not allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-CTA partial sums live in a file-scope device array instead of the handle's growable scratch buffer, so the
+// call allocates nothing (no cudaMalloc / cudaFree, no growable buffer).  Limits and rules:
+//   * at most NSOF_SSIM_NOALLOC_MAX_TILES (4096) tiles of 32 x 32 interior pixels, e.g. 1080 x 1920 (2040 tiles) or
+//     2048 x 2048 (4096); larger images are rejected with NSOF_ERR_UNSUPPORTED;
+//   * the array (32 KB) is held by every GPU that loads the library until the process exits;
+//   * every call on a device shares it: calls that overlap on the GPU (different streams) race -- serialise them;
+//   * it keeps the last call's contents; nothing has to start at zero (k_ssim_tiles writes partial[0 .. tiles) before
+//     k_ssim_finish reads exactly that range).
+// In host code `g_ssim_scratch` is only a stand-in for the symbol: its device address is taken once per device, with
+// that device current, through cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------------------------------
+#define NSOF_SSIM_NOALLOC_MAX_TILES 4096
+#define NSOF_MAX_DEVICES 64
+#ifdef NSOF_EMU
+static double g_ssim_scratch[NSOF_SSIM_NOALLOC_MAX_TILES];
+#else
+static __device__ __align__(256) double g_ssim_scratch[NSOF_SSIM_NOALLOC_MAX_TILES];
+#endif
+static double *g_ssim_scratch_ptr[NSOF_MAX_DEVICES];  // per device; written once (benign if two threads race: same value)
+
+static int ssim_scratch_address(int device, double **out)
+{
+    if (device < 0 || device >= NSOF_MAX_DEVICES) NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "ssim_noalloc: device %d", device);
+    if (!g_ssim_scratch_ptr[device]) {
+#ifdef NSOF_EMU
+        g_ssim_scratch_ptr[device] = g_ssim_scratch;
+#else
+        double *p = nullptr;
+        NSOF_CUDA_TRY(cudaGetSymbolAddress((void **)&p, g_ssim_scratch));  // the device is current (caller set it)
+        g_ssim_scratch_ptr[device] = p;
+#endif
+    }
+    *out = g_ssim_scratch_ptr[device];
+    return NSOF_OK;
+}
+
+extern "C" int nsof_ssim_u8_noalloc(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
+                                    ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range,
+                                    double *out_dev, void *cuda_stream)
+{
+    if (!h || !a || !b || !out_dev) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim_noalloc: NULL argument");
+    if (height < 7 || width < 7) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim_noalloc: win_size 7 exceeds the image extent");
+    if (a_pixel_stride < 1 || b_pixel_stride < 1 || a_pitch < (ptrdiff_t)width * a_pixel_stride || b_pitch < (ptrdiff_t)width * b_pixel_stride)
+        NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim_noalloc: bad pitch / pixel stride");
+    const int iw = width - 6, ih = height - 6;
+    const long long tiles = (long long)((iw + SSIM_TW - 1) / SSIM_TW) * ((ih + SSIM_TH - 1) / SSIM_TH);
+    if (tiles > NSOF_SSIM_NOALLOC_MAX_TILES)
+        NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "ssim_noalloc: %d x %d needs %lld tiles of 32 x 32, the static scratch holds %d (use nsof_ssim_u8)",
+                  height, width, tiles, NSOF_SSIM_NOALLOC_MAX_TILES);
+    NSOF_CUDA_TRY(cudaSetDevice(h->device));
+    double *scratch = nullptr;
+    int rc = ssim_scratch_address(h->device, &scratch);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    SsimJob J = {a, b, a_pitch, b_pitch, a_pixel_stride, b_pixel_stride, height, width,
+                 (0.01 * data_range) * (0.01 * data_range), (0.03 * data_range) * (0.03 * data_range), scratch};
+    const size_t smem = (2 * (SSIM_TW + 6) * (SSIM_TH + 6) + 5 * SSIM_TW * (SSIM_TH + 6)) * sizeof(int);
+    NSOF_KLAUNCH(h, NSOF_K_SSIM, 2. * height * width, k_ssim_tiles, (int)tiles, 1, 1, 256, smem, stream, J);
+    NSOF_KLAUNCH(h, NSOF_K_SSIM, 8. * tiles, k_ssim_finish, 1, 1, 1, 32, 0, stream, (const double *)scratch, (int)tiles,
+                 (double)iw * ih, out_dev);
+    NSOF_CUDA_TRY(cudaGetLastError());
+    return NSOF_OK;
+}
