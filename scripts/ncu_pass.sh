@@ -6,9 +6,9 @@
 #   4. --set full of three level-0 launches of the dominant kernel (source-level pages imported)
 # usage: scripts/ncu_pass.sh <tag>      outputs under gpurun_out/<tag>_*
 set -u
-TAG=${1:-r1v7}
+TAG=${1:-r2}
 OUT=gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline --min-seconds 0"
 mkdir -p $OUT
 $CMD > $OUT/${TAG}_plain.json 2> $OUT/${TAG}_plain.err || { echo "plain run failed"; tail -5 $OUT/${TAG}_plain.err; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:^k_|_t<" -c 4000 --csv \
