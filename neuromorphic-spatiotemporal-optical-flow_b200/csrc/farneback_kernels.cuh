@@ -1159,7 +1159,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
             const int sh8 = (shift & 3) * 8;
             const uint32_t u = sh8 ? ((w0 >> sh8) | (w1 << (32 - sh8))) : w0;
             *(float4 *)(sS + sy * SW + 4 * g) =
-                make_float4((float)(u & 255u), (float)((u >> 8) & 255u), (float)((u >> 16) & 255u), (float)(u >> 24));
+                make_float4(nsof_u8_to_f(u, 0), nsof_u8_to_f(u, 1), nsof_u8_to_f(u, 2), nsof_u8_to_f(u, 3));
         }
     } else {
         for (int sy = warp; sy < SHN; sy += nw) {
@@ -1643,14 +1643,15 @@ NSOF_GLOBAL k_fb_pyr_sep(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_REST
             const bool cb = ci + NSOF_WARP < 2 * twn;
             const int o0 = cols[ci] - Xmin, o1 = cols[cb ? ci + NSOF_WARP : ci] - Xmin;
             const uint8_t *c00 = row0 + o0, *c01 = row0 + o1, *c10 = row1 + o0, *c11 = row1 + o1;
-            float a00 = g0 * (float)c00[0], a01 = g0 * (float)c01[0], a10 = g0 * (float)c10[0], a11 = g0 * (float)c11[0];
+            float a00 = g0 * nsof_small_int_to_f(c00[0]), a01 = g0 * nsof_small_int_to_f(c01[0]);
+            float a10 = g0 * nsof_small_int_to_f(c10[0]), a11 = g0 * nsof_small_int_to_f(c11[0]);
             // the two taps at distance i are added as integers (exact) and converted once
             for (int i = 1; i <= r; i++) {
                 const float g = sg[i];
-                a00 = a00 + g * (float)((int)c00[-i] + (int)c00[i]);
-                a01 = a01 + g * (float)((int)c01[-i] + (int)c01[i]);
-                a10 = a10 + g * (float)((int)c10[-i] + (int)c10[i]);
-                a11 = a11 + g * (float)((int)c11[-i] + (int)c11[i]);
+                a00 = a00 + g * nsof_small_int_to_f((int)c00[-i] + (int)c00[i]);
+                a01 = a01 + g * nsof_small_int_to_f((int)c01[-i] + (int)c01[i]);
+                a10 = a10 + g * nsof_small_int_to_f((int)c10[-i] + (int)c10[i]);
+                a11 = a11 + g * nsof_small_int_to_f((int)c11[-i] + (int)c11[i]);
             }
             sHb[sy * 2 * TW + ci] = a00;
             if (cb) sHb[sy * 2 * TW + ci + NSOF_WARP] = a01;

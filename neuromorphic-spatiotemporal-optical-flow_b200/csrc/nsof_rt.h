@@ -104,6 +104,20 @@ __device__ __forceinline__ double nsof_warp_sum_f64(double v)
     const T &J = J##_s
 #endif
 
+// Small non-negative integer (< 2^23) -> float without the conversion pipe: the integer is planted in the mantissa of
+// 2^23 and 2^23 is subtracted (exact).  I2F runs on the quarter-rate XU pipe; this is one integer add / byte permute and
+// one FADD.  nsof_u8_to_f(word, k): byte k of a packed word.
+#ifdef NSOF_EMU
+static inline float nsof_small_int_to_f(int v) { return (float)v; }
+static inline float nsof_u8_to_f(uint32_t word, int k) { return (float)((word >> (8 * k)) & 255u); }
+#else
+__device__ __forceinline__ float nsof_small_int_to_f(int v) { return __int_as_float(0x4B000000 + v) - 8388608.f; }
+__device__ __forceinline__ float nsof_u8_to_f(uint32_t word, int k)
+{
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + (unsigned)k)) - 8388608.f;
+}
+#endif
+
 NSOF_HD int nsof_imin(int a, int b) { return a < b ? a : b; }
 NSOF_HD int nsof_imax(int a, int b) { return a > b ? a : b; }
 NSOF_HD int nsof_clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
