@@ -137,6 +137,30 @@ def make_farneback_f32():
     print("farneback_f32_cv2.npz", names)
 
 
+def make_hostio():
+    """`py_cpu_nms` of optical_flow_ob.py:96-135 (source-sliced) on seeded box sets, for hostio.nms."""
+    src = open(os.path.join(REF, "optical_flow_ob.py"), encoding="utf-8").read()
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "py_cpu_nms"]
+    ns = dict(np=np)
+    exec(compile(ast.Module(body=body, type_ignores=[]), "optical_flow_ob.py", "exec"), ns)
+    rng = np.random.default_rng(5)
+    out = {}
+    for k, n in enumerate([1, 2, 7, 40, 120]):
+        xy = rng.integers(0, 300, (n, 2))
+        wh = rng.integers(5, 120, (n, 2))
+        dets = np.concatenate([xy, xy + wh, rng.integers(500, 9000, (n, 1))], axis=1).astype(np.float64)
+        if n >= 7:
+            dets[1, :4] = dets[0, :4]            # an exact duplicate box, and a tie in the scores
+            dets[2, 4] = dets[3, 4]
+        for th in (0.2, 0.5):
+            out[f"nms__{k}__dets"] = dets
+            out[f"nms__{k}__keep_{th}"] = np.array(ns["py_cpu_nms"](dets, th), dtype=np.int64)
+    out["n_cases"] = np.array(5)
+    np.savez_compressed(os.path.join(OUT, "hostio_reference.npz"), **out)
+    print("hostio_reference.npz")
+
+
 def make_roi():
     out = {}
     for ds, script, consts, frame_hw in [
@@ -548,6 +572,9 @@ def make_realdata(which=("grasp", "autodriving")):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "hostio":
+        make_hostio()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "f32":
         make_farneback_f32()
         sys.exit(0)
@@ -578,4 +605,5 @@ if __name__ == "__main__":
     make_events_scheme2()
     make_segment()
     make_frames()
+    make_hostio()
     make_realdata()
