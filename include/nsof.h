@@ -210,6 +210,17 @@ NSOF_API int nsof_ssim_u8(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, i
 NSOF_API int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_pitch, int a_pixel_stride, const uint8_t *b,
                                ptrdiff_t b_pitch, int b_pixel_stride, int height, int width, double data_range, double *out);
 
+/* ---- JPEG frames straight to grey on the device (optical_flow_seg.py:439-443) --------------
+ * `cv2.imread(path)` + `cv2.cvtColor(frame, COLOR_RGB2GRAY)` for `n` JPEG streams in HOST memory, all `height` x `width`:
+ * grey frame i lands in DEVICE memory at gray + i * frame_stride (rows `pitch` bytes apart), so a frame crosses PCIe as
+ * its JPEG bytes (~0.2 MB at 1080p) instead of decoded pixels.  Entropy decode + IDCT are nvJPEG's (library code, loaded
+ * with dlopen on first use: NSOF_ERR_UNSUPPORTED when libnvjpeg is absent); the BGR -> grey step is the exact integer
+ * formula of nsof_rgb2gray_u8.  The decoder is not cv2's libjpeg-turbo: grey values agree to a few levels (tests state the
+ * bound), not bit for bit.  nsof_jpeg_info: size of one stream (host-side parse). */
+NSOF_API int nsof_jpeg_info(nsof_handle *h, const uint8_t *jpeg, size_t bytes, int *height, int *width);
+NSOF_API int nsof_jpeg_decode_gray(nsof_handle *h, const uint8_t *const *jpegs, const size_t *bytes, int n, int height,
+                                   int width, uint8_t *gray, ptrdiff_t pitch, ptrdiff_t frame_stride, void *cuda_stream);
+
 /* nsof_ssim_u8 for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and
  * result as nsof_ssim_u8; the per-CTA partial sums live in a file-scope `static __device__` array, so the call makes

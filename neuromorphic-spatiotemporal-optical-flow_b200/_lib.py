@@ -132,6 +132,9 @@ _SIGNATURES = {
     "nsof_remap_flow_batch": (C.c_int, [C.c_void_p, _P(WarpDesc), C.c_int, C.c_int, C.c_void_p]),
     "nsof_remap_flow_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                        C.c_ssize_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_ssize_t]),
+    "nsof_jpeg_info": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, _P(C.c_int), _P(C.c_int)]),
+    "nsof_jpeg_decode_gray": (C.c_int, [C.c_void_p, _P(C.c_void_p), _P(C.c_size_t), C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                        C.c_ssize_t, C.c_ssize_t, C.c_void_p]),
     "nsof_ssim_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int, C.c_int,
                                C.c_double, C.c_void_p, C.c_void_p]),
     "nsof_ssim_u8_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_ssize_t, C.c_int, C.c_void_p, C.c_ssize_t, C.c_int, C.c_int,

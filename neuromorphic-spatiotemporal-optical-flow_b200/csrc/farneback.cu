@@ -128,6 +128,8 @@ extern "C" int nsof_destroy(nsof_handle *h)
     cudaDeviceSynchronize();
     h->arena.release();
     h->tile_buf.release();
+    nsof_jpeg_release(h);
+    h->jpeg_buf.release();
     fb_link_close(h);
     h->link_flags.release();
     h->link_tab.release();

@@ -74,6 +74,8 @@ struct nsof_handle {
     unsigned long long *link_up_flags = nullptr, *link_dn_flags = nullptr;
     void *link_arena_seen = nullptr;  // this rank's arena address when the neighbours were attached
     std::vector<void *> link_ipc;     // IPC mappings to close
+    void *jpeg = nullptr;   // nvJPEG handle + state (decode.cu), created on first use
+    NsofDevBuf jpeg_buf;    // decoded BGR frames of the current nsof_jpeg_decode_gray call
     NsofDevBuf clear_tab;  // rectangle table of nsof_flow_clear
     NsofDevBuf guard_buf;  // halo guard flag of a tiled batch
     FbBatchCtx *ctx = nullptr;  // plan, tables and launch geometry of the current batch
@@ -140,6 +142,7 @@ static inline void nsof_prof_post(nsof_handle *h, cudaStream_t st)
         nsof_prof_post((h), (stream));                                              \
     } while (0)
 
+void nsof_jpeg_release(nsof_handle *h);  // decode.cu
 int nsof_stage_acquire(nsof_handle *h, size_t bytes, NsofStageSlot **slot);
 // device <- pinned staging slot by a kernel (no copy engine); both sides allocated with >= 16 bytes of slack
 int nsof_table_upload(nsof_handle *h, void *dst, NsofStageSlot *slot, size_t bytes, cudaStream_t stream);

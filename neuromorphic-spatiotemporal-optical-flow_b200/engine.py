@@ -438,6 +438,29 @@ class Engine:
                                                       out.strides[0]), "cvtColor_rgb2gray")
         return out
 
+    def imread_gray_device(self, jpeg_blobs, out=None, stream_ptr: int = 0):
+        """`cv2.cvtColor(cv2.imread(path), cv2.COLOR_RGB2GRAY)` (optical_flow_seg.py:439-443) for a list of JPEG byte
+        strings of one size -> uint8 torch tensor (n, H, W) on the device (`out`: write into this tensor instead).
+        Decoder = nvJPEG, not cv2's libjpeg-turbo: grey levels agree to a few units, not bit for bit."""
+        import torch
+        blobs = [bytes(b) for b in jpeg_blobs]
+        n = len(blobs)
+        if n == 0:
+            raise error("(-215:Assertion failed) !_src.empty()")
+        bufs = [np.frombuffer(b, dtype=np.uint8) for b in blobs]
+        hh, ww = C.c_int(), C.c_int()
+        self.lib.check(self.lib.nsof_jpeg_info(self.handle, bufs[0].ctypes.data, bufs[0].size, C.byref(hh), C.byref(ww)), "jpeg_info")
+        H, W = hh.value, ww.value
+        if out is None:
+            out = torch.empty((n, H, W), dtype=torch.uint8, device=f"cuda:{self.device}")
+        assert out.dtype == torch.uint8 and tuple(out.shape) == (n, H, W) and out.stride(2) == 1
+        ptrs = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        lens = (C.c_size_t * n)(*[b.size for b in bufs])
+        self.lib.check(self.lib.nsof_jpeg_decode_gray(self.handle, ptrs, lens, n, H, W, out.data_ptr(), out.stride(1), out.stride(0),
+                                                      C.c_void_p(stream_ptr or torch.cuda.current_stream(self.device).cuda_stream)),
+                       "jpeg_decode_gray")
+        return out
+
     def remap_flow(self, next_frame, flow_region, x_min, y_min, flow_sign=1):
         """optical_flow_prediction.py:281-297 for one region: flow_map = (x, y) + flow_region as float32, every channel
         of `next_frame` (uint8 (H, W) or (H, W, C)) remapped with INTER_LINEAR / BORDER_REPLICATE -> uint8 region."""

@@ -630,6 +630,43 @@ def test_frames_vs_reference(gpu_engine, golden):
         assert np.array_equal(d_out[i].cpu().numpy(), fo.task_results(bgr[i], bgr[i], flow[i], r)), i
 
 
+def test_jpeg_decode_to_grey_vs_cv2(gpu_engine, oracle):
+    """JPEG bytes -> grey frames in HBM (nvJPEG entropy decode + IDCT, our exact grey formula) vs
+    cv2.imdecode + cvtColor(COLOR_RGB2GRAY) of the same bytes (optical_flow_seg.py:439-443).  The decoders differ
+    (libjpeg-turbo: islow IDCT + fancy upsampling), so grey levels agree to a few units, not bit for bit; measured on
+    these frames: mean |d| 0.52, max 7 grey levels (chroma upsampling); bounds below: mean < 0.8, max <= 10.  The decoder difference carries into the flow: mean EPE 0.014 px between the flow of the
+    device-decoded pair and the flow of cv2's frames on a real 480 x 600 ROI crop (bound 0.05) -- a property of feeding
+    another JPEG decoder's pixels to ANY Farneback, so frames decoded by cv2 remain the parity path."""
+    import os
+
+    import torch
+    cv2 = pytest.importorskip("cv2")
+    d = os.path.join(helpers.GOLDEN, "jpeg")
+    blobs = [open(os.path.join(d, f), "rb").read() for f in ("grasp_41.jpg", "grasp_42.jpg")]
+    want = [cv2.cvtColor(cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR), cv2.COLOR_RGB2GRAY) for b in blobs]
+    got = gpu_engine.imread_gray_device(blobs).cpu().numpy()
+    assert got.shape == (2, 1920, 1080) and got.dtype == np.uint8
+    for g, w in zip(got, want):
+        diff = np.abs(g.astype(np.int16) - w.astype(np.int16))
+        assert diff.mean() < 0.8 and diff.max() <= 10, (diff.mean(), diff.max())
+    one = gpu_engine.imread_gray_device([open(os.path.join(d, "autodriving_20.jpg"), "rb").read()]).cpu().numpy()
+    w1 = cv2.cvtColor(cv2.imdecode(np.frombuffer(open(os.path.join(d, "autodriving_20.jpg"), "rb").read(), np.uint8), cv2.IMREAD_COLOR),
+                      cv2.COLOR_RGB2GRAY)
+    assert one.shape == (1, 801, 801) and np.abs(one[0].astype(np.int16) - w1.astype(np.int16)).max() <= 10
+    # pitched destination + the flow of a real ROI crop computed from device-decoded frames
+    dst = torch.zeros((2, 1920, 1152), dtype=torch.uint8, device="cuda")
+    gpu_engine.imread_gray_device(blobs, out=dst[:, :, :1080])
+    torch.cuda.synchronize()
+    assert np.array_equal(dst[:, :, :1080].cpu().numpy(), got) and not dst[:, :, 1080:].any()
+    p = helpers.PARAM_SETS["grasp"]
+    crop = (slice(700, 1180), slice(300, 900))
+    f_dev = gpu_engine.calcOpticalFlowFarneback(got[0][crop], got[1][crop], None, **p)
+    f_cv = gpu_engine.calcOpticalFlowFarneback(want[0][crop], want[1][crop], None, **p)
+    assert helpers.flow_err(f_dev, f_cv).mean() <= 0.05
+    with pytest.raises(Exception):
+        gpu_engine.imread_gray_device([b"not a jpeg at all"])
+
+
 def test_ssim_vs_oracle(gpu_engine, golden):
     """calculateIntegralError (optical_flow_prediction.py:113-115) on the device, incl. a 1080p
     BGR frame pair through the channel-2 view; tolerance 1e-12 (integer window sums are exact, the mean is float64)."""
