@@ -341,7 +341,9 @@ extern "C" int nsof_ssim_u8_host(nsof_handle *h, const uint8_t *a, ptrdiff_t a_p
     if (!h || !a || !b || !out) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: NULL argument");
     if (height < 1 || width < 1 || a_pixel_stride < 1 || b_pixel_stride < 1) NSOF_FAIL(NSOF_ERR_BAD_ARG, "ssim: bad geometry");
     NSOF_CUDA_TRY(cudaSetDevice(h->device));
-    const size_t rowa = (size_t)width * a_pixel_stride, rowb = (size_t)width * b_pixel_stride;
+    // bytes of a row that hold pixels: the last pixel is ONE byte (a channel view of an interleaved frame starts at the
+    // channel's offset, so width * stride bytes from there would run past the end of the caller's array)
+    const size_t rowa = (size_t)(width - 1) * a_pixel_stride + 1, rowb = (size_t)(width - 1) * b_pixel_stride + 1;
     const size_t pa = (rowa + 255) & ~(size_t)255, pb = (rowb + 255) & ~(size_t)255;
     int rc = h->io.ensure(pa * height + pb * height + 256);
     if (rc) return rc;

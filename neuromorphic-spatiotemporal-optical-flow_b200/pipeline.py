@@ -82,7 +82,9 @@ class SequencePipeline:
         self.s1_eng = Engine(engine.device, lib=engine.lib) if self.overlap else engine
         # high priority: stage 1 is the latency chain of the step and needs few SM resources; its blocks must not
         # queue behind the stage-2 CTAs that fill the machine
-        self.side = torch.cuda.Stream(self.dev, priority=-1) if self.overlap else None
+        import os
+        self.side = (torch.cuda.Stream(self.dev, priority=int(os.environ.get("NSOF_S1_PRIORITY", "-1")))
+                     if self.overlap else None)
         self.ev_chunk = [torch.cuda.Event(enable_timing=True) for _ in self.chunks]
         # stage 2 of successive chunks alternates between the caller's stream and `s2_streams - 1` extra streams (own
         # handles): the small coarse-level launches of one batch run beside the large fine-level ones of another
