@@ -250,6 +250,7 @@ NSOF_API int nsof_debug_fuse(nsof_handle *h, int enable);
 /* enable = 0 keeps every launch of nsof_farneback_batch on the caller's stream (default: the pyramid + PolyExp
  * launches of the finer levels run on internal streams beside the coarse-level iterations). */
 NSOF_API int nsof_debug_share_frames(nsof_handle *h, int enable);
+NSOF_API int nsof_debug_lanczos_f64(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fork(nsof_handle *h, int enable);
 /* enable = 1 keeps the large blur+solve tile on every level (default: latency-bound levels take the small one). */
 NSOF_API int nsof_debug_big_tiles(nsof_handle *h, int enable);

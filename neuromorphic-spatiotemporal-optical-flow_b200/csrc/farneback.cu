@@ -117,6 +117,7 @@ extern "C" int nsof_create(int device, nsof_handle **out)
     h->device = device;
     h->last_plan = new std::vector<FbItemPlan>();
     if (const char *e = getenv("NSOF_SHARE_FRAMES")) h->dbg_no_dedup = e[0] == '0';  // A/B measurements (default: on)
+    if (const char *e = getenv("NSOF_LANCZOS_F64")) h->dbg_lz_f64 = e[0] == '1';     // A/B: FP64 Lanczos kernels
     *out = h;
     return NSOF_OK;
 }
@@ -1652,7 +1653,7 @@ extern "C" int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, 
 
 #ifdef NSOF_EMU
 namespace nsof_emu {
-thread_local int bx, by, bz, gdx;
+thread_local int bx, by, bz, gdx, gdy;
 thread_local unsigned char *smem;
 }
 #endif

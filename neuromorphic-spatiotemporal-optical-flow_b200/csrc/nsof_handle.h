@@ -87,6 +87,9 @@ struct nsof_handle {
     int lz_key[4] = {0, 0, 0, 0};
     int lz_P[2] = {0, 0};  // seg_rows, n_seg of the cached Lanczos geometry
     bool lz_smem_set = false;
+    int lz_mma[3] = {0, 0, 0};        // windows of 8 cells, padded width, weight exponent of the tensor-core column pass
+    size_t lz_off[3] = {0, 0, 0};     // byte offsets of yband / window table / int8 weight slices in `lz`
+    bool dbg_lz_f64 = false;          // force the FP64 Lanczos kernels (tests, A/B)
     bool roi_smem_set = false;  // k_s1_roi opted into > 48 KB of dynamic shared memory on this handle's device
     NsofStageSlot stage[4];
     int stage_next = 0;

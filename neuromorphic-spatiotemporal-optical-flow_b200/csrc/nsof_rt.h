@@ -27,13 +27,14 @@ static inline uint2 make_uint2(unsigned x, unsigned y) { uint2 r = {x, y}; retur
 static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r; }
 static inline float4 make_float4(float x, float y, float z, float w) { float4 r = {x, y, z, w}; return r; }
 namespace nsof_emu {
-extern thread_local int bx, by, bz, gdx;
+extern thread_local int bx, by, bz, gdx, gdy;
 extern thread_local unsigned char *smem;
 template <class F> static inline void launch(int gx, int gy, int gz, size_t smem_bytes, F f)
 {
     std::vector<unsigned char> buf(smem_bytes + 64);
     smem = buf.data();
     gdx = gx;
+    gdy = gy;
     for (bz = 0; bz < gz; bz++)
         for (by = 0; by < gy; by++)
             for (bx = 0; bx < gx; bx++) f();
@@ -51,6 +52,7 @@ template <class F> static inline void launch(int gx, int gy, int gz, size_t smem
 #define NSOF_NT 1
 #define NSOF_WARP 1
 static inline int nsof_grid_x() { return nsof_emu::gdx; }
+static inline int nsof_grid_y() { return nsof_emu::gdy; }
 static inline double nsof_warp_sum_f64(double v) { return v; }
 #define NSOF_SYNC() ((void)0)
 #define NSOF_DYN_SMEM(name) unsigned char *name = nsof_emu::smem
@@ -72,6 +74,7 @@ static inline double nsof_warp_sum_f64(double v) { return v; }
 #define NSOF_NT ((int)blockDim.x)
 #define NSOF_WARP 32
 __device__ __forceinline__ int nsof_grid_x() { return (int)gridDim.x; }
+__device__ __forceinline__ int nsof_grid_y() { return (int)gridDim.y; }
 // fixed-order butterfly: deterministic for a given lane assignment
 __device__ __forceinline__ double nsof_warp_sum_f64(double v)
 {

@@ -598,3 +598,132 @@ NSOF_GLOBAL k_s1_roi(const double *NSOF_RESTRICT currents, nsof_roi_params p, co
         if (n_components) n_components[s] = ncomp;
     }
 }
+
+// ---------------------------------------------------------------------------------------------
+// S1-a on the tensor cores.  compress_image is a dense contraction, cells = Wy . img . Wx^T, and img is uint8: the
+// COLUMN pass (contraction over x, the contiguous axis) is an exact integer GEMM once the double weights are cut
+// into int8 slices (Ozaki splitting):  Wx[c][x] = 2^-E * sum_{s<7} q_s[c][x] * 2^{-7(s+1)},  |q_s| <= 127  (49 bits of
+// every weight).  Every slice product sum_x q_s[c][x] * img[y][x] is an int32 dot product the
+// int8 tensor-core path computes exactly (mma.sync m16n8k32 u8 x s8 -> s32: 16 rows x 32 columns of pixels against 32
+// columns x 8 cells of one weight slice); the eight results are combined in double with power-of-two scales.  The row
+// pass over the (H x cells) intermediate is then 0.1 % of the work and stays in FP64 (k_s1_lz_rows_f64).
+// The FP64 kernels above cost 8 DFMA per source pixel and ran at 46 % of the FP64 pipe; this path issues one tensor-core
+// instruction per 512 pixels and slice, reads pixels straight from global memory as fragment registers (no shared memory)
+// and is bound by HBM.  Result vs the numpy restatement: the integer sums are exact, so it is the MORE accurate side
+// (differences ~1e-16; tests hold 1e-13).  Cells are handled in windows of 8 (the N of the instruction); a window loops
+// over the 32-column chunks its cells' taps touch.
+// grid (ceil(H / 128), windows, frames), 256 threads: a warp owns 16 rows.   tmpx: [frame][H][windows * 8] doubles.
+// ---------------------------------------------------------------------------------------------
+#define LZ_SLICES 7   // 49 bits of every weight: residual < 2^-54 per tap relative to the largest weight (<= 1.5e-14 on a cell)
+struct LzMmaConst {
+    double scale[LZ_SLICES];  // 2^-(E + 7 (s + 1))
+};
+
+// W8 is stored in FRAGMENT ORDER: [window][chunk][slice][half][lane] 32-bit words, so that a warp's B operand is one
+// contiguous 256-byte read (the first version read weights as [cell][x] rows: every load instruction touched 8 cache
+// lines, 160 L1 wavefronts per 8 tensor-core instructions, and ran slower than the FP64 kernels).  The contraction index
+// is permuted so that a lane's two A words of a row are adjacent too: lane t of a group covers physical columns
+// 8t .. 8t+7 of the chunk (logical k = 4t + j for the first word, 16 + 4t + j for the second), one 8-byte load per row.
+NSOF_HD size_t lz_w8_word(int nch, int win, int ch, int s, int half, int lane)
+{
+    return ((((size_t)win * nch + ch) * LZ_SLICES + s) * 32 + lane) * 2 + half;  // a lane's two words are one 8-byte load
+}
+
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, 3) k_s1_lz_cols_mma(const uint8_t *NSOF_RESTRICT frames, ptrdiff_t pitch, ptrdiff_t frame_stride, int H, int W, int nch,
+                             const unsigned *NSOF_RESTRICT W8, const int *NSOF_RESTRICT winx, LzMmaConst K, double *NSOF_RESTRICT tmpx)
+{
+    const int win = NSOF_BY, f = NSOF_BZ, nwin = nsof_grid_y();
+    const int c0 = winx[2 * win], nc = winx[2 * win + 1];
+    const uint8_t *img = frames + (size_t)f * frame_stride;
+    const int NC = nwin * 8;
+#ifdef NSOF_EMU
+    for (int r = 0; r < 128; r++) {
+        const int y = NSOF_BX * 128 + r;
+        if (y >= H) break;
+        for (int n = 0; n < 8; n++) {
+            double v = 0.;
+            for (int s = 0; s < LZ_SLICES; s++) {
+                long long acc = 0;
+                for (int x = c0 * 32; x < (c0 + nc) * 32 && x < W; x++) {
+                    const int ch = x / 32, xo = x % 32, t = xo / 8, j8 = xo % 8;
+                    const unsigned word = W8[lz_w8_word(nch, win, ch, s, j8 / 4, n * 4 + t)];
+                    acc += (long long)(int8_t)((word >> (8 * (j8 % 4))) & 255u) * img[(size_t)y * pitch + x];
+                }
+                v += (double)acc * K.scale[s];
+            }
+            tmpx[((size_t)f * H + y) * NC + win * 8 + n] = v;
+        }
+    }
+#else
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int y0 = blockIdx.x * 128 + warp * 16;
+    if (y0 >= H) return;
+    const uint8_t *rowA = img + (size_t)nsof_imin(y0 + g, H - 1) * pitch;
+    const uint8_t *rowB = img + (size_t)nsof_imin(y0 + g + 8, H - 1) * pitch;
+    const int xmax = W - 8;  // W % 8 == 0: an 8-byte group beyond it lies wholly in columns whose weights are zero
+    int acc[LZ_SLICES][4];
+#pragma unroll
+    for (int s = 0; s < LZ_SLICES; s++) acc[s][0] = acc[s][1] = acc[s][2] = acc[s][3] = 0;
+    // software pipeline: the pixels of chunk ch + 1 and ALL sixteen weight words of chunk ch are in flight before the
+    // first tensor-core instruction of chunk ch issues (the first version used two register pairs for the weights and
+    // every IMMA waited for its own load: ~1200 cycles per chunk)
+    const int x0 = nsof_imin(c0 * 32 + 8 * t, xmax);
+    uint2 pa = __ldg((const uint2 *)(rowA + x0)), pb = __ldg((const uint2 *)(rowB + x0));
+    for (int ch = c0; ch < c0 + nc; ch++) {
+        const unsigned *wp = W8 + lz_w8_word(nch, win, ch, 0, 0, lane);
+        unsigned b[LZ_SLICES][2];
+#pragma unroll
+        for (int s = 0; s < LZ_SLICES; s++) { const uint2 w2 = __ldg((const uint2 *)(wp + s * 64)); b[s][0] = w2.x; b[s][1] = w2.y; }
+        const int xn = nsof_imin(nsof_imin(ch + 1, c0 + nc - 1) * 32 + 8 * t, xmax);
+        const uint2 na = __ldg((const uint2 *)(rowA + xn)), nb = __ldg((const uint2 *)(rowB + xn));
+#pragma unroll
+        for (int s = 0; s < LZ_SLICES; s++)
+            asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+r"(acc[s][0]), "+r"(acc[s][1]), "+r"(acc[s][2]), "+r"(acc[s][3])
+                         : "r"(pa.x), "r"(pb.x), "r"(pa.y), "r"(pb.y), "r"(b[s][0]), "r"(b[s][1]));
+        pa = na;
+        pb = nb;
+    }
+    double v[4] = {0., 0., 0., 0.};
+#pragma unroll
+    for (int s = 0; s < LZ_SLICES; s++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) v[i] += (double)acc[s][i] * K.scale[s];
+    const int ya = y0 + g, yb = y0 + g + 8, col = win * 8 + 2 * t;
+    if (ya < H) { double *o = tmpx + ((size_t)f * H + ya) * NC + col; o[0] = v[0]; o[1] = v[1]; }
+    if (yb < H) { double *o = tmpx + ((size_t)f * H + yb) * NC + col; o[0] = v[2]; o[1] = v[3]; }
+#endif
+}
+
+// Row pass over the intermediate: cells[f][r][c] = (1 / 255) * sum_y Wy[r][y] * tmpx[f][y][c], fixed summation order.
+// grid (Hc, frames), 256 threads = 8 parts of the tap band x 32 cell columns.
+NSOF_GLOBAL k_s1_lz_rows_f64(const double *NSOF_RESTRICT tmpx, int H, int NC, int Hc, int Wc, const double *NSOF_RESTRICT Wy,
+                             const int *NSOF_RESTRICT yband, double *NSOF_RESTRICT cells)
+{
+    const int r = NSOF_BX, f = NSOF_BY;
+    const int ya = yband[2 * r], yb = yband[2 * r + 1];
+    NSOF_DYN_SMEM(smem_raw);
+    double *part = (double *)smem_raw;  // [8][32]
+    const int parts = 8, per = (yb - ya + parts - 1) / parts;
+    for (int cb = 0; cb < Wc; cb += 32) {
+        for (int i = NSOF_TID; i < parts * 32; i += NSOF_NT) {
+            const int p = i / 32, c = cb + i % 32;
+            double s = 0.;
+            if (c < Wc) {
+                const int y0 = ya + p * per, y1 = nsof_imin(yb, y0 + per);
+                for (int y = y0; y < y1; y++) s += Wy[(size_t)r * H + y] * tmpx[((size_t)f * H + y) * NC + c];
+            }
+            part[i] = s;
+        }
+        NSOF_SYNC();
+        for (int i = NSOF_TID; i < 32; i += NSOF_NT) {
+            const int c = cb + i;
+            if (c < Wc) {
+                double s = 0.;
+                for (int p = 0; p < parts; p++) s += part[p * 32 + i];
+                cells[((size_t)f * Hc + r) * Wc + c] = s / 255.0;
+            }
+        }
+        NSOF_SYNC();
+    }
+}

@@ -385,6 +385,27 @@ def test_frame_mode_vs_oracle(gpu_engine):
     assert np.allclose(w2, w_o, rtol=0, atol=1e-10) and np.allclose(cur2, cur_o, rtol=1e-9)
 
 
+def test_lanczos_tensor_core_path_vs_fp64_path(gpu_engine):
+    """compress_image on the tensor cores (int8 weight slices, exact int32 sums: k_s1_lz_cols_mma) against the FP64
+    kernels and the numpy restatement, incl. a width that is not a multiple of the 32-column chunk (1080) and one that
+    takes the FP64 fallback (203: rows not word-aligned).  Both within 1e-13 of the restatement."""
+    rng = np.random.default_rng(3)
+    lib, h = gpu_engine.lib, gpu_engine.handle
+    for H, W, m in [(1080, 1920, 80), (1920, 1080, 80), (600, 600, 40), (160, 160, 40), (161, 203, 40), (801, 804, 200)]:
+        fr = rng.integers(0, 256, (3, H, W), dtype=np.uint8)
+        fr[1] = 255          # saturated frame: the largest integer sums
+        fr[2, :, ::2] = 0
+        a = gpu_engine.compress_images(fr, m, m)
+        lib.check(lib.nsof_debug_lanczos_f64(h, 1))
+        try:
+            b = gpu_engine.compress_images(fr, m, m)
+        finally:
+            lib.check(lib.nsof_debug_lanczos_f64(h, 0))
+        o = np.stack([s1.compress_image(f, m, m) for f in fr])
+        assert np.abs(a - o).max() <= 1e-13 and np.abs(b - o).max() <= 1e-13, (H, W, np.abs(a - o).max(), np.abs(b - o).max())
+        assert np.allclose(a[1], 1.0, rtol=0, atol=1e-13)   # weights of a cell sum to 1
+
+
 def test_frame_mode_1080p_mask_bit_exact(gpu_engine, nsof):
     """Full-size stage 1: 1080p frames -> 13 x 24 cells -> state -> current -> u8 -> mask, masks bit-exact vs the
     numpy restatement."""
