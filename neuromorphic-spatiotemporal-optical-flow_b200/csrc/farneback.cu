@@ -1304,8 +1304,9 @@ extern "C" int nsof_fb_tiled_run(nsof_handle *h, int halo_flow, unsigned long lo
     unsigned long long *fl = (unsigned long long *)h->link_flags.p;
     unsigned long long seq = first_seq;
     size_t ei = 0;
-    auto exchange = [&]() -> int {
-        const Ex &e = exs[ei++];
+    // an exchange = push (store the edge rows into the neighbours' halo rows, raise their flags) + wait (own flags)
+    auto push = [&]() -> int {
+        const Ex &e = exs[ei];
         seq++;
         if (world == 1 || e.rows <= 0) return NSOF_OK;  // (a skipped exchange still consumes its number on every rank)
         // peer flags: the UPPER neighbour's "raised by the lower one" slot [1], the LOWER neighbour's slot [0]
@@ -1318,27 +1319,55 @@ extern "C" int nsof_fb_tiled_run(nsof_handle *h, int halo_flow, unsigned long lo
             NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 2 * total, k_fb_halo_push, chunks, (int)e.count, 1, 256, 0, stream, dblocks + e.first,
                          (unsigned)(chunks * e.count), (unsigned *)(fl + 2), f_up, f_dn, seq);
         }
+        return NSOF_OK;
+    };
+    auto wait = [&]() -> int {
+        const Ex &e = exs[ei++];
+        if (world == 1 || e.rows <= 0) return NSOF_OK;
         NSOF_KLAUNCH(h, NSOF_K_HALO_COPY, 0., k_fb_halo_wait, 1, 1, 1, 32, 0, stream,
                      (const unsigned long long *)(h->link_up_arena ? fl + 0 : nullptr),
                      (const unsigned long long *)(h->link_dn_arena ? fl + 1 : nullptr), seq);
         NSOF_CUDA_TRY(cudaGetLastError());
         return NSOF_OK;
     };
-    for (int k = X.max_scales - 1; k >= X.stop_level; k--) {
-        rc = fb_launch_pyramid(h, k, stream);
-        if (rc) return rc;
-        rc = exchange();
-        if (rc) return rc;
-        rc = fb_launch_um_first(h, k, stream);
-        if (rc) return rc;
-        rc = exchange();
-        if (rc) return rc;
-        for (int it = 0; it < T; it++) {
-            rc = fb_launch_blur(h, k, it, T, stream);
-            if (rc) return rc;
-            rc = exchange();
-            if (rc) return rc;
+    // A stage of a level whose bands are at least four edges high runs as  top + bottom edge rows -> push -> rows in
+    // between -> wait  (the sub-window job tables of nsof_fb_tiled_stage_rows): the rows travel, and the neighbours catch
+    // up, while the bulk of the band is computed.  Opt-in (NSOF_TILED_SPLIT=1): measured SLOWER on 2 B200 (8K, 8 pairs:
+    // 527 - 530 vs 549 pairs/s) -- three launches and two more partially filled tile rows per stage cost more than the
+    // ~20 us of flag latency they hide.
+    const char *env_split = getenv("NSOF_TILED_SPLIT");
+    const bool want_split = world > 1 && env_split && env_split[0] == '1';
+    auto stage = [&](int k, int what, int it) -> int {
+        bool split = want_split && exs[ei].rows > 0;
+        if (split) {
+            const std::vector<FbItemPlan> &plan = *h->last_plan;
+            for (int i = 0; i < X.n && split; i++) {
+                int lo, hi;
+                band_rows(plan[i].hk[k], rank, world, &lo, &hi);
+                split = hi - lo >= 4 * X.edge;
+            }
         }
+        auto run = [&](int variant) -> int {
+            return what == 0 ? fb_launch_pyramid(h, k, stream, variant) : what == 1 ? fb_launch_um_first(h, k, stream, variant)
+                                                                                   : fb_launch_blur(h, k, it, T, stream, variant);
+        };
+        int r2;
+        if (!split) {
+            if ((r2 = run(0))) return r2;
+            if ((r2 = push())) return r2;
+            return wait();
+        }
+        if ((r2 = run(1))) return r2;
+        if ((r2 = run(2))) return r2;
+        if ((r2 = push())) return r2;
+        if ((r2 = run(3))) return r2;
+        return wait();
+    };
+    for (int k = X.max_scales - 1; k >= X.stop_level; k--) {
+        if ((rc = stage(k, 0, 0))) return rc;
+        if ((rc = stage(k, 1, 0))) return rc;
+        for (int it = 0; it < T; it++)
+            if ((rc = stage(k, 2, it))) return rc;
     }
     if (next_seq) *next_seq = seq;
     return NSOF_OK;

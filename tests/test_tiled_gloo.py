@@ -98,6 +98,7 @@ def test_tiled_peer_memory_run_reproduces_the_untiled_flow(emu_engine, nsof, wor
                  for (a, b), f in zip(pairs, flows[r])] for r in range(world)}
     want = [emu_engine.calcOpticalFlowFarneback(a, b, None, **PARAMS) for a, b in pairs]
     for rep in range(2):
+        os.environ["NSOF_TILED_SPLIT"] = str(rep)   # second repetition: edges -> push -> interior -> wait
         for r in range(world):
             for f in flows[r]:
                 f.fill(np.nan)
@@ -128,6 +129,7 @@ def test_tiled_peer_memory_run_reproduces_the_untiled_flow(emu_engine, nsof, wor
                 outside = np.ones(H, bool)
                 outside[lo:hi] = False
                 assert np.isnan(flows[r][i][outside]).all()
+    os.environ.pop("NSOF_TILED_SPLIT", None)
     assert tfs[0]._seq == tfs[world - 1]._seq > 0
     for e in engs:
         e.close()
