@@ -67,8 +67,15 @@ def run(name, H, W, box, speed, slice_us=1000, cpu_slices=60):
         # int64 refractory map) for every array
         chunks = (n_slices + 31) // 32
         by = len(x) * (4 if arrays == 1 else 5) + chunks * arrays * H * W * (8 if arrays == 1 else 24)
+        # The bound of this path is NOT bytes: with a bias above `von` every pixel evaluates one powf per slice and array
+        # (w stays in registers over the 32 slices of a chunk).  CUDA's powf is ~2 MUFU (lg2, ex2) + ~40 FP32
+        # instructions, so the ceilings are 16 MUFU / clk / SM and 128 FP32 lanes / clk / SM at 148 SMs x 1.965 GHz.
+        powf_s = n_slices * arrays * H * W / (ms * 1e-3)
+        sm_clk = 148 * 1.965e9
         out[nm] = {"ms": ms, "slices_per_s": n_slices / (ms * 1e-3), "events_per_s": len(x) / (ms * 1e-3),
-                   "algorithmic_GBps": by / (ms * 1e-3) / 1e9}
+                   "algorithmic_GBps": by / (ms * 1e-3) / 1e9, "bound": "fp32 issue (powf), not HBM",
+                   "powf_per_s": powf_s, "frac_of_mufu_peak": powf_s * 2 / (16 * sm_clk),
+                   "frac_of_fp32_peak_at_50_instr_per_update": powf_s * 50 / (128 * sm_clk)}
     # CPU: the reference's numpy loop on the first cpu_slices slices (bias 0.3: every pixel updates every slice, as above)
     n_ev = int(bounds[cpu_slices])
     t0 = time.perf_counter()
