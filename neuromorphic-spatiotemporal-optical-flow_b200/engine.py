@@ -1,7 +1,9 @@
 """Host side of the hot path: one `Engine` per (GPU, stream) wrapping a libnsof handle.
 
-Mirrors the reference's operator interface for the path (same names, argument meaning, return
-shapes and error behaviour):
+Mirrors the reference's operator interface for the path (same names, return shapes and error behaviour; same
+argument meaning except where noted: `process_merged_region` / `process_separate_regions` take the rectangle(s) that
+`opticalFlow3D` has already computed on the device instead of the reference's `(stats, ..., pixel_width, pixel_height)`
+-- call `opticalFlow3D`, which has the reference's exact signature, unless you hold rectangles already):
 
 * ``calcOpticalFlowFarneback(prev, next, flow, pyr_scale, levels, winsize, iterations, poly_n,
   poly_sigma, flags)`` -- cv2's signature as the scripts call it (optical_flow_seg.py:203).
