@@ -64,6 +64,24 @@ class RoiConfig:
         return cls(MEMSIZE=200, OFFSET=15, THRES=114, EXTEND_WIDTH_LEFT=60, EXTEND_WIDTH_RIGHT=60,
                    EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60)
 
+    # The three datasets below have no checked-in script of their own; their constants are data/<ds>/Parameters.txt.
+    @classmethod
+    def uav(cls):  # data/uav/Parameters.txt
+        return cls(MEMSIZE=40, THRES=114, FLAG=1, EXTEND_WIDTH_LEFT=30, EXTEND_WIDTH_RIGHT=30, EXTEND_HEIGHT_UPPER=30,
+                   EXTEND_HEIGHT_LOWER=30, farneback_params=dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3,
+                                                                 poly_n=10, poly_sigma=1.05, flags=0))
+
+    @classmethod
+    def uavnew2(cls):  # data/uavnew2/Parameters.txt
+        return cls(MEMSIZE=40, THRES=245, FLAG=1, EXTEND_WIDTH_LEFT=60, EXTEND_WIDTH_RIGHT=60, EXTEND_HEIGHT_UPPER=60,
+                   EXTEND_HEIGHT_LOWER=60)
+
+    @classmethod
+    def tabletennis(cls):  # data/tabletennis/Parameters.txt
+        return cls(MEMSIZE=10, THRES=245, FLAG=2, EXTEND_WIDTH_LEFT=20, EXTEND_WIDTH_RIGHT=20, EXTEND_HEIGHT_UPPER=20,
+                   EXTEND_HEIGHT_LOWER=20, farneback_params=dict(pyr_scale=0.6, levels=3, winsize=4, iterations=2,
+                                                                 poly_n=1, poly_sigma=1.05, flags=0))
+
 
 def _fb_params(pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags) -> FbParams:
     return FbParams(float(pyr_scale), int(levels), int(winsize), int(iterations), int(poly_n), float(poly_sigma),

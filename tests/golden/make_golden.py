@@ -170,6 +170,17 @@ def make_roi():
         ("autodriving", "optical_flow_yolo.py",
          dict(MEMSIZE=200, OFFSET=15, EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, EXTEND_WIDTH_LEFT=60,
               EXTEND_WIDTH_RIGHT=60, THRES=114, CONNECT=4), (801, 801)),
+        # the three datasets no script is checked in for: constants of data/<ds>/Parameters.txt, functions of
+        # optical_flow_seg.py (the scripts differ in their constants only for this part)
+        ("uav", "optical_flow_seg.py",
+         dict(MEMSIZE=40, OFFSET=0, EXTEND_HEIGHT_UPPER=30, EXTEND_HEIGHT_LOWER=30, EXTEND_WIDTH_LEFT=30,
+              EXTEND_WIDTH_RIGHT=30, THRES=114, CONNECT=4), (161, 161)),
+        ("uavnew2", "optical_flow_seg.py",
+         dict(MEMSIZE=40, OFFSET=0, EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, EXTEND_WIDTH_LEFT=60,
+              EXTEND_WIDTH_RIGHT=60, THRES=245, CONNECT=4), (600, 600)),
+        ("tabletennis", "optical_flow_seg.py",
+         dict(MEMSIZE=10, OFFSET=0, EXTEND_HEIGHT_UPPER=20, EXTEND_HEIGHT_LOWER=20, EXTEND_WIDTH_LEFT=20,
+              EXTEND_WIDTH_RIGHT=20, THRES=245, CONNECT=4), (160, 160)),
     ]:
         mat = scipy.io.loadmat(f"{REF}/data/{ds}/constructed_3D_matrix.mat")["constructed3DMatrix"]
         out[f"{ds}__currents"] = np.ascontiguousarray(np.moveaxis(mat, 2, 0)).astype(np.float64)  # (T, Hc, Wc)
@@ -571,7 +582,108 @@ def make_realdata(which=("grasp", "autodriving")):
               f"our method average accuracy {acc1.mean()!r}, original {acc2.mean()!r}")
 
 
+REALDATA_SMALL = {
+    # The three sequences no script is checked in for.  Constants = data/<ds>/Parameters.txt (which names no OFFSET:
+    # 0 is used, every slice index stays inside the .mat); functions = optical_flow_seg.py, whose main loop honours
+    # FLAG 1 as well as FLAG 2.  Last entry: which pairs with a non-empty gate are kept (every k-th).
+    "uav": (dict(MEMSIZE=40, OFFSET=0, EXTEND_HEIGHT_UPPER=30, EXTEND_HEIGHT_LOWER=30, EXTEND_WIDTH_LEFT=30,
+                 EXTEND_WIDTH_RIGHT=30, THRES=114, CONNECT=4, FLAG=1, PADDING=30, SEG_TH=1,
+                 farneback_params=PARAM_SETS["autodriving_txt"]), 4),
+    "uavnew2": (dict(MEMSIZE=40, OFFSET=0, EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, EXTEND_WIDTH_LEFT=60,
+                     EXTEND_WIDTH_RIGHT=60, THRES=245, CONNECT=4, FLAG=1, PADDING=60, SEG_TH=1,
+                     farneback_params=PARAM_SETS["grasp"]), 4),
+    "tabletennis": (dict(MEMSIZE=10, OFFSET=0, EXTEND_HEIGHT_UPPER=20, EXTEND_HEIGHT_LOWER=20, EXTEND_WIDTH_LEFT=20,
+                         EXTEND_WIDTH_RIGHT=20, THRES=245, CONNECT=4, FLAG=2, PADDING=20, SEG_TH=1,
+                         farneback_params=PARAM_SETS["tabletennis"]), 1),
+}
+
+
+def make_realdata_small(which=("uav", "uavnew2", "tabletennis")):
+    """The main-loop body of optical_flow_seg.py:413-490 over data/uav, data/uavnew2 (FLAG 1: one Farneback call per
+    connected region, pasted in label order, then task_results' merged padding box) and data/tabletennis (FLAG 2,
+    poly_n = 1, even winsize), with the reference's own functions and each dataset's Parameters.txt.
+
+    -> tests/golden/realdata_<ds>.npz: for ALL pairs the region rectangles, num_labels and accuracy1; for the kept
+    pairs memimg, both whole grey frames (the frames are small), the pasted float32 flow at every 4th pixel of
+    every 4th row + |flow| checksum, motion_binary and the ground-truth mask (bit-packed)."""
+    for ds in which:
+        consts, every = REALDATA_SMALL[ds]
+        ns = _script_namespace("optical_flow_seg.py",
+                               ["update_transition_pic", "process_separate_regions", "process_merged_region",
+                                "opticalFlow3D", "task_results", "process_flow_region", "calculate_pixel_accuracy"], consts)
+        base = f"{REF}/data/{ds}"
+        imgs = open(f"{base}/imgs.txt").read().splitlines()
+        mem_state = scipy.io.loadmat(f"{base}/constructed_3D_matrix.mat")["constructed3DMatrix"]
+        rgbimages = sorted([os.path.join(base, "RGB", i) for i in imgs],
+                           key=lambda x: int(os.path.basename(x).split(".")[0]))
+        M, OFFSET, FLAG = consts["MEMSIZE"], consts["OFFSET"], consts["FLAG"]
+        n_pairs = min(len(imgs) - 1, mem_state.shape[2] - OFFSET)
+        rects = np.zeros((n_pairs, 32, 4), np.int32)
+        nrect = np.zeros(n_pairs, np.int32)
+        nlab = np.ones(n_pairs, np.int32)
+        acc1 = np.zeros(n_pairs)
+        per_pair = {}
+        for i in range(n_pairs):
+            mem_state1 = mem_state[:, :, OFFSET + i].astype(np.double)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                mem_state1 = -3366 / np.log10(mem_state1) - 306
+            memimg = np.clip(mem_state1, 0, 255).astype(np.uint8)      # :426-435, mem_state2 = mem_state1
+            prev_frame, next_frame = cv2.imread(rgbimages[i]), cv2.imread(rgbimages[i + 1])
+            prev_gray = cv2.cvtColor(prev_frame, cv2.COLOR_RGB2GRAY)
+            next_gray = cv2.cvtColor(next_frame, cv2.COLOR_RGB2GRAY)
+            image = cv2.imread(f"{base}/gtmask/{imgs[i + 1]}")
+            _, binary_image = cv2.threshold(cv2.cvtColor(image, cv2.COLOR_BGR2GRAY), 127, 256, cv2.THRESH_BINARY)
+            for k in ("mem_cal_times", "mem_velocity_times", "mem_opticalflow_times", "mem_task_times",
+                      "mem_combination_times"):
+                ns[k].clear()
+            res = ns["opticalFlow3D"](memimg, memimg, prev_gray, next_gray, M, M)
+            flow = -res[0]
+            if FLAG == 1:
+                num_labels, info = res[4], [tuple(int(v) for v in r) for r in res[5]]
+                motion = ns["task_results"](prev_frame, next_frame, flow, num_labels, info, EST_FLAG=1, MERGE_FLAG=True)
+            else:
+                info1 = tuple(int(v) for v in res[4])
+                num_labels = 1 if info1 == (0, 0, 0, 0) else 2
+                motion = ns["task_results"](prev_frame, next_frame, flow, num_labels, info1, EST_FLAG=2, MERGE_FLAG=True)
+                info = [] if num_labels == 1 else [info1]
+            nrect[i], nlab[i] = len(info), num_labels
+            for j, r in enumerate(info):
+                rects[i, j] = r
+            acc1[i] = ns["calculate_pixel_accuracy"](motion, binary_image)
+            per_pair[i] = dict(memimg=memimg, prev_gray=prev_gray, next_gray=next_gray, gt=binary_image, motion=motion,
+                               flow=-flow)
+            print(ds, i, nlab[i], info[:3], f"{acc1[i]:.6f}", flush=True)
+        keep = [i for i in range(n_pairs) if nrect[i] > 0][::every]
+        multi = [i for i in range(n_pairs) if nrect[i] > 1 and i not in keep][:4]    # FLAG 1: several regions
+        keep = sorted(keep + multi)
+        H, W = per_pair[0]["prev_gray"].shape
+        out = dict(frame_hw=np.array([H, W]), rects=rects, nrect=nrect, num_labels=nlab, acc1=acc1, acc1_mean=acc1.mean(),
+                   keep=np.array(keep), flag=np.array(FLAG), cv2_version=np.array(cv2.__version__))
+        for i in keep:
+            d = per_pair[i]
+            fl = d["flow"].astype(np.float32)
+            assert np.array_equal(fl.astype(np.float64), d["flow"])
+            out[f"memimg__{i}"] = d["memimg"]
+            out[f"gray__{i}"] = d["prev_gray"]
+            out[f"gray__{i + 1}"] = d["next_gray"]
+            out[f"flow4__{i}"] = np.ascontiguousarray(fl[::4, ::4])
+            out[f"flowsum__{i}"] = np.array([np.abs(fl.astype(np.float64)).sum(), float(np.abs(fl).max())])
+            out[f"motion__{i}"] = np.packbits(d["motion"] > 0, axis=1)
+            out[f"gt__{i}"] = np.packbits(d["gt"] > 0, axis=1)
+            assert set(np.unique(d["gt"])) <= {0, 255} and set(np.unique(d["motion"])) <= {0, 255}
+        path = os.path.join(OUT, f"realdata_{ds}.npz")
+        np.savez_compressed(path, **out)
+        print(f"realdata_{ds}.npz: {len(keep)} of {n_pairs} pairs kept, {os.path.getsize(path) / 1e6:.2f} MB; "
+              f"average accuracy {acc1.mean()!r}")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "realdata_small":
+        make_realdata_small(tuple(sys.argv[2:]) or ("uav", "uavnew2", "tabletennis"))
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "roi":
+        make_roi()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "hostio":
         make_hostio()
         sys.exit(0)

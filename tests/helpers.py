@@ -261,6 +261,90 @@ class RealData:
         return d.mean(), d.max()
 
 
+class RealDataSmall:
+    """tests/golden/realdata_{uav,uavnew2,tabletennis}.npz (make_golden.make_realdata_small): the main-loop body of
+    optical_flow_seg.py:413-490 with the reference's own functions and each dataset's Parameters.txt -- FLAG 1 (one
+    Farneback call per connected region) for the two uav sequences, FLAG 2 with poly_n = 1 for tabletennis."""
+
+    def __init__(self, ds):
+        self.ds = ds
+        self.g = np.load(os.path.join(GOLDEN, f"realdata_{ds}.npz"))
+        self.H, self.W = (int(v) for v in self.g["frame_hw"])
+        self.keep = [int(i) for i in self.g["keep"]]
+        self.flag = int(self.g["flag"])
+
+    def rects(self, i):
+        return [tuple(int(v) for v in r) for r in self.g["rects"][i, :int(self.g["nrect"][i])]]
+
+    def unpack(self, key):
+        return np.unpackbits(self.g[key], axis=1)[:, :self.W].astype(bool)
+
+
+# Per-dataset flow bounds against cv2 (px): mean EPE, share of pixels above 1e-3, maximum.  uavnew2 runs the grasp
+# parameter set and meets the standard bounds.  The other two sets are ill-conditioned on these frames -- winsize 3 / 4
+# leaves the 2x2 systems of flat image regions near-singular (|flow| reaches 37 px on a 161 px frame) -- and OpenCV
+# does not agree with ITSELF there: cv2.setUseOptimized(False) against the default build differs by up to 1.3e-2 px on
+# the uav crops and 7.6e-2 px on the tabletennis crops (measured with the committed frames, cv2 4.x of this image),
+# and the C oracle differs from cv2 by 1.2e-2 / 4.6e-2.  Their maxima are bounded a small factor above that; the mean
+# and the share of pixels above 1e-3 px stay tight, and what the scripts consume (motion mask, accuracy) is exact.
+REALDATA_SMALL_TOL = {
+    "uavnew2": dict(mean=1e-4, share=0.0, max=1e-3, live_share=1e-4, live_max=5e-3),
+    "uav": dict(mean=1e-4, share=5e-3, max=0.15, live_share=5e-3, live_max=0.15),
+    "tabletennis": dict(mean=2e-4, share=3e-2, max=0.3, live_share=3e-2, live_max=0.3),
+}
+
+
+def check_realdata_small(engine, nsof, ds, padding, live_cv2=True, pairs=None):
+    """Engine.opticalFlow3D -> `flow = -flow` -> task_results -> calculate_pixel_accuracy on the kept pairs of one of
+    the three small sequences.  Region rectangles and num_labels equal the reference's; the pasted flow within
+    REALDATA_SMALL_TOL[ds] of cv2's at every 4th pixel, and (when cv2 imports) of cv2 run live on every
+    region crop at EVERY pixel (REALDATA_SMALL_TOL); motion mask bit for bit; accuracy to the last digit.
+    -> (worst mean EPE, worst max EPE, pairs checked)."""
+    cv2 = None
+    if live_cv2:
+        try:
+            import cv2
+        except Exception:
+            cv2 = None
+    rd = RealDataSmall(ds)
+    cfg = getattr(nsof.RoiConfig, ds)()
+    assert cfg.FLAG == rd.flag
+    M, tol = cfg.MEMSIZE, REALDATA_SMALL_TOL[ds]
+    worst = [0.0, 0.0]
+    todo = rd.keep if pairs is None else rd.keep[:pairs]
+    for i in todo:
+        a, b = rd.g[f"gray__{i}"], rd.g[f"gray__{i + 1}"]
+        memimg = rd.g[f"memimg__{i}"]
+        res = engine.opticalFlow3D(memimg, memimg, a, b, M, M, cfg)
+        flow = res[0]
+        if rd.flag == 1:
+            num_labels, info = res[4], [tuple(int(v) for v in r) for r in res[5]]
+            assert num_labels == int(rd.g["num_labels"][i]) and info == rd.rects(i), (ds, i, info, rd.rects(i))
+            regions = info
+        else:
+            info = tuple(int(v) for v in res[4])
+            assert [info] == rd.rects(i), (ds, i, info)
+            num_labels, regions = 2, [info]
+        d = flow_err(flow[::4, ::4], rd.g[f"flow4__{i}"])
+        assert d.mean() <= tol["mean"] and (d > 1e-3).mean() <= tol["share"] and d.max() <= tol["max"], \
+            f"{ds} pair {i}: EPE mean {d.mean():.3e} share>1e-3 {(d > 1e-3).mean():.3e} max {d.max():.3e}"
+        worst = [max(worst[0], d.mean()), max(worst[1], d.max())]
+        ssum, _ = rd.g[f"flowsum__{i}"]
+        assert abs(np.abs(flow).sum() - ssum) <= tol["mean"] * 2 * rd.H * rd.W, (ds, i)
+        if cv2 is not None:
+            want = np.zeros((rd.H, rd.W, 2))
+            for (x0, y0, x1, y1) in regions:      # optical_flow_seg.py:155-159: later regions overwrite earlier ones
+                want[y0:y1, x0:x1] = cv2.calcOpticalFlowFarneback(a[y0:y1, x0:x1], b[y0:y1, x0:x1], None, **cfg.farneback_params)
+            d = flow_err(flow, want)
+            assert d.mean() <= tol["mean"] and (d > 1e-3).mean() <= tol["live_share"] and d.max() <= tol["live_max"], \
+                (ds, i, d.mean(), (d > 1e-3).mean(), d.max())
+            worst[1] = max(worst[1], d.max())
+        motion = engine.task_results(a, b, -flow, num_labels, info, EST_FLAG=rd.flag, MERGE_FLAG=True, padding=padding)
+        assert np.array_equal(motion > 0, rd.unpack(f"motion__{i}")), (ds, i, int(((motion > 0) != rd.unpack(f"motion__{i}")).sum()))
+        assert pixel_accuracy(motion > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i], (ds, i)
+    return worst[0], worst[1], len(todo)
+
+
 def pixel_accuracy(a, b):
     """calculate_pixel_accuracy (optical_flow_seg.py:384-388)."""
     return np.sum(a == b) / a.size * 100

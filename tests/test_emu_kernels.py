@@ -98,7 +98,9 @@ def test_emu_errors_mirror_cv2(emu_engine, nsof):
     assert z.shape == (40, 40, 2) and z.dtype == np.float32 and not z.any()
 
 
-@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801))])
+@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801)),
+                                           ("uav", "uav", (161, 161)), ("uavnew2", "uavnew2", (600, 600)),
+                                           ("tabletennis", "tabletennis", (160, 160))])
 def test_emu_roi_bit_exact_vs_reference(emu_engine, nsof, golden, ds, cfgname, hw):
     cfg = getattr(nsof.RoiConfig, cfgname)()
     cur = golden.roi[f"{ds}__currents"]
@@ -297,6 +299,13 @@ def test_emu_realdata_pair_end_to_end(emu_engine, nsof):
     motion = emu_engine.task_results(a, b, -flow, 2, info)
     assert np.array_equal(motion > 0, rd.unpack(f"motion__{i}"))
     assert helpers.pixel_accuracy(motion > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
+
+
+@pytest.mark.parametrize("ds,padding", [("uav", 30), ("uavnew2", 60), ("tabletennis", 20)])
+def test_emu_realdata_small_sequences(emu_engine, nsof, ds, padding):
+    """The three sequences without a script of their own (data/<ds>/Parameters.txt: FLAG 1 with poly_n 10 / winsize 3,
+    FLAG 1 with the grasp set, FLAG 2 with poly_n 1 / winsize 4) on the emulator build, first pairs of each."""
+    helpers.check_realdata_small(emu_engine, nsof, ds, padding, pairs=3 if ds == "uavnew2" else 6)
 
 
 def test_emu_frame_mode_vs_external_fixtures(emu_engine):

@@ -164,6 +164,17 @@ def test_realdata_end_to_end(gpu_engine, nsof, ds):
         assert not res[0].any() and res[4] == (0, 0, 0, 0)
 
 
+@pytest.mark.parametrize("ds,padding", [("uav", 30), ("uavnew2", 60), ("tabletennis", 20)])
+def test_realdata_small_sequences(gpu_engine, nsof, ds, padding):
+    """The three shipped sequences without a script of their own, each with its data/<ds>/Parameters.txt: uav (FLAG 1,
+    poly_n 10, winsize 3; 22 pairs, up to 3 regions per pair), uavnew2 (FLAG 1, grasp set; 13 pairs, up to 13
+    regions), tabletennis (FLAG 2, poly_n 1, winsize 4; 19 pairs).  Rectangles, num_labels, motion masks and pixel
+    accuracy equal the reference run bit for bit; flow bounds per dataset in helpers.REALDATA_SMALL_TOL (two of the
+    three parameter sets are ill-conditioned on these frames: OpenCV differs from itself by 1e-2 .. 8e-2 px)."""
+    mean, mx, n = helpers.check_realdata_small(gpu_engine, nsof, ds, padding)
+    print(f"{ds}: {n} pairs, worst mean EPE {mean:.3e}, worst max EPE {mx:.3e}")
+
+
 @pytest.mark.parametrize("ds", ["grasp", "autodriving"])
 def test_realdata_full_frame_baseline(gpu_engine, ds):
     """The scripts' baseline block (optical_flow_seg.py:492-545) on whole real frames: full-frame Farneback ->
@@ -271,7 +282,9 @@ def test_errors_mirror_cv2(gpu_engine, nsof):
 
 
 # ------------------------------------------------------------------------------------------- stage 1
-@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801))])
+@pytest.mark.parametrize("ds,cfgname,hw", [("grasp", "grasp", (1920, 1080)), ("autodriving", "autodriving", (801, 801)),
+                                           ("uav", "uav", (161, 161)), ("uavnew2", "uavnew2", (600, 600)),
+                                           ("tabletennis", "tabletennis", (160, 160))])
 def test_roi_bit_exact_vs_reference(gpu_engine, nsof, golden, ds, cfgname, hw):
     cfg = getattr(nsof.RoiConfig, cfgname)()
     cur = golden.roi[f"{ds}__currents"]

@@ -44,7 +44,10 @@ def test_level_geometry_matches_spec(oracle):
 
 
 @pytest.mark.parametrize("ds,cfg", [("grasp", dict(MEMSIZE=80, THRES=250, ext=(20, 20, 20, 20), hw=(1920, 1080))),
-                                    ("autodriving", dict(MEMSIZE=200, THRES=114, ext=(60, 60, 60, 60), hw=(801, 801)))])
+                                    ("autodriving", dict(MEMSIZE=200, THRES=114, ext=(60, 60, 60, 60), hw=(801, 801))),
+                                    ("uav", dict(MEMSIZE=40, THRES=114, ext=(30, 30, 30, 30), hw=(161, 161))),
+                                    ("uavnew2", dict(MEMSIZE=40, THRES=245, ext=(60, 60, 60, 60), hw=(600, 600))),
+                                    ("tabletennis", dict(MEMSIZE=10, THRES=245, ext=(20, 20, 20, 20), hw=(160, 160)))])
 def test_roi_oracle_matches_reference(golden, ds, cfg):
     cur = golden.roi[f"{ds}__currents"]
     memimg = s1.current_to_u8(cur)
