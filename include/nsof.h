@@ -254,6 +254,11 @@ NSOF_API int nsof_debug_lanczos_f64(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fork(nsof_handle *h, int enable);
 /* enable = 1 keeps the large blur+solve tile on every level (default: latency-bound levels take the small one). */
 NSOF_API int nsof_debug_big_tiles(nsof_handle *h, int enable);
+/* enable = 0: the tuned blur+solve kernel gathers R1 from L2 in every tile (default: from a shared-memory window placed
+ * on the tile's flow range whenever the range fits; same values either way).  nsof_debug_r1_window_stats: out2 = {tiles
+ * through the window, tiles on the L2 path} since the previous call (the first call switches the counting on). */
+NSOF_API int nsof_debug_r1_window(nsof_handle *h, int enable);
+NSOF_API int nsof_debug_r1_window_stats(nsof_handle *h, unsigned long long *out2, void *cuda_stream);
 NSOF_API int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w);
 
 /* ---- stage 1: synaptic temporal memory -> ROI ------------------------------------------- */

@@ -117,6 +117,7 @@ extern "C" int nsof_create(int device, nsof_handle **out)
     h->device = device;
     h->last_plan = new std::vector<FbItemPlan>();
     if (const char *e = getenv("NSOF_SHARE_FRAMES")) h->dbg_no_dedup = e[0] == '0';  // A/B measurements (default: on)
+    if (const char *e = getenv("NSOF_R1_WINDOW")) h->dbg_no_r1_window = e[0] == '0';  // A/B measurements (default: on)
     if (const char *e = getenv("NSOF_LANCZOS_F64")) h->dbg_lz_f64 = e[0] == '1';     // A/B: FP64 Lanczos kernels
     *out = h;
     return NSOF_OK;
@@ -137,6 +138,7 @@ extern "C" int nsof_destroy(nsof_handle *h)
     h->tables.release();
     h->clear_tab.release();
     h->guard_buf.release();
+    h->r1_stats_buf.release();
     fb_ctx_free(h);
     h->io.release();
     h->s1.release();
@@ -879,12 +881,14 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
     const uint2 *tl_bs = X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + FB_L_BS];
     (void)na;
     if (!n_bs) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
+    const int bs_flags = (last ? 1 : 0) | (h->dbg_no_r1_window ? 2 : 0);
+    unsigned *bs_stats = h->dbg_r1_stats ? (unsigned *)h->r1_stats_buf.p : nullptr;
     if (X.bs_m7 && X.bs_small[kk])  // latency-bound level: the 32x16 tile (see fb_prepare)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, n_bs, 1, 1,
-                     FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, last);
+                     FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
     else if (X.bs_m7)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, n_bs, 1, 1,
-                     FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, last);
+                     FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
     else if (X.gwin.on)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve_gauss, n_bs, 1, 1,
                      256, X.bs_smem, stream, jobs, tl_bs, X.BTW, X.BTH, X.m, X.bscale, (it & 1) == 0, last, X.gwin);
@@ -1601,6 +1605,37 @@ extern "C" int nsof_debug_big_tiles(nsof_handle *h, int enable)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     h->dbg_big_tiles = enable != 0;
+    return NSOF_OK;
+}
+
+// 0: the UpdateMatrices half of the tuned blur+solve kernel gathers R1 from L2 in every tile (A/B, bit-identity test)
+extern "C" int nsof_debug_r1_window(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_no_r1_window = !enable;
+    return NSOF_OK;
+}
+
+// out2 = {tiles whose R1 gathers came from the shared-memory window, tiles on the L2 path} since the previous call, then
+// zeroed; the first call (or out2 == NULL) switches the counting on.  Synchronises `cuda_stream`.
+extern "C" int nsof_debug_r1_window_stats(nsof_handle *h, unsigned long long *out2, void *cuda_stream)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (!h->dbg_r1_stats) {
+        int rc = h->r1_stats_buf.ensure(2 * sizeof(unsigned));
+        if (rc != NSOF_OK) return rc;
+        NSOF_CUDA_TRY(cudaMemsetAsync(h->r1_stats_buf.p, 0, 2 * sizeof(unsigned), st));
+        NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+        h->dbg_r1_stats = true;
+        if (out2) out2[0] = out2[1] = 0;
+        return NSOF_OK;
+    }
+    unsigned v[2] = {0, 0};
+    NSOF_CUDA_TRY(cudaMemcpyAsync(v, h->r1_stats_buf.p, sizeof(v), cudaMemcpyDeviceToHost, st));
+    NSOF_CUDA_TRY(cudaMemsetAsync(h->r1_stats_buf.p, 0, sizeof(v), st));
+    NSOF_CUDA_TRY(cudaStreamSynchronize(st));
+    if (out2) { out2[0] = v[0]; out2[1] = v[1]; }
     return NSOF_OK;
 }
 

@@ -20,6 +20,7 @@
 // ragged ROI crops batch into exactly as many CTAs as there are tiles.  (Round 1 ran grid (max tiles, items) with
 // early exits: one whole-frame item among 250 small crops made 90 % of the CTAs of every launch empty.)
 #pragma once
+#include <type_traits>
 #include "nsof_rt.h"
 #include <algorithm>
 
@@ -327,8 +328,14 @@ NSOF_DEV float nsof_um_border_scale(int x, int y, int w, int h)
     return scale;
 }
 
-NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int h, int w, int xa, int ya, int xb,
-                           int yb, float2 dx, float2 dy, const float2 r0v[5], float2 out[5])
+// WIN = 1: R1 is not the image plane but a WINDOW of it staged in shared memory -- `pitch` floats per row, `plane` floats
+// per plane, element (0, 0) = image pixel (wx0, wy0), ww x wh the largest in-window (x1, y1) offsets whose right / lower
+// neighbours are still inside.  The caller guarantees that every pixel with an in-image bilinear cell lies inside (the
+// window is placed on the tile's flow range); the offset test below only keeps the address legal for pixels whose
+// values are discarded anyway (NaN flow).  Same loads, same arithmetic, same results as WIN = 0.
+template <bool WIN>
+NSOF_DEV void fb_um_pixel2_t(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int wx0, int wy0, int ww, int wh, int h,
+                             int w, int xa, int ya, int xb, int yb, float2 dx, float2 dy, const float2 r0v[5], float2 out[5])
 {
     float2 fx = nsof_add2(make_float2((float)xa, (float)xb), dx), fy = nsof_add2(make_float2((float)ya, (float)yb), dy);
     const int x1a = (int)floorf(fx.x), y1a = (int)floorf(fy.x), x1b = (int)floorf(fx.y), y1b = (int)floorf(fy.y);
@@ -339,14 +346,29 @@ NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitc
     const float2 one = make_float2(1.f, 1.f), mone = make_float2(-1.f, -1.f);
     const float2 ox = nsof_fma2(fx, mone, one), oy = nsof_fma2(fy, mone, one);  // 1 - fx, 1 - fy (one rounding each)
     const float2 a00 = nsof_mul2(ox, oy), a01 = nsof_mul2(fx, oy), a10 = nsof_mul2(ox, fy), a11 = nsof_mul2(fx, fy);
-    const float *pa = R1 + (ina ? (size_t)y1a * pitch + x1a : (size_t)0);
-    const float *pb = R1 + (inb ? (size_t)y1b * pitch + x1b : (size_t)0);
+    const float *pa, *pb;
+    if (WIN) {
+        const int rxa = x1a - wx0, rya = y1a - wy0, rxb = x1b - wx0, ryb = y1b - wy0;
+        const bool wa = ina && (unsigned)rxa <= (unsigned)ww && (unsigned)rya <= (unsigned)wh;
+        const bool wb = inb && (unsigned)rxb <= (unsigned)ww && (unsigned)ryb <= (unsigned)wh;
+        pa = R1 + (wa ? rya * pitch + rxa : 0);
+        pb = R1 + (wb ? ryb * pitch + rxb : 0);
+    } else {
+        pa = R1 + (ina ? (size_t)y1a * pitch + x1a : (size_t)0);
+        pb = R1 + (inb ? (size_t)y1b * pitch + x1b : (size_t)0);
+    }
     float2 q[5];
 #pragma unroll
     for (int c = 0; c < 5; c++) {
-        const float2 v00 = make_float2(NSOF_LDG(pa), NSOF_LDG(pb)), v01 = make_float2(NSOF_LDG(pa + 1), NSOF_LDG(pb + 1));
-        const float2 v10 = make_float2(NSOF_LDG(pa + pitch), NSOF_LDG(pb + pitch));
-        const float2 v11 = make_float2(NSOF_LDG(pa + pitch + 1), NSOF_LDG(pb + pitch + 1));
+        float2 v00, v01, v10, v11;
+        if (WIN) {  // shared memory: plain loads
+            v00 = make_float2(pa[0], pb[0]); v01 = make_float2(pa[1], pb[1]);
+            v10 = make_float2(pa[pitch], pb[pitch]); v11 = make_float2(pa[pitch + 1], pb[pitch + 1]);
+        } else {
+            v00 = make_float2(NSOF_LDG(pa), NSOF_LDG(pb)); v01 = make_float2(NSOF_LDG(pa + 1), NSOF_LDG(pb + 1));
+            v10 = make_float2(NSOF_LDG(pa + pitch), NSOF_LDG(pb + pitch));
+            v11 = make_float2(NSOF_LDG(pa + pitch + 1), NSOF_LDG(pb + pitch + 1));
+        }
         q[c] = nsof_fma2(a11, v11, nsof_fma2(a10, v10, nsof_fma2(a01, v01, nsof_mul2(a00, v00))));
         pa += plane;
         pb += plane;
@@ -376,6 +398,12 @@ NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitc
     out[2] = nsof_fma2(r5, r5, r66);
     out[3] = nsof_fma2(r4, r2, nsof_mul2(r6, r3));
     out[4] = nsof_fma2(r6, r2, nsof_mul2(r5, r3));
+}
+
+NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int h, int w, int xa, int ya, int xb,
+                           int yb, float2 dx, float2 dy, const float2 r0v[5], float2 out[5])
+{
+    fb_um_pixel2_t<false>(R1, plane, pitch, 0, 0, 0, 0, h, w, xa, ya, xb, yb, dx, dy, r0v, out);
 }
 
 // First UpdateMatrices of a level; the initial flow is zero (coarsest level) or the coarser
@@ -743,12 +771,21 @@ NSOF_GLOBAL k_fb_blur_solve_g(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF
 //            gathers of a warp instruction then fall into one or two 128-byte lines (with 4 pixels per thread
 //            the lanes of one load sat 16 B apart: 4+ lines per instruction, and L1 was the busiest unit of the
 //            kernel at 68 %); R0 loads and M' stores are 128 B per warp instruction.
-// dynamic smem: 16 B (mbarrier) + 5 * (TH+2M) * (TW+2ML) floats.
+//            The 20 gathers per pixel do not go to L2 any more when the tile's flow is coherent (round 2): phase 3a
+//            also reduces the range of the bilinear cells (x1, y1) the tile will touch; if it fits a window of
+//            RH x RS = (TH+3) x (TW+8) pixels, the five R1 planes of that window arrive by bulk row copies in the dead
+//            rows 0 .. TH-1 of the five M planes (second phase of the same mbarrier) and the gathers are LDS.  The
+//            window FOLLOWS the flow (its origin is the smallest x1 / y1), so the limit is the variation of the flow
+//            inside a tile (3 rows, 4 - 7 columns), not its magnitude; tiles over a motion boundary keep the L2 path.
+// dynamic smem: 32 B (mbarrier, 4 range integers) + 5 * (TH+2M) * (TW+2ML) floats.
 // ---------------------------------------------------------------------------------------------
 template <int M, int TW, int TH, int NT, int MINB>
 NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float scale,
-                                                           int src_is_a, int last)
+                                                           int src_is_a, int flags, unsigned *stats)
 {
+    // flags: bit 0 last iteration of the level (flow -> HBM, no UpdateMatrices); bit 1 keep the R1 gathers on the L2
+    // path (nsof_debug_r1_window(h, 0): A/B runs and the bit-identity test).  stats (NULL: off): tiles counted by path.
+    const int last = flags & 1;
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
     constexpr int RPP = (2 * M * PW) / (2 * TW);        // flow rows (TW float2) that fit the dead rows of one plane
@@ -764,7 +801,11 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
     NSOF_DYN_SMEM(smem_raw);
     nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
-    float *sM = (float *)(smem_raw + 16);
+    int *s_rng = (int *)(smem_raw + 16);     // {min x1, max x1, min y1, max y1} of the tile's R1 gathers
+    float *sM = (float *)(smem_raw + 32);
+    // R1 window of phase 3b: RH rows of RS floats per plane, in rows 0 .. TH-1 of the plane's M tile
+    constexpr int RS = TW + 8, RH = (TH * PW) / RS;
+    static_assert(RS % 4 == 0 && RH >= TH + 2, "R1 window: 16-byte rows, at least one row of slack");
 
     // ---- phase 1
     const int gx0 = tx0 - ML;                                         // global x of shared column 0
@@ -773,6 +814,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     if (NSOF_TID == 0) {
         nsof_mbar_init(bar, 1);
         nsof_mbar_expect_tx(bar, row_bytes * (unsigned)(5 * LH));
+        s_rng[0] = s_rng[2] = 0x7fffffff;
+        s_rng[1] = s_rng[3] = -0x7fffffff - 1;
     }
     NSOF_SYNC();
     // every thread issues at most a few row copies: the issue cost is spread over all warps
@@ -843,6 +886,11 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     NSOF_SYNC();
     // ---- phase 3a
     constexpr int GW = TW / 4;
+#ifndef FB_BS_WINDOW
+#define FB_BS_WINDOW 1
+#endif
+    // range of  fl(x + dx), fl(y + dy)  over the tile's pixels, in float (floor is monotonic: one conversion per thread)
+    float tmnx = 3.0e38f, tmxx = -3.0e38f, tmny = 3.0e38f, tmxy = -3.0e38f;
     for (int i = NSOF_TID; i < GW * TH; i += NSOF_NT) {
         const int lx = (i % GW) * 4, ly = i / GW;
         const int x = tx0 + lx, y = ty0 + ly;
@@ -927,12 +975,54 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             float4 *fo = (float4 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
             fo[0] = make_float4(fxv[0], fyv[0], fxv[1], fyv[1]);
             fo[1] = make_float4(fxv[2], fyv[2], fxv[3], fyv[3]);
+#if FB_BS_WINDOW
+            // the same sums phase 3b forms (fb_um_pixel2_t: one rounded addition each); fminf / fmaxf drop a NaN
+            const float fy = (float)y;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (x + q < J.w) {
+                    const float px = (float)(x + q) + fxv[q], py = fy + fyv[q];
+                    tmnx = fminf(tmnx, px); tmxx = fmaxf(tmxx, px);
+                    tmny = fminf(tmny, py); tmxy = fmaxf(tmxy, py);
+                }
+#endif
         }
     }
     if (last) return;
+#if FB_BS_WINDOW
+    {
+        // cells outside the image are not gathered (the out-of-image branch of UpdateMatrices): clamp to the cells that are
+        // (a thread without a valid pixel contributes the neutral pair 1e9 / -2)
+        const int a = nsof_imax((int)floorf(fminf(fmaxf(tmnx, -1.f), 1.0e9f)), 0);
+        const int b = nsof_imin((int)floorf(fmaxf(fminf(tmxx, 1.0e9f), -2.f)), J.w - 2);
+        const int c = nsof_imax((int)floorf(fminf(fmaxf(tmny, -1.f), 1.0e9f)), 0);
+        const int d = nsof_imin((int)floorf(fmaxf(fminf(tmxy, 1.0e9f), -2.f)), J.h - 2);
+        nsof_block_minmax4(s_rng, a, b, c, d);
+    }
+#endif
     NSOF_SYNC();
     // ---- phase 3b
     const float *R0 = J.R[0], *R1 = J.R[1];
+#if FB_BS_WINDOW
+    const int wx0 = s_rng[0] & ~3, wy0 = s_rng[2];
+    const bool win = !(flags & 2) && s_rng[0] <= s_rng[1] && s_rng[2] <= s_rng[3] && s_rng[1] - wx0 <= RS - 2 &&
+                     s_rng[3] - wy0 <= RH - 2;
+    if (stats && NSOF_TID == 0) nsof_count(stats + (win ? 0 : 1));
+    if (win) {
+        // the window's rows of the five R1 planes -> rows 0 .. TH-1 of the M planes (dead since phase 3a)
+        const int ncol = nsof_imin(wx0 + RS, J.pitch) - wx0, nrow = nsof_imin(wy0 + RH, J.h) - wy0;
+        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, (unsigned)(ncol * 4) * (unsigned)(5 * nrow));
+        nsof_fence_proxy_async();
+        for (int r = NSOF_TID; r < 5 * nrow; r += NSOF_NT) {
+            const int c = r / nrow, ly = r - c * nrow;
+            nsof_bulk_g2s(sM + c * SP + ly * RS, R1 + c * plane + (size_t)(wy0 + ly) * J.pitch + wx0, (unsigned)(ncol * 4), bar);
+        }
+        // (the wait is in phase3b, behind the first R0 loads)
+    }
+#else
+    const int wx0 = 0, wy0 = 0;
+    const bool win = false;
+#endif
 #ifndef FB_BS_UNROLL
 #define FB_BS_UNROLL 2
 #endif
@@ -942,20 +1032,60 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #if FB_BS_PAIR
     // two pixels per thread and iteration (i and i + NT: same column, NT / TW rows apart when NT is a multiple of TW), in
     // the two halves of packed FP32 operands (fb_um_pixel2)
+    // (one instantiation per gather path: the block-uniform choice is made once, outside the pixel loop)
+#ifndef FB_BS_R0_AHEAD
+#define FB_BS_R0_AHEAD 1
+#endif
+    auto phase3b = [&](auto win_c) {
+    constexpr bool WIN = decltype(win_c)::value;
+    // window path: with the gathers in shared memory the R0 loads are the only L2 round trip left in an iteration; those
+    // of the pixel pair of iteration k + 1 are issued before the arithmetic of iteration k (the first ones before the wait
+    // for the window copy)
+    constexpr bool AHEAD = WIN && FB_BS_R0_AHEAD;
+    float2 r0n[5];
+    auto r0_pair = [&](int i, float2 *r) {
+        const int ib = i + NSOF_NT;
+        const int xa = tx0 + i % TW, ya = ty0 + i / TW, xb = tx0 + ib % TW, yb = ty0 + ib / TW;
+        if (ib < TW * TH && xa < J.w && ya < J.y_hi && xb < J.w && yb < J.y_hi) {
+            const size_t oa = (size_t)ya * J.pitch + xa, ob = (size_t)yb * J.pitch + xb;
+#pragma unroll
+            for (int c = 0; c < 5; c++) r[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
+        }
+    };
+    if (AHEAD && NSOF_TID < TW * TH) r0_pair(NSOF_TID, r0n);
+    if (WIN) {
+        if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 1);
+        NSOF_SYNC();
+    }
     for (int i = NSOF_TID; i < TW * TH; i += 2 * NSOF_NT) {
         const int ib = i + NSOF_NT;
         const int lxa = i % TW, lya = i / TW, lxb = ib % TW, lyb = ib / TW;
         const int xa = tx0 + lxa, ya = ty0 + lya, xb = tx0 + lxb, yb = ty0 + lyb;
         const bool va = xa < J.w && ya < J.y_hi, vb = ib < TW * TH && xb < J.w && yb < J.y_hi;
+        float2 r0a[5];
+        if (AHEAD) {  // every iteration hands over its prefetch and issues the next one, whichever branch it takes
+#pragma unroll
+            for (int c = 0; c < 5; c++) r0a[c] = r0n[c];
+            if (i + 2 * NSOF_NT < TW * TH) r0_pair(i + 2 * NSOF_NT, r0n);
+        }
         if (va && vb) {
             const float2 fa = *(const float2 *)(sM + (lya / RPP) * SP + TH * PW + (lya % RPP) * (2 * TW) + 2 * lxa);
             const float2 fb = *(const float2 *)(sM + (lyb / RPP) * SP + TH * PW + (lyb % RPP) * (2 * TW) + 2 * lxb);
             const size_t oa = (size_t)ya * J.pitch + xa, ob = (size_t)yb * J.pitch + xb;
             float2 r0v[5], mm[5];
+            if (AHEAD) {
 #pragma unroll
-            for (int c = 0; c < 5; c++) r0v[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
+                for (int c = 0; c < 5; c++) r0v[c] = r0a[c];
+            } else {
+#pragma unroll
+                for (int c = 0; c < 5; c++) r0v[c] = make_float2(NSOF_LDG(R0 + c * plane + oa), NSOF_LDG(R0 + c * plane + ob));
+            }
             if (J.guard) { fb_um_guard(J, ya, fa.y); fb_um_guard(J, yb, fb.y); }
-            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, xa, ya, xb, yb, make_float2(fa.x, fb.x), make_float2(fa.y, fb.y), r0v, mm);
+            if (WIN)
+                fb_um_pixel2_t<true>(sM, SP, RS, wx0, wy0, RS - 2, RH - 2, J.h, J.w, xa, ya, xb, yb, make_float2(fa.x, fb.x),
+                                     make_float2(fa.y, fb.y), r0v, mm);
+            else
+                fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, xa, ya, xb, yb, make_float2(fa.x, fb.x), make_float2(fa.y, fb.y), r0v, mm);
 #pragma unroll
             for (int c = 0; c < 5; c++) { Mout[c * plane + oa] = mm[c].x; Mout[c * plane + ob] = mm[c].y; }
         } else if (va || vb) {
@@ -970,11 +1100,18 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #pragma unroll
             for (int c = 0; c < 5; c++) { const float t = NSOF_LDG(R0 + c * plane + o); r0v[c] = make_float2(t, t); }
             if (J.guard) fb_um_guard(J, y, f.y);
-            fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, x, y, x, y, make_float2(f.x, f.x), make_float2(f.y, f.y), r0v, mm);
+            if (WIN)
+                fb_um_pixel2_t<true>(sM, SP, RS, wx0, wy0, RS - 2, RH - 2, J.h, J.w, x, y, x, y, make_float2(f.x, f.x),
+                                     make_float2(f.y, f.y), r0v, mm);
+            else
+                fb_um_pixel2(R1, plane, J.pitch, J.h, J.w, x, y, x, y, make_float2(f.x, f.x), make_float2(f.y, f.y), r0v, mm);
 #pragma unroll
             for (int c = 0; c < 5; c++) Mout[c * plane + o] = mm[c].x;
         }
     }
+    };
+    if (win) phase3b(std::true_type{});
+    else phase3b(std::false_type{});
 #else
     constexpr int UNR3B = FB_BS_UNROLL;
 #pragma unroll UNR3B
@@ -1007,10 +1144,10 @@ static void (*const k_fb_blur_solve_gauss)(const FbJob *, const uint2 *, int, in
 #define FB_BS7S_TW 32   // small tile: coarse levels / small batches are latency-bound, more and shorter CTAs
 #define FB_BS7S_TH 16
 #define FB_BS7S_NT 128
-static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, const uint2 *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
-static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int, int) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
-#define FB_BS7_SMEM (16 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
-#define FB_BS7S_SMEM (16 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
+static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
+static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
+#define FB_BS7_SMEM (32 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
+#define FB_BS7S_SMEM (32 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
 
 // ---------------------------------------------------------------------------------------------
 // S2-b + S2-c fused for the two pyramid shapes every BASELINE.json config spends its time in:

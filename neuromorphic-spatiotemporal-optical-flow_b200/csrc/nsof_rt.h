@@ -145,6 +145,16 @@ static inline void nsof_mbar_expect_tx(nsof_mbar_t *, unsigned) {}
 static inline void nsof_bulk_g2s(void *dst, const void *src, unsigned bytes, nsof_mbar_t *) { memcpy(dst, src, bytes); }
 static inline void nsof_mbar_wait(nsof_mbar_t *, unsigned) {}
 static inline void nsof_prefetch_l2(const void *, unsigned) {}
+static inline void nsof_fence_proxy_async() {}
+static inline void nsof_count(unsigned *p) { ++*p; }
+// block-wide minimum / maximum into four shared integers {min a, max a, min b, max b} (one emulated thread per block)
+static inline void nsof_block_minmax4(int *s, int mna, int mxa, int mnb, int mxb)
+{
+    if (mna < s[0]) s[0] = mna;
+    if (mxa > s[1]) s[1] = mxa;
+    if (mnb < s[2]) s[2] = mnb;
+    if (mxb > s[3]) s[3] = mxb;
+}
 #define NSOF_LANE 0
 #define NSOF_SYNCWARP() ((void)0)
 static inline float2 nsof_add2(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
@@ -188,8 +198,26 @@ __device__ __forceinline__ void nsof_prefetch_l2(const void *src, unsigned bytes
 {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
+// generic-proxy accesses of shared memory (before the last barrier) -> bulk async copies into the same bytes
+__device__ __forceinline__ void nsof_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void nsof_count(unsigned *p) { atomicAdd(p, 1u); }
 #define NSOF_LANE ((int)(threadIdx.x & 31))
 #define NSOF_SYNCWARP() __syncwarp()
+// block-wide minimum / maximum into four shared integers {min a, max a, min b, max b}: REDUX per warp, then one
+// shared-memory atomic per warp and value.  Every thread of the block calls it (converged).
+__device__ __forceinline__ void nsof_block_minmax4(int *s, int mna, int mxa, int mnb, int mxb)
+{
+    mna = __reduce_min_sync(0xffffffffu, mna);
+    mxa = __reduce_max_sync(0xffffffffu, mxa);
+    mnb = __reduce_min_sync(0xffffffffu, mnb);
+    mxb = __reduce_max_sync(0xffffffffu, mxb);
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(s + 0, mna);
+        atomicMax(s + 1, mxa);
+        atomicMin(s + 2, mnb);
+        atomicMax(s + 3, mxb);
+    }
+}
 // Packed FP32 add of Blackwell (add.rn.f32x2 -> SASS FADD2): two IEEE round-to-nearest additions in one issue slot,
 // per component identical to a scalar FADD.  For kernels that are bound by instruction issue, not by the FP32 pipe.
 #ifndef NSOF_PACKED_F32

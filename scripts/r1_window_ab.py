@@ -1,0 +1,68 @@
+"""A/B of the blur+solve kernel's R1 window (shared-memory gathers, default) against the L2 gathers on the bench
+workload: the device-resident step (8 clips x 32 frames of 1080p, scripts' gate) and the full-frame step (ROI = 100 %),
+window on / off alternating in one process, plus the share of tiles that took the window.
+usage: python scripts/r1_window_ab.py [steps]"""
+import ctypes as C
+import importlib, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+nsof = importlib.import_module("nsof_b200")
+syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
+pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+K = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+Cn, F, H, W = 8, 32, 1080, 1920
+dev = torch.device("cuda:0")
+frames = torch.empty((F, Cn, H, W), dtype=torch.uint8, device=dev)
+for c in range(Cn):
+    frames[:, c] = syn.make_clip(1234 + c, H, W, F, dev)
+
+
+def engines(ds):
+    out = []
+    for s in ds.slots:
+        out += [s.eng] + [e for e, _ in s.s2_extra]
+    return out
+
+
+def timed(ds, fr, n):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        ds.submit(fr)
+    ds.drain()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+for tag, full, clips in (("gated step (248 pairs)", False, Cn), ("full frame (62 pairs)", True, 2)):
+    eng = nsof.Engine(0)
+    fr = frames[:, :clips].contiguous()
+    ds = pm.DeviceStream(eng, clips, F, H, W, depth=2, full_frame=full)
+    for _ in range(3):
+        ds.submit(fr)
+    ds.drain()
+    res = {0: [], 1: []}
+    for rep in range(3):
+        for on in (1, 0):
+            for e in engines(ds):
+                e.lib.check(e.lib.nsof_debug_r1_window(e.handle, on))
+            timed(ds, fr, 2)
+            res[on].append(timed(ds, fr, K))
+    out = (C.c_ulonglong * 2)()
+    for e in engines(ds):
+        e.lib.check(e.lib.nsof_debug_r1_window(e.handle, 1))
+        e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
+    timed(ds, fr, 2)
+    tot = [0, 0]
+    for e in engines(ds):
+        e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
+        tot[0] += out[0]; tot[1] += out[1]
+    print(f"{tag:26s} window on {min(res[1]):7.3f} ms (runs {['%.3f' % v for v in res[1]]})  off {min(res[0]):7.3f} ms "
+          f"(runs {['%.3f' % v for v in res[0]]})  tiles via window {tot[0]} / L2 {tot[1]} = "
+          f"{tot[0] / max(1, sum(tot)):.4f}", flush=True)
+    for s in ds.slots:
+        for e in [s.eng, s.s1_eng] + [e for e, _ in s.s2_extra]:
+            e.close()

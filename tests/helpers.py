@@ -458,3 +458,76 @@ def check_float32_frames(golden, farneback, what):
         assert prev.dtype == np.float32
         for pname in ("grasp", "autodriving_txt"):
             assert_flow_close(farneback(prev, nxt, **PARAM_SETS[pname]), g[f"{case}__{pname}"], pname, f"{what} f32 {case}")
+
+
+def warped_pair(seed, h, w, kind):
+    """Texture and a warped copy: kind "shift20" = translation by (+20.3, -12.6) px (large but uniform: the R1 window
+    follows it), "zoom" = 6 % zoom about the centre (|flow| grows to ~12 px, varies across every tile), "shear" =
+    dy proportional to x (vertical variation of > 3 px inside most tiles: the L2 path)."""
+    if kind == "shift20":
+        return _warp(seed, h, w, lambda y, x: (y + 12.6, x - 20.3))
+    if kind == "zoom":
+        return _warp(seed, h, w, lambda y, x: (h / 2 + (y - h / 2) / 1.06, w / 2 + (x - w / 2) / 1.06))
+    if kind == "shear":
+        return _warp(seed, h, w, lambda y, x: (y - 0.08 * (x - w / 2), x))
+    raise ValueError(kind)
+
+
+def _warp(seed, h, w, src_of):
+    """b(y, x) = base(src_of(y, x)) by bilinear sampling of a larger seeded texture (numpy only)."""
+    rng = np.random.default_rng(seed)
+    pad = 48
+    H, W = h + 2 * pad, w + 2 * pad
+    base = rng.random((H, W)).astype(np.float64)
+    k = np.exp(-0.5 * (np.arange(-9, 10) / 3.0) ** 2)
+    k /= k.sum()
+    base = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 1, base)
+    base = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 0, base)
+    base = (base - base.min()) / (base.max() - base.min()) * 255.0
+    ys, xs = np.mgrid[0:h, 0:w].astype(np.float64)
+    a = base[pad:pad + h, pad:pad + w]
+    sy, sx = src_of(ys, xs)
+    sy = np.clip(sy + pad, 0, H - 2)
+    sx = np.clip(sx + pad, 0, W - 2)
+    y0, x0 = np.floor(sy).astype(int), np.floor(sx).astype(int)
+    fy, fx = sy - y0, sx - x0
+    b = (base[y0, x0] * (1 - fx) * (1 - fy) + base[y0, x0 + 1] * fx * (1 - fy)
+         + base[y0 + 1, x0] * (1 - fx) * fy + base[y0 + 1, x0 + 1] * fx * fy)
+    return np.ascontiguousarray(a.astype(np.uint8)), np.ascontiguousarray(b.astype(np.uint8))
+
+
+def r1_window_stats(eng):
+    import ctypes as C
+    out = (C.c_ulonglong * 2)()
+    eng.lib.check(eng.lib.nsof_debug_r1_window_stats(eng.handle, out, eng._stream()), "r1_window_stats")
+    return int(out[0]), int(out[1])
+
+
+def check_r1_window(eng, hw=(300, 400)):
+    """The tuned blur+solve kernel gathers R1 from a shared-memory window that follows the tile's flow, or from L2 when
+    the flow varies too much inside a tile: both paths load the same values, so the flow must be BIT-IDENTICAL with the
+    window switched off -- for a uniform small shift, a uniform 20 px shift (window far from the tile), a zoom and a
+    shear (tiles of both kinds).  -> {kind: (window tiles, L2 tiles)} of the window-on runs."""
+    p = PARAM_SETS["grasp"]
+    r1_window_stats(eng)   # first call: counting on
+    stats = {}
+    try:
+        for big in (0, 1):   # the 32 x 16 tile of latency-bound levels (default for one small pair) and the 64 x 32 tile
+            eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, big))
+            for kind in ("shift3", "shift20", "zoom", "shear"):
+                a, b = textured_pair(61, *hw) if kind == "shift3" else warped_pair(61, *hw, kind)
+                eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 1))
+                on = eng.calcOpticalFlowFarneback(a, b, None, **p)
+                stats[kind, big] = r1_window_stats(eng)
+                eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 0))
+                off = eng.calcOpticalFlowFarneback(a, b, None, **p)
+                n_on, n_off = r1_window_stats(eng)
+                assert n_on == 0 and n_off == sum(stats[kind, big]), (kind, big, n_on, n_off, stats[kind, big])
+                assert np.array_equal(on, off), (kind, big, np.abs(on - off).max())
+                assert np.isfinite(on).all()
+            assert stats["shift3", big][0] > 0 and stats["shift20", big][0] > 0, stats
+            assert stats["shear", big][1] > 0, stats
+    finally:
+        eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 1))
+        eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, 0))
+    return stats

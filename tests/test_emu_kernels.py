@@ -368,3 +368,9 @@ def test_float32_frames_vs_cv2_golden(emu_engine, golden):
     assert np.array_equal(got, eng.calcOpticalFlowFarneback(a, b, None, **helpers.PARAM_SETS["grasp"]))
     mixed = eng.calcOpticalFlowFarneback(a, np.rint(b).astype(np.uint8), None, **helpers.PARAM_SETS["grasp"])  # mixed: both as float32
     assert mixed.shape == got.shape
+
+
+def test_emu_r1_window_bit_identical(emu_engine):
+    """Blur+solve with the R1 window in shared memory (default) against the L2 gathers, both tile shapes."""
+    stats = helpers.check_r1_window(emu_engine, hw=(200, 280))
+    assert stats["shift3", 1][1] == 0     # a uniform 3 px shift never leaves the window

@@ -164,6 +164,16 @@ def test_realdata_end_to_end(gpu_engine, nsof, ds):
         assert not res[0].any() and res[4] == (0, 0, 0, 0)
 
 
+def test_r1_window_bit_identical(gpu_engine):
+    """the 20 R1 gathers per pixel of the blur+solve kernel come from a shared-memory window placed on
+    the tile's flow range (bulk-copied into the dead M rows) instead of from L2.  Same loads, same arithmetic: the flow is
+    bit-identical with the window switched off, on uniform, large, zooming and shearing motion, for both tile shapes; the
+    tile counters show both paths taken."""
+    stats = helpers.check_r1_window(gpu_engine, hw=(540, 720))
+    print("R1 window tiles (window, L2):", stats)
+    assert stats["shift3", 1][1] == 0
+
+
 @pytest.mark.parametrize("ds,padding", [("uav", 30), ("uavnew2", 60), ("tabletennis", 20)])
 def test_realdata_small_sequences(gpu_engine, nsof, ds, padding):
     """The three shipped sequences without a script of their own, each with its data/<ds>/Parameters.txt: uav (FLAG 1,
