@@ -258,6 +258,9 @@ NSOF_API int nsof_debug_big_tiles(nsof_handle *h, int enable);
  * on the tile's flow range whenever the range fits; same values either way).  nsof_debug_r1_window_stats: out2 = {tiles
  * through the window, tiles on the L2 path} since the previous call (the first call switches the counting on). */
 NSOF_API int nsof_debug_r1_window(nsof_handle *h, int enable);
+/* off_mask bit 0 / 1: no bulk L2 prefetch of the tile's R0 / R1 rows in phase 1 of the tuned blur+solve kernel (A/B);
+ * -1 restores the default (no prefetch while the R1 window is on). */
+NSOF_API int nsof_debug_bs_prefetch(nsof_handle *h, int off_mask);
 NSOF_API int nsof_debug_r1_window_stats(nsof_handle *h, unsigned long long *out2, void *cuda_stream);
 NSOF_API int nsof_debug_fetch(nsof_handle *h, int item, int what, float *out, int *out_h, int *out_w);
 

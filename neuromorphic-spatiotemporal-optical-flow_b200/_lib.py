@@ -151,6 +151,7 @@ _SIGNATURES = {
     "nsof_debug_lanczos_f64": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_big_tiles": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_r1_window": (C.c_int, [C.c_void_p, C.c_int]),
+    "nsof_debug_bs_prefetch": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_r1_window_stats": (C.c_int, [C.c_void_p, _P(C.c_ulonglong), C.c_void_p]),
     "nsof_debug_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, _P(C.c_int), _P(C.c_int)]),
     "nsof_roi_from_state_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _P(RoiParams), C.c_void_p, C.c_void_p,

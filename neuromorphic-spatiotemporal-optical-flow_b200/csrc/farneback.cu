@@ -118,6 +118,7 @@ extern "C" int nsof_create(int device, nsof_handle **out)
     h->last_plan = new std::vector<FbItemPlan>();
     if (const char *e = getenv("NSOF_SHARE_FRAMES")) h->dbg_no_dedup = e[0] == '0';  // A/B measurements (default: on)
     if (const char *e = getenv("NSOF_R1_WINDOW")) h->dbg_no_r1_window = e[0] == '0';  // A/B measurements (default: on)
+    if (const char *e = getenv("NSOF_BS_NO_PREFETCH")) h->dbg_bs_no_prefetch = atoi(e) < 0 ? -1 : (atoi(e) & 3);
     if (const char *e = getenv("NSOF_LANCZOS_F64")) h->dbg_lz_f64 = e[0] == '1';     // A/B: FP64 Lanczos kernels
     *out = h;
     return NSOF_OK;
@@ -881,7 +882,11 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
     const uint2 *tl_bs = X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + FB_L_BS];
     (void)na;
     if (!n_bs) { h->prof_level = -1; return NSOF_OK; }  // empty sub-window
-    const int bs_flags = (last ? 1 : 0) | (h->dbg_no_r1_window ? 2 : 0);
+    // L2 prefetch of the tile's R rows in phase 1: only with the window off (with it, measured on the bench workload:
+    // 8.80 -> 8.50 ms per step without the prefetches -- the window copy replaces the R1 gathers and the R0 loads run one
+    // iteration ahead, so the 390 prefetch instructions per tile were issue cost only)
+    const int pf_off = h->dbg_bs_no_prefetch >= 0 ? (h->dbg_bs_no_prefetch & 3) : (h->dbg_no_r1_window ? 0 : 3);
+    const int bs_flags = (last ? 1 : 0) | (h->dbg_no_r1_window ? 2 : 0) | (pf_off << 2);
     unsigned *bs_stats = h->dbg_r1_stats ? (unsigned *)h->r1_stats_buf.p : nullptr;
     if (X.bs_m7 && X.bs_small[kk])  // latency-bound level: the 32x16 tile (see fb_prepare)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7S, n_bs, 1, 1,
@@ -1613,6 +1618,15 @@ extern "C" int nsof_debug_r1_window(nsof_handle *h, int enable)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     h->dbg_no_r1_window = !enable;
+    return NSOF_OK;
+}
+
+// mask bit 0 / 1: the tuned blur+solve kernel does not prefetch the tile's R0 / R1 rows into L2 in phase 1 (A/B);
+// -1: the default (no prefetch while the R1 window is on, both prefetches with the window off)
+extern "C" int nsof_debug_bs_prefetch(nsof_handle *h, int off_mask)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_bs_no_prefetch = off_mask < 0 ? -1 : (off_mask & 3);
     return NSOF_OK;
 }
 

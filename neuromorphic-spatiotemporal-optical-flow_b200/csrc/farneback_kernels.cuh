@@ -784,7 +784,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
                                                            int src_is_a, int flags, unsigned *stats)
 {
     // flags: bit 0 last iteration of the level (flow -> HBM, no UpdateMatrices); bit 1 keep the R1 gathers on the L2
-    // path (nsof_debug_r1_window(h, 0): A/B runs and the bit-identity test).  stats (NULL: off): tiles counted by path.
+    // path (nsof_debug_r1_window(h, 0): A/B runs and the bit-identity test); bits 2 / 3 no L2 prefetch of the tile's R0 /
+    // R1 rows in phase 1 (nsof_debug_bs_prefetch).  stats (NULL: off): tiles counted by path.
     const int last = flags & 1;
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
@@ -827,14 +828,15 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     // phase 3b reads R0 and gathers R1 around this tile: start pulling those rows into L2 now (bulk prefetch, one
     // instruction per row; R1 with a margin of ML columns / M rows for the displacement), so that the dependent
     // loads two phases later find them there instead of paying DRAM latency at 35 % occupancy
-    if (!last) {
+    if (!last && (flags & 12) != 12) {
         const int px0 = nsof_imax(tx0 - ML, 0), px1 = nsof_imin(tx0 + TW + ML, J.pitch);
         const int py0 = nsof_imax(ty0 - M, 0), py1 = nsof_imin(ty0 + TH + M, J.h);
         const int t0 = nsof_imin(tx0 + TW, J.pitch);
+        const bool pf0 = !(flags & 4), pf1 = !(flags & 8);   // A/B switches (nsof_debug_bs_prefetch)
         for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
             const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
-            nsof_prefetch_l2(J.R[1] + c * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
-            if (gy >= ty0 && gy < ty0 + TH) nsof_prefetch_l2(J.R[0] + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(t0 - tx0) * 4u);
+            if (pf1) nsof_prefetch_l2(J.R[1] + c * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
+            if (pf0 && gy >= ty0 && gy < ty0 + TH) nsof_prefetch_l2(J.R[0] + c * plane + (size_t)gy * J.pitch + tx0, (unsigned)(t0 - tx0) * 4u);
         }
     }
     // one warp polls the mbarrier; the others sleep in the block barrier (a try_wait spin in every warp
@@ -1008,9 +1010,20 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     const bool win = !(flags & 2) && s_rng[0] <= s_rng[1] && s_rng[2] <= s_rng[3] && s_rng[1] - wx0 <= RS - 2 &&
                      s_rng[3] - wy0 <= RH - 2;
     if (stats && NSOF_TID == 0) nsof_count(stats + (win ? 0 : 1));
+    if (!win && (flags & 8)) {
+        // a tile that keeps the L2 gathers while phase 1 skipped the R1 prefetch (the default with the window on: for the
+        // 99 % of tiles that take the window the 390 prefetch instructions were pure issue cost): start it now
+        const int px0 = nsof_imax(tx0 - ML, 0), px1 = nsof_imin(tx0 + TW + ML, J.pitch);
+        const int py0 = nsof_imax(ty0 - M, 0), py1 = nsof_imin(ty0 + TH + M, J.h);
+        for (int r = NSOF_TID; r < 5 * (py1 - py0); r += NSOF_NT) {
+            const int c = r / (py1 - py0), gy = py0 + r - c * (py1 - py0);
+            nsof_prefetch_l2(R1 + c * plane + (size_t)gy * J.pitch + px0, (unsigned)(px1 - px0) * 4u);
+        }
+    }
     if (win) {
         // the window's rows of the five R1 planes -> rows 0 .. TH-1 of the M planes (dead since phase 3a)
-        const int ncol = nsof_imin(wx0 + RS, J.pitch) - wx0, nrow = nsof_imin(wy0 + RH, J.h) - wy0;
+        // (only the rows between the smallest y1 and the largest y1 + 1: 33 of the 35 for a uniform flow)
+        const int ncol = nsof_imin(wx0 + RS, J.pitch) - wx0, nrow = s_rng[3] + 2 - wy0;
         if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, (unsigned)(ncol * 4) * (unsigned)(5 * nrow));
         nsof_fence_proxy_async();
         for (int r = NSOF_TID; r < 5 * nrow; r += NSOF_NT) {

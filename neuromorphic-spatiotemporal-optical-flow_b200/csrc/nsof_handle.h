@@ -109,6 +109,7 @@ struct nsof_handle {
     std::vector<cudaEvent_t> ev_level;
     bool dbg_big_tiles = false;  // keep the 64x32 blur tile on every level (tests)
     bool dbg_no_r1_window = false;  // blur+solve: gather R1 from L2 in every tile (nsof_debug_r1_window(h, 0))
+    int dbg_bs_no_prefetch = -1;    // bit 0 / 1: no L2 prefetch of R0 / R1 rows in blur+solve phase 1; -1: default (see the blur+solve launch in farneback.cu)
     bool dbg_r1_stats = false;      // count the tiles of either path (nsof_debug_r1_window_stats)
     NsofDevBuf r1_stats_buf;        // 2 x unsigned: tiles through the shared-memory window, tiles on the L2 path
     bool no_fork = false;  // nsof_debug_fork(h, 0): everything on the caller's stream

@@ -1,5 +1,5 @@
-"""A/B of the blur+solve kernel's R1 window (shared-memory gathers, default) against the L2 gathers on the bench
-workload: the device-resident step (8 clips x 32 frames of 1080p, scripts' gate) and the full-frame step (ROI = 100 %),
+"""A/B of the blur+solve kernel's R1 window (shared-memory gathers, default) against the L2 gathers, and of the bulk L2
+prefetches of its phase 1, on the bench workload: the device-resident step (8 clips x 32 frames of 1080p, scripts' gate) and the full-frame step (ROI = 100 %),
 window on / off alternating in one process, plus the share of tiles that took the window.
 usage: python scripts/r1_window_ab.py [steps]"""
 import ctypes as C
@@ -44,25 +44,29 @@ for tag, full, clips in (("gated step (248 pairs)", False, Cn), ("full frame (62
     for _ in range(3):
         ds.submit(fr)
     ds.drain()
-    res = {0: [], 1: []}
+    variants = [("window, no prefetch (default)", 1, 3), ("window, R0 + R1 prefetch", 1, 0), ("window, R1 prefetch", 1, 1),
+                ("window, R0 prefetch", 1, 2), ("L2 gathers, prefetch (round 1)", 0, 0), ("L2 gathers, no prefetch", 0, 3)]
+    res = {v[0]: [] for v in variants}
     for rep in range(3):
-        for on in (1, 0):
+        for name, on, mask in variants:
             for e in engines(ds):
                 e.lib.check(e.lib.nsof_debug_r1_window(e.handle, on))
+                e.lib.check(e.lib.nsof_debug_bs_prefetch(e.handle, mask))
             timed(ds, fr, 2)
-            res[on].append(timed(ds, fr, K))
+            res[name].append(timed(ds, fr, K))
     out = (C.c_ulonglong * 2)()
     for e in engines(ds):
         e.lib.check(e.lib.nsof_debug_r1_window(e.handle, 1))
+        e.lib.check(e.lib.nsof_debug_bs_prefetch(e.handle, -1))
         e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
     timed(ds, fr, 2)
     tot = [0, 0]
     for e in engines(ds):
         e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
         tot[0] += out[0]; tot[1] += out[1]
-    print(f"{tag:26s} window on {min(res[1]):7.3f} ms (runs {['%.3f' % v for v in res[1]]})  off {min(res[0]):7.3f} ms "
-          f"(runs {['%.3f' % v for v in res[0]]})  tiles via window {tot[0]} / L2 {tot[1]} = "
-          f"{tot[0] / max(1, sum(tot)):.4f}", flush=True)
+    print(f"{tag}: tiles via window {tot[0]} / L2 {tot[1]} = {tot[0] / max(1, sum(tot)):.4f}")
+    for name, _, _ in variants:
+        print(f"    {name:34s} {min(res[name]):7.3f} ms per step (runs {['%.3f' % v for v in res[name]]})", flush=True)
     for s in ds.slots:
         for e in [s.eng, s.s1_eng] + [e for e, _ in s.s2_extra]:
             e.close()
