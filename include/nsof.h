@@ -254,9 +254,11 @@ NSOF_API int nsof_debug_lanczos_f64(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fork(nsof_handle *h, int enable);
 /* enable = 1 keeps the large blur+solve tile on every level (default: latency-bound levels take the small one). */
 NSOF_API int nsof_debug_big_tiles(nsof_handle *h, int enable);
-/* enable = 0: the tuned blur+solve kernel gathers R1 from L2 in every tile (default: from a shared-memory window placed
- * on the tile's flow range whenever the range fits; same values either way).  nsof_debug_r1_window_stats: out2 = {tiles
- * through the window, tiles on the L2 path} since the previous call (the first call switches the counting on). */
+/* enable = 2: window in the blur+solve kernel only.  enable = 0: the tuned blur+solve kernel gathers R1 from L2 in every tile (default: from a shared-memory window placed
+ * on the tile's flow range whenever the range fits; same values either way), and the first UpdateMatrices of a level runs
+ * the round-1 kernel.  nsof_debug_r1_window_stats: out2[0..3] (FOUR counters) = {blur+solve tiles through the window,
+ * blur+solve tiles on the L2 path, the same two for the first UpdateMatrices} since the previous call (the first call
+ * switches the counting on). */
 NSOF_API int nsof_debug_r1_window(nsof_handle *h, int enable);
 /* off_mask bit 0 / 1: no bulk L2 prefetch of the tile's R0 / R1 rows in phase 1 of the tuned blur+solve kernel (A/B);
  * -1 restores the default (no prefetch while the R1 window is on). */

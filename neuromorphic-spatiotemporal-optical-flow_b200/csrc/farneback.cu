@@ -117,7 +117,10 @@ extern "C" int nsof_create(int device, nsof_handle **out)
     h->device = device;
     h->last_plan = new std::vector<FbItemPlan>();
     if (const char *e = getenv("NSOF_SHARE_FRAMES")) h->dbg_no_dedup = e[0] == '0';  // A/B measurements (default: on)
-    if (const char *e = getenv("NSOF_R1_WINDOW")) h->dbg_no_r1_window = e[0] == '0';  // A/B measurements (default: on)
+    if (const char *e = getenv("NSOF_R1_WINDOW")) {  // A/B measurements (default: on; 2 = blur+solve only)
+        h->dbg_no_r1_window = e[0] == '0';
+        h->dbg_um_round1 = e[0] == '0' || e[0] == '2';
+    }
     if (const char *e = getenv("NSOF_BS_NO_PREFETCH")) h->dbg_bs_no_prefetch = atoi(e) < 0 ? -1 : (atoi(e) & 3);
     if (const char *e = getenv("NSOF_LANCZOS_F64")) h->dbg_lz_f64 = e[0] == '1';     // A/B: FP64 Lanczos kernels
     *out = h;
@@ -857,7 +860,15 @@ static int fb_launch_um_first(nsof_handle *h, int k, cudaStream_t stream, int va
     if (X.params.iterations == 0)
         NSOF_KLAUNCH(h, NSOF_K_FLOW_INIT, 8 * X.sumNc[kk] + 8 * X.sumN[kk], k_fb_flow_init, n_um, 1, 1, 256, 0, stream,
                      jobs, tl_um, X.flow_mul);
-    else if (X.params.flags & NSOF_FB_USE_INITIAL_FLOW)
+    else if (!h->dbg_um_round1) {  // R1 taps from a shared-memory window wherever the tile's initial flow allows it
+        unsigned *um_stats = h->dbg_r1_stats ? (unsigned *)h->r1_stats_buf.p + 2 : nullptr;
+        if (X.params.flags & NSOF_FB_USE_INITIAL_FLOW)
+            NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_win_init, n_um, 1, 1, 256,
+                         FB_UMW_SMEM, stream, jobs, tl_um, X.flow_mul, 0, um_stats);
+        else
+            NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_win, n_um, 1, 1, 256,
+                         FB_UMW_SMEM, stream, jobs, tl_um, X.flow_mul, 0, um_stats);
+    } else if (X.params.flags & NSOF_FB_USE_INITIAL_FLOW)
         NSOF_KLAUNCH(h, NSOF_K_UM_FIRST, 60 * X.sumN[kk] + 8 * X.sumNc[kk], k_fb_um_first_init, n_um, 1, 1, 256, 0, stream,
                      jobs, tl_um, X.flow_mul);
     else
@@ -1617,7 +1628,8 @@ extern "C" int nsof_debug_big_tiles(nsof_handle *h, int enable)
 extern "C" int nsof_debug_r1_window(nsof_handle *h, int enable)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
-    h->dbg_no_r1_window = !enable;
+    h->dbg_no_r1_window = enable == 0;
+    h->dbg_um_round1 = enable == 0 || enable == 2;   // 2: window in blur+solve only (A/B of the two kernels)
     return NSOF_OK;
 }
 
@@ -1630,26 +1642,26 @@ extern "C" int nsof_debug_bs_prefetch(nsof_handle *h, int off_mask)
     return NSOF_OK;
 }
 
-// out2 = {tiles whose R1 gathers came from the shared-memory window, tiles on the L2 path} since the previous call, then
-// zeroed; the first call (or out2 == NULL) switches the counting on.  Synchronises `cuda_stream`.
+// out2[0..3] (FOUR counters) = {blur+solve tiles whose R1 gathers came from the shared-memory window, blur+solve tiles on
+// the L2 path, the same two for the first UpdateMatrices of a level} since the previous call, then zeroed; the first call (or out2 == NULL) switches the counting on.  Synchronises `cuda_stream`.
 extern "C" int nsof_debug_r1_window_stats(nsof_handle *h, unsigned long long *out2, void *cuda_stream)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     if (!h->dbg_r1_stats) {
-        int rc = h->r1_stats_buf.ensure(2 * sizeof(unsigned));
+        int rc = h->r1_stats_buf.ensure(4 * sizeof(unsigned));
         if (rc != NSOF_OK) return rc;
-        NSOF_CUDA_TRY(cudaMemsetAsync(h->r1_stats_buf.p, 0, 2 * sizeof(unsigned), st));
+        NSOF_CUDA_TRY(cudaMemsetAsync(h->r1_stats_buf.p, 0, 4 * sizeof(unsigned), st));
         NSOF_CUDA_TRY(cudaStreamSynchronize(st));
         h->dbg_r1_stats = true;
-        if (out2) out2[0] = out2[1] = 0;
+        if (out2) out2[0] = out2[1] = out2[2] = out2[3] = 0;
         return NSOF_OK;
     }
-    unsigned v[2] = {0, 0};
+    unsigned v[4] = {0, 0, 0, 0};
     NSOF_CUDA_TRY(cudaMemcpyAsync(v, h->r1_stats_buf.p, sizeof(v), cudaMemcpyDeviceToHost, st));
     NSOF_CUDA_TRY(cudaMemsetAsync(h->r1_stats_buf.p, 0, sizeof(v), st));
     NSOF_CUDA_TRY(cudaStreamSynchronize(st));
-    if (out2) { out2[0] = v[0]; out2[1] = v[1]; }
+    if (out2) { out2[0] = v[0]; out2[1] = v[1]; out2[2] = v[2]; out2[3] = v[3]; }
     return NSOF_OK;
 }
 

@@ -265,8 +265,12 @@ NSOF_GLOBAL k_fb_polyexp(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_REST
 // S2-d: FarnebackUpdateMatrices for one pixel (A.6).  r0v = R0 at (x,y); R1 is gathered
 // bilinearly at (x+dx, y+dy) through the read-only path (data-dependent: no TMA tiling).
 // ---------------------------------------------------------------------------------------------
-NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int h, int w, int x, int y,
-                          float dx, float dy, const float r0v[5], float out[5])
+// WIN = 1: R1 is a window of the plane staged in shared memory (see fb_um_pixel2_t): `pitch` floats per row, `plane`
+// floats per plane, element (0, 0) = image pixel (wx0, wy0), (ww, wh) the largest in-window cell offsets.
+#define FB_UM_LD(p) (WIN ? *(p) : NSOF_LDG(p))
+template <bool WIN>
+NSOF_DEV void fb_um_pixel_t(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int wx0, int wy0, int ww, int wh, int h,
+                            int w, int x, int y, float dx, float dy, const float r0v[5], float out[5])
 {
     float fx = (float)x + dx, fy = (float)y + dy;
     const int x1 = (int)floorf(fx), y1 = (int)floorf(fy);
@@ -278,16 +282,22 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
     const bool inb = (unsigned)x1 < (unsigned)(w - 1) && (unsigned)y1 < (unsigned)(h - 1);
     {
         const float a00 = (1.f - fx) * (1.f - fy), a01 = fx * (1.f - fy), a10 = (1.f - fx) * fy, a11 = fx * fy;
-        const float *p = R1 + (inb ? (size_t)y1 * pitch + x1 : (size_t)0);
-        const float q2 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float *p;
+        if (WIN) {
+            const int rx = x1 - wx0, ry = y1 - wy0;
+            p = R1 + ((inb && (unsigned)rx <= (unsigned)ww && (unsigned)ry <= (unsigned)wh) ? ry * pitch + rx : 0);
+        } else {
+            p = R1 + (inb ? (size_t)y1 * pitch + x1 : (size_t)0);
+        }
+        const float q2 = a00 * FB_UM_LD(p) + a01 * FB_UM_LD(p + 1) + a10 * FB_UM_LD(p + pitch) + a11 * FB_UM_LD(p + pitch + 1);
         p += plane;
-        const float q3 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q3 = a00 * FB_UM_LD(p) + a01 * FB_UM_LD(p + 1) + a10 * FB_UM_LD(p + pitch) + a11 * FB_UM_LD(p + pitch + 1);
         p += plane;
-        const float q4 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q4 = a00 * FB_UM_LD(p) + a01 * FB_UM_LD(p + 1) + a10 * FB_UM_LD(p + pitch) + a11 * FB_UM_LD(p + pitch + 1);
         p += plane;
-        const float q5 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q5 = a00 * FB_UM_LD(p) + a01 * FB_UM_LD(p + 1) + a10 * FB_UM_LD(p + pitch) + a11 * FB_UM_LD(p + pitch + 1);
         p += plane;
-        const float q6 = a00 * NSOF_LDG(p) + a01 * NSOF_LDG(p + 1) + a10 * NSOF_LDG(p + pitch) + a11 * NSOF_LDG(p + pitch + 1);
+        const float q6 = a00 * FB_UM_LD(p) + a01 * FB_UM_LD(p + 1) + a10 * FB_UM_LD(p + pitch) + a11 * FB_UM_LD(p + pitch + 1);
         r2 = inb ? q2 : 0.f;
         r3 = inb ? q3 : 0.f;
         r4 = inb ? (r0v[2] + q4) * 0.5f : r0v[2];
@@ -312,6 +322,12 @@ NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch
     out[2] = r5 * r5 + r6 * r6;
     out[3] = r4 * r2 + r6 * r3;
     out[4] = r6 * r2 + r5 * r3;
+}
+
+NSOF_DEV void fb_um_pixel(const float *NSOF_RESTRICT R1, size_t plane, int pitch, int h, int w, int x, int y,
+                          float dx, float dy, const float r0v[5], float out[5])
+{
+    fb_um_pixel_t<false>(R1, plane, pitch, 0, 0, 0, 0, h, w, x, y, dx, dy, r0v, out);
 }
 
 // Two pixels at once with the packed FP32 instructions of Blackwell (FMUL2 / FFMA2 / FADD2): the same operations as
@@ -409,8 +425,8 @@ NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitc
 // First UpdateMatrices of a level; the initial flow is zero (coarsest level) or the coarser
 // level's flow upsampled on the fly (S2-f: resize INTER_LINEAR, times f32(1/pyr_scale)); the
 // upsampled field itself is never written (UpdateFlow_Blur overwrites flow entirely).
-#define FB_UM_TW 128
-#define FB_UM_TH 8
+#define FB_UM_TW 64   // (128 x 8 before the window kernel: its window needs rows, not width)
+#define FB_UM_TH 16
 
 // tiled runs: flag a gather that reaches R1 rows this rank neither owns nor received
 NSOF_DEV void fb_um_guard(const FbJob &J, int y, float dy)
@@ -503,6 +519,156 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_g(const FbJob *NSO
 
 static void (*const k_fb_um_first)(const FbJob *, const uint2 *, float) = k_fb_um_first_g<0>;
 static void (*const k_fb_um_first_init)(const FbJob *, const uint2 *, float) = k_fb_um_first_g<1>;
+
+// The same step with the R1 taps in shared memory (round 2; the kernel above stays as the window-off path).  ncu of the
+// kernel above at level 0: L1 the busiest unit (87 %: with 4 pixels per thread a gather touches 4+ lines), top stall
+// long_scoreboard 5.4, 297 instructions per pixel.  Here every thread owns one column of the tile (one pixel per lane, FB_UM_TH
+// / (NT / TW) rows), computes its pixels' initial flow first (registers), the block reduces the range of the bilinear
+// cells they touch, and when the range fits (TH+3) x (TW+8) pixels -- the initial flow is the upsampled coarser flow: smooth
+// -- the five R1 planes of that window arrive by bulk copies and the 20 taps per pixel are LDS with immediate offsets.
+// Tiles whose range does not fit gather from L2 as above (one pixel per lane).  Arithmetic per pixel = fb_um_pixel.
+// dynamic smem: 32 B (mbarrier, 4 range integers) + 5 * FB_UMW_RH * FB_UMW_RS floats + (TW + TH) x 16 B of coordinates.
+struct alignas(16) FbLin {
+    int i0, i1;
+    float a;
+    int pad;
+};
+#define FB_UMW_RS (FB_UM_TW + 8)
+#define FB_UMW_RH (FB_UM_TH + 3)
+#define FB_UMW_SMEM (32 + 5 * FB_UMW_RH * FB_UMW_RS * sizeof(float) + (FB_UM_TW + FB_UM_TH) * 16)
+template <int INIT>
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_w(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float flow_mul,
+                                                                int flags, unsigned *stats)
+{
+    constexpr int TW = FB_UM_TW, TH = FB_UM_TH, NT = 256, RS = FB_UMW_RS, RH = FB_UMW_RH, SP = RH * RS;
+    constexpr int ROWS = NT / TW, NPX = TH / ROWS;   // rows per pass, pixels per thread
+    static_assert(NT % TW == 0 && TH % ROWS == 0 && RS % 4 == 0, "one column per thread");
+    const uint2 te = tl[NSOF_BX];
+    NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
+    const int tile = (int)te.y;
+    const int tiles_x = (J.w + TW - 1) / TW;
+    const size_t plane = (size_t)J.pitch * J.h;
+    const int tx0 = (tile % tiles_x) * TW, ty0 = J.y_lo + (tile / tiles_x) * TH;
+    NSOF_DYN_SMEM(smem_raw);
+    nsof_mbar_t *bar = (nsof_mbar_t *)smem_raw;
+    int *s_rng = (int *)(smem_raw + 16);
+    float *sW = (float *)(smem_raw + 32);
+    // source coordinates of the flow upsample (fb_lin_coord: double arithmetic) once per tile column / row instead of once
+    // per pixel: {i0, i1, a} of the TW columns, then of the TH rows (the first profile of this kernel spent a third of its
+    // instructions on them)
+    FbLin *s_lin = (FbLin *)(sW + 5 * SP);
+    if (NSOF_TID == 0) {
+        nsof_mbar_init(bar, 1);
+        s_rng[0] = s_rng[2] = 0x7fffffff;
+        s_rng[1] = s_rng[3] = -0x7fffffff - 1;
+    }
+    if (J.ch > 0 && !(INIT && J.init))
+        for (int i = NSOF_TID; i < TW + TH; i += NSOF_NT) {
+            FbLin v;
+            v.pad = 0;
+            if (i < TW) fb_lin_coord(tx0 + i, J.fsx, J.cw, &v.i0, &v.i1, &v.a);
+            else fb_lin_coord(ty0 + i - TW, J.fsy, J.ch, &v.i0, &v.i1, &v.a);
+            s_lin[i] = v;
+        }
+    NSOF_SYNC();
+    const float *R0 = J.R[0], *R1 = J.R[1];
+    // (emulator: the one thread of a block walks the NT thread slots and keeps all their flows)
+#ifdef NSOF_EMU
+    float2 dv[NPX * NT];
+#else
+    float2 dv[NPX];
+#endif
+    float tmnx = 3.0e38f, tmxx = -3.0e38f, tmny = 3.0e38f, tmxy = -3.0e38f;
+    // ---- phase A: the initial flow of this thread's pixels, and the range of fl(x + dx), fl(y + dy)
+    NSOF_FOR_SLOTS(t, ts, NT) {
+        const int lx = t % TW, x = tx0 + lx;
+#pragma unroll
+        for (int k = 0; k < NPX; k++) {
+            const int y = ty0 + t / TW + k * ROWS;
+            float2 d = make_float2(0.f, 0.f);
+            if (x < J.w && y < J.y_hi) {
+                if (INIT && J.init) d = NSOF_LDG(J.cflow + (size_t)y * J.cpitch + x);
+                else if (J.ch > 0) {  // = fb_upsampled_flow(J, x, y, flow_mul) with the tabulated coordinates
+                    const FbLin cx = s_lin[lx], cy = s_lin[TW + (y - ty0)];
+                    const float ax = cx.a, ay = cy.a;
+                    const float2 *r0p = J.cflow + (size_t)cy.i0 * J.cpitch, *r1p = J.cflow + (size_t)cy.i1 * J.cpitch;
+                    const float2 f00 = NSOF_LDG(r0p + cx.i0), f01 = NSOF_LDG(r0p + cx.i1);
+                    const float2 f10 = NSOF_LDG(r1p + cx.i0), f11 = NSOF_LDG(r1p + cx.i1);
+                    const float a0 = 1.f - ax, b0 = 1.f - ay;
+                    d = make_float2(((f00.x * a0 + f01.x * ax) * b0 + (f10.x * a0 + f11.x * ax) * ay) * flow_mul,
+                                    ((f00.y * a0 + f01.y * ax) * b0 + (f10.y * a0 + f11.y * ax) * ay) * flow_mul);
+                }
+                const float px = (float)x + d.x, py = (float)y + d.y;
+                tmnx = fminf(tmnx, px); tmxx = fmaxf(tmxx, px);
+                tmny = fminf(tmny, py); tmxy = fmaxf(tmxy, py);
+            }
+            dv[ts * NPX + k] = d;
+        }
+    }
+    {
+        const int a = nsof_imax((int)floorf(fminf(fmaxf(tmnx, -1.f), 1.0e9f)), 0);
+        const int b = nsof_imin((int)floorf(fmaxf(fminf(tmxx, 1.0e9f), -2.f)), J.w - 2);
+        const int c = nsof_imax((int)floorf(fminf(fmaxf(tmny, -1.f), 1.0e9f)), 0);
+        const int d = nsof_imin((int)floorf(fmaxf(fminf(tmxy, 1.0e9f), -2.f)), J.h - 2);
+        nsof_block_minmax4(s_rng, a, b, c, d);
+    }
+    NSOF_SYNC();
+    const int wx0 = s_rng[0] & ~3, wy0 = s_rng[2];
+    const bool win = !(flags & 2) && s_rng[0] <= s_rng[1] && s_rng[2] <= s_rng[3] && s_rng[1] - wx0 <= RS - 2 &&
+                     s_rng[3] - wy0 <= RH - 2;
+    if (stats && NSOF_TID == 0) nsof_count(stats + (win ? 0 : 1));
+    if (win) {
+        const int ncol = nsof_imin(wx0 + RS, J.pitch) - wx0, nrow = s_rng[3] + 2 - wy0;
+        if (NSOF_TID == 0) nsof_mbar_expect_tx(bar, (unsigned)(ncol * 4) * (unsigned)(5 * nrow));
+        for (int r = NSOF_TID; r < 5 * nrow; r += NSOF_NT) {
+            const int c = r / nrow, ly = r - c * nrow;
+            nsof_bulk_g2s(sW + c * SP + ly * RS, R1 + c * plane + (size_t)(wy0 + ly) * J.pitch + wx0, (unsigned)(ncol * 4), bar);
+        }
+    }
+    // ---- phase C: UpdateMatrices, one pixel per lane
+    auto phase_c = [&](auto win_c) {
+        constexpr bool WIN = decltype(win_c)::value;
+        bool waited = !WIN;
+        NSOF_FOR_SLOTS(t, ts, NT) {
+            const int lx = t % TW, x = tx0 + lx;
+            float r0[NPX][5];
+            // R0 of all the thread's pixels first (independent of the window): in flight while the copy lands
+#pragma unroll
+            for (int k = 0; k < NPX; k++) {
+                const int y = ty0 + t / TW + k * ROWS;
+                if (x < J.w && y < J.y_hi) {
+                    const size_t o = (size_t)y * J.pitch + x;
+#pragma unroll
+                    for (int c = 0; c < 5; c++) r0[k][c] = NSOF_LDG(R0 + c * plane + o);
+                }
+            }
+            if (!waited) {
+                if (NSOF_TID < NSOF_WARP) nsof_mbar_wait(bar, 0);
+                NSOF_SYNC();
+                waited = true;
+            }
+#pragma unroll
+            for (int k = 0; k < NPX; k++) {
+                const int y = ty0 + t / TW + k * ROWS;
+                if (x < J.w && y < J.y_hi) {
+                    const float2 d = dv[ts * NPX + k];
+                    float mm[5];
+                    if (J.guard) fb_um_guard(J, y, d.y);
+                    if (WIN) fb_um_pixel_t<true>(sW, SP, RS, wx0, wy0, RS - 2, RH - 2, J.h, J.w, x, y, d.x, d.y, r0[k], mm);
+                    else fb_um_pixel(R1, plane, J.pitch, J.h, J.w, x, y, d.x, d.y, r0[k], mm);
+                    const size_t o = (size_t)y * J.pitch + x;
+#pragma unroll
+                    for (int c = 0; c < 5; c++) J.Ma[c * plane + o] = mm[c];
+                }
+            }
+        }
+    };
+    if (win) phase_c(std::true_type{});
+    else phase_c(std::false_type{});
+}
+
+static void (*const k_fb_um_first_win)(const FbJob *, const uint2 *, float, int, unsigned *) = k_fb_um_first_w<0>;
+static void (*const k_fb_um_first_win_init)(const FbJob *, const uint2 *, float, int, unsigned *) = k_fb_um_first_w<1>;
 
 // ---------------------------------------------------------------------------------------------
 // OPTFLOW_USE_INITIAL_FLOW (A.8): flow_coarsest = resize(flow0, (w_k, h_k), INTER_AREA) * f32(scale_k), two-channel

@@ -146,6 +146,9 @@ static inline void nsof_bulk_g2s(void *dst, const void *src, unsigned bytes, nso
 static inline void nsof_mbar_wait(nsof_mbar_t *, unsigned) {}
 static inline void nsof_prefetch_l2(const void *, unsigned) {}
 static inline void nsof_fence_proxy_async() {}
+// A kernel whose threads keep per-thread state across a block barrier: the one emulated thread of a block walks the NT
+// thread slots (slot index ts for its state arrays); on the device every thread is its own slot 0.
+#define NSOF_FOR_SLOTS(t, ts, NT) for (int t = 0, ts = 0; t < (NT); t++, ts++)
 static inline void nsof_count(unsigned *p) { ++*p; }
 // block-wide minimum / maximum into four shared integers {min a, max a, min b, max b} (one emulated thread per block)
 static inline void nsof_block_minmax4(int *s, int mna, int mxa, int mnb, int mxb)
@@ -201,6 +204,7 @@ __device__ __forceinline__ void nsof_prefetch_l2(const void *src, unsigned bytes
 // generic-proxy accesses of shared memory (before the last barrier) -> bulk async copies into the same bytes
 __device__ __forceinline__ void nsof_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void nsof_count(unsigned *p) { atomicAdd(p, 1u); }
+#define NSOF_FOR_SLOTS(t, ts, NT) for (int t = (int)threadIdx.x, ts = 0; ts < 1; ts++)
 #define NSOF_LANE ((int)(threadIdx.x & 31))
 #define NSOF_SYNCWARP() __syncwarp()
 // block-wide minimum / maximum into four shared integers {min a, max a, min b, max b}: REDUX per warp, then one

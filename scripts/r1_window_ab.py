@@ -44,8 +44,9 @@ for tag, full, clips in (("gated step (248 pairs)", False, Cn), ("full frame (62
     for _ in range(3):
         ds.submit(fr)
     ds.drain()
-    variants = [("window, no prefetch (default)", 1, 3), ("window, R0 + R1 prefetch", 1, 0), ("window, R1 prefetch", 1, 1),
-                ("window, R0 prefetch", 1, 2), ("L2 gathers, prefetch (round 1)", 0, 0), ("L2 gathers, no prefetch", 0, 3)]
+    variants = [("windows in both kernels (default)", 1, -1), ("window in blur+solve only", 2, -1),
+                ("blur+solve only, R0 + R1 prefetch", 2, 0), ("blur+solve only, R1 prefetch", 2, 1),
+                ("blur+solve only, R0 prefetch", 2, 2), ("L2 gathers, prefetch (round 1)", 0, 0), ("L2 gathers, no prefetch", 0, 3)]
     res = {v[0]: [] for v in variants}
     for rep in range(3):
         for name, on, mask in variants:
@@ -54,17 +55,19 @@ for tag, full, clips in (("gated step (248 pairs)", False, Cn), ("full frame (62
                 e.lib.check(e.lib.nsof_debug_bs_prefetch(e.handle, mask))
             timed(ds, fr, 2)
             res[name].append(timed(ds, fr, K))
-    out = (C.c_ulonglong * 2)()
+    out = (C.c_ulonglong * 4)()
     for e in engines(ds):
         e.lib.check(e.lib.nsof_debug_r1_window(e.handle, 1))
         e.lib.check(e.lib.nsof_debug_bs_prefetch(e.handle, -1))
         e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
     timed(ds, fr, 2)
-    tot = [0, 0]
+    tot = [0, 0, 0, 0]
     for e in engines(ds):
         e.lib.check(e.lib.nsof_debug_r1_window_stats(e.handle, out, None))
-        tot[0] += out[0]; tot[1] += out[1]
-    print(f"{tag}: tiles via window {tot[0]} / L2 {tot[1]} = {tot[0] / max(1, sum(tot)):.4f}")
+        for q in range(4):
+            tot[q] += out[q]
+    print(f"{tag}: blur+solve tiles via window {tot[0]} / L2 {tot[1]} = {tot[0] / max(1, tot[0] + tot[1]):.4f}; first "
+          f"UpdateMatrices {tot[2]} / {tot[3]} = {tot[2] / max(1, tot[2] + tot[3]):.4f}")
     for name, _, _ in variants:
         print(f"    {name:34s} {min(res[name]):7.3f} ms per step (runs {['%.3f' % v for v in res[name]]})", flush=True)
     for s in ds.slots:

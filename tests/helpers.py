@@ -498,16 +498,18 @@ def _warp(seed, h, w, src_of):
 
 def r1_window_stats(eng):
     import ctypes as C
-    out = (C.c_ulonglong * 2)()
+    out = (C.c_ulonglong * 4)()
     eng.lib.check(eng.lib.nsof_debug_r1_window_stats(eng.handle, out, eng._stream()), "r1_window_stats")
-    return int(out[0]), int(out[1])
+    return int(out[0]), int(out[1]), int(out[2]), int(out[3])   # blur+solve (window, L2), first UpdateMatrices (window, L2)
 
 
 def check_r1_window(eng, hw=(300, 400)):
     """The tuned blur+solve kernel gathers R1 from a shared-memory window that follows the tile's flow, or from L2 when
     the flow varies too much inside a tile: both paths load the same values, so the flow must be BIT-IDENTICAL with the
     window switched off -- for a uniform small shift, a uniform 20 px shift (window far from the tile), a zoom and a
-    shear (tiles of both kinds).  -> {kind: (window tiles, L2 tiles)} of the window-on runs."""
+    shear (tiles of both kinds).  The first UpdateMatrices of a level takes its own window kernel (its flow is the upsampled
+    coarser flow) or, with the switch off, the round-1 kernel.  -> {(kind, big tiles): (blur+solve window tiles, L2 tiles,
+    first-UpdateMatrices window tiles, L2 tiles)} of the window-on runs."""
     p = PARAM_SETS["grasp"]
     r1_window_stats(eng)   # first call: counting on
     stats = {}
@@ -521,12 +523,13 @@ def check_r1_window(eng, hw=(300, 400)):
                 stats[kind, big] = r1_window_stats(eng)
                 eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 0))
                 off = eng.calcOpticalFlowFarneback(a, b, None, **p)
-                n_on, n_off = r1_window_stats(eng)
-                assert n_on == 0 and n_off == sum(stats[kind, big]), (kind, big, n_on, n_off, stats[kind, big])
+                n_on, n_off, u_on, u_off = r1_window_stats(eng)   # window off: the round-1 um_first kernel counts nothing
+                assert n_on == 0 and n_off == sum(stats[kind, big][:2]) and u_on == 0 and u_off == 0, (kind, big, n_on, n_off)
                 assert np.array_equal(on, off), (kind, big, np.abs(on - off).max())
                 assert np.isfinite(on).all()
             assert stats["shift3", big][0] > 0 and stats["shift20", big][0] > 0, stats
             assert stats["shear", big][1] > 0, stats
+            assert stats["shift3", big][2] > 0 and stats["shear", big][2] > 0, stats   # first UpdateMatrices: window taken
     finally:
         eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 1))
         eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, 0))
