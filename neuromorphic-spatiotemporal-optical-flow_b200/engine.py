@@ -51,6 +51,7 @@ class RoiConfig:
     EXTEND_HEIGHT_LOWER: int = 20
     FLAG: int = 2          # 1 separate regions, 2 merged region
     CONNECT: int = 4       # connectedComponents connectivity (only 4 is implemented, as the scripts use)
+    PADDING: int = 20      # task_results, FLAG 1 with MERGE_FLAG: margin of the box around all regions (optical_flow_seg.py:48)
     MAP_A: float = -3366.0  # u8 = uint8(clip(MAP_A / log10(I) + MAP_B, 0, 255))  (optical_flow_seg.py:426-435)
     MAP_B: float = -306.0
     farneback_params: dict = field(default_factory=lambda: dict(FARNEBACK_PARAMS))
@@ -62,19 +63,19 @@ class RoiConfig:
     @classmethod
     def autodriving(cls):  # optical_flow_yolo.py:68-80
         return cls(MEMSIZE=200, OFFSET=15, THRES=114, EXTEND_WIDTH_LEFT=60, EXTEND_WIDTH_RIGHT=60,
-                   EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60)
+                   EXTEND_HEIGHT_UPPER=60, EXTEND_HEIGHT_LOWER=60, PADDING=60)
 
     # The three datasets below have no checked-in script of their own; their constants are data/<ds>/Parameters.txt.
     @classmethod
     def uav(cls):  # data/uav/Parameters.txt
         return cls(MEMSIZE=40, THRES=114, FLAG=1, EXTEND_WIDTH_LEFT=30, EXTEND_WIDTH_RIGHT=30, EXTEND_HEIGHT_UPPER=30,
-                   EXTEND_HEIGHT_LOWER=30, farneback_params=dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3,
+                   EXTEND_HEIGHT_LOWER=30, PADDING=30, farneback_params=dict(pyr_scale=0.6, levels=3, winsize=3, iterations=3,
                                                                  poly_n=10, poly_sigma=1.05, flags=0))
 
     @classmethod
     def uavnew2(cls):  # data/uavnew2/Parameters.txt
         return cls(MEMSIZE=40, THRES=245, FLAG=1, EXTEND_WIDTH_LEFT=60, EXTEND_WIDTH_RIGHT=60, EXTEND_HEIGHT_UPPER=60,
-                   EXTEND_HEIGHT_LOWER=60)
+                   EXTEND_HEIGHT_LOWER=60, PADDING=60)
 
     @classmethod
     def tabletennis(cls):  # data/tabletennis/Parameters.txt

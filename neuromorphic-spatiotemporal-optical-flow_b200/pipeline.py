@@ -62,9 +62,13 @@ class SequencePipeline:
         self.segment = bool(segment)  # also run task_results / process_flow_region on every ROI flow (8(f) rank 1)
         self.C, self.F, self.H, self.W = int(clips), int(frames), int(H), int(W)
         self.cfg = cfg or RoiConfig()
-        if self.cfg.FLAG != 2:
-            raise NotImplementedError("the sequence pipelines batch the merged region (FLAG 2, what every script ships "
-                                      "with); FLAG 1 (process_separate_regions) is served by Engine.opticalFlow3D")
+        if self.cfg.FLAG not in (1, 2):
+            raise ValueError("RoiConfig.FLAG must be 1 (separate regions) or 2 (merged region)")
+        if self.cfg.FLAG == 1 and packed:
+            raise NotImplementedError("FLAG 1 (process_separate_regions: overlapping regions pasted in label order) is "
+                                      "served by the device-resident pipelines (SequencePipeline / DeviceStream with "
+                                      "flow frames) and by Engine.opticalFlow3D, not by the packed host path")
+        self.sep = self.cfg.FLAG == 1 and not full_frame   # several regions per pair
         if roi_state not in ("scripts", "notebook") or stage1 not in ("simulate", "given"):
             raise ValueError("roi_state must be 'scripts' or 'notebook', stage1 'simulate' or 'given'")
         self.roi_state, self.stage1_mode = roi_state, stage1
@@ -105,6 +109,8 @@ class SequencePipeline:
         # addressing): a D2H copy would queue on the copy engine behind whole flow crops of earlier chunks / steps
         self.rects_pinned = torch.zeros((self.n_pairs, _lib.NSOF_MAX_RECTS, 4), dtype=i32).pin_memory()
         self.rects_host = self.rects_pinned[:, 0, :]          # FLAG 2: one merged rectangle per pair
+        # FLAG 1: up to MAX_REGIONS regions per pair get a descriptor each (the ROI kernel stores up to NSOF_MAX_RECTS)
+        self.max_regions = 16 if self.sep else 1
         self.n_rects_host = torch.zeros((self.n_pairs,), dtype=i32).pin_memory()
         # output: full flow frames (zero outside each ROI, the reference's paste semantics) or, for the host path,
         # the ROI crops packed back to back (outside its rectangle a pair's flow is zero by definition)
@@ -128,18 +134,21 @@ class SequencePipeline:
                 self.packed_mask = torch.empty((self.packed.numel() // 2,), dtype=torch.uint8, device=self.dev)
             else:
                 self.motion = torch.zeros((self.F - 1, self.C, self.H, self.W), dtype=torch.uint8, device=self.dev)
-            self.seg_descs = (SegDesc * self.n_pairs)()
+            self.seg_descs = (SegDesc * self.n_pairs)()   # FLAG 1: one per pair too (task_results' merged padding box)
             self.seg_params = SegParams(float(SEG_TH), 2, 10, 10, 5)  # optical_flow_seg.py:49, 349-351
         self.sp = _synapse_params(PARAMS)
         self.fsp = FrameSimParams(float(sim["th1"]), float(sim["th2"]), float(sim["dt"]), int(sim["nSubSteps"]),
                                   float(sim["vds"]))
         c = self.cfg
         self.rp = RoiParams(self.Hc, self.Wc, self.H, self.W, M, M, c.EXTEND_WIDTH_LEFT, c.EXTEND_WIDTH_RIGHT,
-                            c.EXTEND_HEIGHT_UPPER, c.EXTEND_HEIGHT_LOWER, 2, c.THRES, c.MAP_A, c.MAP_B)
+                            c.EXTEND_HEIGHT_UPPER, c.EXTEND_HEIGHT_LOWER, 1 if self.sep else 2, c.THRES, c.MAP_A, c.MAP_B)
         self.fb = _fb_params(**c.farneback_params)
-        self.descs = (CropDesc * self.n_pairs)()
+        self.descs = (CropDesc * (self.n_pairs * self.max_regions))()
         self.n_items = 0          # descriptors of the current step
         self.n_dirty = 0          # descriptors whose flow rectangles are non-zero in self.flow (previous step)
+        self.n_seg = self.n_seg_dirty = 0   # the same for the mask descriptors (FLAG 1: one per pair, not per region)
+        self._groups = []         # FLAG 1: descriptor ranges of the chunk just built, one per region rank (see build_descs)
+        self._seg_range = (0, 0)
         self.last_rects = None
         self.last_crop_pixels = 0
         # workspace hint for the largest Farneback batch of a step: ROI crops of about a fifth of the frame plus, in the
@@ -198,6 +207,8 @@ class SequencePipeline:
         obase = self.packed.data_ptr() if self.packed_mode else self.flow.data_ptr()
         p0, p1 = pairs if pairs is not None else (0, self.F - 1)
         n, px = n0, px0
+        if self.sep:
+            return self._build_descs_separate(frames, rects, n_rects, p0, p1, n0), px0
         for i in range(p0 * Cn, p1 * Cn):
             self.offsets[i] = -1
             if self.full_frame:
@@ -235,6 +246,66 @@ class SequencePipeline:
             px += (y1 - y0) * (x1 - x0)
         return n, px
 
+    def _build_descs_separate(self, frames, rects_all, n_rects, p0, p1, n0):
+        """FLAG 1 (process_separate_regions, optical_flow_seg.py:123-166): one Farneback item per connected region, each
+        pasted into the pair's flow frame, LATER regions over earlier ones where their rectangles overlap (:159).  The
+        descriptors of the chunk are ordered by region rank -- all first regions, then all second regions, ... -- and
+        `stage2` runs one batch per rank on the same stream, so the paste order is the stream order.  Segmentation
+        (task_results with EST_FLAG 1, MERGE_FLAG True, :265-283): ONE box per pair around all its regions plus PADDING,
+        read from the pasted frame.  rects_all: (n_pairs, NSOF_MAX_RECTS, 4) as the ROI kernel stores them."""
+        H, W, Cn = self.H, self.W, self.C
+        fbase, obase = frames.data_ptr(), self.flow.data_ptr()
+        n, self._groups = n0, []
+        m0 = m = self.n_seg
+        live = []
+        for i in range(p0 * Cn, p1 * Cn):
+            self.offsets[i] = -1
+            k = int(n_rects[i])
+            if k > self.max_regions:
+                raise MemoryError(f"pair {i}: {k} regions, the pipeline holds {self.max_regions} per pair")
+            if k:
+                live.append((i, k))
+        rank = 0
+        while live:
+            g0 = n
+            for i, k in live:
+                x0, y0, x1, y1 = (int(v) for v in rects_all[i, rank])
+                if x1 <= x0 or y1 <= y0:  # prev_region.size == 0 guard of optical_flow_seg.py:155
+                    continue
+                t, c = divmod(i, Cn)
+                off = y0 * W + x0
+                d = self.descs[n]
+                d.prev = fbase + ((t * Cn + c) * H * W + off)
+                d.next = fbase + (((t + 1) * Cn + c) * H * W + off)
+                d.h, d.w = y1 - y0, x1 - x0
+                d.prev_pitch = d.next_pitch = W
+                d.flow = obase + ((t * Cn + c) * H * W + off) * 8
+                d.flow_pitch = W * 8
+                n += 1
+            if n > g0:
+                self._groups.append((g0, n))
+            rank += 1
+            live = [(i, k) for i, k in live if k > rank]
+        if self.segment:
+            pad = int(self.cfg.PADDING)
+            for i in range(p0 * Cn, p1 * Cn):
+                k = int(n_rects[i])
+                if not k:
+                    continue
+                r = rects_all[i, :k]
+                x0, y0 = max(0, int(r[:, 0].min()) - pad), max(0, int(r[:, 1].min()) - pad)
+                x1, y1 = min(W, int(r[:, 2].max()) + pad), min(H, int(r[:, 3].max()) + pad)
+                if x1 <= x0 or y1 <= y0:
+                    continue
+                t, c = divmod(i, Cn)
+                off = (t * Cn + c) * H * W + y0 * W + x0
+                g = self.seg_descs[m]
+                g.flow, g.flow_pitch, g.h, g.w = obase + off * 8, W * 8, y1 - y0, x1 - x0
+                g.mask, g.mask_pitch = self.motion.data_ptr() + off, W
+                m += 1
+        self._seg_range, self.n_seg = (m0, m), m
+        return n
+
     def _descs_at(self, n0):
         return C.cast(C.byref(self.descs, n0 * _DESC_SIZE), C.POINTER(CropDesc))
 
@@ -244,11 +315,21 @@ class SequencePipeline:
         if self.packed_mode or not self.n_dirty:
             return
         self.lib.check(self.lib.nsof_flow_clear(self.h, self.descs, self.n_dirty, self._stream()), "flow_clear")
-        if self.segment:  # the same for the mask frames (a whole-frame zero_() of 249 MB cost 0.5 ms per step)
-            self.lib.check(self.lib.nsof_mask_clear(self.h, self.seg_descs, self.n_dirty, self._stream()), "mask_clear")
-        self.n_dirty = 0
+        if self.segment and self.n_seg_dirty:  # the same for the mask frames (a whole-frame zero_() of 249 MB cost 0.5 ms per step)
+            self.lib.check(self.lib.nsof_mask_clear(self.h, self.seg_descs, self.n_seg_dirty, self._stream()), "mask_clear")
+        self.n_dirty = self.n_seg_dirty = 0
 
     def stage2(self, n0, n1, eng=None):
+        if self.sep:   # FLAG 1: one batch per region rank, in stream order; then one mask box per pair
+            for a, b in self._groups:
+                self.lib.check(self.lib.nsof_farneback_batch((eng or self.eng).handle, self._descs_at(a), b - a,
+                                                             C.byref(self.fb), self._stream()), "farneback_batch")
+            m0, m1 = self._seg_range
+            if self.segment and m1 > m0:
+                segs = C.cast(C.byref(self.seg_descs, m0 * C.sizeof(SegDesc)), C.POINTER(SegDesc))
+                self.lib.check(self.lib.nsof_flow_segment_batch((eng or self.eng).handle, segs, m1 - m0,
+                                                                C.byref(self.seg_params), self._stream()), "flow_segment")
+            return
         if n1 > n0:
             self.lib.check(self.lib.nsof_farneback_batch((eng or self.eng).handle, self._descs_at(n0), n1 - n0,
                                                          C.byref(self.fb), self._stream()), "farneback_batch")
@@ -300,21 +381,26 @@ class SequencePipeline:
         else:
             cur = t.cuda.current_stream(self.dev)
             n = px = 0
+            self.n_seg = 0
+            rects_np = self.rects_pinned.numpy() if self.sep else self.rects_host.numpy()
             for j, pr in enumerate(self.chunks):
                 if self.overlap:
                     self.ev_chunk[j].synchronize()  # the chunk's rectangles are on the host
                 else:
                     self.stage1_chunk(frames, j, self.eng)
                     cur.synchronize()
-                n1, px = self.build_descs(frames, self.rects_host.numpy(), self.n_rects_host.numpy(), pr, n, px)
+                n1, px = self.build_descs(frames, rects_np, self.n_rects_host.numpy(), pr, n, px)
                 self.stage2_chunk(j, n, n1, cur)
                 n = n1
             for j in range(len(self.chunks)):  # the caller's stream ends the step after every batch
                 if j % (1 + len(self.s2_extra)):
                     cur.wait_event(self.ev_s2[j])
-            self.last_rects = (self.rects_host.numpy().copy(), self.n_rects_host.numpy().copy())
+            # FLAG 2: (n_pairs, 4); FLAG 1: (n_pairs, max_regions, 4), the first n_rects[i] rows of pair i valid
+            self.last_rects = ((rects_np[:, :self.max_regions].copy() if self.sep else rects_np.copy()),
+                               self.n_rects_host.numpy().copy())
         self.n_items = n
         self.n_dirty = 0 if self.packed_mode else n
+        self.n_seg_dirty = 0 if (self.packed_mode or not self.segment) else (self.n_seg if self.sep else n)
         self.last_crop_pixels = px
         self.packed_floats = px * 2
         return n

@@ -374,3 +374,17 @@ def test_emu_r1_window_bit_identical(emu_engine):
     """Blur+solve with the R1 window in shared memory (default) against the L2 gathers, both tile shapes."""
     stats = helpers.check_r1_window(emu_engine, hw=(200, 280))
     assert stats["shift3", 1][1] == 0     # a uniform 3 px shift never leaves the window
+
+
+def test_pipeline_flag_checks(emu_engine, nsof):
+    """RoiConfig.FLAG in the sequence pipelines: 1 and 2 are served (1 = one item per connected region, device-resident
+    pipelines only); the packed host path refuses FLAG 1 instead of silently merging, anything else is an error."""
+    import importlib
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    cfg = nsof.RoiConfig.uavnew2()
+    assert cfg.FLAG == 1 and cfg.PADDING == 60
+    with pytest.raises(NotImplementedError):
+        pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg, packed=True)
+    cfg.FLAG = 3
+    with pytest.raises(ValueError):
+        pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg)

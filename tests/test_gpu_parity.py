@@ -235,6 +235,55 @@ def test_realdata_sequence_from_mat(gpu_engine, nsof, golden, roi_state):
             assert helpers.pixel_accuracy(motion[k, 0] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
 
 
+def test_sequence_pipeline_separate_regions(gpu_engine, nsof, golden):
+    """FLAG 1 (process_separate_regions, the configuration data/uavnew2/Parameters.txt names) through the device-resident
+    SequencePipeline: the 13 kept uavnew2 pairs as 13 two-frame clips, array states given (slice OFFSET + i, the scripts'
+    gate), up to 13 overlapping regions per pair pasted in label order (one Farneback batch per region rank), then
+    task_results' merged padding box.  Region lists equal the reference run; the pasted flow frames equal, BIT FOR BIT,
+    Engine.opticalFlow3D's host-side paste of the same regions; motion masks and accuracy equal the reference's.  Two
+    steps: the second one runs on frames whose previous rectangles had to be cleared."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    rd = helpers.RealDataSmall("uavnew2")
+    cfg = nsof.RoiConfig.uavnew2()
+    keep, M = rd.keep, cfg.MEMSIZE
+    Cn = len(keep)
+    frames = np.stack([np.stack([rd.g[f"gray__{i}"] for i in keep]), np.stack([rd.g[f"gray__{i + 1}"] for i in keep])])
+    cur = golden.roi["uavnew2__currents"]
+    pipe = pm.SequencePipeline(gpu_engine, Cn, 2, rd.H, rd.W, cfg, stage1="given", segment=True, roi_state="scripts",
+                               overlap=False, chunks=[(0, 1)])
+    state = torch.from_numpy(np.ascontiguousarray(np.stack([cur[i] for i in keep])))
+    pipe.currents[0].copy_(state)
+    pipe.currents[1].copy_(state)
+    d_frames = torch.from_numpy(np.ascontiguousarray(frames)).cuda()
+    with pytest.raises(NotImplementedError):
+        pm.SequencePipeline(gpu_engine, Cn, 2, rd.H, rd.W, cfg, packed=True)
+    for step in range(2):
+        if step == 1:   # other regions in the second step: pair c gets the state of pair c + 1
+            state = torch.roll(state, -1, 0)
+            pipe.currents[0].copy_(state)
+        pipe.step(d_frames)
+        torch.cuda.synchronize()
+        rects, n_rects = pipe.last_rects
+        flow, motion = pipe.flow.cpu().numpy(), pipe.motion.cpu().numpy()
+        for c, i in enumerate(keep):
+            j = keep[(c + step) % Cn]                      # whose array state gates clip c in this step
+            a, b = frames[0, c], frames[1, c]
+            memimg = rd.g[f"memimg__{j}"]
+            want, _, _, _, num_labels, info = gpu_engine.opticalFlow3D(memimg, memimg, a, b, M, M, cfg)
+            info = [tuple(int(v) for v in r) for r in info]
+            assert int(n_rects[c]) == len(info) and [tuple(int(v) for v in r) for r in rects[c, :len(info)]] == info, (step, c)
+            assert info == rd.rects(j)
+            assert np.array_equal(flow[0, c], want.astype(np.float32)), (step, c, np.abs(flow[0, c] - want).max())
+            m = gpu_engine.task_results(a, b, -want, num_labels, info, EST_FLAG=1, MERGE_FLAG=True, padding=cfg.PADDING)
+            assert np.array_equal(motion[0, c], m), (step, c)
+            if step == 0:
+                assert np.array_equal(motion[0, c] > 0, rd.unpack(f"motion__{i}")), c
+                assert helpers.pixel_accuracy(motion[0, c] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
+
+
 def test_full_size_properties(gpu_engine):
     """Size-independent properties at 1080p: a constant frame pair -> exactly zero flow (identical TEXTURED frames do
     not: OpenCV's UpdateMatrices takes r2 = R0/2 on the last row/column, cv2 itself returns up to 0.09 px there);
