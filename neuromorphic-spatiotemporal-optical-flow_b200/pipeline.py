@@ -64,10 +64,10 @@ class SequencePipeline:
         self.cfg = cfg or RoiConfig()
         if self.cfg.FLAG not in (1, 2):
             raise ValueError("RoiConfig.FLAG must be 1 (separate regions) or 2 (merged region)")
-        if self.cfg.FLAG == 1 and packed:
-            raise NotImplementedError("FLAG 1 (process_separate_regions: overlapping regions pasted in label order) is "
-                                      "served by the device-resident pipelines (SequencePipeline / DeviceStream with "
-                                      "flow frames) and by Engine.opticalFlow3D, not by the packed host path")
+        if self.cfg.FLAG == 1 and packed and segment:
+            raise NotImplementedError("FLAG 1 with packed output hands out one flow crop per region; the motion mask of "
+                                      "task_results needs the pasted frame: use the device-resident pipelines "
+                                      "(SequencePipeline / DeviceStream with flow frames) or segment=False")
         self.sep = self.cfg.FLAG == 1 and not full_frame   # several regions per pair
         if roi_state not in ("scripts", "notebook") or stage1 not in ("simulate", "given"):
             raise ValueError("roi_state must be 'scripts' or 'notebook', stage1 'simulate' or 'given'")
@@ -125,6 +125,7 @@ class SequencePipeline:
         else:
             self.flow = torch.zeros((self.F - 1, self.C, self.H, self.W, 2), dtype=torch.float32, device=self.dev)
         self.offsets = [-1] * self.n_pairs
+        self.region_offsets = [[] for _ in range(self.n_pairs)]   # FLAG 1, packed: one offset per region, in label order
         self.packed_floats = 0
         # motion_binary (optical_flow_seg.py:262): uint8 frames, zero outside the ROI; packed mode: the crops' masks
         # back to back, pair i's mask at packed_mask[offsets[i] // 2 :][: h * w]
@@ -207,6 +208,8 @@ class SequencePipeline:
         obase = self.packed.data_ptr() if self.packed_mode else self.flow.data_ptr()
         p0, p1 = pairs if pairs is not None else (0, self.F - 1)
         n, px = n0, px0
+        if self.sep and self.packed_mode:
+            return self._build_descs_separate_packed(frames, rects, n_rects, p0, p1, n0, px0)
         if self.sep:
             return self._build_descs_separate(frames, rects, n_rects, p0, p1, n0), px0
         for i in range(p0 * Cn, p1 * Cn):
@@ -305,6 +308,40 @@ class SequencePipeline:
                 m += 1
         self._seg_range, self.n_seg = (m0, m), m
         return n
+
+    def _build_descs_separate_packed(self, frames, rects_all, n_rects, p0, p1, n0, px0):
+        """FLAG 1 with packed output: every region's flow crop is stored on its own (region_offsets[i][j], label order), so
+        nothing overlaps in memory and the chunk is ONE batch; the consumer pastes in label order if it wants the frame."""
+        H, W, Cn = self.H, self.W, self.C
+        fbase, obase = frames.data_ptr(), self.packed.data_ptr()
+        n, px = n0, px0
+        for i in range(p0 * Cn, p1 * Cn):
+            self.offsets[i], self.region_offsets[i] = -1, []
+            k = int(n_rects[i])
+            if k > self.max_regions:
+                raise MemoryError(f"pair {i}: {k} regions, the pipeline holds {self.max_regions} per pair")
+            t, c = divmod(i, Cn)
+            for j in range(k):
+                x0, y0, x1, y1 = (int(v) for v in rects_all[i, j])
+                if x1 <= x0 or y1 <= y0:
+                    self.region_offsets[i].append(-1)
+                    continue
+                if (px + (y1 - y0) * (x1 - x0)) * 2 > self.packed.numel():
+                    raise MemoryError("packed flow buffer too small for this step's regions")
+                off = y0 * W + x0
+                d = self.descs[n]
+                d.prev = fbase + ((t * Cn + c) * H * W + off)
+                d.next = fbase + (((t + 1) * Cn + c) * H * W + off)
+                d.h, d.w = y1 - y0, x1 - x0
+                d.prev_pitch = d.next_pitch = W
+                d.flow, d.flow_pitch = obase + px * 8, (x1 - x0) * 8
+                self.region_offsets[i].append(px * 2)
+                if self.offsets[i] < 0:
+                    self.offsets[i] = px * 2
+                n += 1
+                px += (y1 - y0) * (x1 - x0)
+        self._groups, self._seg_range = ([(n0, n)] if n > n0 else []), (0, 0)
+        return n, px
 
     def _descs_at(self, n0):
         return C.cast(C.byref(self.descs, n0 * _DESC_SIZE), C.POINTER(CropDesc))
@@ -475,7 +512,7 @@ class HostPipeline:
 
     def __init__(self, device: int, clips: int, frames: int, H: int, W: int, cfg: RoiConfig | None = None,
                  slots: int | None = None, full_frame: bool = False, lib=None, chunks=None, copy_streams=None,
-                 segment: bool = False, roi_state: str = "scripts"):
+                 segment: bool = False, roi_state: str = "scripts", stage1: str = "simulate"):
         import torch
         self.torch = torch
         self.dev = torch.device(f"cuda:{device}")
@@ -490,7 +527,7 @@ class HostPipeline:
             if chunks is None:
                 chunks = chunk_schedule(self.F - 1, first=1, grow=2, cap=4)
             self.pipe = SequencePipeline(self.eng, clips, frames, H, W, cfg, full_frame=full_frame, packed=True,
-                                         chunks=chunks, overlap=True, segment=segment, roi_state=roi_state)
+                                         chunks=chunks, overlap=True, segment=segment, roi_state=roi_state, stage1=stage1)
             if full_frame:  # no stage 1: the side stream/handle of the pipe is unused
                 self.pipe.side = None
             self.frames = torch.empty((self.F, self.C, H, W), dtype=torch.uint8, device=self.dev)
@@ -528,7 +565,8 @@ class HostPipeline:
         packed float32 host tensor); pair t's flow crop is packed[offsets[t] : offsets[t] + 2 h w].view(h, w, 2).
         With segment=True a fifth entry, the packed uint8 motion masks: pair t's is
         masks[offsets[t] // 2 : offsets[t] // 2 + h w].view(h, w).  The packed tensors are shared by all clips of
-        the step.  Synchronous: results are on the host on return."""
+        the step.  FLAG 1: rects is (F-1, max_regions, 4) and offsets[t] a list with one offset per region of pair t (label
+        order; segment=True is refused).  Synchronous: results are on the host on return."""
         self.enqueue_input(clips_host)
         self.enqueue_flow()
         return self.collect()
@@ -575,7 +613,7 @@ class HostPipeline:
                     self.main.wait_event(self.ev_in[j])
                 else:
                     p.ev_chunk[j].synchronize()
-                    rects, n_rects = p.rects_host.numpy(), p.n_rects_host.numpy()
+                    rects, n_rects = (p.rects_pinned if p.sep else p.rects_host).numpy(), p.n_rects_host.numpy()
                 n1, px1 = p.build_descs(self.frames, rects, n_rects, pr, n, px)
                 with t.cuda.stream(self.main):
                     p.stage2_chunk(j, n, n1, self.main)
@@ -608,6 +646,12 @@ class HostPipeline:
             for c in range(Cn):
                 out.append((None, None, [p.offsets[tt * Cn + c] for tt in range(F - 1)], self.flow_host)
                            + ((self.mask_host,) if p.segment else ()))
+        elif p.sep:  # FLAG 1: per pair up to max_regions rectangles and as many offsets (label order)
+            R = p.rects_pinned.numpy()[:, :p.max_regions].reshape(F - 1, Cn, p.max_regions, 4)
+            N = p.n_rects_host.numpy().reshape(F - 1, Cn)
+            for c in range(Cn):
+                out.append((R[:, c].copy(), N[:, c].copy(), [list(p.region_offsets[tt * Cn + c]) for tt in range(F - 1)],
+                            self.flow_host))
         else:
             R, N = p.rects_host.numpy().reshape(F - 1, Cn, 4), p.n_rects_host.numpy().reshape(F - 1, Cn)
             for c in range(Cn):

@@ -377,14 +377,14 @@ def test_emu_r1_window_bit_identical(emu_engine):
 
 
 def test_pipeline_flag_checks(emu_engine, nsof):
-    """RoiConfig.FLAG in the sequence pipelines: 1 and 2 are served (1 = one item per connected region, device-resident
-    pipelines only); the packed host path refuses FLAG 1 instead of silently merging, anything else is an error."""
+    """RoiConfig.FLAG in the sequence pipelines: 1 and 2 are served (1 = one item per connected region); the packed host
+    path hands out one crop per region and refuses masks for FLAG 1 instead of silently merging; anything else is an error."""
     import importlib
     pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
     cfg = nsof.RoiConfig.uavnew2()
     assert cfg.FLAG == 1 and cfg.PADDING == 60
-    with pytest.raises(NotImplementedError):
-        pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg, packed=True)
+    with pytest.raises(NotImplementedError):   # a mask needs the pasted frame
+        pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg, packed=True, segment=True)
     cfg.FLAG = 3
     with pytest.raises(ValueError):
         pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg)

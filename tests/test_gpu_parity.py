@@ -259,7 +259,7 @@ def test_sequence_pipeline_separate_regions(gpu_engine, nsof, golden):
     pipe.currents[1].copy_(state)
     d_frames = torch.from_numpy(np.ascontiguousarray(frames)).cuda()
     with pytest.raises(NotImplementedError):
-        pm.SequencePipeline(gpu_engine, Cn, 2, rd.H, rd.W, cfg, packed=True)
+        pm.SequencePipeline(gpu_engine, Cn, 2, rd.H, rd.W, cfg, packed=True, segment=True)
     for step in range(2):
         if step == 1:   # other regions in the second step: pair c gets the state of pair c + 1
             state = torch.roll(state, -1, 0)
@@ -282,6 +282,43 @@ def test_sequence_pipeline_separate_regions(gpu_engine, nsof, golden):
             if step == 0:
                 assert np.array_equal(motion[0, c] > 0, rd.unpack(f"motion__{i}")), c
                 assert helpers.pixel_accuracy(motion[0, c] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
+
+
+def test_host_pipeline_separate_regions(gpu_engine, nsof, golden):
+    """FLAG 1 through the host-buffer path (HostPipeline, packed output): pinned clips in, per pair the region list and one
+    packed flow crop PER REGION out (label order).  Regions equal the reference run; every crop equals, bit for bit, a
+    single Farneback call on that region's crop pair."""
+    import importlib
+
+    import torch
+    pm = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.pipeline")
+    rd = helpers.RealDataSmall("uavnew2")
+    cfg = nsof.RoiConfig.uavnew2()
+    keep = rd.keep[:6]
+    Cn = len(keep)
+    clips = [torch.from_numpy(np.stack([rd.g[f"gray__{i}"], rd.g[f"gray__{i + 1}"]])).pin_memory() for i in keep]
+    hp = pm.HostPipeline(0, Cn, 2, rd.H, rd.W, cfg, stage1="given", chunks=[(0, 1)])
+    cur = golden.roi["uavnew2__currents"]
+    state = torch.from_numpy(np.ascontiguousarray(np.stack([cur[i] for i in keep])))
+    hp.pipe.currents[0].copy_(state)
+    hp.pipe.currents[1].copy_(state)
+    torch.cuda.synchronize()
+    res = hp.run(clips)
+    n_regions = 0
+    for c, i in enumerate(keep):
+        rects, n_rects, offsets, packed = res[c]
+        want = rd.rects(i)
+        assert int(n_rects[0]) == len(want) and [tuple(int(v) for v in r) for r in rects[0, :len(want)]] == want, c
+        assert len(offsets[0]) == len(want)
+        a, b = clips[c][0].numpy(), clips[c][1].numpy()
+        for (x0, y0, x1, y1), off in zip(want, offsets[0]):
+            h, w = y1 - y0, x1 - x0
+            got = packed[off:off + 2 * h * w].view(h, w, 2).numpy()
+            ref = gpu_engine.calcOpticalFlowFarneback(np.ascontiguousarray(a[y0:y1, x0:x1]), np.ascontiguousarray(b[y0:y1, x0:x1]),
+                                                      None, **cfg.farneback_params)
+            assert np.array_equal(got, ref), (c, (x0, y0, x1, y1))
+            n_regions += 1
+    assert n_regions > Cn   # several regions per pair somewhere
 
 
 def test_full_size_properties(gpu_engine):
