@@ -536,8 +536,14 @@ struct alignas(16) FbLin {
 #define FB_UMW_RS (FB_UM_TW + 8)
 #define FB_UMW_RH (FB_UM_TH + 3)
 #define FB_UMW_SMEM (32 + 5 * FB_UMW_RH * FB_UMW_RS * sizeof(float) + (FB_UM_TW + FB_UM_TH) * 16)
+// five CTAs per SM (48 registers, an 8-byte spill): the kernel waits on DRAM twice per tile (coarse flow, then window + R0),
+// a fifth resident tile hides more of it than the spill costs -- 8.49 -> 8.33 ms per gated step, 12.55 -> 12.40 ms per
+// full-frame step against four CTAs; six (40 registers, 72-byte spill): 8.45 / 12.65 ms
+#ifndef FB_UMW_MINB
+#define FB_UMW_MINB 5
+#endif
 template <int INIT>
-NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UM_MINB) k_fb_um_first_w(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float flow_mul,
+NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_UMW_MINB) k_fb_um_first_w(const FbJob *NSOF_RESTRICT jobs, const uint2 *NSOF_RESTRICT tl, float flow_mul,
                                                                 int flags, unsigned *stats)
 {
     constexpr int TW = FB_UM_TW, TH = FB_UM_TH, NT = 256, RS = FB_UMW_RS, RH = FB_UMW_RH, SP = RH * RS;
