@@ -426,7 +426,9 @@ NSOF_DEV void fb_um_pixel2(const float *NSOF_RESTRICT R1, size_t plane, int pitc
 // level's flow upsampled on the fly (S2-f: resize INTER_LINEAR, times f32(1/pyr_scale)); the
 // upsampled field itself is never written (UpdateFlow_Blur overwrites flow entirely).
 #define FB_UM_TW 64   // (128 x 8 before the window kernel: its window needs rows, not width)
+#ifndef FB_UM_TH
 #define FB_UM_TH 16
+#endif
 
 // tiled runs: flag a gather that reaches R1 rows this rank neither owns nor received
 NSOF_DEV void fb_um_guard(const FbJob &J, int y, float dy)

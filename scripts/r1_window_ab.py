@@ -1,7 +1,7 @@
 """A/B of the blur+solve kernel's R1 window (shared-memory gathers, default) against the L2 gathers, and of the bulk L2
 prefetches of its phase 1, on the bench workload: the device-resident step (8 clips x 32 frames of 1080p, scripts' gate) and the full-frame step (ROI = 100 %),
 window on / off alternating in one process, plus the share of tiles that took the window.
-usage: python scripts/r1_window_ab.py [steps]"""
+usage: python scripts/r1_window_ab.py [steps] [default]"""
 import ctypes as C
 import importlib, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -47,6 +47,8 @@ for tag, full, clips in (("gated step (248 pairs)", False, Cn), ("full frame (62
     variants = [("windows in both kernels (default)", 1, -1), ("window in blur+solve only", 2, -1),
                 ("blur+solve only, R0 + R1 prefetch", 2, 0), ("blur+solve only, R1 prefetch", 2, 1),
                 ("blur+solve only, R0 prefetch", 2, 2), ("L2 gathers, prefetch (round 1)", 0, 0), ("L2 gathers, no prefetch", 0, 3)]
+    if len(sys.argv) > 2 and sys.argv[2] == "default":   # only the default configuration (A/B of build variants)
+        variants = variants[:1]
     res = {v[0]: [] for v in variants}
     for rep in range(3):
         for name, on, mask in variants:
