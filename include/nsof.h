@@ -254,6 +254,9 @@ NSOF_API int nsof_debug_lanczos_f64(nsof_handle *h, int enable);
 NSOF_API int nsof_debug_fork(nsof_handle *h, int enable);
 /* enable = 1 keeps the large blur+solve tile on every level (default: latency-bound levels take the small one). */
 NSOF_API int nsof_debug_big_tiles(nsof_handle *h, int enable);
+/* enable = 1: winsize 3 .. 5 (box window) run the generic blur+solve kernel instead of the tuned kernel's small-radius
+ * instantiations (default). */
+NSOF_API int nsof_debug_generic_blur(nsof_handle *h, int enable);
 /* enable = 2: window in the blur+solve kernel only.  enable = 0: the tuned blur+solve kernel gathers R1 from L2 in every tile (default: from a shared-memory window placed
  * on the tile's flow range whenever the range fits; same values either way), and the first UpdateMatrices of a level runs
  * the round-1 kernel.  nsof_debug_r1_window_stats: out2[0..3] (FOUR counters) = {blur+solve tiles through the window,

@@ -150,6 +150,7 @@ _SIGNATURES = {
     "nsof_debug_share_frames": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_lanczos_f64": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_big_tiles": (C.c_int, [C.c_void_p, C.c_int]),
+    "nsof_debug_generic_blur": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_r1_window": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_bs_prefetch": (C.c_int, [C.c_void_p, C.c_int]),
     "nsof_debug_r1_window_stats": (C.c_int, [C.c_void_p, _P(C.c_ulonglong), C.c_void_p]),

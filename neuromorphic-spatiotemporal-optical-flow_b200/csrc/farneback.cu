@@ -121,6 +121,7 @@ extern "C" int nsof_create(int device, nsof_handle **out)
         h->dbg_no_r1_window = e[0] == '0';
         h->dbg_um_round1 = e[0] == '0' || e[0] == '2';
     }
+    if (const char *e = getenv("NSOF_GENERIC_BLUR")) h->dbg_generic_blur = e[0] == '1';   // A/B: winsize 3 .. 5 on the generic kernel
     if (const char *e = getenv("NSOF_BS_NO_PREFETCH")) h->dbg_bs_no_prefetch = atoi(e) < 0 ? -1 : (atoi(e) & 3);
     if (const char *e = getenv("NSOF_LANCZOS_F64")) h->dbg_lz_f64 = e[0] == '1';     // A/B: FP64 Lanczos kernels
     *out = h;
@@ -423,6 +424,8 @@ static int configure_smem(nsof_handle *h)
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_blur_solve_gauss, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M7S, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BS7S_SMEM));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BSM_SMEM(1)));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BSM_SMEM(2)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(1)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
@@ -504,6 +507,7 @@ struct FbBatchCtx {
     int BTW = 0, BTH = 0;
     size_t bs_smem = 0, pe_smem = 0;
     bool bs_m7 = false;
+    int bs_msmall = 0;   // 1 / 2: winsize 3 / 4 .. 5 with the box window on the tuned kernel's small-radius instantiations
     PolyConst pc;
     float flow_mul = 0.f, bscale = 0.f;
     FbGaussWin gwin;  // S2-e': weights of the Gaussian window (flags & NSOF_FB_GAUSSIAN)
@@ -643,7 +647,9 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     X.bs_smem = 0;
     // winsize 14/15 with the box window: the tuned kernel (every BASELINE.json config)
     X.bs_m7 = (m == 7) && !(params->flags & NSOF_FB_GAUSSIAN);
+    X.bs_msmall = ((m == 1 || m == 2) && !(params->flags & NSOF_FB_GAUSSIAN) && !h->dbg_generic_blur) ? m : 0;
     if (X.bs_m7) { X.BTW = FB_BS7_TW; X.BTH = FB_BS7_TH; X.bs_smem = FB_BS7_SMEM; }
+    else if (X.bs_msmall) { X.BTW = FB_BS7_TW; X.BTH = FB_BS7_TH; X.bs_smem = FB_BSM_SMEM(m); }
     else if (params->iterations > 0 && !pick_blur_tile(m, &X.BTW, &X.BTH, &X.bs_smem))
         NSOF_FAIL(NSOF_ERR_UNSUPPORTED, "farneback: winsize %d needs more than 227 KB of shared memory", params->winsize);
     const int pn = params->poly_n;
@@ -904,6 +910,12 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
                      FB_BS7S_NT, FB_BS7S_SMEM, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
     else if (X.bs_m7)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, n_bs, 1, 1,
+                     FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
+    else if (X.bs_msmall == 1)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M1, n_bs, 1, 1,
+                     FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
+    else if (X.bs_msmall == 2)
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M2, n_bs, 1, 1,
                      FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
     else if (X.gwin.on)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, k_fb_blur_solve_gauss, n_bs, 1, 1,
@@ -1621,6 +1633,15 @@ extern "C" int nsof_debug_big_tiles(nsof_handle *h, int enable)
 {
     if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
     h->dbg_big_tiles = enable != 0;
+    return NSOF_OK;
+}
+
+// 1: winsize 3 .. 5 take the generic blur+solve kernel (k_fb_blur_solve_g) instead of the tuned kernel's small-radius
+// instantiations (tests: the two must agree within the cv2 tolerance; A/B)
+extern "C" int nsof_debug_generic_blur(nsof_handle *h, int enable)
+{
+    if (!h) NSOF_FAIL(NSOF_ERR_BAD_ARG, "NULL handle");
+    h->dbg_generic_blur = enable != 0;
     return NSOF_OK;
 }
 

@@ -964,8 +964,12 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     constexpr int ML = (M + 3) & ~3, PW = TW + 2 * ML, LH = TH + 2 * M, SP = LH * PW;
     constexpr int NV = (2 * M + 4 + (ML - M) + 3) / 4;  // float4s covering the window columns of 4 outputs
     constexpr int RPP = (2 * M * PW) / (2 * TW);        // flow rows (TW float2) that fit the dead rows of one plane
-    static_assert(5 * RPP >= TH, "the flow tile must fit the dead halo rows");
-    static_assert((TH * PW) % 4 == 0 && (2 * TW) % 4 == 0, "flow rows must stay 16-byte aligned");
+    // small radii (winsize 3 / 4: M = 1 / 2): the dead halo rows cannot hold the flow tile; it gets its own region behind the
+    // five planes, and the whole plane (not only rows 0 .. TH-1) is free for the R1 window of phase 3b
+    constexpr bool FSEP = 5 * RPP < TH;
+    constexpr int RPQ = FSEP ? 1 : RPP;
+    static_assert((TH * PW) % 4 == 0 && (2 * TW) % 4 == 0 && SP % 4 == 0, "flow rows must stay 16-byte aligned");
+    const auto flow_at = [](int ly) { return FSEP ? 5 * SP + ly * (2 * TW) : (ly / RPQ) * SP + TH * PW + (ly % RPQ) * (2 * TW); };
     const uint2 te = tl[NSOF_BX];
     NSOF_JOB_TO_SMEM(FbJob, J, jobs + te.x);
     const int tile = (int)te.y;
@@ -979,7 +983,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     int *s_rng = (int *)(smem_raw + 16);     // {min x1, max x1, min y1, max y1} of the tile's R1 gathers
     float *sM = (float *)(smem_raw + 32);
     // R1 window of phase 3b: RH rows of RS floats per plane, in rows 0 .. TH-1 of the plane's M tile
-    constexpr int RS = TW + 8, RH = (TH * PW) / RS;
+    constexpr int RS = TW + 8, RH = ((FSEP ? LH : TH) * PW) / RS;
     static_assert(RS % 4 == 0 && RH >= TH + 2, "R1 window: 16-byte rows, at least one row of slack");
 
     // ---- phase 1
@@ -1041,21 +1045,37 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
     // neighbours leak into small windows, a direct tree does not: relative error <= 4 ulp of sum |v|.  The double
     // version cost 2 x 46 dependent FP64 additions per column and a float<->double conversion per element on
     // the quarter-rate XU pipe, which ncu showed as the busiest pipe of the kernel.)
-    static_assert(M == 7, "the window tree is written for 2M+1 = 15 = 8 + 4 + 2 + 1 rows");
+    // Small radii (M <= 3: winsize 3 .. 7): the 2M+1 rows are added left to right as they stream by.
+    static_assert(M == 7 || M <= 3, "window sums: the 15-row tree or the short direct sum");
     for (int it = NSOF_TID; it < 5 * (PW / 2); it += NSOF_NT) {
         const int c = it / (PW / 2);
         float2 *p = (float2 *)(sM + c * SP) + (it - c * (PW / 2));
-        float2 v[LH], p2[LH], p4[LH], p8[LH];
+        if constexpr (M == 7) {
+            float2 v[LH], p2[LH], p4[LH], p8[LH];
 #pragma unroll
-        for (int j = 0; j < LH; j++) {
-            v[j] = p[j * (PW / 2)];
-            // the column pair is a natural operand of the packed FP32 add (FADD2): half the issue slots of this phase
-            if (j >= 1) p2[j - 1] = nsof_add2(v[j - 1], v[j]);
-            if (j >= 3) p4[j - 3] = nsof_add2(p2[j - 3], p2[j - 1]);
-            if (j >= 7) p8[j - 7] = nsof_add2(p4[j - 7], p4[j - 3]);
-            if (j >= 14) {
-                const int y = j - 14;  // row y of the column pair is dead (already loaded)
-                p[y * (PW / 2)] = nsof_add2(nsof_add2(p8[y], p4[y + 8]), nsof_add2(p2[y + 12], v[j]));
+            for (int j = 0; j < LH; j++) {
+                v[j] = p[j * (PW / 2)];
+                // the column pair is a natural operand of the packed FP32 add (FADD2): half the issue slots of this phase
+                if (j >= 1) p2[j - 1] = nsof_add2(v[j - 1], v[j]);
+                if (j >= 3) p4[j - 3] = nsof_add2(p2[j - 3], p2[j - 1]);
+                if (j >= 7) p8[j - 7] = nsof_add2(p4[j - 7], p4[j - 3]);
+                if (j >= 14) {
+                    const int y = j - 14;  // row y of the column pair is dead (already loaded)
+                    p[y * (PW / 2)] = nsof_add2(nsof_add2(p8[y], p4[y + 8]), nsof_add2(p2[y + 12], v[j]));
+                }
+            }
+        } else {
+            float2 v[LH];
+#pragma unroll
+            for (int j = 0; j < LH; j++) {
+                v[j] = p[j * (PW / 2)];
+                if (j >= 2 * M) {
+                    const int y = j - 2 * M;  // row y is dead (already loaded)
+                    float2 a = v[y];
+#pragma unroll
+                    for (int k = 1; k <= 2 * M; k++) a = nsof_add2(a, v[y + k]);
+                    p[y * (PW / 2)] = a;
+                }
             }
         }
     }
@@ -1075,8 +1095,9 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
 #ifndef FB_BS_PACK3A
 #define FB_BS_PACK3A 1
 #endif
-#if FB_BS_PACK3A
-        static_assert(M == 7 && ML - M == 1 && NV == 5, "the packed window sums are written for columns v[1..18] of 20");
+        float fxv[4], fyv[4];
+        if constexpr (FB_BS_PACK3A && M == 7) {
+        static_assert(M != 7 || (ML - M == 1 && NV == 5), "the packed window sums are written for columns v[1..18] of 20");
 #pragma unroll
         for (int c = 0; c < 5; c++) {
             // window of output q = v[1+q .. 15+q].  v[4..15] is common to the four windows: it arrives as six aligned
@@ -1094,7 +1115,6 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             s[c][2] = common + (t0.w + b12);
             s[c][3] = common + (b12 + t4.z);
         }
-        float fxv[4], fyv[4];
         {
             // 2x2 solve of two pixels per packed instruction (same operations as the scalar form below)
             const float2 sc = make_float2(scale, scale), nsc = make_float2(-scale, -scale), eps = make_float2(1e-3f, 1e-3f);
@@ -1111,7 +1131,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
                 fyv[q] = fy2.x; fyv[q + 1] = fy2.y;
             }
         }
-#else
+        } else {
 #pragma unroll
         for (int c = 0; c < 5; c++) {
             float v[NV * 4];
@@ -1132,7 +1152,6 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             s[c][2] = common + ((v2 + w1) + w2);
             s[c][3] = common + ((w1 + w2) + w3);
         }
-        float fxv[4], fyv[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const float g11 = s[0][q] * scale, g12 = s[1][q] * scale, g22 = s[2][q] * scale;
@@ -1141,14 +1160,14 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             fxv[q] = (g11 * h2 - g12 * h1) * idet;
             fyv[q] = (g22 * h1 - g12 * h2) * idet;
         }
-#endif
+        }
         if (last) {
             float2 *fo = J.flow + (size_t)y * J.fpitch + x;
 #pragma unroll
             for (int q = 0; q < 4; q++)
                 if (x + q < J.w) fo[q] = make_float2(fxv[q], fyv[q]);
         } else {
-            float4 *fo = (float4 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+            float4 *fo = (float4 *)(sM + flow_at(ly) + 2 * lx);
             fo[0] = make_float4(fxv[0], fyv[0], fxv[1], fyv[1]);
             fo[1] = make_float4(fxv[2], fyv[2], fxv[3], fyv[3]);
 #if FB_BS_WINDOW
@@ -1256,8 +1275,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             if (i + 2 * NSOF_NT < TW * TH) r0_pair(i + 2 * NSOF_NT, r0n);
         }
         if (va && vb) {
-            const float2 fa = *(const float2 *)(sM + (lya / RPP) * SP + TH * PW + (lya % RPP) * (2 * TW) + 2 * lxa);
-            const float2 fb = *(const float2 *)(sM + (lyb / RPP) * SP + TH * PW + (lyb % RPP) * (2 * TW) + 2 * lxb);
+            const float2 fa = *(const float2 *)(sM + flow_at(lya) + 2 * lxa);
+            const float2 fb = *(const float2 *)(sM + flow_at(lyb) + 2 * lxb);
             const size_t oa = (size_t)ya * J.pitch + xa, ob = (size_t)yb * J.pitch + xb;
             float2 r0v[5], mm[5];
             if (AHEAD) {
@@ -1277,7 +1296,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
             for (int c = 0; c < 5; c++) { Mout[c * plane + oa] = mm[c].x; Mout[c * plane + ob] = mm[c].y; }
         } else if (va || vb) {
             const int lx = va ? lxa : lxb, ly = va ? lya : lyb, x = va ? xa : xb, y = va ? ya : yb;
-            const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+            const float2 f = *(const float2 *)(sM + flow_at(ly) + 2 * lx);
             const size_t o = (size_t)y * J.pitch + x;
             // a pixel without a partner goes through the SAME packed routine (both halves = this pixel): which pixels
             // lose their partner depends on where the tiles start, and the scalar routine's compiler-chosen FMA
@@ -1306,7 +1325,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(NT, MINB) k_fb_blur_solve_t(const FbJob *NSOF_RES
         const int lx = i % TW, ly = i / TW;
         const int x = tx0 + lx, y = ty0 + ly;
         if (x >= J.w || y >= J.y_hi) continue;
-        const float2 f = *(const float2 *)(sM + (ly / RPP) * SP + TH * PW + (ly % RPP) * (2 * TW) + 2 * lx);
+        const float2 f = *(const float2 *)(sM + flow_at(ly) + 2 * lx);
         const size_t o = (size_t)y * J.pitch + x;
         float r0v[5], mm[5];
 #pragma unroll
@@ -1334,6 +1353,10 @@ static void (*const k_fb_blur_solve_gauss)(const FbJob *, const uint2 *, int, in
 static void (*const FB_BLUR_SOLVE_M7)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<7, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
 static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<7, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
 #define FB_BS7_SMEM (32 + 5 * (FB_BS7_TH + 14) * (FB_BS7_TW + 16) * sizeof(float))
+// radii 1 and 2 (winsize 3 / 4, the two other parameter sets the reference ships): same kernel, flow tile in its own region
+static void (*const FB_BLUR_SOLVE_M1)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<1, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
+static void (*const FB_BLUR_SOLVE_M2)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<2, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
+#define FB_BSM_SMEM(m) (32 + 5 * (FB_BS7_TH + 2 * (m)) * (FB_BS7_TW + 8) * sizeof(float) + FB_BS7_TH * FB_BS7_TW * 8)
 #define FB_BS7S_SMEM (32 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
 
 // ---------------------------------------------------------------------------------------------

@@ -108,6 +108,7 @@ struct nsof_handle {
     cudaEvent_t ev_fork = nullptr;
     std::vector<cudaEvent_t> ev_level;
     bool dbg_big_tiles = false;  // keep the 64x32 blur tile on every level (tests)
+    bool dbg_generic_blur = false;  // winsize 3 .. 5 on the generic blur+solve kernel (nsof_debug_generic_blur)
     bool dbg_um_round1 = false;     // first UpdateMatrices of a level: the round-1 kernel (L2 gathers) instead of the window kernel
     bool dbg_no_r1_window = false;  // blur+solve: gather R1 from L2 in every tile (nsof_debug_r1_window(h, 0))
     int dbg_bs_no_prefetch = -1;    // bit 0 / 1: no L2 prefetch of R0 / R1 rows in blur+solve phase 1; -1: default (see the blur+solve launch in farneback.cu)

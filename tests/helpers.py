@@ -534,3 +534,32 @@ def check_r1_window(eng, hw=(300, 400)):
         eng.lib.check(eng.lib.nsof_debug_r1_window(eng.handle, 1))
         eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, 0))
     return stats
+
+
+def check_small_radius_blur(eng, golden, hw=(300, 420)):
+    """winsize 3 and 4 (the two other parameter sets the reference ships) run the tuned blur+solve kernel's small-radius
+    instantiations by default; `nsof_debug_generic_blur(1)` puts them back on the generic kernel (double running sums).
+    Both paths must meet the cv2 tolerances on the golden cases, agree with each other to 2e-3 px (the sums differ in the
+    last bits; the near-singular systems of these sets amplify that), and the tile counters must show which one ran."""
+    a, b = textured_pair(7, *hw)
+    r1_window_stats(eng)
+    out = {}
+    try:
+        for pname in ("autodriving_txt", "tabletennis"):
+            p = PARAM_SETS[pname]
+            flows = {}
+            for generic in (0, 1):
+                eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, generic))
+                flows[generic] = eng.calcOpticalFlowFarneback(a, b, None, **p)
+                st = r1_window_stats(eng)
+                assert (st[0] + st[1] > 0) == (generic == 0), (pname, generic, st)
+                for case in ("synth_96x128", "synth_75x101"):
+                    got = eng.calcOpticalFlowFarneback(golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"], None, **p)
+                    assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"generic={generic} {case}")
+                r1_window_stats(eng)
+            d = flow_err(flows[0], flows[1])
+            assert d.mean() <= 2e-5 and d.max() <= 2e-3, (pname, d.mean(), d.max())
+            out[pname] = (d.mean(), d.max())
+    finally:
+        eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, 0))
+    return out

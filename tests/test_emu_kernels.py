@@ -388,3 +388,7 @@ def test_pipeline_flag_checks(emu_engine, nsof):
     cfg.FLAG = 3
     with pytest.raises(ValueError):
         pm.SequencePipeline(emu_engine, 1, 2, 600, 600, cfg)
+
+
+def test_emu_small_radius_blur_paths(emu_engine, golden):
+    helpers.check_small_radius_blur(emu_engine, golden, hw=(150, 210))

@@ -235,6 +235,12 @@ def test_realdata_sequence_from_mat(gpu_engine, nsof, golden, roi_state):
             assert helpers.pixel_accuracy(motion[k, 0] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
 
 
+def test_small_radius_blur_paths(gpu_engine, golden):
+    """winsize 3 / 4 on the tuned blur+solve kernel (default) and on the generic one: cv2 goldens, mutual agreement,
+    tile counters (helpers.check_small_radius_blur)."""
+    print(helpers.check_small_radius_blur(gpu_engine, golden, hw=(540, 720)))
+
+
 def test_sequence_pipeline_separate_regions(gpu_engine, nsof, golden):
     """FLAG 1 (process_separate_regions, the configuration data/uavnew2/Parameters.txt names) through the device-resident
     SequencePipeline: the 13 kept uavnew2 pairs as 13 two-frame clips, array states given (slice OFFSET + i, the scripts'
