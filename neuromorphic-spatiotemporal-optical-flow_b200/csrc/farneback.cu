@@ -428,6 +428,8 @@ static int configure_smem(nsof_handle *h)
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_BLUR_SOLVE_M2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_BSM_SMEM(2)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(1)));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0_N1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0, 1)));
+    NSOF_CUDA_TRY(cudaFuncSetAttribute(FB_PYR_POLYEXP_M0_N10, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_pp_smem(0, 10)));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_pyr_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
     NSOF_CUDA_TRY(cudaFuncSetAttribute(k_fb_polyexp, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MAX_DYN_SMEM));
     h->smem_configured = true;
@@ -640,7 +642,8 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
     for (auto *v : {&X.ps_sw, &X.ps_sh}) v->assign(LV, 0);
     X.sum_tiles_bs.assign(LV, 0);
     X.n_init.assign(LV, 0);
-    const bool may_fuse = !h->dbg_no_fuse && params->poly_n == FB_PP_N;
+    // fused pyramid + PolyExp: poly_n 5 on the level-0 and exact-2x shapes, poly_n 1 / 10 (the other shipped sets) on level 0
+    const bool may_fuse = !h->dbg_no_fuse && (params->poly_n == FB_PP_N || params->poly_n == 1 || params->poly_n == 10);
     const int m = params->winsize / 2;
     X.m = m;
     X.BTW = X.BTH = 0;
@@ -677,6 +680,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
             else J.resize_mode = 2;
             J.sx = (double)J.sw / J.w; J.sy = (double)J.sh / J.h;
             J.fast = (may_fuse && X.ksize[k] == 3 && J.resize_mode < 2) ? J.resize_mode + 1 : 0;
+            if (J.fast == 2 && params->poly_n != FB_PP_N) J.fast = 0;
             if (params->flags & NSOF_FB_SRC_F32) J.fast = 0;  // float32 frames: the direct pyramid kernel (typed loads)
             // row window
             J.y_lo = 0; J.y_hi = J.h; J.gy_lo = 0; J.gy_hi = J.h; J.guard = nullptr;
@@ -827,8 +831,9 @@ static int fb_launch_pyramid(nsof_handle *h, int k, cudaStream_t stream, int var
     const auto lp = [&](int l) { return X.dtiles + X.list_off[(size_t)kk * FB_NLISTS + l]; };
     (void)na;
     if (ln(FB_L_PP0))
-        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 1] + 40 * X.path_N[3 * kk + 1], FB_PYR_POLYEXP_M0,
-                     ln(FB_L_PP0), 1, 1, 256, fb_pp_smem(0), stream, jobs, lp(FB_L_PP0), gk, pc);
+        NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 1] + 40 * X.path_N[3 * kk + 1],
+                     (pc.n == 1 ? FB_PYR_POLYEXP_M0_N1 : pc.n == 10 ? FB_PYR_POLYEXP_M0_N10 : FB_PYR_POLYEXP_M0),
+                     ln(FB_L_PP0), 1, 1, 256, fb_pp_smem(0, pc.n), stream, jobs, lp(FB_L_PP0), gk, pc);
     if (ln(FB_L_PP1))
         NSOF_KLAUNCH(h, NSOF_K_PYR_POLYEXP, 2 * X.path_N0[3 * kk + 2] + 40 * X.path_N[3 * kk + 2], FB_PYR_POLYEXP_M1,
                      ln(FB_L_PP1), 1, 1, 256, fb_pp_smem(1), stream, jobs, lp(FB_L_PP1), gk, pc);

@@ -1858,9 +1858,13 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
 #define FB_PP_N 5
 static void (*const FB_PYR_POLYEXP_M0)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, FB_PP_N, FB_PP_TW, FB_PP_TH>;
 static void (*const FB_PYR_POLYEXP_M1)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<1, FB_PP_N, FB_PP_TW, FB_PP_TH>;
-static inline size_t fb_pp_smem(int mode)
+// level 0 of the two other parameter sets the reference ships (poly_n 1 and 10; their pyr_scale 0.6 leaves only level 0
+// on a fused shape)
+static void (*const FB_PYR_POLYEXP_M0_N1)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, 1, FB_PP_TW, FB_PP_TH>;
+static void (*const FB_PYR_POLYEXP_M0_N10)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, 10, FB_PP_TW, FB_PP_TH>;
+static inline size_t fb_pp_smem(int mode, int n = FB_PP_N)
 {
-    const int IW = FB_PP_TW + 2 * FB_PP_N, IH = FB_PP_TH + 2 * FB_PP_N, IP = (IW + 3) & ~3;
+    const int IW = FB_PP_TW + 2 * n, IH = FB_PP_TH + 2 * n, IP = (IW + 3) & ~3;
     const int SWN = (mode ? 2 * IW : IW) + 2, SHN = (mode ? 2 * IH : IH) + 2, SW = (SWN + 3) & ~3, RP = (SWN + 32 + 15) & ~15;
 #if FB_PP_PACKED
     const int si_bytes = (IH - FB_PP_TH / 2) * IP * 8;

@@ -563,3 +563,30 @@ def check_small_radius_blur(eng, golden, hw=(300, 420)):
     finally:
         eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, 0))
     return out
+
+
+def check_fused_pyramid_all_n(eng, hw=(230, 310), exact=False):
+    """Level 0 of every shipped parameter set (poly_n 5, 10, 1) runs the fused pyramid + PolyExp kernel; its operations are
+    those of the unfused pair of kernels in the same order: flows bit-identical with `nsof_debug_fuse(0)` on the emulator
+    build (exact=True); on the device the compiler contracts the two kernels' multiply-adds differently (6e-6 px on the
+    grasp set), so there the two must agree to mean 2e-5 / max 2e-3 px.  The profile must name the kernel that ran."""
+    a, b = textured_pair(9, *hw)
+    try:
+        for pname in ("grasp", "autodriving_txt", "tabletennis"):
+            p = PARAM_SETS[pname]
+            eng.lib.check(eng.lib.nsof_debug_fuse(eng.handle, 1))
+            eng.profile(True)
+            f1 = eng.calcOpticalFlowFarneback(a, b, None, **p)
+            eng.profile(False)
+            assert "fb_pyr_polyexp.L0" in eng.profile_read(), pname
+            eng.lib.check(eng.lib.nsof_debug_fuse(eng.handle, 0))
+            eng.profile(True)
+            f0 = eng.calcOpticalFlowFarneback(a, b, None, **p)
+            eng.profile(False)
+            assert "fb_pyr_polyexp.L0" not in eng.profile_read(), pname
+            d = flow_err(f1, f0)
+            assert d.mean() <= 2e-5 and d.max() <= 2e-3, (pname, d.mean(), d.max())
+            if exact:
+                assert np.array_equal(f1, f0), (pname, np.abs(f1 - f0).max())
+    finally:
+        eng.lib.check(eng.lib.nsof_debug_fuse(eng.handle, 1))

@@ -392,3 +392,7 @@ def test_pipeline_flag_checks(emu_engine, nsof):
 
 def test_emu_small_radius_blur_paths(emu_engine, golden):
     helpers.check_small_radius_blur(emu_engine, golden, hw=(150, 210))
+
+
+def test_emu_fused_pyramid_all_poly_n(emu_engine):
+    helpers.check_fused_pyramid_all_n(emu_engine, exact=True)

@@ -235,6 +235,12 @@ def test_realdata_sequence_from_mat(gpu_engine, nsof, golden, roi_state):
             assert helpers.pixel_accuracy(motion[k, 0] > 0, rd.unpack(f"gt__{i}")) == rd.g["acc1"][i]
 
 
+def test_fused_pyramid_all_poly_n(gpu_engine):
+    """poly_n 1 and 10 (tabletennis / uav / autodriving Parameters.txt) take the fused level-0 kernel too; same operations
+    as the unfused kernels (helpers.check_fused_pyramid_all_n: bit-identical on the emulator, last-bit FMA differences here)."""
+    helpers.check_fused_pyramid_all_n(gpu_engine, hw=(540, 720))
+
+
 def test_small_radius_blur_paths(gpu_engine, golden):
     """winsize 3 / 4 on the tuned blur+solve kernel (default) and on the generic one: cv2 goldens, mutual agreement,
     tile counters (helpers.check_small_radius_blur)."""
