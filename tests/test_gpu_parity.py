@@ -959,19 +959,20 @@ def test_event_scheme2_vs_reference(gpu_engine, golden):
             assert np.abs(got - want).max() <= 2e-5, (name, np.abs(got - want).max())
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_tiled_lockstep_ranks_bit_identical_on_one_gpu(gpu_engine, nsof, world):
+@pytest.mark.parametrize("world,pname", [(2, "grasp"), (3, "grasp"), (2, "autodriving_txt"), (2, "tabletennis")])
+def test_tiled_lockstep_ranks_bit_identical_on_one_gpu(gpu_engine, nsof, world, pname):
     """Row tiling (configs[4]) on ONE GPU: the ranks are handles of this process stepped in lockstep, stage by stage,
     with the halo rows copied between their workspaces by plain device copies (no waiting kernels, no NCCL).  Every
     band must equal the untiled flow BIT FOR BIT: the per-pixel arithmetic may not depend on where the tiles start
-    (an unpaired pixel of the packed UpdateMatrices once took the scalar routine and differed in the last bit)."""
+    (an unpaired pixel of the packed UpdateMatrices once took the scalar routine and differed in the last bit).  Also for
+    the two other shipped parameter sets (small-radius blur+solve instantiations, fused level 0 at poly_n 10 / 1)."""
     import importlib
 
     import torch
     tiled = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.tiled")
     eng_mod = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.engine")
     syn = importlib.import_module("neuromorphic-spatiotemporal-optical-flow_b200.synthetic")
-    P = nsof.FARNEBACK_PARAMS
+    P = helpers.PARAM_SETS[pname]
     H, W = 1080, 1000
     dev = torch.device("cuda:0")
     frames = syn.make_clip(4321, H, W, 3, dev, velocity=(5.0, -4.0))

@@ -28,7 +28,8 @@ def _pairs():
     return [helpers.textured_pair(7, H, W, dx=2.5, dy=-3.0), helpers.textured_pair(8, H, W, dx=-1.0, dy=4.5)]
 
 
-def _worker(rank, world, port, out_dir, halo, overlap=True):
+def _worker(rank, world, port, out_dir, halo, overlap=True, params=None):
+    params = params or PARAMS
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
                       MASTER_PORT=str(port))
     nsof = importlib.import_module("nsof_b200")
@@ -43,7 +44,7 @@ def _worker(rank, world, port, out_dir, halo, overlap=True):
     tf = tiled.TiledFarneback(eng, rank, world, halo_r1=halo, overlap=overlap)
     status = "ok"
     try:
-        tf.run(crops, **PARAMS)
+        tf.run(crops, **params)
     except RuntimeError as e:
         status = "guard" if "halo" in str(e) else "error: " + str(e)
     lo, hi = tiled.band_rows(H, rank, world)
@@ -73,6 +74,23 @@ def test_tiled_ranks_reproduce_the_untiled_flow(tmp_path, emu_engine, world):
         # levels with a band of >= 4 halos ran as edges -> exchange -> interior (nsof_fb_tiled_stage_rows), the rest whole
         assert int(z["split"]) == (3 if world == 2 else 2)
     assert covered == H
+
+
+@pytest.mark.parametrize("pname", ["autodriving_txt", "tabletennis"])
+def test_tiled_other_parameter_sets(tmp_path, emu_engine, pname):
+    """The two other shipped parameter sets (window radius 1 / 2 on the tuned blur+solve kernel's small-radius
+    instantiations, poly_n 10 / 1 with the fused level-0 pyramid, bilinear 0.6 pyramid above it) row-tiled over 2 ranks:
+    bands bit-identical to the untiled flow."""
+    params = helpers.PARAM_SETS[pname]
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), 12, True, params), nprocs=2, join=True)
+    want = [emu_engine.calcOpticalFlowFarneback(a, b, None, **params) for a, b in _pairs()]
+    for r in range(2):
+        z = np.load(tmp_path / f"r{r}.npz")
+        assert str(z["status"]) == "ok", str(z["status"])
+        lo, hi = int(z["lo"]), int(z["hi"])
+        for i, wnt in enumerate(want):
+            got = z[f"flow{i}"]
+            assert np.array_equal(got[lo:hi], wnt[lo:hi]), (pname, r, i, np.abs(got[lo:hi] - wnt[lo:hi]).max())
 
 
 def test_tiled_guard_trips_when_the_halo_is_too_small(tmp_path):
