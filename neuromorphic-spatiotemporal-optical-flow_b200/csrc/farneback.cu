@@ -732,7 +732,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
                 X.ps_sw[kk] = std::max(X.ps_sw[kk], (int)ceil(FB_PS_TW * J.sx) + 2 * (X.ksize[k] / 2) + 4);
                 X.ps_sh[kk] = std::max(X.ps_sh[kk], (int)ceil(FB_PS_TH * J.sy) + 2 * (X.ksize[k] / 2) + 4);
             }
-            if (X.bs_m7) X.sum_tiles_bs[kk] += (long long)((J.w + X.BTW - 1) / X.BTW) * ((rows + X.BTH - 1) / X.BTH);
+            if (X.bs_m7 || X.bs_msmall) X.sum_tiles_bs[kk] += (long long)((J.w + X.BTW - 1) / X.BTW) * ((rows + X.BTH - 1) / X.BTH);
             (void)irows;
         }
     }
@@ -748,7 +748,7 @@ static int fb_prepare(nsof_handle *h, const nsof_crop_desc *items, int n, const 
         const int k = kk % max_scales;
         // fewer 64x32 tiles than two waves of the 148 SMs (3 CTAs each): the level is latency-bound, take the 32x16
         // tile (4x the CTAs, each a quarter of the serial work)
-        X.bs_small[kk] = X.bs_m7 && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles;
+        X.bs_small[kk] = (X.bs_m7 || X.bs_msmall) && X.sum_tiles_bs[kk] < 2 * 148 * 3 && !h->dbg_big_tiles;
         // two CTAs per SM; larger windows (extreme resize ratios) take the direct pyramid kernel
         X.pyr_sep[kk] = fb_ps_smem(X.ksize[k] / 2, X.ps_sw[kk], X.ps_sh[kk]) <= 100 * 1024 && !(params->flags & NSOF_FB_SRC_F32);
         const FbJob *jobs = (const FbJob *)(hs + X.job_off[kk]);
@@ -916,6 +916,11 @@ static int fb_launch_blur(nsof_handle *h, int k, int it, int iters, cudaStream_t
     else if (X.bs_m7)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M7, n_bs, 1, 1,
                      FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);
+    else if (X.bs_msmall && X.bs_small[kk])
+        NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk,
+                     (X.bs_msmall == 1 ? FB_BLUR_SOLVE_M1S : FB_BLUR_SOLVE_M2S), n_bs, 1, 1, FB_BS7S_NT,
+                     (X.bs_msmall == 1 ? FB_BSMS_SMEM(1) : FB_BSMS_SMEM(2)), stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags,
+                     bs_stats);
     else if (X.bs_msmall == 1)
         NSOF_KLAUNCH(h, last ? NSOF_K_BLUR_FLOW : NSOF_K_BLUR_UM, (last ? 28 : 80) * Nk, FB_BLUR_SOLVE_M1, n_bs, 1, 1,
                      FB_BS7_NT, X.bs_smem, stream, jobs, tl_bs, X.bscale, (it & 1) == 0, bs_flags, bs_stats);

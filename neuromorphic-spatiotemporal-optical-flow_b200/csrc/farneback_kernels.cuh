@@ -1357,6 +1357,10 @@ static void (*const FB_BLUR_SOLVE_M7S)(const FbJob *, const uint2 *, float, int,
 static void (*const FB_BLUR_SOLVE_M1)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<1, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
 static void (*const FB_BLUR_SOLVE_M2)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<2, FB_BS7_TW, FB_BS7_TH, FB_BS7_NT, FB_BS7_MINB>;
 #define FB_BSM_SMEM(m) (32 + 5 * (FB_BS7_TH + 2 * (m)) * (FB_BS7_TW + 8) * sizeof(float) + FB_BS7_TH * FB_BS7_TW * 8)
+// ... and their small tiles for latency-bound levels (a 161 x 161 uav frame is 18 tiles of 64 x 32)
+static void (*const FB_BLUR_SOLVE_M1S)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<1, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
+static void (*const FB_BLUR_SOLVE_M2S)(const FbJob *, const uint2 *, float, int, int, unsigned *) = k_fb_blur_solve_t<2, FB_BS7S_TW, FB_BS7S_TH, FB_BS7S_NT, 6>;
+#define FB_BSMS_SMEM(m) (32 + 5 * (FB_BS7S_TH + 2 * (m)) * (FB_BS7S_TW + 8) * sizeof(float) + FB_BS7S_TH * FB_BS7S_TW * 8)
 #define FB_BS7S_SMEM (32 + 5 * (FB_BS7S_TH + 14) * (FB_BS7S_TW + 16) * sizeof(float))
 
 // ---------------------------------------------------------------------------------------------

@@ -548,20 +548,23 @@ def check_small_radius_blur(eng, golden, hw=(300, 420)):
         for pname in ("autodriving_txt", "tabletennis"):
             p = PARAM_SETS[pname]
             flows = {}
-            for generic in (0, 1):
-                eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, generic))
+            for generic in (0, 1, 2):   # 0: tuned kernel, small tiles where the level is small; 2: its 64 x 32 tiles everywhere
+                eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, generic == 1))
+                eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, generic == 2))
                 flows[generic] = eng.calcOpticalFlowFarneback(a, b, None, **p)
                 st = r1_window_stats(eng)
-                assert (st[0] + st[1] > 0) == (generic == 0), (pname, generic, st)
+                assert (st[0] + st[1] > 0) == (generic != 1), (pname, generic, st)
                 for case in ("synth_96x128", "synth_75x101"):
                     got = eng.calcOpticalFlowFarneback(golden.fb[f"{case}__prev"], golden.fb[f"{case}__next"], None, **p)
                     assert_flow_close(got, golden.fb[f"{case}__{pname}"], pname, f"generic={generic} {case}")
                 r1_window_stats(eng)
             d = flow_err(flows[0], flows[1])
             assert d.mean() <= 2e-5 and d.max() <= 2e-3, (pname, d.mean(), d.max())
+            assert np.array_equal(flows[0], flows[2]), pname   # the tile shape does not change a bit
             out[pname] = (d.mean(), d.max())
     finally:
         eng.lib.check(eng.lib.nsof_debug_generic_blur(eng.handle, 0))
+        eng.lib.check(eng.lib.nsof_debug_big_tiles(eng.handle, 0))
     return out
 
 
