@@ -503,14 +503,14 @@ def r1_window_stats(eng):
     return int(out[0]), int(out[1]), int(out[2]), int(out[3])   # blur+solve (window, L2), first UpdateMatrices (window, L2)
 
 
-def check_r1_window(eng, hw=(300, 400)):
+def check_r1_window(eng, hw=(300, 400), pname="grasp"):
     """The tuned blur+solve kernel gathers R1 from a shared-memory window that follows the tile's flow, or from L2 when
     the flow varies too much inside a tile: both paths load the same values, so the flow must be BIT-IDENTICAL with the
     window switched off -- for a uniform small shift, a uniform 20 px shift (window far from the tile), a zoom and a
     shear (tiles of both kinds).  The first UpdateMatrices of a level takes its own window kernel (its flow is the upsampled
     coarser flow) or, with the switch off, the round-1 kernel.  -> {(kind, big tiles): (blur+solve window tiles, L2 tiles,
     first-UpdateMatrices window tiles, L2 tiles)} of the window-on runs."""
-    p = PARAM_SETS["grasp"]
+    p = PARAM_SETS[pname]   # grasp: the M = 7 kernel; autodriving_txt / tabletennis: its small-radius instantiations
     r1_window_stats(eng)   # first call: counting on
     stats = {}
     try:

@@ -370,10 +370,13 @@ def test_float32_frames_vs_cv2_golden(emu_engine, golden):
     assert mixed.shape == got.shape
 
 
-def test_emu_r1_window_bit_identical(emu_engine):
-    """Blur+solve with the R1 window in shared memory (default) against the L2 gathers, both tile shapes."""
-    stats = helpers.check_r1_window(emu_engine, hw=(200, 280))
-    assert stats["shift3", 1][1] == 0     # a uniform 3 px shift never leaves the window
+@pytest.mark.parametrize("pname", ["grasp", "autodriving_txt", "tabletennis"])
+def test_emu_r1_window_bit_identical(emu_engine, pname):
+    """Blur+solve with the R1 window in shared memory (default) against the L2 gathers, both tile shapes, all three
+    window radii the shipped parameter sets use."""
+    stats = helpers.check_r1_window(emu_engine, hw=(200, 280), pname=pname)
+    if pname == "grasp":
+        assert stats["shift3", 1][1] == 0     # a uniform 3 px shift never leaves the window
 
 
 def test_pipeline_flag_checks(emu_engine, nsof):

@@ -172,6 +172,8 @@ def test_r1_window_bit_identical(gpu_engine):
     stats = helpers.check_r1_window(gpu_engine, hw=(540, 720))
     print("R1 window tiles (window, L2):", stats)
     assert stats["shift3", 1][1] == 0
+    for pname in ("autodriving_txt", "tabletennis"):   # the small-radius instantiations of the kernel
+        helpers.check_r1_window(gpu_engine, hw=(540, 720), pname=pname)
 
 
 @pytest.mark.parametrize("ds,padding", [("uav", 30), ("uavnew2", 60), ("tabletennis", 20)])
