@@ -1392,7 +1392,8 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
                                                          const float *NSOF_RESTRICT gk, PolyConst pc)
 {
     constexpr int IW = TW + 2 * N, IH = TH + 2 * N, IP = (IW + 3) & ~3;
-    constexpr int SWN = (MODE ? 2 * IW : IW) + 2, SHN = (MODE ? 2 * IH : IH) + 2;  // source window actually needed
+    // MODE 2: I comes from HBM (written by the generic pyramid kernel): no source window at all
+    constexpr int SWN = MODE == 2 ? 4 : (MODE ? 2 * IW : IW) + 2, SHN = MODE == 2 ? 4 : (MODE ? 2 * IH : IH) + 2;  // source window
     constexpr int SW = (SWN + 3) & ~3;                                              // pitch of the float window
     constexpr int RP = (SWN + 32 + 15) & ~15;                                       // pitch of the raw uint8 window
     constexpr int A_BYTES = (3 * TH * IP * 4 > SHN * SW * 4 ? 3 * TH * IP * 4 : SHN * SW * 4);  // S (float) | sr
@@ -1452,6 +1453,16 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
     const int lx_lo = nsof_imax(0, N - tx0), lx_hi = nsof_imin(IW, J.w - (tx0 - N));
     const int ly_lo = nsof_imax(0, N - ty0), ly_hi = nsof_imin(IH, J.h - (ty0 - N));
     const int cx_lo = tx0 - N + lx_lo, cy_lo = ty0 - N + ly_lo;
+    if constexpr (MODE == 2) {
+        // ---- A/B replaced: the in-image part of the I tile + halo straight from the level image in HBM
+        const float *Iin = J.I + (size_t)img * J.pitch * J.h;
+        const int wn = lx_hi - lx_lo, hn = ly_hi - ly_lo;
+        for (int i = NSOF_TID; i < wn * hn; i += NSOF_NT) {
+            const int ry = i / wn, rx = i - ry * wn;
+            FB_SI_ST(ly_lo + ry, lx_lo + rx, NSOF_LDG(Iin + (size_t)(cy_lo + ry) * J.pitch + cx_lo + rx));
+        }
+        (void)src; (void)sp; (void)bar; (void)sS; (void)sraw; (void)gk;
+    } else {
     // source window: shared (sy, sx) <-> source (Ylo + sy, Xlo + sx), BORDER_REFLECT_101 outside the source
     const int Xlo = (MODE ? 2 * cx_lo : cx_lo) - 1, Ylo = (MODE ? 2 * cy_lo : cy_lo) - 1;
 
@@ -1571,6 +1582,7 @@ NSOF_GLOBAL NSOF_LAUNCH_BOUNDS(256, FB_PP_MINB) k_fb_pyr_polyexp_t(const FbJob *
             }
         }
     }
+    }  // MODE != 2
     NSOF_SYNC();
     if (lx_lo > 0 || lx_hi < IW || ly_lo > 0 || ly_hi < IH) {  // replicate border of the level image
         for (int ly = warp; ly < IH; ly += nw) {
@@ -1866,10 +1878,15 @@ static void (*const FB_PYR_POLYEXP_M1)(const FbJob *, const uint2 *, const float
 // on a fused shape)
 static void (*const FB_PYR_POLYEXP_M0_N1)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, 1, FB_PP_TW, FB_PP_TH>;
 static void (*const FB_PYR_POLYEXP_M0_N10)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<0, 10, FB_PP_TW, FB_PP_TH>;
+// MODE 2: PolyExp alone with the same moment passes, I read from HBM -- the levels the generic pyramid kernel serves
+// (ksize 9 / 19 of the coarse levels, bilinear ratios of pyr_scale 0.6) instead of the generic k_fb_polyexp
+static void (*const FB_POLYEXP_T_N1)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<2, 1, FB_PP_TW, FB_PP_TH>;
+static void (*const FB_POLYEXP_T_N10)(const FbJob *, const uint2 *, const float *, PolyConst) = k_fb_pyr_polyexp_t<2, 10, FB_PP_TW, FB_PP_TH>;
 static inline size_t fb_pp_smem(int mode, int n = FB_PP_N)
 {
     const int IW = FB_PP_TW + 2 * n, IH = FB_PP_TH + 2 * n, IP = (IW + 3) & ~3;
-    const int SWN = (mode ? 2 * IW : IW) + 2, SHN = (mode ? 2 * IH : IH) + 2, SW = (SWN + 3) & ~3, RP = (SWN + 32 + 15) & ~15;
+    const int SWN = mode == 2 ? 4 : (mode ? 2 * IW : IW) + 2, SHN = mode == 2 ? 4 : (mode ? 2 * IH : IH) + 2, SW = (SWN + 3) & ~3,
+              RP = (SWN + 32 + 15) & ~15;
 #if FB_PP_PACKED
     const int si_bytes = (IH - FB_PP_TH / 2) * IP * 8;
 #else

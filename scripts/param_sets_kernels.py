@@ -26,7 +26,7 @@ for name, p in (("autodriving_txt", dict(pyr_scale=0.6, levels=3, winsize=3, ite
     st = eng.profile_read()
     tot = sum(s["ms"] for s in st.values())
     print(f"{name}: {tot / 2:.3f} ms per step of {pf.n_pairs} pairs (serialised kernel sum)")
-    for k, s in sorted(st.items(), key=lambda kv: -kv[1]["ms"])[:12]:
+    for k, s in sorted(st.items(), key=lambda kv: -kv[1]["ms"])[:int(os.environ.get("NSOF_ROWS", "12"))]:
         gb = s["algorithmic_bytes"] / (s["ms"] * 1e-3) / 1e9 if s["ms"] > 0 else 0
         print(f"    {k:22s} {s['ms'] / 2:7.3f} ms {s['ms'] / tot * 100:5.1f} %  {gb:7.0f} GB/s algorithmic")
     del pf
