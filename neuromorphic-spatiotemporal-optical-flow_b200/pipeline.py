@@ -110,7 +110,7 @@ class SequencePipeline:
         self.rects_pinned = torch.zeros((self.n_pairs, _lib.NSOF_MAX_RECTS, 4), dtype=i32).pin_memory()
         self.rects_host = self.rects_pinned[:, 0, :]          # FLAG 2: one merged rectangle per pair
         # FLAG 1: up to MAX_REGIONS regions per pair get a descriptor each (the ROI kernel stores up to NSOF_MAX_RECTS)
-        self.max_regions = 16 if self.sep else 1
+        self.max_regions = 32 if self.sep else 1
         self.n_rects_host = torch.zeros((self.n_pairs,), dtype=i32).pin_memory()
         # output: full flow frames (zero outside each ROI, the reference's paste semantics) or, for the host path,
         # the ROI crops packed back to back (outside its rectangle a pair's flow is zero by definition)
